@@ -1,0 +1,177 @@
+/*
+ * clipnerf_b200 -- C ABI of the B200 (sm_100a) CLIP-NeRF volumetric render path.
+ *
+ * This is the drop-in boundary of the repo: every entry point replaces one piece of
+ * the reference's TensorFlow hot path (TWeber132/thesis-clip-nerf; citations are
+ * file:line in that repository).  The reference has no FFI of its own (it is pure
+ * TensorFlow/Keras), so these are the functions a maintainer would bind from the
+ * reference's Python modules (see INTEGRATION.md for the ctypes stubs).
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes, no C++ / torch types.
+ *   - every pointer is a DEVICE pointer unless the name ends in _host.
+ *   - the caller allocates every output and workspace; the library owns no device
+ *     memory and keeps no global mutable state except a thread-local error string.
+ *   - work is enqueued on `stream` (a cudaStream_t passed as void*); nothing here
+ *     synchronises with the host.
+ *   - return value: 0 = ok, < 0 = argument / shape / alignment error
+ *     (text via cn_last_error()), > 0 = a cudaError_t.
+ *   - there is no CPU fallback.
+ *
+ * Row order ("sample-view rows"): the per-view MLP stage works on rows
+ *   row = ((b * nv + v) * nr + r) * S + i      (b-major "(b nv) nr np", layers.py:366)
+ * and the fusion stage on rows  q = (b * nr + r) * S + i.  Rows are grouped in
+ * tiles of CN_TILE_ROWS; nr * S must be a multiple of CN_TILE_ROWS.
+ *
+ * bf16 tile images: a [128 rows x 64 cols] bf16 "slab" is 16 KiB, row r at byte
+ * r*128, the 16-byte chunk c of a row stored at chunk position c ^ (r & 7)
+ * (the 128-byte swizzle tcgen05 shared-memory descriptors expect).  An activation
+ * tile [128 x 128] is 2 slabs (32 KiB), an MLP-input tile [128 x 384] is 6 slabs.
+ */
+#ifndef CLIPNERF_B200_H
+#define CLIPNERF_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CN_ABI_VERSION 1
+#define CN_TILE_ROWS 128
+#define CN_HIDDEN 128
+#define CN_FEAT_C 256          /* combined_features channels (model_v0.py:60)            */
+#define CN_IN_DIM 379          /* 60 + 60 + 3 + 256 (layers.py:362)                      */
+#define CN_IN_PAD 384          /* K of the first Dense, padded to a multiple of 64       */
+#define CN_SLAB_BYTES 16384
+#define CN_ACT_TILE_BYTES 32768
+#define CN_X_TILE_BYTES 98304
+
+/* number of fp32 parameters of one MVResNetMLPNeRFEmbedding(6,128) + RenderReadout(4)
+ * in the flat layout described at cn_pack_weights(). */
+#define CN_EMB_PARAMS 246784
+#define CN_READOUT_PARAMS 516
+#define CN_NET_PARAMS (CN_EMB_PARAMS + CN_READOUT_PARAMS)
+
+/* bytes of the packed (bf16 operand images + fp32 bias tables) form of one net */
+#define CN_PACKED_BYTES (2 * 491520 + 16384)
+
+int cn_abi_version(void);
+const char *cn_last_error(void);
+
+/* Source views of one batch of scenes: the 5-tuple of MVNeRFDataGenerator.get_input
+ * (src/lib/data_generator/mvnerf.py:28-43) plus combined_features (model_v0.py:60). */
+typedef struct CnScene {
+  const float *images;     /* [b, nv, H, W, 3]  in [0,1]                  */
+  const float *features;   /* [b, nv, H, W, 256]                          */
+  const float *intrinsics; /* [b, nv, 4, 4]                               */
+  const float *extr_inv;   /* [b, nv, 4, 4]  world -> camera              */
+  int32_t b, nv, H, W;
+} CnScene;
+
+/* ---- sampling ------------------------------------------------------------------ */
+
+/* sample_along_ray (nerf_utils.py:49-61): z[n, S] = fp32(near + i*step) + u[n, S]*step */
+int cn_sample_coarse(const float *u, float *z, int64_t n_rays, int32_t S, double near_, double far_,
+                     void *stream);
+
+/* sample_pdf (nerf_utils.py:143-176) + concat + sort (model_v0.py:150-156), S = 64.
+ *   z_c, w_c, u : [n, 64]   ->  z_fine [n, 128] ascending (stable),
+ *   perm  [n,128] u8 : source index of each sorted value (0..63 coarse, 64..127 new),
+ *   above [n, 64] u8 : inverse-CDF bin index of each draw (1..63).                      */
+int cn_sample_pdf_fwd(const float *z_c, const float *w_c, const float *u, int64_t n_rays,
+                      float *z_fine, uint8_t *perm, uint8_t *above, void *stream);
+/* gradient of the above w.r.t. the coarse weights (no stop_gradient in the reference,
+ * model_v0.py:153-158):  dz_fine [n,128] -> dw_c [n,64] (accumulated, +=).              */
+int cn_sample_pdf_bwd(const float *z_c, const float *w_c, const float *u, const uint8_t *perm,
+                      const float *dz_fine, int64_t n_rays, float *dw_c, void *stream);
+
+/* ---- projection + bilinear gather + positional encoding ------------------------- */
+
+/* compute_pixel_in_image_mv + get_projection_features_mv +
+ * world_to_camera_direction_vector_mv + position_encoding + the concat of
+ * layers.py:362 (nerf_utils.py:64-126,277-285): writes the MLP input rows as bf16
+ * tile images X [b*nv*nr*S/128 tiles][6 slabs].  Column order inside X:
+ * [feat 0..255 | posenc(p_cam) 60 | posenc(d_cam) 60 | 2*img-1 (3) | 0 (5)].          */
+int cn_project_gather_fwd(const CnScene *scene, const float *ray_o, const float *ray_d,
+                          const float *z, int32_t nr, int32_t S, void *x_tiles, void *stream);
+/* fp32 debug / parity view of the same computation: pix [b,nv,nr,S,2],
+ * corner (x0,y0) int32 [b,nv,nr,S,2], gathered [b,nv,nr,S,259] in reference order.    */
+int cn_project_gather_debug(const CnScene *scene, const float *ray_o, const float *ray_d,
+                            const float *z, int32_t nr, int32_t S, float *pix, int32_t *corner,
+                            float *gathered, void *stream);
+/* backward: dX tile images -> scatter-add into d_features [b,nv,H,W,256] (nullable)
+ * and dz [b,nr,S] (nullable, +=) through bilinear coordinates and posenc(p_cam).       */
+int cn_project_gather_bwd(const CnScene *scene, const float *ray_o, const float *ray_d,
+                          const float *z, int32_t nr, int32_t S, const void *dx_tiles,
+                          float *d_features, float *dz, void *stream);
+
+/* ---- compositing --------------------------------------------------------------- */
+
+/* volumetric_render (model_v0.py:89-100): z [n,S], rgbs [n,S,4] = (r,g,b,sigma)
+ * -> rgb [n,3], depth [n], weights [n,S].  S in {64,128}.                              */
+int cn_composite_fwd(const float *z, const float *rgbs, int64_t n_rays, int32_t S, float *rgb,
+                     float *depth, float *weights, void *stream);
+/* backward; transmittance is recomputed.  d_depth, d_weights, dz nullable.
+ * d_y [n,S,4] receives the gradient w.r.t. the readout pre-activations
+ * (sigmoid / softplus derivatives folded in, layers.py:395-396).                       */
+int cn_composite_bwd(const float *z, const float *rgbs, int64_t n_rays, int32_t S,
+                     const float *d_rgb, const float *d_depth, const float *d_weights,
+                     float *d_y, float *dz, void *stream);
+
+/* ---- MLP (tcgen05 / TMEM) ------------------------------------------------------- */
+
+/* Flat fp32 parameter layout of one net (Keras variable order, kernel[in][out]):
+ *   layer_0.kernel [379,128], layer_0.bias [128],
+ *   for blk in feature_blocks[0..2], fusion_blocks[0..2]:
+ *       layer_0.kernel [128,128], layer_0.bias, layer_1.kernel [128,128], layer_1.bias
+ *   output_layer.kernel [128,4], output_layer.bias [4]          (CN_NET_PARAMS floats)
+ * cn_pack_weights writes the bf16 operand images + bias tables (CN_PACKED_BYTES).      */
+int cn_pack_weights(const float *params, void *packed, void *stream);
+
+/* per-view stage: Dense 379->128 + 3 ResNet blocks (layers.py:363-365).
+ *   x_tiles -> h3_tiles [n_tiles] (bf16 activation tiles).
+ *   acts (nullable): saved block operands for the backward,
+ *   [n_tiles][3 blocks][2] activation tiles (relu(h), relu(t)).                        */
+int cn_mlp_feature_fwd(const void *packed, const void *x_tiles, int64_t n_tiles, void *h3_tiles,
+                       void *acts, void *stream);
+/* fusion stage: mean over views + 3 ResNet blocks + RenderReadout
+ * (layers.py:366-376,392-397).  h3_tiles is [b][nv][tiles_per_view]; output
+ * rgbs [b*tiles_per_view*128, 4] = (sigmoid rgb, softplus sigma).
+ *   acts (nullable): [n_out_tiles][7] activation tiles (3 x (relu(h), relu(t)), relu(e)). */
+int cn_mlp_fusion_fwd(const void *packed, const void *h3_tiles, int32_t b, int32_t nv,
+                      int64_t tiles_per_view, float *rgbs, void *acts, void *stream);
+
+/* readout backward: d_y [rows,4] + relu(e) tiles -> g tiles (bf16), d(output_layer)
+ * accumulated into grad (flat layout above).                                           */
+int cn_mlp_readout_bwd(const float *params, const float *d_y, const void *acts, int32_t act_stride_tiles,
+                       int32_t act_index, int64_t n_tiles, void *g_tiles, float *grad, void *stream);
+/* backward of one ResNet block for every tile: g_y -> g_h (in place allowed),
+ * dW/db of both Dense layers accumulated into grad.  blk in 0..5.                     */
+int cn_mlp_block_bwd(const void *packed, int32_t blk, const void *acts, int32_t act_stride_tiles,
+                     int32_t act_index, int64_t n_tiles, const void *gy_tiles, void *gh_tiles,
+                     float *grad, void *stream);
+/* mean-over-views backward: g_m [b][tiles_per_view] -> g_h3 [b][nv][tiles_per_view] = g_m / nv */
+int cn_mlp_mean_bwd(const void *gm_tiles, int32_t b, int32_t nv, int64_t tiles_per_view,
+                    void *gh3_tiles, void *stream);
+/* first Dense backward: dX = g0 . W0^T (tile images, same column order as X) ... */
+int cn_mlp_l0_dgrad(const void *packed, const void *g0_tiles, int64_t n_tiles, void *dx_tiles,
+                    void *stream);
+/* ... and dW0 += X^T . g0, db0 += sum(g0), accumulated into grad.                      */
+int cn_mlp_l0_wgrad(const void *x_tiles, const void *g0_tiles, int64_t n_tiles, float *grad,
+                    void *stream);
+
+/* ---- diagnostics ---------------------------------------------------------------- */
+
+/* One 128 x 128 x K tcgen05.mma tile with caller-supplied operand images and
+ * descriptor fields; used by tests to pin the shared-memory descriptor encoding.       */
+int cn_probe_umma(const void *a_img, int32_t a_bytes, const void *b_img, int32_t b_bytes,
+                  int32_t n_mma, int32_t a_major_mn, int32_t b_major_mn, int32_t a_lbo,
+                  int32_t a_sbo, int32_t a_kstep, int32_t b_lbo, int32_t b_sbo, int32_t b_kstep,
+                  float *d_out, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CLIPNERF_B200_H */

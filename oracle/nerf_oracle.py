@@ -1,0 +1,561 @@
+"""CPU oracle for the CLIP-NeRF volumetric render hot path.
+
+TEST INFRASTRUCTURE ONLY.  Nothing in the product package may import this
+module; only ``tests/``, ``__graft_entry__.smoke()`` and the ``cpu_baseline`` /
+``--impl reference`` legs of ``bench.py`` do, and only as the checker / the timed
+CPU baseline.
+
+What this is
+------------
+An op-for-op PyTorch (CPU, fp32 by default, fp64 on request) restatement of the
+TensorFlow/Keras reference path ``MVVNeRFRenderer._call`` and of every function it
+calls.  Each function cites the reference file:line it follows
+(paths relative to the reference checkout root).
+
+Parity status: the reference cannot run here (TensorFlow, tensorflow_addons are
+not installed; no network) and it ships no tests / golden vectors.  The
+restatement is pinned in two ways:
+  * ``oracle/tf_shim`` executes the *reference's own source files* on top of a
+    small torch-backed ``tensorflow`` stand-in and ``tests/test_oracle_vs_reference_source.py``
+    compares this module against them (run in the build container, where
+    ``/root/reference`` exists); golden vectors produced that way are committed
+    under ``tests/golden/``.
+  * closed-form unit tests and fp64 ``gradcheck``.
+Third-party arithmetic that is *not* in the reference tree
+(``tensorflow_addons.image.interpolate_bilinear``, TF kernels' reduction order)
+is restated from its published algorithm; where TF leaves the order of a
+floating-point reduction unspecified this oracle pins a sequential order and
+says so at the call site.
+
+Random numbers are explicit inputs (``u_strat``, ``u_pdf``) so that the CUDA path
+can be compared bit-for-bit on indices.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+Tensor = torch.Tensor
+
+# --------------------------------------------------------------------------
+# Host-side ray / camera bookkeeping (numpy in the reference as well)
+# --------------------------------------------------------------------------
+
+
+def get_specific_rays(u, v, extrinsics, intrinsics, norm_direction_vector=True):
+    """``src/lib/mvnerf/nerf_utils.py:27-35``: d = R . K^-1 . [u, v, 1], o = pose[:3, 3]."""
+    pixels = np.stack((u, v, np.ones_like(u)), axis=0)
+    rays_d = extrinsics[:3, :3] @ np.linalg.inv(intrinsics[:3, :3]) @ pixels
+    rays_d = rays_d.T
+    if norm_direction_vector:
+        rays_d = rays_d / np.linalg.norm(rays_d, axis=1, keepdims=True)
+    rays_o = np.broadcast_to(extrinsics[:3, -1], rays_d.shape)
+    return rays_o, rays_d
+
+
+def get_rays(image_width, image_height, extrinsics, intrinsics, norm_direction_vector=True):
+    """``nerf_utils.py:15-24``: row-major pixel grid, u = column, v = row."""
+    u, v = np.meshgrid(np.arange(image_width, dtype=np.float32),
+                       np.arange(image_height, dtype=np.float32), indexing='xy')
+    u = u.reshape(-1)
+    v = v.reshape(-1)
+    rays_o, rays_d = get_specific_rays(u, v, extrinsics, intrinsics, norm_direction_vector)
+    rays_d = rays_d.reshape(image_height, image_width, 3)
+    rays_o = rays_o.reshape(image_height, image_width, 3)
+    return rays_o, rays_d
+
+
+def bbox_biased_sample(n_sample, bboxes, image_height, image_width, in_box_p=0.8, rng=None):
+    """``nerf_utils.py:38-46``.  The reference draws from numpy's *global* RNG
+    (``np.random.randint``); pass ``rng=None`` to do the same, or a
+    ``np.random.RandomState`` for a private stream with identical draws."""
+    r = np.random if rng is None else rng
+    n_inside = int(n_sample * in_box_p)
+    n_random = n_sample - n_inside
+    in_samples = r.randint(bboxes[:2], bboxes[2:], (n_inside, 2))
+    random_samples = r.randint((image_height, image_width), size=(n_random, 2))
+    return np.concatenate([in_samples, random_samples], axis=0)
+
+
+def camera_parameters(camera_config):
+    """``src/lib/data_generator/util.py:4-10``: K 3x3 -> 4x4, E^-1 = inv(pose)."""
+    src_extrinsic = camera_config['pose']
+    src_intrinsic = np.reshape(camera_config['intrinsics'], (3, 3))
+    src_intrinsic = np.concatenate((src_intrinsic, np.zeros((3, 1))), axis=1)
+    src_intrinsic = np.concatenate((src_intrinsic, np.array([[0, 0, 0, 1]])), axis=0)
+    src_extrinsic_inv = np.linalg.inv(src_extrinsic)
+    return src_extrinsic_inv, src_intrinsic
+
+
+def get_input(colors, camera_configs, r_d, r_o):
+    """``src/lib/data_generator/mvnerf.py:28-43`` (5-tuple of fp32 arrays, batch of 1)."""
+    e_invs, ks = [], []
+    for cc in camera_configs:
+        e, k = camera_parameters(cc)
+        e_invs.append(e)
+        ks.append(k)
+    return (np.array([r_o], dtype=np.float32),
+            np.array([r_d], dtype=np.float32),
+            np.array([np.array(colors) / 255.0], dtype=np.float32),
+            np.array([ks], dtype=np.float32),
+            np.array([e_invs], dtype=np.float32))
+
+
+def get_target(color, rays):
+    """``mvnerf.py:46-48``: rays are (row, col) ints."""
+    return np.array(color[rays[:, 0], rays[:, 1], :3]) / 255.0
+
+
+def quantize_render(all_rgbs: np.ndarray, all_depths: np.ndarray, image_shape):
+    """``src/lib/mvnerf/model_v0.py:275-280``: x255, clip, *truncating* uint8 cast;
+    depth min-max normalised then truncated."""
+    rgbs = np.reshape(np.array(all_rgbs), (*image_shape, 3)) * 255
+    rgbs = np.clip(rgbs, 0, 255).astype(np.uint8)
+    depths = np.reshape(np.array(all_depths), (*image_shape, 1))
+    norm = (depths - np.min(depths)) / (np.max(depths) - np.min(depths))
+    depths = (norm * 255).astype(np.uint8)
+    return rgbs, depths
+
+
+# --------------------------------------------------------------------------
+# Tensor ops of the hot path
+# --------------------------------------------------------------------------
+
+
+def sample_along_ray(rays_origin: Tensor, rays_direction: Tensor, near: float, far: float,
+                     n_samples: int, u_strat: Tensor) -> Tuple[Tensor, Tensor]:
+    """``nerf_utils.py:49-61``.  ``u_strat`` [b, nr, S] replaces ``tf.random.uniform``.
+
+    The interval table is built in Python doubles and cast once (``:51``);
+    ``z = 1 * lo + u * step`` with separately rounded product and sum (no FMA).
+    """
+    step = (far - near) / n_samples
+    dt = rays_origin.dtype
+    lower = torch.tensor([near + i * step for i in range(n_samples + 1)], dtype=torch.float32).to(dt)[:-1]
+    lower_bound = torch.ones_like(rays_direction[..., 0])[..., None] * lower
+    random_added = u_strat * step
+    z = lower_bound + random_added
+    world_points = rays_origin[:, :, None, :] + z[..., None] * rays_direction[:, :, None, :]
+    return world_points, z
+
+
+def _affine_rows(M: Tensor, x: Tensor, y: Tensor, z: Tensor, w, rows: int) -> List[Tensor]:
+    """rows of M . [x, y, z, w] as explicitly ordered fp32 products and sums
+    ((m0 x + m1 y) + m2 z) + m3 w, each operation rounded on its own.
+
+    ``tf.matmul`` (cuBLAS batched 4x4 GEMMs, ``nerf_utils.py:71,74,100``) leaves the order of the
+    four-term dot product unspecified; the oracle pins this one so that pixel coordinates and
+    bilinear corner indices can be compared bit-for-bit."""
+    out = []
+    for i in range(rows):
+        acc = M[..., i, 0] * x
+        acc = acc + M[..., i, 1] * y
+        acc = acc + M[..., i, 2] * z
+        acc = acc + M[..., i, 3] * w
+        out.append(acc)
+    return out
+
+
+def compute_pixel_in_image_mv(world_points: Tensor, src_intrinsics: Tensor,
+                              src_extrinsics_inv: Tensor) -> Tuple[Tensor, Tensor]:
+    """``nerf_utils.py:64-81``: p = E^-1 [x,1]; q = K p; pix = clip(q.xy / max(q.z, 1e-8), +-1e6).
+
+    Returns pix [b, nv, nr, S, 2] and camera points [b, nv, nr, S, 4].
+    """
+    x = world_points[:, None, :, :, 0]
+    y = world_points[:, None, :, :, 1]
+    z = world_points[:, None, :, :, 2]
+    E = src_extrinsics_inv[:, :, None, None]                                # [b, nv, 1, 1, 4, 4]
+    K = src_intrinsics[:, :, None, None]
+    p = _affine_rows(E, x, y, z, 1.0, 4)
+    cam = torch.stack(p, dim=-1)                                            # [b, nv, nr, S, 4]
+    q = _affine_rows(K, p[0], p[1], p[2], p[3], 3)
+    den = torch.clamp(q[2], min=1e-8)
+    pix = torch.stack([q[0] / den, q[1] / den], dim=-1)
+    pix = torch.clamp(pix, min=-1e6, max=1e6)
+    return pix, cam
+
+
+def world_to_camera_direction_vector_mv(world_dirs: Tensor, extrinsics_inverse: Tensor) -> Tensor:
+    """``nerf_utils.py:84-105``: homogeneous **w = 1** (quirk Q1) so the result is R d + t."""
+    E = extrinsics_inverse[:, :, None]                                      # [b, nv, 1, 4, 4]
+    d = world_dirs[:, None]                                                 # [b, 1, nr, 3]
+    rows = _affine_rows(E, d[..., 0], d[..., 1], d[..., 2], 1.0, 3)
+    return torch.stack(rows, dim=-1)                                        # [b, nv, nr, 3]
+
+
+def interpolate_bilinear(grid: Tensor, query_points: Tensor, indexing: str = 'xy') -> Tensor:
+    """Restatement of ``tensorflow_addons.image.interpolate_bilinear`` (TFA <= 0.20,
+    ``tensorflow_addons/image/dense_image_warp.py``; called at ``nerf_utils.py:282``).
+
+    grid [B, H, W, C], query_points [B, N, 2] -> [B, N, C].  Per axis:
+    ``floor = clamp(floor(q), 0, size-2)``, ``alpha = clamp(q - floor, 0, 1)``;
+    ``top = ax*(TR-TL)+TL``, ``bottom = ax*(BR-BL)+BL``, ``out = ay*(bottom-top)+top``.
+    """
+    B, H, W, C = grid.shape
+    if indexing == 'xy':
+        qx, qy = query_points[..., 0], query_points[..., 1]
+    else:
+        qy, qx = query_points[..., 0], query_points[..., 1]
+
+    def axis(q, size):
+        max_floor = float(size - 2)
+        fl = torch.clamp(torch.floor(q), min=0.0, max=max_floor)   # tf.minimum(tf.maximum(0, floor(q)), size-2)
+        int_fl = fl.detach().to(torch.int64)
+        alpha = torch.clamp(q - fl.detach(), min=0.0, max=1.0)
+        return int_fl, alpha
+
+    fy, ay = axis(qy, H)
+    fx, ax = axis(qx, W)
+    flat = grid.reshape(B, H * W, C)
+
+    def gather(yc, xc):
+        lin = (yc * W + xc)[..., None].expand(-1, -1, C)
+        return torch.gather(flat, 1, lin)
+
+    tl = gather(fy, fx)
+    tr = gather(fy, fx + 1)
+    bl = gather(fy + 1, fx)
+    br = gather(fy + 1, fx + 1)
+    ax = ax[..., None]
+    ay = ay[..., None]
+    top = ax * (tr - tl) + tl
+    bottom = ax * (br - bl) + bl
+    return ay * (bottom - top) + top
+
+
+def get_projection_features_mv(inputs: Tensor, features: Tensor, pixel_locations: Tensor) -> Tensor:
+    """``nerf_utils.py:277-285``: concat(image*2-1, features) (259 ch) and bilinear gather.
+
+    inputs [b, nv, H, W, 3] (already ``2*I-1``), features [b, nv, H, W, C],
+    pixel_locations [b, nv, nr, S, 2] -> [b, nv, nr, S, 3+C].
+    """
+    b, nv, H, W, _ = inputs.shape
+    nr, S = pixel_locations.shape[2], pixel_locations.shape[3]
+    comb = torch.cat([inputs, features], dim=-1).reshape(b * nv, H, W, -1)
+    flat_pix = pixel_locations.reshape(b * nv, nr * S, 2)
+    out = interpolate_bilinear(comb, flat_pix, indexing='xy')
+    return out.reshape(b, nv, nr, S, -1)
+
+
+def position_encoding(position: Tensor, n_freq: int = 10, pos_encoding_freq: float = math.pi) -> Tensor:
+    """``nerf_utils.py:108-126``: f_k = fp32(pi) * 2^k; per coordinate
+    ``[sin f0, cos f0, sin f1, cos f1, ...]``, coordinate-major ('d n f')."""
+    dt = position.dtype
+    freq = (torch.tensor(pos_encoding_freq, dtype=torch.float32) *
+            torch.pow(torch.tensor(2.0, dtype=torch.float32), torch.arange(n_freq, dtype=torch.float32))).to(dt)
+    arg = position[..., None] * freq                                       # [..., d, n]
+    enc = torch.stack([torch.sin(arg), torch.cos(arg)], dim=-1)            # [..., d, n, 2]
+    return enc.reshape(*position.shape[:-1], -1)
+
+
+def sigma_to_alpha(sigma: Tensor, dists: Tensor) -> Tensor:
+    """``nerf_utils.py:129-140``."""
+    return 1.0 - torch.exp(-dists * F.relu(sigma))
+
+
+def volumetric_render(zs: Tensor, density: Tensor, chromacity: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
+    """``model_v0.py:89-100``: last interval repeats the previous one,
+    T = exclusive cumprod(1 - alpha + 1e-10), no background term."""
+    dists = zs[..., 1:] - zs[..., :-1]
+    dists = torch.cat([dists, dists[..., -1:]], dim=-1)
+    alpha = sigma_to_alpha(density, dists)
+    t_incl = torch.cumprod(1 - alpha + 1e-10, dim=-1)
+    transmittance = torch.cat([torch.ones_like(t_incl[..., :1]), t_incl[..., :-1]], dim=-1)
+    weights = alpha * transmittance
+    rgb = torch.sum(weights[..., None] * chromacity, dim=-2)
+    depth = torch.sum(weights * zs, dim=-1)
+    return rgb, depth, weights
+
+
+def _seq_cumsum(x: Tensor) -> Tensor:
+    """Inclusive cumulative sum along the last axis as a strict left-to-right chain of additions in
+    the tensor's own dtype (``torch.cumsum`` on CPU accumulates fp32 inputs in double)."""
+    cols = [x[..., 0]]
+    for k in range(1, x.shape[-1]):
+        cols.append(cols[-1] + x[..., k])
+    return torch.stack(cols, dim=-1)
+
+
+def sample_pdf(bins: Tensor, weights: Tensor, n_samples: int, u: Tensor,
+               return_indices: bool = False):
+    """``nerf_utils.py:143-176`` (quirk Q5).  ``u`` [b, nr, n_samples] replaces
+    ``tf.random.uniform``.  bins [b, nr, 63], weights [b, nr, 62].
+
+    * ``above = #{k : u >= cdf[k]}`` over the 63-entry cdf -- NOT clamped;
+    * an index of 63 reads 0 (TF-GPU ``gather_nd`` out-of-bounds semantics; the
+      reference only runs on GPU, ``src/train_nerf.py:86-87``);
+    * reduction order: TF does not specify the order of ``reduce_sum`` / ``cumsum``
+      on GPU; the oracle pins a **sequential left-to-right fp32 sum** for both
+      (``_seq_cumsum``), which is what makes the bin indices reproducible bit-for-bit.
+    """
+    stable = weights + 1e-5
+    w_sum = _seq_cumsum(stable)[..., -1:]
+    w_sum = torch.where(torch.abs(w_sum) == 0, torch.ones_like(w_sum), w_sum)
+    pdf = stable / w_sum
+    cdf = _seq_cumsum(pdf)
+    cdf = torch.cat([torch.zeros_like(cdf[..., :1]), cdf], dim=-1)          # 63 entries
+    nb = bins.shape[-1]
+    above = (u[..., :, None] >= cdf[..., None, :]).sum(dim=-1)              # int64 in [1, 63]
+    below = torch.clamp(above - 1, 0, nb - 1)
+
+    def gather_oob0(src, idx):
+        pad = torch.cat([src, torch.zeros_like(src[..., :1])], dim=-1)      # index nb -> 0
+        return torch.gather(pad, -1, torch.clamp(idx, 0, nb))
+
+    cdf_a = gather_oob0(cdf, above)
+    cdf_b = gather_oob0(cdf, below)
+    bins_a = gather_oob0(bins, above)
+    bins_b = gather_oob0(bins, below)
+    denom = cdf_a - cdf_b
+    denom = torch.where(denom < 1e-5, torch.ones_like(denom), denom)
+    t = (u - cdf_b) / denom
+    samples = bins_b + t * (bins_a - bins_b)
+    if return_indices:
+        return samples, above.to(torch.int32), below.to(torch.int32)
+    return samples
+
+
+# --------------------------------------------------------------------------
+# MLP (Keras Dense: y = x @ kernel[in, out] + bias)
+# --------------------------------------------------------------------------
+
+N_FREQ = 10
+HIDDEN = 128
+IN_DIM = 3 * 2 * N_FREQ * 2 + 3 + 256          # 60 + 60 + 3 + 256 = 379
+
+
+def embedding_param_shapes(in_dim: int = IN_DIM, hidden: int = HIDDEN, n_blocks: int = 6):
+    """Variable names/shapes of ``MVResNetMLPNeRFEmbedding(6, 128)`` (``layers.py:334-352``)."""
+    shapes = [('layer_0.kernel', (in_dim, hidden)), ('layer_0.bias', (hidden,))]
+    nf = n_blocks // 2
+    for grp, n in (('feature_blocks', nf), ('fusion_blocks', n_blocks - nf)):
+        for i in range(n):
+            for l in ('layer_0', 'layer_1'):
+                shapes.append((f'{grp}.{i}.{l}.kernel', (hidden, hidden)))
+                shapes.append((f'{grp}.{i}.{l}.bias', (hidden,)))
+    return shapes
+
+
+def readout_param_shapes(hidden: int = HIDDEN, out: int = 4):
+    """``RenderReadout(4)`` (``layers.py:382-397``)."""
+    return [('output_layer.kernel', (hidden, out)), ('output_layer.bias', (out,))]
+
+
+def init_params(seed: int, bias_std: float = 0.0, dtype=torch.float32) -> Dict[str, Tensor]:
+    """glorot_uniform kernels / zero biases (Keras defaults); ``bias_std`` > 0 draws
+    N(0, bias_std) biases so that parity tests exercise the bias path."""
+    g = torch.Generator().manual_seed(seed)
+    p: Dict[str, Tensor] = {}
+    for net in ('coarse', 'fine'):
+        for name, shape in embedding_param_shapes():
+            full = f'{net}_embedding.{name}'
+            if name.endswith('kernel'):
+                lim = math.sqrt(6.0 / (shape[0] + shape[1]))
+                p[full] = ((torch.rand(shape, generator=g) * 2 - 1) * lim).to(dtype)
+            else:
+                p[full] = (torch.randn(shape, generator=g) * bias_std).to(dtype)
+        for name, shape in readout_param_shapes():
+            full = f'{net}_readout.{name}'
+            if name.endswith('kernel'):
+                lim = math.sqrt(6.0 / (shape[0] + shape[1]))
+                p[full] = ((torch.rand(shape, generator=g) * 2 - 1) * lim).to(dtype)
+            else:
+                p[full] = (torch.randn(shape, generator=g) * bias_std).to(dtype)
+    return p
+
+
+def resnet_mlp_block(x: Tensor, p: Dict[str, Tensor], prefix: str, activation: str = 'relu',
+                     shortcut_kernel: Optional[Tensor] = None) -> Tensor:
+    """``layers.py:262-298``: y = shortcut(x) + act(act(x) W0 + b0) W1 + b1."""
+    if activation == 'relu':
+        act = F.relu
+    elif activation == 'elu':
+        act = F.elu
+    else:
+        raise ValueError(f'activation {activation} not supported')
+    r = act(x)
+    r = r @ p[f'{prefix}.layer_0.kernel'] + p[f'{prefix}.layer_0.bias']
+    r = act(r)
+    r = r @ p[f'{prefix}.layer_1.kernel'] + p[f'{prefix}.layer_1.bias']
+    sc = x if shortcut_kernel is None else x @ shortcut_kernel
+    return sc + r
+
+
+def mv_embedding_from_x(x: Tensor, p: Dict[str, Tensor], prefix: str, n_views: int,
+                        complete_output: bool = False):
+    """Everything of ``MVResNetMLPNeRFEmbedding.call`` after the concat (``layers.py:363-379``):
+    x [(b nv), ..., 379] -> Dense 379->128, 3 per-view blocks, mean over views, 3 fusion blocks."""
+    x = x @ p[f'{prefix}.layer_0.kernel'] + p[f'{prefix}.layer_0.bias']
+    outputs = [x]
+    for i in range(3):
+        outputs.append(resnet_mlp_block(outputs[-1], p, f'{prefix}.feature_blocks.{i}'))
+    pre = outputs[-1].reshape(-1, n_views, *outputs[-1].shape[1:])
+    outputs.append(pre.mean(dim=1))
+    for i in range(3):
+        outputs.append(resnet_mlp_block(outputs[-1], p, f'{prefix}.fusion_blocks.{i}'))
+    return outputs if complete_output else outputs[-1]
+
+
+def mv_embedding(points: Tensor, dirs: Tensor, feats: Tensor, p: Dict[str, Tensor], prefix: str,
+                 n_views: int, complete_output: bool = False):
+    """``MVResNetMLPNeRFEmbedding.call`` (``layers.py:354-379``).
+
+    points/dirs [(b nv), nr, S, 3], feats [(b nv), nr, S, 259]; input order
+    [posenc(points) 60 | posenc(dirs) 60 | feats 259] (``layers.py:362``)."""
+    enc_p = position_encoding(points)
+    enc_d = position_encoding(dirs)
+    x = torch.cat([enc_p, enc_d, feats], dim=-1)
+    return mv_embedding_from_x(x, p, prefix, n_views, complete_output)
+
+
+def render_readout(x: Tensor, p: Dict[str, Tensor], prefix: str) -> Tuple[Tensor, Tensor]:
+    """``RenderReadout.call`` (``layers.py:392-397``)."""
+    y = F.relu(x) @ p[f'{prefix}.output_layer.kernel'] + p[f'{prefix}.output_layer.bias']
+    return torch.sigmoid(y[..., :3]), F.softplus(y[..., 3])
+
+
+# --------------------------------------------------------------------------
+# MVVNeRFRenderer._call
+# --------------------------------------------------------------------------
+
+
+def _render_pass(ray_o, ray_d, zs, norm_images, feats, K, Einv, p, net, n_views):
+    b, nr, S = zs.shape
+    pts = ray_o[:, :, None, :] + zs[..., None] * ray_d[:, :, None, :]
+    pix, cam = compute_pixel_in_image_mv(pts, K, Einv)
+    g = get_projection_features_mv(norm_images, feats, pix)
+    cam_dirs = world_to_camera_direction_vector_mv(ray_d, Einv)            # [b, nv, nr, 3]
+    rep_dirs = cam_dirs[:, :, :, None, :].expand(-1, -1, -1, S, -1).reshape(b * n_views, nr, S, 3)
+    cam3 = cam.reshape(b * n_views, nr, S, 4)[..., :3]
+    g = g.reshape(b * n_views, nr, S, -1)
+    emb = mv_embedding(cam3, rep_dirs, g, p, f'{net}_embedding', n_views)
+    chroma, density = render_readout(emb, p, f'{net}_readout')
+    rgb, depth, weights = volumetric_render(zs, density, chroma)
+    return rgb, depth, weights, chroma, density
+
+
+def mvnerf_call(inputs: Sequence[Tensor], combined_features: Tensor, p: Dict[str, Tensor], *,
+                near: float, far: float, n_samples: int, u_strat: Tensor, u_pdf: Tensor,
+                return_aux: bool = False):
+    """``MVVNeRFRenderer._call`` (``model_v0.py:113-184``).
+
+    inputs = (ray_o [b,nr,3], ray_d [b,nr,3], images [b,nv,H,W,3] in [0,1],
+    K [b,nv,4,4], E^-1 [b,nv,4,4]); combined_features [b,nv,H,W,256].
+    No ``stop_gradient`` anywhere (quirk Q4).
+    Returns (rgb, depth, fine_rgb, fine_depth).
+    """
+    ray_o, ray_d, images, K, Einv = inputs
+    n_views = images.shape[1]
+    norm_images = images * 2 - 1.0
+    _, z = sample_along_ray(ray_o, ray_d, near, far, n_samples, u_strat)
+    rgb, depth, weights, _, _ = _render_pass(ray_o, ray_d, z, norm_images, combined_features,
+                                             K, Einv, p, 'coarse', n_views)
+    z_mid = 0.5 * (z[..., 1:] + z[..., :-1])
+    probs = weights[..., 1:-1]
+    z_samples, above, below = sample_pdf(z_mid, probs, n_samples, u_pdf, return_indices=True)
+    all_zs = torch.cat([z, z_samples], dim=-1)
+    all_zs, perm = torch.sort(all_zs, dim=-1, stable=True)
+    fine_rgb, fine_depth, fine_w, _, _ = _render_pass(ray_o, ray_d, all_zs, norm_images, combined_features,
+                                                      K, Einv, p, 'fine', n_views)
+    if return_aux:
+        aux = dict(z=z, weights=weights, z_samples=z_samples, above=above, below=below,
+                   all_zs=all_zs, perm=perm.to(torch.int32), fine_weights=fine_w)
+        return (rgb, depth, fine_rgb, fine_depth), aux
+    return rgb, depth, fine_rgb, fine_depth
+
+
+def mse(labels: Tensor, pred: Tensor) -> Tensor:
+    """``tf.keras.losses.MeanSquaredError`` with default reduction: mean over every element."""
+    return torch.mean((pred - labels) ** 2)
+
+
+def train_loss(outputs, labels: Tensor) -> Tensor:
+    """``model_v0.py:193``: MSE(labels, rgb) + MSE(labels, fine_rgb)."""
+    rgb, _, fine_rgb, _ = outputs
+    return mse(labels, rgb) + mse(labels, fine_rgb)
+
+
+def clip_gradients(grads: Sequence[Tensor], clip: float = 1.0) -> List[Tensor]:
+    """``nerf_utils.py:8-12``: per-element ``clip_by_value``."""
+    return [torch.clamp(g, -clip, clip) for g in grads]
+
+
+def warmup_lr(step: float, target_lr: float, warmup_steps: float, scale_down_after: float = 400000.0) -> float:
+    """``WarmupScheduler.__call__`` (``nerf_utils.py:288-300``)."""
+    warmup_steps = max(1.0, float(warmup_steps))
+    step = float(step)
+    if step <= warmup_steps:
+        return step / warmup_steps * target_lr
+    if step <= scale_down_after:
+        return target_lr
+    return 0.1 * target_lr
+
+
+# --------------------------------------------------------------------------
+# Synthetic scenes shared by tests, smoke() and bench.py
+# --------------------------------------------------------------------------
+
+
+def polar_pose(azimuth: float, polar: float, radius: float, t_center=(0.6, 0.0, 0.1)) -> np.ndarray:
+    """Camera-to-world pose looking at ``t_center`` from a hemisphere, the way the
+    reference's ``Affine.polar`` (``dependencies/manipulation_tasks/.../transform.py:58-75``)
+    places cameras: position on a sphere of ``radius`` around ``t_center``, optical
+    axis (+z) towards the centre."""
+    c = np.asarray(t_center, dtype=np.float64)
+    pos = c + radius * np.array([math.sin(polar) * math.cos(azimuth),
+                                 math.sin(polar) * math.sin(azimuth),
+                                 math.cos(polar)])
+    zc = c - pos
+    zc /= np.linalg.norm(zc)
+    up = np.array([0.0, 0.0, 1.0])
+    xc = np.cross(zc, up)
+    if np.linalg.norm(xc) == 0:
+        xc = np.array([math.cos(azimuth), math.sin(azimuth), 0.0])
+    else:
+        xc /= np.linalg.norm(xc)
+    yc = np.cross(zc, xc)
+    pose = np.eye(4)
+    pose[:3, 0], pose[:3, 1], pose[:3, 2], pose[:3, 3] = xc, yc, zc, pos
+    return pose
+
+
+def synthetic_scene(seed: int, b: int, nv: int, nr: int, H: int, W: int, C: int = 256,
+                    n_samples: int = 64, rays: str = 'random', dtype=torch.float32):
+    """Synthetic inputs of SURVEY.md 8(d): U[0,1) images, N(0,1) features, hemisphere
+    cameras, rays from the target camera (random (row, col) pixels via
+    ``bbox_biased_sample`` or the full row-major grid), U[0,1) u_strat / u_pdf / target."""
+    rs = np.random.RandomState(seed)
+    g = torch.Generator().manual_seed(seed)
+    f = 0.5 * W / math.tan(math.radians(30.0))
+    K3 = np.array([[f, 0, W / 2], [0, f, H / 2], [0, 0, 1]], dtype=np.float64)
+    ro, rd, Ks, Es, pix_rc = [], [], [], [], []
+    for _ in range(b):
+        poses = [polar_pose(rs.uniform(0, 2 * math.pi), rs.uniform(0.2, 1.1), rs.uniform(0.7, 0.9))
+                 for _ in range(nv + 1)]
+        tgt = poses[-1]
+        if rays == 'grid':
+            o, d = get_rays(W, H, tgt, K3.astype(np.float32))
+            o, d = o.reshape(-1, 3)[:nr], d.reshape(-1, 3)[:nr]
+            rc = np.stack(np.divmod(np.arange(nr), W), axis=1)
+        else:
+            rc = bbox_biased_sample(nr, np.array([0, 0, H, W]), H, W, rng=rs)
+            o, d = get_specific_rays(rc[:, 1], rc[:, 0], tgt, K3.astype(np.float32))
+        cfgs = [dict(pose=pp, intrinsics=K3.reshape(-1)) for pp in poses[:-1]]
+        e_invs, ks = zip(*[camera_parameters(c) for c in cfgs])
+        ro.append(o); rd.append(d); Ks.append(np.array(ks)); Es.append(np.array(e_invs)); pix_rc.append(rc)
+    inputs = (torch.tensor(np.array(ro), dtype=torch.float32).to(dtype),
+              torch.tensor(np.array(rd), dtype=torch.float32).to(dtype),
+              torch.rand((b, nv, H, W, 3), generator=g).to(dtype),
+              torch.tensor(np.array(Ks), dtype=torch.float32).to(dtype),
+              torch.tensor(np.array(Es), dtype=torch.float32).to(dtype))
+    feats = torch.randn((b, nv, H, W, C), generator=g).to(dtype)
+    u_strat = torch.rand((b, nr, n_samples), generator=g).to(dtype)
+    u_pdf = torch.rand((b, nr, n_samples), generator=g).to(dtype)
+    target = torch.rand((b, nr, 3), generator=g).to(dtype)
+    return dict(inputs=inputs, features=feats, u_strat=u_strat, u_pdf=u_pdf, target=target,
+                pixels_rc=np.array(pix_rc))

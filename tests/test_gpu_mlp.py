@@ -1,0 +1,112 @@
+"""tcgen05 MLP kernels against the oracle's fp32/fp64 MLP on the same (bf16-representable) inputs.
+
+Tolerance: bf16 operands / fp32 accumulation -> normalised max error <= 1e-2 on activations and
+outputs, <= 2e-2 on gradients (BASELINE.json)."""
+import pytest
+import torch
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(cuda, b=1, nv=3, rows_per_view=512, seed=0):
+    from clipnerf_b200 import layout, params
+    from oracle import nerf_oracle as O
+    g = torch.Generator().manual_seed(seed)
+    named = O.init_params(seed, bias_std=0.02)
+    flat = params.from_named(named, 'fine')
+    n = b * nv * rows_per_view
+    x_ref = torch.randn(n, 379, generator=g)
+    x_ref[:, :120] = torch.sin(x_ref[:, :120] * 3)           # posenc-like columns in [-1, 1]
+    x_ref = x_ref.to(torch.bfloat16).to(torch.float32)
+    cols = torch.tensor([layout.x_col_to_ref(j) for j in range(379)])
+    x_int = torch.zeros(n, 384)
+    x_int[:, :379] = x_ref[:, cols]
+    return named, flat, x_ref, layout.matrix_to_tiles(x_int).to(cuda)
+
+
+def _oracle_stages(named, x_ref, b, nv, dtype=torch.float64):
+    from oracle import nerf_oracle as O
+    p = {k: v.to(dtype) for k, v in named.items()}
+    x = x_ref.to(dtype).reshape(b * nv, -1, 379)
+    outs = O.mv_embedding_from_x(x, p, 'fine_embedding', nv, complete_output=True)
+    chroma, sigma = O.render_readout(outs[-1], p, 'fine_readout')
+    return outs, chroma, sigma
+
+
+@pytest.mark.parametrize('nv,rows', [(3, 512), (1, 384), (2, 128)])
+def test_mlp_forward(cuda, nv, rows):
+    from clipnerf_b200 import layout, ops
+    b = 1
+    named, flat, x_ref, x_tiles = _setup(cuda, b, nv, rows)
+    outs, chroma, sigma = _oracle_stages(named, x_ref, b, nv)
+    packed = ops.pack_weights(flat.to(cuda))
+    h3, acts_f = ops.mlp_feature_fwd(packed, x_tiles, True)
+    h3m = layout.tiles_to_matrix(h3, 128)
+    e = rel_err(h3m, outs[3].reshape(-1, 128))
+    assert e < 1e-2, f'h3 rel err {e}'
+    rgbs, acts_u = ops.mlp_fusion_fwd(packed, h3, b, nv, True)
+    ref = torch.cat([chroma, sigma[..., None]], -1).reshape(-1, 4)
+    e = rel_err(rgbs, ref)
+    assert e < 1e-2, f'rgbs rel err {e}'
+    # saved operands: relu of the block inputs / hidden activations
+    a = layout.tiles_to_matrix(acts_f, 128).view(-1, 6, 128, 128)
+    a1_ref = torch.relu(outs[0]).reshape(-1, 128, 128)
+    assert rel_err(a[:, 0], a1_ref) < 1e-2
+    au = layout.tiles_to_matrix(acts_u, 128).view(-1, 7, 128, 128)
+    assert rel_err(au[:, 0], torch.relu(outs[4]).reshape(-1, 128, 128)) < 1e-2
+    assert rel_err(au[:, 6], torch.relu(outs[7]).reshape(-1, 128, 128)) < 1e-2
+
+
+def test_mlp_forward_odd_tile_count(cuda):
+    """an odd number of 128-row tiles leaves the second slot of the last tile pair empty."""
+    from clipnerf_b200 import layout, ops
+    named, flat, x_ref, x_tiles = _setup(cuda, 1, 1, 128 * 3)
+    outs, chroma, sigma = _oracle_stages(named, x_ref, 1, 1)
+    packed = ops.pack_weights(flat.to(cuda))
+    h3, _ = ops.mlp_feature_fwd(packed, x_tiles, False)
+    assert rel_err(layout.tiles_to_matrix(h3, 128), outs[3].reshape(-1, 128)) < 1e-2
+    rgbs, _ = ops.mlp_fusion_fwd(packed, h3, 1, 1, False)
+    assert rel_err(rgbs, torch.cat([chroma, sigma[..., None]], -1).reshape(-1, 4)) < 1e-2
+
+
+def test_mlp_backward(cuda):
+    """full MLP backward chain (readout, 6 blocks, mean, first Dense) against fp64 autograd."""
+    from clipnerf_b200 import layout, ops, params
+    from oracle import nerf_oracle as O
+    b, nv, rows = 1, 3, 256
+    named, flat, x_ref, x_tiles = _setup(cuda, b, nv, rows, seed=1)
+    p = {k: v.double().requires_grad_(True) for k, v in named.items()}
+    x = x_ref.double().reshape(b * nv, -1, 379).requires_grad_(True)
+    outs = O.mv_embedding_from_x(x, p, 'fine_embedding', nv, complete_output=True)
+    y = torch.relu(outs[-1]) @ p['fine_readout.output_layer.kernel'] + p['fine_readout.output_layer.bias']
+    g = torch.Generator().manual_seed(7)
+    d_y = torch.randn(b * rows, 4, generator=g)
+    (y.reshape(-1, 4) * d_y.double()).sum().backward()
+
+    dev_flat = flat.to(cuda)
+    packed = ops.pack_weights(dev_flat)
+    h3, acts_f = ops.mlp_feature_fwd(packed, x_tiles, True)
+    rgbs, acts_u = ops.mlp_fusion_fwd(packed, h3, b, nv, True)
+    grad = torch.zeros_like(dev_flat)
+    gt = ops.mlp_readout_bwd(dev_flat, d_y.to(cuda), acts_u, 7, 6, grad)
+    for blk in (5, 4, 3):
+        ops.mlp_block_bwd(packed, blk, acts_u, 7, 2 * (blk - 3), gt, grad)
+    gf = ops.mlp_mean_bwd(gt, b, nv)
+    for blk in (2, 1, 0):
+        ops.mlp_block_bwd(packed, blk, acts_f, 6, 2 * blk, gf, grad)
+    ops.mlp_l0_wgrad(x_tiles, gf, grad)
+    dx = ops.mlp_l0_dgrad(packed, gf)
+
+    got = params.to_named(grad.cpu(), 'fine')
+    worst = 0.0
+    for name, gv in got.items():
+        ref = p[name].grad
+        e = rel_err(gv, ref)
+        worst = max(worst, e)
+        assert e < 2e-2, f'{name}: rel err {e}'
+    dxm = layout.x_matrix_to_ref(layout.tiles_to_matrix(dx, 384)).cpu()
+    e = rel_err(dxm, x.grad.reshape(-1, 379))
+    assert e < 2e-2, f'dX rel err {e}'
+    print('worst parameter-gradient rel err', worst, 'dX', e)

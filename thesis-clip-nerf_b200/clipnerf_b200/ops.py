@@ -1,0 +1,207 @@
+"""One thin torch wrapper per C-ABI entry point (``include/clipnerf_b200.h``).
+
+Every function takes CUDA tensors, allocates its outputs with torch (the library owns no device
+memory), enqueues on torch's current stream and returns without synchronising."""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Tuple
+
+import torch
+
+from . import _abi
+from ._abi import ACT_TILE_BYTES, PACKED_BYTES, TILE_ROWS, X_TILE_BYTES, CnScene, call
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    assert t.is_cuda, 'clipnerf_b200 ops need CUDA tensors (no CPU fallback)'
+    if t.dtype != torch.float32 or not t.is_contiguous():
+        t = t.to(torch.float32).contiguous()
+    return t
+
+
+def _bytes(n: int, device) -> torch.Tensor:
+    return torch.empty(n, dtype=torch.uint8, device=device)
+
+
+class Scene:
+    """Source views: images [b,nv,H,W,3], features [b,nv,H,W,256], K [b,nv,4,4], E^-1 [b,nv,4,4]."""
+
+    def __init__(self, images, features, intrinsics, extr_inv):
+        self.images, self.features = _f32c(images), _f32c(features)
+        self.intrinsics, self.extr_inv = _f32c(intrinsics), _f32c(extr_inv)
+        b, nv, H, W, c3 = self.images.shape
+        assert c3 == 3 and tuple(self.features.shape) == (b, nv, H, W, 256), 'features must be [b,nv,H,W,256]'
+        assert tuple(self.intrinsics.shape) == (b, nv, 4, 4) and tuple(self.extr_inv.shape) == (b, nv, 4, 4)
+        self.b, self.nv, self.H, self.W = b, nv, H, W
+        self.c = CnScene(self.images.data_ptr(), self.features.data_ptr(), self.intrinsics.data_ptr(),
+                         self.extr_inv.data_ptr(), b, nv, H, W)
+
+    @property
+    def device(self):
+        return self.images.device
+
+
+def sample_coarse(u: torch.Tensor, near: float, far: float) -> torch.Tensor:
+    u = _f32c(u)
+    z = torch.empty_like(u)
+    call('cn_sample_coarse', _ptr(u), _ptr(z), u.numel() // u.shape[-1], u.shape[-1], float(near), float(far),
+         _stream())
+    return z
+
+
+def sample_pdf_fwd(z_c, w_c, u) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    z_c, w_c, u = _f32c(z_c), _f32c(w_c), _f32c(u)
+    assert z_c.shape[-1] == 64 and w_c.shape == z_c.shape and u.shape == z_c.shape
+    n = z_c.numel() // 64
+    z_fine = torch.empty(*z_c.shape[:-1], 128, dtype=torch.float32, device=z_c.device)
+    perm = torch.empty(*z_c.shape[:-1], 128, dtype=torch.uint8, device=z_c.device)
+    above = torch.empty(*z_c.shape[:-1], 64, dtype=torch.uint8, device=z_c.device)
+    call('cn_sample_pdf_fwd', _ptr(z_c), _ptr(w_c), _ptr(u), n, _ptr(z_fine), _ptr(perm), _ptr(above), _stream())
+    return z_fine, perm, above
+
+
+def sample_pdf_bwd(z_c, w_c, u, perm, dz_fine, dw_c: Optional[torch.Tensor] = None) -> torch.Tensor:
+    z_c, w_c, u, dz_fine = _f32c(z_c), _f32c(w_c), _f32c(u), _f32c(dz_fine)
+    if dw_c is None:
+        dw_c = torch.zeros_like(w_c)
+    call('cn_sample_pdf_bwd', _ptr(z_c), _ptr(w_c), _ptr(u), _ptr(perm), _ptr(dz_fine), z_c.numel() // 64,
+         _ptr(dw_c), _stream())
+    return dw_c
+
+
+def n_tiles(rows: int) -> int:
+    assert rows % TILE_ROWS == 0, f'{rows} rows is not a multiple of {TILE_ROWS}'
+    return rows // TILE_ROWS
+
+
+def project_gather_fwd(scene: Scene, ray_o, ray_d, z) -> torch.Tensor:
+    ray_o, ray_d, z = _f32c(ray_o), _f32c(ray_d), _f32c(z)
+    b, nr, S = z.shape
+    x = _bytes(n_tiles(b * scene.nv * nr * S) * X_TILE_BYTES, z.device)
+    call('cn_project_gather_fwd', ctypes.byref(scene.c), _ptr(ray_o), _ptr(ray_d), _ptr(z), nr, S, _ptr(x), _stream())
+    return x
+
+
+def project_gather_debug(scene: Scene, ray_o, ray_d, z):
+    ray_o, ray_d, z = _f32c(ray_o), _f32c(ray_d), _f32c(z)
+    b, nr, S = z.shape
+    dev = z.device
+    pix = torch.empty(b, scene.nv, nr, S, 2, dtype=torch.float32, device=dev)
+    corner = torch.empty(b, scene.nv, nr, S, 2, dtype=torch.int32, device=dev)
+    g = torch.empty(b, scene.nv, nr, S, 259, dtype=torch.float32, device=dev)
+    call('cn_project_gather_debug', ctypes.byref(scene.c), _ptr(ray_o), _ptr(ray_d), _ptr(z), nr, S, _ptr(pix),
+         _ptr(corner), _ptr(g), _stream())
+    return pix, corner, g
+
+
+def project_gather_bwd(scene: Scene, ray_o, ray_d, z, dx_tiles, d_features: Optional[torch.Tensor],
+                       dz: Optional[torch.Tensor]) -> None:
+    ray_o, ray_d, z = _f32c(ray_o), _f32c(ray_d), _f32c(z)
+    b, nr, S = z.shape
+    call('cn_project_gather_bwd', ctypes.byref(scene.c), _ptr(ray_o), _ptr(ray_d), _ptr(z), nr, S, _ptr(dx_tiles),
+         _ptr(d_features), _ptr(dz), _stream())
+
+
+def composite_fwd(z, rgbs):
+    z, rgbs = _f32c(z), _f32c(rgbs)
+    S = z.shape[-1]
+    n = z.numel() // S
+    dev = z.device
+    rgb = torch.empty(*z.shape[:-1], 3, dtype=torch.float32, device=dev)
+    depth = torch.empty(*z.shape[:-1], dtype=torch.float32, device=dev)
+    w = torch.empty_like(z)
+    call('cn_composite_fwd', _ptr(z), _ptr(rgbs), n, S, _ptr(rgb), _ptr(depth), _ptr(w), _stream())
+    return rgb, depth, w
+
+
+def composite_bwd(z, rgbs, d_rgb, d_depth=None, d_weights=None, need_dz=False):
+    z, rgbs, d_rgb = _f32c(z), _f32c(rgbs), _f32c(d_rgb)
+    d_depth = None if d_depth is None else _f32c(d_depth)
+    d_weights = None if d_weights is None else _f32c(d_weights)
+    S = z.shape[-1]
+    n = z.numel() // S
+    d_y = torch.empty(*z.shape, 4, dtype=torch.float32, device=z.device)
+    dz = torch.empty_like(z) if need_dz else None
+    call('cn_composite_bwd', _ptr(z), _ptr(rgbs), n, S, _ptr(d_rgb), _ptr(d_depth), _ptr(d_weights), _ptr(d_y),
+         _ptr(dz), _stream())
+    return d_y, dz
+
+
+def pack_weights(params: torch.Tensor) -> torch.Tensor:
+    params = _f32c(params)
+    assert params.numel() == _abi.NET_PARAMS
+    packed = _bytes(PACKED_BYTES, params.device)
+    call('cn_pack_weights', _ptr(params), _ptr(packed), _stream())
+    return packed
+
+
+def mlp_feature_fwd(packed, x_tiles, save_acts: bool):
+    nt = x_tiles.numel() // X_TILE_BYTES
+    h3 = _bytes(nt * ACT_TILE_BYTES, x_tiles.device)
+    acts = _bytes(nt * 6 * ACT_TILE_BYTES, x_tiles.device) if save_acts else None
+    call('cn_mlp_feature_fwd', _ptr(packed), _ptr(x_tiles), nt, _ptr(h3), _ptr(acts), _stream())
+    return h3, acts
+
+
+def mlp_fusion_fwd(packed, h3_tiles, b: int, nv: int, save_acts: bool):
+    nt = h3_tiles.numel() // ACT_TILE_BYTES
+    assert nt % (b * nv) == 0
+    tpv = nt // (b * nv)
+    rgbs = torch.empty(b * tpv * TILE_ROWS, 4, dtype=torch.float32, device=h3_tiles.device)
+    acts = _bytes(b * tpv * 7 * ACT_TILE_BYTES, h3_tiles.device) if save_acts else None
+    call('cn_mlp_fusion_fwd', _ptr(packed), _ptr(h3_tiles), b, nv, tpv, _ptr(rgbs), _ptr(acts), _stream())
+    return rgbs, acts
+
+
+def mlp_readout_bwd(params, d_y, acts, act_stride: int, act_index: int, grad):
+    nt = d_y.numel() // (4 * TILE_ROWS)
+    g = _bytes(nt * ACT_TILE_BYTES, d_y.device)
+    call('cn_mlp_readout_bwd', _ptr(params), _ptr(d_y), _ptr(acts), act_stride, act_index, nt, _ptr(g), _ptr(grad),
+         _stream())
+    return g
+
+
+def mlp_block_bwd(packed, blk: int, acts, act_stride: int, act_index: int, gy_tiles, grad, gh_tiles=None):
+    nt = gy_tiles.numel() // ACT_TILE_BYTES
+    if gh_tiles is None:
+        gh_tiles = gy_tiles
+    call('cn_mlp_block_bwd', _ptr(packed), blk, _ptr(acts), act_stride, act_index, nt, _ptr(gy_tiles),
+         _ptr(gh_tiles), _ptr(grad), _stream())
+    return gh_tiles
+
+
+def mlp_mean_bwd(gm_tiles, b: int, nv: int):
+    nt = gm_tiles.numel() // ACT_TILE_BYTES
+    tpv = nt // b
+    out = _bytes(nt * nv * ACT_TILE_BYTES, gm_tiles.device)
+    call('cn_mlp_mean_bwd', _ptr(gm_tiles), b, nv, tpv, _ptr(out), _stream())
+    return out
+
+
+def mlp_l0_dgrad(packed, g0_tiles):
+    nt = g0_tiles.numel() // ACT_TILE_BYTES
+    dx = _bytes(nt * X_TILE_BYTES, g0_tiles.device)
+    call('cn_mlp_l0_dgrad', _ptr(packed), _ptr(g0_tiles), nt, _ptr(dx), _stream())
+    return dx
+
+
+def mlp_l0_wgrad(x_tiles, g0_tiles, grad):
+    nt = g0_tiles.numel() // ACT_TILE_BYTES
+    call('cn_mlp_l0_wgrad', _ptr(x_tiles), _ptr(g0_tiles), nt, _ptr(grad), _stream())
+
+
+def probe_umma(a_img: torch.Tensor, b_img: torch.Tensor, n_mma: int, a_mn: bool, b_mn: bool, a_lbo: int, a_sbo: int,
+               a_kstep: int, b_lbo: int, b_sbo: int, b_kstep: int) -> torch.Tensor:
+    d = torch.zeros(128, 128, dtype=torch.float32, device=a_img.device)
+    call('cn_probe_umma', _ptr(a_img), a_img.numel(), _ptr(b_img), b_img.numel(), n_mma, int(a_mn), int(b_mn), a_lbo,
+         a_sbo, a_kstep, b_lbo, b_sbo, b_kstep, _ptr(d), _stream())
+    return d

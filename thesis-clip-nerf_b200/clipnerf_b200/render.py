@@ -1,0 +1,110 @@
+"""Differentiable CLIP-NeRF render call on the sm_100a kernels.
+
+``render_rays`` is the replacement of ``MVVNeRFRenderer._call`` (reference
+``src/lib/mvnerf/model_v0.py:113-184``): coarse pass (stratified samples -> project / gather /
+posenc -> per-view MLP -> view mean + fusion MLP + readout -> composite), hierarchical resampling,
+fine pass; the backward walks the same chain in reverse, including the gradient that flows from the
+fine samples through the inverse-CDF sampler into the coarse net (no stop_gradient, quirk Q4).
+
+Random draws are explicit inputs (``u_strat``, ``u_pdf``)."""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import ops
+from ._abi import NET_PARAMS, TILE_ROWS
+
+
+class _Pass:
+    """Everything one (coarse or fine) pass keeps for its backward."""
+    __slots__ = ('z', 'x', 'acts_f', 'acts_u', 'rgbs', 'rgb', 'depth', 'weights', 'packed')
+
+
+def _pass_fwd(packed, scene: ops.Scene, ray_o, ray_d, z, save: bool) -> _Pass:
+    P = _Pass()
+    P.z, P.packed = z, packed
+    P.x = ops.project_gather_fwd(scene, ray_o, ray_d, z)
+    h3, P.acts_f = ops.mlp_feature_fwd(packed, P.x, save)
+    P.rgbs, P.acts_u = ops.mlp_fusion_fwd(packed, h3, scene.b, scene.nv, save)
+    P.rgb, P.depth, P.weights = ops.composite_fwd(z, P.rgbs.view(*z.shape, 4))
+    if not save:
+        P.x = None
+    return P
+
+
+def _pass_bwd(P: _Pass, params, grad, scene: ops.Scene, ray_o, ray_d, d_rgb, d_depth, d_weights, d_features,
+              need_dz: bool) -> Optional[torch.Tensor]:
+    d_y, dz = ops.composite_bwd(P.z, P.rgbs.view(*P.z.shape, 4), d_rgb, d_depth, d_weights, need_dz)
+    g = ops.mlp_readout_bwd(params, d_y, P.acts_u, 7, 6, grad)
+    for blk in (5, 4, 3):
+        ops.mlp_block_bwd(P.packed, blk, P.acts_u, 7, 2 * (blk - 3), g, grad)
+    gf = ops.mlp_mean_bwd(g, scene.b, scene.nv)
+    for blk in (2, 1, 0):
+        ops.mlp_block_bwd(P.packed, blk, P.acts_f, 6, 2 * blk, gf, grad)
+    ops.mlp_l0_wgrad(P.x, gf, grad)
+    if d_features is not None or need_dz:
+        dx = ops.mlp_l0_dgrad(P.packed, gf)
+        ops.project_gather_bwd(scene, ray_o, ray_d, P.z, dx, d_features, dz)
+    return dz
+
+
+class _RenderFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, params_c, params_f, features, images, intrinsics, extr_inv, ray_o, ray_d, u_strat, u_pdf,
+                near, far):
+        need_grad = any(ctx.needs_input_grad[:3])
+        scene = ops.Scene(images, features, intrinsics, extr_inv)
+        pk_c = ops.pack_weights(params_c)
+        pk_f = ops.pack_weights(params_f)
+        z_c = ops.sample_coarse(u_strat, near, far)
+        C = _pass_fwd(pk_c, scene, ray_o, ray_d, z_c, need_grad)
+        z_f, perm, _above = ops.sample_pdf_fwd(z_c, C.weights, u_pdf)
+        Fp = _pass_fwd(pk_f, scene, ray_o, ray_d, z_f, need_grad)
+        if need_grad:
+            ctx.scene, ctx.C, ctx.F = scene, C, Fp
+            ctx.perm, ctx.u_pdf = perm, ops._f32c(u_pdf)
+            ctx.rays = (ops._f32c(ray_o), ops._f32c(ray_d))
+            ctx.save_for_backward(params_c, params_f)
+        ctx.mark_non_differentiable()
+        return C.rgb, C.depth, Fp.rgb, Fp.depth
+
+    @staticmethod
+    def backward(ctx, d_rgb_c, d_depth_c, d_rgb_f, d_depth_f):
+        params_c, params_f = ctx.saved_tensors
+        scene, C, Fp = ctx.scene, ctx.C, ctx.F
+        ray_o, ray_d = ctx.rays
+        dev = params_c.device
+        need_feat = ctx.needs_input_grad[2]
+        g_c = torch.zeros(NET_PARAMS, dtype=torch.float32, device=dev)
+        g_f = torch.zeros(NET_PARAMS, dtype=torch.float32, device=dev)
+        d_features = torch.zeros_like(scene.features) if need_feat else None
+
+        def z_or_none(t):
+            return None if t is None else t.contiguous()
+
+        d_rgb_f = torch.zeros_like(Fp.rgb) if d_rgb_f is None else d_rgb_f
+        d_rgb_c = torch.zeros_like(C.rgb) if d_rgb_c is None else d_rgb_c
+        # fine pass first: its dz feeds the coarse weights through the inverse-CDF sampler
+        dz_f = _pass_bwd(Fp, params_f, g_f, scene, ray_o, ray_d, d_rgb_f, z_or_none(d_depth_f), None, d_features, True)
+        dw_c = ops.sample_pdf_bwd(C.z, C.weights, ctx.u_pdf, ctx.perm, dz_f)
+        _pass_bwd(C, params_c, g_c, scene, ray_o, ray_d, d_rgb_c, z_or_none(d_depth_c), dw_c, d_features, False)
+        ctx.C = ctx.F = ctx.scene = None
+        return (g_c, g_f, d_features) + (None,) * 9
+
+
+def render_rays(params_coarse: torch.Tensor, params_fine: torch.Tensor, inputs, combined_features: torch.Tensor,
+                u_strat: torch.Tensor, u_pdf: torch.Tensor, near: float, far: float
+                ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
+    """(rgb [b,nr,3], depth [b,nr], fine_rgb, fine_depth) = _call(inputs, features).
+
+    inputs: the 5-tuple of ``MVNeRFDataGenerator.get_input`` as CUDA tensors
+    (ray_o [b,nr,3], ray_d [b,nr,3], images [b,nv,H,W,3] in [0,1], K [b,nv,4,4], E^-1 [b,nv,4,4]);
+    ``params_*``: flat parameter vectors (``params.py``); n_samples is fixed at 64 coarse + 128 fine
+    (``u_strat`` / ``u_pdf`` are [b, nr, 64]); nr must be even (tiles of 128 rows)."""
+    ray_o, ray_d, images, K, Einv = inputs
+    assert u_strat.shape[-1] == 64 and u_pdf.shape[-1] == 64, 'n_samples is fixed at 64 (sample_pdf kernel)'
+    assert (ray_o.shape[1] * 64) % TILE_ROWS == 0, 'n_rays must be even'
+    return _RenderFn.apply(params_coarse, params_fine, combined_features, images, K, Einv, ray_o, ray_d, u_strat,
+                           u_pdf, float(near), float(far))

@@ -1,0 +1,30 @@
+// Host-side plumbing of the C ABI: version, thread-local error text, launch checking.
+#include <cstdarg>
+#include <cstdio>
+
+#include "common.cuh"
+
+namespace cn {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int check_launch(const char *what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return (int)e;
+  }
+  return 0;
+}
+
+}  // namespace cn
+
+extern "C" int cn_abi_version(void) { return CN_ABI_VERSION; }
+extern "C" const char *cn_last_error(void) { return cn::g_err; }
