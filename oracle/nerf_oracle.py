@@ -369,40 +369,71 @@ def init_params(seed: int, bias_std: float = 0.0, dtype=torch.float32) -> Dict[s
     return p
 
 
+class _RoundBF16(torch.autograd.Function):
+    """round-to-nearest-even to bfloat16 with a straight-through gradient."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.to(torch.bfloat16).to(x.dtype)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g
+
+
+def _ident(x):
+    return x
+
+
+def _quantizer(quant: Optional[str]):
+    """``quant='bf16'`` makes the oracle round exactly where the CUDA path stores bf16 tensor-core
+    operands (MLP input rows, weights, ReLU outputs, the per-view stage output); everything else
+    (biases, residual stream, accumulation, readout) stays in the working dtype.  ``None`` is the
+    reference's plain fp32 arithmetic.  The quantised variant exists to separate implementation
+    errors from the (much larger, ReLU-mask-flipping) effect of reduced operand precision."""
+    if quant is None:
+        return _ident
+    if quant == 'bf16':
+        return _RoundBF16.apply
+    raise ValueError(f'unknown quant {quant!r}')
+
+
 def resnet_mlp_block(x: Tensor, p: Dict[str, Tensor], prefix: str, activation: str = 'relu',
-                     shortcut_kernel: Optional[Tensor] = None) -> Tensor:
+                     shortcut_kernel: Optional[Tensor] = None, quant: Optional[str] = None) -> Tensor:
     """``layers.py:262-298``: y = shortcut(x) + act(act(x) W0 + b0) W1 + b1."""
+    q = _quantizer(quant)
     if activation == 'relu':
         act = F.relu
     elif activation == 'elu':
         act = F.elu
     else:
         raise ValueError(f'activation {activation} not supported')
-    r = act(x)
-    r = r @ p[f'{prefix}.layer_0.kernel'] + p[f'{prefix}.layer_0.bias']
-    r = act(r)
-    r = r @ p[f'{prefix}.layer_1.kernel'] + p[f'{prefix}.layer_1.bias']
+    r = q(act(x))
+    r = r @ q(p[f'{prefix}.layer_0.kernel']) + p[f'{prefix}.layer_0.bias']
+    r = q(act(r))
+    r = r @ q(p[f'{prefix}.layer_1.kernel']) + p[f'{prefix}.layer_1.bias']
     sc = x if shortcut_kernel is None else x @ shortcut_kernel
     return sc + r
 
 
 def mv_embedding_from_x(x: Tensor, p: Dict[str, Tensor], prefix: str, n_views: int,
-                        complete_output: bool = False):
+                        complete_output: bool = False, quant: Optional[str] = None):
     """Everything of ``MVResNetMLPNeRFEmbedding.call`` after the concat (``layers.py:363-379``):
     x [(b nv), ..., 379] -> Dense 379->128, 3 per-view blocks, mean over views, 3 fusion blocks."""
-    x = x @ p[f'{prefix}.layer_0.kernel'] + p[f'{prefix}.layer_0.bias']
+    q = _quantizer(quant)
+    x = q(x) @ q(p[f'{prefix}.layer_0.kernel']) + p[f'{prefix}.layer_0.bias']
     outputs = [x]
     for i in range(3):
-        outputs.append(resnet_mlp_block(outputs[-1], p, f'{prefix}.feature_blocks.{i}'))
-    pre = outputs[-1].reshape(-1, n_views, *outputs[-1].shape[1:])
+        outputs.append(resnet_mlp_block(outputs[-1], p, f'{prefix}.feature_blocks.{i}', quant=quant))
+    pre = q(outputs[-1]).reshape(-1, n_views, *outputs[-1].shape[1:])
     outputs.append(pre.mean(dim=1))
     for i in range(3):
-        outputs.append(resnet_mlp_block(outputs[-1], p, f'{prefix}.fusion_blocks.{i}'))
+        outputs.append(resnet_mlp_block(outputs[-1], p, f'{prefix}.fusion_blocks.{i}', quant=quant))
     return outputs if complete_output else outputs[-1]
 
 
 def mv_embedding(points: Tensor, dirs: Tensor, feats: Tensor, p: Dict[str, Tensor], prefix: str,
-                 n_views: int, complete_output: bool = False):
+                 n_views: int, complete_output: bool = False, quant: Optional[str] = None):
     """``MVResNetMLPNeRFEmbedding.call`` (``layers.py:354-379``).
 
     points/dirs [(b nv), nr, S, 3], feats [(b nv), nr, S, 259]; input order
@@ -410,7 +441,7 @@ def mv_embedding(points: Tensor, dirs: Tensor, feats: Tensor, p: Dict[str, Tenso
     enc_p = position_encoding(points)
     enc_d = position_encoding(dirs)
     x = torch.cat([enc_p, enc_d, feats], dim=-1)
-    return mv_embedding_from_x(x, p, prefix, n_views, complete_output)
+    return mv_embedding_from_x(x, p, prefix, n_views, complete_output, quant)
 
 
 def render_readout(x: Tensor, p: Dict[str, Tensor], prefix: str) -> Tuple[Tensor, Tensor]:
@@ -424,7 +455,7 @@ def render_readout(x: Tensor, p: Dict[str, Tensor], prefix: str) -> Tuple[Tensor
 # --------------------------------------------------------------------------
 
 
-def _render_pass(ray_o, ray_d, zs, norm_images, feats, K, Einv, p, net, n_views):
+def _render_pass(ray_o, ray_d, zs, norm_images, feats, K, Einv, p, net, n_views, quant=None):
     b, nr, S = zs.shape
     pts = ray_o[:, :, None, :] + zs[..., None] * ray_d[:, :, None, :]
     pix, cam = compute_pixel_in_image_mv(pts, K, Einv)
@@ -433,7 +464,7 @@ def _render_pass(ray_o, ray_d, zs, norm_images, feats, K, Einv, p, net, n_views)
     rep_dirs = cam_dirs[:, :, :, None, :].expand(-1, -1, -1, S, -1).reshape(b * n_views, nr, S, 3)
     cam3 = cam.reshape(b * n_views, nr, S, 4)[..., :3]
     g = g.reshape(b * n_views, nr, S, -1)
-    emb = mv_embedding(cam3, rep_dirs, g, p, f'{net}_embedding', n_views)
+    emb = mv_embedding(cam3, rep_dirs, g, p, f'{net}_embedding', n_views, quant=quant)
     chroma, density = render_readout(emb, p, f'{net}_readout')
     rgb, depth, weights = volumetric_render(zs, density, chroma)
     return rgb, depth, weights, chroma, density
@@ -441,12 +472,12 @@ def _render_pass(ray_o, ray_d, zs, norm_images, feats, K, Einv, p, net, n_views)
 
 def mvnerf_call(inputs: Sequence[Tensor], combined_features: Tensor, p: Dict[str, Tensor], *,
                 near: float, far: float, n_samples: int, u_strat: Tensor, u_pdf: Tensor,
-                return_aux: bool = False):
+                return_aux: bool = False, quant: Optional[str] = None):
     """``MVVNeRFRenderer._call`` (``model_v0.py:113-184``).
 
     inputs = (ray_o [b,nr,3], ray_d [b,nr,3], images [b,nv,H,W,3] in [0,1],
     K [b,nv,4,4], E^-1 [b,nv,4,4]); combined_features [b,nv,H,W,256].
-    No ``stop_gradient`` anywhere (quirk Q4).
+    No ``stop_gradient`` anywhere (quirk Q4).  ``quant``: see ``_quantizer`` (None = reference).
     Returns (rgb, depth, fine_rgb, fine_depth).
     """
     ray_o, ray_d, images, K, Einv = inputs
@@ -454,14 +485,14 @@ def mvnerf_call(inputs: Sequence[Tensor], combined_features: Tensor, p: Dict[str
     norm_images = images * 2 - 1.0
     _, z = sample_along_ray(ray_o, ray_d, near, far, n_samples, u_strat)
     rgb, depth, weights, _, _ = _render_pass(ray_o, ray_d, z, norm_images, combined_features,
-                                             K, Einv, p, 'coarse', n_views)
+                                             K, Einv, p, 'coarse', n_views, quant)
     z_mid = 0.5 * (z[..., 1:] + z[..., :-1])
     probs = weights[..., 1:-1]
     z_samples, above, below = sample_pdf(z_mid, probs, n_samples, u_pdf, return_indices=True)
     all_zs = torch.cat([z, z_samples], dim=-1)
     all_zs, perm = torch.sort(all_zs, dim=-1, stable=True)
     fine_rgb, fine_depth, fine_w, _, _ = _render_pass(ray_o, ray_d, all_zs, norm_images, combined_features,
-                                                      K, Einv, p, 'fine', n_views)
+                                                      K, Einv, p, 'fine', n_views, quant)
     if return_aux:
         aux = dict(z=z, weights=weights, z_samples=z_samples, above=above, below=below,
                    all_zs=all_zs, perm=perm.to(torch.int32), fine_weights=fine_w)

@@ -17,8 +17,8 @@ def pytest_configure(config):
 def rel_err(a, b):
     """normalised max error  max|a-b| / max|b|  (the tolerance metric of BASELINE.json)."""
     import torch
-    a = torch.as_tensor(a).double().cpu()
-    b = torch.as_tensor(b).double().cpu()
+    a = torch.as_tensor(a).detach().double().cpu()
+    b = torch.as_tensor(b).detach().double().cpu()
     return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
 
 

@@ -21,33 +21,108 @@ def _run(cuda, sc, named, need_feat_grad=True):
     return out, pc, pf, feats
 
 
+def _report(tag, errs, tol_out=1e-2, tol_grad=2e-2, skip=()):
+    for k, v in errs.items():
+        print(f'[{tag}] {k:62s} {v:.3e}')
+    bad = {k: v for k, v in errs.items()
+           if k not in skip and not v < (tol_grad if k.startswith('grad') else tol_out)}
+    assert not bad, bad
+
+
 @pytest.mark.parametrize('nv', [1, 3])
-def test_render_forward_backward(cuda, nv):
+def test_coarse_pass_gradients(cuda, nv):
+    """loss = MSE(coarse rgb): stratified z is identical on both sides, so every coarse-net
+    gradient and the feature-map gradient must agree with the (bf16-operand) oracle."""
     from clipnerf_b200 import params
     from oracle import nerf_oracle as O
     sc = O.synthetic_scene(11, 1, nv, 32, 48, 64)
     named = O.init_params(5, bias_std=0.02)
-    # oracle in fp32 (the reference's dtype), gradients by autograd
     p = {k: v.clone().requires_grad_(True) for k, v in named.items()}
     feats = sc['features'].clone().requires_grad_(True)
-    ref, aux = O.mvnerf_call(sc['inputs'], feats, p, near=NEAR, far=FAR, n_samples=64, u_strat=sc['u_strat'],
-                             u_pdf=sc['u_pdf'], return_aux=True)
-    O.train_loss(ref, sc['target']).backward()
-
+    ref = O.mvnerf_call(sc['inputs'], feats, p, near=NEAR, far=FAR, n_samples=64, u_strat=sc['u_strat'],
+                        u_pdf=sc['u_pdf'], quant='bf16')
+    (O.mse(sc['target'], ref[0]) + 0.1 * ref[1].mean()).backward()
     out, pc, pf, fd = _run(cuda, sc, named)
-    names = ('rgb', 'depth', 'fine_rgb', 'fine_depth')
-    for n_, a, b_ in zip(names, out, ref):
-        e = rel_err(a, b_.detach())
-        assert e < 1e-2, f'{n_}: rel err {e}'
     tgt = sc['target'].to(cuda)
-    loss = torch.mean((out[0] - tgt) ** 2) + torch.mean((out[2] - tgt) ** 2)
-    loss.backward()
-    for net, flat in (('coarse', pc), ('fine', pf)):
-        for name, gv in params.to_named(flat.grad.cpu(), net).items():
-            e = rel_err(gv, p[name].grad)
-            assert e < 2e-2, f'{name}: grad rel err {e}'
-    e = rel_err(fd.grad, feats.grad)
-    assert e < 2e-2, f'feature-map grad rel err {e}'
+    (torch.mean((out[0] - tgt) ** 2) + 0.1 * out[1].mean()).backward()
+    errs = {'rgb': rel_err(out[0], ref[0]), 'depth': rel_err(out[1], ref[1])}
+    for name, gv in params.to_named(pc.grad.cpu(), 'coarse').items():
+        errs['grad ' + name] = rel_err(gv, p[name].grad)
+    errs['grad features'] = rel_err(fd.grad, feats.grad)
+    assert float(pf.grad.abs().max()) == 0.0
+    _report(f'coarse nv={nv}', errs)
+
+
+@pytest.mark.parametrize('nv', [1, 3])
+def test_fine_pass_and_sampler_gradients(cuda, nv):
+    """Fine pass + hierarchical sampler with the SAME coarse weights on both sides (so z_fine is
+    bit-identical): fine-net gradients, feature-map gradient and the gradient that reaches the
+    coarse weights through sort -> inverse CDF (no stop_gradient, model_v0.py:153-158).
+
+    This path is tested with shared weights because, end to end, it is ill-conditioned in the
+    reference itself: a 1e-4 relative change of the coarse net moves the fine samples by ~1e-4 m,
+    i.e. ~0.1 rad of phase at the top posenc frequency, and changes this gradient by ~20 %."""
+    from clipnerf_b200 import ops, params, render
+    from oracle import nerf_oracle as O
+    sc = O.synthetic_scene(17, 1, nv, 32, 48, 64)
+    named = O.init_params(9, bias_std=0.02)
+    i_ro, i_rd, img, K, E = sc['inputs']
+    g = torch.Generator().manual_seed(3)
+    _, z_c = O.sample_along_ray(i_ro, i_rd, NEAR, FAR, 64, sc['u_strat'])
+    w_c = (torch.rand(1, 32, 64, generator=g) ** 4 * 0.2)
+    # ---- oracle
+    p = {k: v.clone().requires_grad_(True) for k, v in named.items()}
+    feats = sc['features'].clone().requires_grad_(True)
+    w_leaf = w_c.clone().requires_grad_(True)
+    zs = O.sample_pdf(0.5 * (z_c[..., 1:] + z_c[..., :-1]), w_leaf[..., 1:-1], 64, sc['u_pdf'])
+    all_zs, _ = torch.sort(torch.cat([z_c, zs], -1), dim=-1, stable=True)
+    rgb_r, depth_r, _, _, _ = O._render_pass(i_ro, i_rd, all_zs, img * 2 - 1.0, feats, K, E, p, 'fine', nv, 'bf16')
+    (O.mse(sc['target'], rgb_r) + 0.1 * depth_r.mean()).backward()
+    # ---- CUDA, from the same building blocks render_rays uses
+    ro, rd = i_ro.to(cuda), i_rd.to(cuda)
+    scene = ops.Scene(img.to(cuda), sc['features'].to(cuda), K.to(cuda), E.to(cuda))
+    pf = params.from_named(named, 'fine').to(cuda)
+    z_f, perm, _ = ops.sample_pdf_fwd(z_c.to(cuda), w_c.to(cuda), sc['u_pdf'].to(cuda))
+    assert torch.equal(z_f.cpu(), all_zs.detach())
+    Fp = render._pass_fwd(ops.pack_weights(pf), scene, ro, rd, z_f, True)
+    tgt = sc['target'].to(cuda)
+    d_rgb = 2.0 * (Fp.rgb - tgt) / tgt.numel()
+    d_depth = torch.full_like(Fp.depth, 0.1 / Fp.depth.numel())
+    g_f = torch.zeros_like(pf)
+    d_feat = torch.zeros_like(scene.features)
+    dz_f = render._pass_bwd(Fp, pf, g_f, scene, ro, rd, d_rgb, d_depth, None, d_feat, True)
+    dw_c = ops.sample_pdf_bwd(z_c.to(cuda), w_c.to(cuda), sc['u_pdf'].to(cuda), perm, dz_f)
+    errs = {'fine_rgb': rel_err(Fp.rgb, rgb_r), 'fine_depth': rel_err(Fp.depth, depth_r)}
+    for name, gv in params.to_named(g_f.cpu(), 'fine').items():
+        errs['grad ' + name] = rel_err(gv, p[name].grad)
+    errs['grad features'] = rel_err(d_feat, feats.grad)
+    errs['grad coarse weights (through the sampler)'] = rel_err(dw_c, w_leaf.grad)
+    _report(f'fine nv={nv}', errs)
+
+
+def test_render_end_to_end(cuda):
+    """Whole _call, both losses.  Outputs and fine-net gradients are asserted; the coarse-net and
+    feature-map gradients contain the ill-conditioned sampler path (see above) and are reported."""
+    from clipnerf_b200 import params
+    from oracle import nerf_oracle as O
+    for quant in ('bf16', None):
+        sc = O.synthetic_scene(13, 1, 3, 64, 48, 64)
+        named = O.init_params(7, bias_std=0.02)
+        p = {k: v.clone().requires_grad_(True) for k, v in named.items()}
+        feats = sc['features'].clone().requires_grad_(True)
+        ref = O.mvnerf_call(sc['inputs'], feats, p, near=NEAR, far=FAR, n_samples=64, u_strat=sc['u_strat'],
+                            u_pdf=sc['u_pdf'], quant=quant)
+        O.train_loss(ref, sc['target']).backward()
+        out, pc, pf, fd = _run(cuda, sc, named)
+        tgt = sc['target'].to(cuda)
+        (torch.mean((out[0] - tgt) ** 2) + torch.mean((out[2] - tgt) ** 2)).backward()
+        errs = {n_: rel_err(a, b_) for n_, a, b_ in zip(('rgb', 'depth', 'fine_rgb', 'fine_depth'), out, ref)}
+        for net, flat in (('coarse', pc), ('fine', pf)):
+            for name, gv in params.to_named(flat.grad.cpu(), net).items():
+                errs[f'grad {name}'] = rel_err(gv, p[name].grad)
+        errs['grad features'] = rel_err(fd.grad, feats.grad)
+        skip = [k for k in errs if 'coarse' in k or 'features' in k]
+        _report(f'e2e quant={quant}', errs, skip=skip)
 
 
 def test_render_inference_matches_training_forward(cuda):

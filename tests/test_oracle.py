@@ -1,0 +1,203 @@
+"""CPU tests of the oracle: closed-form cases, reference quirks and fp64 gradient
+checks.  The reference ships no tests; these pin the restatement itself."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import nerf_oracle as O
+
+NEAR, FAR = 0.3, 1.3
+
+
+def test_get_rays_pixel_order_and_normalisation():
+    W, H = 8, 6
+    K = np.array([[10.0, 0, W / 2], [0, 10.0, H / 2], [0, 0, 1]], dtype=np.float32)
+    pose = O.polar_pose(0.3, 0.7, 0.8)
+    o, d = O.get_rays(W, H, pose, K)
+    assert o.shape == (H, W, 3) and d.shape == (H, W, 3)
+    assert np.allclose(np.linalg.norm(d, axis=-1), 1.0)
+    assert np.allclose(o, pose[:3, 3])
+    # row-major grid: element [v, u] is pixel (u = column, v = row)
+    u, v = 5.0, 2.0
+    ref = pose[:3, :3] @ np.linalg.inv(K) @ np.array([u, v, 1.0])
+    assert np.allclose(d[2, 5], ref / np.linalg.norm(ref))
+
+
+def test_bbox_biased_sample_and_target_are_row_col():
+    rs = np.random.RandomState(0)
+    H, W = 12, 20
+    rays = O.bbox_biased_sample(50, np.array([0, 0, H, W]), H, W, rng=rs)
+    assert rays.shape == (50, 2) and rays[:, 0].max() < H and rays[:, 1].max() < W
+    color = rs.randint(0, 255, (H, W, 4)).astype(np.uint8)
+    t = O.get_target(color, rays)
+    assert np.allclose(t[3], color[rays[3, 0], rays[3, 1], :3] / 255.0)
+
+
+def test_camera_parameters_pad_and_inverse():
+    pose = O.polar_pose(1.0, 0.5, 0.9)
+    e_inv, k = O.camera_parameters(dict(pose=pose, intrinsics=np.arange(9.0)))
+    assert k.shape == (4, 4) and k[3, 3] == 1 and np.all(k[:3, 3] == 0) and np.all(k[3, :3] == 0)
+    assert np.allclose(e_inv @ pose, np.eye(4), atol=1e-12)
+
+
+def test_quantize_render_truncates():
+    rgb = np.array([[0.999, 0.5, 1.2], [-0.1, 0.00392, 0.00391]] * 2, dtype=np.float32)   # 4 pixels
+    depth = np.array([0.0, 1.0, 0.5, 0.25], dtype=np.float32)
+    q, dq = O.quantize_render(rgb, depth, (2, 2))
+    assert q.dtype == np.uint8 and q[0, 0].tolist() == [254, 127, 255] and q[0, 1].tolist() == [0, 0, 0]
+    assert dq.reshape(-1).tolist() == [0, 255, 127, 63]
+
+
+def test_sample_along_ray_strata():
+    g = torch.Generator().manual_seed(0)
+    u = torch.rand(2, 5, 64, generator=g)
+    o = torch.zeros(2, 5, 3)
+    d = torch.tensor([0.0, 0.0, 1.0]).expand(2, 5, 3)
+    pts, z = O.sample_along_ray(o, d, NEAR, FAR, 64, u)
+    step = (FAR - NEAR) / 64
+    lo = torch.tensor([NEAR + i * step for i in range(64)], dtype=torch.float32)
+    assert torch.all(z >= lo) and torch.all(z <= lo + step * 1.0001)
+    assert torch.equal(pts[..., 2], z) and torch.all(z[..., 1:] >= z[..., :-1])
+
+
+def test_projection_identity_camera():
+    K = torch.tensor([[100.0, 0, 16, 0], [0, 100.0, 12, 0], [0, 0, 1, 0], [0, 0, 0, 1]]).view(1, 1, 4, 4)
+    E = torch.eye(4).view(1, 1, 4, 4)
+    pts = torch.tensor([[[[0.1, -0.05, 2.0], [0.0, 0.0, -1.0]]]])           # second point is behind the camera
+    pix, cam = O.compute_pixel_in_image_mv(pts, K, E)
+    assert torch.allclose(pix[0, 0, 0, 0], torch.tensor([16 + 100 * 0.1 / 2, 12 - 100 * 0.05 / 2]))
+    assert torch.allclose(cam[0, 0, 0, 0], torch.tensor([0.1, -0.05, 2.0, 1.0]))
+    # q.z = -1 -> max(q.z, 1e-8) -> huge ratio -> clipped to +-1e6 (quirk Q7)
+    assert torch.all(pix[0, 0, 0, 1].abs() <= 1e6)
+
+
+def test_direction_uses_homogeneous_one():
+    """quirk Q1: the camera-frame direction is R d + t, not R d."""
+    E = torch.eye(4).view(1, 1, 4, 4).clone()
+    E[0, 0, :3, 3] = torch.tensor([1.0, 2.0, 3.0])
+    d = torch.tensor([[[0.0, 0.0, 1.0]]])
+    out = O.world_to_camera_direction_vector_mv(d, E)
+    assert torch.allclose(out[0, 0, 0], torch.tensor([1.0, 2.0, 4.0]))
+
+
+def test_bilinear_constant_integer_and_border():
+    H, W, C = 5, 7, 3
+    grid = torch.arange(H * W * C, dtype=torch.float32).view(1, H, W, C)
+    const = torch.full((1, H, W, C), 2.5)
+    q = torch.tensor([[[1.3, 2.7], [3.0, 1.0], [-5.0, -5.0], [100.0, 100.0], [W - 1.0, H - 1.0]]])
+    assert torch.allclose(O.interpolate_bilinear(const, q), torch.full((1, 5, C), 2.5))
+    out = O.interpolate_bilinear(grid, q)
+    assert torch.allclose(out[0, 1], grid[0, 1, 3])                       # integer location: exact pixel
+    assert torch.allclose(out[0, 2], grid[0, 0, 0])                       # out of frustum: border, never zero
+    assert torch.allclose(out[0, 3], grid[0, H - 1, W - 1])
+    assert torch.allclose(out[0, 4], grid[0, H - 1, W - 1])               # floor clamped to size-2, alpha = 1
+    tl, tr, bl, br = grid[0, 2, 1], grid[0, 2, 2], grid[0, 3, 1], grid[0, 3, 2]
+    top, bot = 0.3 * (tr - tl) + tl, 0.3 * (br - bl) + bl
+    assert torch.allclose(out[0, 0], 0.7 * (bot - top) + top, atol=1e-5)
+
+
+def test_position_encoding_layout():
+    p = torch.tensor([[[[0.25, -0.5, 1.0]]]])
+    enc = O.position_encoding(p)
+    assert enc.shape[-1] == 60
+    f = np.float32(np.pi)
+    for c in range(3):
+        for k in range(10):
+            arg = np.float32(p[0, 0, 0, c].item()) * np.float32(f * 2 ** k)
+            assert abs(enc[0, 0, 0, c * 20 + 2 * k].item() - math.sin(arg)) < 1e-5
+            assert abs(enc[0, 0, 0, c * 20 + 2 * k + 1].item() - math.cos(arg)) < 1e-5
+
+
+def test_volumetric_render_uniform_sigma_closed_form():
+    S = 64
+    z = torch.linspace(NEAR, FAR, S).view(1, 1, S).double()
+    sigma = torch.full((1, 1, S), 3.0).double()
+    c = torch.full((1, 1, S, 3), 0.5).double()
+    rgb, depth, w = O.volumetric_render(z, sigma, c)
+    delta = (FAR - NEAR) / (S - 1)
+    T = torch.exp(-3.0 * (z - NEAR))
+    assert torch.allclose(w, (1 - math.exp(-3.0 * delta)) * T, atol=1e-8)
+    assert torch.allclose(rgb, 0.5 * w.sum(-1, keepdim=True).expand(1, 1, 3))
+    assert torch.allclose(depth, (w * z).sum(-1))
+    # last interval repeats the previous one; no background term: sum(w) < 1
+    assert float(w.sum()) < 1.0
+
+
+def test_sample_pdf_spike_and_out_of_range_corner():
+    z = torch.linspace(NEAR, FAR, 64).view(1, 1, 64)
+    bins = 0.5 * (z[..., 1:] + z[..., :-1])
+    w = torch.zeros(1, 1, 62)
+    w[..., 30] = 1.0
+    u = torch.linspace(0.01, 0.98, 64).view(1, 1, 64)
+    s, above, below = O.sample_pdf(bins, w, 64, u, return_indices=True)
+    assert torch.all(above == 31) and torch.all(below == 30)
+    assert torch.all(s >= bins[..., 30] - 1e-6) and torch.all(s <= bins[..., 31] + 1e-6)
+    # u >= cdf[62] -> above = 63 is out of range: the gather reads 0 (TF-GPU semantics, quirk Q5)
+    for seed in range(100):       # find weights whose fp32 cdf ends below 1 (else u < 1 can never reach it)
+        w2 = torch.rand(1, 1, 62, generator=torch.Generator().manual_seed(seed))
+        sw = w2 + 1e-5
+        cdf_last = float(O._seq_cumsum(sw / O._seq_cumsum(sw)[..., -1:])[0, 0, -1])
+        if cdf_last < 1.0:
+            break
+    assert cdf_last < 1.0
+    u2 = torch.full((1, 1, 64), cdf_last)
+    s2, above2, below2 = O.sample_pdf(bins, w2, 64, u2, return_indices=True)
+    assert torch.all(above2 == 63) and torch.all(below2 == 62)
+    cdf_b = cdf_last
+    expected = bins[..., 62] + (u2 - cdf_b) / 1.0 * (0.0 - bins[..., 62])
+    assert torch.allclose(s2, expected.expand_as(s2), atol=1e-6)
+
+
+def test_gradcheck_composite_and_sampler():
+    g = torch.Generator().manual_seed(1)
+    z = torch.sort(torch.rand(1, 2, 16, generator=g).double() + 0.3, dim=-1).values.requires_grad_(True)
+    sig = (torch.rand(1, 2, 16, generator=g).double() * 4 + 0.1).requires_grad_(True)
+    c = torch.rand(1, 2, 16, 3, generator=g).double().requires_grad_(True)
+    assert torch.autograd.gradcheck(lambda a, b_, c_: O.volumetric_render(a, b_, c_), (z, sig, c), atol=1e-6)
+    bins = torch.linspace(0.3, 1.3, 63).view(1, 1, 63).double()
+    w = (torch.rand(1, 1, 62, generator=g).double() + 0.05).requires_grad_(True)
+    u = torch.rand(1, 1, 64, generator=g).double()
+    assert torch.autograd.gradcheck(lambda w_: O.sample_pdf(bins, w_, 64, u), (w,), atol=1e-6)
+
+
+def test_gradcheck_bilinear_wrt_grid_and_queries():
+    g = torch.Generator().manual_seed(2)
+    grid = torch.rand(1, 4, 5, 3, generator=g).double().requires_grad_(True)
+    q = (torch.rand(1, 6, 2, generator=g).double() * torch.tensor([3.0, 2.0]) + 0.37).requires_grad_(True)
+    assert torch.autograd.gradcheck(lambda a, b_: O.interpolate_bilinear(a, b_), (grid, q), atol=1e-6)
+
+
+def test_call_end_to_end_and_no_stop_gradient():
+    """quirk Q4: the fine loss alone must reach the COARSE net through sort -> sample_pdf -> weights."""
+    sc = O.synthetic_scene(0, 1, 2, 4, 16, 20)
+    p = {k: v.clone().requires_grad_(True) for k, v in O.init_params(0, bias_std=0.02).items()}
+    out, aux = O.mvnerf_call(sc['inputs'], sc['features'], p, near=NEAR, far=FAR, n_samples=64,
+                             u_strat=sc['u_strat'], u_pdf=sc['u_pdf'], return_aux=True)
+    assert [tuple(o.shape) for o in out] == [(1, 4, 3), (1, 4), (1, 4, 3), (1, 4)]
+    assert aux['all_zs'].shape[-1] == 128 and torch.all(aux['all_zs'][..., 1:] >= aux['all_zs'][..., :-1])
+    assert int(aux['above'].min()) >= 1 and int(aux['above'].max()) <= 63
+    O.mse(sc['target'], out[2]).backward()
+    g = p['coarse_embedding.layer_0.kernel'].grad
+    assert g is not None and float(g.abs().max()) > 0
+    assert p['coarse_readout.output_layer.bias'].grad is not None
+
+
+def test_view_mean_is_b_major():
+    """quirk Q8: '(b nv)' flattening is b-major and fusion is a plain mean over views."""
+    p = O.init_params(1)
+    x = torch.randn(4, 2, 3, 379, generator=torch.Generator().manual_seed(0))     # (b=2, nv=2) flattened
+    outs = O.mv_embedding_from_x(x, p, 'coarse_embedding', 2, complete_output=True)
+    assert outs[3].shape[0] == 4 and outs[4].shape[0] == 2
+    assert torch.allclose(outs[4][1], 0.5 * (outs[3][2] + outs[3][3]), atol=1e-6)
+    assert len(outs) == 8
+
+
+def test_warmup_schedule_and_clip():
+    assert O.warmup_lr(0, 1e-4, 10000, 450000) == 0.0
+    assert abs(O.warmup_lr(5000, 1e-4, 10000, 450000) - 5e-5) < 1e-12
+    assert O.warmup_lr(10001, 1e-4, 10000, 450000) == 1e-4
+    assert abs(O.warmup_lr(450001, 1e-4, 10000, 450000) - 1e-5) < 1e-12
+    g = O.clip_gradients([torch.tensor([-3.0, 0.2, 7.0])], 1.0)[0]
+    assert g.tolist() == [-1.0, 0.20000000298023224, 1.0]

@@ -6,10 +6,10 @@ nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gp
 rc=0
 for f in tests/test_gpu_probe.py tests/test_gpu_kernels.py tests/test_gpu_mlp.py tests/test_gpu_render.py; do
   name=$(basename $f .py)
-  timeout 300 python -m pytest $f -q -m gpu -x --tb=short -rA > gpurun_out/$name.log 2>&1
+  timeout 300 python -m pytest $f -q -m gpu --tb=short -rA -s > gpurun_out/$name.log 2>&1
   r=$?
   echo "$name exit $r" | tee -a gpurun_out/summary.txt
-  tail -25 gpurun_out/$name.log
+  tail -60 gpurun_out/$name.log
   [ $r -ne 0 ] && rc=$r
 done
 exit $rc
