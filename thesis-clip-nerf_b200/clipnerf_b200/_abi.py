@@ -77,9 +77,23 @@ class CnError(RuntimeError):
     pass
 
 
+# kernels launched by each entry point (for launch accounting in bench.py)
+KERNELS_PER_CALL = {name: 1 for name in PROTOTYPES}
+KERNELS_PER_CALL.update({'cn_abi_version': 0, 'cn_last_error': 0, 'cn_mlp_l0_wgrad': 2})
+
+LAUNCHES = 0          # running count of kernel launches issued through the ABI
+TIMER = None          # optional callable(name) -> context manager, set by bench.py to time stages
+
+
 def call(name: str, *args):
+    global LAUNCHES
     lib = load()
-    rc = getattr(lib, name)(*args)
+    if TIMER is not None:
+        with TIMER(name):
+            rc = getattr(lib, name)(*args)
+    else:
+        rc = getattr(lib, name)(*args)
     if rc != 0:
         msg = lib.cn_last_error().decode('utf-8', 'replace')
         raise CnError(f'{name} failed (rc={rc}): {msg}')
+    LAUNCHES += KERNELS_PER_CALL[name]

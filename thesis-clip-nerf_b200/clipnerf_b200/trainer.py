@@ -1,0 +1,82 @@
+"""Training step of the NeRF MLPs on the sm_100a render path: the replacement of
+``MVVNeRFRenderer.train_step`` + ``optimize`` (reference ``src/lib/mvnerf/model_v0.py:186-197``,
+``src/lib/mvnerf/nerf_utils.py:8-12``) for the part of the model that lives on the hot path.
+
+One process per GPU.  All trainable NeRF variables of both nets live in ONE flat fp32 buffer
+``[2, NET_PARAMS]`` whose gradient is a single flat buffer as well, so data parallelism over ray
+shards is exactly one NCCL all-reduce per step (no collective is needed for rendering)."""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from . import params as P
+from ._abi import NET_PARAMS
+from .render import render_rays
+
+
+def warmup_lr(step: int, target_lr: float, warmup_steps: float = 10000.0, scale_down_after: float = 450000.0) -> float:
+    """``WarmupScheduler`` (nerf_utils.py:288-300) with the arguments of train_nerf.py:22."""
+    warmup_steps = max(1.0, float(warmup_steps))
+    if step <= warmup_steps:
+        return step / warmup_steps * target_lr
+    return target_lr if step <= scale_down_after else 0.1 * target_lr
+
+
+class RenderTrainer:
+    def __init__(self, device, seed: int = 0, target_lr: float = 1e-4, warmup_steps: float = 10000.0,
+                 clip: float = 1.0, bias_std: float = 0.0, process_group=None):
+        g = torch.Generator().manual_seed(seed)
+        flat = torch.stack([P.glorot_init(g, bias_std), P.glorot_init(g, bias_std)])
+        self.params = flat.to(device).requires_grad_(True)          # [2, NET_PARAMS]: coarse, fine
+        self.m = torch.zeros_like(self.params)
+        self.v = torch.zeros_like(self.params)
+        self.iterations = 0
+        self.target_lr, self.warmup_steps, self.clip = target_lr, warmup_steps, clip
+        self.beta1, self.beta2, self.eps = 0.9, 0.999, 1e-7           # tf.keras.optimizers.Adam defaults
+        self.group = process_group
+        self.world = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
+
+    @property
+    def coarse(self):
+        return self.params[0]
+
+    @property
+    def fine(self):
+        return self.params[1]
+
+    def loss_and_backward(self, inputs, features, target, u_strat, u_pdf, near, far):
+        """forward + backward of MSE(coarse) + MSE(fine) (model_v0.py:190-194); returns (loss, outputs)."""
+        self.params.grad = None
+        out = render_rays(self.params[0], self.params[1], inputs, features, u_strat, u_pdf, near, far)
+        loss = torch.mean((out[0] - target) ** 2) + torch.mean((out[2] - target) ** 2)
+        loss.backward()
+        return loss.detach(), out
+
+    def allreduce_gradients(self):
+        """the one collective of the path: mean of the flat gradient buffer over ray shards."""
+        if self.world > 1:
+            dist.all_reduce(self.params.grad, op=dist.ReduceOp.SUM, group=self.group)
+            self.params.grad.div_(self.world)
+
+    @torch.no_grad()
+    def apply_gradients(self):
+        """per-element clip to [-clip, clip] (nerf_utils.py:9-11) then Keras-style Adam."""
+        g = self.params.grad
+        if self.clip > 0:
+            g.clamp_(-self.clip, self.clip)
+        self.iterations += 1
+        t = self.iterations
+        lr = warmup_lr(t, self.target_lr, self.warmup_steps)
+        lr_t = lr * (1.0 - self.beta2 ** t) ** 0.5 / (1.0 - self.beta1 ** t)
+        self.m.mul_(self.beta1).add_(g, alpha=1.0 - self.beta1)
+        self.v.mul_(self.beta2).addcmul_(g, g, value=1.0 - self.beta2)
+        self.params.addcdiv_(self.m, self.v.sqrt().add_(self.eps), value=-lr_t)
+
+    def train_step(self, inputs, features, target, u_strat, u_pdf, near, far):
+        loss, _ = self.loss_and_backward(inputs, features, target, u_strat, u_pdf, near, far)
+        self.allreduce_gradients()
+        self.apply_gradients()
+        return loss
