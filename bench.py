@@ -96,15 +96,8 @@ class ClockSampler:
 
 def make_scene(seed, nr, nv, device=None, pinned=False):
     """synthetic scene of SURVEY.md 8(d): hemisphere cameras, random target-view pixels."""
-    from oracle import nerf_oracle as O   # input generator shared with the tests (not on the timed path)
-    sc = O.synthetic_scene(seed, 1, nv, nr, H, W, C)
-    if device is not None:
-        sc['features'] = sc['features'].to(device)
-    if pinned:
-        sc['inputs'] = tuple(t.pin_memory() for t in sc['inputs'])
-        for k in ('u_strat', 'u_pdf', 'target'):
-            sc[k] = sc[k].pin_memory()
-    return sc
+    from clipnerf_b200 import synthetic
+    return synthetic.scene(seed, nr, nv, H, W, C, device=device, pin=pinned)
 
 
 # ----------------------------------------------------------------------------------------------

@@ -82,6 +82,10 @@ int cn_sample_coarse(const float *u, float *z, int64_t n_rays, int32_t S, double
  *   above [n, 64] u8 : inverse-CDF bin index of each draw (1..63).                      */
 int cn_sample_pdf_fwd(const float *z_c, const float *w_c, const float *u, int64_t n_rays,
                       float *z_fine, uint8_t *perm, uint8_t *above, void *stream);
+/* op-level sample_pdf with the reference's own signature (nerf_utils.py:143): bins [n,63],
+ * weights [n,62], u [n,64] -> samples [n,64] (unsorted), above [n,64] int32 (nullable).        */
+int cn_sample_pdf(const float *bins, const float *weights, const float *u, int64_t n_rays,
+                  float *samples, int32_t *above, void *stream);
 /* gradient of the above w.r.t. the coarse weights (no stop_gradient in the reference,
  * model_v0.py:153-158):  dz_fine [n,128] -> dw_c [n,64] (accumulated, +=).              */
 int cn_sample_pdf_bwd(const float *z_c, const float *w_c, const float *u, const uint8_t *perm,
@@ -96,11 +100,20 @@ int cn_sample_pdf_bwd(const float *z_c, const float *w_c, const float *u, const 
  * [feat 0..255 | posenc(p_cam) 60 | posenc(d_cam) 60 | 2*img-1 (3) | 0 (5)].          */
 int cn_project_gather_fwd(const CnScene *scene, const float *ray_o, const float *ray_d,
                           const float *z, int32_t nr, int32_t S, void *x_tiles, void *stream);
-/* fp32 debug / parity view of the same computation: pix [b,nv,nr,S,2],
- * corner (x0,y0) int32 [b,nv,nr,S,2], gathered [b,nv,nr,S,259] in reference order.    */
+/* fp32 op-level view of the same computation in the reference's tensor layouts
+ * (compute_pixel_in_image_mv + get_projection_features_mv): pix [b,nv,nr,S,2],
+ * corner (x0,y0) int32 [b,nv,nr,S,2], gathered [b,nv,nr,S,259] (nullable),
+ * cam [b,nv,nr,S,4] camera-frame homogeneous points (nullable).                       */
 int cn_project_gather_debug(const CnScene *scene, const float *ray_o, const float *ray_d,
                             const float *z, int32_t nr, int32_t S, float *pix, int32_t *corner,
-                            float *gathered, void *stream);
+                            float *gathered, float *cam, void *stream);
+/* tensorflow_addons.image.interpolate_bilinear(grid [B,H,W,C], query [B,N,2], 'xy')
+ * -> out [B,N,C]  (call site nerf_utils.py:282; edge clamp, alpha clamp)              */
+int cn_interpolate_bilinear(const float *grid, const float *query, int32_t B, int32_t H, int32_t W,
+                            int32_t C, int64_t N, float *out, void *stream);
+/* position_encoding (nerf_utils.py:108-126): pos [n,D] -> out [n, D*n_freq*2]         */
+int cn_position_encoding(const float *pos, int64_t n, int32_t D, int32_t n_freq, float freq0,
+                         float *out, void *stream);
 /* backward: dX tile images -> scatter-add into d_features [b,nv,H,W,256] (nullable)
  * and dz [b,nr,S] (nullable, +=) through bilinear coordinates and posenc(p_cam).       */
 int cn_project_gather_bwd(const CnScene *scene, const float *ray_o, const float *ray_d,

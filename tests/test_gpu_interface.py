@@ -1,0 +1,143 @@
+"""The reference's module surface on the GPU: op-level functions of nerf_utils.py with their own
+signatures, and MVVNeRFRenderer / render_view as train_nerf.py uses them."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+NEAR, FAR = 0.3, 1.3
+
+
+def test_op_level_functions_match_oracle(cuda):
+    from oracle import nerf_oracle as O
+    from src.lib.mvnerf import nerf_utils as U
+    from src.lib.mvnerf.model_v0 import MVVNeRFRenderer
+    sc = O.synthetic_scene(21, 2, 3, 16, 24, 32)
+    ro, rd, img, K, E = sc['inputs']
+    d = lambda t: t.to(cuda)  # noqa: E731
+    pts_r, z_r = O.sample_along_ray(ro, rd, NEAR, FAR, 64, sc['u_strat'])
+    pts, z = U.sample_along_ray(d(ro), d(rd), NEAR, FAR, 2, 16, 64, u=d(sc['u_strat']))
+    assert torch.equal(z.cpu(), z_r) and rel_err(pts, pts_r) < 1e-6
+    pix_r, cam_r = O.compute_pixel_in_image_mv(pts_r, K, E)
+    pix, cam = U.compute_pixel_in_image_mv(d(pts_r), d(K), d(E))
+    assert torch.equal(pix.cpu(), pix_r) and torch.equal(cam.cpu(), cam_r)
+    dirs_r = O.world_to_camera_direction_vector_mv(rd, E)
+    dirs = U.world_to_camera_direction_vector_mv(d(rd), d(E), 3)
+    assert torch.equal(dirs.cpu(), dirs_r)
+    g_r = O.get_projection_features_mv(img * 2 - 1.0, sc['features'], pix_r)
+    g = U.get_projection_features_mv(d(img * 2 - 1.0), d(sc['features']), d(pix_r), 16, 64, 2)
+    assert torch.equal(g.cpu(), g_r)
+    enc_r = O.position_encoding(cam_r[..., :3].reshape(6, 16, 64, 3))
+    enc = U.position_encoding(d(cam_r[..., :3].reshape(6, 16, 64, 3)), 10, np.pi)
+    assert enc.shape == enc_r.shape and float((enc.cpu() - enc_r).abs().max()) < 2e-4
+    w = torch.rand(2, 16, 62, generator=torch.Generator().manual_seed(1))
+    bins = 0.5 * (z_r[..., 1:] + z_r[..., :-1])
+    s_r = O.sample_pdf(bins, w, 64, sc['u_pdf'])
+    s = U.sample_pdf(d(bins), d(w), 64, u=d(sc['u_pdf']))
+    assert torch.equal(s.cpu(), s_r)
+    sig = torch.rand(2, 16, 64) * 10
+    col = torch.rand(2, 16, 64, 3)
+    rgb_r, dep_r, w_r = O.volumetric_render(z_r, sig, col)
+    rgb, dep, ww = MVVNeRFRenderer.volumetric_render(d(z_r), d(sig), d(col))
+    assert rel_err(rgb, rgb_r) < 1e-5 and rel_err(dep, dep_r) < 1e-5 and rel_err(ww, w_r) < 1e-5
+    a = U.sigma_to_alpha(d(sig), d(z_r))
+    assert rel_err(a, O.sigma_to_alpha(sig, z_r)) < 1e-6
+
+
+def _model(cuda, nv, named=None):
+    from clipnerf_b200 import params
+    from src.lib.mvnerf.model_v0 import MVVNeRFRenderer
+    m = MVVNeRFRenderer(n_rays_train=32, n_rays_infer=32, n_views=nv, near=NEAR, far=FAR,
+                        original_image_size=(24, 32), device=cuda)
+    if named is not None:
+        with torch.no_grad():
+            for net in ('coarse', 'fine'):
+                flat = params.from_named(named, net).to(cuda)
+                getattr(m, f'{net}_embedding').flat.copy_(flat[:246784])
+                getattr(m, f'{net}_readout').flat.copy_(flat[246784:])
+    return m
+
+
+def test_model_call_infer_and_train_step(cuda, tmp_path):
+    from oracle import nerf_oracle as O
+    sc = O.synthetic_scene(22, 1, 2, 32, 24, 32)
+    named = O.init_params(3, bias_std=0.02)
+    m = _model(cuda, 2, named)
+    feats = sc['features'].to(cuda)
+    ref = O.mvnerf_call(sc['inputs'], sc['features'], named, near=NEAR, far=FAR, n_samples=64, u_strat=sc['u_strat'],
+                        u_pdf=sc['u_pdf'])
+    inputs_np = tuple(t.numpy() for t in sc['inputs'])          # the generator hands numpy arrays
+    out = m.infer(inputs_np, feats, sc['u_strat'], sc['u_pdf'])
+    for a, b in zip(out, ref):
+        assert rel_err(a, b) < 1e-2
+    # call() goes through the plug-in feature producer
+    m.feature_fn = lambda images: feats.reshape(-1, *feats.shape[2:])
+    m.compile()
+    before = m.coarse_embedding.flat.detach().clone()
+    losses = [float(m.train_step((inputs_np, sc['target'].numpy()))['loss']) for _ in range(8)]
+    assert np.isfinite(losses).all() and losses[-1] < losses[0]
+    assert not torch.equal(before, m.coarse_embedding.flat.detach())
+    # store / load round trip, False when a group is missing
+    path = str(tmp_path / 'model_final')
+    assert m.load(path) is False
+    m.store(path)
+    m2 = _model(cuda, 2)
+    assert m2.load(path) is True
+    assert torch.equal(m2.fine_embedding.flat, m.fine_embedding.flat)
+    assert torch.equal(m2.coarse_readout.flat, m.coarse_readout.flat)
+    # fit over a generator
+    from clipnerf_b200.synthetic import SyntheticNerfDataset
+    from src.lib.data_generator.mvnerf import MVNeRFDataGenerator
+    ds = SyntheticNerfDataset(n_scenes=2, n_perspectives=4, H=24, W=32)
+    gen = MVNeRFDataGenerator(ds, n_rays_train=32, batch_size=1, n_views=2, shuffle=True)
+    m.feature_fn = lambda images: torch.tanh(images.mean(-1, keepdim=True)).expand(-1, -1, -1, 256).contiguous()
+    hist = m.fit(gen, epochs=2, initial_epoch=0)
+    assert len(hist['loss']) == 2 and np.isfinite(hist['loss']).all()
+
+
+def test_render_view_bookkeeping(cuda):
+    """full-image render: pixel order, odd-size chunking and the truncating uint8 conversion are exact
+    given the float outputs; the floats agree with the oracle within 1e-2."""
+    from clipnerf_b200.synthetic import SyntheticNerfDataset
+    from oracle import nerf_oracle as O
+    from src.lib.mvnerf.model_v0 import render_view
+    H, W = 15, 21                                   # 315 rays: odd, and not a multiple of the chunk
+    ds = SyntheticNerfDataset(n_scenes=1, n_perspectives=3, H=H, W=W, seed=4)
+    colors = [ds.datasets['color'].read_sample_at_idx(0, i) for i in range(2)]
+    cams = [ds.datasets['camera_config'].read_sample_at_idx(0, i) for i in range(2)]
+    tgt = ds.datasets['camera_config'].read_sample_at_idx(0, 2)
+    named = O.init_params(4, bias_std=0.02)
+    m = _model(cuda, 2, named)
+    g = torch.Generator().manual_seed(0)
+    feats = torch.randn(1, 2, H, W, 256, generator=g)
+    m.feature_fn = lambda images: feats.to(cuda).reshape(-1, H, W, 256)
+    u_s, u_p = torch.rand(1, H * W + 1, 64, generator=g), torch.rand(1, H * W + 1, 64, generator=g)
+    # fixed draws: patch the model's RNG so that both chunks see the rows of (u_s, u_p) they cover
+    calls = []
+
+    def fake_rand(b, nr):
+        calls.append(nr)
+        k = len(calls) - 1
+        src = u_s if k % 2 == 0 else u_p
+        start = sum(calls[:k][::2]) if k % 2 == 0 else sum(calls[:k][1::2])
+        return src[:, start:start + nr].to(cuda)
+
+    m._rand = fake_rand
+    rgb8, depth8 = render_view(m, colors, cams, tgt, chunk=200)
+    assert rgb8.shape == (H, W, 3) and rgb8.dtype == np.uint8 and depth8.shape == (H, W, 1)
+    # oracle on the same rays (row-major, u = column)
+    K3 = np.reshape(tgt['intrinsics'], (3, 3)).astype(np.float32)
+    o, d = O.get_rays(W, H, tgt['pose'], K3)
+    inputs = O.get_input([c[..., :3] for c in colors], cams, d.reshape(-1, 3), o.reshape(-1, 3))
+    # chunk 1 = rays [0,200), chunk 2 = rays [200,315) padded by one copy of the last ray
+    us = torch.cat([u_s[:, :200], u_s[:, 200:315]], 1)
+    up = torch.cat([u_p[:, :200], u_p[:, 200:315]], 1)
+    ref = O.mvnerf_call([torch.tensor(a) for a in inputs], feats, named, near=NEAR, far=FAR, n_samples=64,
+                        u_strat=us, u_pdf=up)
+    ref8, refd8 = O.quantize_render(ref[2][0].numpy(), ref[3][0].numpy(), (H, W))
+    diff = np.abs(rgb8.astype(int) - ref8.astype(int))
+    assert diff.max() <= 4 and (diff <= 1).mean() > 0.9, (diff.max(), (diff <= 1).mean())
+    assert np.abs(depth8.astype(int) - refd8.astype(int)).max() <= 6

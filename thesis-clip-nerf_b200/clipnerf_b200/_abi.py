@@ -33,9 +33,12 @@ PROTOTYPES = {
     'cn_last_error': [],
     'cn_sample_coarse': [_P, _P, c_int64, c_int32, c_double, c_double, _P],
     'cn_sample_pdf_fwd': [_P, _P, _P, c_int64, _P, _P, _P, _P],
+    'cn_sample_pdf': [_P, _P, _P, c_int64, _P, _P, _P],
     'cn_sample_pdf_bwd': [_P, _P, _P, _P, _P, c_int64, _P, _P],
     'cn_project_gather_fwd': [ctypes.POINTER(CnScene), _P, _P, _P, c_int32, c_int32, _P, _P],
-    'cn_project_gather_debug': [ctypes.POINTER(CnScene), _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P],
+    'cn_project_gather_debug': [ctypes.POINTER(CnScene), _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P, _P],
+    'cn_interpolate_bilinear': [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int64, _P, _P],
+    'cn_position_encoding': [_P, c_int64, c_int32, c_int32, c_float, _P, _P],
     'cn_project_gather_bwd': [ctypes.POINTER(CnScene), _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P],
     'cn_composite_fwd': [_P, _P, c_int64, c_int32, _P, _P, _P, _P],
     'cn_composite_bwd': [_P, _P, c_int64, c_int32, _P, _P, _P, _P, _P, _P],

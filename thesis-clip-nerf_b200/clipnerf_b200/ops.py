@@ -91,16 +91,43 @@ def project_gather_fwd(scene: Scene, ray_o, ray_d, z) -> torch.Tensor:
     return x
 
 
-def project_gather_debug(scene: Scene, ray_o, ray_d, z):
+def project_gather_debug(scene: Scene, ray_o, ray_d, z, gather: bool = True, cam: bool = False):
     ray_o, ray_d, z = _f32c(ray_o), _f32c(ray_d), _f32c(z)
     b, nr, S = z.shape
     dev = z.device
     pix = torch.empty(b, scene.nv, nr, S, 2, dtype=torch.float32, device=dev)
     corner = torch.empty(b, scene.nv, nr, S, 2, dtype=torch.int32, device=dev)
-    g = torch.empty(b, scene.nv, nr, S, 259, dtype=torch.float32, device=dev)
+    g = torch.empty(b, scene.nv, nr, S, 259, dtype=torch.float32, device=dev) if gather else None
+    c = torch.empty(b, scene.nv, nr, S, 4, dtype=torch.float32, device=dev) if cam else None
     call('cn_project_gather_debug', ctypes.byref(scene.c), _ptr(ray_o), _ptr(ray_d), _ptr(z), nr, S, _ptr(pix),
-         _ptr(corner), _ptr(g), _stream())
-    return pix, corner, g
+         _ptr(corner), _ptr(g), _ptr(c), _stream())
+    return (pix, corner, g, c) if cam else (pix, corner, g)
+
+
+def interpolate_bilinear(grid, query):
+    grid, query = _f32c(grid), _f32c(query)
+    B, H, W, C = grid.shape
+    N = query.shape[1]
+    out = torch.empty(B, N, C, dtype=torch.float32, device=grid.device)
+    call('cn_interpolate_bilinear', _ptr(grid), _ptr(query), B, H, W, C, N, _ptr(out), _stream())
+    return out
+
+
+def position_encoding(pos, n_freq: int = 10, freq0: float = 3.14159274101257324):
+    pos = _f32c(pos)
+    D = pos.shape[-1]
+    out = torch.empty(*pos.shape[:-1], D * n_freq * 2, dtype=torch.float32, device=pos.device)
+    call('cn_position_encoding', _ptr(pos), pos.numel() // D, D, n_freq, float(freq0), _ptr(out), _stream())
+    return out
+
+
+def sample_pdf(bins, weights, u, return_above: bool = False):
+    bins, weights, u = _f32c(bins), _f32c(weights), _f32c(u)
+    assert bins.shape[-1] == 63 and weights.shape[-1] == 62 and u.shape[-1] == 64, 'sample_pdf is built for 64 samples'
+    samples = torch.empty_like(u)
+    above = torch.empty(u.shape, dtype=torch.int32, device=u.device) if return_above else None
+    call('cn_sample_pdf', _ptr(bins), _ptr(weights), _ptr(u), u.numel() // 64, _ptr(samples), _ptr(above), _stream())
+    return (samples, above) if return_above else samples
 
 
 def project_gather_bwd(scene: Scene, ray_o, ray_d, z, dx_tiles, d_features: Optional[torch.Tensor],

@@ -164,7 +164,7 @@ project_gather_fwd_kernel(CnScene sc, const float *__restrict__ ray_o, const flo
 __global__ void __launch_bounds__(256)
 project_gather_debug_kernel(CnScene sc, const float *__restrict__ ray_o, const float *__restrict__ ray_d,
                             const float *__restrict__ z, int nr, int S, float *__restrict__ pix,
-                            int32_t *__restrict__ corner, float *__restrict__ gathered) {
+                            int32_t *__restrict__ corner, float *__restrict__ gathered, float *__restrict__ cam) {
   const int64_t n_samples = (int64_t)sc.b * nr * S;
   const int64_t n = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (n >= n_samples) return;
@@ -184,7 +184,12 @@ project_gather_debug_kernel(CnScene sc, const float *__restrict__ ray_o, const f
     if (l == 0) {
       pix[o * 2 + 0] = pr.px; pix[o * 2 + 1] = pr.py;
       corner[o * 2 + 0] = pr.x0; corner[o * 2 + 1] = pr.y0;
+      if (cam) {
+        cam[o * 4 + 0] = pr.p[0]; cam[o * 4 + 1] = pr.p[1]; cam[o * 4 + 2] = pr.p[2];
+        cam[o * 4 + 3] = dot4_rn(E + 12, rc.x[0], rc.x[1], rc.x[2], 1.f);
+      }
     }
+    if (!gathered) continue;
     const int64_t pix00 = ((int64_t)bv * H + pr.y0) * W + pr.x0;
     const float *f00 = sc.features + pix00 * CN_FEAT_C;
     const float *f10 = f00 + (int64_t)W * CN_FEAT_C;
@@ -316,6 +321,39 @@ project_gather_bwd_kernel(CnScene sc, const float *__restrict__ ray_o, const flo
   if (kZGrad && l == 0) dz[n] += dz_acc;
 }
 
+// tensorflow_addons.image.interpolate_bilinear(grid [B,H,W,C], query [B,N,2], indexing='xy'):
+// one warp per query, lanes stride over the channels
+__global__ void __launch_bounds__(256)
+interpolate_bilinear_kernel(const float *__restrict__ grid, const float *__restrict__ query, int B, int H, int W,
+                            int C, int64_t N, float *__restrict__ out) {
+  const int64_t n = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (n >= (int64_t)B * N) return;
+  const int l = lane_id();
+  const int64_t b = n / N;
+  int x0, y0;
+  float ax, ay, tx, ty;
+  bilinear_axis(query[n * 2 + 0], W, x0, ax, tx);
+  bilinear_axis(query[n * 2 + 1], H, y0, ay, ty);
+  const float *g00 = grid + (((int64_t)b * H + y0) * W + x0) * C;
+  const float *g10 = g00 + (int64_t)W * C;
+  for (int c = l; c < C; c += 32) out[n * C + c] = lerp2_rn(g00[c], g00[C + c], g10[c], g10[C + c], ax, ay);
+}
+
+// position_encoding (nerf_utils.py:108-126): [n, 3] -> [n, 3 * n_freq * 2], 'd n f' order
+__global__ void position_encoding_kernel(const float *__restrict__ pos, int64_t n, int D, int n_freq, float freq0,
+                                         float *__restrict__ out) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int per = D * n_freq;
+  if (idx >= n * per) return;
+  const int64_t row = idx / per;
+  const int c = (int)(idx % per) / n_freq, k = (int)(idx % per) % n_freq;
+  const float fk = __fmul_rn(freq0, exp2f((float)k));
+  float s, co;
+  sincosf(__fmul_rn(pos[row * D + c], fk), &s, &co);
+  out[idx * 2 + 0] = s;
+  out[idx * 2 + 1] = co;
+}
+
 static int check_scene(const CnScene *s, const char *who) {
   CN_REQUIRE(s, "%s: null scene", who);
   CN_REQUIRE(s->images && s->features && s->intrinsics && s->extr_inv, "%s: null scene pointer", who);
@@ -342,15 +380,41 @@ extern "C" int cn_project_gather_fwd(const CnScene *scene, const float *ray_o, c
 
 extern "C" int cn_project_gather_debug(const CnScene *scene, const float *ray_o, const float *ray_d, const float *z,
                                        int32_t nr, int32_t S, float *pix, int32_t *corner, float *gathered,
-                                       void *stream) {
+                                       float *cam, void *stream) {
   using namespace cn;
   if (int e = check_scene(scene, "cn_project_gather_debug")) return e;
-  CN_REQUIRE(ray_o && ray_d && z && pix && corner && gathered, "cn_project_gather_debug: null pointer");
+  CN_REQUIRE(ray_o && ray_d && z && pix && corner, "cn_project_gather_debug: null pointer");
   CN_REQUIRE(nr > 0 && S > 0, "cn_project_gather_debug: nr=%d S=%d", nr, S);
   const int64_t n = (int64_t)scene->b * nr * S;
   project_gather_debug_kernel<<<(unsigned)((n + 7) / 8), 256, 0, (cudaStream_t)stream>>>(*scene, ray_o, ray_d, z, nr,
-                                                                                        S, pix, corner, gathered);
+                                                                                        S, pix, corner, gathered, cam);
   return check_launch("cn_project_gather_debug");
+}
+
+extern "C" int cn_interpolate_bilinear(const float *grid, const float *query, int32_t B, int32_t H, int32_t W,
+                                       int32_t C, int64_t N, float *out, void *stream) {
+  using namespace cn;
+  CN_REQUIRE(grid && query && out, "cn_interpolate_bilinear: null pointer");
+  CN_REQUIRE(B > 0 && H >= 2 && W >= 2 && C > 0 && N >= 0, "cn_interpolate_bilinear: B=%d H=%d W=%d C=%d N=%lld", B, H,
+             W, C, (long long)N);
+  if (N == 0) return 0;
+  const int64_t n = (int64_t)B * N;
+  interpolate_bilinear_kernel<<<(unsigned)((n + 7) / 8), 256, 0, (cudaStream_t)stream>>>(grid, query, B, H, W, C, N,
+                                                                                        out);
+  return check_launch("cn_interpolate_bilinear");
+}
+
+extern "C" int cn_position_encoding(const float *pos, int64_t n, int32_t D, int32_t n_freq, float freq0, float *out,
+                                    void *stream) {
+  using namespace cn;
+  CN_REQUIRE(pos && out, "cn_position_encoding: null pointer");
+  CN_REQUIRE(n >= 0 && D > 0 && n_freq > 0 && n_freq <= 24, "cn_position_encoding: n=%lld D=%d n_freq=%d",
+             (long long)n, D, n_freq);
+  const int64_t total = n * D * n_freq;
+  if (total == 0) return 0;
+  position_encoding_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(pos, n, D, n_freq,
+                                                                                             freq0, out);
+  return check_launch("cn_position_encoding");
 }
 
 extern "C" int cn_project_gather_bwd(const CnScene *scene, const float *ray_o, const float *ray_d, const float *z,

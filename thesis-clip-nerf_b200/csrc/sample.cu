@@ -51,10 +51,15 @@ struct Draw {
   bool denom_replaced;
 };
 
+// bins are the midpoints of the coarse z (model_v0.py:150); the op-level entry point
+// cn_sample_pdf passes explicit bins instead and parks them in aux[] (kExplicitBins)
+template <bool kExplicitBins = false>
 __device__ __forceinline__ float bin_at(const PdfShared &sh, int k) {
-  return k >= kNB ? 0.f : __fmul_rn(0.5f, __fadd_rn(sh.zc[k + 1], sh.zc[k]));
+  if (k >= kNB) return 0.f;
+  return kExplicitBins ? sh.aux[k] : __fmul_rn(0.5f, __fadd_rn(sh.zc[k + 1], sh.zc[k]));
 }
 
+template <bool kExplicitBins = false>
 __device__ __forceinline__ Draw pdf_draw(const PdfShared &sh, float uu) {
   Draw d;
   int above = 0;
@@ -63,8 +68,8 @@ __device__ __forceinline__ Draw pdf_draw(const PdfShared &sh, float uu) {
   d.below = min(max(above - 1, 0), kNB - 1);
   d.cdf_a = above >= kNB ? 0.f : sh.cdf[above];  // out-of-range gather reads 0 (TF-GPU gather_nd)
   d.cdf_b = sh.cdf[d.below];
-  d.bins_a = bin_at(sh, above);
-  d.bins_b = bin_at(sh, d.below);
+  d.bins_a = bin_at<kExplicitBins>(sh, above);
+  d.bins_b = bin_at<kExplicitBins>(sh, d.below);
   float den = __fsub_rn(d.cdf_a, d.cdf_b);
   d.denom_replaced = den < 1e-5f;
   d.denom = d.denom_replaced ? 1.f : den;
@@ -119,6 +124,30 @@ sample_pdf_fwd_kernel(const float *__restrict__ z_c, const float *__restrict__ w
     const int e = l + 32 * h;
     z_fine[n * 2 * kS + e] = sh.aux[e];
     perm[n * 2 * kS + e] = sh.prm[e];
+  }
+}
+
+// op-level form of sample_pdf (nerf_utils.py:143-176): explicit bins [n,63] and weights [n,62]
+__global__ void __launch_bounds__(128)
+sample_pdf_op_kernel(const float *__restrict__ bins, const float *__restrict__ weights, const float *__restrict__ u,
+                     int64_t n_rays, float *__restrict__ samples, int32_t *__restrict__ above_out) {
+  __shared__ PdfShared shs[4];
+  const int warp = threadIdx.x >> 5;
+  const int l = lane_id();
+  const int64_t n = (int64_t)blockIdx.x * 4 + warp;
+  if (n >= n_rays) return;
+  PdfShared &sh = shs[warp];
+  for (int k = l; k < kNB; k += 32) sh.aux[k] = bins[n * kNB + k];
+  for (int k = l; k < kS - 2; k += 32) sh.wc[k + 1] = weights[n * (kS - 2) + k];  // wc[1..62] like w_c[1:-1]
+  __syncwarp();
+  bool rep;
+  pdf_build_cdf(sh, rep);
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int j = l + 32 * h;
+    const Draw d = pdf_draw<true>(sh, u[n * kS + j]);
+    samples[n * kS + j] = __fadd_rn(d.bins_b, __fmul_rn(d.t, __fsub_rn(d.bins_a, d.bins_b)));
+    if (above_out) above_out[n * kS + j] = d.above;
   }
 }
 
@@ -217,6 +246,17 @@ extern "C" int cn_sample_pdf_fwd(const float *z_c, const float *w_c, const float
   sample_pdf_fwd_kernel<<<(unsigned)((n_rays + 3) / 4), 128, 0, (cudaStream_t)stream>>>(z_c, w_c, u, n_rays, z_fine,
                                                                                        perm, above);
   return check_launch("cn_sample_pdf_fwd");
+}
+
+extern "C" int cn_sample_pdf(const float *bins, const float *weights, const float *u, int64_t n_rays, float *samples,
+                             int32_t *above, void *stream) {
+  using namespace cn;
+  CN_REQUIRE(bins && weights && u && samples, "cn_sample_pdf: null pointer");
+  CN_REQUIRE(n_rays >= 0, "cn_sample_pdf: n_rays %lld", (long long)n_rays);
+  if (n_rays == 0) return 0;
+  sample_pdf_op_kernel<<<(unsigned)((n_rays + 3) / 4), 128, 0, (cudaStream_t)stream>>>(bins, weights, u, n_rays,
+                                                                                      samples, above);
+  return check_launch("cn_sample_pdf");
 }
 
 extern "C" int cn_sample_pdf_bwd(const float *z_c, const float *w_c, const float *u, const uint8_t *perm,

@@ -1,0 +1,231 @@
+"""Drop-in for the reference's ``src/lib/mvnerf/model_v0.py``: ``MVVNeRFRenderer`` and ``render_view``
+with the same constructor keywords, attributes and methods that ``src/train_nerf.py`` consumes,
+on top of the sm_100a render path.
+
+What is and is not here
+-----------------------
+* ``_call`` / ``infer`` / ``volumetric_render`` / ``train_step`` / ``render_view`` -- the hot path --
+  run on the CUDA kernels (``clipnerf_b200.render.render_rays``); no CPU fallback.
+* The image encoders that *produce* ``combined_features`` (``VisualFeatures``, the frozen CLIP
+  SavedModel, ``CombineCLIPVisual*``) are upstream of the path and out of scope.  ``call`` /
+  ``render_view`` therefore take the feature producer as a plug-in: set ``model.feature_fn`` to a
+  callable ``images [(b n), H, W, 3] -> [(b n), H, W, 256]`` (any torch module), or pass
+  ``combined_features`` explicitly to ``infer`` / ``_call``.
+* Keras plumbing (``compile`` / ``fit`` / ``summary`` / ``store`` / ``load``) is re-stated minimally
+  on torch; checkpoints are one ``torch.save`` file per reference checkpoint group
+  (``<path>_<group>.pt`` instead of the TF ``.index`` / ``.data`` pair).
+"""
+import os
+
+import numpy as np
+import torch
+
+from clipnerf_b200 import ops
+from clipnerf_b200.render import render_rays
+
+from ..data_generator.mvnerf import MVNeRFDataGenerator  # noqa: F401  (re-exported like the reference)
+from ..data_generator.util import camera_parameters
+from .layers import MVResNetMLPNeRFEmbedding, RenderReadout
+from .nerf_utils import get_rays, optimize
+
+_GROUPS = ('coarse_embedding', 'coarse_readout', 'fine_embedding', 'fine_readout', 'visual_features',
+           'combine_clip_visual')
+
+
+class _UpstreamStub(torch.nn.Module):
+    """placeholder for an out-of-scope encoder group (keeps attribute names / checkpoint groups)."""
+
+    def __init__(self, what):
+        super().__init__()
+        self.what = what
+
+    # train_nerf.py:30-31 names these two sub-encoders when it builds optimizer groups
+    @property
+    def vision_transformer(self):
+        return self
+
+    @property
+    def conv_features(self):
+        return self
+
+    def forward(self, *a, **k):
+        raise NotImplementedError(f'{self.what} is upstream of the render path and not part of clipnerf_b200; '
+                                  f'set model.feature_fn (see INTEGRATION.md)')
+
+    def summary(self):
+        print(f'{self.what}: out of scope (plug-in)')
+
+
+class MVVNeRFRenderer(torch.nn.Module):
+    def __init__(self, n_rays_train, n_rays_infer, n_views=2, n_samples=64, n_features=256,
+                 embed_direction_vector=True, batch_size=1, near=0.7, far=1.5, original_image_size=(480, 640),
+                 feature_fn=None, device=None, **kwargs):
+        super().__init__()
+        if n_samples != 64 or n_features != 256:
+            raise ValueError('the sm_100a path is specialised for n_samples=64 and n_features=256 '
+                             '(src/configs/nerf_model/default.yaml)')
+        self.n_views = n_views
+        self.coarse_embedding = MVResNetMLPNeRFEmbedding(6, 128, embed_direction_vector=embed_direction_vector,
+                                                         n_views=n_views)
+        self.coarse_readout = RenderReadout(4)
+        self.fine_embedding = MVResNetMLPNeRFEmbedding(6, 128, embed_direction_vector=embed_direction_vector,
+                                                       n_views=n_views)
+        self.fine_readout = RenderReadout(4)
+        self.visual_features = _UpstreamStub('VisualFeatures')
+        self.clip_visual = _UpstreamStub('CLIPVisualEncoder')
+        self.combine_clip_visual = _UpstreamStub('CombineCLIPVisualV0')
+        self.feature_fn = feature_fn
+        self.n_samples = n_samples
+        self.n_rays_train = n_rays_train
+        self.n_rays_infer = n_rays_infer
+        self.batch_size = batch_size
+        self.infer_batch_size = 1
+        self.near, self.far = near, far
+        self.original_image_size = tuple(original_image_size)
+        self.optimizer = None
+        self.loss = None
+        self.loss_tracker = []
+        self._generator = None
+        if device is not None:
+            self.to(device)
+
+    # ------------------------------------------------------------------ helpers
+    @property
+    def device(self):
+        return self.coarse_embedding.flat.device
+
+    def _flat(self, net):
+        emb = self.coarse_embedding if net == 'coarse' else self.fine_embedding
+        ro = self.coarse_readout if net == 'coarse' else self.fine_readout
+        return torch.cat([emb.flat, ro.flat])
+
+    def _to_dev(self, x):
+        return torch.as_tensor(np.asarray(x) if not torch.is_tensor(x) else x, dtype=torch.float32).to(self.device)
+
+    def _rand(self, b, nr):
+        if self._generator is None:
+            self._generator = torch.Generator(device=self.device)
+            self._generator.manual_seed(torch.initial_seed() % (2 ** 31))
+        return torch.rand(b, nr, self.n_samples, device=self.device, generator=self._generator)
+
+    # ------------------------------------------------------------------ reference API
+    def encode(self, image):
+        if self.feature_fn is None:
+            return self.visual_features(image)
+        return self.feature_fn(self._to_dev(image))
+
+    def infer(self, inputs, batched_features, u_strat=None, u_pdf=None):
+        with torch.no_grad():
+            return self._call(inputs, self.n_rays_infer, self.infer_batch_size, batched_features, u_strat, u_pdf)
+
+    def call(self, inputs, training=False, mask=None):
+        src = self._to_dev(inputs[2])
+        b, n = src.shape[:2]
+        feats = self.encode(src.reshape(b * n, *src.shape[2:])).reshape(b, n, src.shape[2], src.shape[3], -1)
+        return self._call(inputs, self.n_rays_train, self.batch_size, feats)
+
+    def forward(self, inputs, training=False):
+        return self.call(inputs, training=training)
+
+    @staticmethod
+    def volumetric_render(zs, density, chromacity):
+        """(rgb, depth, weights) of reference :89-100 on the warp-scan compositing kernel."""
+        rgbs = torch.cat([chromacity, density[..., None]], dim=-1)
+        return ops.composite_fwd(zs, rgbs)
+
+    def _call(self, inputs, n_rays, batch_size, combined_features, u_strat=None, u_pdf=None):
+        """(rgb, depth, fine_rgb, fine_depth); reference :113-184.  ``n_rays`` is free (any even
+        number), not the 512 the reference's input_signature pins."""
+        ray_o, ray_d, images, K, Einv = [self._to_dev(t) for t in inputs]
+        feats = combined_features if torch.is_tensor(combined_features) else self._to_dev(combined_features)
+        b, nr = ray_o.shape[:2]
+        u_strat = self._rand(b, nr) if u_strat is None else self._to_dev(u_strat)
+        u_pdf = self._rand(b, nr) if u_pdf is None else self._to_dev(u_pdf)
+        return render_rays(self._flat('coarse'), self._flat('fine'), (ray_o, ray_d, images, K, Einv),
+                           feats.to(self.device), u_strat, u_pdf, self.near, self.far)
+
+    # ------------------------------------------------------------------ training plumbing (Keras-like)
+    def compile(self, optimizer=None, loss=None):
+        """``optimizer``: a torch optimizer (or None -> Adam 1e-4 on the NeRF MLPs); ``loss``: callable
+        ``(labels, prediction) -> scalar`` (default mean squared error)."""
+        self.optimizer = optimizer if optimizer is not None else torch.optim.Adam(self.parameters(), lr=1e-4,
+                                                                                 eps=1e-7)
+        self.loss = loss if loss is not None else (lambda y, p: torch.mean((p - y) ** 2))
+
+    def train_step(self, data):
+        """reference :186-197: loss = L(labels, rgb) + L(labels, fine_rgb); per-element clip 1.0."""
+        inputs, labels = data
+        labels = self._to_dev(labels)
+        rgb, depth, fine_rgb, fine_depth = self.call(inputs, training=True)
+        loss = self.loss(labels, rgb) + self.loss(labels, fine_rgb)
+        variables = [p for p in self.parameters() if p.requires_grad]
+        gradients = torch.autograd.grad(loss, variables, allow_unused=True)
+        optimize(self.optimizer, variables, gradients, 1.0)
+        self.loss_tracker.append(float(loss.detach()))
+        return {'loss': loss.detach()}
+
+    def fit(self, generator, epochs=1, initial_epoch=0, verbose=0):
+        history = []
+        for epoch in range(initial_epoch, epochs):
+            losses = [float(self.train_step(generator[i])['loss']) for i in range(len(generator))]
+            generator.on_epoch_end()
+            history.append(float(np.mean(losses)) if losses else float('nan'))
+            if verbose:
+                print(f'Epoch {epoch + 1}/{epochs} - loss: {history[-1]:.6f}')
+        return {'loss': history}
+
+    def summary(self):
+        n = sum(p.numel() for p in self.parameters())
+        print(f'MVVNeRFRenderer (clipnerf_b200): {n} trainable NeRF parameters '
+              f'(coarse/fine embedding 246784 each, readouts 516 each); encoders are plug-ins')
+
+    def store(self, path):
+        for g in _GROUPS:
+            torch.save(getattr(self, g).state_dict(), f'{path}_{g}.pt')
+
+    def load(self, path, old=False):
+        """returns False unless every checkpoint group exists (reference :213-240)."""
+        files = [f'{path}_{g}.pt' for g in _GROUPS]
+        if not all(os.path.exists(f) for f in files):
+            return False
+        for g, f in zip(_GROUPS, files):
+            getattr(self, g).load_state_dict(torch.load(f, map_location=self.device))
+        return True
+
+
+def render_view(model, src_colors, src_camera_configs, tgt_camera_config, chunk=None):
+    """full-image render of the target view (reference :243-281) -> (uint8 HxWx3, uint8 HxWx1).
+
+    Same bookkeeping: row-major rays over the source image size, fine rgb x255 clipped and
+    *truncated* to uint8, depth min-max normalised then truncated.  The reference walks the image
+    in 600 chunks of ``n_rays_infer`` = 512 rays with a device->host copy each; here the features
+    are encoded once and the image is rendered in a few large launches (``chunk`` rays each,
+    default 65536), results staying on the device until the end."""
+    tgt_intrinsic = np.reshape(tgt_camera_config['intrinsics'], (3, 3)).astype(np.float32)
+    image_shape = src_colors[0].shape[:2]
+    tgt_r_o, tgt_r_d = get_rays(image_shape[1], image_shape[0], tgt_camera_config['pose'], tgt_intrinsic)
+    all_o = np.reshape(tgt_r_o, (-1, 3))
+    all_d = np.reshape(tgt_r_d, (-1, 3))
+    src_images = np.array([[image[..., :3] / 255.0 for image in src_colors]])
+    dev = model.device
+    imgs = torch.as_tensor(src_images, dtype=torch.float32, device=dev)
+    feats = model.encode(imgs.reshape(-1, *imgs.shape[2:])).reshape(1, imgs.shape[1], imgs.shape[2], imgs.shape[3], -1)
+    e_invs, ks = zip(*[camera_parameters(c) for c in src_camera_configs])
+    K, Einv = np.array([ks], dtype=np.float32), np.array([e_invs], dtype=np.float32)
+    n = len(all_o)
+    chunk = chunk or 65536
+    rgbs, depths = [], []
+    for i in range(0, n, chunk):
+        o, d = all_o[i:i + chunk], all_d[i:i + chunk]
+        m = len(o)
+        if m % 2:                      # tiles hold two coarse rays: pad with a copy of the last ray
+            o, d = np.concatenate([o, o[-1:]]), np.concatenate([d, d[-1:]])
+        with torch.no_grad():
+            _, _, fine_rgb, fine_depth = model._call((o[None], d[None], imgs, K, Einv), len(o), 1, feats)
+        rgbs.append(fine_rgb[0, :m])
+        depths.append(fine_depth[0, :m])
+    all_rgbs = torch.cat(rgbs).cpu().numpy().reshape(*image_shape, 3) * 255
+    all_rgbs = np.clip(all_rgbs, 0, 255).astype(np.uint8)
+    all_depths = torch.cat(depths).cpu().numpy().reshape(*image_shape, 1)
+    norm = (all_depths - np.min(all_depths)) / (np.max(all_depths) - np.min(all_depths))
+    return all_rgbs, (norm * 255).astype(np.uint8)
