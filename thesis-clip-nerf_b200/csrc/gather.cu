@@ -215,7 +215,7 @@ __device__ __forceinline__ float warp_sum_f(float v) {
 }
 
 template <bool kFeatGrad, bool kZGrad>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 project_gather_bwd_kernel(CnScene sc, const float *__restrict__ ray_o, const float *__restrict__ ray_d,
                           const float *__restrict__ z, int nr, int S, const uint8_t *__restrict__ dx_tiles,
                           float *__restrict__ d_features, float *__restrict__ dz) {

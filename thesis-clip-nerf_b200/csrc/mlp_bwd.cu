@@ -3,54 +3,42 @@
 //   saved by the forward: A1 = relu(h), A2 = relu(t)   (bf16 tile images)
 //   g_a2 = g_y Wb^T            (dgrad 1, K-major operands)
 //   dWb += A2^T g_y            (wgrad,  MN-major operands: the SAME smem tiles read transposed)
-//   g_t  = g_a2 * [A2 > 0]     (epilogue 1)  -> bf16 tile in smem,  dba += colsum(g_t)
+//   g_t  = g_a2 * [A2 > 0]     (epilogue 1)  -> bf16 tile in smem,  dba += colsum(g_t)   (bias warps)
 //   g_a1 = g_t Wa^T            (dgrad 2)
 //   dWa += A1^T g_t            (wgrad)
-//   g_h  = g_y + g_a1 * [A1>0] (epilogue 2)  -> global,             dbb += colsum(g_y)
+//   g_h  = g_y + g_a1 * [A1>0] (epilogue 2)  -> global,             dbb += colsum(g_y)   (bias warps)
 // Both weight matrices stay resident in shared memory for the whole kernel and the two weight
 // gradients stay resident in TMEM (2 x 128 columns) across all tiles of the CTA; they are
 // flushed once with vector red.global.add at the end.
-//   warp 0: TMA producer (g_y, A2, A1 tiles), warp 1: MMA issuer, warps 2-5: epilogue.
+//   warp 0: TMA producer (g_y, A2, A1 tiles), warp 1: MMA issuer, warps 2-9: epilogue (4 TMEM lane
+//   quadrants x 2 column halves), warps 10-11: bias gradients (column sums read from the smem tiles).
+//   g_h leaves through a staging tile and one TMA store per tile.
 #include "common.cuh"
 #include "mlp_layout.cuh"
 
 namespace cn {
 
-constexpr int kBwdThreads = 192;
+constexpr int kBwdThreads = 384;  // warp 0 producer, 1 MMA, 2-9 epilogue (4 lane quadrants x 2 column halves), 10-11 bias sums
+constexpr int kBwdEpiThreads = 256;
 constexpr uint32_t kBwSmemWb = 0;
 constexpr uint32_t kBwSmemWa = 1 * CN_ACT_TILE_BYTES;
 constexpr uint32_t kBwSmemGy = 2 * CN_ACT_TILE_BYTES;
 constexpr uint32_t kBwSmemA2 = 3 * CN_ACT_TILE_BYTES;
 constexpr uint32_t kBwSmemA1 = 4 * CN_ACT_TILE_BYTES;
 constexpr uint32_t kBwSmemGt = 5 * CN_ACT_TILE_BYTES;
-constexpr uint32_t kBwSmemDb = 6 * CN_ACT_TILE_BYTES;  // 2 x 128 floats
-constexpr uint32_t kBwdSmemBytes = kBwSmemDb + 3 * 128 * 4 + 1024;
+constexpr uint32_t kBwSmemOut = 6 * CN_ACT_TILE_BYTES;  // g_h staging for the TMA store
+constexpr uint32_t kBwdSmemBytes = 7 * CN_ACT_TILE_BYTES + 1024;
 
 struct BwdBars {
   uint64_t w_full;
   uint64_t full_gy, full_a2, full_a1;
-  uint64_t free_gy, free_a2, free_a1;  // 128 epilogue arrivals + 1 tcgen05.commit
-  uint64_t gt_ready;                   // 128 epilogue arrivals
-  uint64_t gt_free;                    // commit after wgrad-a
+  uint64_t free_gy;                    // 256 epilogue + 64 bias-sum arrivals + 1 tcgen05.commit
+  uint64_t free_a2, free_a1;           // 256 epilogue arrivals + 1 tcgen05.commit
+  uint64_t gt_ready;                   // 256 epilogue arrivals
+  uint64_t gt_free;                    // commit after wgrad-a + 64 bias-sum arrivals
   uint64_t tmp1_ready, tmp2_ready;     // commits
   uint64_t all_done;                   // commit after the last tile
 };
-
-// column sums over the 32 rows held by the warp: on return v[0] of lane j is the sum of column j
-__device__ __forceinline__ float colsum32(float (&v)[32]) {
-  const uint32_t lane = lane_id();
-#pragma unroll
-  for (int o = 16; o >= 1; o >>= 1) {
-    const bool hi = (lane & o) != 0;
-#pragma unroll
-    for (int i = 0; i < o; ++i) {
-      const float send = hi ? v[i] : v[i + o];
-      const float keep = hi ? v[i + o] : v[i];
-      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
-    }
-  }
-  return v[0];
-}
 
 __global__ void __launch_bounds__(kBwdThreads, 1)
 mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restrict__ w_b_img,
@@ -64,19 +52,17 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
   const uint32_t s_base = smem_u32(smem);
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
-  float *sdb = reinterpret_cast<float *>(smem + kBwSmemDb);  // [0]=dba, [1]=dbb
 
-  for (int i = threadIdx.x; i < 2 * 128; i += kBwdThreads) sdb[i] = 0.f;
   if (threadIdx.x == 0) {
     mbar_init(smem_u32(&bars.w_full), 1);
     mbar_init(smem_u32(&bars.full_gy), 1);
     mbar_init(smem_u32(&bars.full_a2), 1);
     mbar_init(smem_u32(&bars.full_a1), 1);
-    mbar_init(smem_u32(&bars.free_gy), 129);
-    mbar_init(smem_u32(&bars.free_a2), 129);
-    mbar_init(smem_u32(&bars.free_a1), 129);
-    mbar_init(smem_u32(&bars.gt_ready), 128);
-    mbar_init(smem_u32(&bars.gt_free), 1);
+    mbar_init(smem_u32(&bars.free_gy), kBwdEpiThreads + 64 + 1);
+    mbar_init(smem_u32(&bars.free_a2), kBwdEpiThreads + 1);
+    mbar_init(smem_u32(&bars.free_a1), kBwdEpiThreads + 1);
+    mbar_init(smem_u32(&bars.gt_ready), kBwdEpiThreads);
+    mbar_init(smem_u32(&bars.gt_free), 64 + 1);
     mbar_init(smem_u32(&bars.tmp1_ready), 1);
     mbar_init(smem_u32(&bars.tmp2_ready), 1);
     mbar_init(smem_u32(&bars.all_done), 1);
@@ -160,108 +146,144 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
       }
       umma_commit(smem_u32(&bars.all_done));
     }
-  } else {
-    // =========================== epilogue warpgroup ===========================
-    const uint32_t quad = warp & 3u;
-    const uint32_t row = quad * 32u + lane;
-    const uint32_t lane_off = (quad * 32u) << 16;
+  } else if (warp >= 10) {
+    // =========================== bias gradients ===========================
+    // column sums of the g_y and g_t tiles straight from shared memory; each lane owns two columns of
+    // slab `sl` for the whole kernel (two fp32 accumulators per tile kind), one flush at the end
+    const uint32_t sl = warp - 10;
+    const uint32_t chunk = lane >> 2, within = (lane & 3u) * 4u;
+    float bb0 = 0.f, bb1 = 0.f, ba0 = 0.f, ba1 = 0.f;
     uint32_t it = 0;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const uint32_t par = it & 1u;
-      // ---- keep this row of g_y in registers (needed again by epilogue 2), release the smem tile
       mbar_wait(smem_u32(&bars.full_gy), par);
-      uint4 gy[16];
+      const uint8_t *gy = smem + kBwSmemGy + sl * CN_SLAB_BYTES + within;
+#pragma unroll 8
+      for (uint32_t r = 0; r < 128; ++r) {
+        const uint32_t v = *reinterpret_cast<const uint32_t *>(gy + r * 128u + ((chunk ^ (r & 7u)) << 4));
+        bb0 += bf16_lo(v);
+        bb1 += bf16_hi(v);
+      }
+      mbar_arrive(smem_u32(&bars.free_gy));
+      mbar_wait(smem_u32(&bars.gt_ready), par);
+      const uint8_t *gt = smem + kBwSmemGt + sl * CN_SLAB_BYTES + within;
+#pragma unroll 8
+      for (uint32_t r = 0; r < 128; ++r) {
+        const uint32_t v = *reinterpret_cast<const uint32_t *>(gt + r * 128u + ((chunk ^ (r & 7u)) << 4));
+        ba0 += bf16_lo(v);
+        ba1 += bf16_hi(v);
+      }
+      mbar_arrive(smem_u32(&bars.gt_free));
+    }
+    const int col = sl * 64 + lane * 2;
+    atomicAdd(&g_bb[col], bb0);
+    atomicAdd(&g_bb[col + 1], bb1);
+    atomicAdd(&g_ba[col], ba0);
+    atomicAdd(&g_ba[col + 1], ba1);
+  } else {
+    // =========================== epilogue: 8 warps, (row, column half) per thread ===========================
+    const uint32_t e = warp - 2;
+    const uint32_t half = e >> 2;
+    const uint32_t quad = warp & 3u;
+    const uint32_t row = quad * 32u + lane;
+    const uint32_t lane_off = (quad * 32u) << 16;
+    const bool leader = (e == 0 && lane == 0);
+    uint32_t it = 0;
+    bool pending = false;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const uint32_t par = it & 1u;
+      // ---- keep this half row of g_y in registers (needed again by epilogue 2), release the smem tile
+      mbar_wait(smem_u32(&bars.full_gy), par);
+      uint4 gy[8];
 #pragma unroll
-      for (int c = 0; c < 16; ++c) gy[c] = *reinterpret_cast<const uint4 *>(smem + kBwSmemGy + tile_chunk_off(row, c));
+      for (int c = 0; c < 8; ++c)
+        gy[c] = *reinterpret_cast<const uint4 *>(smem + kBwSmemGy + tile_chunk_off(row, half * 8 + c));
       mbar_arrive(smem_u32(&bars.free_gy));
       // ---- epilogue 1: g_t = g_a2 * [A2 > 0]
       mbar_wait(smem_u32(&bars.tmp1_ready), par);
       mbar_wait(smem_u32(&bars.full_a2), par);
-      mbar_wait(smem_u32(&bars.gt_free), par ^ 1u);  // previous tile's wgrad-a has finished reading GT
+      mbar_wait(smem_u32(&bars.gt_free), par ^ 1u);  // previous tile's wgrad-a / bias sums are done with GT
       tc_fence_after();
-#pragma unroll 1
-      for (int c4 = 0; c4 < 4; ++c4) {
-        uint32_t r[32];
-        float v[32];
-        tmem_ld32(t_tmp1 + lane_off + c4 * 32, r);
+      {
+        uint32_t r[64];
+        tmem_ld32(t_tmp1 + lane_off + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+        tmem_ld32(t_tmp1 + lane_off + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
         tmem_wait_ld();
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const uint4 m = *reinterpret_cast<const uint4 *>(smem + kBwSmemA2 + tile_chunk_off(row, c4 * 4 + q));
+        for (int q = 0; q < 8; ++q) {
+          const uint4 m = *reinterpret_cast<const uint4 *>(smem + kBwSmemA2 + tile_chunk_off(row, half * 8 + q));
           const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
+          uint32_t ow[4];
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            v[q * 8 + 2 * i] = bf16_lo(mw[i]) > 0.f ? __uint_as_float(r[q * 8 + 2 * i]) : 0.f;
-            v[q * 8 + 2 * i + 1] = bf16_hi(mw[i]) > 0.f ? __uint_as_float(r[q * 8 + 2 * i + 1]) : 0.f;
-          }
-          *reinterpret_cast<uint4 *>(smem + kBwSmemGt + tile_chunk_off(row, c4 * 4 + q)) =
-              make_uint4(pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
-                         pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]));
+          for (int i = 0; i < 4; ++i)
+            ow[i] = pack_bf16x2(bf16_lo(mw[i]) > 0.f ? __uint_as_float(r[q * 8 + 2 * i]) : 0.f,
+                                bf16_hi(mw[i]) > 0.f ? __uint_as_float(r[q * 8 + 2 * i + 1]) : 0.f);
+          *reinterpret_cast<uint4 *>(smem + kBwSmemGt + tile_chunk_off(row, half * 8 + q)) =
+              make_uint4(ow[0], ow[1], ow[2], ow[3]);
         }
-        const float cs = colsum32(v);
-        atomicAdd(&sdb[0 * 128 + c4 * 32 + lane], cs);
       }
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(smem_u32(&bars.gt_ready));
       mbar_arrive(smem_u32(&bars.free_a2));
-      // ---- epilogue 2: g_h = g_y + g_a1 * [A1 > 0]
+      // ---- epilogue 2: g_h = g_y + g_a1 * [A1 > 0]  -> staging tile -> TMA store
       mbar_wait(smem_u32(&bars.tmp2_ready), par);
       mbar_wait(smem_u32(&bars.full_a1), par);
       tc_fence_after();
-      uint8_t *dst = gh_tiles + tile * (int64_t)CN_ACT_TILE_BYTES;
-#pragma unroll 1
-      for (int c4 = 0; c4 < 4; ++c4) {
-        uint32_t r[32];
-        float vy[32], vh[32];
-        tmem_ld32(t_tmp2 + lane_off + c4 * 32, r);
+      if (pending) {  // the previous tile's store must have finished reading the staging tile
+        if (leader) bulk_wait_read0();
+        named_bar_sync(1, kBwdEpiThreads);
+        pending = false;
+      }
+      {
+        uint32_t r[64];
+        tmem_ld32(t_tmp2 + lane_off + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+        tmem_ld32(t_tmp2 + lane_off + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
         tmem_wait_ld();
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const uint4 m = *reinterpret_cast<const uint4 *>(smem + kBwSmemA1 + tile_chunk_off(row, c4 * 4 + q));
+        for (int q = 0; q < 8; ++q) {
+          const uint4 m = *reinterpret_cast<const uint4 *>(smem + kBwSmemA1 + tile_chunk_off(row, half * 8 + q));
           const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
-          const uint4 gq = gy[c4 * 4 + q];
-          const uint32_t gw[4] = {gq.x, gq.y, gq.z, gq.w};
+          const uint32_t gw[4] = {gy[q].x, gy[q].y, gy[q].z, gy[q].w};
+          uint32_t ow[4];
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const float y0 = bf16_lo(gw[i]), y1 = bf16_hi(gw[i]);
-            vy[q * 8 + 2 * i] = y0;
-            vy[q * 8 + 2 * i + 1] = y1;
-            vh[q * 8 + 2 * i] = y0 + (bf16_lo(mw[i]) > 0.f ? __uint_as_float(r[q * 8 + 2 * i]) : 0.f);
-            vh[q * 8 + 2 * i + 1] = y1 + (bf16_hi(mw[i]) > 0.f ? __uint_as_float(r[q * 8 + 2 * i + 1]) : 0.f);
-          }
-          *reinterpret_cast<uint4 *>(dst + tile_chunk_off(row, c4 * 4 + q)) =
-              make_uint4(pack_bf16x2(vh[q * 8 + 0], vh[q * 8 + 1]), pack_bf16x2(vh[q * 8 + 2], vh[q * 8 + 3]),
-                         pack_bf16x2(vh[q * 8 + 4], vh[q * 8 + 5]), pack_bf16x2(vh[q * 8 + 6], vh[q * 8 + 7]));
+          for (int i = 0; i < 4; ++i)
+            ow[i] = pack_bf16x2(
+                bf16_lo(gw[i]) + (bf16_lo(mw[i]) > 0.f ? __uint_as_float(r[q * 8 + 2 * i]) : 0.f),
+                bf16_hi(gw[i]) + (bf16_hi(mw[i]) > 0.f ? __uint_as_float(r[q * 8 + 2 * i + 1]) : 0.f));
+          *reinterpret_cast<uint4 *>(smem + kBwSmemOut + tile_chunk_off(row, half * 8 + q)) =
+              make_uint4(ow[0], ow[1], ow[2], ow[3]);
         }
-        const float csy = colsum32(vy);
-        atomicAdd(&sdb[1 * 128 + c4 * 32 + lane], csy);
       }
       tc_fence_before();
       mbar_arrive(smem_u32(&bars.free_a1));
+      fence_proxy_async_smem();
+      named_bar_sync(1, kBwdEpiThreads);
+      if (leader) {
+        bulk_s2g(gh_tiles + tile * (int64_t)CN_ACT_TILE_BYTES, s_base + kBwSmemOut, CN_ACT_TILE_BYTES);
+        bulk_commit();
+      }
+      pending = true;
     }
-    // ---- flush the weight gradients held in TMEM and the bias gradients held in smem
+    // ---- flush the weight gradients held in TMEM (each thread: its input unit, 64 output units)
     mbar_wait(smem_u32(&bars.all_done), 0);
     tc_fence_after();
 #pragma unroll 1
     for (int mtx = 0; mtx < 2; ++mtx) {
-      float *gdst = (mtx == 0 ? g_wa : g_wb) + row * 128;  // accumulator row = input unit
-      const uint32_t tsrc = (mtx == 0 ? t_dwa : t_dwb) + lane_off;
+      float *gdst = (mtx == 0 ? g_wa : g_wb) + row * 128 + half * 64;  // accumulator row = input unit
+      const uint32_t tsrc = (mtx == 0 ? t_dwa : t_dwb) + lane_off + half * 64;
 #pragma unroll 1
-      for (int c4 = 0; c4 < 4; ++c4) {
+      for (int c2 = 0; c2 < 2; ++c2) {
         uint32_t r[32];
-        tmem_ld32(tsrc + c4 * 32, r);
+        tmem_ld32(tsrc + c2 * 32, r);
         tmem_wait_ld();
 #pragma unroll
         for (int q = 0; q < 8; ++q)
-          red_add_f4(gdst + c4 * 32 + q * 4, __uint_as_float(r[q * 4 + 0]), __uint_as_float(r[q * 4 + 1]),
+          red_add_f4(gdst + c2 * 32 + q * 4, __uint_as_float(r[q * 4 + 0]), __uint_as_float(r[q * 4 + 1]),
                      __uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3]));
       }
     }
-    named_bar_sync(1, 128);  // all smem bias partial sums are in
-    const int c = threadIdx.x - 64;
-    atomicAdd(&g_ba[c], sdb[c]);
-    atomicAdd(&g_bb[c], sdb[128 + c]);
+    if (leader) bulk_wait0();
   }
 
   tc_fence_before();

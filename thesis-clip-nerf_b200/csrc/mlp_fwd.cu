@@ -10,8 +10,10 @@
 //   warp 0      TMA producer   : streams X slabs and weight slabs (16 KiB each) through an
 //                                8-slot shared-memory ring with cp.async.bulk + mbarriers
 //   warp 1      MMA issuer     : one thread issues tcgen05.mma (M=128, N=128, K=16, bf16 -> fp32)
-//   warps 2-5   epilogue tile 0: TMEM -> registers -> bias / ReLU -> bf16 -> swizzled smem operand
-//   warps 6-9   epilogue tile 1
+//   warps 2-9   epilogue tile 0: TMEM -> registers -> bias / ReLU -> bf16 -> swizzled smem operand
+//   warps 10-17 epilogue tile 1  (8 warps per tile: 4 TMEM lane quadrants x 2 column halves)
+// The fusion stage stages the nv per-view tiles of each 128-row tile in shared memory with TMA and
+// averages them from there.
 // TMEM (512 columns): per tile a 128-column fp32 residual stream `h` and a 128-column `tmp`.
 // The second GEMM of every block accumulates straight into `h`, so the residual add is free and
 // the stream stays fp32; Dense biases of the residual branch are applied as cumulative bias
@@ -21,50 +23,53 @@
 
 namespace cn {
 
-constexpr int kRingSlots = 8;
-constexpr int kFwdThreads = 320;
+constexpr int kFwdThreads = 576;                                   // 2 + 16 warps
+constexpr int kEpiThreads = 256;                                   // epilogue threads per tile
+constexpr int kMaxStageViews = 3;                                  // views staged in smem by the fusion prologue
 constexpr uint32_t kSmemAct = 0;                                   // 2 x 32 KiB
-constexpr uint32_t kSmemRing = 2 * CN_ACT_TILE_BYTES;              // 8 x 16 KiB
-constexpr uint32_t kSmemTab = kSmemRing + kRingSlots * CN_SLAB_BYTES;
+constexpr uint32_t kSmemRing = 2 * CN_ACT_TILE_BYTES;
 constexpr uint32_t kSmemTabBytes = 7 * 128 * 4 + 512 * 4 + 16;
-constexpr uint32_t kFwdSmemBytes = kSmemTab + kSmemTabBytes + 1024;  // + alignment slack
+// 8-slot ring of 16 KiB slabs: X slabs + weights (per-view stage); per-view tiles + weights (fusion stage)
+template <bool kFusion> struct FwdSmem {
+  static constexpr int kRingSlots = 8;
+  static constexpr uint32_t kTab = kSmemRing + kRingSlots * CN_SLAB_BYTES;
+  static constexpr uint32_t kBytes = kTab + kSmemTabBytes + 1024;  // + alignment slack
+};
 
 struct FwdBars {
-  uint64_t full[kRingSlots];
-  uint64_t empty[kRingSlots];
+  uint64_t full[8];
+  uint64_t empty[8];
   uint64_t h_ready[2];
   uint64_t tmp_ready[2];
   uint64_t act_ready[2];
   uint64_t h_free[2];
+  uint64_t views_ready[2];  // fusion stage: the ring slots holding tile t's per-view slabs have landed
 };
 
-// TMEM accumulator (this thread's lane, 128 columns) + bias -> (ReLU) -> bf16 row of the
-// swizzled activation tile in shared memory.
+// TMEM accumulator (this thread's lane, 64 columns of half `half`) + bias -> (ReLU) -> bf16 half row
+// of the swizzled activation tile in shared memory.  Both 32-column loads are issued before the wait.
 template <bool kRelu>
 __device__ __forceinline__ void epi_tmem_to_act(uint32_t taddr, const float *__restrict__ bias, uint8_t *act,
-                                                uint32_t row) {
-#pragma unroll 1
-  for (int c4 = 0; c4 < 4; ++c4) {
-    uint32_t r[32];
-    tmem_ld32(taddr + c4 * 32, r);
-    tmem_wait_ld();
+                                                uint32_t row, uint32_t half) {
+  uint32_t r[64];
+  tmem_ld32(taddr + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+  tmem_ld32(taddr + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+  tmem_wait_ld();
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const float4 b0 = *reinterpret_cast<const float4 *>(bias + c4 * 32 + q * 8);
-      const float4 b1 = *reinterpret_cast<const float4 *>(bias + c4 * 32 + q * 8 + 4);
-      float v[8];
-      v[0] = __uint_as_float(r[q * 8 + 0]) + b0.x; v[1] = __uint_as_float(r[q * 8 + 1]) + b0.y;
-      v[2] = __uint_as_float(r[q * 8 + 2]) + b0.z; v[3] = __uint_as_float(r[q * 8 + 3]) + b0.w;
-      v[4] = __uint_as_float(r[q * 8 + 4]) + b1.x; v[5] = __uint_as_float(r[q * 8 + 5]) + b1.y;
-      v[6] = __uint_as_float(r[q * 8 + 6]) + b1.z; v[7] = __uint_as_float(r[q * 8 + 7]) + b1.w;
-      if (kRelu) {
+  for (int q = 0; q < 8; ++q) {
+    const float4 b0 = *reinterpret_cast<const float4 *>(bias + half * 64 + q * 8);
+    const float4 b1 = *reinterpret_cast<const float4 *>(bias + half * 64 + q * 8 + 4);
+    float v[8];
+    v[0] = __uint_as_float(r[q * 8 + 0]) + b0.x; v[1] = __uint_as_float(r[q * 8 + 1]) + b0.y;
+    v[2] = __uint_as_float(r[q * 8 + 2]) + b0.z; v[3] = __uint_as_float(r[q * 8 + 3]) + b0.w;
+    v[4] = __uint_as_float(r[q * 8 + 4]) + b1.x; v[5] = __uint_as_float(r[q * 8 + 5]) + b1.y;
+    v[6] = __uint_as_float(r[q * 8 + 6]) + b1.z; v[7] = __uint_as_float(r[q * 8 + 7]) + b1.w;
+    if (kRelu) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
-      }
-      const uint4 o = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
-                                 pack_bf16x2(v[6], v[7]));
-      *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, c4 * 4 + q)) = o;
+      for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
     }
+    *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, half * 8 + q)) =
+        make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
   }
 }
 
@@ -73,6 +78,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1)
 mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ in_tiles, int64_t n_tiles,
                int nv, int64_t tiles_per_view, uint8_t *__restrict__ out_tiles, float *__restrict__ rgbs,
                uint8_t *__restrict__ acts) {
+  using L = FwdSmem<kFusion>;
+  constexpr int kRingSlots = L::kRingSlots;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) FwdBars bars;
   __shared__ uint32_t tmem_slot;
@@ -81,9 +88,11 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
   const uint32_t s_base = smem_u32(smem);
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
-  float *tab = reinterpret_cast<float *>(smem + kSmemTab);
+  float *tab = reinterpret_cast<float *>(smem + L::kTab);
   constexpr int kActsPerTile = kFusion ? 7 : 6;
   constexpr int kBlk0 = kFusion ? 3 : 0;
+  const bool staged = kFusion && nv <= kMaxStageViews;  // view tiles go through the ring (else: global loads)
+  const uint32_t view_slots = staged ? 2u * (uint32_t)nv : 0u;
 
   // ---- one-time setup
   {
@@ -100,8 +109,9 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
     for (int t = 0; t < 2; ++t) {
       mbar_init(smem_u32(&bars.h_ready[t]), 1);
       mbar_init(smem_u32(&bars.tmp_ready[t]), 1);
-      mbar_init(smem_u32(&bars.act_ready[t]), 128);
-      mbar_init(smem_u32(&bars.h_free[t]), 128);
+      mbar_init(smem_u32(&bars.act_ready[t]), kEpiThreads);
+      mbar_init(smem_u32(&bars.h_free[t]), kEpiThreads);
+      mbar_init(smem_u32(&bars.views_ready[t]), 1);
     }
     fence_barrier_init();
   }
@@ -127,6 +137,16 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         bulk_g2s(s_base + kSmemRing + slot * CN_SLAB_BYTES, src, CN_SLAB_BYTES, smem_u32(&bars.full[slot]));
         ++pc;
       };
+      auto load_weights = [&](int blk, int j) {
+        for (int s = 0; s < 2; ++s) load(packed + pack_fwd_block(kBlk0 + blk, j) + s * CN_SLAB_BYTES);
+      };
+      // fusion stage: the nv per-view tiles of fusion tile `tile` go through the ring as 2 slabs each
+      auto stage_views = [&](int64_t tile) {
+        const int64_t b = tile / tiles_per_view, tt = tile % tiles_per_view;
+        for (int v = 0; v < nv; ++v)
+          for (int sl = 0; sl < 2; ++sl)
+            load(in_tiles + ((b * nv + v) * tiles_per_view + tt) * (int64_t)CN_ACT_TILE_BYTES + sl * CN_SLAB_BYTES);
+      };
       for (int64_t p = blockIdx.x; p < n_pairs; p += gridDim.x) {
         const bool valid1 = 2 * p + 1 < n_tiles;
         if (!kFusion) {
@@ -135,10 +155,16 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
             load(in_tiles + (2 * p) * (int64_t)CN_X_TILE_BYTES + kb * CN_SLAB_BYTES);
             if (valid1) load(in_tiles + (2 * p + 1) * (int64_t)CN_X_TILE_BYTES + kb * CN_SLAB_BYTES);
           }
+          for (int blk = 0; blk < 3; ++blk)
+            for (int j = 0; j < 2; ++j) load_weights(blk, j);
+        } else {
+          if (staged) stage_views(2 * p);
+          load_weights(0, 0);  // first weights before the second tile's views: MMA of tile 0 can start
+          if (staged && valid1) stage_views(2 * p + 1);
+          load_weights(0, 1);
+          for (int blk = 1; blk < 3; ++blk)
+            for (int j = 0; j < 2; ++j) load_weights(blk, j);
         }
-        for (int blk = 0; blk < 3; ++blk)
-          for (int j = 0; j < 2; ++j)
-            for (int s = 0; s < 2; ++s) load(packed + pack_fwd_block(kBlk0 + blk, j) + s * CN_SLAB_BYTES);
       }
     }
   } else if (warp == 1) {
@@ -193,9 +219,20 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         }
         for (int blk = 0; blk < 3; ++blk) {
           for (int j = 0; j < 2; ++j) {
+            // ring order of the fusion stage: views(t0), Wa0, views(t1), Wb0, ...  The view slabs are read by
+            // the epilogue warps, but this thread stays the ONLY in-order waiter on the ring's full barriers
+            // (a waiter that skips ring rounds would alias mbarrier phase parities) and forwards "landed".
+            if (kFusion && blk == 0 && j == 0 && view_slots) {
+              for (uint32_t i = 0; i < view_slots; ++i) (void)next_slot();
+              mbar_arrive(smem_u32(&bars.views_ready[0]));
+            }
             const uint32_t s0 = next_slot();
             const uint32_t s1 = next_slot();
             for (int t = 0; t < nt; ++t) {
+              if (kFusion && blk == 0 && j == 0 && t == 1 && view_slots) {
+                for (uint32_t i = 0; i < view_slots; ++i) (void)next_slot();
+                mbar_arrive(smem_u32(&bars.views_ready[1]));
+              }
               mbar_wait(smem_u32(&bars.act_ready[t]), n_act[t] & 1u);
               ++n_act[t];
               tc_fence_after();
@@ -214,17 +251,20 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
       }
     }
   } else {
-    // =========================== epilogue warpgroups ===========================
-    const int t = (warp - 2) >> 2;                  // tile slot of this warpgroup
+    // =========================== epilogue: 8 warps per tile ===========================
+    const uint32_t e = warp - 2;                    // 0..15
+    const int t = e >> 3;                           // tile slot of this warp
+    const uint32_t half = (e >> 2) & 1u;            // column half [64*half, 64*half + 64)
     const uint32_t quad = warp & 3u;                // TMEM lane quadrant this warp may access
     const uint32_t row = quad * 32u + lane;         // row of the tile == TMEM lane
-    const bool wg_leader = ((warp - 2) & 3u) == 0 && lane == 0;
+    const bool wg_leader = (e & 7u) == 0 && lane == 0;
     const uint32_t bar_id = 1 + t;
     uint8_t *act = smem + kSmemAct + t * CN_ACT_TILE_BYTES;
     const uint32_t act_u32 = s_base + kSmemAct + t * CN_ACT_TILE_BYTES;
     const uint32_t t_h = tmem + ((quad * 32u) << 16) + t * 256;
     const uint32_t t_tmp = t_h + 128;
-    uint32_t n_h = 0, n_tmp = 0;
+    uint32_t n_h = 0, n_tmp = 0, n_views = 0;
+    uint32_t ring_base = 0;                         // ring position at the start of the current pair
     bool store_pending = false;
 
     // make this thread's writes to ACT visible to the async proxy, optionally stream the tile to
@@ -232,7 +272,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
     auto publish = [&](uint8_t *gdst, bool signal_mma) {
       fence_proxy_async_smem();
       if (gdst) {
-        named_bar_sync(bar_id, 128);
+        named_bar_sync(bar_id, kEpiThreads);
         if (wg_leader) {
           bulk_s2g(gdst, act_u32, CN_ACT_TILE_BYTES);
           bulk_commit();
@@ -248,7 +288,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
     auto acquire = [&]() {
       if (store_pending) {
         if (wg_leader) bulk_wait_read0();
-        named_bar_sync(bar_id, 128);
+        named_bar_sync(bar_id, kEpiThreads);
         store_pending = false;
       }
     };
@@ -263,16 +303,28 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         const int64_t b = tile / tiles_per_view, tt = tile % tiles_per_view;
         const float inv_nv = 1.f / (float)nv;
         acquire();
+        // ring position of this tile's view slabs: views(t0) | Wa0 (2 slots) | views(t1) | ...
+        const uint32_t vbase = ring_base + (t ? view_slots + 2u : 0u);
+        if (staged) {
+          mbar_wait(smem_u32(&bars.views_ready[t]), n_views & 1u);
+          ++n_views;
+        }
 #pragma unroll 1
-        for (int c4 = 0; c4 < 4; ++c4) {
+        for (int c2 = 0; c2 < 2; ++c2) {
           uint32_t r[32];
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
+            const uint32_t chunk = half * 8 + c2 * 4 + q;
             float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             for (int v = 0; v < nv; ++v) {
-              const uint8_t *src = in_tiles + ((b * nv + v) * tiles_per_view + tt) * (int64_t)CN_ACT_TILE_BYTES +
-                                   tile_chunk_off(row, c4 * 4 + q);
-              const uint4 x = ldg_nc_u4(src);
+              uint4 x;
+              if (staged)  // chunk's slab (= half) of view v sits in ring slot vbase + 2v + half
+                x = *reinterpret_cast<const uint4 *>(smem + kSmemRing +
+                                                     ((vbase + 2u * v + half) % kRingSlots) * CN_SLAB_BYTES +
+                                                     tile_chunk_off(row, chunk & 7u));
+              else
+                x = ldg_nc_u4(in_tiles + ((b * nv + v) * tiles_per_view + tt) * (int64_t)CN_ACT_TILE_BYTES +
+                              tile_chunk_off(row, chunk));
               acc[0] += bf16_lo(x.x); acc[1] += bf16_hi(x.x); acc[2] += bf16_lo(x.y); acc[3] += bf16_hi(x.y);
               acc[4] += bf16_lo(x.z); acc[5] += bf16_hi(x.z); acc[6] += bf16_lo(x.w); acc[7] += bf16_hi(x.w);
             }
@@ -283,11 +335,17 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
               r[q * 8 + i] = __float_as_uint(m[i]);
               m[i] = fmaxf(m[i], 0.f);
             }
-            *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, c4 * 4 + q)) =
+            *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, chunk)) =
                 make_uint4(pack_bf16x2(m[0], m[1]), pack_bf16x2(m[2], m[3]), pack_bf16x2(m[4], m[5]),
                            pack_bf16x2(m[6], m[7]));
           }
-          tmem_st32(t_h + c4 * 32, r);
+          tmem_st32(t_h + half * 64 + c2 * 32, r);
+        }
+        if (staged) {
+          // every thread has read its rows: hand the view slots back to the producer
+          named_bar_sync(bar_id, kEpiThreads);
+          if (wg_leader)
+            for (uint32_t i = 0; i < view_slots; ++i) mbar_arrive(smem_u32(&bars.empty[(vbase + i) % kRingSlots]));
         }
         tmem_wait_st();
         publish(my_acts, true);
@@ -301,7 +359,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         if (!(kFusion && blk == 0)) {
           // E_a: relu(h + cumulative bias) -> operand of the block's first Dense
           acquire();
-          epi_tmem_to_act<true>(t_h, tab + (2 * blk) * 128, act, row);
+          epi_tmem_to_act<true>(t_h, tab + (2 * blk) * 128, act, row, half);
           publish(my_acts ? my_acts + (2 * blk) * CN_ACT_TILE_BYTES : nullptr, true);
         }
         // E_b: relu(t + ba) -> operand of the block's second Dense
@@ -309,7 +367,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         ++n_tmp;
         tc_fence_after();
         acquire();
-        epi_tmem_to_act<true>(t_tmp, tab + (2 * blk + 1) * 128, act, row);
+        epi_tmem_to_act<true>(t_tmp, tab + (2 * blk + 1) * 128, act, row, half);
         publish(my_acts ? my_acts + (2 * blk + 1) * CN_ACT_TILE_BYTES : nullptr, true);
         mbar_wait(smem_u32(&bars.h_ready[t]), n_h & 1u);
         ++n_h;
@@ -319,19 +377,22 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
       acquire();
       if (!kFusion) {
         // ---- h3 = h + cumulative bias -> bf16 tile for the fusion stage
-        epi_tmem_to_act<false>(t_h, tab + 6 * 128, act, row);
+        epi_tmem_to_act<false>(t_h, tab + 6 * 128, act, row, half);
         tc_fence_before();
         mbar_arrive(smem_u32(&bars.h_free[t]));
         publish(out_tiles + tile * (int64_t)CN_ACT_TILE_BYTES, false);
       } else {
-        // ---- readout: relu(e) . Wr + br, sigmoid / softplus (layers.py:392-397)
+        // ---- readout: relu(e) . Wr + br, sigmoid / softplus (layers.py:392-397).  The two column-half
+        // warps of a row split the OUTPUTS (half 0: r,g; half 1: b,sigma), each over all 128 inputs; the
+        // relu(e) tile saved for the backward is still written half by half.
         const float *wr = tab + 7 * 128;
-        float y0 = wr[512 + 0], y1 = wr[512 + 1], y2 = wr[512 + 2], y3 = wr[512 + 3];
+        float ya = wr[512 + 2 * half], yb = wr[512 + 2 * half + 1];
 #pragma unroll 1
         for (int c4 = 0; c4 < 4; ++c4) {
           uint32_t r[32];
           tmem_ld32(t_h + c4 * 32, r);
           tmem_wait_ld();
+          const bool mine = (uint32_t)(c4 >> 1) == half;
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
             float v[8];
@@ -339,23 +400,23 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
             for (int i = 0; i < 8; ++i) {
               const int col = c4 * 32 + q * 8 + i;
               v[i] = fmaxf(__uint_as_float(r[q * 8 + i]) + tab[6 * 128 + col], 0.f);
-              const float4 w = *reinterpret_cast<const float4 *>(wr + col * 4);
-              y0 += v[i] * w.x; y1 += v[i] * w.y; y2 += v[i] * w.z; y3 += v[i] * w.w;
+              const float2 w = *reinterpret_cast<const float2 *>(wr + col * 4 + 2 * half);
+              ya += v[i] * w.x;
+              yb += v[i] * w.y;
             }
-            if (my_acts)
+            if (my_acts && mine)
               *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, c4 * 4 + q)) =
                   make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
                              pack_bf16x2(v[6], v[7]));
           }
         }
-        float4 o;
-        o.x = 1.f / (1.f + expf(-y0));
-        o.y = 1.f / (1.f + expf(-y1));
-        o.z = 1.f / (1.f + expf(-y2));
-        o.w = y3 > 20.f ? y3 : log1pf(expf(y3));
-        reinterpret_cast<float4 *>(rgbs)[tile * 128 + row] = o;
+        float2 o;
+        o.x = 1.f / (1.f + expf(-ya));
+        o.y = half ? (yb > 20.f ? yb : log1pf(expf(yb))) : 1.f / (1.f + expf(-yb));
+        reinterpret_cast<float2 *>(rgbs)[(tile * 128 + row) * 2 + half] = o;
         publish(my_acts ? my_acts + 6 * CN_ACT_TILE_BYTES : nullptr, false);
       }
+      ring_base += 12u + view_slots * ((2 * p + 1 < n_tiles) ? 2u : 1u);
     }
     if (wg_leader) bulk_wait0();
   }
@@ -372,17 +433,19 @@ static int launch_fwd(bool fusion, const void *packed, const void *in_tiles, int
   const unsigned grid = (unsigned)(n_pairs < kNumSMs ? n_pairs : kNumSMs);
   cudaError_t e;
   if (fusion) {
-    e = cudaFuncSetAttribute(mlp_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmemBytes);
+    constexpr uint32_t bytes = FwdSmem<true>::kBytes;
+    e = cudaFuncSetAttribute(mlp_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e == cudaSuccess)
-      mlp_fwd_kernel<true><<<grid, kFwdThreads, kFwdSmemBytes, st>>>(
-          (const uint8_t *)packed, (const uint8_t *)in_tiles, n_tiles, nv, tiles_per_view, (uint8_t *)out_tiles, rgbs,
-          (uint8_t *)acts);
+      mlp_fwd_kernel<true><<<grid, kFwdThreads, bytes, st>>>((const uint8_t *)packed, (const uint8_t *)in_tiles,
+                                                             n_tiles, nv, tiles_per_view, (uint8_t *)out_tiles, rgbs,
+                                                             (uint8_t *)acts);
   } else {
-    e = cudaFuncSetAttribute(mlp_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmemBytes);
+    constexpr uint32_t bytes = FwdSmem<false>::kBytes;
+    e = cudaFuncSetAttribute(mlp_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e == cudaSuccess)
-      mlp_fwd_kernel<false><<<grid, kFwdThreads, kFwdSmemBytes, st>>>(
-          (const uint8_t *)packed, (const uint8_t *)in_tiles, n_tiles, nv, tiles_per_view, (uint8_t *)out_tiles, rgbs,
-          (uint8_t *)acts);
+      mlp_fwd_kernel<false><<<grid, kFwdThreads, bytes, st>>>((const uint8_t *)packed, (const uint8_t *)in_tiles,
+                                                              n_tiles, nv, tiles_per_view, (uint8_t *)out_tiles, rgbs,
+                                                              (uint8_t *)acts);
   }
   if (e != cudaSuccess) {
     set_error("mlp_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
