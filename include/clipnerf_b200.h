@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define CN_ABI_VERSION 1
+#define CN_ABI_VERSION 2
 #define CN_TILE_ROWS 128
 #define CN_HIDDEN 128
 #define CN_FEAT_C 256          /* combined_features channels (model_v0.py:60)            */
@@ -93,13 +93,28 @@ int cn_sample_pdf_bwd(const float *z_c, const float *w_c, const float *u, const 
 
 /* ---- projection + bilinear gather + positional encoding ------------------------- */
 
+/* The gather and its backward work on SPATIALLY BINNED sample-view rows: every row is keyed by
+ * the 8x8-texel tile (and the cell inside it) that its clamped bilinear footprint falls in, the
+ * rows are counting-sorted by key, and each CTA stages one 9x9-texel tile of the feature map in
+ * shared memory (cp.async.bulk) and serves all rows of that tile from there; the backward
+ * accumulates the tile's gradient on chip and adds it to d_features with one bulk reduction
+ * (cp.reduce.async.bulk) per tile row.  The sorted row records live in a caller-allocated
+ * workspace that the forward fills and the backward re-uses.                                   */
+size_t cn_gather_ws_bytes(int32_t b, int32_t nv, int32_t H, int32_t W, int32_t nr, int32_t S);
+
+/* projection + binning only (fills `ws`; no MLP-input rows are written)                        */
+int cn_project_bin(const CnScene *scene, const float *ray_o, const float *ray_d, const float *z,
+                   int32_t nr, int32_t S, void *ws, size_t ws_bytes, void *stream);
+
 /* compute_pixel_in_image_mv + get_projection_features_mv +
  * world_to_camera_direction_vector_mv + position_encoding + the concat of
  * layers.py:362 (nerf_utils.py:64-126,277-285): writes the MLP input rows as bf16
  * tile images X [b*nv*nr*S/128 tiles][6 slabs].  Column order inside X:
- * [feat 0..255 | posenc(p_cam) 60 | posenc(d_cam) 60 | 2*img-1 (3) | 0 (5)].          */
+ * [feat 0..255 | posenc(p_cam) 60 | posenc(d_cam) 60 | 2*img-1 (3) | 0 (5)].
+ * Fills `ws` (cn_gather_ws_bytes) with the binned row records.                                 */
 int cn_project_gather_fwd(const CnScene *scene, const float *ray_o, const float *ray_d,
-                          const float *z, int32_t nr, int32_t S, void *x_tiles, void *stream);
+                          const float *z, int32_t nr, int32_t S, void *x_tiles, void *ws,
+                          size_t ws_bytes, void *stream);
 /* fp32 op-level view of the same computation in the reference's tensor layouts
  * (compute_pixel_in_image_mv + get_projection_features_mv): pix [b,nv,nr,S,2],
  * corner (x0,y0) int32 [b,nv,nr,S,2], gathered [b,nv,nr,S,259] (nullable),
@@ -114,11 +129,12 @@ int cn_interpolate_bilinear(const float *grid, const float *query, int32_t B, in
 /* position_encoding (nerf_utils.py:108-126): pos [n,D] -> out [n, D*n_freq*2]         */
 int cn_position_encoding(const float *pos, int64_t n, int32_t D, int32_t n_freq, float freq0,
                          float *out, void *stream);
-/* backward: dX tile images -> scatter-add into d_features [b,nv,H,W,256] (nullable)
- * and dz [b,nr,S] (nullable, +=) through bilinear coordinates and posenc(p_cam).       */
+/* backward: dX tile images -> d_features [b,nv,H,W,256] (nullable, +=) and dz [b,nr,S]
+ * (nullable, +=) through bilinear coordinates and posenc(p_cam).  `ws` must hold the records
+ * written by cn_project_gather_fwd / cn_project_bin for the same scene, rays and z.            */
 int cn_project_gather_bwd(const CnScene *scene, const float *ray_o, const float *ray_d,
-                          const float *z, int32_t nr, int32_t S, const void *dx_tiles,
-                          float *d_features, float *dz, void *stream);
+                          const float *z, int32_t nr, int32_t S, const void *dx_tiles, void *ws,
+                          size_t ws_bytes, float *d_features, float *dz, void *stream);
 
 /* ---- compositing --------------------------------------------------------------- */
 
@@ -183,6 +199,13 @@ int cn_probe_umma(const void *a_img, int32_t a_bytes, const void *b_img, int32_t
                   int32_t n_mma, int32_t a_major_mn, int32_t b_major_mn, int32_t a_lbo,
                   int32_t a_sbo, int32_t a_kstep, int32_t b_lbo, int32_t b_sbo, int32_t b_kstep,
                   float *d_out, void *stream);
+
+/* Throughput probe for the two ways of adding a 9x9-texel tile (81 KiB) to a [n_img,H,W,256]
+ * fp32 map: mode 0 = cp.reduce.async.bulk.add.f32 from shared memory, mode 1 =
+ * red.global.add.v4.f32 from registers.  Every CTA adds `iters` tiles at pseudo-random
+ * positions; the caller times the launch.                                                      */
+int cn_probe_tile_reduce(float *map, int32_t n_img, int32_t H, int32_t W, int32_t iters, int32_t mode,
+                         int32_t ctas_per_sm, void *stream);
 
 #ifdef __cplusplus
 }

@@ -6,12 +6,12 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_char_p, c_double, c_float, c_int32, c_int64, c_void_p
+from ctypes import c_char_p, c_double, c_float, c_int32, c_int64, c_size_t, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), 'lib', 'libclipnerf_b200.so')
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 TILE_ROWS = 128
 SLAB_BYTES = 16384
 ACT_TILE_BYTES = 32768
@@ -35,11 +35,13 @@ PROTOTYPES = {
     'cn_sample_pdf_fwd': [_P, _P, _P, c_int64, _P, _P, _P, _P],
     'cn_sample_pdf': [_P, _P, _P, c_int64, _P, _P, _P],
     'cn_sample_pdf_bwd': [_P, _P, _P, _P, _P, c_int64, _P, _P],
-    'cn_project_gather_fwd': [ctypes.POINTER(CnScene), _P, _P, _P, c_int32, c_int32, _P, _P],
+    'cn_gather_ws_bytes': [c_int32, c_int32, c_int32, c_int32, c_int32, c_int32],
+    'cn_project_bin': [ctypes.POINTER(CnScene), _P, _P, _P, c_int32, c_int32, _P, c_size_t, _P],
+    'cn_project_gather_fwd': [ctypes.POINTER(CnScene), _P, _P, _P, c_int32, c_int32, _P, _P, c_size_t, _P],
     'cn_project_gather_debug': [ctypes.POINTER(CnScene), _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P, _P],
     'cn_interpolate_bilinear': [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int64, _P, _P],
     'cn_position_encoding': [_P, c_int64, c_int32, c_int32, c_float, _P, _P],
-    'cn_project_gather_bwd': [ctypes.POINTER(CnScene), _P, _P, _P, c_int32, c_int32, _P, _P, _P, _P],
+    'cn_project_gather_bwd': [ctypes.POINTER(CnScene), _P, _P, _P, c_int32, c_int32, _P, _P, c_size_t, _P, _P, _P],
     'cn_composite_fwd': [_P, _P, c_int64, c_int32, _P, _P, _P, _P],
     'cn_composite_bwd': [_P, _P, c_int64, c_int32, _P, _P, _P, _P, _P, _P],
     'cn_pack_weights': [_P, _P, _P],
@@ -52,8 +54,9 @@ PROTOTYPES = {
     'cn_mlp_l0_wgrad': [_P, _P, c_int64, _P, _P],
     'cn_probe_umma': [_P, c_int32, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,
                       c_int32, c_int32, _P, _P],
+    'cn_probe_tile_reduce': [_P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P],
 }
-_RESTYPES = {'cn_last_error': c_char_p}
+_RESTYPES = {'cn_last_error': c_char_p, 'cn_gather_ws_bytes': c_size_t}
 
 _lib = None
 
@@ -82,13 +85,14 @@ class CnError(RuntimeError):
 
 # kernels launched by each entry point (for launch accounting in bench.py)
 KERNELS_PER_CALL = {name: 1 for name in PROTOTYPES}
-KERNELS_PER_CALL.update({'cn_abi_version': 0, 'cn_last_error': 0, 'cn_mlp_l0_wgrad': 2})
+KERNELS_PER_CALL.update({'cn_abi_version': 0, 'cn_last_error': 0, 'cn_gather_ws_bytes': 0, 'cn_mlp_l0_wgrad': 2,
+                         'cn_project_bin': 4, 'cn_project_gather_fwd': 5})
 
 LAUNCHES = 0          # running count of kernel launches issued through the ABI
 TIMER = None          # optional callable(name) -> context manager, set by bench.py to time stages
 
 
-def call(name: str, *args):
+def call(name: str, *args, extra_launches=None):
     global LAUNCHES
     lib = load()
     if TIMER is not None:
@@ -99,4 +103,4 @@ def call(name: str, *args):
     if rc != 0:
         msg = lib.cn_last_error().decode('utf-8', 'replace')
         raise CnError(f'{name} failed (rc={rc}): {msg}')
-    LAUNCHES += KERNELS_PER_CALL[name]
+    LAUNCHES += KERNELS_PER_CALL[name] if extra_launches is None else extra_launches

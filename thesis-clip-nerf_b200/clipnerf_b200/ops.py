@@ -83,12 +83,33 @@ def n_tiles(rows: int) -> int:
     return rows // TILE_ROWS
 
 
-def project_gather_fwd(scene: Scene, ray_o, ray_d, z) -> torch.Tensor:
+def gather_workspace(scene: Scene, nr: int, S: int) -> torch.Tensor:
+    """caller-owned workspace of the binned gather (sorted row records; filled by the forward or by
+    ``project_bin`` and re-used by the backward of the same scene / rays / z)."""
+    n = _abi.load().cn_gather_ws_bytes(scene.b, scene.nv, scene.H, scene.W, nr, S)
+    assert n > 0
+    return _bytes(n, scene.device)
+
+
+def project_bin(scene: Scene, ray_o, ray_d, z, ws: Optional[torch.Tensor] = None) -> torch.Tensor:
     ray_o, ray_d, z = _f32c(ray_o), _f32c(ray_d), _f32c(z)
     b, nr, S = z.shape
+    if ws is None:
+        ws = gather_workspace(scene, nr, S)
+    call('cn_project_bin', ctypes.byref(scene.c), _ptr(ray_o), _ptr(ray_d), _ptr(z), nr, S, _ptr(ws), ws.numel(),
+         _stream())
+    return ws
+
+
+def project_gather_fwd(scene: Scene, ray_o, ray_d, z, ws: Optional[torch.Tensor] = None, return_ws: bool = False):
+    ray_o, ray_d, z = _f32c(ray_o), _f32c(ray_d), _f32c(z)
+    b, nr, S = z.shape
+    if ws is None:
+        ws = gather_workspace(scene, nr, S)
     x = _bytes(n_tiles(b * scene.nv * nr * S) * X_TILE_BYTES, z.device)
-    call('cn_project_gather_fwd', ctypes.byref(scene.c), _ptr(ray_o), _ptr(ray_d), _ptr(z), nr, S, _ptr(x), _stream())
-    return x
+    call('cn_project_gather_fwd', ctypes.byref(scene.c), _ptr(ray_o), _ptr(ray_d), _ptr(z), nr, S, _ptr(x), _ptr(ws),
+         ws.numel(), _stream())
+    return (x, ws) if return_ws else x
 
 
 def project_gather_debug(scene: Scene, ray_o, ray_d, z, gather: bool = True, cam: bool = False):
@@ -131,11 +152,15 @@ def sample_pdf(bins, weights, u, return_above: bool = False):
 
 
 def project_gather_bwd(scene: Scene, ray_o, ray_d, z, dx_tiles, d_features: Optional[torch.Tensor],
-                       dz: Optional[torch.Tensor]) -> None:
+                       dz: Optional[torch.Tensor], ws: Optional[torch.Tensor] = None) -> None:
+    """``ws``: the workspace the forward filled for the same (scene, rays, z); rebuilt when omitted."""
     ray_o, ray_d, z = _f32c(ray_o), _f32c(ray_d), _f32c(z)
     b, nr, S = z.shape
+    if ws is None:
+        ws = project_bin(scene, ray_o, ray_d, z)
+    n_kernels = (2 if dz is not None else 0) + (1 if d_features is not None else 0)
     call('cn_project_gather_bwd', ctypes.byref(scene.c), _ptr(ray_o), _ptr(ray_d), _ptr(z), nr, S, _ptr(dx_tiles),
-         _ptr(d_features), _ptr(dz), _stream())
+         _ptr(ws), ws.numel(), _ptr(d_features), _ptr(dz), _stream(), extra_launches=n_kernels)
 
 
 def composite_fwd(z, rgbs):
@@ -224,6 +249,12 @@ def mlp_l0_dgrad(packed, g0_tiles):
 def mlp_l0_wgrad(x_tiles, g0_tiles, grad):
     nt = g0_tiles.numel() // ACT_TILE_BYTES
     call('cn_mlp_l0_wgrad', _ptr(x_tiles), _ptr(g0_tiles), nt, _ptr(grad), _stream())
+
+
+def probe_tile_reduce(map_: torch.Tensor, iters: int, mode: int, ctas_per_sm: int = 1) -> None:
+    n_img, H, W, C = map_.shape
+    assert C == 256 and map_.dtype == torch.float32
+    call('cn_probe_tile_reduce', _ptr(map_), n_img, H, W, iters, mode, ctas_per_sm, _stream())
 
 
 def probe_umma(a_img: torch.Tensor, b_img: torch.Tensor, n_mma: int, a_mn: bool, b_mn: bool, a_lbo: int, a_sbo: int,

@@ -19,18 +19,18 @@ from ._abi import NET_PARAMS, TILE_ROWS
 
 class _Pass:
     """Everything one (coarse or fine) pass keeps for its backward."""
-    __slots__ = ('z', 'x', 'acts_f', 'acts_u', 'rgbs', 'rgb', 'depth', 'weights', 'packed')
+    __slots__ = ('z', 'x', 'ws', 'acts_f', 'acts_u', 'rgbs', 'rgb', 'depth', 'weights', 'packed')
 
 
 def _pass_fwd(packed, scene: ops.Scene, ray_o, ray_d, z, save: bool) -> _Pass:
     P = _Pass()
     P.z, P.packed = z, packed
-    P.x = ops.project_gather_fwd(scene, ray_o, ray_d, z)
+    P.x, P.ws = ops.project_gather_fwd(scene, ray_o, ray_d, z, return_ws=True)
     h3, P.acts_f = ops.mlp_feature_fwd(packed, P.x, save)
     P.rgbs, P.acts_u = ops.mlp_fusion_fwd(packed, h3, scene.b, scene.nv, save)
     P.rgb, P.depth, P.weights = ops.composite_fwd(z, P.rgbs.view(*z.shape, 4))
     if not save:
-        P.x = None
+        P.x = P.ws = None
     return P
 
 
@@ -46,7 +46,7 @@ def _pass_bwd(P: _Pass, params, grad, scene: ops.Scene, ray_o, ray_d, d_rgb, d_d
     ops.mlp_l0_wgrad(P.x, gf, grad)
     if d_features is not None or need_dz:
         dx = ops.mlp_l0_dgrad(P.packed, gf)
-        ops.project_gather_bwd(scene, ray_o, ray_d, P.z, dx, d_features, dz)
+        ops.project_gather_bwd(scene, ray_o, ray_d, P.z, dx, d_features, dz, P.ws)
     return dz
 
 

@@ -13,6 +13,7 @@ namespace cn {
 // ---------------------------------------------------------------- host error plumbing
 void set_error(const char *fmt, ...);
 int check_launch(const char *what);
+int check_scene(const CnScene *s, const char *who);
 
 #define CN_REQUIRE(cond, ...)        \
   do {                               \
@@ -122,6 +123,12 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void *src, uin
 }
 __device__ __forceinline__ void bulk_s2g(void *dst, uint32_t src_smem, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src_smem), "r"(bytes)
+               : "memory");
+}
+// shared -> global element-wise fp32 add performed by the TMA unit / L2 (no SM issue slots)
+__device__ __forceinline__ void bulk_reduce_add_f32(void *dst, uint32_t src_smem, uint32_t bytes) {
+  asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst),
+               "r"(src_smem), "r"(bytes)
                : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }

@@ -69,7 +69,62 @@ probe_umma_kernel(const uint8_t *__restrict__ a_img, uint32_t a_bytes, const uin
   if (warp == 0) tmem_dealloc(tmem, 128);
 }
 
+// ---- tile reduce probe: 81 KiB tiles added to a [n_img, H, W, 256] fp32 map
+constexpr int kProbeTT = 9;
+__global__ void __launch_bounds__(256)
+probe_tile_reduce_kernel(float *__restrict__ map, int n_img, int H, int W, int iters, int mode) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  float *tile = reinterpret_cast<float *>(smem);
+  for (int i = threadIdx.x; i < kProbeTT * kProbeTT * 256; i += blockDim.x) tile[i] = 1.f;
+  fence_proxy_async_smem();
+  __syncthreads();
+  const int tiles_x = (W - 1) / 8, tiles_y = (H - 1) / 8;
+  uint32_t rng = 0x9e3779b9u * (blockIdx.x + 1);
+  for (int it = 0; it < iters; ++it) {
+    rng = rng * 1664525u + 1013904223u;
+    const int tx = (rng >> 8) % tiles_x;
+    rng = rng * 1664525u + 1013904223u;
+    const int ty = (rng >> 8) % tiles_y;
+    rng = rng * 1664525u + 1013904223u;
+    const int img = (rng >> 8) % n_img;
+    float *dst = map + (((int64_t)img * H + ty * 8) * W + tx * 8) * 256;
+    if (mode == 0) {
+      if (threadIdx.x == 0) {
+        for (int yy = 0; yy < kProbeTT; ++yy)
+          bulk_reduce_add_f32(dst + (int64_t)yy * W * 256, smem_u32(tile) + yy * kProbeTT * 1024, kProbeTT * 1024);
+        bulk_commit();
+        bulk_wait_read0();
+      }
+      __syncthreads();
+    } else {
+      // 81 texels x 64 float4 per texel, one float4 per thread per step
+      for (int i = threadIdx.x; i < kProbeTT * kProbeTT * 64; i += blockDim.x) {
+        const int tex = i >> 6, c4 = i & 63;
+        const int y = tex / kProbeTT, x = tex % kProbeTT;
+        red_add_f4(dst + ((int64_t)y * W + x) * 256 + c4 * 4, 1.f, 1.f, 1.f, 1.f);
+      }
+    }
+  }
+  if (mode == 0 && threadIdx.x == 0) bulk_wait0();
+}
+
 }  // namespace cn
+
+extern "C" int cn_probe_tile_reduce(float *map, int32_t n_img, int32_t H, int32_t W, int32_t iters, int32_t mode,
+                                    int32_t ctas_per_sm, void *stream) {
+  using namespace cn;
+  CN_REQUIRE(map && n_img > 0 && H >= 17 && W >= 17 && iters > 0 && ctas_per_sm > 0 && ctas_per_sm <= 2,
+             "cn_probe_tile_reduce: bad arguments");
+  const size_t smem = kProbeTT * kProbeTT * 1024 + 1024;
+  cudaError_t e = cudaFuncSetAttribute(probe_tile_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) {
+    set_error("cn_probe_tile_reduce: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
+  probe_tile_reduce_kernel<<<kNumSMs * ctas_per_sm, 256, smem, (cudaStream_t)stream>>>(map, n_img, H, W, iters, mode);
+  return check_launch("cn_probe_tile_reduce");
+}
 
 extern "C" int cn_probe_umma(const void *a_img, int32_t a_bytes, const void *b_img, int32_t b_bytes, int32_t n_mma,
                              int32_t a_major_mn, int32_t b_major_mn, int32_t a_lbo, int32_t a_sbo, int32_t a_kstep,
