@@ -136,6 +136,15 @@ int cn_project_gather_bwd(const CnScene *scene, const float *ray_o, const float 
                           const float *z, int32_t nr, int32_t S, const void *dx_tiles, void *ws,
                           size_t ws_bytes, float *d_features, float *dz, void *stream);
 
+/* Feature-map gradient of several passes in ONE sweep (e.g. coarse + fine): every texel of
+ * d_features [b,nv,H,W,256] sums the rows of its four neighbouring cells of every set and is
+ * written exactly once (accumulate = 0: the map needs no zero fill; accumulate = 1: +=).
+ * Host arrays of length n_sets (<= 4): nr, S, ws, ws_bytes, dx_tiles; every workspace must have
+ * been filled by cn_project_gather_fwd / cn_project_bin for this scene.                       */
+int cn_feature_grad(const CnScene *scene, int32_t n_sets, const int32_t *nr_host, const int32_t *S_host,
+                    void *const *ws_host, const size_t *ws_bytes_host, const void *const *dx_tiles_host,
+                    float *d_features, int32_t accumulate, void *stream);
+
 /* ---- compositing --------------------------------------------------------------- */
 
 /* volumetric_render (model_v0.py:89-100): z [n,S], rgbs [n,S,4] = (r,g,b,sigma)

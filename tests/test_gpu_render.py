@@ -89,8 +89,9 @@ def test_fine_pass_and_sampler_gradients(cuda, nv):
     d_rgb = 2.0 * (Fp.rgb - tgt) / tgt.numel()
     d_depth = torch.full_like(Fp.depth, 0.1 / Fp.depth.numel())
     g_f = torch.zeros_like(pf)
-    d_feat = torch.zeros_like(scene.features)
-    dz_f = render._pass_bwd(Fp, pf, g_f, scene, ro, rd, d_rgb, d_depth, None, d_feat, True)
+    dz_f, dx_f = render._pass_bwd(Fp, pf, g_f, scene, ro, rd, d_rgb, d_depth, None, True, True)
+    d_feat = torch.full_like(scene.features, float('nan'))      # every texel is written exactly once
+    ops.feature_grad(scene, [(Fp.ws, dx_f, z_f.shape[1], z_f.shape[2])], d_feat, accumulate=False)
     dw_c = ops.sample_pdf_bwd(z_c.to(cuda), w_c.to(cuda), sc['u_pdf'].to(cuda), perm, dz_f)
     errs = {'fine_rgb': rel_err(Fp.rgb, rgb_r), 'fine_depth': rel_err(Fp.depth, depth_r)}
     for name, gv in params.to_named(g_f.cpu(), 'fine').items():

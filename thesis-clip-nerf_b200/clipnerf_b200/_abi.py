@@ -42,6 +42,7 @@ PROTOTYPES = {
     'cn_interpolate_bilinear': [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int64, _P, _P],
     'cn_position_encoding': [_P, c_int64, c_int32, c_int32, c_float, _P, _P],
     'cn_project_gather_bwd': [ctypes.POINTER(CnScene), _P, _P, _P, c_int32, c_int32, _P, _P, c_size_t, _P, _P, _P],
+    'cn_feature_grad': [ctypes.POINTER(CnScene), c_int32, _P, _P, _P, _P, _P, _P, c_int32, _P],
     'cn_composite_fwd': [_P, _P, c_int64, c_int32, _P, _P, _P, _P],
     'cn_composite_bwd': [_P, _P, c_int64, c_int32, _P, _P, _P, _P, _P, _P],
     'cn_pack_weights': [_P, _P, _P],
@@ -86,7 +87,7 @@ class CnError(RuntimeError):
 # kernels launched by each entry point (for launch accounting in bench.py)
 KERNELS_PER_CALL = {name: 1 for name in PROTOTYPES}
 KERNELS_PER_CALL.update({'cn_abi_version': 0, 'cn_last_error': 0, 'cn_gather_ws_bytes': 0, 'cn_mlp_l0_wgrad': 2,
-                         'cn_project_bin': 4, 'cn_project_gather_fwd': 5})
+                         'cn_project_bin': 4, 'cn_project_gather_fwd': 5, 'cn_feature_grad': 2})
 
 LAUNCHES = 0          # running count of kernel launches issued through the ABI
 TIMER = None          # optional callable(name) -> context manager, set by bench.py to time stages

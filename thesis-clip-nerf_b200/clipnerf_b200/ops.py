@@ -158,9 +158,23 @@ def project_gather_bwd(scene: Scene, ray_o, ray_d, z, dx_tiles, d_features: Opti
     b, nr, S = z.shape
     if ws is None:
         ws = project_bin(scene, ray_o, ray_d, z)
-    n_kernels = (2 if dz is not None else 0) + (1 if d_features is not None else 0)
+    n_kernels = (2 if dz is not None else 0) + (2 if d_features is not None else 0)
     call('cn_project_gather_bwd', ctypes.byref(scene.c), _ptr(ray_o), _ptr(ray_d), _ptr(z), nr, S, _ptr(dx_tiles),
          _ptr(ws), ws.numel(), _ptr(d_features), _ptr(dz), _stream(), extra_launches=n_kernels)
+
+
+def feature_grad(scene: Scene, sets, d_features: torch.Tensor, accumulate: bool) -> None:
+    """d_features (+)= feature-map gradient of every (ws, dx_tiles, nr, S) in ``sets`` in one sweep."""
+    n = len(sets)
+    assert 1 <= n <= 4
+    I32, SZ, VP = ctypes.c_int32 * n, ctypes.c_size_t * n, ctypes.c_void_p * n
+    nr = I32(*[s[2] for s in sets])
+    S = I32(*[s[3] for s in sets])
+    ws = VP(*[s[0].data_ptr() for s in sets])
+    wsb = SZ(*[s[0].numel() for s in sets])
+    dx = VP(*[s[1].data_ptr() for s in sets])
+    assert d_features.is_contiguous() and d_features.dtype == torch.float32
+    call('cn_feature_grad', ctypes.byref(scene.c), n, nr, S, ws, wsb, dx, _ptr(d_features), int(accumulate), _stream())
 
 
 def composite_fwd(z, rgbs):

@@ -34,8 +34,10 @@ def _pass_fwd(packed, scene: ops.Scene, ray_o, ray_d, z, save: bool) -> _Pass:
     return P
 
 
-def _pass_bwd(P: _Pass, params, grad, scene: ops.Scene, ray_o, ray_d, d_rgb, d_depth, d_weights, d_features,
-              need_dz: bool) -> Optional[torch.Tensor]:
+def _pass_bwd(P: _Pass, params, grad, scene: ops.Scene, ray_o, ray_d, d_rgb, d_depth, d_weights, want_dx: bool,
+              need_dz: bool):
+    """backward of one pass up to dX (the gradient of the MLP input rows); the feature-map gradient of both
+    passes is taken from the two dX images in one sweep afterwards (ops.feature_grad)."""
     d_y, dz = ops.composite_bwd(P.z, P.rgbs.view(*P.z.shape, 4), d_rgb, d_depth, d_weights, need_dz)
     g = ops.mlp_readout_bwd(params, d_y, P.acts_u, 7, 6, grad)
     for blk in (5, 4, 3):
@@ -44,10 +46,12 @@ def _pass_bwd(P: _Pass, params, grad, scene: ops.Scene, ray_o, ray_d, d_rgb, d_d
     for blk in (2, 1, 0):
         ops.mlp_block_bwd(P.packed, blk, P.acts_f, 6, 2 * blk, gf, grad)
     ops.mlp_l0_wgrad(P.x, gf, grad)
-    if d_features is not None or need_dz:
+    dx = None
+    if want_dx or need_dz:
         dx = ops.mlp_l0_dgrad(P.packed, gf)
-        ops.project_gather_bwd(scene, ray_o, ray_d, P.z, dx, d_features, dz, P.ws)
-    return dz
+        if need_dz:
+            ops.project_gather_bwd(scene, ray_o, ray_d, P.z, dx, None, dz, P.ws)
+    return dz, dx
 
 
 class _RenderFn(torch.autograd.Function):
@@ -79,7 +83,8 @@ class _RenderFn(torch.autograd.Function):
         need_feat = ctx.needs_input_grad[2]
         g_c = torch.zeros(NET_PARAMS, dtype=torch.float32, device=dev)
         g_f = torch.zeros(NET_PARAMS, dtype=torch.float32, device=dev)
-        d_features = torch.zeros_like(scene.features) if need_feat else None
+        # written exactly once per texel by ops.feature_grad: no zero fill
+        d_features = torch.empty_like(scene.features) if need_feat else None
 
         def z_or_none(t):
             return None if t is None else t.contiguous()
@@ -87,9 +92,14 @@ class _RenderFn(torch.autograd.Function):
         d_rgb_f = torch.zeros_like(Fp.rgb) if d_rgb_f is None else d_rgb_f
         d_rgb_c = torch.zeros_like(C.rgb) if d_rgb_c is None else d_rgb_c
         # fine pass first: its dz feeds the coarse weights through the inverse-CDF sampler
-        dz_f = _pass_bwd(Fp, params_f, g_f, scene, ray_o, ray_d, d_rgb_f, z_or_none(d_depth_f), None, d_features, True)
+        dz_f, dx_f = _pass_bwd(Fp, params_f, g_f, scene, ray_o, ray_d, d_rgb_f, z_or_none(d_depth_f), None, need_feat,
+                               True)
         dw_c = ops.sample_pdf_bwd(C.z, C.weights, ctx.u_pdf, ctx.perm, dz_f)
-        _pass_bwd(C, params_c, g_c, scene, ray_o, ray_d, d_rgb_c, z_or_none(d_depth_c), dw_c, d_features, False)
+        _, dx_c = _pass_bwd(C, params_c, g_c, scene, ray_o, ray_d, d_rgb_c, z_or_none(d_depth_c), dw_c, need_feat, False)
+        if need_feat:
+            nr = C.z.shape[1]
+            ops.feature_grad(scene, [(Fp.ws, dx_f, nr, Fp.z.shape[2]), (C.ws, dx_c, nr, C.z.shape[2])], d_features,
+                             accumulate=False)
         ctx.C = ctx.F = ctx.scene = None
         return (g_c, g_f, d_features) + (None,) * 9
 

@@ -37,7 +37,8 @@ constexpr int kCells = kT * kT;
 constexpr int kChunk = 128;                      // max rows per work item
 
 // header ints of the workspace
-enum { kHdrItems = 0, kHdrCurFwd = 1, kHdrCurZg = 2, kHdrCurSc = 3, kHdrTicket = 4, kHdrInts = 64 };
+enum { kHdrItems = 0, kHdrCurFwd = 1, kHdrCurZg = 2, kHdrCurSc = 3, kHdrHeavyN = 4, kHdrTicket = 5, kHdrInts = 64 };
+constexpr int kHeavyCap = 8192;               // deferred (heavy) texels of the feature-gradient sweep
 
 struct Ws {
   int64_t rows;
@@ -51,6 +52,7 @@ struct Ws {
   int2 *keyrank;   // [rows]     (key, rank inside key)
   int4 *rec_s;     // [rows]     records sorted by key
   float2 *gpix;    // [rows]     feature part of d loss / d (alpha_x, alpha_y)
+  int *heavy;      // [kHeavyCap] texels deferred by feature_grad_kernel
   size_t total;
 };
 
@@ -81,6 +83,7 @@ static Ws ws_layout(int b, int nv, int H, int W, int64_t rows, void *base) {
   w.keyrank = (int2 *)take((size_t)rows * 8);
   w.rec_s = (int4 *)take((size_t)rows * 16);
   w.gpix = (float2 *)take((size_t)rows * 8);
+  w.heavy = (int *)take((size_t)kHeavyCap * 4);
   w.total = o;
   return w;
 }
@@ -109,7 +112,8 @@ __global__ void __launch_bounds__(128)
 project_bin_kernel(CnScene sc, const float *__restrict__ ray_o, const float *__restrict__ ray_d,
                    const float *__restrict__ z, int nr, int S, Ws g, uint8_t *__restrict__ x_tiles) {
   __shared__ __align__(1024) uint8_t sx[2 * CN_SLAB_BYTES];  // slabs 4 and 5 of this X tile
-  __shared__ uint32_t sdpe[128][30];                          // posenc(direction) words per ray of the tile
+  extern __shared__ uint32_t sdpe_dyn[];                      // posenc(direction) words, [rays of the tile][30]
+  uint32_t(*sdpe)[30] = reinterpret_cast<uint32_t(*)[30]>(sdpe_dyn);
   const int tid = threadIdx.x;
   const int lane = tid & 31;
   const int64_t row = (int64_t)blockIdx.x * 128 + tid;
@@ -136,19 +140,20 @@ project_bin_kernel(CnScene sc, const float *__restrict__ ray_o, const float *__r
   }
   if (!x_tiles) return;
 
-  // ---- posenc(direction): once per (ray, view) of the tile, by the ray's first row in the tile
-  const int slot = id.r - id0.r;  // rows of a tile share (b, v); rays are consecutive
-  if (id.i == 0 || tid == 0) {
-    for (int l = 0; l < 30; ++l) {
-      const int c = l / 10, k = l % 10;
-      // direction in the source camera frame with homogeneous w = 1 (quirk Q1)
-      const float dc = dot4_rn(E + 4 * c, rc.d[0], rc.d[1], rc.d[2], 1.f);
-      // libm-accurate sincosf: the values are rounded to bf16 and the parity tests compare ReLU masks
-      // downstream of these operands, so the last fp32 bits matter more often than one would think
-      float s, co;
-      sincosf(__fmul_rn(dc, pe_freq(k)), &s, &co);
-      sdpe[slot][l] = pack_bf16x2(s, co);
-    }
+  // ---- posenc(direction): once per (ray, view) of the tile, its 30 (coordinate, frequency) pairs spread
+  // over the rows the ray has in this tile
+  const int seg0 = max(0, tid - id.i);                 // first thread of this ray's segment
+  const int seg_len = min(128 - seg0, S - (id.i - (tid - seg0)));
+  const int slot = id.r - id0.r;                       // rows of a tile share (b, v); its rays are consecutive
+  for (int l = tid - seg0; l < 30; l += seg_len) {
+    const int c = l / 10, k = l % 10;
+    // direction in the source camera frame with homogeneous w = 1 (quirk Q1)
+    const float dc = dot4_rn(E + 4 * c, rc.d[0], rc.d[1], rc.d[2], 1.f);
+    // libm-accurate sincosf: the values are rounded to bf16 and the parity tests compare ReLU masks
+    // downstream of these operands, so the last fp32 bits matter more often than one would think
+    float s, co;
+    sincosf(__fmul_rn(dc, pe_freq(k)), &s, &co);
+    sdpe[slot][l] = pack_bf16x2(s, co);
   }
   // ---- posenc(position): X columns 256..315 = words 0..29 of slab 4
   uint8_t *my4 = sx + tid * 128;
@@ -324,7 +329,9 @@ __global__ void __launch_bounds__(256) bin_fill_kernel(Ws g) {
 // ------------------------------------------------------------------------------------------
 constexpr int kRowsConsumerWarps = 16;
 constexpr int kRowsThreads = 32 * (1 + kRowsConsumerWarps);
-constexpr uint32_t kRowsSmem = 2 * kTileBytes + 1024;
+constexpr uint32_t kRowsRecBytes = kChunk * 16;                       // records of one work item
+constexpr uint32_t kRowsSlotBytes = kTileBytes + kRowsRecBytes;       // tile + records
+constexpr uint32_t kRowsSmem = 2 * kRowsSlotBytes + 1024;
 
 struct TileDesc {
   int start, count;
@@ -345,6 +352,26 @@ __device__ __forceinline__ TileGeo tile_geo(int bin, int tiles_x, int tiles_y, i
   t.nx = min(kTT, W - t.x0);
   t.ny = min(kTT, H - t.y0);
   return t;
+}
+
+struct Corners {
+  float4 tl0, tl1, tr0, tr1, bl0, bl1, br0, br1;
+};
+// channels 4l..4l+3 and 128+4l..128+4l+3 of the four corners (conflict-free 512-byte reads)
+__device__ __forceinline__ Corners load_corners(const float *tile, int loc, uint32_t l) {
+  const int lx = loc & 0xff, ly = (loc >> 8) & 0xff;
+  const float *t00 = tile + (ly * kTT + lx) * CN_FEAT_C;
+  const float *t10 = t00 + kTT * CN_FEAT_C;
+  Corners c;
+  c.tl0 = *reinterpret_cast<const float4 *>(t00 + 4 * l);
+  c.tl1 = *reinterpret_cast<const float4 *>(t00 + 128 + 4 * l);
+  c.tr0 = *reinterpret_cast<const float4 *>(t00 + CN_FEAT_C + 4 * l);
+  c.tr1 = *reinterpret_cast<const float4 *>(t00 + CN_FEAT_C + 128 + 4 * l);
+  c.bl0 = *reinterpret_cast<const float4 *>(t10 + 4 * l);
+  c.bl1 = *reinterpret_cast<const float4 *>(t10 + 128 + 4 * l);
+  c.br0 = *reinterpret_cast<const float4 *>(t10 + CN_FEAT_C + 4 * l);
+  c.br1 = *reinterpret_cast<const float4 *>(t10 + CN_FEAT_C + 128 + 4 * l);
+  return c;
 }
 
 template <bool kBackward>
@@ -368,7 +395,7 @@ tile_rows_kernel(CnScene sc, Ws g, int *__restrict__ cursor, uint8_t *__restrict
   const int n_items = g.hdr[kHdrItems];
 
   if (warp == 0) {
-    // =========================== producer: tiles of the feature map ===========================
+    // ============ producer: 9x9-texel tile of the feature map + the item's row records ============
     if (l == 0) {
       for (uint32_t k = 0;; ++k) {
         const uint32_t slot = k & 1u;
@@ -384,12 +411,13 @@ tile_rows_kernel(CnScene sc, Ws g, int *__restrict__ cursor, uint8_t *__restrict
         sdesc[slot].start = item.y;
         sdesc[slot].count = item.z;
         const uint32_t row_bytes = (uint32_t)t.nx * kTexBytes;
-        mbar_expect_tx(smem_u32(&bar_full[slot]), row_bytes * (uint32_t)t.ny);
+        const uint32_t bar = smem_u32(&bar_full[slot]);
+        mbar_expect_tx(bar, row_bytes * (uint32_t)t.ny + (uint32_t)item.z * 16u);
         const float *src = sc.features + (((int64_t)t.bv * sc.H + t.y0) * sc.W + t.x0) * CN_FEAT_C;
-        const uint32_t dst = smem_u32(smem) + slot * kTileBytes;
+        const uint32_t dst = smem_u32(smem) + slot * kRowsSlotBytes;
+        bulk_g2s(dst + kTileBytes, g.rec_s + item.y, (uint32_t)item.z * 16u, bar);
         for (int yy = 0; yy < t.ny; ++yy)
-          bulk_g2s(dst + yy * (kTT * kTexBytes), src + (int64_t)yy * sc.W * CN_FEAT_C, row_bytes,
-                   smem_u32(&bar_full[slot]));
+          bulk_g2s(dst + yy * (kTT * kTexBytes), src + (int64_t)yy * sc.W * CN_FEAT_C, row_bytes, bar);
       }
     }
   } else {
@@ -398,67 +426,61 @@ tile_rows_kernel(CnScene sc, Ws g, int *__restrict__ cursor, uint8_t *__restrict
     for (uint32_t k = 0;; ++k) {
       const uint32_t slot = k & 1u;
       mbar_wait(smem_u32(&bar_full[slot]), (k >> 1) & 1u);
-      const int start = sdesc[slot].start, count = sdesc[slot].count;
+      const int count = sdesc[slot].count;
       if (count == 0) break;
-      const float *tile = reinterpret_cast<const float *>(smem + slot * kTileBytes);
-      int4 rec = make_int4(0, 0, 0, 0);
-      uint2 ga = make_uint2(0, 0), gb = make_uint2(0, 0);
-      auto fetch = [&](int j) {
-        rec = __ldg(g.rec_s + start + j);
-        if (kBackward) {
-          const uint8_t *t = x_tiles + (int64_t)(rec.x >> 7) * CN_X_TILE_BYTES;
-          const uint32_t rr = (uint32_t)rec.x & 127u;
-          ga = __ldg(reinterpret_cast<const uint2 *>(t + tile_chunk_off(rr, l >> 1) + (l & 1) * 8));
-          gb = __ldg(reinterpret_cast<const uint2 *>(t + tile_chunk_off(rr, 16 + (l >> 1)) + (l & 1) * 8));
-        }
-      };
-      if ((int)cw < count) fetch(cw);
-      for (int j = cw; j < count; j += kRowsConsumerWarps) {
-        const int4 cur = rec;
-        const uint2 ca = ga, cb = gb;
-        if (j + kRowsConsumerWarps < count) fetch(j + kRowsConsumerWarps);
-        const int row = cur.x;
-        const int lx = cur.y & 0xff, ly = (cur.y >> 8) & 0xff;
-        const float ax = __int_as_float(cur.z), ay = __int_as_float(cur.w);
-        const float *t00 = tile + (ly * kTT + lx) * CN_FEAT_C;
-        const float *t10 = t00 + kTT * CN_FEAT_C;
-        // channels 4l..4l+3 and 128+4l..128+4l+3 of the four corners (conflict-free 512-byte reads)
-        const float4 tl0 = *reinterpret_cast<const float4 *>(t00 + 4 * l);
-        const float4 tl1 = *reinterpret_cast<const float4 *>(t00 + 128 + 4 * l);
-        const float4 tr0 = *reinterpret_cast<const float4 *>(t00 + CN_FEAT_C + 4 * l);
-        const float4 tr1 = *reinterpret_cast<const float4 *>(t00 + CN_FEAT_C + 128 + 4 * l);
-        const float4 bl0 = *reinterpret_cast<const float4 *>(t10 + 4 * l);
-        const float4 bl1 = *reinterpret_cast<const float4 *>(t10 + 128 + 4 * l);
-        const float4 br0 = *reinterpret_cast<const float4 *>(t10 + CN_FEAT_C + 4 * l);
-        const float4 br1 = *reinterpret_cast<const float4 *>(t10 + CN_FEAT_C + 128 + 4 * l);
-        if (!kBackward) {
-          uint8_t *xt = x_tiles + (int64_t)(row >> 7) * CN_X_TILE_BYTES;
-          const uint32_t rr = (uint32_t)row & 127u;
-          const float4 g0 = lerp2_f4(tl0, tr0, bl0, br0, ax, ay);
-          const float4 g1 = lerp2_f4(tl1, tr1, bl1, br1, ax, ay);
+      const float *tile = reinterpret_cast<const float *>(smem + slot * kRowsSlotBytes);
+      const int4 *recs = reinterpret_cast<const int4 *>(smem + slot * kRowsSlotBytes + kTileBytes);
+      if (!kBackward) {
+        for (int j = cw; j < count; j += kRowsConsumerWarps) {
+          const int4 cur = recs[j];
+          const float ax = __int_as_float(cur.z), ay = __int_as_float(cur.w);
+          const Corners c = load_corners(tile, cur.y, l);
+          uint8_t *xt = x_tiles + (int64_t)(cur.x >> 7) * CN_X_TILE_BYTES;
+          const uint32_t rr = (uint32_t)cur.x & 127u;
+          const float4 g0 = lerp2_f4(c.tl0, c.tr0, c.bl0, c.br0, ax, ay);
+          const float4 g1 = lerp2_f4(c.tl1, c.tr1, c.bl1, c.br1, ax, ay);
           // channels 4l..4l+3 -> half of chunk l/2; channels 128+4l.. -> half of chunk 16 + l/2
           *reinterpret_cast<uint2 *>(xt + tile_chunk_off(rr, l >> 1) + (l & 1) * 8) =
               make_uint2(pack_bf16x2(g0.x, g0.y), pack_bf16x2(g0.z, g0.w));
           *reinterpret_cast<uint2 *>(xt + tile_chunk_off(rr, 16 + (l >> 1)) + (l & 1) * 8) =
               make_uint2(pack_bf16x2(g1.x, g1.y), pack_bf16x2(g1.z, g1.w));
-        } else {
-          // d out / d ax = (1-ay)(TR-TL) + ay(BR-BL);  d out / d ay = (1-ax)(BL-TL) + ax(BR-TR)
-          const float g0[4] = {bf16_lo(ca.x), bf16_hi(ca.x), bf16_lo(ca.y), bf16_hi(ca.y)};
-          const float g1[4] = {bf16_lo(cb.x), bf16_hi(cb.x), bf16_lo(cb.y), bf16_hi(cb.y)};
-          const float tlv[8] = {tl0.x, tl0.y, tl0.z, tl0.w, tl1.x, tl1.y, tl1.z, tl1.w};
-          const float trv[8] = {tr0.x, tr0.y, tr0.z, tr0.w, tr1.x, tr1.y, tr1.z, tr1.w};
-          const float blv[8] = {bl0.x, bl0.y, bl0.z, bl0.w, bl1.x, bl1.y, bl1.z, bl1.w};
-          const float brv[8] = {br0.x, br0.y, br0.z, br0.w, br1.x, br1.y, br1.z, br1.w};
-          float gax = 0.f, gay = 0.f;
+        }
+      } else {
+        // batches of 4 rows per warp: all dX loads of the batch are in flight before the first use
+        for (int j0 = cw; j0 < count; j0 += 4 * kRowsConsumerWarps) {
+          int4 rec[4];
+          uint2 ga[4], gb[4];
 #pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            const float gc = c < 4 ? g0[c] : g1[c - 4];
-            gax += gc * ((1.f - ay) * (trv[c] - tlv[c]) + ay * (brv[c] - blv[c]));
-            gay += gc * ((1.f - ax) * (blv[c] - tlv[c]) + ax * (brv[c] - trv[c]));
+          for (int u = 0; u < 4; ++u) {
+            const int j = j0 + u * kRowsConsumerWarps;
+            rec[u] = recs[min(j, count - 1)];
+            const uint8_t *t = x_tiles + (int64_t)(rec[u].x >> 7) * CN_X_TILE_BYTES;
+            const uint32_t rr = (uint32_t)rec[u].x & 127u;
+            ga[u] = __ldg(reinterpret_cast<const uint2 *>(t + tile_chunk_off(rr, l >> 1) + (l & 1) * 8));
+            gb[u] = __ldg(reinterpret_cast<const uint2 *>(t + tile_chunk_off(rr, 16 + (l >> 1)) + (l & 1) * 8));
           }
-          gax = warp_sum_f(gax);
-          gay = warp_sum_f(gay);
-          if (l == 0) g.gpix[row] = make_float2(gax, gay);
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            if (j0 + u * kRowsConsumerWarps >= count) break;
+            const float ax = __int_as_float(rec[u].z), ay = __int_as_float(rec[u].w);
+            const Corners c = load_corners(tile, rec[u].y, l);
+            // d out / d ax = (1-ay)(TR-TL) + ay(BR-BL);  d out / d ay = (1-ax)(BL-TL) + ax(BR-TR)
+            const float gv[8] = {bf16_lo(ga[u].x), bf16_hi(ga[u].x), bf16_lo(ga[u].y), bf16_hi(ga[u].y),
+                                 bf16_lo(gb[u].x), bf16_hi(gb[u].x), bf16_lo(gb[u].y), bf16_hi(gb[u].y)};
+            const float tlv[8] = {c.tl0.x, c.tl0.y, c.tl0.z, c.tl0.w, c.tl1.x, c.tl1.y, c.tl1.z, c.tl1.w};
+            const float trv[8] = {c.tr0.x, c.tr0.y, c.tr0.z, c.tr0.w, c.tr1.x, c.tr1.y, c.tr1.z, c.tr1.w};
+            const float blv[8] = {c.bl0.x, c.bl0.y, c.bl0.z, c.bl0.w, c.bl1.x, c.bl1.y, c.bl1.z, c.bl1.w};
+            const float brv[8] = {c.br0.x, c.br0.y, c.br0.z, c.br0.w, c.br1.x, c.br1.y, c.br1.z, c.br1.w};
+            float gax = 0.f, gay = 0.f;
+#pragma unroll
+            for (int ch = 0; ch < 8; ++ch) {
+              gax += gv[ch] * ((1.f - ay) * (trv[ch] - tlv[ch]) + ay * (brv[ch] - blv[ch]));
+              gay += gv[ch] * ((1.f - ax) * (blv[ch] - tlv[ch]) + ax * (brv[ch] - trv[ch]));
+            }
+            gax = warp_sum_f(gax);
+            gay = warp_sum_f(gay);
+            if (l == 0) g.gpix[rec[u].x] = make_float2(gax, gay);
+          }
         }
       }
       __syncwarp();
@@ -468,143 +490,200 @@ tile_rows_kernel(CnScene sc, Ws g, int *__restrict__ cursor, uint8_t *__restrict
 }
 
 // ------------------------------------------------------------------------------------------
-// feature-map gradient: pull-accumulate per texel, bulk reduce-add per tile row
+// feature-map gradient: every texel PULLS the rows of its (up to) four neighbouring cells
 // ------------------------------------------------------------------------------------------
-constexpr int kScatterWarps = 8;
-constexpr int kScatterThreads = 32 * kScatterWarps;
-constexpr uint32_t kScatterSmem = kTileBytes + 1024;
+// The sorted order makes the rows of one (view, cell) a contiguous range [key_off[k], key_off[k+1]),
+// so d_features[texel] = sum over the 4 cells whose 2x2 footprint contains the texel of
+// weight(row, corner) * dX[row] is a segmented sum with no write conflicts: one warp owns a texel,
+// accumulates its 256 channels in registers (lane l: channels 4l..4l+3 and 128+4l..128+4l+3) and
+// writes the 1 KiB result once with plain coalesced stores -- no atomics, no zero-filled map, no
+// read-modify-write traffic.  Several row sets (coarse + fine pass) are summed in the same sweep.
+// Texels with more than kHeavyRows rows (border texels that collect every clamped out-of-frustum
+// sample) are deferred to a second kernel in which a whole CTA splits the rows.
+constexpr int kMaxSets = 4;
+constexpr int kFgWarps = 16;
+constexpr int kFgThreads = 32 * kFgWarps;
+constexpr int kHeavyRows = 192;
+constexpr int kUnitRows = 2;  // a work unit = kUnitRows x 8 texels of one 8x8 texel tile
 
-struct SRec {
-  uint32_t base128;  // (row >> 7) * 768 + (row & 127): start of the row inside the dX image, in 128-byte units
-  uint32_t cell_sw;  // cell | (row & 7) << 8
-  float ax, ay;
+struct GradSet {
+  const int *key_off;    // [n_keys] start of every key in rec_s
+  const int4 *rec_s;     // sorted records
+  const uint8_t *dx;     // dX tile images of this pass
+  int rows;
+};
+struct GradArgs {
+  GradSet set[kMaxSets];
+  int n_sets;
+  int n_keys, tiles_x, tiles_y;  // cell tiling of the records (same scene for every set)
+  int ttx, tty;                  // texel tiling: ceil(W/8), ceil(H/8)
+  int n_units;
+  int accumulate;
+  int *cursor;      // work-unit cursor
+  int *heavy_n;     // number of deferred texels
+  int *heavy_list;  // [heavy_cap] texel index (bv*H + Y)*W + X
+  int heavy_cap;
 };
 
-__device__ __forceinline__ SRec make_srec(int4 r) {
-  SRec s;
-  const uint32_t row = (uint32_t)r.x;
-  s.base128 = (row >> 7) * (CN_X_TILE_BYTES / 128) + (row & 127u);
-  const uint32_t lx = (uint32_t)r.y & 0xffu, ly = ((uint32_t)r.y >> 8) & 0xffu;
-  s.cell_sw = (ly * kT + lx) | ((row & 7u) << 8);
-  s.ax = __int_as_float(r.z);
-  s.ay = __int_as_float(r.w);
-  return s;
+// (range start, length) of the rows of pair p = set*4 + corner for texel (bv, Y, X); corner = dy*2 + dx
+__device__ __forceinline__ void texel_pair_range(const CnScene &sc, const GradArgs &a, int p, int bv, int Y, int X,
+                                                 int &st, int &len) {
+  st = 0;
+  len = 0;
+  if (p >= a.n_sets * 4) return;
+  const int fy = Y - ((p >> 1) & 1), fx = X - (p & 1);
+  if (fy < 0 || fy > sc.H - 2 || fx < 0 || fx > sc.W - 2) return;
+  const int key = ((bv * a.tiles_y + fy / kT) * a.tiles_x + fx / kT) * kCells + (fy % kT) * kT + (fx % kT);
+  const GradSet &gs = a.set[p >> 2];
+  st = __ldg(gs.key_off + key);
+  const int en = key + 1 < a.n_keys ? __ldg(gs.key_off + key + 1) : gs.rows;
+  len = en - st;
 }
 
-__global__ void __launch_bounds__(kScatterThreads, 2)
-tile_scatter_kernel(CnScene sc, Ws g, int *__restrict__ cursor, const uint8_t *__restrict__ dx_tiles,
-                    float *__restrict__ d_features) {
-  extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(16) SRec srec[2][kChunk];
-  __shared__ int cstart[kCells + 1];
-  __shared__ int s_claim[2];
-  uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  float *out = reinterpret_cast<float *>(smem);
-  const int tid = threadIdx.x;
-  const uint32_t warp = tid >> 5, l = lane_id();
-  const int n_items = g.hdr[kHdrItems];
-
-  if (tid == 0) {
-    s_claim[0] = atomicAdd(cursor, 1);
-    s_claim[1] = atomicAdd(cursor, 1);
-  }
-  __syncthreads();
-  int cur = s_claim[0], nxt = s_claim[1];
-  __syncthreads();
-  int4 item = make_int4(0, 0, 0, 0);
-  if (cur < n_items) {
-    item = g.items[cur];
-    if (tid < item.z) srec[0][tid] = make_srec(__ldg(g.rec_s + item.y + tid));
-  }
-  __syncthreads();
-  bool flush_pending = false;
-  // lane l owns bf16 chunk l of a dX row = channels 8l..8l+7: slab l/8, 16-byte chunk (l%8) ^ (row%8)
-  const uint32_t lane_slab_off = (l >> 3) * CN_SLAB_BYTES;
-
-  for (uint32_t k = 0; cur < n_items; ++k) {
-    const uint32_t buf = k & 1u;
-    // ---- prefetch the next item's records, claim the one after
-    int4 item_n = make_int4(0, 0, 0, 0), rec_n = make_int4(0, 0, 0, 0);
-    int claim = 0;
-    if (nxt < n_items) {
-      item_n = g.items[nxt];
-      if (tid < item_n.z) rec_n = __ldg(g.rec_s + item_n.y + tid);
+// acc += sum over flat row indices f in [f0, f1) (step `stride` batches of 32) of this texel's pairs
+__device__ __forceinline__ void texel_accumulate(const GradArgs &a, int st, int len, int off_incl, int n, int batch0,
+                                                 int batch_stride, float (&acc)[8]) {
+  const uint32_t l = lane_id();
+  const int n_pairs = a.n_sets * 4;
+  // lane constant part of the dX address: channels 4l..4l+3 live in chunk l/2 (half l%2) of slabs 0..1,
+  // channels 128+4l.. in the same position two slabs further
+  const uint32_t lane_off = ((l >> 4) * CN_SLAB_BYTES) + (((l >> 1) & 7u) << 4) + (l & 1u) * 8u;
+  for (int b0 = batch0 * 32; b0 < n; b0 += batch_stride * 32) {
+    // ---- lane f: record of flat row b0 + f
+    const int f = b0 + (int)l;
+    int my_p = 0;
+    for (int p = 0; p < n_pairs; ++p) my_p += (f >= __shfl_sync(0xffffffffu, off_incl, p)) ? 1 : 0;
+    my_p = min(my_p, n_pairs - 1);
+    const int p_st = __shfl_sync(0xffffffffu, st, my_p);
+    const int p_off = __shfl_sync(0xffffffffu, off_incl - len, my_p);
+    float w = 0.f;
+    uint64_t addr = 0;
+    if (f < n) {
+      const GradSet &gs = a.set[my_p >> 2];
+      const int4 r = __ldg(gs.rec_s + p_st + (f - p_off));
+      const float ax = __int_as_float(r.z), ay = __int_as_float(r.w);
+      w = ((my_p & 1) ? ax : 1.f - ax) * ((my_p & 2) ? ay : 1.f - ay);
+      const uint32_t row = (uint32_t)r.x;
+      addr = (uint64_t)(uintptr_t)gs.dx + ((uint64_t)(row >> 7) * CN_X_TILE_BYTES + (row & 127u) * 128u) + (row & 7u);
     }
-    if (tid == 0) claim = atomicAdd(cursor, 1);
-    // ---- first row of every cell (rows of an item are sorted by cell)
-    const int count = item.z;
-    if (tid < count) {
-      const int c = (int)(srec[buf][tid].cell_sw & 0xffu);
-      const int cp = tid > 0 ? (int)(srec[buf][tid - 1].cell_sw & 0xffu) : -1;
-      for (int q = cp + 1; q <= c; ++q) cstart[q] = tid;
-      if (tid == count - 1)
-        for (int q = c + 1; q <= kCells; ++q) cstart[q] = count;
-    }
-    if (flush_pending && tid == 0) bulk_wait_read0();  // the previous tile has left shared memory
-    __syncthreads();
-
-    const TileGeo t = tile_geo(item.x, g.tiles_x, g.tiles_y, sc.H, sc.W);
-    for (int tex = warp; tex < kTT * kTT; tex += kScatterWarps) {
-      const int y = tex / kTT, x = tex - y * kTT;
-      if (y >= t.ny || x >= t.nx) continue;
-      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    const int nb = min(32, n - b0);
+    const uint32_t a_lo = (uint32_t)addr, a_hi = (uint32_t)(addr >> 32);
+    for (int u0 = 0; u0 < nb; u0 += 4) {
+      uint2 va[4], vb[4];
+      float wu[4];
 #pragma unroll
-      for (int corner = 0; corner < 4; ++corner) {
-        const int dy = corner >> 1, dx = corner & 1;
-        const int cy = y - dy, cx = x - dx;
-        if (cy < 0 || cy >= kT || cx < 0 || cx >= kT) continue;
-        const int c = cy * kT + cx;
-        const int j1 = cstart[c + 1];
-        for (int j = cstart[c]; j < j1; j += 4) {
-          // four independent 16-byte loads in flight per lane before the FMAs
-          uint4 v[4];
-          float w[4];
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            if (j + u < j1) {
-              const SRec r = srec[buf][j + u];
-              const float wx = dx ? r.ax : 1.f - r.ax;
-              const float wy = dy ? r.ay : 1.f - r.ay;
-              w[u] = wx * wy;
-              const uint8_t *p =
-                  dx_tiles + (int64_t)r.base128 * 128 + lane_slab_off + (((l & 7u) ^ (r.cell_sw >> 8)) << 4);
-              v[u] = __ldg(reinterpret_cast<const uint4 *>(p));
-            } else {
-              w[u] = 0.f;
-              v[u] = make_uint4(0u, 0u, 0u, 0u);
-            }
-          }
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            acc[0] = fmaf(w[u], bf16_lo(v[u].x), acc[0]); acc[1] = fmaf(w[u], bf16_hi(v[u].x), acc[1]);
-            acc[2] = fmaf(w[u], bf16_lo(v[u].y), acc[2]); acc[3] = fmaf(w[u], bf16_hi(v[u].y), acc[3]);
-            acc[4] = fmaf(w[u], bf16_lo(v[u].z), acc[4]); acc[5] = fmaf(w[u], bf16_hi(v[u].z), acc[5]);
-            acc[6] = fmaf(w[u], bf16_lo(v[u].w), acc[6]); acc[7] = fmaf(w[u], bf16_hi(v[u].w), acc[7]);
-          }
-        }
+      for (int u = 0; u < 4; ++u) {
+        const int src = min(u0 + u, nb - 1);
+        wu[u] = (u0 + u < nb) ? __shfl_sync(0xffffffffu, w, src) : 0.f;
+        const uint32_t lo = __shfl_sync(0xffffffffu, a_lo, src), hi = __shfl_sync(0xffffffffu, a_hi, src);
+        const uint64_t base = ((uint64_t)hi << 32) | (lo & ~127u);
+        const uint8_t *p = reinterpret_cast<const uint8_t *>(base + (lane_off ^ ((lo & 7u) << 4)));
+        va[u] = __ldg(reinterpret_cast<const uint2 *>(p));
+        vb[u] = __ldg(reinterpret_cast<const uint2 *>(p + 2 * CN_SLAB_BYTES));
       }
-      float4 *o = reinterpret_cast<float4 *>(out + tex * CN_FEAT_C + 8 * l);
-      o[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-      o[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        acc[0] = fmaf(wu[u], bf16_lo(va[u].x), acc[0]); acc[1] = fmaf(wu[u], bf16_hi(va[u].x), acc[1]);
+        acc[2] = fmaf(wu[u], bf16_lo(va[u].y), acc[2]); acc[3] = fmaf(wu[u], bf16_hi(va[u].y), acc[3]);
+        acc[4] = fmaf(wu[u], bf16_lo(vb[u].x), acc[4]); acc[5] = fmaf(wu[u], bf16_hi(vb[u].x), acc[5]);
+        acc[6] = fmaf(wu[u], bf16_lo(vb[u].y), acc[6]); acc[7] = fmaf(wu[u], bf16_hi(vb[u].y), acc[7]);
+      }
     }
-    fence_proxy_async_smem();
-    __syncthreads();
-    if (tid == 0) {
-      float *dst = d_features + (((int64_t)t.bv * sc.H + t.y0) * sc.W + t.x0) * CN_FEAT_C;
-      for (int yy = 0; yy < t.ny; ++yy)
-        bulk_reduce_add_f32(dst + (int64_t)yy * sc.W * CN_FEAT_C, smem_u32(out) + yy * (kTT * kTexBytes),
-                            (uint32_t)t.nx * kTexBytes);
-      bulk_commit();
-      s_claim[0] = claim;
-    }
-    flush_pending = true;
-    if (nxt < n_items && tid < item_n.z) srec[buf ^ 1u][tid] = make_srec(rec_n);
-    __syncthreads();
-    cur = nxt;
-    nxt = s_claim[0];
-    item = item_n;
   }
-  if (flush_pending && tid == 0) bulk_wait0();
+}
+
+// inclusive scan of `len` over the first 16 lanes
+__device__ __forceinline__ int pair_scan(int len, int &total) {
+  const uint32_t l = lane_id();
+  int inc = len;
+#pragma unroll
+  for (int o = 1; o < 16; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (l >= (uint32_t)o) inc += v;
+  }
+  total = __shfl_sync(0xffffffffu, inc, 15);
+  return inc;
+}
+
+__device__ __forceinline__ void texel_store(float *__restrict__ d_features, int64_t texel, const float (&acc)[8],
+                                            int accumulate) {
+  const uint32_t l = lane_id();
+  float4 *o = reinterpret_cast<float4 *>(d_features + texel * CN_FEAT_C);
+  float4 r0 = make_float4(acc[0], acc[1], acc[2], acc[3]), r1 = make_float4(acc[4], acc[5], acc[6], acc[7]);
+  if (accumulate) {
+    const float4 p0 = o[l], p1 = o[32 + l];
+    r0.x += p0.x; r0.y += p0.y; r0.z += p0.z; r0.w += p0.w;
+    r1.x += p1.x; r1.y += p1.y; r1.z += p1.z; r1.w += p1.w;
+  }
+  o[l] = r0;
+  o[32 + l] = r1;
+}
+
+__global__ void __launch_bounds__(kFgThreads, 2)
+feature_grad_kernel(CnScene sc, GradArgs a, float *__restrict__ d_features) {
+  const uint32_t l = lane_id();
+  for (;;) {
+    int unit = 0;
+    if (l == 0) unit = atomicAdd(a.cursor, 1);
+    unit = __shfl_sync(0xffffffffu, unit, 0);
+    if (unit >= a.n_units) break;
+    const int q = unit % (kT / kUnitRows);
+    const int tile = unit / (kT / kUnitRows);
+    const int tx = tile % a.ttx;
+    const int ty = (tile / a.ttx) % a.tty;
+    const int bv = tile / (a.ttx * a.tty);
+    for (int t = 0; t < kUnitRows * kT; ++t) {
+      const int Y = ty * kT + q * kUnitRows + t / kT, X = tx * kT + t % kT;
+      if (Y >= sc.H || X >= sc.W) continue;
+      int st, len, n;
+      texel_pair_range(sc, a, (int)l, bv, Y, X, st, len);
+      const int off_incl = pair_scan(len, n);
+      const int64_t texel = ((int64_t)bv * sc.H + Y) * sc.W + X;
+      if (n > kHeavyRows) {
+        int slot = 0;
+        if (l == 0) slot = atomicAdd(a.heavy_n, 1);
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (slot < a.heavy_cap) {
+          if (l == 0) a.heavy_list[slot] = (int)texel;
+          continue;
+        }
+        // list full: fall through and do it here
+      }
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      texel_accumulate(a, st, len, off_incl, n, 0, 1, acc);
+      texel_store(d_features, texel, acc, a.accumulate);
+    }
+  }
+}
+
+// deferred texels: one CTA per texel, warps take batches of 32 rows round-robin, partial sums meet in smem
+__global__ void __launch_bounds__(kFgThreads, 1)
+feature_grad_heavy_kernel(CnScene sc, GradArgs a, float *__restrict__ d_features) {
+  __shared__ float part[kFgWarps][CN_FEAT_C];
+  const uint32_t l = lane_id(), warp = threadIdx.x >> 5;
+  const int n_heavy = min(*a.heavy_n, a.heavy_cap);
+  for (int h = blockIdx.x; h < n_heavy; h += gridDim.x) {
+    const int64_t texel = a.heavy_list[h];
+    const int X = (int)(texel % sc.W);
+    const int Y = (int)((texel / sc.W) % sc.H);
+    const int bv = (int)(texel / ((int64_t)sc.W * sc.H));
+    int st, len, n;
+    texel_pair_range(sc, a, (int)l, bv, Y, X, st, len);
+    const int off_incl = pair_scan(len, n);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    texel_accumulate(a, st, len, off_incl, n, (int)warp, kFgWarps, acc);
+    *reinterpret_cast<float4 *>(&part[warp][4 * l]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    *reinterpret_cast<float4 *>(&part[warp][128 + 4 * l]) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+    __syncthreads();
+    if (threadIdx.x < CN_FEAT_C) {
+      float s = 0.f;
+#pragma unroll
+      for (int w = 0; w < kFgWarps; ++w) s += part[w][threadIdx.x];
+      float *o = d_features + texel * CN_FEAT_C + threadIdx.x;
+      *o = a.accumulate ? *o + s : s;
+    }
+    __syncthreads();
+  }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -715,7 +794,9 @@ static int run_bin(const CnScene *scene, const float *ray_o, const float *ray_d,
     set_error("cn_project_bin: cudaMemsetAsync: %s", cudaGetErrorString(e));
     return (int)e;
   }
-  project_bin_kernel<<<(unsigned)(g.rows / 128), 128, 0, st>>>(*scene, ray_o, ray_d, z, nr, S, g, x_tiles);
+  const int n_slots = 127 / S + 2;  // rays that can have rows in one 128-row tile
+  project_bin_kernel<<<(unsigned)(g.rows / 128), 128, (size_t)n_slots * 30 * 4, st>>>(*scene, ray_o, ray_d, z, nr, S, g,
+                                                                                   x_tiles);
   bin_scan1_kernel<<<g.n_blk, 256, 0, st>>>(g);
   bin_scan2_kernel<<<g.n_blk, 256, 0, st>>>(g);
   bin_fill_kernel<<<(unsigned)((g.rows + 255) / 256), 256, 0, st>>>(g);
@@ -732,6 +813,40 @@ static int run_tile_rows(const CnScene *scene, const Ws &g, int cursor_index, ui
   }
   tile_rows_kernel<kBackward><<<kNumSMs, kRowsThreads, kRowsSmem, st>>>(*scene, g, g.hdr + cursor_index, x_tiles);
   return check_launch("tile_rows");
+}
+
+
+static int run_feature_grad(const CnScene *scene, int n_sets, const Ws *const *ws, const void *const *dx,
+                            float *d_features, int accumulate, cudaStream_t st) {
+  GradArgs a;
+  a.n_sets = n_sets;
+  for (int i = 0; i < kMaxSets; ++i) {
+    const Ws *w = ws[i < n_sets ? i : 0];
+    a.set[i].key_off = w->count;
+    a.set[i].rec_s = w->rec_s;
+    a.set[i].dx = (const uint8_t *)dx[i < n_sets ? i : 0];
+    a.set[i].rows = (int)w->rows;
+  }
+  const Ws *w0 = ws[0];
+  a.n_keys = w0->n_keys;
+  a.tiles_x = w0->tiles_x;
+  a.tiles_y = w0->tiles_y;
+  a.ttx = (scene->W + kT - 1) / kT;
+  a.tty = (scene->H + kT - 1) / kT;
+  a.n_units = scene->b * scene->nv * a.ttx * a.tty * (kT / kUnitRows);
+  a.accumulate = accumulate;
+  a.cursor = w0->hdr + kHdrCurSc;
+  a.heavy_n = w0->hdr + kHdrHeavyN;
+  a.heavy_list = w0->heavy;
+  a.heavy_cap = kHeavyCap;
+  cudaError_t ce = cudaMemsetAsync(w0->hdr + kHdrCurSc, 0, 2 * sizeof(int), st);  // cursor + heavy count
+  if (ce != cudaSuccess) {
+    set_error("cn_feature_grad: cudaMemsetAsync: %s", cudaGetErrorString(ce));
+    return (int)ce;
+  }
+  feature_grad_kernel<<<2 * kNumSMs, kFgThreads, 0, st>>>(*scene, a, d_features);
+  feature_grad_heavy_kernel<<<kNumSMs, kFgThreads, 0, st>>>(*scene, a, d_features);
+  return check_launch("cn_feature_grad");
 }
 
 }  // namespace cn
@@ -775,7 +890,7 @@ extern "C" int cn_project_gather_bwd(const CnScene *scene, const float *ray_o, c
   if (int e = get_ws(scene, nr, S, ws, ws_bytes, "cn_project_gather_bwd", &g)) return e;
   if (!d_features && !dz) return 0;
   cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t ce = cudaMemsetAsync(g.hdr + kHdrCurZg, 0, 2 * sizeof(int), st);  // both backward cursors
+  cudaError_t ce = cudaMemsetAsync(g.hdr + kHdrCurZg, 0, sizeof(int), st);
   if (ce != cudaSuccess) {
     set_error("cn_project_gather_bwd: cudaMemsetAsync: %s", cudaGetErrorString(ce));
     return (int)ce;
@@ -787,14 +902,28 @@ extern "C" int cn_project_gather_bwd(const CnScene *scene, const float *ray_o, c
     if (int e = check_launch("cn_project_gather_bwd (dz)")) return e;
   }
   if (d_features) {
-    ce = cudaFuncSetAttribute(tile_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem);
-    if (ce != cudaSuccess) {
-      set_error("cn_project_gather_bwd: cudaFuncSetAttribute: %s", cudaGetErrorString(ce));
-      return (int)ce;
-    }
-    tile_scatter_kernel<<<2 * kNumSMs, kScatterThreads, kScatterSmem, st>>>(*scene, g, g.hdr + kHdrCurSc,
-                                                                            (const uint8_t *)dx_tiles, d_features);
-    if (int e = check_launch("cn_project_gather_bwd (scatter)")) return e;
+    const Ws *gp = &g;
+    const void *dxp = dx_tiles;
+    if (int e = run_feature_grad(scene, 1, &gp, &dxp, d_features, 1, st)) return e;
   }
   return 0;
+}
+
+extern "C" int cn_feature_grad(const CnScene *scene, int32_t n_sets, const int32_t *nr, const int32_t *S,
+                               void *const *ws, const size_t *ws_bytes, const void *const *dx_tiles,
+                               float *d_features, int32_t accumulate, void *stream) {
+  using namespace cn;
+  if (int e = check_scene(scene, "cn_feature_grad")) return e;
+  CN_REQUIRE(n_sets >= 1 && n_sets <= kMaxSets, "cn_feature_grad: n_sets must be 1..%d (got %d)", kMaxSets, n_sets);
+  CN_REQUIRE(nr && S && ws && ws_bytes && dx_tiles && d_features, "cn_feature_grad: null pointer");
+  CN_REQUIRE(((uintptr_t)d_features & 15) == 0, "cn_feature_grad: d_features alignment");
+  CN_REQUIRE((int64_t)scene->b * scene->nv * scene->H * scene->W < ((int64_t)1 << 31), "cn_feature_grad: map too large");
+  Ws g[kMaxSets];
+  const Ws *gp[kMaxSets];
+  for (int i = 0; i < n_sets; ++i) {
+    CN_REQUIRE(dx_tiles[i] && ((uintptr_t)dx_tiles[i] & 127) == 0, "cn_feature_grad: dx_tiles[%d] null or misaligned", i);
+    if (int e = get_ws(scene, nr[i], S[i], ws[i], ws_bytes[i], "cn_feature_grad", &g[i])) return e;
+    gp[i] = &g[i];
+  }
+  return run_feature_grad(scene, n_sets, gp, dx_tiles, d_features, accumulate, (cudaStream_t)stream);
 }
