@@ -501,8 +501,11 @@ tile_rows_kernel(CnScene sc, Ws g, int *__restrict__ cursor, uint8_t *__restrict
 // Texels with more than kHeavyRows rows (border texels that collect every clamped out-of-frustum
 // sample) are deferred to a second kernel in which a whole CTA splits the rows.
 constexpr int kMaxSets = 4;
-constexpr int kFgWarps = 16;
+constexpr int kFgWarps = 8;                     // main sweep: 3 CTAs of 8 warps per SM (<= 85 registers)
 constexpr int kFgThreads = 32 * kFgWarps;
+constexpr int kFgCtasPerSm = 3;
+constexpr int kHeavyWarps = 16;                 // deferred texels: one 16-warp CTA per texel
+constexpr int kHeavyThreads = 32 * kHeavyWarps;
 constexpr int kHeavyRows = 192;
 constexpr int kUnitRows = 2;  // a work unit = kUnitRows x 8 texels of one 8x8 texel tile
 
@@ -540,54 +543,67 @@ __device__ __forceinline__ void texel_pair_range(const CnScene &sc, const GradAr
   len = en - st;
 }
 
-// acc += sum over flat row indices f in [f0, f1) (step `stride` batches of 32) of this texel's pairs
-__device__ __forceinline__ void texel_accumulate(const GradArgs &a, int st, int len, int off_incl, int n, int batch0,
-                                                 int batch_stride, float (&acc)[8]) {
+// lane f of the warp: record of flat row b0 + f of this texel's pairs (raw, not yet consumed), and its pair
+struct RowFetch {
+  int4 rec;
+  int pair;   // set * 4 + corner, -1 = no row
+};
+__device__ __forceinline__ RowFetch fetch_rows(const GradArgs &a, int st, int len, int off_incl, int n, int b0) {
   const uint32_t l = lane_id();
   const int n_pairs = a.n_sets * 4;
+  const int f = b0 + (int)l;
+  int my_p = 0;
+  for (int p = 0; p < n_pairs; ++p) my_p += (f >= __shfl_sync(0xffffffffu, off_incl, p)) ? 1 : 0;
+  my_p = min(my_p, n_pairs - 1);
+  const int p_st = __shfl_sync(0xffffffffu, st, my_p);
+  const int p_off = __shfl_sync(0xffffffffu, off_incl - len, my_p);
+  RowFetch r;
+  r.pair = -1;
+  r.rec = make_int4(0, 0, 0, 0);
+  if (f < n) {
+    r.pair = my_p;
+    r.rec = __ldg(a.set[my_p >> 2].rec_s + p_st + (f - p_off));
+  }
+  return r;
+}
+
+// acc += sum over the nb rows held by lanes 0..nb-1 of  weight(row, corner) * dX[row]
+__device__ __forceinline__ void accumulate_rows(const GradArgs &a, const RowFetch &rf, int nb, float (&acc)[8]) {
+  const uint32_t l = lane_id();
   // lane constant part of the dX address: channels 4l..4l+3 live in chunk l/2 (half l%2) of slabs 0..1,
   // channels 128+4l.. in the same position two slabs further
   const uint32_t lane_off = ((l >> 4) * CN_SLAB_BYTES) + (((l >> 1) & 7u) << 4) + (l & 1u) * 8u;
-  for (int b0 = batch0 * 32; b0 < n; b0 += batch_stride * 32) {
-    // ---- lane f: record of flat row b0 + f
-    const int f = b0 + (int)l;
-    int my_p = 0;
-    for (int p = 0; p < n_pairs; ++p) my_p += (f >= __shfl_sync(0xffffffffu, off_incl, p)) ? 1 : 0;
-    my_p = min(my_p, n_pairs - 1);
-    const int p_st = __shfl_sync(0xffffffffu, st, my_p);
-    const int p_off = __shfl_sync(0xffffffffu, off_incl - len, my_p);
-    float w = 0.f;
-    uint64_t addr = 0;
-    if (f < n) {
-      const GradSet &gs = a.set[my_p >> 2];
-      const int4 r = __ldg(gs.rec_s + p_st + (f - p_off));
-      const float ax = __int_as_float(r.z), ay = __int_as_float(r.w);
-      w = ((my_p & 1) ? ax : 1.f - ax) * ((my_p & 2) ? ay : 1.f - ay);
-      const uint32_t row = (uint32_t)r.x;
-      addr = (uint64_t)(uintptr_t)gs.dx + ((uint64_t)(row >> 7) * CN_X_TILE_BYTES + (row & 127u) * 128u) + (row & 7u);
+  float w = 0.f;
+  uint64_t addr = 0;
+  if (rf.pair >= 0) {
+    const float ax = __int_as_float(rf.rec.z), ay = __int_as_float(rf.rec.w);
+    w = ((rf.pair & 1) ? ax : 1.f - ax) * ((rf.pair & 2) ? ay : 1.f - ay);
+    const uint32_t row = (uint32_t)rf.rec.x;
+    // 128-byte aligned row start inside the dX image; the swizzle phase (row % 8) rides in the low bits
+    addr = (uint64_t)(uintptr_t)a.set[rf.pair >> 2].dx +
+           ((uint64_t)(row >> 7) * CN_X_TILE_BYTES + (row & 127u) * 128u) + (row & 7u);
+  }
+  const uint32_t a_lo = (uint32_t)addr, a_hi = (uint32_t)(addr >> 32);
+  constexpr int U = 8;
+  for (int u0 = 0; u0 < nb; u0 += U) {
+    uint2 va[U], vb[U];
+    float wu[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int src = min(u0 + u, nb - 1);
+      wu[u] = (u0 + u < nb) ? __shfl_sync(0xffffffffu, w, src) : 0.f;
+      const uint32_t lo = __shfl_sync(0xffffffffu, a_lo, src), hi = __shfl_sync(0xffffffffu, a_hi, src);
+      const uint64_t base = ((uint64_t)hi << 32) | (lo & ~127u);
+      const uint8_t *p = reinterpret_cast<const uint8_t *>(base + (lane_off ^ ((lo & 7u) << 4)));
+      va[u] = __ldg(reinterpret_cast<const uint2 *>(p));
+      vb[u] = __ldg(reinterpret_cast<const uint2 *>(p + 2 * CN_SLAB_BYTES));
     }
-    const int nb = min(32, n - b0);
-    const uint32_t a_lo = (uint32_t)addr, a_hi = (uint32_t)(addr >> 32);
-    for (int u0 = 0; u0 < nb; u0 += 4) {
-      uint2 va[4], vb[4];
-      float wu[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int src = min(u0 + u, nb - 1);
-        wu[u] = (u0 + u < nb) ? __shfl_sync(0xffffffffu, w, src) : 0.f;
-        const uint32_t lo = __shfl_sync(0xffffffffu, a_lo, src), hi = __shfl_sync(0xffffffffu, a_hi, src);
-        const uint64_t base = ((uint64_t)hi << 32) | (lo & ~127u);
-        const uint8_t *p = reinterpret_cast<const uint8_t *>(base + (lane_off ^ ((lo & 7u) << 4)));
-        va[u] = __ldg(reinterpret_cast<const uint2 *>(p));
-        vb[u] = __ldg(reinterpret_cast<const uint2 *>(p + 2 * CN_SLAB_BYTES));
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        acc[0] = fmaf(wu[u], bf16_lo(va[u].x), acc[0]); acc[1] = fmaf(wu[u], bf16_hi(va[u].x), acc[1]);
-        acc[2] = fmaf(wu[u], bf16_lo(va[u].y), acc[2]); acc[3] = fmaf(wu[u], bf16_hi(va[u].y), acc[3]);
-        acc[4] = fmaf(wu[u], bf16_lo(vb[u].x), acc[4]); acc[5] = fmaf(wu[u], bf16_hi(vb[u].x), acc[5]);
-        acc[6] = fmaf(wu[u], bf16_lo(vb[u].y), acc[6]); acc[7] = fmaf(wu[u], bf16_hi(vb[u].y), acc[7]);
-      }
+    for (int u = 0; u < U; ++u) {
+      acc[0] = fmaf(wu[u], bf16_lo(va[u].x), acc[0]); acc[1] = fmaf(wu[u], bf16_hi(va[u].x), acc[1]);
+      acc[2] = fmaf(wu[u], bf16_lo(va[u].y), acc[2]); acc[3] = fmaf(wu[u], bf16_hi(va[u].y), acc[3]);
+      acc[4] = fmaf(wu[u], bf16_lo(vb[u].x), acc[4]); acc[5] = fmaf(wu[u], bf16_hi(vb[u].x), acc[5]);
+      acc[6] = fmaf(wu[u], bf16_lo(vb[u].y), acc[6]); acc[7] = fmaf(wu[u], bf16_hi(vb[u].y), acc[7]);
     }
   }
 }
@@ -619,47 +635,80 @@ __device__ __forceinline__ void texel_store(float *__restrict__ d_features, int6
   o[32 + l] = r1;
 }
 
-__global__ void __launch_bounds__(kFgThreads, 2)
+// Per warp, three dependent global loads lead to a texel's sum (key offsets -> records -> dX rows), so
+// the texels of a work unit run through a 3-stage software pipeline: while the dX rows of texel t
+// are summed, the records of texel t+1 and the key offsets of texel t+2 are already in flight.
+__global__ void __launch_bounds__(kFgThreads, kFgCtasPerSm)
 feature_grad_kernel(CnScene sc, GradArgs a, float *__restrict__ d_features) {
   const uint32_t l = lane_id();
+  constexpr int kUnitTexels = kUnitRows * kT;
+  int next_unit = 0;
+  if (l == 0) next_unit = atomicAdd(a.cursor, 1);
   for (;;) {
-    int unit = 0;
-    if (l == 0) unit = atomicAdd(a.cursor, 1);
-    unit = __shfl_sync(0xffffffffu, unit, 0);
+    const int unit = __shfl_sync(0xffffffffu, next_unit, 0);
     if (unit >= a.n_units) break;
+    if (l == 0) next_unit = atomicAdd(a.cursor, 1);  // consumed at the top of the next round
     const int q = unit % (kT / kUnitRows);
     const int tile = unit / (kT / kUnitRows);
     const int tx = tile % a.ttx;
     const int ty = (tile / a.ttx) % a.tty;
     const int bv = tile / (a.ttx * a.tty);
-    for (int t = 0; t < kUnitRows * kT; ++t) {
-      const int Y = ty * kT + q * kUnitRows + t / kT, X = tx * kT + t % kT;
-      if (Y >= sc.H || X >= sc.W) continue;
-      int st, len, n;
-      texel_pair_range(sc, a, (int)l, bv, Y, X, st, len);
-      const int off_incl = pair_scan(len, n);
-      const int64_t texel = ((int64_t)bv * sc.H + Y) * sc.W + X;
-      if (n > kHeavyRows) {
-        int slot = 0;
-        if (l == 0) slot = atomicAdd(a.heavy_n, 1);
-        slot = __shfl_sync(0xffffffffu, slot, 0);
-        if (slot < a.heavy_cap) {
-          if (l == 0) a.heavy_list[slot] = (int)texel;
-          continue;
+    const int Y0 = ty * kT + q * kUnitRows, X0 = tx * kT;
+    auto ranges = [&](int t, int &st, int &len) {  // stage A
+      st = 0;
+      len = 0;
+      const int Y = Y0 + t / kT, X = X0 + t % kT;
+      if (t < kUnitTexels && Y < sc.H && X < sc.W) texel_pair_range(sc, a, (int)l, bv, Y, X, st, len);
+    };
+    int st1, len1, st2, len2;          // ranges of texel t+1 (loaded), t+2 (in flight)
+    int st0, len0, off0, n0;           // texel t: ranges, scan
+    RowFetch rf0;                      // texel t: first 32 records (in flight)
+    ranges(0, st0, len0);
+    ranges(1, st1, len1);
+    off0 = pair_scan(len0, n0);
+    rf0 = fetch_rows(a, st0, len0, off0, min(n0, n0 > kHeavyRows ? 0 : 32), 0);
+    for (int t = 0; t < kUnitTexels; ++t) {
+      ranges(t + 2, st2, len2);
+      // stage B for texel t+1
+      int n1;
+      const int off1 = pair_scan(len1, n1);
+      const RowFetch rf1 = fetch_rows(a, st1, len1, off1, min(n1, n1 > kHeavyRows ? 0 : 32), 0);
+      // stage C for texel t
+      const int Y = Y0 + t / kT, X = X0 + t % kT;
+      if (Y < sc.H && X < sc.W) {
+        const int64_t texel = ((int64_t)bv * sc.H + Y) * sc.W + X;
+        bool deferred = false;
+        if (n0 > kHeavyRows) {
+          int slot = 0;
+          if (l == 0) slot = atomicAdd(a.heavy_n, 1);
+          slot = __shfl_sync(0xffffffffu, slot, 0);
+          if (slot < a.heavy_cap) {
+            if (l == 0) a.heavy_list[slot] = (int)texel;
+            deferred = true;
+          } else {
+            rf0 = fetch_rows(a, st0, len0, off0, n0, 0);  // list full: do it here after all
+          }
         }
-        // list full: fall through and do it here
+        if (!deferred) {
+          float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+          accumulate_rows(a, rf0, min(32, n0), acc);
+          for (int b0 = 32; b0 < n0; b0 += 32) {
+            const RowFetch rf = fetch_rows(a, st0, len0, off0, n0, b0);
+            accumulate_rows(a, rf, min(32, n0 - b0), acc);
+          }
+          texel_store(d_features, texel, acc, a.accumulate);
+        }
       }
-      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      texel_accumulate(a, st, len, off_incl, n, 0, 1, acc);
-      texel_store(d_features, texel, acc, a.accumulate);
+      st0 = st1; len0 = len1; off0 = off1; n0 = n1; rf0 = rf1;
+      st1 = st2; len1 = len2;
     }
   }
 }
 
 // deferred texels: one CTA per texel, warps take batches of 32 rows round-robin, partial sums meet in smem
-__global__ void __launch_bounds__(kFgThreads, 1)
+__global__ void __launch_bounds__(kHeavyThreads, 1)
 feature_grad_heavy_kernel(CnScene sc, GradArgs a, float *__restrict__ d_features) {
-  __shared__ float part[kFgWarps][CN_FEAT_C];
+  __shared__ float part[kHeavyWarps][CN_FEAT_C];
   const uint32_t l = lane_id(), warp = threadIdx.x >> 5;
   const int n_heavy = min(*a.heavy_n, a.heavy_cap);
   for (int h = blockIdx.x; h < n_heavy; h += gridDim.x) {
@@ -671,14 +720,17 @@ feature_grad_heavy_kernel(CnScene sc, GradArgs a, float *__restrict__ d_features
     texel_pair_range(sc, a, (int)l, bv, Y, X, st, len);
     const int off_incl = pair_scan(len, n);
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    texel_accumulate(a, st, len, off_incl, n, (int)warp, kFgWarps, acc);
+    for (int b0 = (int)warp * 32; b0 < n; b0 += kHeavyWarps * 32) {
+      const RowFetch rf = fetch_rows(a, st, len, off_incl, n, b0);
+      accumulate_rows(a, rf, min(32, n - b0), acc);
+    }
     *reinterpret_cast<float4 *>(&part[warp][4 * l]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
     *reinterpret_cast<float4 *>(&part[warp][128 + 4 * l]) = make_float4(acc[4], acc[5], acc[6], acc[7]);
     __syncthreads();
     if (threadIdx.x < CN_FEAT_C) {
       float s = 0.f;
 #pragma unroll
-      for (int w = 0; w < kFgWarps; ++w) s += part[w][threadIdx.x];
+      for (int w = 0; w < kHeavyWarps; ++w) s += part[w][threadIdx.x];
       float *o = d_features + texel * CN_FEAT_C + threadIdx.x;
       *o = a.accumulate ? *o + s : s;
     }
@@ -844,8 +896,8 @@ static int run_feature_grad(const CnScene *scene, int n_sets, const Ws *const *w
     set_error("cn_feature_grad: cudaMemsetAsync: %s", cudaGetErrorString(ce));
     return (int)ce;
   }
-  feature_grad_kernel<<<2 * kNumSMs, kFgThreads, 0, st>>>(*scene, a, d_features);
-  feature_grad_heavy_kernel<<<kNumSMs, kFgThreads, 0, st>>>(*scene, a, d_features);
+  feature_grad_kernel<<<kFgCtasPerSm * kNumSMs, kFgThreads, 0, st>>>(*scene, a, d_features);
+  feature_grad_heavy_kernel<<<kNumSMs, kHeavyThreads, 0, st>>>(*scene, a, d_features);
   return check_launch("cn_feature_grad");
 }
 
