@@ -206,11 +206,19 @@ def test_binned_gather_matches_direct_gather(cuda, shape):
     assert torch.equal(got[:, 120:123], want[:, :3].to(torch.bfloat16).to(torch.float32))
 
 
-def test_binned_scatter_many_rows(cuda):
-    """feature-map gradient and dz with hundreds of rows per bin against fp64 autograd of the oracle."""
+@pytest.mark.parametrize('corner', [False, True])
+def test_binned_scatter_many_rows(cuda, corner):
+    """feature-map gradient and dz with hundreds of rows per bin against fp64 autograd of the oracle.
+    corner=True moves the principal point far outside the frame, so every sample is clamped to the same
+    frame corner: 12288 rows on one cell (the 'huge texel' path that spreads a texel over all CTAs)."""
     from clipnerf_b200 import layout, ops
     from oracle import nerf_oracle as O
-    sc = _scene(seed=6, b=1, nv=2, nr=64, H=24, W=32)
+    sc = _scene(seed=6, b=1, nv=2, nr=192 if corner else 64, H=24, W=32)
+    if corner:
+        K = sc['inputs'][3].clone()
+        K[..., 0, 2] = -4000.0
+        K[..., 1, 2] = 5000.0
+        sc['inputs'] = sc['inputs'][:3] + (K,) + sc['inputs'][4:]
     scene, ro, rd = _cuda_scene(sc, cuda)
     i_ro, i_rd, img, K, E = [t.double() for t in sc['inputs']]
     feats = sc['features'].double().requires_grad_(True)
@@ -232,9 +240,13 @@ def test_binned_scatter_many_rows(cuda):
     dx = layout.matrix_to_tiles(gint).to(cuda)
     x, ws = ops.project_gather_fwd(scene, ro, rd, z32.to(cuda), return_ws=True)
     d_feat = torch.zeros_like(scene.features)
-    dz = torch.zeros(1, 64, 64, device=cuda)
+    dz = torch.zeros(1, z32.shape[1], 64, device=cuda)
     ops.project_gather_bwd(scene, ro, rd, z32.to(cuda), dx, d_feat, dz, ws)
     assert rel_err(d_feat, feats.grad) < 1e-4, rel_err(d_feat, feats.grad)
+    # one sweep that writes every texel exactly once (no zero fill) gives the same map
+    d_once = torch.full_like(d_feat, float('nan'))
+    ops.feature_grad(scene, [(ws, dx, z32.shape[1], 64)], d_once, accumulate=False)
+    assert rel_err(d_once, feats.grad) < 1e-4
     assert rel_err(dz, z.grad) < 2e-3, rel_err(dz, z.grad)
     # the workspace can be re-used: a second backward accumulates the same amounts again
     ops.project_gather_bwd(scene, ro, rd, z32.to(cuda), dx, d_feat, dz, ws)

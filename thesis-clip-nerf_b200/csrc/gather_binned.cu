@@ -37,8 +37,8 @@ constexpr int kCells = kT * kT;
 constexpr int kChunk = 128;                      // max rows per work item
 
 // header ints of the workspace
-enum { kHdrItems = 0, kHdrCurFwd = 1, kHdrCurZg = 2, kHdrCurSc = 3, kHdrHeavyN = 4, kHdrTicket = 5, kHdrInts = 64 };
-constexpr int kHeavyCap = 8192;               // deferred (heavy) texels of the feature-gradient sweep
+enum { kHdrItems = 0, kHdrCurFwd = 1, kHdrCurZg = 2, kHdrCurSc = 3, kHdrHeavyN = 4 /* 2 ints */, kHdrTicket = 6, kHdrInts = 64 };
+constexpr int kHeavyCap = 65536;              // deferred (texel, chunk) entries of the feature-gradient sweep
 
 struct Ws {
   int64_t rows;
@@ -52,7 +52,7 @@ struct Ws {
   int2 *keyrank;   // [rows]     (key, rank inside key)
   int4 *rec_s;     // [rows]     records sorted by key
   float2 *gpix;    // [rows]     feature part of d loss / d (alpha_x, alpha_y)
-  int *heavy;      // [kHeavyCap] texels deferred by feature_grad_kernel
+  int2 *heavy;     // [kHeavyCap] (texel, first row) chunks deferred by feature_grad_kernel
   size_t total;
 };
 
@@ -83,7 +83,7 @@ static Ws ws_layout(int b, int nv, int H, int W, int64_t rows, void *base) {
   w.keyrank = (int2 *)take((size_t)rows * 8);
   w.rec_s = (int4 *)take((size_t)rows * 16);
   w.gpix = (float2 *)take((size_t)rows * 8);
-  w.heavy = (int *)take((size_t)kHeavyCap * 4);
+  w.heavy = (int2 *)take((size_t)kHeavyCap * 8);
   w.total = o;
   return w;
 }
@@ -504,9 +504,8 @@ constexpr int kMaxSets = 4;
 constexpr int kFgWarps = 8;                     // main sweep: 3 CTAs of 8 warps per SM (<= 85 registers)
 constexpr int kFgThreads = 32 * kFgWarps;
 constexpr int kFgCtasPerSm = 3;
-constexpr int kHeavyWarps = 16;                 // deferred texels: one 16-warp CTA per texel
-constexpr int kHeavyThreads = 32 * kHeavyWarps;
-constexpr int kHeavyRows = 192;
+constexpr int kHeavyRows = 192;                 // a texel with more rows is deferred to the second kernel ...
+constexpr int kHeavyChunk = 256;                // ... as independent chunks of this many rows
 constexpr int kUnitRows = 2;  // a work unit = kUnitRows x 8 texels of one 8x8 texel tile
 
 struct GradSet {
@@ -523,8 +522,8 @@ struct GradArgs {
   int n_units;
   int accumulate;
   int *cursor;      // work-unit cursor
-  int *heavy_n;     // number of deferred texels
-  int *heavy_list;  // [heavy_cap] texel index (bv*H + Y)*W + X
+  int *heavy_n;     // number of deferred entries, and the cursor of the second kernel
+  int2 *heavy_list; // [heavy_cap] (texel index (bv*H + Y)*W + X, first flat row of the chunk)
   int heavy_cap;
 };
 
@@ -567,6 +566,31 @@ __device__ __forceinline__ RowFetch fetch_rows(const GradArgs &a, int st, int le
   return r;
 }
 
+// rows u0 .. u0+U-1 (masked at nb) of the batch held by the warp's lanes: all 2U loads first, then the FMAs
+template <int U>
+__device__ __forceinline__ void accumulate_group(float w, uint32_t a_lo, uint32_t a_hi, uint32_t lane_off, int u0,
+                                                 int nb, float (&acc)[8]) {
+  uint2 va[U], vb[U];
+  float wu[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const int src = min(u0 + u, nb - 1);
+    wu[u] = (u0 + u < nb) ? __shfl_sync(0xffffffffu, w, src) : 0.f;
+    const uint32_t lo = __shfl_sync(0xffffffffu, a_lo, src), hi = __shfl_sync(0xffffffffu, a_hi, src);
+    const uint64_t base = ((uint64_t)hi << 32) | (lo & ~127u);
+    const uint8_t *p = reinterpret_cast<const uint8_t *>(base + (lane_off ^ ((lo & 7u) << 4)));
+    va[u] = __ldg(reinterpret_cast<const uint2 *>(p));
+    vb[u] = __ldg(reinterpret_cast<const uint2 *>(p + 2 * CN_SLAB_BYTES));
+  }
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    acc[0] = fmaf(wu[u], bf16_lo(va[u].x), acc[0]); acc[1] = fmaf(wu[u], bf16_hi(va[u].x), acc[1]);
+    acc[2] = fmaf(wu[u], bf16_lo(va[u].y), acc[2]); acc[3] = fmaf(wu[u], bf16_hi(va[u].y), acc[3]);
+    acc[4] = fmaf(wu[u], bf16_lo(vb[u].x), acc[4]); acc[5] = fmaf(wu[u], bf16_hi(vb[u].x), acc[5]);
+    acc[6] = fmaf(wu[u], bf16_lo(vb[u].y), acc[6]); acc[7] = fmaf(wu[u], bf16_hi(vb[u].y), acc[7]);
+  }
+}
+
 // acc += sum over the nb rows held by lanes 0..nb-1 of  weight(row, corner) * dX[row]
 __device__ __forceinline__ void accumulate_rows(const GradArgs &a, const RowFetch &rf, int nb, float (&acc)[8]) {
   const uint32_t l = lane_id();
@@ -584,26 +608,15 @@ __device__ __forceinline__ void accumulate_rows(const GradArgs &a, const RowFetc
            ((uint64_t)(row >> 7) * CN_X_TILE_BYTES + (row & 127u) * 128u) + (row & 7u);
   }
   const uint32_t a_lo = (uint32_t)addr, a_hi = (uint32_t)(addr >> 32);
-  constexpr int U = 8;
-  for (int u0 = 0; u0 < nb; u0 += U) {
-    uint2 va[U], vb[U];
-    float wu[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int src = min(u0 + u, nb - 1);
-      wu[u] = (u0 + u < nb) ? __shfl_sync(0xffffffffu, w, src) : 0.f;
-      const uint32_t lo = __shfl_sync(0xffffffffu, a_lo, src), hi = __shfl_sync(0xffffffffu, a_hi, src);
-      const uint64_t base = ((uint64_t)hi << 32) | (lo & ~127u);
-      const uint8_t *p = reinterpret_cast<const uint8_t *>(base + (lane_off ^ ((lo & 7u) << 4)));
-      va[u] = __ldg(reinterpret_cast<const uint2 *>(p));
-      vb[u] = __ldg(reinterpret_cast<const uint2 *>(p + 2 * CN_SLAB_BYTES));
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      acc[0] = fmaf(wu[u], bf16_lo(va[u].x), acc[0]); acc[1] = fmaf(wu[u], bf16_hi(va[u].x), acc[1]);
-      acc[2] = fmaf(wu[u], bf16_lo(va[u].y), acc[2]); acc[3] = fmaf(wu[u], bf16_hi(va[u].y), acc[3]);
-      acc[4] = fmaf(wu[u], bf16_lo(vb[u].x), acc[4]); acc[5] = fmaf(wu[u], bf16_hi(vb[u].x), acc[5]);
-      acc[6] = fmaf(wu[u], bf16_lo(vb[u].y), acc[6]); acc[7] = fmaf(wu[u], bf16_hi(vb[u].y), acc[7]);
+  // groups of 8 rows (16 loads in flight per lane) while more than 4 rows remain, else a group of 4
+  int u0 = 0;
+  while (u0 < nb) {
+    if (nb - u0 > 4) {
+      accumulate_group<8>(w, a_lo, a_hi, lane_off, u0, nb, acc);
+      u0 += 8;
+    } else {
+      accumulate_group<4>(w, a_lo, a_hi, lane_off, u0, nb, acc);
+      u0 += 4;
     }
   }
 }
@@ -679,12 +692,17 @@ feature_grad_kernel(CnScene sc, GradArgs a, float *__restrict__ d_features) {
         const int64_t texel = ((int64_t)bv * sc.H + Y) * sc.W + X;
         bool deferred = false;
         if (n0 > kHeavyRows) {
+          const int n_chunks = (n0 + kHeavyChunk - 1) / kHeavyChunk;
           int slot = 0;
-          if (l == 0) slot = atomicAdd(a.heavy_n, 1);
+          if (l == 0) slot = atomicAdd(a.heavy_n, n_chunks);
           slot = __shfl_sync(0xffffffffu, slot, 0);
-          if (slot < a.heavy_cap) {
-            if (l == 0) a.heavy_list[slot] = (int)texel;
+          if (slot + n_chunks <= a.heavy_cap) {
+            for (int c = (int)l; c < n_chunks; c += 32) a.heavy_list[slot + c] = make_int2((int)texel, c * kHeavyChunk);
             deferred = true;
+            if (!a.accumulate) {  // the chunks are summed with red.global.add: start from zero
+              const float z8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+              texel_store(d_features, texel, z8, 0);
+            }
           } else {
             rf0 = fetch_rows(a, st0, len0, off0, n0, 0);  // list full: do it here after all
           }
@@ -705,36 +723,39 @@ feature_grad_kernel(CnScene sc, GradArgs a, float *__restrict__ d_features) {
   }
 }
 
-// deferred texels: one CTA per texel, warps take batches of 32 rows round-robin, partial sums meet in smem
-__global__ void __launch_bounds__(kHeavyThreads, 1)
+// deferred texels (frame borders collect every clamped out-of-frustum sample): independent chunks of
+// kHeavyChunk rows, one warp each, partial sums added with red.global.add.v4.f32
+__global__ void __launch_bounds__(kFgThreads, kFgCtasPerSm)
 feature_grad_heavy_kernel(CnScene sc, GradArgs a, float *__restrict__ d_features) {
-  __shared__ float part[kHeavyWarps][CN_FEAT_C];
-  const uint32_t l = lane_id(), warp = threadIdx.x >> 5;
-  const int n_heavy = min(*a.heavy_n, a.heavy_cap);
-  for (int h = blockIdx.x; h < n_heavy; h += gridDim.x) {
-    const int64_t texel = a.heavy_list[h];
+  const uint32_t l = lane_id();
+  const int n_entries = min(a.heavy_n[0], a.heavy_cap);
+  for (;;) {
+    int e = 0;
+    if (l == 0) e = atomicAdd(a.heavy_n + 1, 1);
+    e = __shfl_sync(0xffffffffu, e, 0);
+    if (e >= n_entries) break;
+    const int2 ent = a.heavy_list[e];
+    const int64_t texel = ent.x;
     const int X = (int)(texel % sc.W);
     const int Y = (int)((texel / sc.W) % sc.H);
     const int bv = (int)(texel / ((int64_t)sc.W * sc.H));
     int st, len, n;
     texel_pair_range(sc, a, (int)l, bv, Y, X, st, len);
     const int off_incl = pair_scan(len, n);
+    const int end = min(n, ent.y + kHeavyChunk);
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int b0 = (int)warp * 32; b0 < n; b0 += kHeavyWarps * 32) {
-      const RowFetch rf = fetch_rows(a, st, len, off_incl, n, b0);
-      accumulate_rows(a, rf, min(32, n - b0), acc);
+    RowFetch rf = fetch_rows(a, st, len, off_incl, end, ent.y);
+    for (int b0 = ent.y; b0 < end; b0 += 32) {
+      RowFetch rf_next;
+      rf_next.pair = -1;
+      rf_next.rec = make_int4(0, 0, 0, 0);
+      if (b0 + 32 < end) rf_next = fetch_rows(a, st, len, off_incl, end, b0 + 32);  // in flight during the sums
+      accumulate_rows(a, rf, min(32, end - b0), acc);
+      rf = rf_next;
     }
-    *reinterpret_cast<float4 *>(&part[warp][4 * l]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
-    *reinterpret_cast<float4 *>(&part[warp][128 + 4 * l]) = make_float4(acc[4], acc[5], acc[6], acc[7]);
-    __syncthreads();
-    if (threadIdx.x < CN_FEAT_C) {
-      float s = 0.f;
-#pragma unroll
-      for (int w = 0; w < kHeavyWarps; ++w) s += part[w][threadIdx.x];
-      float *o = d_features + texel * CN_FEAT_C + threadIdx.x;
-      *o = a.accumulate ? *o + s : s;
-    }
-    __syncthreads();
+    float *o = d_features + texel * CN_FEAT_C;
+    red_add_f4(o + 4 * l, acc[0], acc[1], acc[2], acc[3]);
+    red_add_f4(o + 128 + 4 * l, acc[4], acc[5], acc[6], acc[7]);
   }
 }
 
@@ -891,13 +912,13 @@ static int run_feature_grad(const CnScene *scene, int n_sets, const Ws *const *w
   a.heavy_n = w0->hdr + kHdrHeavyN;
   a.heavy_list = w0->heavy;
   a.heavy_cap = kHeavyCap;
-  cudaError_t ce = cudaMemsetAsync(w0->hdr + kHdrCurSc, 0, 2 * sizeof(int), st);  // cursor + heavy count
+  cudaError_t ce = cudaMemsetAsync(w0->hdr + kHdrCurSc, 0, 3 * sizeof(int), st);  // cursor + deferred entries + their cursor
   if (ce != cudaSuccess) {
     set_error("cn_feature_grad: cudaMemsetAsync: %s", cudaGetErrorString(ce));
     return (int)ce;
   }
   feature_grad_kernel<<<kFgCtasPerSm * kNumSMs, kFgThreads, 0, st>>>(*scene, a, d_features);
-  feature_grad_heavy_kernel<<<kNumSMs, kHeavyThreads, 0, st>>>(*scene, a, d_features);
+  feature_grad_heavy_kernel<<<kFgCtasPerSm * kNumSMs, kFgThreads, 0, st>>>(*scene, a, d_features);
   return check_launch("cn_feature_grad");
 }
 
