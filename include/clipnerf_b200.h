@@ -171,13 +171,13 @@ int cn_pack_weights(const float *params, void *packed, void *stream);
 /* per-view stage: Dense 379->128 + 3 ResNet blocks (layers.py:363-365).
  *   x_tiles -> h3_tiles [n_tiles] (bf16 activation tiles).
  *   acts (nullable): saved block operands for the backward,
- *   [n_tiles][3 blocks][2] activation tiles (relu(h), relu(t)).                        */
+ *   [n_tiles][3] activation tiles relu(h) (one per block; relu(t) is recomputed).       */
 int cn_mlp_feature_fwd(const void *packed, const void *x_tiles, int64_t n_tiles, void *h3_tiles,
                        void *acts, void *stream);
 /* fusion stage: mean over views + 3 ResNet blocks + RenderReadout
  * (layers.py:366-376,392-397).  h3_tiles is [b][nv][tiles_per_view]; output
  * rgbs [b*tiles_per_view*128, 4] = (sigmoid rgb, softplus sigma).
- *   acts (nullable): [n_out_tiles][7] activation tiles (3 x (relu(h), relu(t)), relu(e)). */
+ *   acts (nullable): [n_out_tiles][4] activation tiles (3 x relu(h), relu(e)).           */
 int cn_mlp_fusion_fwd(const void *packed, const void *h3_tiles, int32_t b, int32_t nv,
                       int64_t tiles_per_view, float *rgbs, void *acts, void *stream);
 
@@ -186,7 +186,9 @@ int cn_mlp_fusion_fwd(const void *packed, const void *h3_tiles, int32_t b, int32
 int cn_mlp_readout_bwd(const float *params, const float *d_y, const void *acts, int32_t act_stride_tiles,
                        int32_t act_index, int64_t n_tiles, void *g_tiles, float *grad, void *stream);
 /* backward of one ResNet block for every tile: g_y -> g_h (in place allowed),
- * dW/db of both Dense layers accumulated into grad.  blk in 0..5.                     */
+ * dW/db of both Dense layers accumulated into grad.  blk in 0..5.  acts tile
+ * [act_index] of every tile is the block's saved relu(h); the hidden activation is
+ * recomputed on the tensor cores (bit-identical to the forward).                      */
 int cn_mlp_block_bwd(const void *packed, int32_t blk, const void *acts, int32_t act_stride_tiles,
                      int32_t act_index, int64_t n_tiles, const void *gy_tiles, void *gh_tiles,
                      float *grad, void *stream);

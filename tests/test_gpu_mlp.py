@@ -51,12 +51,12 @@ def test_mlp_forward(cuda, nv, rows):
     e = rel_err(rgbs, ref)
     assert e < 1e-2, f'rgbs rel err {e}'
     # saved operands: relu of the block inputs / hidden activations
-    a = layout.tiles_to_matrix(acts_f, 128).view(-1, 6, 128, 128)
+    a = layout.tiles_to_matrix(acts_f, 128).view(-1, 3, 128, 128)
     a1_ref = torch.relu(outs[0]).reshape(-1, 128, 128)
     assert rel_err(a[:, 0], a1_ref) < 1e-2
-    au = layout.tiles_to_matrix(acts_u, 128).view(-1, 7, 128, 128)
+    au = layout.tiles_to_matrix(acts_u, 128).view(-1, 4, 128, 128)
     assert rel_err(au[:, 0], torch.relu(outs[4]).reshape(-1, 128, 128)) < 1e-2
-    assert rel_err(au[:, 6], torch.relu(outs[7]).reshape(-1, 128, 128)) < 1e-2
+    assert rel_err(au[:, 3], torch.relu(outs[7]).reshape(-1, 128, 128)) < 1e-2
     # against the oracle that rounds operands to bf16 at the same points: only accumulation order
     # and one bf16 rounding of the stored tiles remain
     outs_q, chroma_q, sigma_q = _oracle_stages(named, x_ref, b, nv, quant='bf16')
@@ -102,15 +102,15 @@ def test_mlp_backward(cuda):
     h3, acts_f = ops.mlp_feature_fwd(packed, x_tiles, True)
     rgbs, acts_u = ops.mlp_fusion_fwd(packed, h3, b, nv, True)
     grad = torch.zeros_like(dev_flat)
-    gt = ops.mlp_readout_bwd(dev_flat, d_y.to(cuda), acts_u, 7, 6, grad)
+    gt = ops.mlp_readout_bwd(dev_flat, d_y.to(cuda), acts_u, 4, 3, grad)
     errs['g_e'] = rel_err(layout.tiles_to_matrix(gt, 128), outs[7].grad.reshape(-1, 128))
     for blk in (5, 4, 3):
-        ops.mlp_block_bwd(packed, blk, acts_u, 7, 2 * (blk - 3), gt, grad)
+        ops.mlp_block_bwd(packed, blk, acts_u, 4, blk - 3, gt, grad)
         errs[f'g_out{blk + 1}'] = rel_err(layout.tiles_to_matrix(gt, 128), outs[blk + 1].grad.reshape(-1, 128))
     gf = ops.mlp_mean_bwd(gt, b, nv)
     errs['g_h3'] = rel_err(layout.tiles_to_matrix(gf, 128), outs[3].grad.reshape(-1, 128))
     for blk in (2, 1, 0):
-        ops.mlp_block_bwd(packed, blk, acts_f, 6, 2 * blk, gf, grad)
+        ops.mlp_block_bwd(packed, blk, acts_f, 3, blk, gf, grad)
         errs[f'g_out{blk}'] = rel_err(layout.tiles_to_matrix(gf, 128), outs[blk].grad.reshape(-1, 128))
     ops.mlp_l0_wgrad(x_tiles, gf, grad)
     dx = ops.mlp_l0_dgrad(packed, gf)
@@ -152,12 +152,12 @@ def test_mlp_many_tiles_per_cta(cuda):
     assert rel_err(layout.tiles_to_matrix(h3, 128), outs[3].reshape(-1, 128)) < 4e-3
     assert rel_err(rgbs, torch.cat([chroma, sigma[..., None]], -1).reshape(-1, 4)) < 4e-3
     grad = torch.zeros_like(dev_flat)
-    gt = ops.mlp_readout_bwd(dev_flat, d_y.to(cuda), acts_u, 7, 6, grad)
+    gt = ops.mlp_readout_bwd(dev_flat, d_y.to(cuda), acts_u, 4, 3, grad)
     for blk in (5, 4, 3):
-        ops.mlp_block_bwd(packed, blk, acts_u, 7, 2 * (blk - 3), gt, grad)
+        ops.mlp_block_bwd(packed, blk, acts_u, 4, blk - 3, gt, grad)
     gf = ops.mlp_mean_bwd(gt, b, nv)
     for blk in (2, 1, 0):
-        ops.mlp_block_bwd(packed, blk, acts_f, 6, 2 * blk, gf, grad)
+        ops.mlp_block_bwd(packed, blk, acts_f, 3, blk, gf, grad)
     ops.mlp_l0_wgrad(x_tiles, gf, grad)
     dx = ops.mlp_l0_dgrad(packed, gf)
     errs = {name: rel_err(gv, p[name].grad) for name, gv in params.to_named(grad.cpu(), 'fine').items()}

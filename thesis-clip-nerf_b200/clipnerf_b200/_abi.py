@@ -86,7 +86,7 @@ class CnError(RuntimeError):
 
 # kernels launched by each entry point (for launch accounting in bench.py)
 KERNELS_PER_CALL = {name: 1 for name in PROTOTYPES}
-KERNELS_PER_CALL.update({'cn_abi_version': 0, 'cn_last_error': 0, 'cn_gather_ws_bytes': 0, 'cn_mlp_l0_wgrad': 2,
+KERNELS_PER_CALL.update({'cn_abi_version': 0, 'cn_last_error': 0, 'cn_gather_ws_bytes': 0,
                          'cn_project_bin': 4, 'cn_project_gather_fwd': 5, 'cn_feature_grad': 2})
 
 LAUNCHES = 0          # running count of kernel launches issued through the ABI

@@ -202,6 +202,12 @@ def composite_bwd(z, rgbs, d_rgb, d_depth=None, d_weights=None, need_dz=False):
     return d_y, dz
 
 
+# activation tiles saved per 128-row tile for the backward: relu(h) of the 3 blocks of a stage (the hidden
+# activation relu(t) is recomputed by cn_mlp_block_bwd); the fusion stage also keeps relu(e) for the readout
+FEATURE_ACTS = 3
+FUSION_ACTS = 4
+
+
 def pack_weights(params: torch.Tensor) -> torch.Tensor:
     params = _f32c(params)
     assert params.numel() == _abi.NET_PARAMS
@@ -213,7 +219,7 @@ def pack_weights(params: torch.Tensor) -> torch.Tensor:
 def mlp_feature_fwd(packed, x_tiles, save_acts: bool):
     nt = x_tiles.numel() // X_TILE_BYTES
     h3 = _bytes(nt * ACT_TILE_BYTES, x_tiles.device)
-    acts = _bytes(nt * 6 * ACT_TILE_BYTES, x_tiles.device) if save_acts else None
+    acts = _bytes(nt * FEATURE_ACTS * ACT_TILE_BYTES, x_tiles.device) if save_acts else None
     call('cn_mlp_feature_fwd', _ptr(packed), _ptr(x_tiles), nt, _ptr(h3), _ptr(acts), _stream())
     return h3, acts
 
@@ -223,7 +229,7 @@ def mlp_fusion_fwd(packed, h3_tiles, b: int, nv: int, save_acts: bool):
     assert nt % (b * nv) == 0
     tpv = nt // (b * nv)
     rgbs = torch.empty(b * tpv * TILE_ROWS, 4, dtype=torch.float32, device=h3_tiles.device)
-    acts = _bytes(b * tpv * 7 * ACT_TILE_BYTES, h3_tiles.device) if save_acts else None
+    acts = _bytes(b * tpv * FUSION_ACTS * ACT_TILE_BYTES, h3_tiles.device) if save_acts else None
     call('cn_mlp_fusion_fwd', _ptr(packed), _ptr(h3_tiles), b, nv, tpv, _ptr(rgbs), _ptr(acts), _stream())
     return rgbs, acts
 

@@ -39,12 +39,12 @@ def _pass_bwd(P: _Pass, params, grad, scene: ops.Scene, ray_o, ray_d, d_rgb, d_d
     """backward of one pass up to dX (the gradient of the MLP input rows); the feature-map gradient of both
     passes is taken from the two dX images in one sweep afterwards (ops.feature_grad)."""
     d_y, dz = ops.composite_bwd(P.z, P.rgbs.view(*P.z.shape, 4), d_rgb, d_depth, d_weights, need_dz)
-    g = ops.mlp_readout_bwd(params, d_y, P.acts_u, 7, 6, grad)
+    g = ops.mlp_readout_bwd(params, d_y, P.acts_u, ops.FUSION_ACTS, 3, grad)
     for blk in (5, 4, 3):
-        ops.mlp_block_bwd(P.packed, blk, P.acts_u, 7, 2 * (blk - 3), g, grad)
+        ops.mlp_block_bwd(P.packed, blk, P.acts_u, ops.FUSION_ACTS, blk - 3, g, grad)
     gf = ops.mlp_mean_bwd(g, scene.b, scene.nv)
     for blk in (2, 1, 0):
-        ops.mlp_block_bwd(P.packed, blk, P.acts_f, 6, 2 * blk, gf, grad)
+        ops.mlp_block_bwd(P.packed, blk, P.acts_f, ops.FEATURE_ACTS, blk, gf, grad)
     ops.mlp_l0_wgrad(P.x, gf, grad)
     dx = None
     if want_dx or need_dz:

@@ -670,7 +670,7 @@ feature_grad_kernel(CnScene sc, GradArgs a, float *__restrict__ d_features) {
     auto ranges = [&](int t, int &st, int &len) {  // stage A
       st = 0;
       len = 0;
-      const int Y = Y0 + t / kT, X = X0 + t % kT;
+      const int Y = Y0 + t % kUnitRows, X = X0 + t / kUnitRows;  // column-major: the 4 texels of a cell are adjacent in time
       if (t < kUnitTexels && Y < sc.H && X < sc.W) texel_pair_range(sc, a, (int)l, bv, Y, X, st, len);
     };
     int st1, len1, st2, len2;          // ranges of texel t+1 (loaded), t+2 (in flight)
@@ -687,7 +687,7 @@ feature_grad_kernel(CnScene sc, GradArgs a, float *__restrict__ d_features) {
       const int off1 = pair_scan(len1, n1);
       const RowFetch rf1 = fetch_rows(a, st1, len1, off1, min(n1, n1 > kHeavyRows ? 0 : 32), 0);
       // stage C for texel t
-      const int Y = Y0 + t / kT, X = X0 + t % kT;
+      const int Y = Y0 + t % kUnitRows, X = X0 + t / kUnitRows;
       if (Y < sc.H && X < sc.W) {
         const int64_t texel = ((int64_t)bv * sc.H + Y) * sc.W + X;
         bool deferred = false;

@@ -1,18 +1,19 @@
 // Backward of one pre-activation ResNet block (layers.py:262-298) for every 128-row tile, on
 // tcgen05 / TMEM:      y = h + relu(relu(h) Wa + ba) Wb + bb
-//   saved by the forward: A1 = relu(h), A2 = relu(t)   (bf16 tile images)
+//   saved by the forward: A1 = relu(h) only (bf16 tile image).  The hidden activation is RECOMPUTED
+//   here -- one extra GEMM per tile buys a third of the kernel's HBM traffic, which is what bounds it:
+//   A2   = relu(A1 Wa + ba)    (forward GEMM, same bf16 operands and K order as the forward: bit-identical)
 //   g_a2 = g_y Wb^T            (dgrad 1, K-major operands)
 //   dWb += A2^T g_y            (wgrad,  MN-major operands: the SAME smem tiles read transposed)
 //   g_t  = g_a2 * [A2 > 0]     (epilogue 1)  -> bf16 tile in smem,  dba += colsum(g_t)   (bias warps)
 //   g_a1 = g_t Wa^T            (dgrad 2)
 //   dWa += A1^T g_t            (wgrad)
 //   g_h  = g_y + g_a1 * [A1>0] (epilogue 2)  -> global,             dbb += colsum(g_y)   (bias warps)
-// Both weight matrices stay resident in shared memory for the whole kernel and the two weight
+// The three weight images stay resident in shared memory for the whole kernel and the two weight
 // gradients stay resident in TMEM (2 x 128 columns) across all tiles of the CTA; they are
 // flushed once with vector red.global.add at the end.
-//   warp 0: TMA producer (g_y, A2, A1 tiles), warp 1: MMA issuer, warps 2-9: epilogue (4 TMEM lane
+//   warp 0: TMA producer (g_y, A1 tiles), warp 1: MMA issuer, warps 2-9: epilogue (4 TMEM lane
 //   quadrants x 2 column halves), warps 10-11: bias gradients (column sums read from the smem tiles).
-//   g_h leaves through a staging tile and one TMA store per tile.
 #include "common.cuh"
 #include "mlp_layout.cuh"
 
@@ -20,20 +21,23 @@ namespace cn {
 
 constexpr int kBwdThreads = 384;  // warp 0 producer, 1 MMA, 2-9 epilogue (4 lane quadrants x 2 column halves), 10-11 bias sums
 constexpr int kBwdEpiThreads = 256;
-constexpr uint32_t kBwSmemWb = 0;
-constexpr uint32_t kBwSmemWa = 1 * CN_ACT_TILE_BYTES;
-constexpr uint32_t kBwSmemGy = 2 * CN_ACT_TILE_BYTES;
-constexpr uint32_t kBwSmemA2 = 3 * CN_ACT_TILE_BYTES;
+constexpr uint32_t kBwSmemWb = 0;                       // Wb, dgrad image
+constexpr uint32_t kBwSmemWa = 1 * CN_ACT_TILE_BYTES;   // Wa, dgrad image
+constexpr uint32_t kBwSmemWf = 2 * CN_ACT_TILE_BYTES;   // Wa, forward image (recompute of the hidden activation)
+constexpr uint32_t kBwSmemGy = 3 * CN_ACT_TILE_BYTES;
 constexpr uint32_t kBwSmemA1 = 4 * CN_ACT_TILE_BYTES;
-constexpr uint32_t kBwSmemGt = 5 * CN_ACT_TILE_BYTES;
-constexpr uint32_t kBwSmemOut = 6 * CN_ACT_TILE_BYTES;  // g_h staging for the TMA store
+constexpr uint32_t kBwSmemA2 = 5 * CN_ACT_TILE_BYTES;   // written by epilogue 0
+constexpr uint32_t kBwSmemGt = 6 * CN_ACT_TILE_BYTES;   // written by epilogue 1
 constexpr uint32_t kBwdSmemBytes = 7 * CN_ACT_TILE_BYTES + 1024;
 
 struct BwdBars {
   uint64_t w_full;
-  uint64_t full_gy, full_a2, full_a1;
+  uint64_t full_gy, full_a1;
   uint64_t free_gy;                    // 256 epilogue + 64 bias-sum arrivals + 1 tcgen05.commit
-  uint64_t free_a2, free_a1;           // 256 epilogue arrivals + 1 tcgen05.commit
+  uint64_t free_a1;                    // 256 epilogue arrivals + 1 tcgen05.commit
+  uint64_t t_ready;                    // commit: A1 Wa is in TMEM
+  uint64_t a2_ready;                   // 256 epilogue arrivals: relu(t) is in shared memory
+  uint64_t a2_free;                    // commit after wgrad-b
   uint64_t gt_ready;                   // 256 epilogue arrivals
   uint64_t gt_free;                    // commit after wgrad-a + 64 bias-sum arrivals
   uint64_t tmp1_ready, tmp2_ready;     // commits
@@ -42,25 +46,29 @@ struct BwdBars {
 
 __global__ void __launch_bounds__(kBwdThreads, 1)
 mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restrict__ w_b_img,
+                     const uint8_t *__restrict__ w_a_fwd_img, const float *__restrict__ bias_a,
                      const uint8_t *__restrict__ acts, int64_t act_stride_bytes, int64_t n_tiles,
                      const uint8_t *__restrict__ gy_tiles, uint8_t *__restrict__ gh_tiles, float *__restrict__ g_wa,
                      float *__restrict__ g_ba, float *__restrict__ g_wb, float *__restrict__ g_bb) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) BwdBars bars;
   __shared__ uint32_t tmem_slot;
+  __shared__ __align__(16) float s_ba[128];
   uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const uint32_t s_base = smem_u32(smem);
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
 
+  if (threadIdx.x < 128) s_ba[threadIdx.x] = bias_a[threadIdx.x];
   if (threadIdx.x == 0) {
     mbar_init(smem_u32(&bars.w_full), 1);
     mbar_init(smem_u32(&bars.full_gy), 1);
-    mbar_init(smem_u32(&bars.full_a2), 1);
     mbar_init(smem_u32(&bars.full_a1), 1);
     mbar_init(smem_u32(&bars.free_gy), kBwdEpiThreads + 64 + 1);
-    mbar_init(smem_u32(&bars.free_a2), kBwdEpiThreads + 1);
     mbar_init(smem_u32(&bars.free_a1), kBwdEpiThreads + 1);
+    mbar_init(smem_u32(&bars.t_ready), 1);
+    mbar_init(smem_u32(&bars.a2_ready), kBwdEpiThreads);
+    mbar_init(smem_u32(&bars.a2_free), 1);
     mbar_init(smem_u32(&bars.gt_ready), kBwdEpiThreads);
     mbar_init(smem_u32(&bars.gt_free), 64 + 1);
     mbar_init(smem_u32(&bars.tmp1_ready), 1);
@@ -81,31 +89,28 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
   if (warp == 0) {
     // =========================== TMA producer ===========================
     if (lane == 0) {
-      mbar_expect_tx(smem_u32(&bars.w_full), 2 * CN_ACT_TILE_BYTES);
+      mbar_expect_tx(smem_u32(&bars.w_full), 3 * CN_ACT_TILE_BYTES);
       bulk_g2s(s_base + kBwSmemWb, w_b_img, CN_ACT_TILE_BYTES, smem_u32(&bars.w_full));
       bulk_g2s(s_base + kBwSmemWa, w_a_img, CN_ACT_TILE_BYTES, smem_u32(&bars.w_full));
+      bulk_g2s(s_base + kBwSmemWf, w_a_fwd_img, CN_ACT_TILE_BYTES, smem_u32(&bars.w_full));
       uint32_t it = 0;
       for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
         const uint32_t par = (it & 1u) ^ 1u;
+        mbar_wait(smem_u32(&bars.free_a1), par);
+        mbar_expect_tx(smem_u32(&bars.full_a1), CN_ACT_TILE_BYTES);
+        bulk_g2s(s_base + kBwSmemA1, acts + tile * act_stride_bytes, CN_ACT_TILE_BYTES, smem_u32(&bars.full_a1));
         mbar_wait(smem_u32(&bars.free_gy), par);
         mbar_expect_tx(smem_u32(&bars.full_gy), CN_ACT_TILE_BYTES);
         bulk_g2s(s_base + kBwSmemGy, gy_tiles + tile * (int64_t)CN_ACT_TILE_BYTES, CN_ACT_TILE_BYTES,
                  smem_u32(&bars.full_gy));
-        mbar_wait(smem_u32(&bars.free_a2), par);
-        mbar_expect_tx(smem_u32(&bars.full_a2), CN_ACT_TILE_BYTES);
-        bulk_g2s(s_base + kBwSmemA2, acts + tile * act_stride_bytes + CN_ACT_TILE_BYTES, CN_ACT_TILE_BYTES,
-                 smem_u32(&bars.full_a2));
-        mbar_wait(smem_u32(&bars.free_a1), par);
-        mbar_expect_tx(smem_u32(&bars.full_a1), CN_ACT_TILE_BYTES);
-        bulk_g2s(s_base + kBwSmemA1, acts + tile * act_stride_bytes, CN_ACT_TILE_BYTES, smem_u32(&bars.full_a1));
       }
     }
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
     if (lane == 0) {
-      constexpr uint32_t idesc_kk = umma_idesc(128, 128, 0, 0);  // dgrad: both operands K-major
+      constexpr uint32_t idesc_kk = umma_idesc(128, 128, 0, 0);  // forward / dgrad: both operands K-major
       constexpr uint32_t idesc_mn = umma_idesc(128, 128, 1, 1);  // wgrad: both operands MN-major
-      auto dgrad = [&](uint32_t d_tmem, uint32_t a_off, uint32_t b_off) {
+      auto gemm_kk = [&](uint32_t d_tmem, uint32_t a_off, uint32_t b_off) {
 #pragma unroll
         for (int s = 0; s < 2; ++s)
 #pragma unroll
@@ -125,22 +130,25 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
       uint32_t it = 0;
       for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
         const uint32_t par = it & 1u;
-        mbar_wait(smem_u32(&bars.full_gy), par);
-        tc_fence_after();
-        dgrad(t_tmp1, kBwSmemGy, kBwSmemWb);
-        umma_commit(smem_u32(&bars.tmp1_ready));
-        mbar_wait(smem_u32(&bars.full_a2), par);
-        tc_fence_after();
-        wgrad(t_dwb, kBwSmemA2, kBwSmemGy, it == 0);
-        umma_commit(smem_u32(&bars.free_gy));
-        umma_commit(smem_u32(&bars.free_a2));
-        mbar_wait(smem_u32(&bars.gt_ready), par);
-        tc_fence_after();
-        dgrad(t_tmp2, kBwSmemGt, kBwSmemWa);
-        umma_commit(smem_u32(&bars.tmp2_ready));
+        // A1 of this tile landing implies that epilogue 2 of the previous tile is done with tmp2
         mbar_wait(smem_u32(&bars.full_a1), par);
         tc_fence_after();
-        wgrad(t_dwa, kBwSmemA1, kBwSmemGt, it == 0);
+        gemm_kk(t_tmp2, kBwSmemA1, kBwSmemWf);               // t = A1 Wa
+        umma_commit(smem_u32(&bars.t_ready));
+        mbar_wait(smem_u32(&bars.full_gy), par);
+        tc_fence_after();
+        gemm_kk(t_tmp1, kBwSmemGy, kBwSmemWb);               // g_a2 = g_y Wb^T
+        umma_commit(smem_u32(&bars.tmp1_ready));
+        mbar_wait(smem_u32(&bars.a2_ready), par);
+        tc_fence_after();
+        wgrad(t_dwb, kBwSmemA2, kBwSmemGy, it == 0);         // dWb += A2^T g_y
+        umma_commit(smem_u32(&bars.free_gy));
+        umma_commit(smem_u32(&bars.a2_free));
+        mbar_wait(smem_u32(&bars.gt_ready), par);
+        tc_fence_after();
+        gemm_kk(t_tmp2, kBwSmemGt, kBwSmemWa);               // g_a1 = g_t Wa^T
+        umma_commit(smem_u32(&bars.tmp2_ready));
+        wgrad(t_dwa, kBwSmemA1, kBwSmemGt, it == 0);         // dWa += A1^T g_t
         umma_commit(smem_u32(&bars.free_a1));
         umma_commit(smem_u32(&bars.gt_free));
       }
@@ -187,9 +195,7 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
     const uint32_t quad = warp & 3u;
     const uint32_t row = quad * 32u + lane;
     const uint32_t lane_off = (quad * 32u) << 16;
-    const bool leader = (e == 0 && lane == 0);
     uint32_t it = 0;
-    bool pending = false;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const uint32_t par = it & 1u;
       // ---- keep this half row of g_y in registers (needed again by epilogue 2), release the smem tile
@@ -199,9 +205,42 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
       for (int c = 0; c < 8; ++c)
         gy[c] = *reinterpret_cast<const uint4 *>(smem + kBwSmemGy + tile_chunk_off(row, half * 8 + c));
       mbar_arrive(smem_u32(&bars.free_gy));
+      // ---- epilogue 0: A2 = relu(A1 Wa + ba) -> bf16 operand tile; its sign mask stays in registers
+      uint32_t mask[2] = {0u, 0u};
+      mbar_wait(smem_u32(&bars.t_ready), par);
+      mbar_wait(smem_u32(&bars.a2_free), par ^ 1u);  // previous tile's wgrad-b is done with A2
+      tc_fence_after();
+      {
+        uint32_t r[64];
+        tmem_ld32(t_tmp2 + lane_off + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+        tmem_ld32(t_tmp2 + lane_off + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+        tmem_wait_ld();
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const float4 b0 = *reinterpret_cast<const float4 *>(s_ba + half * 64 + q * 8);
+          const float4 b1 = *reinterpret_cast<const float4 *>(s_ba + half * 64 + q * 8 + 4);
+          float v[8];
+          v[0] = __uint_as_float(r[q * 8 + 0]) + b0.x; v[1] = __uint_as_float(r[q * 8 + 1]) + b0.y;
+          v[2] = __uint_as_float(r[q * 8 + 2]) + b0.z; v[3] = __uint_as_float(r[q * 8 + 3]) + b0.w;
+          v[4] = __uint_as_float(r[q * 8 + 4]) + b1.x; v[5] = __uint_as_float(r[q * 8 + 5]) + b1.y;
+          v[6] = __uint_as_float(r[q * 8 + 6]) + b1.z; v[7] = __uint_as_float(r[q * 8 + 7]) + b1.w;
+          uint32_t ow[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            ow[i] = pack_bf16x2(fmaxf(v[2 * i], 0.f), fmaxf(v[2 * i + 1], 0.f));
+            // the mask of the BF16 value (what the forward stored and the old backward tested)
+            if (ow[i] & 0x0000ffffu) mask[q >> 2] |= 1u << ((q & 3) * 8 + 2 * i);
+            if (ow[i] & 0xffff0000u) mask[q >> 2] |= 1u << ((q & 3) * 8 + 2 * i + 1);
+          }
+          *reinterpret_cast<uint4 *>(smem + kBwSmemA2 + tile_chunk_off(row, half * 8 + q)) =
+              make_uint4(ow[0], ow[1], ow[2], ow[3]);
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(smem_u32(&bars.a2_ready));
       // ---- epilogue 1: g_t = g_a2 * [A2 > 0]
       mbar_wait(smem_u32(&bars.tmp1_ready), par);
-      mbar_wait(smem_u32(&bars.full_a2), par);
       mbar_wait(smem_u32(&bars.gt_free), par ^ 1u);  // previous tile's wgrad-a / bias sums are done with GT
       tc_fence_after();
       {
@@ -211,13 +250,12 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
         tmem_wait_ld();
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-          const uint4 m = *reinterpret_cast<const uint4 *>(smem + kBwSmemA2 + tile_chunk_off(row, half * 8 + q));
-          const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
+          const uint32_t m = mask[q >> 2] >> ((q & 3) * 8);
           uint32_t ow[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            ow[i] = pack_bf16x2(bf16_lo(mw[i]) > 0.f ? __uint_as_float(r[q * 8 + 2 * i]) : 0.f,
-                                bf16_hi(mw[i]) > 0.f ? __uint_as_float(r[q * 8 + 2 * i + 1]) : 0.f);
+            ow[i] = pack_bf16x2((m >> (2 * i)) & 1u ? __uint_as_float(r[q * 8 + 2 * i]) : 0.f,
+                                (m >> (2 * i + 1)) & 1u ? __uint_as_float(r[q * 8 + 2 * i + 1]) : 0.f);
           *reinterpret_cast<uint4 *>(smem + kBwSmemGt + tile_chunk_off(row, half * 8 + q)) =
               make_uint4(ow[0], ow[1], ow[2], ow[3]);
         }
@@ -225,21 +263,15 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(smem_u32(&bars.gt_ready));
-      mbar_arrive(smem_u32(&bars.free_a2));
-      // ---- epilogue 2: g_h = g_y + g_a1 * [A1 > 0]  -> staging tile -> TMA store
+      // ---- epilogue 2: g_h = g_y + g_a1 * [A1 > 0]  -> global (one full 128-byte line per thread)
       mbar_wait(smem_u32(&bars.tmp2_ready), par);
-      mbar_wait(smem_u32(&bars.full_a1), par);
       tc_fence_after();
-      if (pending) {  // the previous tile's store must have finished reading the staging tile
-        if (leader) bulk_wait_read0();
-        named_bar_sync(1, kBwdEpiThreads);
-        pending = false;
-      }
       {
         uint32_t r[64];
         tmem_ld32(t_tmp2 + lane_off + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
         tmem_ld32(t_tmp2 + lane_off + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
         tmem_wait_ld();
+        uint8_t *dst = gh_tiles + tile * (int64_t)CN_ACT_TILE_BYTES;
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
           const uint4 m = *reinterpret_cast<const uint4 *>(smem + kBwSmemA1 + tile_chunk_off(row, half * 8 + q));
@@ -251,19 +283,11 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
             ow[i] = pack_bf16x2(
                 bf16_lo(gw[i]) + (bf16_lo(mw[i]) > 0.f ? __uint_as_float(r[q * 8 + 2 * i]) : 0.f),
                 bf16_hi(gw[i]) + (bf16_hi(mw[i]) > 0.f ? __uint_as_float(r[q * 8 + 2 * i + 1]) : 0.f));
-          *reinterpret_cast<uint4 *>(smem + kBwSmemOut + tile_chunk_off(row, half * 8 + q)) =
-              make_uint4(ow[0], ow[1], ow[2], ow[3]);
+          *reinterpret_cast<uint4 *>(dst + tile_chunk_off(row, half * 8 + q)) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
         }
       }
       tc_fence_before();
       mbar_arrive(smem_u32(&bars.free_a1));
-      fence_proxy_async_smem();
-      named_bar_sync(1, kBwdEpiThreads);
-      if (leader) {
-        bulk_s2g(gh_tiles + tile * (int64_t)CN_ACT_TILE_BYTES, s_base + kBwSmemOut, CN_ACT_TILE_BYTES);
-        bulk_commit();
-      }
-      pending = true;
     }
     // ---- flush the weight gradients held in TMEM (each thread: its input unit, 64 output units)
     mbar_wait(smem_u32(&bars.all_done), 0);
@@ -283,7 +307,6 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
                      __uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3]));
       }
     }
-    if (leader) bulk_wait0();
   }
 
   tc_fence_before();
@@ -373,7 +396,7 @@ extern "C" int cn_mlp_block_bwd(const void *packed, int32_t blk, const void *act
   using namespace cn;
   CN_REQUIRE(packed && acts && gy_tiles && gh_tiles && grad, "cn_mlp_block_bwd: null pointer");
   CN_REQUIRE(blk >= 0 && blk < 6, "cn_mlp_block_bwd: blk %d", blk);
-  CN_REQUIRE(act_stride_tiles >= 2 && act_index >= 0 && act_index + 2 <= act_stride_tiles,
+  CN_REQUIRE(act_stride_tiles >= 1 && act_index >= 0 && act_index < act_stride_tiles,
              "cn_mlp_block_bwd: act_stride_tiles=%d act_index=%d", act_stride_tiles, act_index);
   CN_REQUIRE(n_tiles >= 0, "cn_mlp_block_bwd: n_tiles %lld", (long long)n_tiles);
   CN_REQUIRE((((uintptr_t)packed | (uintptr_t)acts | (uintptr_t)gy_tiles | (uintptr_t)gh_tiles) & 127) == 0 &&
@@ -389,7 +412,8 @@ extern "C" int cn_mlp_block_bwd(const void *packed, int32_t blk, const void *act
   const uint8_t *pk = (const uint8_t *)packed;
   const unsigned grid = (unsigned)(n_tiles < kNumSMs ? n_tiles : kNumSMs);
   mlp_block_bwd_kernel<<<grid, kBwdThreads, kBwdSmemBytes, (cudaStream_t)stream>>>(
-      pk + pack_bwd_block(blk, 0), pk + pack_bwd_block(blk, 1),
+      pk + pack_bwd_block(blk, 0), pk + pack_bwd_block(blk, 1), pk + pack_fwd_block(blk, 0),
+      reinterpret_cast<const float *>(pk + kPackTables) + (blk < 3 ? kTabFeature : kTabFusion) + (2 * (blk % 3) + 1) * 128,
       (const uint8_t *)acts + (int64_t)act_index * CN_ACT_TILE_BYTES, (int64_t)act_stride_tiles * CN_ACT_TILE_BYTES,
       n_tiles, (const uint8_t *)gy_tiles, (uint8_t *)gh_tiles, grad + param_block_w(blk, 0),
       grad + param_block_b(blk, 0), grad + param_block_w(blk, 1), grad + param_block_b(blk, 1));

@@ -89,7 +89,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
   float *tab = reinterpret_cast<float *>(smem + L::kTab);
-  constexpr int kActsPerTile = kFusion ? 7 : 6;
+  constexpr int kActsPerTile = kFusion ? 4 : 3;  // relu(h) of every block (+ relu(e)); relu(t) is recomputed by the backward
   constexpr int kBlk0 = kFusion ? 3 : 0;
   const bool staged = kFusion && nv <= kMaxStageViews;  // view tiles go through the ring (else: global loads)
   const uint32_t view_slots = staged ? 2u * (uint32_t)nv : 0u;
@@ -360,7 +360,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
           // E_a: relu(h + cumulative bias) -> operand of the block's first Dense
           acquire();
           epi_tmem_to_act<true>(t_h, tab + (2 * blk) * 128, act, row, half);
-          publish(my_acts ? my_acts + (2 * blk) * CN_ACT_TILE_BYTES : nullptr, true);
+          publish(my_acts ? my_acts + blk * CN_ACT_TILE_BYTES : nullptr, true);
         }
         // E_b: relu(t + ba) -> operand of the block's second Dense
         mbar_wait(smem_u32(&bars.tmp_ready[t]), n_tmp & 1u);
@@ -368,7 +368,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         tc_fence_after();
         acquire();
         epi_tmem_to_act<true>(t_tmp, tab + (2 * blk + 1) * 128, act, row, half);
-        publish(my_acts ? my_acts + (2 * blk + 1) * CN_ACT_TILE_BYTES : nullptr, true);
+        publish(nullptr, true);
         mbar_wait(smem_u32(&bars.h_ready[t]), n_h & 1u);
         ++n_h;
         tc_fence_after();
@@ -414,7 +414,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         o.x = 1.f / (1.f + expf(-ya));
         o.y = half ? (yb > 20.f ? yb : log1pf(expf(yb))) : 1.f / (1.f + expf(-yb));
         reinterpret_cast<float2 *>(rgbs)[(tile * 128 + row) * 2 + half] = o;
-        publish(my_acts ? my_acts + 6 * CN_ACT_TILE_BYTES : nullptr, false);
+        publish(my_acts ? my_acts + 3 * CN_ACT_TILE_BYTES : nullptr, false);
       }
       ring_base += 12u + view_slots * ((2 * p + 1 < n_tiles) ? 2u : 1u);
     }

@@ -2,7 +2,8 @@
 //   cn_mlp_l0_dgrad : dX = g0 . W0^T   per 128-row tile, written as a bf16 MLP-input tile image
 //                     (same column order as X) for cn_project_gather_bwd
 //   cn_mlp_l0_wgrad : dW0 += X^T . g0  over all tiles; the three 128 x 128 accumulators
-//                     (384 input columns) stay in TMEM for the whole kernel
+//                     (384 input columns) stay in TMEM for the whole kernel; db0 = column sums of g0
+//                     by the otherwise idle epilogue warps, straight from the shared-memory operand
 #include "common.cuh"
 #include "mlp_layout.cuh"
 
@@ -161,7 +162,7 @@ struct WgBars {
 
 __global__ void __launch_bounds__(kWgThreads, 1)
 mlp_l0_wgrad_kernel(const uint8_t *__restrict__ x_tiles, const uint8_t *__restrict__ g0_tiles, int64_t n_tiles,
-                    float *__restrict__ g_w0) {
+                    float *__restrict__ g_w0, float *__restrict__ g_b0) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) WgBars bars;
   __shared__ uint32_t tmem_slot;
@@ -174,7 +175,7 @@ mlp_l0_wgrad_kernel(const uint8_t *__restrict__ x_tiles, const uint8_t *__restri
   if (threadIdx.x == 0) {
     for (int i = 0; i < kPairs; ++i) {
       mbar_init(smem_u32(&bars.full[i]), 1);
-      mbar_init(smem_u32(&bars.empty[i]), 1);
+      mbar_init(smem_u32(&bars.empty[i]), 1 + 128);  // tcgen05.commit + the 128 bias-sum threads
     }
     mbar_init(smem_u32(&bars.all_done), 1);
     fence_barrier_init();
@@ -235,6 +236,35 @@ mlp_l0_wgrad_kernel(const uint8_t *__restrict__ x_tiles, const uint8_t *__restri
     const uint32_t quad = warp & 3u;
     const uint32_t row = quad * 32u + lane;
     const uint32_t lane_off = (quad * 32u) << 16;
+    // ---- db0 = column sums of g0, read from the shared-memory operand while the tensor pipe works:
+    // warp q sums rows [32q, 32q+32), lane l the columns 2l, 2l+1 of both slabs
+    {
+      float b00 = 0.f, b01 = 0.f, b10 = 0.f, b11 = 0.f;
+      const uint32_t chunk = lane >> 2, within = (lane & 3u) * 4u;
+      uint32_t cc = 0;
+      for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (int p = 0; p < 4; ++p, ++cc) {
+          const uint32_t ps = cc % kPairs;
+          mbar_wait(smem_u32(&bars.full[ps]), (cc / kPairs) & 1u);
+          if (p == 0) {
+            const uint8_t *g = smem + ps * CN_ACT_TILE_BYTES + within;
+#pragma unroll 8
+            for (uint32_t r = quad * 32u; r < quad * 32u + 32u; ++r) {
+              const uint32_t off = r * 128u + ((chunk ^ (r & 7u)) << 4);
+              const uint32_t v0 = *reinterpret_cast<const uint32_t *>(g + off);
+              const uint32_t v1 = *reinterpret_cast<const uint32_t *>(g + CN_SLAB_BYTES + off);
+              b00 += bf16_lo(v0); b01 += bf16_hi(v0);
+              b10 += bf16_lo(v1); b11 += bf16_hi(v1);
+            }
+          }
+          mbar_arrive(smem_u32(&bars.empty[ps]));
+        }
+      }
+      atomicAdd(&g_b0[2 * lane], b00);
+      atomicAdd(&g_b0[2 * lane + 1], b01);
+      atomicAdd(&g_b0[64 + 2 * lane], b10);
+      atomicAdd(&g_b0[64 + 2 * lane + 1], b11);
+    }
     mbar_wait(smem_u32(&bars.all_done), 0);
     tc_fence_after();
 #pragma unroll 1
@@ -258,18 +288,6 @@ mlp_l0_wgrad_kernel(const uint8_t *__restrict__ x_tiles, const uint8_t *__restri
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem, 512);
-}
-
-// column sums of bf16 activation tiles (db0 = sum over rows of g0)
-__global__ void __launch_bounds__(128)
-tile_colsum_kernel(const uint8_t *__restrict__ tiles, int64_t n_tiles, float *__restrict__ out) {
-  const int col = threadIdx.x;
-  float acc = 0.f;
-  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const uint8_t *t = tiles + tile * (int64_t)CN_ACT_TILE_BYTES;
-    for (int r = 0; r < 128; ++r) acc += __bfloat162float(*reinterpret_cast<const __nv_bfloat16 *>(t + tile_off(r, col)));
-  }
-  atomicAdd(&out[col], acc);
 }
 
 }  // namespace cn
@@ -308,10 +326,6 @@ extern "C" int cn_mlp_l0_wgrad(const void *x_tiles, const void *g0_tiles, int64_
   }
   const unsigned grid = (unsigned)(n_tiles < kNumSMs ? n_tiles : kNumSMs);
   mlp_l0_wgrad_kernel<<<grid, kWgThreads, kWgSmemBytes, (cudaStream_t)stream>>>(
-      (const uint8_t *)x_tiles, (const uint8_t *)g0_tiles, n_tiles, grad + kParamW0);
-  int rc = check_launch("cn_mlp_l0_wgrad");
-  if (rc) return rc;
-  const unsigned g2 = (unsigned)(n_tiles < 8 * kNumSMs ? n_tiles : 8 * kNumSMs);
-  tile_colsum_kernel<<<g2, 128, 0, (cudaStream_t)stream>>>((const uint8_t *)g0_tiles, n_tiles, grad + kParamB0);
-  return check_launch("cn_mlp_l0_wgrad(colsum)");
+      (const uint8_t *)x_tiles, (const uint8_t *)g0_tiles, n_tiles, grad + kParamW0, grad + kParamB0);
+  return check_launch("cn_mlp_l0_wgrad");
 }
