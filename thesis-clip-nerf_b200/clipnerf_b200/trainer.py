@@ -80,3 +80,83 @@ class RenderTrainer:
         self.allreduce_gradients()
         self.apply_gradients()
         return loss
+
+
+class DevicePrefetcher:
+    """Host batches (pinned tensors) -> device batches, one batch ahead, on a dedicated copy stream.
+
+    The role Keras' ``fit`` gives its ``Sequence`` enqueuer thread in the reference
+    (``src/train_nerf.py:132`` -> ``MVNeRFDataGenerator.__getitem__``): the host->device copy of
+    batch i+1 runs on the copy engine while the kernels of batch i run.  Every batch is copied exactly
+    once; two device buffer sets are recycled, guarded by events (a set is overwritten only after the
+    step that read it has finished)."""
+
+    def __init__(self, batches, device, depth: int = 2):
+        self.it = iter(batches)
+        self.device = device
+        self.copy_stream = torch.cuda.Stream(device)
+        self.slots = [None] * depth            # device tensors of each buffer set
+        self.free = [None] * depth             # event: the consumer is done with the set
+        self.k = 0
+        self.next = None
+        self._upload()
+
+    def _upload(self):
+        try:
+            host = next(self.it)
+        except StopIteration:
+            self.next = None
+            return
+        k = self.k % len(self.slots)
+        self.k += 1
+        with torch.cuda.stream(self.copy_stream):
+            if self.free[k] is not None:
+                self.copy_stream.wait_event(self.free[k])
+            if self.slots[k] is None:
+                self.slots[k] = [torch.empty_like(t, device=self.device) for t in host]
+            for d, h in zip(self.slots[k], host):
+                d.copy_(h, non_blocking=True)
+            ready = torch.cuda.Event()
+            ready.record(self.copy_stream)
+        self.next = (k, ready)
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        if self.next is None:
+            raise StopIteration
+        k, ready = self.next
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(ready)
+        if self.free[k] is None:
+            self.free[k] = torch.cuda.Event()
+        batch = self.slots[k]
+        self._upload()                          # next batch goes out while this one is consumed
+        return batch, self.free[k]
+
+
+def fit_host_batches(trainer: RenderTrainer, batches, features, near, far):
+    """Training loop over HOST batches ``(ray_o, ray_d, images, K, E^-1, target, u_strat, u_pdf)`` in pinned
+    memory: prefetched uploads, one ``train_step`` per batch, the loss of every step copied back to the host
+    asynchronously (read one step late, so the host never stalls the launch queue).  Returns the losses."""
+    dev = trainer.params.device
+    cur = torch.cuda.current_stream(dev)
+    losses, pending = [], []
+    for batch, done in DevicePrefetcher(batches, dev):
+        features.grad = None
+        loss = trainer.train_step(batch[:5], features, batch[5], batch[6], batch[7], near, far)
+        done.record(cur)
+        host_loss = torch.empty((), dtype=torch.float32, pin_memory=True)
+        host_loss.copy_(loss, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        pending.append((host_loss, ev))
+        if len(pending) > 1:
+            h, e = pending.pop(0)
+            e.synchronize()
+            losses.append(float(h))
+    for h, e in pending:
+        e.synchronize()
+        losses.append(float(h))
+    return losses

@@ -2,54 +2,85 @@
 // tcgen05 / TMEM:      y = h + relu(relu(h) Wa + ba) Wb + bb
 //   saved by the forward: A1 = relu(h) only (bf16 tile image).  The hidden activation is RECOMPUTED
 //   here -- one extra GEMM per tile buys a third of the kernel's HBM traffic, which is what bounds it:
-//   A2   = relu(A1 Wa + ba)    (forward GEMM, same bf16 operands and K order as the forward: bit-identical)
-//   g_a2 = g_y Wb^T            (dgrad 1, K-major operands)
-//   dWb += A2^T g_y            (wgrad,  MN-major operands: the SAME smem tiles read transposed)
-//   g_t  = g_a2 * [A2 > 0]     (epilogue 1)  -> bf16 tile in smem,  dba += colsum(g_t)   (bias warps)
-//   g_a1 = g_t Wa^T            (dgrad 2)
-//   dWa += A1^T g_t            (wgrad)
-//   g_h  = g_y + g_a1 * [A1>0] (epilogue 2)  -> global,             dbb += colsum(g_y)   (bias warps)
-// The three weight images stay resident in shared memory for the whole kernel and the two weight
-// gradients stay resident in TMEM (2 x 128 columns) across all tiles of the CTA; they are
-// flushed once with vector red.global.add at the end.
-//   warp 0: TMA producer (g_y, A1 tiles), warp 1: MMA issuer, warps 2-9: epilogue (4 TMEM lane
-//   quadrants x 2 column halves), warps 10-11: bias gradients (column sums read from the smem tiles).
+//   T  : t    = A1 Wa             (acc0; B = the dgrad image of Wa read MN-major: bit-identical to the forward)
+//   E0 : A2   = relu(t + ba)      -> bf16 operand tile in smem
+//   G2 : g_a2 = g_y Wb^T          (acc1, K-major operands)          issued while E0 runs
+//   WB : dWb += A2^T g_y          (MN-major views of the same smem tiles)
+//   E1 : g_t  = g_a2 * [A2 > 0]   -> overwrites A2 in place (same thread, same bytes)
+//   G1 : g_a1 = g_t Wa^T          (acc1)
+//   WA : dWa += A1^T g_t
+//   E2 : g_h  = g_y + g_a1 * [A1 > 0]  -> overwrites g_y in place, TMA store to global
+//   the next tile's T is issued behind WB so that its E0 never waits for the tensor pipe.
+// Cost model (tools/ubench_tc.cu, B200): MMA 128x128x16 = 64 cycles (512 per GEMM); a TMEM -> bf16 ->
+// st.shared epilogue is ISSUE bound (~1000 cycles per tile with select/add/max per element and 8 warps),
+// so every epilogue here is 3 packed instructions per element PAIR (cvt.bf16x2 / set.bf16x2 / mul|fma.bf16x2)
+// on 16 warps (~400 cycles).  With that the kernel is bound by its 96 KiB of HBM traffic per tile.
+// Shared memory: Wa, Wb (dgrad images, resident) + 2 x A1 + 2 x g_y (double buffered TMA) + 1 x A2|g_t.
+// TMEM: acc0, acc1, and the two weight gradients, resident across all tiles of the CTA and flushed once
+// with vector red.global.add.
+//   warp 0: TMA producer (+ g_h stores), warp 1: MMA issuer, warps 2-17: epilogue (4 TMEM lane quadrants x
+//   4 column quarters), warps 18-19: bias gradients (column sums read from the smem tiles).
 #include "common.cuh"
 #include "mlp_layout.cuh"
 
 namespace cn {
 
-constexpr int kBwdThreads = 384;  // warp 0 producer, 1 MMA, 2-9 epilogue (4 lane quadrants x 2 column halves), 10-11 bias sums
-constexpr int kBwdEpiThreads = 256;
+constexpr int kBwdEpiWarps = 16;
+constexpr int kBwdEpiThreads = kBwdEpiWarps * 32;
+constexpr int kBwdThreads = 64 + kBwdEpiThreads + 64;
 constexpr uint32_t kBwSmemWb = 0;                       // Wb, dgrad image
-constexpr uint32_t kBwSmemWa = 1 * CN_ACT_TILE_BYTES;   // Wa, dgrad image
-constexpr uint32_t kBwSmemWf = 2 * CN_ACT_TILE_BYTES;   // Wa, forward image (recompute of the hidden activation)
-constexpr uint32_t kBwSmemGy = 3 * CN_ACT_TILE_BYTES;
-constexpr uint32_t kBwSmemA1 = 4 * CN_ACT_TILE_BYTES;
-constexpr uint32_t kBwSmemA2 = 5 * CN_ACT_TILE_BYTES;   // written by epilogue 0
-constexpr uint32_t kBwSmemGt = 6 * CN_ACT_TILE_BYTES;   // written by epilogue 1
+constexpr uint32_t kBwSmemWa = 1 * CN_ACT_TILE_BYTES;   // Wa, dgrad image (also the recompute's MN-major B)
+constexpr uint32_t kBwSmemA1 = 2 * CN_ACT_TILE_BYTES;   // 2 buffers
+constexpr uint32_t kBwSmemGy = 4 * CN_ACT_TILE_BYTES;   // 2 buffers (g_y in, g_h out)
+constexpr uint32_t kBwSmemA2 = 6 * CN_ACT_TILE_BYTES;   // A2, then g_t
 constexpr uint32_t kBwdSmemBytes = 7 * CN_ACT_TILE_BYTES + 1024;
 
 struct BwdBars {
   uint64_t w_full;
-  uint64_t full_gy, full_a1;
-  uint64_t free_gy;                    // 256 epilogue + 64 bias-sum arrivals + 1 tcgen05.commit
-  uint64_t free_a1;                    // 256 epilogue arrivals + 1 tcgen05.commit
-  uint64_t t_ready;                    // commit: A1 Wa is in TMEM
-  uint64_t a2_ready;                   // 256 epilogue arrivals: relu(t) is in shared memory
-  uint64_t a2_free;                    // commit after wgrad-b
-  uint64_t gt_ready;                   // 256 epilogue arrivals
-  uint64_t gt_free;                    // commit after wgrad-a + 64 bias-sum arrivals
-  uint64_t tmp1_ready, tmp2_ready;     // commits
-  uint64_t all_done;                   // commit after the last tile
+  uint64_t full_a1[2], full_gy[2];     // TMA landed
+  uint64_t free_a1[2];                 // 512 E2 arrivals + commit behind WA
+  uint64_t gy_staged[2];               // 512 E2 arrivals: g_h is in the g_y buffer
+  uint64_t gy_bias_done[2];            // 64 bias-sum arrivals: g_y has been summed
+  uint64_t t_ready, g2wb_done, g1_ready;  // commits
+  uint64_t a2_ready, gt_ready;         // 512 epilogue arrivals each
+  uint64_t a2buf_free;                 // commit behind WA + 64 bias-sum arrivals
+  uint64_t acc1_free;                  // 512 E2 arrivals
+  uint64_t all_done;
 };
+
+__device__ __forceinline__ uint32_t cvt_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ uint32_t cvt_relu_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+// per half: 1.0 where a > 0 else 0.0
+__device__ __forceinline__ uint32_t gt0_bf16x2(uint32_t a) {
+  uint32_t r;
+  asm("set.gt.bf16x2.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(0u));
+  return r;
+}
+__device__ __forceinline__ uint32_t mul_bf16x2(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t fma_bf16x2(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
 
 __global__ void __launch_bounds__(kBwdThreads, 1)
 mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restrict__ w_b_img,
-                     const uint8_t *__restrict__ w_a_fwd_img, const float *__restrict__ bias_a,
-                     const uint8_t *__restrict__ acts, int64_t act_stride_bytes, int64_t n_tiles,
-                     const uint8_t *__restrict__ gy_tiles, uint8_t *__restrict__ gh_tiles, float *__restrict__ g_wa,
-                     float *__restrict__ g_ba, float *__restrict__ g_wb, float *__restrict__ g_bb) {
+                     const float *__restrict__ bias_a, const uint8_t *__restrict__ acts, int64_t act_stride_bytes,
+                     int64_t n_tiles, const uint8_t *__restrict__ gy_tiles, uint8_t *__restrict__ gh_tiles,
+                     float *__restrict__ g_wa, float *__restrict__ g_ba, float *__restrict__ g_wb,
+                     float *__restrict__ g_bb) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) BwdBars bars;
   __shared__ uint32_t tmem_slot;
@@ -62,17 +93,20 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
   if (threadIdx.x < 128) s_ba[threadIdx.x] = bias_a[threadIdx.x];
   if (threadIdx.x == 0) {
     mbar_init(smem_u32(&bars.w_full), 1);
-    mbar_init(smem_u32(&bars.full_gy), 1);
-    mbar_init(smem_u32(&bars.full_a1), 1);
-    mbar_init(smem_u32(&bars.free_gy), kBwdEpiThreads + 64 + 1);
-    mbar_init(smem_u32(&bars.free_a1), kBwdEpiThreads + 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(smem_u32(&bars.full_a1[b]), 1);
+      mbar_init(smem_u32(&bars.full_gy[b]), 1);
+      mbar_init(smem_u32(&bars.free_a1[b]), kBwdEpiThreads + 1);
+      mbar_init(smem_u32(&bars.gy_staged[b]), kBwdEpiThreads);
+      mbar_init(smem_u32(&bars.gy_bias_done[b]), 64);
+    }
     mbar_init(smem_u32(&bars.t_ready), 1);
+    mbar_init(smem_u32(&bars.g2wb_done), 1);
+    mbar_init(smem_u32(&bars.g1_ready), 1);
     mbar_init(smem_u32(&bars.a2_ready), kBwdEpiThreads);
-    mbar_init(smem_u32(&bars.a2_free), 1);
     mbar_init(smem_u32(&bars.gt_ready), kBwdEpiThreads);
-    mbar_init(smem_u32(&bars.gt_free), 64 + 1);
-    mbar_init(smem_u32(&bars.tmp1_ready), 1);
-    mbar_init(smem_u32(&bars.tmp2_ready), 1);
+    mbar_init(smem_u32(&bars.a2buf_free), 64 + 1);
+    mbar_init(smem_u32(&bars.acc1_free), kBwdEpiThreads);
     mbar_init(smem_u32(&bars.all_done), 1);
     fence_barrier_init();
   }
@@ -84,31 +118,55 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = tmem_slot;
-  const uint32_t t_tmp1 = tmem, t_tmp2 = tmem + 128, t_dwa = tmem + 256, t_dwb = tmem + 384;
+  const uint32_t t_acc0 = tmem, t_acc1 = tmem + 128, t_dwa = tmem + 256, t_dwb = tmem + 384;
+  const int64_t n_mine = n_tiles > blockIdx.x ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
 
   if (warp == 0) {
-    // =========================== TMA producer ===========================
+    // =========================== TMA producer + g_h stores ===========================
     if (lane == 0) {
-      mbar_expect_tx(smem_u32(&bars.w_full), 3 * CN_ACT_TILE_BYTES);
+      mbar_expect_tx(smem_u32(&bars.w_full), 2 * CN_ACT_TILE_BYTES);
       bulk_g2s(s_base + kBwSmemWb, w_b_img, CN_ACT_TILE_BYTES, smem_u32(&bars.w_full));
       bulk_g2s(s_base + kBwSmemWa, w_a_img, CN_ACT_TILE_BYTES, smem_u32(&bars.w_full));
-      bulk_g2s(s_base + kBwSmemWf, w_a_fwd_img, CN_ACT_TILE_BYTES, smem_u32(&bars.w_full));
-      uint32_t it = 0;
-      for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-        const uint32_t par = (it & 1u) ^ 1u;
-        mbar_wait(smem_u32(&bars.free_a1), par);
-        mbar_expect_tx(smem_u32(&bars.full_a1), CN_ACT_TILE_BYTES);
-        bulk_g2s(s_base + kBwSmemA1, acts + tile * act_stride_bytes, CN_ACT_TILE_BYTES, smem_u32(&bars.full_a1));
-        mbar_wait(smem_u32(&bars.free_gy), par);
-        mbar_expect_tx(smem_u32(&bars.full_gy), CN_ACT_TILE_BYTES);
-        bulk_g2s(s_base + kBwSmemGy, gy_tiles + tile * (int64_t)CN_ACT_TILE_BYTES, CN_ACT_TILE_BYTES,
-                 smem_u32(&bars.full_gy));
+      auto load_a1 = [&](int64_t it) {
+        const int64_t tile = blockIdx.x + it * gridDim.x;
+        const uint32_t b = (uint32_t)it & 1u;
+        mbar_expect_tx(smem_u32(&bars.full_a1[b]), CN_ACT_TILE_BYTES);
+        bulk_g2s(s_base + kBwSmemA1 + b * CN_ACT_TILE_BYTES, acts + tile * act_stride_bytes, CN_ACT_TILE_BYTES,
+                 smem_u32(&bars.full_a1[b]));
+      };
+      auto load_gy = [&](int64_t it) {
+        const int64_t tile = blockIdx.x + it * gridDim.x;
+        const uint32_t b = (uint32_t)it & 1u;
+        mbar_expect_tx(smem_u32(&bars.full_gy[b]), CN_ACT_TILE_BYTES);
+        bulk_g2s(s_base + kBwSmemGy + b * CN_ACT_TILE_BYTES, gy_tiles + tile * (int64_t)CN_ACT_TILE_BYTES,
+                 CN_ACT_TILE_BYTES, smem_u32(&bars.full_gy[b]));
+      };
+      for (int64_t it = 0; it < 2 && it < n_mine; ++it) {
+        load_a1(it);
+        load_gy(it);
       }
+      for (int64_t it = 0; it < n_mine; ++it) {
+        const int64_t tile = blockIdx.x + it * gridDim.x;
+        const uint32_t b = (uint32_t)it & 1u, ph2 = ((uint32_t)it >> 1) & 1u;
+        // E2 of this tile has replaced g_y by g_h in place: stream it out, then refill the buffer
+        mbar_wait(smem_u32(&bars.gy_staged[b]), ph2);
+        bulk_s2g(gh_tiles + tile * (int64_t)CN_ACT_TILE_BYTES, s_base + kBwSmemGy + b * CN_ACT_TILE_BYTES,
+                 CN_ACT_TILE_BYTES);
+        bulk_commit();
+        if (it + 2 < n_mine) {
+          bulk_wait_read0();
+          load_gy(it + 2);
+          mbar_wait(smem_u32(&bars.free_a1[b]), ph2);
+          load_a1(it + 2);
+        }
+      }
+      bulk_wait0();
     }
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
     if (lane == 0) {
-      constexpr uint32_t idesc_kk = umma_idesc(128, 128, 0, 0);  // forward / dgrad: both operands K-major
+      constexpr uint32_t idesc_kk = umma_idesc(128, 128, 0, 0);  // dgrad: both operands K-major
+      constexpr uint32_t idesc_kn = umma_idesc(128, 128, 0, 1);  // recompute: A K-major, B MN-major
       constexpr uint32_t idesc_mn = umma_idesc(128, 128, 1, 1);  // wgrad: both operands MN-major
       auto gemm_kk = [&](uint32_t d_tmem, uint32_t a_off, uint32_t b_off) {
 #pragma unroll
@@ -119,6 +177,13 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
                      umma_desc(s_base + b_off + s * CN_SLAB_BYTES + j * kKmajKstep, kKmajLbo, kSboBytes), idesc_kk,
                      (s | j) ? 1u : 0u);
       };
+      // t = A1 Wa with Wa stored [in][out] (K rows, N contiguous): K step 16 = 16 rows of the weight image
+      auto gemm_t = [&](uint32_t a_off) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          umma_f16(t_acc0, umma_desc(s_base + a_off + (j >> 2) * CN_SLAB_BYTES + (j & 3) * kKmajKstep, kKmajLbo, kSboBytes),
+                   umma_desc(s_base + kBwSmemWa + j * kMNmajKstep, kMNmajLbo, kSboBytes), idesc_kn, j ? 1u : 0u);
+      };
       auto wgrad = [&](uint32_t d_tmem, uint32_t a_off, uint32_t b_off, bool first) {
 #pragma unroll
         for (int j = 0; j < 8; ++j)  // 8 steps of 16 rows
@@ -127,61 +192,75 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
                    (!first || j) ? 1u : 0u);
       };
       mbar_wait(smem_u32(&bars.w_full), 0);
-      uint32_t it = 0;
-      for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-        const uint32_t par = it & 1u;
-        // A1 of this tile landing implies that epilogue 2 of the previous tile is done with tmp2
-        mbar_wait(smem_u32(&bars.full_a1), par);
+      if (n_mine > 0) {
+        mbar_wait(smem_u32(&bars.full_a1[0]), 0);
         tc_fence_after();
-        gemm_kk(t_tmp2, kBwSmemA1, kBwSmemWf);               // t = A1 Wa
+        gemm_t(kBwSmemA1);
         umma_commit(smem_u32(&bars.t_ready));
-        mbar_wait(smem_u32(&bars.full_gy), par);
+      }
+      for (int64_t it = 0; it < n_mine; ++it) {
+        const uint32_t b = (uint32_t)it & 1u, ph2 = ((uint32_t)it >> 1) & 1u, par = (uint32_t)it & 1u;
+        const uint32_t a1 = kBwSmemA1 + b * CN_ACT_TILE_BYTES, gy = kBwSmemGy + b * CN_ACT_TILE_BYTES;
+        const bool has_next = it + 1 < n_mine;
+        const uint32_t nb = b ^ 1u, nph2 = ((uint32_t)(it + 1) >> 1) & 1u;
+        mbar_wait(smem_u32(&bars.full_gy[b]), ph2);
+        mbar_wait(smem_u32(&bars.acc1_free), par ^ 1u);          // E2 of the previous tile has drained acc1
         tc_fence_after();
-        gemm_kk(t_tmp1, kBwSmemGy, kBwSmemWb);               // g_a2 = g_y Wb^T
-        umma_commit(smem_u32(&bars.tmp1_ready));
-        mbar_wait(smem_u32(&bars.a2_ready), par);
+        gemm_kk(t_acc1, gy, kBwSmemWb);                           // G2: g_a2 = g_y Wb^T
+        mbar_wait(smem_u32(&bars.a2_ready), par);                 // (also: E0 has drained acc0)
         tc_fence_after();
-        wgrad(t_dwb, kBwSmemA2, kBwSmemGy, it == 0);         // dWb += A2^T g_y
-        umma_commit(smem_u32(&bars.free_gy));
-        umma_commit(smem_u32(&bars.a2_free));
+        wgrad(t_dwb, kBwSmemA2, gy, it == 0);                     // WB: dWb += A2^T g_y
+        umma_commit(smem_u32(&bars.g2wb_done));
+        bool next_issued = false;
+        if (has_next && mbar_try_wait(smem_u32(&bars.full_a1[nb]), nph2)) {
+          tc_fence_after();
+          gemm_t(kBwSmemA1 + nb * CN_ACT_TILE_BYTES);             // T of the next tile, behind WB
+          umma_commit(smem_u32(&bars.t_ready));
+          next_issued = true;
+        }
         mbar_wait(smem_u32(&bars.gt_ready), par);
         tc_fence_after();
-        gemm_kk(t_tmp2, kBwSmemGt, kBwSmemWa);               // g_a1 = g_t Wa^T
-        umma_commit(smem_u32(&bars.tmp2_ready));
-        wgrad(t_dwa, kBwSmemA1, kBwSmemGt, it == 0);         // dWa += A1^T g_t
-        umma_commit(smem_u32(&bars.free_a1));
-        umma_commit(smem_u32(&bars.gt_free));
+        gemm_kk(t_acc1, kBwSmemA2, kBwSmemWa);                    // G1: g_a1 = g_t Wa^T
+        umma_commit(smem_u32(&bars.g1_ready));
+        wgrad(t_dwa, a1, kBwSmemA2, it == 0);                     // WA: dWa += A1^T g_t
+        umma_commit(smem_u32(&bars.free_a1[b]));
+        umma_commit(smem_u32(&bars.a2buf_free));
+        if (has_next && !next_issued) {
+          mbar_wait(smem_u32(&bars.full_a1[nb]), nph2);
+          tc_fence_after();
+          gemm_t(kBwSmemA1 + nb * CN_ACT_TILE_BYTES);
+          umma_commit(smem_u32(&bars.t_ready));
+        }
       }
       umma_commit(smem_u32(&bars.all_done));
     }
-  } else if (warp >= 10) {
+  } else if (warp >= 2 + kBwdEpiWarps) {
     // =========================== bias gradients ===========================
     // column sums of the g_y and g_t tiles straight from shared memory; each lane owns two columns of
     // slab `sl` for the whole kernel (two fp32 accumulators per tile kind), one flush at the end
-    const uint32_t sl = warp - 10;
+    const uint32_t sl = warp - (2 + kBwdEpiWarps);
     const uint32_t chunk = lane >> 2, within = (lane & 3u) * 4u;
     float bb0 = 0.f, bb1 = 0.f, ba0 = 0.f, ba1 = 0.f;
-    uint32_t it = 0;
-    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-      const uint32_t par = it & 1u;
-      mbar_wait(smem_u32(&bars.full_gy), par);
-      const uint8_t *gy = smem + kBwSmemGy + sl * CN_SLAB_BYTES + within;
+    for (int64_t it = 0; it < n_mine; ++it) {
+      const uint32_t b = (uint32_t)it & 1u, ph2 = ((uint32_t)it >> 1) & 1u, par = (uint32_t)it & 1u;
+      mbar_wait(smem_u32(&bars.full_gy[b]), ph2);
+      const uint8_t *gy = smem + kBwSmemGy + b * CN_ACT_TILE_BYTES + sl * CN_SLAB_BYTES + within;
 #pragma unroll 8
       for (uint32_t r = 0; r < 128; ++r) {
         const uint32_t v = *reinterpret_cast<const uint32_t *>(gy + r * 128u + ((chunk ^ (r & 7u)) << 4));
         bb0 += bf16_lo(v);
         bb1 += bf16_hi(v);
       }
-      mbar_arrive(smem_u32(&bars.free_gy));
+      mbar_arrive(smem_u32(&bars.gy_bias_done[b]));
       mbar_wait(smem_u32(&bars.gt_ready), par);
-      const uint8_t *gt = smem + kBwSmemGt + sl * CN_SLAB_BYTES + within;
+      const uint8_t *gt = smem + kBwSmemA2 + sl * CN_SLAB_BYTES + within;
 #pragma unroll 8
       for (uint32_t r = 0; r < 128; ++r) {
         const uint32_t v = *reinterpret_cast<const uint32_t *>(gt + r * 128u + ((chunk ^ (r & 7u)) << 4));
         ba0 += bf16_lo(v);
         ba1 += bf16_hi(v);
       }
-      mbar_arrive(smem_u32(&bars.gt_free));
+      mbar_arrive(smem_u32(&bars.a2buf_free));
     }
     const int col = sl * 64 + lane * 2;
     atomicAdd(&g_bb[col], bb0);
@@ -189,121 +268,111 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
     atomicAdd(&g_ba[col], ba0);
     atomicAdd(&g_ba[col + 1], ba1);
   } else {
-    // =========================== epilogue: 8 warps, (row, column half) per thread ===========================
+    // =========================== epilogue: 16 warps, (row, 32-column quarter) per thread ===========================
     const uint32_t e = warp - 2;
-    const uint32_t half = e >> 2;
-    const uint32_t quad = warp & 3u;
+    const uint32_t cq = e >> 2;                      // column quarter [32 cq, 32 cq + 32)
+    const uint32_t quad = warp & 3u;                 // TMEM lane quadrant this warp may access
     const uint32_t row = quad * 32u + lane;
     const uint32_t lane_off = (quad * 32u) << 16;
-    uint32_t it = 0;
-    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-      const uint32_t par = it & 1u;
-      // ---- keep this half row of g_y in registers (needed again by epilogue 2), release the smem tile
-      mbar_wait(smem_u32(&bars.full_gy), par);
-      uint4 gy[8];
+    uint32_t choff[4];                               // byte offsets of this thread's four 16-byte chunks in a tile
 #pragma unroll
-      for (int c = 0; c < 8; ++c)
-        gy[c] = *reinterpret_cast<const uint4 *>(smem + kBwSmemGy + tile_chunk_off(row, half * 8 + c));
-      mbar_arrive(smem_u32(&bars.free_gy));
-      // ---- epilogue 0: A2 = relu(A1 Wa + ba) -> bf16 operand tile; its sign mask stays in registers
-      uint32_t mask[2] = {0u, 0u};
+    for (int q = 0; q < 4; ++q) choff[q] = tile_chunk_off(row, cq * 4 + q);
+    uint8_t *const a2buf = smem + kBwSmemA2;
+    for (int64_t it = 0; it < n_mine; ++it) {
+      const uint32_t b = (uint32_t)it & 1u, ph2 = ((uint32_t)it >> 1) & 1u, par = (uint32_t)it & 1u;
+      uint8_t *const a1buf = smem + kBwSmemA1 + b * CN_ACT_TILE_BYTES;
+      uint8_t *const gybuf = smem + kBwSmemGy + b * CN_ACT_TILE_BYTES;
+      // ---- E0: A2 = relu(t + ba) -> bf16 operand tile
       mbar_wait(smem_u32(&bars.t_ready), par);
-      mbar_wait(smem_u32(&bars.a2_free), par ^ 1u);  // previous tile's wgrad-b is done with A2
+      mbar_wait(smem_u32(&bars.a2buf_free), par ^ 1u);  // WA / bias sums of the previous tile are done with g_t
       tc_fence_after();
       {
-        uint32_t r[64];
-        tmem_ld32(t_tmp2 + lane_off + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
-        tmem_ld32(t_tmp2 + lane_off + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+        uint32_t r[32];
+        tmem_ld32(t_acc0 + lane_off + cq * 32, r);
         tmem_wait_ld();
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const float4 b0 = *reinterpret_cast<const float4 *>(s_ba + half * 64 + q * 8);
-          const float4 b1 = *reinterpret_cast<const float4 *>(s_ba + half * 64 + q * 8 + 4);
-          float v[8];
-          v[0] = __uint_as_float(r[q * 8 + 0]) + b0.x; v[1] = __uint_as_float(r[q * 8 + 1]) + b0.y;
-          v[2] = __uint_as_float(r[q * 8 + 2]) + b0.z; v[3] = __uint_as_float(r[q * 8 + 3]) + b0.w;
-          v[4] = __uint_as_float(r[q * 8 + 4]) + b1.x; v[5] = __uint_as_float(r[q * 8 + 5]) + b1.y;
-          v[6] = __uint_as_float(r[q * 8 + 6]) + b1.z; v[7] = __uint_as_float(r[q * 8 + 7]) + b1.w;
-          uint32_t ow[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            ow[i] = pack_bf16x2(fmaxf(v[2 * i], 0.f), fmaxf(v[2 * i + 1], 0.f));
-            // the mask of the BF16 value (what the forward stored and the old backward tested)
-            if (ow[i] & 0x0000ffffu) mask[q >> 2] |= 1u << ((q & 3) * 8 + 2 * i);
-            if (ow[i] & 0xffff0000u) mask[q >> 2] |= 1u << ((q & 3) * 8 + 2 * i + 1);
-          }
-          *reinterpret_cast<uint4 *>(smem + kBwSmemA2 + tile_chunk_off(row, half * 8 + q)) =
-              make_uint4(ow[0], ow[1], ow[2], ow[3]);
+        for (int q = 0; q < 4; ++q) {
+          const float4 b0 = *reinterpret_cast<const float4 *>(s_ba + cq * 32 + q * 8);
+          const float4 b1 = *reinterpret_cast<const float4 *>(s_ba + cq * 32 + q * 8 + 4);
+          uint4 o;
+          o.x = cvt_relu_bf16x2(__uint_as_float(r[q * 8 + 0]) + b0.x, __uint_as_float(r[q * 8 + 1]) + b0.y);
+          o.y = cvt_relu_bf16x2(__uint_as_float(r[q * 8 + 2]) + b0.z, __uint_as_float(r[q * 8 + 3]) + b0.w);
+          o.z = cvt_relu_bf16x2(__uint_as_float(r[q * 8 + 4]) + b1.x, __uint_as_float(r[q * 8 + 5]) + b1.y);
+          o.w = cvt_relu_bf16x2(__uint_as_float(r[q * 8 + 6]) + b1.z, __uint_as_float(r[q * 8 + 7]) + b1.w);
+          *reinterpret_cast<uint4 *>(a2buf + choff[q]) = o;
         }
       }
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(smem_u32(&bars.a2_ready));
-      // ---- epilogue 1: g_t = g_a2 * [A2 > 0]
-      mbar_wait(smem_u32(&bars.tmp1_ready), par);
-      mbar_wait(smem_u32(&bars.gt_free), par ^ 1u);  // previous tile's wgrad-a / bias sums are done with GT
+      // ---- E1: g_t = g_a2 * [A2 > 0], in place over A2 (WB has finished reading it)
+      mbar_wait(smem_u32(&bars.g2wb_done), par);
       tc_fence_after();
       {
-        uint32_t r[64];
-        tmem_ld32(t_tmp1 + lane_off + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
-        tmem_ld32(t_tmp1 + lane_off + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+        uint32_t r[32];
+        tmem_ld32(t_acc1 + lane_off + cq * 32, r);
+        uint4 a[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) a[q] = *reinterpret_cast<const uint4 *>(a2buf + choff[q]);
         tmem_wait_ld();
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const uint32_t m = mask[q >> 2] >> ((q & 3) * 8);
-          uint32_t ow[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i)
-            ow[i] = pack_bf16x2((m >> (2 * i)) & 1u ? __uint_as_float(r[q * 8 + 2 * i]) : 0.f,
-                                (m >> (2 * i + 1)) & 1u ? __uint_as_float(r[q * 8 + 2 * i + 1]) : 0.f);
-          *reinterpret_cast<uint4 *>(smem + kBwSmemGt + tile_chunk_off(row, half * 8 + q)) =
-              make_uint4(ow[0], ow[1], ow[2], ow[3]);
+        for (int q = 0; q < 4; ++q) {
+          uint4 o;
+          o.x = mul_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 0]), __uint_as_float(r[q * 8 + 1])), gt0_bf16x2(a[q].x));
+          o.y = mul_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 2]), __uint_as_float(r[q * 8 + 3])), gt0_bf16x2(a[q].y));
+          o.z = mul_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 4]), __uint_as_float(r[q * 8 + 5])), gt0_bf16x2(a[q].z));
+          o.w = mul_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 6]), __uint_as_float(r[q * 8 + 7])), gt0_bf16x2(a[q].w));
+          *reinterpret_cast<uint4 *>(a2buf + choff[q]) = o;
         }
       }
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(smem_u32(&bars.gt_ready));
-      // ---- epilogue 2: g_h = g_y + g_a1 * [A1 > 0]  -> global (one full 128-byte line per thread)
-      mbar_wait(smem_u32(&bars.tmp2_ready), par);
+      // ---- E2: g_h = g_y + g_a1 * [A1 > 0], in place over g_y (G2 / WB / bias sums have finished reading it)
+      mbar_wait(smem_u32(&bars.g1_ready), par);
+      mbar_wait(smem_u32(&bars.gy_bias_done[b]), ph2);
+      mbar_wait(smem_u32(&bars.full_gy[b]), ph2);     // (already complete: makes the TMA writes visible to this thread)
+      mbar_wait(smem_u32(&bars.full_a1[b]), ph2);
       tc_fence_after();
       {
-        uint32_t r[64];
-        tmem_ld32(t_tmp2 + lane_off + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
-        tmem_ld32(t_tmp2 + lane_off + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+        uint32_t r[32];
+        tmem_ld32(t_acc1 + lane_off + cq * 32, r);
+        uint4 a[4], g[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          a[q] = *reinterpret_cast<const uint4 *>(a1buf + choff[q]);
+          g[q] = *reinterpret_cast<const uint4 *>(gybuf + choff[q]);
+        }
         tmem_wait_ld();
-        uint8_t *dst = gh_tiles + tile * (int64_t)CN_ACT_TILE_BYTES;
+        tc_fence_before();
+        mbar_arrive(smem_u32(&bars.acc1_free));
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const uint4 m = *reinterpret_cast<const uint4 *>(smem + kBwSmemA1 + tile_chunk_off(row, half * 8 + q));
-          const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
-          const uint32_t gw[4] = {gy[q].x, gy[q].y, gy[q].z, gy[q].w};
-          uint32_t ow[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i)
-            ow[i] = pack_bf16x2(
-                bf16_lo(gw[i]) + (bf16_lo(mw[i]) > 0.f ? __uint_as_float(r[q * 8 + 2 * i]) : 0.f),
-                bf16_hi(gw[i]) + (bf16_hi(mw[i]) > 0.f ? __uint_as_float(r[q * 8 + 2 * i + 1]) : 0.f));
-          *reinterpret_cast<uint4 *>(dst + tile_chunk_off(row, half * 8 + q)) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+        for (int q = 0; q < 4; ++q) {
+          uint4 o;
+          o.x = fma_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 0]), __uint_as_float(r[q * 8 + 1])), gt0_bf16x2(a[q].x), g[q].x);
+          o.y = fma_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 2]), __uint_as_float(r[q * 8 + 3])), gt0_bf16x2(a[q].y), g[q].y);
+          o.z = fma_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 4]), __uint_as_float(r[q * 8 + 5])), gt0_bf16x2(a[q].z), g[q].z);
+          o.w = fma_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 6]), __uint_as_float(r[q * 8 + 7])), gt0_bf16x2(a[q].w), g[q].w);
+          *reinterpret_cast<uint4 *>(gybuf + choff[q]) = o;
         }
       }
-      tc_fence_before();
-      mbar_arrive(smem_u32(&bars.free_a1));
+      mbar_arrive(smem_u32(&bars.free_a1[b]));
+      fence_proxy_async_smem();
+      mbar_arrive(smem_u32(&bars.gy_staged[b]));
     }
-    // ---- flush the weight gradients held in TMEM (each thread: its input unit, 64 output units)
+    // ---- flush the weight gradients held in TMEM (each thread: its input unit, 32 output units)
     mbar_wait(smem_u32(&bars.all_done), 0);
     tc_fence_after();
+    if (n_mine > 0) {
 #pragma unroll 1
-    for (int mtx = 0; mtx < 2; ++mtx) {
-      float *gdst = (mtx == 0 ? g_wa : g_wb) + row * 128 + half * 64;  // accumulator row = input unit
-      const uint32_t tsrc = (mtx == 0 ? t_dwa : t_dwb) + lane_off + half * 64;
-#pragma unroll 1
-      for (int c2 = 0; c2 < 2; ++c2) {
+      for (int mtx = 0; mtx < 2; ++mtx) {
+        float *gdst = (mtx == 0 ? g_wa : g_wb) + row * 128 + cq * 32;  // accumulator row = input unit
         uint32_t r[32];
-        tmem_ld32(tsrc + c2 * 32, r);
+        tmem_ld32((mtx == 0 ? t_dwa : t_dwb) + lane_off + cq * 32, r);
         tmem_wait_ld();
 #pragma unroll
         for (int q = 0; q < 8; ++q)
-          red_add_f4(gdst + c2 * 32 + q * 4, __uint_as_float(r[q * 4 + 0]), __uint_as_float(r[q * 4 + 1]),
+          red_add_f4(gdst + q * 4, __uint_as_float(r[q * 4 + 0]), __uint_as_float(r[q * 4 + 1]),
                      __uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3]));
       }
     }
@@ -412,7 +481,7 @@ extern "C" int cn_mlp_block_bwd(const void *packed, int32_t blk, const void *act
   const uint8_t *pk = (const uint8_t *)packed;
   const unsigned grid = (unsigned)(n_tiles < kNumSMs ? n_tiles : kNumSMs);
   mlp_block_bwd_kernel<<<grid, kBwdThreads, kBwdSmemBytes, (cudaStream_t)stream>>>(
-      pk + pack_bwd_block(blk, 0), pk + pack_bwd_block(blk, 1), pk + pack_fwd_block(blk, 0),
+      pk + pack_bwd_block(blk, 0), pk + pack_bwd_block(blk, 1),
       reinterpret_cast<const float *>(pk + kPackTables) + (blk < 3 ? kTabFeature : kTabFusion) + (2 * (blk % 3) + 1) * 128,
       (const uint8_t *)acts + (int64_t)act_index * CN_ACT_TILE_BYTES, (int64_t)act_stride_tiles * CN_ACT_TILE_BYTES,
       n_tiles, (const uint8_t *)gy_tiles, (uint8_t *)gh_tiles, grad + param_block_w(blk, 0),
