@@ -45,6 +45,24 @@ __host__ __device__ __forceinline__ int x_col_to_ref(int j) {
 }
 
 #ifdef __CUDACC__
+// ---------------------------------------------------------------- optional per-role timeline (make TRACE=1)
+// CTA 0 stamps clock64() into slot (iteration * 32 + point); every translation unit has its own buffer and
+// exports a reader (CN_TRACE_READER), used by tools/trace_*.py to see where a warp-specialised pipeline waits.
+#ifdef CN_TRACE
+static __device__ long long cn_trace_buf[32 * 32];
+#define CN_TRACE_AT(it, k)                                                              \
+  do {                                                                                  \
+    if (blockIdx.x == 0 && (it) < 32) cn_trace_buf[(it) * 32 + (k)] = clock64();        \
+  } while (0)
+#define CN_TRACE_READER(name)                                                           \
+  extern "C" int name(long long *dst, int n) {                                          \
+    return (int)cudaMemcpyFromSymbol(dst, cn_trace_buf, sizeof(long long) * n);         \
+  }
+#else
+#define CN_TRACE_AT(it, k) do { } while (0)
+#define CN_TRACE_READER(name)
+#endif
+
 // ---------------------------------------------------------------- small utilities
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -65,6 +83,33 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t *>(&v);
+}
+// packed bf16x2 helpers (low half = first argument / lower column)
+__device__ __forceinline__ uint32_t cvt_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ uint32_t cvt_relu_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+// per half: 1.0 where a > 0 else 0.0
+__device__ __forceinline__ uint32_t gt0_bf16x2(uint32_t a) {
+  uint32_t r;
+  asm("set.gt.bf16x2.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(0u));
+  return r;
+}
+__device__ __forceinline__ uint32_t mul_bf16x2(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t fma_bf16x2(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
 }
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }

@@ -19,7 +19,7 @@
 // TMEM: acc0, acc1, and the two weight gradients, resident across all tiles of the CTA and flushed once
 // with vector red.global.add.
 //   warp 0: TMA producer (+ g_h stores), warp 1: MMA issuer, warps 2-17: epilogue (4 TMEM lane quadrants x
-//   4 column quarters), warps 18-19: bias gradients (column sums read from the smem tiles).
+//   4 column quarters), warps 18-21: bias gradients (column sums read from the smem tiles).
 #include "common.cuh"
 #include "mlp_layout.cuh"
 
@@ -27,7 +27,7 @@ namespace cn {
 
 constexpr int kBwdEpiWarps = 16;
 constexpr int kBwdEpiThreads = kBwdEpiWarps * 32;
-constexpr int kBwdThreads = 64 + kBwdEpiThreads + 64;
+constexpr int kBwdThreads = 64 + kBwdEpiThreads + 128;
 constexpr uint32_t kBwSmemWb = 0;                       // Wb, dgrad image
 constexpr uint32_t kBwSmemWa = 1 * CN_ACT_TILE_BYTES;   // Wa, dgrad image (also the recompute's MN-major B)
 constexpr uint32_t kBwSmemA1 = 2 * CN_ACT_TILE_BYTES;   // 2 buffers
@@ -38,42 +38,16 @@ constexpr uint32_t kBwdSmemBytes = 7 * CN_ACT_TILE_BYTES + 1024;
 struct BwdBars {
   uint64_t w_full;
   uint64_t full_a1[2], full_gy[2];     // TMA landed
-  uint64_t free_a1[2];                 // 512 E2 arrivals + commit behind WA
-  uint64_t gy_staged[2];               // 512 E2 arrivals: g_h is in the g_y buffer
-  uint64_t gy_bias_done[2];            // 64 bias-sum arrivals: g_y has been summed
+  // epilogue / bias warps arrive ONCE PER WARP (lane 0 behind __syncwarp): 16 resp. 2 arrivals
+  uint64_t free_a1[2];                 // E2 warps + commit behind WA
+  uint64_t gy_staged[2];               // E2 warps: g_h is in the g_y buffer
+  uint64_t gy_bias_done[2];            // bias warps: g_y has been summed
   uint64_t t_ready, g2wb_done, g1_ready;  // commits
-  uint64_t a2_ready, gt_ready;         // 512 epilogue arrivals each
-  uint64_t a2buf_free;                 // commit behind WA + 64 bias-sum arrivals
-  uint64_t acc1_free;                  // 512 E2 arrivals
+  uint64_t a2_ready, gt_ready;         // epilogue warps
+  uint64_t a2buf_free;                 // commit behind WA + bias warps
+  uint64_t acc1_free;                  // E2 warps
   uint64_t all_done;
 };
-
-__device__ __forceinline__ uint32_t cvt_bf16x2(float lo, float hi) {
-  uint32_t r;
-  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-  return r;
-}
-__device__ __forceinline__ uint32_t cvt_relu_bf16x2(float lo, float hi) {
-  uint32_t r;
-  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-  return r;
-}
-// per half: 1.0 where a > 0 else 0.0
-__device__ __forceinline__ uint32_t gt0_bf16x2(uint32_t a) {
-  uint32_t r;
-  asm("set.gt.bf16x2.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(0u));
-  return r;
-}
-__device__ __forceinline__ uint32_t mul_bf16x2(uint32_t a, uint32_t b) {
-  uint32_t r;
-  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
-  return r;
-}
-__device__ __forceinline__ uint32_t fma_bf16x2(uint32_t a, uint32_t b, uint32_t c) {
-  uint32_t r;
-  asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
-  return r;
-}
 
 __global__ void __launch_bounds__(kBwdThreads, 1)
 mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restrict__ w_b_img,
@@ -96,17 +70,17 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
     for (int b = 0; b < 2; ++b) {
       mbar_init(smem_u32(&bars.full_a1[b]), 1);
       mbar_init(smem_u32(&bars.full_gy[b]), 1);
-      mbar_init(smem_u32(&bars.free_a1[b]), kBwdEpiThreads + 1);
-      mbar_init(smem_u32(&bars.gy_staged[b]), kBwdEpiThreads);
-      mbar_init(smem_u32(&bars.gy_bias_done[b]), 64);
+      mbar_init(smem_u32(&bars.free_a1[b]), kBwdEpiWarps + 1);
+      mbar_init(smem_u32(&bars.gy_staged[b]), kBwdEpiWarps);
+      mbar_init(smem_u32(&bars.gy_bias_done[b]), 2);
     }
     mbar_init(smem_u32(&bars.t_ready), 1);
     mbar_init(smem_u32(&bars.g2wb_done), 1);
     mbar_init(smem_u32(&bars.g1_ready), 1);
-    mbar_init(smem_u32(&bars.a2_ready), kBwdEpiThreads);
-    mbar_init(smem_u32(&bars.gt_ready), kBwdEpiThreads);
-    mbar_init(smem_u32(&bars.a2buf_free), 64 + 1);
-    mbar_init(smem_u32(&bars.acc1_free), kBwdEpiThreads);
+    mbar_init(smem_u32(&bars.a2_ready), kBwdEpiWarps);
+    mbar_init(smem_u32(&bars.gt_ready), kBwdEpiWarps);
+    mbar_init(smem_u32(&bars.a2buf_free), 2 + 1);
+    mbar_init(smem_u32(&bars.acc1_free), kBwdEpiWarps);
     mbar_init(smem_u32(&bars.all_done), 1);
     fence_barrier_init();
   }
@@ -150,13 +124,16 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
         const uint32_t b = (uint32_t)it & 1u, ph2 = ((uint32_t)it >> 1) & 1u;
         // E2 of this tile has replaced g_y by g_h in place: stream it out, then refill the buffer
         mbar_wait(smem_u32(&bars.gy_staged[b]), ph2);
+        CN_TRACE_AT(it, 24);
         bulk_s2g(gh_tiles + tile * (int64_t)CN_ACT_TILE_BYTES, s_base + kBwSmemGy + b * CN_ACT_TILE_BYTES,
                  CN_ACT_TILE_BYTES);
         bulk_commit();
         if (it + 2 < n_mine) {
           bulk_wait_read0();
           load_gy(it + 2);
+          CN_TRACE_AT(it, 25);
           mbar_wait(smem_u32(&bars.free_a1[b]), ph2);
+          CN_TRACE_AT(it, 26);
           load_a1(it + 2);
         }
       }
@@ -206,11 +183,16 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
         mbar_wait(smem_u32(&bars.full_gy[b]), ph2);
         mbar_wait(smem_u32(&bars.acc1_free), par ^ 1u);          // E2 of the previous tile has drained acc1
         tc_fence_after();
+        CN_TRACE_AT(it, 0);
         gemm_kk(t_acc1, gy, kBwSmemWb);                           // G2: g_a2 = g_y Wb^T
+        CN_TRACE_AT(it, 1);
+        mbar_wait(smem_u32(&bars.gy_bias_done[b]), ph2);          // g_y has been summed: E2 may overwrite it
         mbar_wait(smem_u32(&bars.a2_ready), par);                 // (also: E0 has drained acc0)
         tc_fence_after();
+        CN_TRACE_AT(it, 2);
         wgrad(t_dwb, kBwSmemA2, gy, it == 0);                     // WB: dWb += A2^T g_y
         umma_commit(smem_u32(&bars.g2wb_done));
+        CN_TRACE_AT(it, 3);
         bool next_issued = false;
         if (has_next && mbar_try_wait(smem_u32(&bars.full_a1[nb]), nph2)) {
           tc_fence_after();
@@ -218,13 +200,17 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
           umma_commit(smem_u32(&bars.t_ready));
           next_issued = true;
         }
+        CN_TRACE_AT(it, 4);
         mbar_wait(smem_u32(&bars.gt_ready), par);
         tc_fence_after();
+        CN_TRACE_AT(it, 5);
         gemm_kk(t_acc1, kBwSmemA2, kBwSmemWa);                    // G1: g_a1 = g_t Wa^T
         umma_commit(smem_u32(&bars.g1_ready));
+        CN_TRACE_AT(it, 6);
         wgrad(t_dwa, a1, kBwSmemA2, it == 0);                     // WA: dWa += A1^T g_t
         umma_commit(smem_u32(&bars.free_a1[b]));
         umma_commit(smem_u32(&bars.a2buf_free));
+        CN_TRACE_AT(it, 7);
         if (has_next && !next_issued) {
           mbar_wait(smem_u32(&bars.full_a1[nb]), nph2);
           tc_fence_after();
@@ -236,37 +222,46 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
     }
   } else if (warp >= 2 + kBwdEpiWarps) {
     // =========================== bias gradients ===========================
-    // column sums of the g_y and g_t tiles straight from shared memory; each lane owns two columns of
-    // slab `sl` for the whole kernel (two fp32 accumulators per tile kind), one flush at the end
-    const uint32_t sl = warp - (2 + kBwdEpiWarps);
-    const uint32_t chunk = lane >> 2, within = (lane & 3u) * 4u;
-    float bb0 = 0.f, bb1 = 0.f, ba0 = 0.f, ba1 = 0.f;
+    // column sums of the g_y (warps 18-19) and g_t (warps 20-21) tiles straight from shared memory, one 64-column
+    // slab per warp: lane = (row group of 4, 16-byte chunk), 8 fp32 accumulators per lane for the whole kernel,
+    // one shuffle reduction and flush at the end
+    const uint32_t bw = warp - (2 + kBwdEpiWarps);
+    const uint32_t sl = bw & 1u;
+    const bool is_gt = bw >= 2;
+    const uint32_t rg = lane >> 3, chunk = lane & 7u;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     for (int64_t it = 0; it < n_mine; ++it) {
       const uint32_t b = (uint32_t)it & 1u, ph2 = ((uint32_t)it >> 1) & 1u, par = (uint32_t)it & 1u;
-      mbar_wait(smem_u32(&bars.full_gy[b]), ph2);
-      const uint8_t *gy = smem + kBwSmemGy + b * CN_ACT_TILE_BYTES + sl * CN_SLAB_BYTES + within;
-#pragma unroll 8
-      for (uint32_t r = 0; r < 128; ++r) {
-        const uint32_t v = *reinterpret_cast<const uint32_t *>(gy + r * 128u + ((chunk ^ (r & 7u)) << 4));
-        bb0 += bf16_lo(v);
-        bb1 += bf16_hi(v);
+      const uint8_t *src;
+      if (is_gt) {
+        mbar_wait(smem_u32(&bars.gt_ready), par);
+        src = smem + kBwSmemA2 + sl * CN_SLAB_BYTES;
+      } else {
+        mbar_wait(smem_u32(&bars.full_gy[b]), ph2);
+        src = smem + kBwSmemGy + b * CN_ACT_TILE_BYTES + sl * CN_SLAB_BYTES;
       }
-      mbar_arrive(smem_u32(&bars.gy_bias_done[b]));
-      mbar_wait(smem_u32(&bars.gt_ready), par);
-      const uint8_t *gt = smem + kBwSmemA2 + sl * CN_SLAB_BYTES + within;
+      if (lane == 0) CN_TRACE_AT(it, is_gt ? 22 : 20);
 #pragma unroll 8
-      for (uint32_t r = 0; r < 128; ++r) {
-        const uint32_t v = *reinterpret_cast<const uint32_t *>(gt + r * 128u + ((chunk ^ (r & 7u)) << 4));
-        ba0 += bf16_lo(v);
-        ba1 += bf16_hi(v);
+      for (uint32_t i = 0; i < 32; ++i) {
+        const uint32_t r = i * 4u + rg;
+        const uint4 v = *reinterpret_cast<const uint4 *>(src + r * 128u + ((chunk ^ (r & 7u)) << 4));
+        acc[0] += bf16_lo(v.x); acc[1] += bf16_hi(v.x); acc[2] += bf16_lo(v.y); acc[3] += bf16_hi(v.y);
+        acc[4] += bf16_lo(v.z); acc[5] += bf16_hi(v.z); acc[6] += bf16_lo(v.w); acc[7] += bf16_hi(v.w);
       }
-      mbar_arrive(smem_u32(&bars.a2buf_free));
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(is_gt ? &bars.a2buf_free : &bars.gy_bias_done[b]));
+      if (lane == 0 && sl == 0) CN_TRACE_AT(it, is_gt ? 23 : 21);
     }
-    const int col = sl * 64 + lane * 2;
-    atomicAdd(&g_bb[col], bb0);
-    atomicAdd(&g_bb[col + 1], bb1);
-    atomicAdd(&g_ba[col], ba0);
-    atomicAdd(&g_ba[col + 1], ba1);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], 8);
+      acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], 16);
+    }
+    if (rg == 0) {
+      float *dst = (is_gt ? g_ba : g_bb) + sl * 64 + chunk * 8;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) atomicAdd(dst + k, acc[k]);
+    }
   } else {
     // =========================== epilogue: 16 warps, (row, 32-column quarter) per thread ===========================
     const uint32_t e = warp - 2;
@@ -286,10 +281,12 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
       mbar_wait(smem_u32(&bars.t_ready), par);
       mbar_wait(smem_u32(&bars.a2buf_free), par ^ 1u);  // WA / bias sums of the previous tile are done with g_t
       tc_fence_after();
+      if (threadIdx.x == 64) CN_TRACE_AT(it, 8);
       {
         uint32_t r[32];
         tmem_ld32(t_acc0 + lane_off + cq * 32, r);
         tmem_wait_ld();
+        if (threadIdx.x == 64) CN_TRACE_AT(it, 9);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const float4 b0 = *reinterpret_cast<const float4 *>(s_ba + cq * 32 + q * 8);
@@ -302,12 +299,16 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
           *reinterpret_cast<uint4 *>(a2buf + choff[q]) = o;
         }
       }
+      if (threadIdx.x == 64) CN_TRACE_AT(it, 10);
       fence_proxy_async_smem();
       tc_fence_before();
-      mbar_arrive(smem_u32(&bars.a2_ready));
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&bars.a2_ready));
+      if (threadIdx.x == 64) CN_TRACE_AT(it, 11);
       // ---- E1: g_t = g_a2 * [A2 > 0], in place over A2 (WB has finished reading it)
       mbar_wait(smem_u32(&bars.g2wb_done), par);
       tc_fence_after();
+      if (threadIdx.x == 64) CN_TRACE_AT(it, 12);
       {
         uint32_t r[32];
         tmem_ld32(t_acc1 + lane_off + cq * 32, r);
@@ -327,13 +328,13 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
       }
       fence_proxy_async_smem();
       tc_fence_before();
-      mbar_arrive(smem_u32(&bars.gt_ready));
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&bars.gt_ready));
+      if (threadIdx.x == 64) CN_TRACE_AT(it, 14);
       // ---- E2: g_h = g_y + g_a1 * [A1 > 0], in place over g_y (G2 / WB / bias sums have finished reading it)
-      mbar_wait(smem_u32(&bars.g1_ready), par);
-      mbar_wait(smem_u32(&bars.gy_bias_done[b]), ph2);
-      mbar_wait(smem_u32(&bars.full_gy[b]), ph2);     // (already complete: makes the TMA writes visible to this thread)
-      mbar_wait(smem_u32(&bars.full_a1[b]), ph2);
+      mbar_wait(smem_u32(&bars.g1_ready), par);        // (the MMA thread saw gy_bias_done before it issued G1)
       tc_fence_after();
+      if (threadIdx.x == 64) CN_TRACE_AT(it, 15);
       {
         uint32_t r[32];
         tmem_ld32(t_acc1 + lane_off + cq * 32, r);
@@ -345,7 +346,8 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
         }
         tmem_wait_ld();
         tc_fence_before();
-        mbar_arrive(smem_u32(&bars.acc1_free));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bars.acc1_free));
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           uint4 o;
@@ -356,9 +358,13 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
           *reinterpret_cast<uint4 *>(gybuf + choff[q]) = o;
         }
       }
-      mbar_arrive(smem_u32(&bars.free_a1[b]));
       fence_proxy_async_smem();
-      mbar_arrive(smem_u32(&bars.gy_staged[b]));
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(smem_u32(&bars.free_a1[b]));
+        mbar_arrive(smem_u32(&bars.gy_staged[b]));
+      }
+      if (threadIdx.x == 64) CN_TRACE_AT(it, 17);
     }
     // ---- flush the weight gradients held in TMEM (each thread: its input unit, 32 output units)
     mbar_wait(smem_u32(&bars.all_done), 0);
@@ -458,6 +464,10 @@ __global__ void mean_bwd_kernel(const uint4 *__restrict__ gm, int b, int nv, int
 }
 
 }  // namespace cn
+
+namespace cn {
+CN_TRACE_READER(cn_debug_read_trace)
+}
 
 extern "C" int cn_mlp_block_bwd(const void *packed, int32_t blk, const void *acts, int32_t act_stride_tiles,
                                 int32_t act_index, int64_t n_tiles, const void *gy_tiles, void *gh_tiles, float *grad,

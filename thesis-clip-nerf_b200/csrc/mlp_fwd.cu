@@ -64,12 +64,13 @@ __device__ __forceinline__ void epi_tmem_to_act(uint32_t taddr, const float *__r
     v[2] = __uint_as_float(r[q * 8 + 2]) + b0.z; v[3] = __uint_as_float(r[q * 8 + 3]) + b0.w;
     v[4] = __uint_as_float(r[q * 8 + 4]) + b1.x; v[5] = __uint_as_float(r[q * 8 + 5]) + b1.y;
     v[6] = __uint_as_float(r[q * 8 + 6]) + b1.z; v[7] = __uint_as_float(r[q * 8 + 7]) + b1.w;
-    if (kRelu) {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
-    }
-    *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, half * 8 + q)) =
-        make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+    uint4 o;
+    if (kRelu)  // relu folded into the conversion (F2FP.RELU): the epilogue is issue bound
+      o = make_uint4(cvt_relu_bf16x2(v[0], v[1]), cvt_relu_bf16x2(v[2], v[3]), cvt_relu_bf16x2(v[4], v[5]),
+                     cvt_relu_bf16x2(v[6], v[7]));
+    else
+      o = make_uint4(cvt_bf16x2(v[0], v[1]), cvt_bf16x2(v[2], v[3]), cvt_bf16x2(v[4], v[5]), cvt_bf16x2(v[6], v[7]));
+    *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, half * 8 + q)) = o;
   }
 }
 
@@ -147,16 +148,20 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
           for (int sl = 0; sl < 2; ++sl)
             load(in_tiles + ((b * nv + v) * tiles_per_view + tt) * (int64_t)CN_ACT_TILE_BYTES + sl * CN_SLAB_BYTES);
       };
-      for (int64_t p = blockIdx.x; p < n_pairs; p += gridDim.x) {
+      int64_t pi = 0;
+      for (int64_t p = blockIdx.x; p < n_pairs; p += gridDim.x, ++pi) {
         const bool valid1 = 2 * p + 1 < n_tiles;
         if (!kFusion) {
           for (int kb = 0; kb < 6; ++kb) {
             load(packed + kPackFwdW0 + kb * CN_SLAB_BYTES);
+            if (kb == 0) CN_TRACE_AT(pi, 20);
             load(in_tiles + (2 * p) * (int64_t)CN_X_TILE_BYTES + kb * CN_SLAB_BYTES);
             if (valid1) load(in_tiles + (2 * p + 1) * (int64_t)CN_X_TILE_BYTES + kb * CN_SLAB_BYTES);
           }
+          CN_TRACE_AT(pi, 21);
           for (int blk = 0; blk < 3; ++blk)
             for (int j = 0; j < 2; ++j) load_weights(blk, j);
+          CN_TRACE_AT(pi, 22);
         } else {
           if (staged) stage_views(2 * p);
           load_weights(0, 0);  // first weights before the second tile's views: MMA of tile 0 can start
@@ -193,8 +198,10 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
                      (accumulate || s || j) ? 1u : 0u);
         }
       };
-      for (int64_t p = blockIdx.x; p < n_pairs; p += gridDim.x) {
+      int64_t pi = 0;
+      for (int64_t p = blockIdx.x; p < n_pairs; p += gridDim.x, ++pi) {
         const int nt = (2 * p + 1 < n_tiles) ? 2 : 1;
+        CN_TRACE_AT(pi, 0);
         if (!kFusion) {
           // the previous pair's final epilogue must have drained h before it is overwritten
           for (int t = 0; t < nt; ++t) {
@@ -216,6 +223,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
             }
             umma_commit(smem_u32(&bars.empty[sw]));
           }
+          CN_TRACE_AT(pi, 1);
         }
         for (int blk = 0; blk < 3; ++blk) {
           for (int j = 0; j < 2; ++j) {
@@ -236,6 +244,8 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
               mbar_wait(smem_u32(&bars.act_ready[t]), n_act[t] & 1u);
               ++n_act[t];
               tc_fence_after();
+              if (blk == 0 && j == 0 && t == 0) CN_TRACE_AT(pi, 2);
+              if (blk == 2 && j == 1 && t == 1) CN_TRACE_AT(pi, 3);
               if (j == 0) {
                 gemm_act(t, tmem + t * 256 + 128, s0, s1, false);
                 umma_commit(smem_u32(&bars.tmp_ready[t]));
@@ -293,7 +303,9 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
       }
     };
 
-    for (int64_t p = blockIdx.x; p < n_pairs; p += gridDim.x) {
+    int64_t pi = 0;
+    const bool tr = threadIdx.x == 64;
+    for (int64_t p = blockIdx.x; p < n_pairs; p += gridDim.x, ++pi) {
       const int64_t tile = 2 * p + t;
       if (tile >= n_tiles) break;
       uint8_t *my_acts = acts ? acts + tile * (int64_t)kActsPerTile * CN_ACT_TILE_BYTES : nullptr;
@@ -353,6 +365,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         mbar_wait(smem_u32(&bars.h_ready[t]), n_h & 1u);
         ++n_h;
         tc_fence_after();
+        if (tr) CN_TRACE_AT(pi, 8);
       }
 
       for (int blk = 0; blk < 3; ++blk) {
@@ -361,18 +374,23 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
           acquire();
           epi_tmem_to_act<true>(t_h, tab + (2 * blk) * 128, act, row, half);
           publish(my_acts ? my_acts + blk * CN_ACT_TILE_BYTES : nullptr, true);
+          if (tr && blk == 0) CN_TRACE_AT(pi, 9);
         }
         // E_b: relu(t + ba) -> operand of the block's second Dense
         mbar_wait(smem_u32(&bars.tmp_ready[t]), n_tmp & 1u);
         ++n_tmp;
         tc_fence_after();
+        if (tr && blk == 0) CN_TRACE_AT(pi, 10);
         acquire();
         epi_tmem_to_act<true>(t_tmp, tab + (2 * blk + 1) * 128, act, row, half);
         publish(nullptr, true);
+        if (tr && blk == 0) CN_TRACE_AT(pi, 11);
         mbar_wait(smem_u32(&bars.h_ready[t]), n_h & 1u);
         ++n_h;
         tc_fence_after();
+        if (tr && blk == 0) CN_TRACE_AT(pi, 12);
       }
+      if (tr) CN_TRACE_AT(pi, 13);
 
       acquire();
       if (!kFusion) {
@@ -416,6 +434,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         reinterpret_cast<float2 *>(rgbs)[(tile * 128 + row) * 2 + half] = o;
         publish(my_acts ? my_acts + 3 * CN_ACT_TILE_BYTES : nullptr, false);
       }
+      if (tr) CN_TRACE_AT(pi, 14);
       ring_base += 12u + view_slots * ((2 * p + 1 < n_tiles) ? 2u : 1u);
     }
     if (wg_leader) bulk_wait0();
@@ -426,6 +445,8 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
+
+CN_TRACE_READER(cn_debug_read_trace_fwd)
 
 static int launch_fwd(bool fusion, const void *packed, const void *in_tiles, int64_t n_tiles, int nv,
                       int64_t tiles_per_view, void *out_tiles, float *rgbs, void *acts, cudaStream_t st) {
