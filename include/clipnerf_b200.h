@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define CN_ABI_VERSION 2
+#define CN_ABI_VERSION 3
 #define CN_TILE_ROWS 128
 #define CN_HIDDEN 128
 #define CN_FEAT_C 256          /* combined_features channels (model_v0.py:60)            */
@@ -188,19 +188,24 @@ int cn_mlp_readout_bwd(const float *params, const float *d_y, const void *acts, 
 /* backward of one ResNet block for every tile: g_y -> g_h (in place allowed),
  * dW/db of both Dense layers accumulated into grad.  blk in 0..5.  acts tile
  * [act_index] of every tile is the block's saved relu(h); the hidden activation is
- * recomputed on the tensor cores (bit-identical to the forward).                      */
+ * recomputed on the tensor cores (bit-identical to the forward).
+ * The mean over views (layers.py:368-370) is folded in: with gy_views = nv > 1, tile
+ * (b, v, t) reads the fusion-stage gradient tile (b, t) of gy_tiles [b][gy_tiles_per_view]
+ * (gh_tiles must then be a separate [n_tiles] buffer) and `scale` = 1/nv multiplies what is
+ * accumulated into grad, in fp32 (the bf16 g stream itself stays unscaled; every later
+ * per-view stage kernel takes the same scale).  gy_views = 1, scale = 1: plain block.   */
 int cn_mlp_block_bwd(const void *packed, int32_t blk, const void *acts, int32_t act_stride_tiles,
-                     int32_t act_index, int64_t n_tiles, const void *gy_tiles, void *gh_tiles,
-                     float *grad, void *stream);
+                     int32_t act_index, int64_t n_tiles, const void *gy_tiles, int32_t gy_views,
+                     int64_t gy_tiles_per_view, void *gh_tiles, float scale, float *grad, void *stream);
 /* mean-over-views backward: g_m [b][tiles_per_view] -> g_h3 [b][nv][tiles_per_view] = g_m / nv */
 int cn_mlp_mean_bwd(const void *gm_tiles, int32_t b, int32_t nv, int64_t tiles_per_view,
                     void *gh3_tiles, void *stream);
-/* first Dense backward: dX = g0 . W0^T (tile images, same column order as X) ... */
+/* first Dense backward: dX = scale * g0 . W0^T (tile images, same column order as X) ... */
 int cn_mlp_l0_dgrad(const void *packed, const void *g0_tiles, int64_t n_tiles, void *dx_tiles,
-                    void *stream);
-/* ... and dW0 += X^T . g0, db0 += sum(g0), accumulated into grad.                      */
-int cn_mlp_l0_wgrad(const void *x_tiles, const void *g0_tiles, int64_t n_tiles, float *grad,
-                    void *stream);
+                    float scale, void *stream);
+/* ... and dW0 += scale * X^T . g0, db0 += scale * sum(g0), accumulated into grad.      */
+int cn_mlp_l0_wgrad(const void *x_tiles, const void *g0_tiles, int64_t n_tiles, float scale,
+                    float *grad, void *stream);
 
 /* ---- diagnostics ---------------------------------------------------------------- */
 

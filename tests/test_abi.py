@@ -42,5 +42,5 @@ def test_argument_errors_do_not_need_a_gpu():
     one = ctypes.c_void_p(16)
     rc = lib.cn_composite_fwd(one, one, 4, 48, one, one, one, None)
     assert rc < 0 and b'S must be 64 or 128' in lib.cn_last_error()
-    rc = lib.cn_mlp_block_bwd(one, 9, one, 6, 0, 1, one, one, one, None)
+    rc = lib.cn_mlp_block_bwd(one, 9, one, 6, 0, 1, one, 1, 0, one, 1.0, one, None)
     assert rc < 0 and b'blk' in lib.cn_last_error()

@@ -107,13 +107,23 @@ def test_mlp_backward(cuda):
     for blk in (5, 4, 3):
         ops.mlp_block_bwd(packed, blk, acts_u, 4, blk - 3, gt, grad)
         errs[f'g_out{blk + 1}'] = rel_err(layout.tiles_to_matrix(gt, 128), outs[blk + 1].grad.reshape(-1, 128))
+    # the stand-alone mean backward (g_m / nv per view) is still an ABI entry point ...
     gf = ops.mlp_mean_bwd(gt, b, nv)
     errs['g_h3'] = rel_err(layout.tiles_to_matrix(gf, 128), outs[3].grad.reshape(-1, 128))
+    # ... but the render path folds it into the per-view stage: block 2 reads the fusion-stage tile for every
+    # view, the bf16 g stream stays unscaled (nv x the reference's) and 1/nv is applied in fp32 at the outputs
+    s = 1.0 / nv
+    gf = None
     for blk in (2, 1, 0):
-        ops.mlp_block_bwd(packed, blk, acts_f, 3, blk, gf, grad)
-        errs[f'g_out{blk}'] = rel_err(layout.tiles_to_matrix(gf, 128), outs[blk].grad.reshape(-1, 128))
-    ops.mlp_l0_wgrad(x_tiles, gf, grad)
-    dx = ops.mlp_l0_dgrad(packed, gf)
+        if blk == 2 and nv > 1:
+            gf = ops.mlp_block_bwd(packed, blk, acts_f, 3, blk, gt, grad, views=nv, scale=s)
+        elif blk == 2:
+            gf = ops.mlp_block_bwd(packed, blk, acts_f, 3, blk, gt.clone(), grad)
+        else:
+            ops.mlp_block_bwd(packed, blk, acts_f, 3, blk, gf, grad, scale=s)
+        errs[f'g_out{blk}'] = rel_err(layout.tiles_to_matrix(gf, 128).float() * s, outs[blk].grad.reshape(-1, 128))
+    ops.mlp_l0_wgrad(x_tiles, gf, grad, s)
+    dx = ops.mlp_l0_dgrad(packed, gf, s)
     dxm = layout.x_matrix_to_ref(layout.tiles_to_matrix(dx, 384)).cpu()
     errs['dX'] = rel_err(dxm, x.grad.reshape(-1, 379))
     for name, gv in params.to_named(grad.cpu(), 'fine').items():
@@ -155,11 +165,13 @@ def test_mlp_many_tiles_per_cta(cuda):
     gt = ops.mlp_readout_bwd(dev_flat, d_y.to(cuda), acts_u, 4, 3, grad)
     for blk in (5, 4, 3):
         ops.mlp_block_bwd(packed, blk, acts_u, 4, blk - 3, gt, grad)
-    gf = ops.mlp_mean_bwd(gt, b, nv)
-    for blk in (2, 1, 0):
-        ops.mlp_block_bwd(packed, blk, acts_f, 3, blk, gf, grad)
-    ops.mlp_l0_wgrad(x_tiles, gf, grad)
-    dx = ops.mlp_l0_dgrad(packed, gf)
+    s = 1.0 / nv
+    gf = ops.mlp_block_bwd(packed, 2, acts_f, 3, 2, gt, grad, views=nv, scale=s) if nv > 1 else \
+        ops.mlp_block_bwd(packed, 2, acts_f, 3, 2, gt, grad)
+    for blk in (1, 0):
+        ops.mlp_block_bwd(packed, blk, acts_f, 3, blk, gf, grad, scale=s)
+    ops.mlp_l0_wgrad(x_tiles, gf, grad, s)
+    dx = ops.mlp_l0_dgrad(packed, gf, s)
     errs = {name: rel_err(gv, p[name].grad) for name, gv in params.to_named(grad.cpu(), 'fine').items()}
     for k, v in errs.items():
         print(f'{k:55s} {v:.3e}')
@@ -169,5 +181,5 @@ def test_mlp_many_tiles_per_cta(cuda):
     ref = p['fine_embedding.layer_0.kernel']  # noqa: F841  (dX checked through the l0 kernel below)
     dxm = layout.x_matrix_to_ref(layout.tiles_to_matrix(dx, 384)).cpu()
     g0 = layout.tiles_to_matrix(gf, 128).cpu()
-    dx_ref = g0 @ named['fine_embedding.layer_0.kernel'].to(torch.bfloat16).to(torch.float32).t()
+    dx_ref = s * (g0 @ named['fine_embedding.layer_0.kernel'].to(torch.bfloat16).to(torch.float32).t())
     assert rel_err(dxm, dx_ref) < 1e-2

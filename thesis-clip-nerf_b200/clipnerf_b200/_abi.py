@@ -11,7 +11,7 @@ from ctypes import c_char_p, c_double, c_float, c_int32, c_int64, c_size_t, c_vo
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), 'lib', 'libclipnerf_b200.so')
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 TILE_ROWS = 128
 SLAB_BYTES = 16384
 ACT_TILE_BYTES = 32768
@@ -49,10 +49,10 @@ PROTOTYPES = {
     'cn_mlp_feature_fwd': [_P, _P, c_int64, _P, _P, _P],
     'cn_mlp_fusion_fwd': [_P, _P, c_int32, c_int32, c_int64, _P, _P, _P],
     'cn_mlp_readout_bwd': [_P, _P, _P, c_int32, c_int32, c_int64, _P, _P, _P],
-    'cn_mlp_block_bwd': [_P, c_int32, _P, c_int32, c_int32, c_int64, _P, _P, _P, _P],
+    'cn_mlp_block_bwd': [_P, c_int32, _P, c_int32, c_int32, c_int64, _P, c_int32, c_int64, _P, c_float, _P, _P],
     'cn_mlp_mean_bwd': [_P, c_int32, c_int32, c_int64, _P, _P],
-    'cn_mlp_l0_dgrad': [_P, _P, c_int64, _P, _P],
-    'cn_mlp_l0_wgrad': [_P, _P, c_int64, _P, _P],
+    'cn_mlp_l0_dgrad': [_P, _P, c_int64, _P, c_float, _P],
+    'cn_mlp_l0_wgrad': [_P, _P, c_int64, c_float, _P, _P],
     'cn_probe_umma': [_P, c_int32, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,
                       c_int32, c_int32, _P, _P],
     'cn_probe_tile_reduce': [_P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P],

@@ -242,12 +242,21 @@ def mlp_readout_bwd(params, d_y, acts, act_stride: int, act_index: int, grad):
     return g
 
 
-def mlp_block_bwd(packed, blk: int, acts, act_stride: int, act_index: int, gy_tiles, grad, gh_tiles=None):
+def mlp_block_bwd(packed, blk: int, acts, act_stride: int, act_index: int, gy_tiles, grad, gh_tiles=None,
+                  views: int = 1, scale: float = 1.0):
+    """views > 1: ``gy_tiles`` is the fusion-stage gradient [b][tiles_per_view], shared by the ``views`` per-view
+    tiles of every row tile (mean over views, layers.py:368-370); the result goes to a new per-view buffer."""
     nt = gy_tiles.numel() // ACT_TILE_BYTES
-    if gh_tiles is None:
+    tpv = 0
+    if views > 1:
+        tpv = nt            # tiles per view summed over scenes: scenes are contiguous, so b folds into the index
+        nt = nt * views
+        assert gh_tiles is None
+        gh_tiles = _bytes(nt * ACT_TILE_BYTES, gy_tiles.device)
+    elif gh_tiles is None:
         gh_tiles = gy_tiles
-    call('cn_mlp_block_bwd', _ptr(packed), blk, _ptr(acts), act_stride, act_index, nt, _ptr(gy_tiles),
-         _ptr(gh_tiles), _ptr(grad), _stream())
+    call('cn_mlp_block_bwd', _ptr(packed), blk, _ptr(acts), act_stride, act_index, nt, _ptr(gy_tiles), views, tpv,
+         _ptr(gh_tiles), float(scale), _ptr(grad), _stream())
     return gh_tiles
 
 
@@ -259,16 +268,16 @@ def mlp_mean_bwd(gm_tiles, b: int, nv: int):
     return out
 
 
-def mlp_l0_dgrad(packed, g0_tiles):
+def mlp_l0_dgrad(packed, g0_tiles, scale: float = 1.0):
     nt = g0_tiles.numel() // ACT_TILE_BYTES
     dx = _bytes(nt * X_TILE_BYTES, g0_tiles.device)
-    call('cn_mlp_l0_dgrad', _ptr(packed), _ptr(g0_tiles), nt, _ptr(dx), _stream())
+    call('cn_mlp_l0_dgrad', _ptr(packed), _ptr(g0_tiles), nt, _ptr(dx), float(scale), _stream())
     return dx
 
 
-def mlp_l0_wgrad(x_tiles, g0_tiles, grad):
+def mlp_l0_wgrad(x_tiles, g0_tiles, grad, scale: float = 1.0):
     nt = g0_tiles.numel() // ACT_TILE_BYTES
-    call('cn_mlp_l0_wgrad', _ptr(x_tiles), _ptr(g0_tiles), nt, _ptr(grad), _stream())
+    call('cn_mlp_l0_wgrad', _ptr(x_tiles), _ptr(g0_tiles), nt, float(scale), _ptr(grad), _stream())
 
 
 def probe_tile_reduce(map_: torch.Tensor, iters: int, mode: int, ctas_per_sm: int = 1) -> None:

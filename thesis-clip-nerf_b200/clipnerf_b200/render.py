@@ -42,13 +42,17 @@ def _pass_bwd(P: _Pass, params, grad, scene: ops.Scene, ray_o, ray_d, d_rgb, d_d
     g = ops.mlp_readout_bwd(params, d_y, P.acts_u, ops.FUSION_ACTS, 3, grad)
     for blk in (5, 4, 3):
         ops.mlp_block_bwd(P.packed, blk, P.acts_u, ops.FUSION_ACTS, blk - 3, g, grad)
-    gf = ops.mlp_mean_bwd(g, scene.b, scene.nv)
-    for blk in (2, 1, 0):
-        ops.mlp_block_bwd(P.packed, blk, P.acts_f, ops.FEATURE_ACTS, blk, gf, grad)
-    ops.mlp_l0_wgrad(P.x, gf, grad)
+    # mean over views: every per-view tile reads the fusion-stage gradient tile itself; the factor 1/nv is
+    # applied in fp32 wherever the per-view stage leaves the bf16 g stream (weight / bias gradients, dX)
+    s = 1.0 / scene.nv
+    gf = ops.mlp_block_bwd(P.packed, 2, P.acts_f, ops.FEATURE_ACTS, 2, g, grad, views=scene.nv, scale=s) \
+        if scene.nv > 1 else ops.mlp_block_bwd(P.packed, 2, P.acts_f, ops.FEATURE_ACTS, 2, g, grad)
+    for blk in (1, 0):
+        ops.mlp_block_bwd(P.packed, blk, P.acts_f, ops.FEATURE_ACTS, blk, gf, grad, scale=s)
+    ops.mlp_l0_wgrad(P.x, gf, grad, s)
     dx = None
     if want_dx or need_dz:
-        dx = ops.mlp_l0_dgrad(P.packed, gf)
+        dx = ops.mlp_l0_dgrad(P.packed, gf, s)
         if need_dz:
             ops.project_gather_bwd(scene, ray_o, ray_d, P.z, dx, None, dz, P.ws)
     return dz, dx

@@ -52,9 +52,9 @@ struct BwdBars {
 __global__ void __launch_bounds__(kBwdThreads, 1)
 mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restrict__ w_b_img,
                      const float *__restrict__ bias_a, const uint8_t *__restrict__ acts, int64_t act_stride_bytes,
-                     int64_t n_tiles, const uint8_t *__restrict__ gy_tiles, uint8_t *__restrict__ gh_tiles,
-                     float *__restrict__ g_wa, float *__restrict__ g_ba, float *__restrict__ g_wb,
-                     float *__restrict__ g_bb) {
+                     int64_t n_tiles, const uint8_t *__restrict__ gy_tiles, int64_t gy_views, int64_t gy_tpv,
+                     uint8_t *__restrict__ gh_tiles, float scale, float *__restrict__ g_wa, float *__restrict__ g_ba,
+                     float *__restrict__ g_wb, float *__restrict__ g_bb) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) BwdBars bars;
   __shared__ uint32_t tmem_slot;
@@ -112,7 +112,9 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
         const int64_t tile = blockIdx.x + it * gridDim.x;
         const uint32_t b = (uint32_t)it & 1u;
         mbar_expect_tx(smem_u32(&bars.full_gy[b]), CN_ACT_TILE_BYTES);
-        bulk_g2s(s_base + kBwSmemGy + b * CN_ACT_TILE_BYTES, gy_tiles + tile * (int64_t)CN_ACT_TILE_BYTES,
+        // mean over views folded in: every view tile of a (scene, row tile) reads the same fusion-stage g tile
+        const int64_t src = gy_views > 1 ? (tile / (gy_views * gy_tpv)) * gy_tpv + tile % gy_tpv : tile;
+        bulk_g2s(s_base + kBwSmemGy + b * CN_ACT_TILE_BYTES, gy_tiles + src * (int64_t)CN_ACT_TILE_BYTES,
                  CN_ACT_TILE_BYTES, smem_u32(&bars.full_gy[b]));
       };
       for (int64_t it = 0; it < 2 && it < n_mine; ++it) {
@@ -260,7 +262,7 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
     if (rg == 0) {
       float *dst = (is_gt ? g_ba : g_bb) + sl * 64 + chunk * 8;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) atomicAdd(dst + k, acc[k]);
+      for (int k = 0; k < 8; ++k) atomicAdd(dst + k, acc[k] * scale);
     }
   } else {
     // =========================== epilogue: 16 warps, (row, 32-column quarter) per thread ===========================
@@ -378,8 +380,8 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
         tmem_wait_ld();
 #pragma unroll
         for (int q = 0; q < 8; ++q)
-          red_add_f4(gdst + q * 4, __uint_as_float(r[q * 4 + 0]), __uint_as_float(r[q * 4 + 1]),
-                     __uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3]));
+          red_add_f4(gdst + q * 4, __uint_as_float(r[q * 4 + 0]) * scale, __uint_as_float(r[q * 4 + 1]) * scale,
+                     __uint_as_float(r[q * 4 + 2]) * scale, __uint_as_float(r[q * 4 + 3]) * scale);
       }
     }
   }
@@ -470,14 +472,18 @@ CN_TRACE_READER(cn_debug_read_trace)
 }
 
 extern "C" int cn_mlp_block_bwd(const void *packed, int32_t blk, const void *acts, int32_t act_stride_tiles,
-                                int32_t act_index, int64_t n_tiles, const void *gy_tiles, void *gh_tiles, float *grad,
-                                void *stream) {
+                                int32_t act_index, int64_t n_tiles, const void *gy_tiles, int32_t gy_views,
+                                int64_t gy_tiles_per_view, void *gh_tiles, float scale, float *grad, void *stream) {
   using namespace cn;
   CN_REQUIRE(packed && acts && gy_tiles && gh_tiles && grad, "cn_mlp_block_bwd: null pointer");
   CN_REQUIRE(blk >= 0 && blk < 6, "cn_mlp_block_bwd: blk %d", blk);
   CN_REQUIRE(act_stride_tiles >= 1 && act_index >= 0 && act_index < act_stride_tiles,
              "cn_mlp_block_bwd: act_stride_tiles=%d act_index=%d", act_stride_tiles, act_index);
   CN_REQUIRE(n_tiles >= 0, "cn_mlp_block_bwd: n_tiles %lld", (long long)n_tiles);
+  CN_REQUIRE(gy_views >= 1 && (gy_views == 1 || (gy_tiles_per_view > 0 && n_tiles % ((int64_t)gy_views * gy_tiles_per_view) == 0 &&
+                                                 gy_tiles != gh_tiles)),
+             "cn_mlp_block_bwd: gy_views=%d gy_tiles_per_view=%lld (shared g_y needs a separate g_h buffer)", gy_views,
+             (long long)gy_tiles_per_view);
   CN_REQUIRE((((uintptr_t)packed | (uintptr_t)acts | (uintptr_t)gy_tiles | (uintptr_t)gh_tiles) & 127) == 0 &&
                  ((uintptr_t)grad & 15) == 0,
              "cn_mlp_block_bwd: alignment");
@@ -494,7 +500,8 @@ extern "C" int cn_mlp_block_bwd(const void *packed, int32_t blk, const void *act
       pk + pack_bwd_block(blk, 0), pk + pack_bwd_block(blk, 1),
       reinterpret_cast<const float *>(pk + kPackTables) + (blk < 3 ? kTabFeature : kTabFusion) + (2 * (blk % 3) + 1) * 128,
       (const uint8_t *)acts + (int64_t)act_index * CN_ACT_TILE_BYTES, (int64_t)act_stride_tiles * CN_ACT_TILE_BYTES,
-      n_tiles, (const uint8_t *)gy_tiles, (uint8_t *)gh_tiles, grad + param_block_w(blk, 0),
+      n_tiles, (const uint8_t *)gy_tiles, (int64_t)gy_views, gy_tiles_per_view, (uint8_t *)gh_tiles, scale,
+      grad + param_block_w(blk, 0),
       grad + param_block_b(blk, 0), grad + param_block_w(blk, 1), grad + param_block_b(blk, 1));
   return check_launch("cn_mlp_block_bwd");
 }

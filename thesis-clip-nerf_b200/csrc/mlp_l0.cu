@@ -12,7 +12,7 @@ namespace cn {
 // ============================================================================================
 // dgrad
 // ============================================================================================
-constexpr int kDgThreads = 192;
+constexpr int kDgThreads = 64 + 256;  // producer, MMA, 8 epilogue warps (4 lane quadrants x 2 column halves)
 constexpr uint32_t kDgSmemW = 0;                          // 3 x 32 KiB, resident
 constexpr uint32_t kDgSmemG = 3 * CN_ACT_TILE_BYTES;      // 2 x 32 KiB (double buffer)
 constexpr uint32_t kDgSmemOut = 5 * CN_ACT_TILE_BYTES;    // 32 KiB staging for the bulk store
@@ -26,7 +26,7 @@ struct DgBars {
 
 __global__ void __launch_bounds__(kDgThreads, 1)
 mlp_l0_dgrad_kernel(const uint8_t *__restrict__ w0d, const uint8_t *__restrict__ g0_tiles, int64_t n_tiles,
-                    uint8_t *__restrict__ dx_tiles) {
+                    uint8_t *__restrict__ dx_tiles, float scale) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) DgBars bars;
   __shared__ uint32_t tmem_slot;
@@ -43,7 +43,7 @@ mlp_l0_dgrad_kernel(const uint8_t *__restrict__ w0d, const uint8_t *__restrict__
     }
     for (int i = 0; i < 4; ++i) {
       mbar_init(smem_u32(&bars.acc_ready[i]), 1);
-      mbar_init(smem_u32(&bars.acc_free[i]), 128);
+      mbar_init(smem_u32(&bars.acc_free[i]), 8);
     }
     fence_barrier_init();
   }
@@ -100,6 +100,7 @@ mlp_l0_dgrad_kernel(const uint8_t *__restrict__ w0d, const uint8_t *__restrict__
     }
   } else {
     const uint32_t quad = warp & 3u;
+    const uint32_t half = (warp - 2) >> 2;
     const uint32_t row = quad * 32u + lane;
     const uint32_t lane_off = (quad * 32u) << 16;
     const bool leader = (warp == 2 && lane == 0);
@@ -111,28 +112,27 @@ mlp_l0_dgrad_kernel(const uint8_t *__restrict__ w0d, const uint8_t *__restrict__
         const uint32_t slot = unit & 3u;
         mbar_wait(smem_u32(&bars.acc_ready[slot]), (unit >> 2) & 1u);
         tc_fence_after();
+        uint32_t r[64];
+        tmem_ld32(tmem + lane_off + slot * 128 + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+        tmem_ld32(tmem + lane_off + slot * 128 + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
         if (pending) {
           if (leader) bulk_wait_read0();
-          named_bar_sync(1, 128);
+          named_bar_sync(1, 256);
           pending = false;
         }
-#pragma unroll 1
-        for (int c4 = 0; c4 < 4; ++c4) {
-          uint32_t r[32];
-          tmem_ld32(tmem + lane_off + slot * 128 + c4 * 32, r);
-          tmem_wait_ld();
-#pragma unroll
-          for (int q = 0; q < 4; ++q)
-            *reinterpret_cast<uint4 *>(out + tile_chunk_off(row, c4 * 4 + q)) = make_uint4(
-                pack_bf16x2(__uint_as_float(r[q * 8 + 0]), __uint_as_float(r[q * 8 + 1])),
-                pack_bf16x2(__uint_as_float(r[q * 8 + 2]), __uint_as_float(r[q * 8 + 3])),
-                pack_bf16x2(__uint_as_float(r[q * 8 + 4]), __uint_as_float(r[q * 8 + 5])),
-                pack_bf16x2(__uint_as_float(r[q * 8 + 6]), __uint_as_float(r[q * 8 + 7])));
-        }
+        tmem_wait_ld();
         tc_fence_before();
-        mbar_arrive(smem_u32(&bars.acc_free[slot]));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bars.acc_free[slot]));
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          *reinterpret_cast<uint4 *>(out + tile_chunk_off(row, half * 8 + q)) = make_uint4(
+              cvt_bf16x2(__uint_as_float(r[q * 8 + 0]) * scale, __uint_as_float(r[q * 8 + 1]) * scale),
+              cvt_bf16x2(__uint_as_float(r[q * 8 + 2]) * scale, __uint_as_float(r[q * 8 + 3]) * scale),
+              cvt_bf16x2(__uint_as_float(r[q * 8 + 4]) * scale, __uint_as_float(r[q * 8 + 5]) * scale),
+              cvt_bf16x2(__uint_as_float(r[q * 8 + 6]) * scale, __uint_as_float(r[q * 8 + 7]) * scale));
         fence_proxy_async_smem();
-        named_bar_sync(1, 128);
+        named_bar_sync(1, 256);
         if (leader) {
           bulk_s2g(dx_tiles + tile * (int64_t)CN_X_TILE_BYTES + c * CN_ACT_TILE_BYTES, s_base + kDgSmemOut,
                    CN_ACT_TILE_BYTES);
@@ -162,7 +162,7 @@ struct WgBars {
 
 __global__ void __launch_bounds__(kWgThreads, 1)
 mlp_l0_wgrad_kernel(const uint8_t *__restrict__ x_tiles, const uint8_t *__restrict__ g0_tiles, int64_t n_tiles,
-                    float *__restrict__ g_w0, float *__restrict__ g_b0) {
+                    float *__restrict__ g_w0, float *__restrict__ g_b0, float scale) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) WgBars bars;
   __shared__ uint32_t tmem_slot;
@@ -260,10 +260,10 @@ mlp_l0_wgrad_kernel(const uint8_t *__restrict__ x_tiles, const uint8_t *__restri
           mbar_arrive(smem_u32(&bars.empty[ps]));
         }
       }
-      atomicAdd(&g_b0[2 * lane], b00);
-      atomicAdd(&g_b0[2 * lane + 1], b01);
-      atomicAdd(&g_b0[64 + 2 * lane], b10);
-      atomicAdd(&g_b0[64 + 2 * lane + 1], b11);
+      atomicAdd(&g_b0[2 * lane], b00 * scale);
+      atomicAdd(&g_b0[2 * lane + 1], b01 * scale);
+      atomicAdd(&g_b0[64 + 2 * lane], b10 * scale);
+      atomicAdd(&g_b0[64 + 2 * lane + 1], b11 * scale);
     }
     mbar_wait(smem_u32(&bars.all_done), 0);
     tc_fence_after();
@@ -279,8 +279,8 @@ mlp_l0_wgrad_kernel(const uint8_t *__restrict__ x_tiles, const uint8_t *__restri
           float *dst = g_w0 + ref * 128 + c4 * 32;
 #pragma unroll
           for (int q = 0; q < 8; ++q)
-            red_add_f4(dst + q * 4, __uint_as_float(r[q * 4 + 0]), __uint_as_float(r[q * 4 + 1]),
-                       __uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3]));
+            red_add_f4(dst + q * 4, __uint_as_float(r[q * 4 + 0]) * scale, __uint_as_float(r[q * 4 + 1]) * scale,
+                       __uint_as_float(r[q * 4 + 2]) * scale, __uint_as_float(r[q * 4 + 3]) * scale);
         }
       }
     }
@@ -293,7 +293,7 @@ mlp_l0_wgrad_kernel(const uint8_t *__restrict__ x_tiles, const uint8_t *__restri
 }  // namespace cn
 
 extern "C" int cn_mlp_l0_dgrad(const void *packed, const void *g0_tiles, int64_t n_tiles, void *dx_tiles,
-                               void *stream) {
+                               float scale, void *stream) {
   using namespace cn;
   CN_REQUIRE(packed && g0_tiles && dx_tiles, "cn_mlp_l0_dgrad: null pointer");
   CN_REQUIRE(n_tiles >= 0, "cn_mlp_l0_dgrad: n_tiles %lld", (long long)n_tiles);
@@ -307,11 +307,12 @@ extern "C" int cn_mlp_l0_dgrad(const void *packed, const void *g0_tiles, int64_t
   }
   const unsigned grid = (unsigned)(n_tiles < kNumSMs ? n_tiles : kNumSMs);
   mlp_l0_dgrad_kernel<<<grid, kDgThreads, kDgSmemBytes, (cudaStream_t)stream>>>(
-      (const uint8_t *)packed + kPackBwdW0, (const uint8_t *)g0_tiles, n_tiles, (uint8_t *)dx_tiles);
+      (const uint8_t *)packed + kPackBwdW0, (const uint8_t *)g0_tiles, n_tiles, (uint8_t *)dx_tiles, scale);
   return check_launch("cn_mlp_l0_dgrad");
 }
 
-extern "C" int cn_mlp_l0_wgrad(const void *x_tiles, const void *g0_tiles, int64_t n_tiles, float *grad, void *stream) {
+extern "C" int cn_mlp_l0_wgrad(const void *x_tiles, const void *g0_tiles, int64_t n_tiles, float scale, float *grad,
+                               void *stream) {
   using namespace cn;
   CN_REQUIRE(x_tiles && g0_tiles && grad, "cn_mlp_l0_wgrad: null pointer");
   CN_REQUIRE(n_tiles >= 0, "cn_mlp_l0_wgrad: n_tiles %lld", (long long)n_tiles);
@@ -326,6 +327,6 @@ extern "C" int cn_mlp_l0_wgrad(const void *x_tiles, const void *g0_tiles, int64_
   }
   const unsigned grid = (unsigned)(n_tiles < kNumSMs ? n_tiles : kNumSMs);
   mlp_l0_wgrad_kernel<<<grid, kWgThreads, kWgSmemBytes, (cudaStream_t)stream>>>(
-      (const uint8_t *)x_tiles, (const uint8_t *)g0_tiles, n_tiles, grad + kParamW0, grad + kParamB0);
+      (const uint8_t *)x_tiles, (const uint8_t *)g0_tiles, n_tiles, grad + kParamW0, grad + kParamB0, scale);
   return check_launch("cn_mlp_l0_wgrad");
 }
