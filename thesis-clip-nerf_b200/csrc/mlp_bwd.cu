@@ -396,54 +396,112 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
 // ------------------------------------------------------------------------------------------
 
 // readout backward (layers.py:392-397): g_e = (d_y Wr^T) * [relu(e) > 0]; dWr += relu(e)^T d_y; dbr += sum d_y
-__global__ void __launch_bounds__(128)
+// Persistent CTAs of 256 threads; the relu(e) tile of the NEXT tile streams into shared memory (bulk TMA, double
+// buffered) while this one is processed; g_e leaves through a staged bulk store.
+//   phase A: thread = (row, column half): 8 x 16-byte chunks, 4 FMAs per element, packed bf16x2 mask
+//   phase B: thread = (column pair, row half): dWr accumulated in registers over all tiles of the CTA
+constexpr int kRoThreads = 256;
+constexpr uint32_t kRoSmemBytes = 3 * CN_ACT_TILE_BYTES + 1024;
+
+__global__ void __launch_bounds__(kRoThreads, 2)
 readout_bwd_kernel(const float *__restrict__ wr, const float *__restrict__ d_y, const uint8_t *__restrict__ acts,
                    int64_t act_stride_bytes, int64_t n_tiles, uint8_t *__restrict__ g_tiles,
                    float *__restrict__ g_wr, float *__restrict__ g_br) {
-  __shared__ float s_wr[512];
-  __shared__ float s_dy[128 * 4];
-  __shared__ __align__(16) uint8_t s_a[CN_ACT_TILE_BYTES];
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(16) float s_wr[512];
+  __shared__ __align__(16) float s_dy[128 * 4];
+  __shared__ __align__(8) uint64_t full[2];
+  uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const uint32_t s_base = smem_u32(smem);
   const int tid = threadIdx.x;
-  for (int i = tid; i < 512; i += 128) s_wr[i] = wr[i];
-  float acc[4] = {0.f, 0.f, 0.f, 0.f};  // dWr[tid][0..3]
-  float accb = 0.f;                     // dbr[tid] for tid < 4
-  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    __syncthreads();
-    const float4 dy = reinterpret_cast<const float4 *>(d_y)[tile * 128 + tid];
-    reinterpret_cast<float4 *>(s_dy)[tid] = dy;
-    const uint8_t *src = acts + tile * act_stride_bytes;
-    uint8_t *dst = g_tiles + tile * (int64_t)CN_ACT_TILE_BYTES;
-    for (int c = 0; c < 16; ++c) {
-      const uint32_t off = tile_chunk_off(tid, c);
-      const uint4 a = ldg_nc_u4(src + off);
-      *reinterpret_cast<uint4 *>(s_a + off) = a;
-      const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
-      uint32_t ow[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int k0 = c * 8 + 2 * i;
-        const float g0 = dy.x * s_wr[k0 * 4 + 0] + dy.y * s_wr[k0 * 4 + 1] + dy.z * s_wr[k0 * 4 + 2] +
-                         dy.w * s_wr[k0 * 4 + 3];
-        const float g1 = dy.x * s_wr[k0 * 4 + 4] + dy.y * s_wr[k0 * 4 + 5] + dy.z * s_wr[k0 * 4 + 6] +
-                         dy.w * s_wr[k0 * 4 + 7];
-        ow[i] = pack_bf16x2(bf16_lo(aw[i]) > 0.f ? g0 : 0.f, bf16_hi(aw[i]) > 0.f ? g1 : 0.f);
-      }
-      *reinterpret_cast<uint4 *>(dst + off) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
-    }
-    __syncthreads();
-    // thread k accumulates dWr[k][:] over the 128 rows of the tile
-    for (int r = 0; r < 128; ++r) {
-      const float a = __bfloat162float(*reinterpret_cast<const __nv_bfloat16 *>(s_a + tile_off(r, tid)));
-      acc[0] += a * s_dy[r * 4 + 0];
-      acc[1] += a * s_dy[r * 4 + 1];
-      acc[2] += a * s_dy[r * 4 + 2];
-      acc[3] += a * s_dy[r * 4 + 3];
-    }
-    if (tid < 4)
-      for (int r = 0; r < 128; ++r) accb += s_dy[r * 4 + tid];
+  uint8_t *const s_out = smem + 2 * CN_ACT_TILE_BYTES;
+  for (int i = tid; i < 512; i += kRoThreads) s_wr[i] = wr[i];
+  if (tid == 0) {
+    mbar_init(smem_u32(&full[0]), 1);
+    mbar_init(smem_u32(&full[1]), 1);
+    fence_barrier_init();
   }
+  __syncthreads();
+  const int64_t n_mine = n_tiles > blockIdx.x ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  auto load = [&](int64_t it) {
+    const int64_t tile = blockIdx.x + it * gridDim.x;
+    const uint32_t b = (uint32_t)it & 1u;
+    mbar_expect_tx(smem_u32(&full[b]), CN_ACT_TILE_BYTES);
+    bulk_g2s(s_base + b * CN_ACT_TILE_BYTES, acts + tile * act_stride_bytes, CN_ACT_TILE_BYTES, smem_u32(&full[b]));
+  };
+  if (tid == 0 && n_mine > 0) load(0);
+  // phase A role: row, column half; phase B role: column pair, row half
+  const uint32_t row = tid & 127u, half = tid >> 7;
+  const uint32_t kp = tid & 63u, rq = tid >> 6;     // columns 2kp, 2kp+1 ; rows [32 rq, 32 rq + 32)
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // dWr[2kp][0..3], dWr[2kp+1][0..3]
+  float accb = 0.f;
+  for (int64_t it = 0; it < n_mine; ++it) {
+    const int64_t tile = blockIdx.x + it * gridDim.x;
+    const uint32_t b = (uint32_t)it & 1u;
+    const uint8_t *s_a = smem + b * CN_ACT_TILE_BYTES;
+    if (tid < 128) reinterpret_cast<float4 *>(s_dy)[tid] = reinterpret_cast<const float4 *>(d_y)[tile * 128 + tid];
+    if (tid == 0) {
+      bulk_wait_read0();                             // the previous g_e store has left s_out
+      if (it + 1 < n_mine) load(it + 1);             // (its buffer was released by the barrier that ended phase B)
+    }
+    __syncthreads();
+    mbar_wait(smem_u32(&full[b]), ((uint32_t)it >> 1) & 1u);
+    // ---- phase A
+    {
+      const float4 dy = reinterpret_cast<const float4 *>(s_dy)[row];
+#pragma unroll 2
+      for (int c = 0; c < 8; ++c) {
+        const uint32_t off = tile_chunk_off(row, half * 8 + c);
+        const uint4 a = *reinterpret_cast<const uint4 *>(s_a + off);
+        const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+        uint32_t ow[4];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) atomicAdd(&g_wr[tid * 4 + j], acc[j]);
+        for (int i = 0; i < 4; ++i) {
+          const int k0 = (half * 8 + c) * 8 + 2 * i;
+          const float4 w0 = *reinterpret_cast<const float4 *>(s_wr + k0 * 4);
+          const float4 w1 = *reinterpret_cast<const float4 *>(s_wr + k0 * 4 + 4);
+          const float g0 = dy.x * w0.x + dy.y * w0.y + dy.z * w0.z + dy.w * w0.w;
+          const float g1 = dy.x * w1.x + dy.y * w1.y + dy.z * w1.z + dy.w * w1.w;
+          ow[i] = mul_bf16x2(cvt_bf16x2(g0, g1), gt0_bf16x2(aw[i]));
+        }
+        *reinterpret_cast<uint4 *>(s_out + off) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+      }
+    }
+    // ---- phase B: this thread's two columns over its 32 rows
+    {
+      const uint32_t chunk = kp >> 2, within = (kp & 3u) * 4u, slab = chunk >> 3;
+#pragma unroll 8
+      for (uint32_t r = rq * 32u; r < rq * 32u + 32u; ++r) {
+        const uint32_t v = *reinterpret_cast<const uint32_t *>(s_a + slab * CN_SLAB_BYTES + r * 128u +
+                                                               (((chunk & 7u) ^ (r & 7u)) << 4) + within);
+        const float4 dy = reinterpret_cast<const float4 *>(s_dy)[r];
+        const float a0 = bf16_lo(v), a1 = bf16_hi(v);
+        acc[0] += a0 * dy.x; acc[1] += a0 * dy.y; acc[2] += a0 * dy.z; acc[3] += a0 * dy.w;
+        acc[4] += a1 * dy.x; acc[5] += a1 * dy.y; acc[6] += a1 * dy.z; acc[7] += a1 * dy.w;
+      }
+      if (tid < 4)
+        for (int r = 0; r < 128; ++r) accb += s_dy[r * 4 + tid];
+    }
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      bulk_s2g(g_tiles + tile * (int64_t)CN_ACT_TILE_BYTES, s_base + 2 * CN_ACT_TILE_BYTES, CN_ACT_TILE_BYTES);
+      bulk_commit();
+    }
+  }
+  if (tid == 0) bulk_wait0();
+  // the four row quarters of a column pair meet in shared memory: one atomic per dWr element per CTA
+  __syncthreads();
+  float *red = reinterpret_cast<float *>(smem);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[(rq * 64 + kp) * 8 + j] = acc[j];
+  __syncthreads();
+  for (int i = tid; i < 512; i += kRoThreads) {
+    const int p2 = i >> 3, j = i & 7;
+    const float v = red[(0 * 64 + p2) * 8 + j] + red[(1 * 64 + p2) * 8 + j] + red[(2 * 64 + p2) * 8 + j] +
+                    red[(3 * 64 + p2) * 8 + j];
+    atomicAdd(&g_wr[(2 * p2 + (j >> 2)) * 4 + (j & 3)], v);
+  }
   if (tid < 4) atomicAdd(&g_br[tid], accb);
 }
 
@@ -513,10 +571,15 @@ extern "C" int cn_mlp_readout_bwd(const float *params, const float *d_y, const v
   CN_REQUIRE(act_stride_tiles >= 1 && act_index >= 0 && act_index < act_stride_tiles,
              "cn_mlp_readout_bwd: act_stride_tiles=%d act_index=%d", act_stride_tiles, act_index);
   CN_REQUIRE(n_tiles >= 0, "cn_mlp_readout_bwd: n_tiles %lld", (long long)n_tiles);
-  CN_REQUIRE((((uintptr_t)d_y | (uintptr_t)acts | (uintptr_t)g_tiles) & 15) == 0, "cn_mlp_readout_bwd: alignment");
+  CN_REQUIRE((((uintptr_t)d_y | (uintptr_t)acts | (uintptr_t)g_tiles) & 127) == 0, "cn_mlp_readout_bwd: alignment");
   if (n_tiles == 0) return 0;
-  const unsigned grid = (unsigned)(n_tiles < 4 * kNumSMs ? n_tiles : 4 * kNumSMs);
-  readout_bwd_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(
+  cudaError_t e = cudaFuncSetAttribute(readout_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRoSmemBytes);
+  if (e != cudaSuccess) {
+    set_error("cn_mlp_readout_bwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
+  const unsigned grid = (unsigned)(n_tiles < 2 * kNumSMs ? n_tiles : 2 * kNumSMs);
+  readout_bwd_kernel<<<grid, kRoThreads, kRoSmemBytes, (cudaStream_t)stream>>>(
       params + kParamWr, d_y, (const uint8_t *)acts + (int64_t)act_index * CN_ACT_TILE_BYTES,
       (int64_t)act_stride_tiles * CN_ACT_TILE_BYTES, n_tiles, (uint8_t *)g_tiles, grad + kParamWr, grad + kParamBr);
   return check_launch("cn_mlp_readout_bwd");
