@@ -11,15 +11,21 @@
 //   WA : dWa += A1^T g_t
 //   E2 : g_h  = g_y + g_a1 * [A1 > 0]  -> overwrites g_y in place, TMA store to global
 //   the next tile's T is issued behind WB so that its E0 never waits for the tensor pipe.
-// Cost model (tools/ubench_tc.cu, B200): MMA 128x128x16 = 64 cycles (512 per GEMM); a TMEM -> bf16 ->
-// st.shared epilogue is ISSUE bound (~1000 cycles per tile with select/add/max per element and 8 warps),
-// so every epilogue here is 3 packed instructions per element PAIR (cvt.bf16x2 / set.bf16x2 / mul|fma.bf16x2)
-// on 16 warps (~400 cycles).  With that the kernel is bound by its 96 KiB of HBM traffic per tile.
+// Cost model (tools/ubench_tc.cu, tools/trace_block_bwd.py, B200): MMA 128x128x16 = 64 cycles (512 per GEMM), and an
+// SS-mode 128x128 MMA reads its 8 KiB of operands at 128 B/clk -- ALL of the SM's shared-memory bandwidth.  The five
+// GEMMs of a tile already move 320 KiB through shared memory, so the kernel is bound by SHARED-MEMORY TRAFFIC before
+// it is bound by the tensor pipe or by its 96 KiB of HBM traffic per tile.  Hence:
+//   * every epilogue is 3 packed instructions per element PAIR (cvt.bf16x2 / set.bf16x2 / mul|fma.bf16x2), 16 warps;
+//   * the ReLU mask of A2 stays in registers between E0 and E1 (no re-read of the tile);
+//   * the bias gradients (column sums of g_t and g_y) are taken from the registers the epilogue already holds, by a
+//     packed bf16x2 butterfly over the 32 rows of a warp (15 shuffles), accumulated in fp32 across tiles -- no extra
+//     pass over the tiles in shared memory;
+//   * g_h replaces g_y in its buffer and leaves by ONE bulk store (a store straight from registers costs 32 partial
+//     lines per instruction: measured 2000 cycles per tile in the LSU).
 // Shared memory: Wa, Wb (dgrad images, resident) + 2 x A1 + 2 x g_y (double buffered TMA) + 1 x A2|g_t.
 // TMEM: acc0, acc1, and the two weight gradients, resident across all tiles of the CTA and flushed once
 // with vector red.global.add.
-//   warp 0: TMA producer (+ g_h stores), warp 1: MMA issuer, warps 2-17: epilogue (4 TMEM lane quadrants x
-//   4 column quarters), warps 18-21: bias gradients (column sums read from the smem tiles).
+//   warp 0: TMA producer, warp 1: MMA issuer, warps 2-17: epilogue (4 TMEM lane quadrants x 4 column quarters).
 #include "common.cuh"
 #include "mlp_layout.cuh"
 
@@ -27,7 +33,7 @@ namespace cn {
 
 constexpr int kBwdEpiWarps = 16;
 constexpr int kBwdEpiThreads = kBwdEpiWarps * 32;
-constexpr int kBwdThreads = 64 + kBwdEpiThreads + 128;
+constexpr int kBwdThreads = 64 + kBwdEpiThreads;
 constexpr uint32_t kBwSmemWb = 0;                       // Wb, dgrad image
 constexpr uint32_t kBwSmemWa = 1 * CN_ACT_TILE_BYTES;   // Wa, dgrad image (also the recompute's MN-major B)
 constexpr uint32_t kBwSmemA1 = 2 * CN_ACT_TILE_BYTES;   // 2 buffers
@@ -40,14 +46,52 @@ struct BwdBars {
   uint64_t full_a1[2], full_gy[2];     // TMA landed
   // epilogue / bias warps arrive ONCE PER WARP (lane 0 behind __syncwarp): 16 resp. 2 arrivals
   uint64_t free_a1[2];                 // E2 warps + commit behind WA
-  uint64_t gy_staged[2];               // E2 warps: g_h is in the g_y buffer
-  uint64_t gy_bias_done[2];            // bias warps: g_y has been summed
+  uint64_t gy_staged[2];               // E2 warps: g_h has replaced g_y in its buffer (G2 / WB are behind G1: done)
   uint64_t t_ready, g2wb_done, g1_ready;  // commits
   uint64_t a2_ready, gt_ready;         // epilogue warps
-  uint64_t a2buf_free;                 // commit behind WA + bias warps
+  uint64_t a2buf_free;                 // commit behind WA
   uint64_t acc1_free;                  // E2 warps
   uint64_t all_done;
 };
+
+// Column sums over the 32 rows (lanes) of a warp of 16 packed bf16x2 words per lane (32 columns): a butterfly that
+// halves what a lane holds at every step.  The first two levels (sums of 2 and 4 values) stay packed bf16x2
+// (8 + 4 exchanges), the last three run in fp32 (4 + 2 + 1 exchanges) -- the rounding of a packed add grows with the
+// partial sum, so the late levels are the ones worth 32 bits.  Returns, in lane l, the sum of column l.
+__device__ __forceinline__ float colsum_bf16x2(uint32_t (&w)[16], uint32_t lane) {
+#pragma unroll
+  for (int lvl = 0; lvl < 2; ++lvl) {
+    const int half = 8 >> lvl;                 // words kept after this level
+    const uint32_t bit = 16u >> lvl;           // partner = lane ^ bit; lanes with the bit set keep the upper half
+    const bool up = (lane & bit) != 0;
+#pragma unroll
+    for (int j = 0; j < half; ++j) {
+      const uint32_t send = up ? w[j] : w[j + half];
+      const uint32_t keep = up ? w[j + half] : w[j];
+      const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, bit);
+      asm("add.rn.bf16x2 %0, %1, %2;" : "=r"(w[j]) : "r"(keep), "r"(recv));
+    }
+  }
+  float f[8];  // words 4 (lane >> 3) + {0..3}  ->  columns 8 (lane >> 3) + {0..7}
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    f[2 * j] = bf16_lo(w[j]);
+    f[2 * j + 1] = bf16_hi(w[j]);
+  }
+#pragma unroll
+  for (int lvl = 0; lvl < 3; ++lvl) {
+    const int half = 4 >> lvl;
+    const uint32_t bit = 4u >> lvl;
+    const bool up = (lane & bit) != 0;
+#pragma unroll
+    for (int j = 0; j < half; ++j) {
+      const float send = up ? f[j] : f[j + half];
+      const float keep = up ? f[j + half] : f[j];
+      f[j] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
+    }
+  }
+  return f[0];
+}
 
 __global__ void __launch_bounds__(kBwdThreads, 1)
 mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restrict__ w_b_img,
@@ -72,14 +116,13 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
       mbar_init(smem_u32(&bars.full_gy[b]), 1);
       mbar_init(smem_u32(&bars.free_a1[b]), kBwdEpiWarps + 1);
       mbar_init(smem_u32(&bars.gy_staged[b]), kBwdEpiWarps);
-      mbar_init(smem_u32(&bars.gy_bias_done[b]), 2);
     }
     mbar_init(smem_u32(&bars.t_ready), 1);
     mbar_init(smem_u32(&bars.g2wb_done), 1);
     mbar_init(smem_u32(&bars.g1_ready), 1);
     mbar_init(smem_u32(&bars.a2_ready), kBwdEpiWarps);
     mbar_init(smem_u32(&bars.gt_ready), kBwdEpiWarps);
-    mbar_init(smem_u32(&bars.a2buf_free), 2 + 1);
+    mbar_init(smem_u32(&bars.a2buf_free), 1);
     mbar_init(smem_u32(&bars.acc1_free), kBwdEpiWarps);
     mbar_init(smem_u32(&bars.all_done), 1);
     fence_barrier_init();
@@ -96,7 +139,7 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
   const int64_t n_mine = n_tiles > blockIdx.x ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
 
   if (warp == 0) {
-    // =========================== TMA producer + g_h stores ===========================
+    // =========================== TMA producer ===========================
     if (lane == 0) {
       mbar_expect_tx(smem_u32(&bars.w_full), 2 * CN_ACT_TILE_BYTES);
       bulk_g2s(s_base + kBwSmemWb, w_b_img, CN_ACT_TILE_BYTES, smem_u32(&bars.w_full));
@@ -133,7 +176,6 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
         if (it + 2 < n_mine) {
           bulk_wait_read0();
           load_gy(it + 2);
-          CN_TRACE_AT(it, 25);
           mbar_wait(smem_u32(&bars.free_a1[b]), ph2);
           CN_TRACE_AT(it, 26);
           load_a1(it + 2);
@@ -188,7 +230,6 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
         CN_TRACE_AT(it, 0);
         gemm_kk(t_acc1, gy, kBwSmemWb);                           // G2: g_a2 = g_y Wb^T
         CN_TRACE_AT(it, 1);
-        mbar_wait(smem_u32(&bars.gy_bias_done[b]), ph2);          // g_y has been summed: E2 may overwrite it
         mbar_wait(smem_u32(&bars.a2_ready), par);                 // (also: E0 has drained acc0)
         tc_fence_after();
         CN_TRACE_AT(it, 2);
@@ -222,48 +263,6 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
       }
       umma_commit(smem_u32(&bars.all_done));
     }
-  } else if (warp >= 2 + kBwdEpiWarps) {
-    // =========================== bias gradients ===========================
-    // column sums of the g_y (warps 18-19) and g_t (warps 20-21) tiles straight from shared memory, one 64-column
-    // slab per warp: lane = (row group of 4, 16-byte chunk), 8 fp32 accumulators per lane for the whole kernel,
-    // one shuffle reduction and flush at the end
-    const uint32_t bw = warp - (2 + kBwdEpiWarps);
-    const uint32_t sl = bw & 1u;
-    const bool is_gt = bw >= 2;
-    const uint32_t rg = lane >> 3, chunk = lane & 7u;
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int64_t it = 0; it < n_mine; ++it) {
-      const uint32_t b = (uint32_t)it & 1u, ph2 = ((uint32_t)it >> 1) & 1u, par = (uint32_t)it & 1u;
-      const uint8_t *src;
-      if (is_gt) {
-        mbar_wait(smem_u32(&bars.gt_ready), par);
-        src = smem + kBwSmemA2 + sl * CN_SLAB_BYTES;
-      } else {
-        mbar_wait(smem_u32(&bars.full_gy[b]), ph2);
-        src = smem + kBwSmemGy + b * CN_ACT_TILE_BYTES + sl * CN_SLAB_BYTES;
-      }
-      if (lane == 0) CN_TRACE_AT(it, is_gt ? 22 : 20);
-#pragma unroll 8
-      for (uint32_t i = 0; i < 32; ++i) {
-        const uint32_t r = i * 4u + rg;
-        const uint4 v = *reinterpret_cast<const uint4 *>(src + r * 128u + ((chunk ^ (r & 7u)) << 4));
-        acc[0] += bf16_lo(v.x); acc[1] += bf16_hi(v.x); acc[2] += bf16_lo(v.y); acc[3] += bf16_hi(v.y);
-        acc[4] += bf16_lo(v.z); acc[5] += bf16_hi(v.z); acc[6] += bf16_lo(v.w); acc[7] += bf16_hi(v.w);
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(is_gt ? &bars.a2buf_free : &bars.gy_bias_done[b]));
-      if (lane == 0 && sl == 0) CN_TRACE_AT(it, is_gt ? 23 : 21);
-    }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], 8);
-      acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], 16);
-    }
-    if (rg == 0) {
-      float *dst = (is_gt ? g_ba : g_bb) + sl * 64 + chunk * 8;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) atomicAdd(dst + k, acc[k] * scale);
-    }
   } else {
     // =========================== epilogue: 16 warps, (row, 32-column quarter) per thread ===========================
     const uint32_t e = warp - 2;
@@ -275,77 +274,89 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
 #pragma unroll
     for (int q = 0; q < 4; ++q) choff[q] = tile_chunk_off(row, cq * 4 + q);
     uint8_t *const a2buf = smem + kBwSmemA2;
+    // bias gradients: lane l accumulates column 32 cq + l, summed over the warp's 32 rows of every tile
+    float dba = 0.f, dbb = 0.f;
     for (int64_t it = 0; it < n_mine; ++it) {
-      const uint32_t b = (uint32_t)it & 1u, ph2 = ((uint32_t)it >> 1) & 1u, par = (uint32_t)it & 1u;
-      uint8_t *const a1buf = smem + kBwSmemA1 + b * CN_ACT_TILE_BYTES;
+      const uint32_t b = (uint32_t)it & 1u, par = (uint32_t)it & 1u;
+      const uint8_t *const a1buf = smem + kBwSmemA1 + b * CN_ACT_TILE_BYTES;
       uint8_t *const gybuf = smem + kBwSmemGy + b * CN_ACT_TILE_BYTES;
+      uint32_t a2w[16];                               // A2 of this thread: ReLU mask source of E1
       // ---- E0: A2 = relu(t + ba) -> bf16 operand tile
       mbar_wait(smem_u32(&bars.t_ready), par);
-      mbar_wait(smem_u32(&bars.a2buf_free), par ^ 1u);  // WA / bias sums of the previous tile are done with g_t
+      mbar_wait(smem_u32(&bars.a2buf_free), par ^ 1u);  // WA of the previous tile is done with g_t
       tc_fence_after();
       if (threadIdx.x == 64) CN_TRACE_AT(it, 8);
       {
         uint32_t r[32];
         tmem_ld32(t_acc0 + lane_off + cq * 32, r);
         tmem_wait_ld();
-        if (threadIdx.x == 64) CN_TRACE_AT(it, 9);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const float4 b0 = *reinterpret_cast<const float4 *>(s_ba + cq * 32 + q * 8);
           const float4 b1 = *reinterpret_cast<const float4 *>(s_ba + cq * 32 + q * 8 + 4);
-          uint4 o;
-          o.x = cvt_relu_bf16x2(__uint_as_float(r[q * 8 + 0]) + b0.x, __uint_as_float(r[q * 8 + 1]) + b0.y);
-          o.y = cvt_relu_bf16x2(__uint_as_float(r[q * 8 + 2]) + b0.z, __uint_as_float(r[q * 8 + 3]) + b0.w);
-          o.z = cvt_relu_bf16x2(__uint_as_float(r[q * 8 + 4]) + b1.x, __uint_as_float(r[q * 8 + 5]) + b1.y);
-          o.w = cvt_relu_bf16x2(__uint_as_float(r[q * 8 + 6]) + b1.z, __uint_as_float(r[q * 8 + 7]) + b1.w);
-          *reinterpret_cast<uint4 *>(a2buf + choff[q]) = o;
+          a2w[q * 4 + 0] = cvt_relu_bf16x2(__uint_as_float(r[q * 8 + 0]) + b0.x, __uint_as_float(r[q * 8 + 1]) + b0.y);
+          a2w[q * 4 + 1] = cvt_relu_bf16x2(__uint_as_float(r[q * 8 + 2]) + b0.z, __uint_as_float(r[q * 8 + 3]) + b0.w);
+          a2w[q * 4 + 2] = cvt_relu_bf16x2(__uint_as_float(r[q * 8 + 4]) + b1.x, __uint_as_float(r[q * 8 + 5]) + b1.y);
+          a2w[q * 4 + 3] = cvt_relu_bf16x2(__uint_as_float(r[q * 8 + 6]) + b1.z, __uint_as_float(r[q * 8 + 7]) + b1.w);
+          *reinterpret_cast<uint4 *>(a2buf + choff[q]) =
+              make_uint4(a2w[q * 4 + 0], a2w[q * 4 + 1], a2w[q * 4 + 2], a2w[q * 4 + 3]);
         }
       }
-      if (threadIdx.x == 64) CN_TRACE_AT(it, 10);
       fence_proxy_async_smem();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&bars.a2_ready));
       if (threadIdx.x == 64) CN_TRACE_AT(it, 11);
-      // ---- E1: g_t = g_a2 * [A2 > 0], in place over A2 (WB has finished reading it)
+      // ---- E1: g_t = g_a2 * [A2 > 0], over A2 (WB has finished reading it); dba += colsum(g_t)
       mbar_wait(smem_u32(&bars.g2wb_done), par);
       tc_fence_after();
       if (threadIdx.x == 64) CN_TRACE_AT(it, 12);
       {
         uint32_t r[32];
         tmem_ld32(t_acc1 + lane_off + cq * 32, r);
-        uint4 a[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) a[q] = *reinterpret_cast<const uint4 *>(a2buf + choff[q]);
         tmem_wait_ld();
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          uint4 o;
-          o.x = mul_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 0]), __uint_as_float(r[q * 8 + 1])), gt0_bf16x2(a[q].x));
-          o.y = mul_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 2]), __uint_as_float(r[q * 8 + 3])), gt0_bf16x2(a[q].y));
-          o.z = mul_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 4]), __uint_as_float(r[q * 8 + 5])), gt0_bf16x2(a[q].z));
-          o.w = mul_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 6]), __uint_as_float(r[q * 8 + 7])), gt0_bf16x2(a[q].w));
-          *reinterpret_cast<uint4 *>(a2buf + choff[q]) = o;
-        }
+        for (int j = 0; j < 16; ++j)
+          a2w[j] = mul_bf16x2(cvt_bf16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1])), gt0_bf16x2(a2w[j]));
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          *reinterpret_cast<uint4 *>(a2buf + choff[q]) =
+              make_uint4(a2w[q * 4 + 0], a2w[q * 4 + 1], a2w[q * 4 + 2], a2w[q * 4 + 3]);
       }
       fence_proxy_async_smem();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&bars.gt_ready));
       if (threadIdx.x == 64) CN_TRACE_AT(it, 14);
-      // ---- E2: g_h = g_y + g_a1 * [A1 > 0], in place over g_y (G2 / WB / bias sums have finished reading it)
-      mbar_wait(smem_u32(&bars.g1_ready), par);        // (the MMA thread saw gy_bias_done before it issued G1)
+      {
+        dba += colsum_bf16x2(a2w, lane);               // off the critical path: G1 is running
+      }
+      // ---- E2: g_h = g_y + g_a1 * [A1 > 0], in place over g_y (TMA store by the producer warp); dbb += colsum(g_y)
+      uint32_t gw[16];
+      {
+        uint4 g[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) g[q] = *reinterpret_cast<const uint4 *>(gybuf + choff[q]);  // (landed before G2)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          gw[q * 4 + 0] = g[q].x; gw[q * 4 + 1] = g[q].y; gw[q * 4 + 2] = g[q].z; gw[q * 4 + 3] = g[q].w;
+        }
+      }
+      {
+        uint32_t t16[16];                              // the butterfly consumes its input: work on a copy, while G1 runs
+#pragma unroll
+        for (int j = 0; j < 16; ++j) t16[j] = gw[j];
+        dbb += colsum_bf16x2(t16, lane);
+      }
+      mbar_wait(smem_u32(&bars.g1_ready), par);
       tc_fence_after();
       if (threadIdx.x == 64) CN_TRACE_AT(it, 15);
       {
         uint32_t r[32];
         tmem_ld32(t_acc1 + lane_off + cq * 32, r);
-        uint4 a[4], g[4];
+        uint4 a[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          a[q] = *reinterpret_cast<const uint4 *>(a1buf + choff[q]);
-          g[q] = *reinterpret_cast<const uint4 *>(gybuf + choff[q]);
-        }
+        for (int q = 0; q < 4; ++q) a[q] = *reinterpret_cast<const uint4 *>(a1buf + choff[q]);
         tmem_wait_ld();
         tc_fence_before();
         __syncwarp();
@@ -353,15 +364,15 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           uint4 o;
-          o.x = fma_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 0]), __uint_as_float(r[q * 8 + 1])), gt0_bf16x2(a[q].x), g[q].x);
-          o.y = fma_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 2]), __uint_as_float(r[q * 8 + 3])), gt0_bf16x2(a[q].y), g[q].y);
-          o.z = fma_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 4]), __uint_as_float(r[q * 8 + 5])), gt0_bf16x2(a[q].z), g[q].z);
-          o.w = fma_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 6]), __uint_as_float(r[q * 8 + 7])), gt0_bf16x2(a[q].w), g[q].w);
+          o.x = fma_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 0]), __uint_as_float(r[q * 8 + 1])), gt0_bf16x2(a[q].x), gw[q * 4 + 0]);
+          o.y = fma_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 2]), __uint_as_float(r[q * 8 + 3])), gt0_bf16x2(a[q].y), gw[q * 4 + 1]);
+          o.z = fma_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 4]), __uint_as_float(r[q * 8 + 5])), gt0_bf16x2(a[q].z), gw[q * 4 + 2]);
+          o.w = fma_bf16x2(cvt_bf16x2(__uint_as_float(r[q * 8 + 6]), __uint_as_float(r[q * 8 + 7])), gt0_bf16x2(a[q].w), gw[q * 4 + 3]);
           *reinterpret_cast<uint4 *>(gybuf + choff[q]) = o;
         }
       }
       fence_proxy_async_smem();
-      __syncwarp();
+      __syncwarp();                                  // every lane has consumed its A1 chunks and written g_h
       if (lane == 0) {
         mbar_arrive(smem_u32(&bars.free_a1[b]));
         mbar_arrive(smem_u32(&bars.gy_staged[b]));
@@ -382,6 +393,19 @@ mlp_block_bwd_kernel(const uint8_t *__restrict__ w_a_img, const uint8_t *__restr
         for (int q = 0; q < 8; ++q)
           red_add_f4(gdst + q * 4, __uint_as_float(r[q * 4 + 0]) * scale, __uint_as_float(r[q * 4 + 1]) * scale,
                      __uint_as_float(r[q * 4 + 2]) * scale, __uint_as_float(r[q * 4 + 3]) * scale);
+      }
+      // ---- bias gradients: the four row quadrants of a column meet in shared memory (the tiles are dead now),
+      // one atomic per column and CTA
+      float *red = reinterpret_cast<float *>(a2buf);   // [2 biases][4 quadrants][128 columns]
+      red[(0 * 4 + quad) * 128 + cq * 32 + lane] = dba;
+      red[(1 * 4 + quad) * 128 + cq * 32 + lane] = dbb;
+      named_bar_sync(1, kBwdEpiThreads);
+      const uint32_t et = threadIdx.x - 64;
+      if (et < 256) {
+        const uint32_t which = et >> 7, col = et & 127u;
+        const float v = red[(which * 4 + 0) * 128 + col] + red[(which * 4 + 1) * 128 + col] +
+                        red[(which * 4 + 2) * 128 + col] + red[(which * 4 + 3) * 128 + col];
+        atomicAdd((which == 0 ? g_ba : g_bb) + col, v * scale);
       }
     }
   }
