@@ -23,22 +23,30 @@
 
 namespace cn {
 
-constexpr int kFwdThreads = 576;                                   // 2 + 16 warps
+constexpr int kFwdThreads = 608;                                   // 2 + 16 warps + the X producer warp
 constexpr int kEpiThreads = 256;                                   // epilogue threads per tile
 constexpr int kMaxStageViews = 3;                                  // views staged in smem by the fusion prologue
 constexpr uint32_t kSmemAct = 0;                                   // 2 x 32 KiB
 constexpr uint32_t kSmemRing = 2 * CN_ACT_TILE_BYTES;
 constexpr uint32_t kSmemTabBytes = 7 * 128 * 4 + 512 * 4 + 16;
-// 8-slot ring of 16 KiB slabs: X slabs + weights (per-view stage); per-view tiles + weights (fusion stage)
+// Rings of 16 KiB slabs.  Fusion stage: ONE 8-slot ring (per-view tiles + weights).  Per-view stage: a 4-slot weight
+// ring and a 5-slot ring of X slabs with its own producer warp, so that the first X slabs of the NEXT pair stream in
+// from HBM while the blocks of this pair run.  tools/trace_mlp_fwd.py: the first Dense of a pair still takes ~9000 of
+// the pair's ~28000 cycles -- 80 KiB in flight against ~3500 cycles of loaded HBM latency is 23 B/clk, the SM's fair
+// share of HBM; the stage moves 224 KiB per tile through HBM (X in, 3 activation tiles + h3 out) and is bound by that.
 template <bool kFusion> struct FwdSmem {
-  static constexpr int kRingSlots = 8;
-  static constexpr uint32_t kTab = kSmemRing + kRingSlots * CN_SLAB_BYTES;
+  static constexpr int kRingSlots = kFusion ? 8 : 4;
+  static constexpr int kXSlots = kFusion ? 0 : 5;
+  static constexpr uint32_t kXRing = kSmemRing + kRingSlots * CN_SLAB_BYTES;
+  static constexpr uint32_t kTab = kXRing + kXSlots * CN_SLAB_BYTES;
   static constexpr uint32_t kBytes = kTab + kSmemTabBytes + 1024;  // + alignment slack
 };
 
 struct FwdBars {
   uint64_t full[8];
   uint64_t empty[8];
+  uint64_t xfull[8];
+  uint64_t xempty[8];
   uint64_t h_ready[2];
   uint64_t tmp_ready[2];
   uint64_t act_ready[2];
@@ -107,6 +115,10 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
       mbar_init(smem_u32(&bars.full[i]), 1);
       mbar_init(smem_u32(&bars.empty[i]), 1);
     }
+    for (int i = 0; i < L::kXSlots; ++i) {
+      mbar_init(smem_u32(&bars.xfull[i]), 1);
+      mbar_init(smem_u32(&bars.xempty[i]), 1);
+    }
     for (int t = 0; t < 2; ++t) {
       mbar_init(smem_u32(&bars.h_ready[t]), 1);
       mbar_init(smem_u32(&bars.tmp_ready[t]), 1);
@@ -152,12 +164,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
       for (int64_t p = blockIdx.x; p < n_pairs; p += gridDim.x, ++pi) {
         const bool valid1 = 2 * p + 1 < n_tiles;
         if (!kFusion) {
-          for (int kb = 0; kb < 6; ++kb) {
-            load(packed + kPackFwdW0 + kb * CN_SLAB_BYTES);
-            if (kb == 0) CN_TRACE_AT(pi, 20);
-            load(in_tiles + (2 * p) * (int64_t)CN_X_TILE_BYTES + kb * CN_SLAB_BYTES);
-            if (valid1) load(in_tiles + (2 * p + 1) * (int64_t)CN_X_TILE_BYTES + kb * CN_SLAB_BYTES);
-          }
+          for (int kb = 0; kb < 6; ++kb) load(packed + kPackFwdW0 + kb * CN_SLAB_BYTES);
           CN_TRACE_AT(pi, 21);
           for (int blk = 0; blk < 3; ++blk)
             for (int j = 0; j < 2; ++j) load_weights(blk, j);
@@ -170,6 +177,27 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
           for (int blk = 1; blk < 3; ++blk)
             for (int j = 0; j < 2; ++j) load_weights(blk, j);
         }
+      }
+    }
+  } else if (warp == 18) {
+    // =========================== X producer (per-view stage) ===========================
+    if (!kFusion && lane == 0) {
+      constexpr int kXS = L::kXSlots > 0 ? L::kXSlots : 1;
+      uint32_t xc = 0;
+      int64_t pi = 0;
+      for (int64_t p = blockIdx.x; p < n_pairs; p += gridDim.x, ++pi) {
+        const int nt = (2 * p + 1 < n_tiles) ? 2 : 1;
+        for (int kb = 0; kb < 6; ++kb)
+          for (int t = 0; t < nt; ++t) {
+            const uint32_t slot = xc % kXS;
+            mbar_wait(smem_u32(&bars.xempty[slot]), ((xc / kXS) & 1u) ^ 1u);
+            mbar_expect_tx(smem_u32(&bars.xfull[slot]), CN_SLAB_BYTES);
+            bulk_g2s(s_base + L::kXRing + slot * CN_SLAB_BYTES,
+                     in_tiles + (2 * p + t) * (int64_t)CN_X_TILE_BYTES + kb * CN_SLAB_BYTES, CN_SLAB_BYTES,
+                     smem_u32(&bars.xfull[slot]));
+            ++xc;
+            if (kb == 0 && t == 0) CN_TRACE_AT(pi, 20);
+          }
       }
     }
   } else if (warp == 1) {
@@ -185,6 +213,14 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         return slot;
       };
       auto slot_addr = [&](uint32_t slot) { return s_base + kSmemRing + slot * CN_SLAB_BYTES; };
+      constexpr int kXS = L::kXSlots > 0 ? L::kXSlots : 1;
+      uint32_t xcc = 0;
+      auto next_x_slot = [&]() -> uint32_t {
+        const uint32_t slot = xcc % kXS;
+        mbar_wait(smem_u32(&bars.xfull[slot]), (xcc / kXS) & 1u);
+        ++xcc;
+        return slot;
+      };
       // D(tmem) (+)= ACT[t] (2 slabs) . W (2 ring slots)
       auto gemm_act = [&](int t, uint32_t d_tmem, uint32_t s0, uint32_t s1, bool accumulate) {
         const uint32_t a_base = s_base + kSmemAct + t * CN_ACT_TILE_BYTES;
@@ -212,13 +248,14 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
           for (int kb = 0; kb < 6; ++kb) {
             const uint32_t sw = next_slot();
             for (int t = 0; t < nt; ++t) {
-              const uint32_t sx = next_slot();
+              const uint32_t sx = next_x_slot();
+              const uint32_t x_addr = s_base + L::kXRing + sx * CN_SLAB_BYTES;
               tc_fence_after();
 #pragma unroll
               for (int j = 0; j < 4; ++j)
-                umma_f16(tmem + t * 256, umma_desc(slot_addr(sx) + j * kKmajKstep, kKmajLbo, kSboBytes),
+                umma_f16(tmem + t * 256, umma_desc(x_addr + j * kKmajKstep, kKmajLbo, kSboBytes),
                          umma_desc(slot_addr(sw) + j * kKmajKstep, kKmajLbo, kSboBytes), idesc, (kb | j) ? 1u : 0u);
-              umma_commit(smem_u32(&bars.empty[sx]));
+              umma_commit(smem_u32(&bars.xempty[sx]));
               if (kb == 5) umma_commit(smem_u32(&bars.h_ready[t]));
             }
             umma_commit(smem_u32(&bars.empty[sw]));
@@ -260,7 +297,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         }
       }
     }
-  } else {
+  } else if (warp < 18) {
     // =========================== epilogue: 8 warps per tile ===========================
     const uint32_t e = warp - 2;                    // 0..15
     const int t = e >> 3;                           // tile slot of this warp
