@@ -3,7 +3,7 @@
 import json
 import sys
 
-d = json.load(open(sys.argv[1]))
+d = json.loads([l for l in open(sys.argv[1]).read().splitlines() if l.startswith('{')][-1])
 print(f"value {d['value']:.0f} {d['unit']}  ms/step {d['ms_per_step']:.3f}  e2e {d['e2e']['value']:.0f}  launches {d.get('gpu_launches')}"
       f"  clocks {d.get('clocks')}")
 print('roofline', d.get('roofline'))
