@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define CN_ABI_VERSION 3
+#define CN_ABI_VERSION 4
 #define CN_TILE_ROWS 128
 #define CN_HIDDEN 128
 #define CN_FEAT_C 256          /* combined_features channels (model_v0.py:60)            */
@@ -136,6 +136,16 @@ int cn_project_gather_bwd(const CnScene *scene, const float *ray_o, const float 
                           const float *z, int32_t nr, int32_t S, const void *dx_tiles, void *ws,
                           size_t ws_bytes, float *d_features, float *dz, void *stream);
 
+/* Same backward with the gradient w.r.t. the rays themselves: d_ray_o [b,nr,3] and d_ray_d [b,nr,3]
+ * (both +=, caller zero-fills; dz nullable, +=).  x = o + z d enters through the projection / posenc(p_cam)
+ * chain, d also through posenc(E^-1 [d;1]) (nerf_utils.py:84-105).  This is what the pose-query models need
+ * (DeltaNGF / LanguageNeRF / GraspMVNeRF `_call`, delta_ngf/model.py:196-232, and the pose gradient taken by
+ * DNGFOptimizer.optimize_pose, grasp_optimizer.py:158-184): a query point is a ray with S = 1, z = 0,
+ * origin = point (`poses[..., :3, 3]`), direction = approach axis (`poses[..., :3, :3] . z_dir`).        */
+int cn_project_gather_bwd_rays(const CnScene *scene, const float *ray_o, const float *ray_d,
+                               const float *z, int32_t nr, int32_t S, const void *dx_tiles, void *ws,
+                               size_t ws_bytes, float *dz, float *d_ray_o, float *d_ray_d, void *stream);
+
 /* Feature-map gradient of several passes in ONE sweep (e.g. coarse + fine): every texel of
  * d_features [b,nv,H,W,256] sums the rows of its four neighbouring cells of every set and is
  * written exactly once (accumulate = 0: the map needs no zero fill; accumulate = 1: +=).
@@ -180,6 +190,16 @@ int cn_mlp_feature_fwd(const void *packed, const void *x_tiles, int64_t n_tiles,
  *   acts (nullable): [n_out_tiles][4] activation tiles (3 x relu(h), relu(e)).           */
 int cn_mlp_fusion_fwd(const void *packed, const void *h3_tiles, int32_t b, int32_t nv,
                       int64_t tiles_per_view, float *rgbs, void *acts, void *stream);
+
+/* fusion stage with `complete_output` taps (layers.py:352,376-377; consumed as
+ * `fine_embedding(...)[4:]` by delta_ngf/model.py:240-241, lmvnerf/model_v4.py, grasp_mvnerf/model.py):
+ * taps [4][b*tiles_per_view*128][128] fp32 = (mean over views, output of fusion block 1, 2, 3), pre-activation.
+ * Everything else as cn_mlp_fusion_fwd.                                                       */
+int cn_mlp_fusion_fwd_taps(const void *packed, const void *h3_tiles, int32_t b, int32_t nv,
+                           int64_t tiles_per_view, float *rgbs, void *acts, float *taps, void *stream);
+/* g_tiles [n_tiles] (bf16 activation-tile images) = (accumulate ? g_tiles : 0) + rows [n_tiles*128][128] fp32:
+ * the gradient of a tapped stage output joins the gradient stream of cn_mlp_block_bwd.        */
+int cn_tile_add_rows(void *g_tiles, const float *rows, int64_t n_tiles, int32_t accumulate, void *stream);
 
 /* readout backward: d_y [rows,4] + relu(e) tiles -> g tiles (bf16), d(output_layer)
  * accumulated into grad (flat layout above).                                           */

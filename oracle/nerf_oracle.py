@@ -590,3 +590,176 @@ def synthetic_scene(seed: int, b: int, nv: int, nr: int, H: int, W: int, C: int 
     target = torch.rand((b, nr, 3), generator=g).to(dtype)
     return dict(inputs=inputs, features=feats, u_strat=u_strat, u_pdf=u_pdf, target=target,
                 pixels_rc=np.array(pix_rc))
+
+
+# --------------------------------------------------------------------------
+# Pose-query field: DeltaNGF / LanguageNeRF / GraspMVNeRF `_call` + GraspReadout
+# (src/lib/delta_ngf/model.py, src/lib/lmvnerf/model_v4.py, src/lib/grasp_mvnerf/model.py)
+# --------------------------------------------------------------------------
+
+
+def _affine_matrix(translation, euler_xyz=None) -> np.ndarray:
+    """``manipulation_tasks.transform.Affine(translation, rotation)`` for the two forms the models use
+    (dependencies/manipulation_tasks/manipulation_tasks/transform.py:11-23): identity rotation or
+    ``Rotation.from_euler('xyz', r)`` (scipy, as the reference)."""
+    from scipy.spatial.transform import Rotation
+    m = np.eye(4)
+    m[:3, 3] = np.array(translation)
+    m[:3, :3] = Rotation.from_quat((0, 0, 0, 1)).as_matrix() if euler_xyz is None else \
+        Rotation.from_euler('xyz', euler_xyz).as_matrix()
+    return m
+
+
+def transforms_to_check(n_5d_poses: int = 7) -> Tensor:
+    """The fixed query offsets of one grasp pose, [6 * n_5d_poses, 4, 4] fp32, base-major
+    (``delta_ngf/model.py:63-97``): 6 gripper bases x 7 steps along the local z axis."""
+    ox, oy, oz = 0.02, 0.015, 0.0125
+    step = (ox - 0.005) / ((n_5d_poses - 1) / 2)
+    bases = [_affine_matrix([0, oy, 0]), _affine_matrix([0, -oy, 0]),
+             _affine_matrix([-ox, oy, oz], [0.0, np.pi / 2, 0.0]), _affine_matrix([ox, oy, oz], [0.0, -np.pi / 2, 0.0]),
+             _affine_matrix([-ox, -oy, oz], [0.0, np.pi / 2, 0.0]), _affine_matrix([ox, -oy, oz], [0.0, -np.pi / 2, 0.0])]
+    c = int((n_5d_poses - 1) / 2)
+    steps = [_affine_matrix([0.0, 0.0, i * step]) for i in range(-c, c + 1)]
+    return torch.tensor(np.array([b @ t for b in bases for t in steps]), dtype=torch.float32)
+
+
+def rotation_from_quaternion(q: Tensor) -> Tensor:
+    """``tensorflow_graphics.geometry.transformation.rotation_matrix_3d.from_quaternion`` (third party,
+    unpinned version; call site ``delta_ngf/model.py:29``): q = [x, y, z, w], assumed normalised."""
+    x, y, z, w = q.unbind(-1)
+    tx, ty, tz = 2.0 * x, 2.0 * y, 2.0 * z
+    twx, twy, twz = tx * w, ty * w, tz * w
+    txx, txy, txz = tx * x, ty * x, tz * x
+    tyy, tyz, tzz = ty * y, tz * y, tz * z
+    m = torch.stack([1.0 - (tyy + tzz), txy - twz, txz + twy,
+                     txy + twz, 1.0 - (txx + tzz), tyz - twx,
+                     txz - twy, tyz + twx, 1.0 - (txx + tyy)], dim=-1)
+    return m.reshape(*q.shape[:-1], 3, 3)
+
+
+def t_m_to_h_matrix(translations: Tensor, rot: Tensor) -> Tensor:
+    """``delta_ngf/model.py:16-25``: [[R | t], [0 0 0 1]]."""
+    top = torch.cat([rot, translations[..., None]], dim=-1)
+    last = torch.tensor([0., 0., 0., 1.], dtype=top.dtype).expand(*top.shape[:-2], 1, 4)
+    return torch.cat([top, last], dim=-2)
+
+
+def compute_matrices(translations: Tensor, rotations: Tensor, rotation_representation: str = 'quaternion') -> Tensor:
+    """``DeltaNGF.compute_matrices`` (``delta_ngf/model.py:172-183``): the 6-d form normalises both vectors
+    WITHOUT orthogonalising the second one."""
+    if rotation_representation == 'quaternion':
+        return t_m_to_h_matrix(translations, rotation_from_quaternion(rotations))
+    if rotation_representation == '6d':
+        r1 = rotations[..., :3] / rotations[..., :3].norm(dim=-1, keepdim=True)
+        r2 = rotations[..., 3:] / rotations[..., 3:].norm(dim=-1, keepdim=True)
+        r3 = torch.linalg.cross(r1, r2, dim=-1)
+        return t_m_to_h_matrix(translations, torch.stack([r1, r2, r3], dim=-1))
+    raise ValueError('Unknown rotation representation: ' + rotation_representation)
+
+
+def grasp_readout_param_shapes(use_bias: bool = True):
+    """``GraspReadout`` variables (``delta_ngf/layers.py:8-28``): 582 337 parameters with use_bias."""
+    s = []
+    for i in range(1, 5):
+        s += [(f'activation_downscale_{i}.kernel', (128, 64)), (f'activation_downscale_{i}.bias', (64,))]
+    s += [('combined_activation_downscale.kernel', (256, 64)), ('combined_activation_downscale.bias', (64,))]
+    s += [('readout.0.layer_0.kernel', (2688, 128)), ('readout.0.layer_0.bias', (128,)),
+          ('readout.0.layer_1.kernel', (128, 64)), ('readout.0.layer_1.bias', (64,)),
+          ('readout.0.shortcut.kernel', (2688, 64)),
+          ('readout.1.layer_0.kernel', (64, 64)), ('readout.1.layer_0.bias', (64,)),
+          ('readout.1.layer_1.kernel', (64, 64)), ('readout.1.layer_1.bias', (64,)),
+          ('readout.2.output_layer.kernel', (64, 1))]
+    if use_bias:
+        s.append(('readout.2.output_layer.bias', (1,)))
+    return s
+
+
+def init_grasp_readout(seed: int, bias_std: float = 0.0, use_bias: bool = True, dtype=torch.float32) -> Dict[str, Tensor]:
+    """he_normal kernels (``delta_ngf/layers.py``; glorot for the combined downscale), zero biases."""
+    g = torch.Generator().manual_seed(seed)
+    p = {}
+    for name, shape in grasp_readout_param_shapes(use_bias):
+        full = f'grasp_readout.{name}'
+        if name.endswith('kernel'):
+            p[full] = (torch.randn(shape, generator=g) * math.sqrt(2.0 / shape[0])).to(dtype)
+        else:
+            p[full] = (torch.randn(shape, generator=g) * bias_std).to(dtype)
+    return p
+
+
+def grasp_readout(embeddings: Sequence[Tensor], p: Dict[str, Tensor], prefix: str = 'grasp_readout',
+                  activation: str = 'elu') -> Tensor:
+    """``GraspReadout.call`` (``delta_ngf/layers.py:30-42``; relu variant ``grasp_mvnerf/layers.py:22-31``):
+    4 x [b, np, n5, 128] -> [b, np]."""
+    act = F.elu if activation == 'elu' else F.relu
+    ds = [act(embeddings[i] @ p[f'{prefix}.activation_downscale_{i + 1}.kernel']
+              + p[f'{prefix}.activation_downscale_{i + 1}.bias']) for i in range(4)]
+    c = torch.cat(ds, dim=-1)
+    c = act(c @ p[f'{prefix}.combined_activation_downscale.kernel'] + p[f'{prefix}.combined_activation_downscale.bias'])
+    c = c.reshape(*c.shape[:-2], -1)                                   # 'b np n5 d -> b np (n5 d)'
+    y = resnet_mlp_block(c, p, f'{prefix}.readout.0', activation=activation,
+                         shortcut_kernel=p[f'{prefix}.readout.0.shortcut.kernel'])
+    y = resnet_mlp_block(y, p, f'{prefix}.readout.1', activation=activation)
+    y = F.relu(y) @ p[f'{prefix}.readout.2.output_layer.kernel']
+    if f'{prefix}.readout.2.output_layer.bias' in p:
+        y = y + p[f'{prefix}.readout.2.output_layer.bias']
+    return y[..., 0]
+
+
+def query_embeddings_from_points(images: Tensor, K: Tensor, Einv: Tensor, pts: Tensor, dirs: Tensor, features: Tensor,
+                                 p: Dict[str, Tensor], net: str = 'fine', quant: Optional[str] = None) -> List[Tensor]:
+    """the part of ``DeltaNGF._call`` between the query points and the ``GraspReadout``
+    (``delta_ngf/model.py:202-241``): world points / approach directions [b, n, 3] -> the last four
+    `complete_output` stage outputs of the fine embedding, each [b, n, 128]."""
+    b, nv = images.shape[:2]
+    n = pts.shape[1]
+    pix, cam = compute_pixel_in_image_mv(pts[:, :, None, :], K, Einv)    # [b, nv, n, 1, 2], [..., 4]
+    g = get_projection_features_mv(images * 2 - 1.0, features, pix)
+    cam_dirs = world_to_camera_direction_vector_mv(dirs, Einv)           # [b, nv, n, 3]
+    cam3 = cam.reshape(b * nv, n, 1, 4)[..., :3]
+    cam_dirs = cam_dirs.reshape(b * nv, n, 1, 3)
+    g = g.reshape(b * nv, n, 1, -1)
+    out = mv_embedding(cam3, cam_dirs, g, p, f'{net}_embedding', nv, complete_output=True, quant=quant)[4:]
+    return [o[:, :, 0] for o in out]
+
+
+def query_embeddings(images: Tensor, K: Tensor, Einv: Tensor, transforms: Tensor, features: Tensor,
+                     p: Dict[str, Tensor], net: str = 'fine', quant: Optional[str] = None,
+                     n_5d_poses: int = 7) -> List[Tensor]:
+    """``DeltaNGF._call`` up to the embeddings (``delta_ngf/model.py:188-241``): transforms [b, np, 4, 4] ->
+    the last four `complete_output` stage outputs, each [b, np, n5, 128]."""
+    b = images.shape[0]
+    n_pts = transforms.shape[1]
+    ttc = transforms_to_check(n_5d_poses).to(transforms.dtype)
+    n5 = ttc.shape[0]
+    poses = transforms[:, :, None] @ ttc[None, None]                   # [b, np, n5, 4, 4] (row order np, n5)
+    pts = poses[..., :3, 3].reshape(b, n_pts * n5, 3)
+    dirs = poses[..., :3, 2].reshape(b, n_pts * n5, 3)                 # R . z_dir
+    out = query_embeddings_from_points(images, K, Einv, pts, dirs, features, p, net, quant)
+    return [o.reshape(b, n_pts, n5, -1) for o in out]
+
+
+def query_call(images: Tensor, K: Tensor, Einv: Tensor, transforms: Tensor, features: Tensor,
+               p: Dict[str, Tensor], net: str = 'fine', quant: Optional[str] = None, activation: str = 'elu') -> Tensor:
+    """``DeltaNGF._call`` (``delta_ngf/model.py:188-245``) -> grasp_success [b, np]."""
+    return grasp_readout(query_embeddings(images, K, Einv, transforms, features, p, net, quant), p,
+                         activation=activation)
+
+
+def cosine_similarity_loss(y_true: Tensor, y_pred: Tensor) -> Tensor:
+    """``tf.keras.losses.CosineSimilarity(axis=-1)``: -mean(sum(l2norm(y_true) * l2norm(y_pred)))."""
+    def l2n(x):
+        return x * torch.rsqrt(torch.clamp((x * x).sum(-1, keepdim=True), min=1e-12))
+    return -(l2n(y_true) * l2n(y_pred)).sum(-1).mean()
+
+
+def synthetic_poses(seed: int, b: int, n_pts: int, representation: str = 'quaternion', dtype=torch.float32):
+    """grasp poses around the scene centre the synthetic cameras look at: translations, rotations"""
+    g = torch.Generator().manual_seed(seed + 17)
+    t = torch.tensor([0.6, 0.0, 0.1]) + (torch.rand((b, n_pts, 3), generator=g) - 0.5) * 0.1
+    if representation == 'quaternion':
+        q = torch.randn((b, n_pts, 4), generator=g)
+        r = q / q.norm(dim=-1, keepdim=True)
+    else:
+        r = torch.randn((b, n_pts, 6), generator=g)
+    return t.to(dtype), r.to(dtype)

@@ -47,3 +47,61 @@ def reference_call(inputs, combined_features, p, *, near, far, n_samples, u_stra
     out = mv.MVVNeRFRenderer._call(fake_self, tuple(inputs), nr, b, combined_features)
     assert not tf_shim._UNIFORM_QUEUE, 'the reference did not consume both random draws'
     return out
+
+
+def _set_block(blk, p, pre):
+    for l in ('layer_0', 'layer_1'):
+        _set_dense(getattr(blk, l), p[f'{pre}.{l}.kernel'], p[f'{pre}.{l}.bias'])
+    if blk.shortcut is not None:
+        _set_dense(blk.shortcut, p[f'{pre}.shortcut.kernel'], None)
+
+
+def build_reference_query_model(p: Dict[str, torch.Tensor], n_views: int, batch_size: int, n_points: int,
+                                which: str = 'delta_ngf', rotation_representation: str = 'quaternion'):
+    """the reference's ``DeltaNGF`` / ``GraspMVNeRF`` object (constructed by its own ``__init__``, so
+    ``transforms_to_check`` is the reference's) carrying the oracle's parameters.  The image encoder
+    (``VisualFeatures``: ViT + conv, outside the path -- its output is an input here) is stubbed out."""
+    md, _ly = tf_shim.load_reference_query(which)
+    md.VisualFeatures = lambda *a, **k: None
+    if which == 'delta_ngf':
+        model = md.DeltaNGF(n_views=n_views, batch_size=batch_size, n_points_train=n_points,
+                            rotation_representation=rotation_representation)
+    else:
+        model = md.GraspMVNeRF(n_views=n_views, n_points_train=n_points)
+    emb, pre = model.fine_embedding, 'fine_embedding'
+    _set_dense(emb.layer_0, p[f'{pre}.layer_0.kernel'], p[f'{pre}.layer_0.bias'])
+    for grp, blocks in (('feature_blocks', emb.feature_blocks), ('fusion_blocks', emb.fusion_blocks)):
+        for i, blk in enumerate(blocks):
+            _set_block(blk, p, f'{pre}.{grp}.{i}')
+    gr, pre = model.grasp_readout, 'grasp_readout'
+    for i in range(1, 5):
+        _set_dense(getattr(gr, f'activation_downscale_{i}'), p[f'{pre}.activation_downscale_{i}.kernel'],
+                   p[f'{pre}.activation_downscale_{i}.bias'])
+    _set_dense(gr.combined_activation_downscale, p[f'{pre}.combined_activation_downscale.kernel'],
+               p[f'{pre}.combined_activation_downscale.bias'])
+    seq = gr.readout.layers
+    _set_block(seq[0], p, f'{pre}.readout.0')
+    _set_block(seq[1], p, f'{pre}.readout.1')
+    _set_dense(seq[2].output_layer, p[f'{pre}.readout.2.output_layer.kernel'],
+               p.get(f'{pre}.readout.2.output_layer.bias'))
+    seq[2].output_layer.use_bias = f'{pre}.readout.2.output_layer.bias' in p
+    return model
+
+
+def reference_query_call(images, K, Einv, transforms, features, p, which: str = 'delta_ngf'):
+    """``DeltaNGF._call`` (delta_ngf/model.py:188-245) / ``GraspMVNeRF._call`` (grasp_mvnerf/model.py:113-158)
+    executed from the reference's source."""
+    b, nv = images.shape[:2]
+    n_points = transforms.shape[1]
+    model = build_reference_query_model(p, nv, b, n_points, which)
+    if which == 'delta_ngf':
+        return model._call((None, None, None, None, images, K, Einv), transforms, n_points, features)
+    return model._call((transforms, images, K, Einv), n_points, features)
+
+
+def reference_compute_matrices(translations, rotations, rotation_representation):
+    """``DeltaNGF.compute_matrices`` (delta_ngf/model.py:172-183) from the reference's source"""
+    md, _ = tf_shim.load_reference_query('delta_ngf')
+    fake = types.SimpleNamespace(rotation_representation=rotation_representation, translations=translations,
+                                 quaternions=rotations, six_d_rotations=rotations)
+    return md.DeltaNGF.compute_matrices(fake)

@@ -61,7 +61,18 @@ def _build_tf():
     tf.newaxis = None
     # dummy classes: einops probes `tensorflow.Tensor / Variable`; torch tensors must stay with its torch backend
     tf.Tensor = type('Tensor', (), {})
-    tf.Variable = type('Variable', (), {})
+
+    class Variable:
+        """tf.Variable(value, trainable=...) -> a leaf torch tensor (isinstance checks against this class stay False)"""
+        def __new__(cls, value, trainable=True, dtype=None, **k):
+            t = torch.as_tensor(np.asarray(value), dtype=_dtype(dtype)).clone()
+            return t.requires_grad_(bool(trainable) and t.is_floating_point())
+    tf.Variable = Variable
+    tf.tile = lambda x, multiples: x.repeat(*_ints(multiples))
+    tf.reshape = lambda x, shape: x.reshape(_ints(shape))
+    tf.linalg = types.SimpleNamespace(
+        normalize=lambda x, axis=-1: (x / x.norm(dim=axis, keepdim=True), x.norm(dim=axis, keepdim=True)),
+        cross=lambda a, b: torch.linalg.cross(a, b, dim=-1))
 
     def convert_to_tensor(x, dtype=None):
         return torch.as_tensor(np.asarray(x), dtype=_dtype(dtype)) if not torch.is_tensor(x) else x.to(_dtype(dtype) or x.dtype)
@@ -120,7 +131,7 @@ def _build_tf():
             assert list(u.shape) == _ints(shape), (u.shape, shape)
             return u
         return torch.rand(_ints(shape)) * (maxval - minval) + minval
-    tf.random = types.SimpleNamespace(uniform=uniform)
+    tf.random = types.SimpleNamespace(uniform=uniform, normal=lambda shape, **k: torch.randn(_ints(shape)))
 
     def function(*args, **kwargs):
         if len(args) == 1 and callable(args[0]) and not kwargs:
@@ -142,7 +153,7 @@ def _build_tf():
     class Dense(Layer):
         def __init__(self, units, use_bias=True, kernel_initializer='glorot_uniform', activation=None, **k):
             self.units, self.use_bias, self.kernel, self.bias = units, use_bias, None, None
-            assert activation is None
+            self.activation = {None: None, 'elu': torch.nn.functional.elu, 'relu': torch.relu}[activation]
 
         def build(self, in_dim, dtype=torch.float32):
             lim = (6.0 / (in_dim + self.units)) ** 0.5
@@ -153,7 +164,8 @@ def _build_tf():
             if self.kernel is None:
                 self.build(x.shape[-1], x.dtype)
             y = x @ self.kernel
-            return y + self.bias if self.use_bias else y
+            y = y + self.bias if self.use_bias else y
+            return y if self.activation is None else self.activation(y)
 
     class _Act(Layer):
         def __init__(self, fn):
@@ -164,10 +176,20 @@ def _build_tf():
 
     def _unsupported(name):
         class U(Layer):
-            def __init__(self, *a, **k):
+            """constructible (model constructors build their encoders), not callable"""
+            def call(self, *a, **k):
                 raise NotImplementedError(f'tf_shim: keras.layers.{name} is outside the hot path')
         U.__name__ = name
         return U
+
+    class Sequential(Layer):
+        def __init__(self, layers=None, **k):
+            self.layers = list(layers or [])
+
+        def call(self, x, *a, **k):
+            for l in self.layers:
+                x = l(x)
+            return x
 
     acts = types.SimpleNamespace(relu=torch.relu, softplus=torch.nn.functional.softplus, sigmoid=torch.sigmoid,
                                  elu=torch.nn.functional.elu)
@@ -177,11 +199,12 @@ def _build_tf():
               'MaxPool2D', 'Dropout', 'Add', 'Concatenate', 'Conv2DTranspose'):
         setattr(layers, n, _unsupported(n))
     keras = types.SimpleNamespace(
-        Model=Layer, layers=layers, activations=acts, Sequential=_unsupported('Sequential'),
+        Model=Layer, layers=layers, activations=acts, Sequential=Sequential,
         optimizers=types.SimpleNamespace(schedules=types.SimpleNamespace(LearningRateSchedule=object), Adam=object),
         utils=types.SimpleNamespace(Sequence=object),
         metrics=types.SimpleNamespace(Mean=lambda name=None: None),
-        losses=types.SimpleNamespace(MeanSquaredError=lambda: (lambda y, p: torch.mean((p - y) ** 2))),
+        losses=types.SimpleNamespace(MeanSquaredError=lambda: (lambda y, p: torch.mean((p - y) ** 2)),
+                                     CosineSimilarity=lambda axis=-1: None),
         models=types.SimpleNamespace(load_model=lambda *a, **k: (_ for _ in ()).throw(NotImplementedError('CLIP weights'))))
     tf.keras = keras
     return tf
@@ -214,6 +237,18 @@ def install():
     sys.modules['tensorflow_addons'] = tfa
     sys.modules['tensorflow_addons.image'] = tfa.image
     sys.modules['tensorflow_addons.optimizers'] = tfa.optimizers
+    # tensorflow_graphics (third party, not in the reference tree): only rotation_matrix_3d.from_quaternion is
+    # used (delta_ngf/model.py:29); it maps to the oracle's restatement of the published formula
+    tfg = types.ModuleType('tensorflow_graphics')
+    tfg.geometry = types.ModuleType('tensorflow_graphics.geometry')
+    tfg.geometry.transformation = types.ModuleType('tensorflow_graphics.geometry.transformation')
+    tfg.geometry.transformation.rotation_matrix_3d = types.SimpleNamespace(from_quaternion=O.rotation_from_quaternion)
+    sys.modules['tensorflow_graphics'] = tfg
+    sys.modules['tensorflow_graphics.geometry'] = tfg.geometry
+    sys.modules['tensorflow_graphics.geometry.transformation'] = tfg.geometry.transformation
+    dep = os.path.join(REFERENCE_ROOT, 'dependencies', 'manipulation_tasks')
+    if os.path.isdir(dep) and dep not in sys.path:
+        sys.path.append(dep)          # the reference's own Affine (numpy / scipy only)
     for opt in ('ftfy', 'matplotlib', 'matplotlib.pyplot', 'PIL', 'PIL.Image'):
         try:
             importlib.import_module(opt)
@@ -240,3 +275,10 @@ def load_reference():
     ly = importlib.import_module('refsrc.lib.mvnerf.layers')
     mv = importlib.import_module('refsrc.lib.mvnerf.model_v0')
     return nu, ly, mv
+
+
+def load_reference_query(which: str = 'delta_ngf'):
+    """the reference's pose-query model module and its GraspReadout layers module:
+    'delta_ngf' -> (delta_ngf.model, delta_ngf.layers), 'grasp_mvnerf' -> (grasp_mvnerf.model, grasp_mvnerf.layers)"""
+    load_reference()
+    return (importlib.import_module(f'refsrc.lib.{which}.model'), importlib.import_module(f'refsrc.lib.{which}.layers'))

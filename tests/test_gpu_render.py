@@ -29,13 +29,13 @@ def _report(tag, errs, tol_out=1e-2, tol_grad=2e-2, skip=()):
     assert not bad, bad
 
 
-@pytest.mark.parametrize('nv', [1, 3])
-def test_coarse_pass_gradients(cuda, nv):
+@pytest.mark.parametrize('nv,b', [(1, 1), (3, 1), (2, 2)])
+def test_coarse_pass_gradients(cuda, nv, b):
     """loss = MSE(coarse rgb): stratified z is identical on both sides, so every coarse-net
     gradient and the feature-map gradient must agree with the (bf16-operand) oracle."""
     from clipnerf_b200 import params
     from oracle import nerf_oracle as O
-    sc = O.synthetic_scene(11, 1, nv, 32, 48, 64)
+    sc = O.synthetic_scene(11, b, nv, 32, 48, 64)
     named = O.init_params(5, bias_std=0.02)
     p = {k: v.clone().requires_grad_(True) for k, v in named.items()}
     feats = sc['features'].clone().requires_grad_(True)

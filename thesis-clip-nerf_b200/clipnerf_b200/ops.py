@@ -163,6 +163,17 @@ def project_gather_bwd(scene: Scene, ray_o, ray_d, z, dx_tiles, d_features: Opti
          _ptr(ws), ws.numel(), _ptr(d_features), _ptr(dz), _stream(), extra_launches=n_kernels)
 
 
+def project_gather_bwd_rays(scene: Scene, ray_o, ray_d, z, dx_tiles, ws: torch.Tensor, need_dz: bool = False):
+    """(d_ray_o [b,nr,3], d_ray_d [b,nr,3], dz [b,nr,S] or None) of the rows whose MLP-input gradient is ``dx_tiles``."""
+    ray_o, ray_d, z = _f32c(ray_o), _f32c(ray_d), _f32c(z)
+    b, nr, S = z.shape
+    d_o, d_d = torch.zeros_like(ray_o), torch.zeros_like(ray_d)
+    dz = torch.zeros_like(z) if need_dz else None
+    call('cn_project_gather_bwd_rays', ctypes.byref(scene.c), _ptr(ray_o), _ptr(ray_d), _ptr(z), nr, S, _ptr(dx_tiles),
+         _ptr(ws), ws.numel(), _ptr(dz), _ptr(d_o), _ptr(d_d), _stream())
+    return d_o, d_d, dz
+
+
 def feature_grad(scene: Scene, sets, d_features: torch.Tensor, accumulate: bool) -> None:
     """d_features (+)= feature-map gradient of every (ws, dx_tiles, nr, S) in ``sets`` in one sweep."""
     n = len(sets)
@@ -234,6 +245,32 @@ def mlp_fusion_fwd(packed, h3_tiles, b: int, nv: int, save_acts: bool):
     return rgbs, acts
 
 
+def mlp_fusion_fwd_taps(packed, h3_tiles, b: int, nv: int, save_acts: bool):
+    """fusion stage returning the four `complete_output` stage outputs: taps [4, b*tpv*128, 128] fp32."""
+    nt = h3_tiles.numel() // ACT_TILE_BYTES
+    assert nt % (b * nv) == 0
+    tpv = nt // (b * nv)
+    rows = b * tpv * TILE_ROWS
+    rgbs = torch.empty(rows, 4, dtype=torch.float32, device=h3_tiles.device)
+    taps = torch.empty(4, rows, 128, dtype=torch.float32, device=h3_tiles.device)
+    acts = _bytes(b * tpv * FUSION_ACTS * ACT_TILE_BYTES, h3_tiles.device) if save_acts else None
+    call('cn_mlp_fusion_fwd_taps', _ptr(packed), _ptr(h3_tiles), b, nv, tpv, _ptr(rgbs), _ptr(acts), _ptr(taps),
+         _stream())
+    return taps, rgbs, acts
+
+
+def tile_add_rows(g_tiles: Optional[torch.Tensor], rows: torch.Tensor) -> torch.Tensor:
+    """g_tiles (bf16 tile images; created when None) (+)= rows [n_tiles*128, 128] fp32"""
+    rows = _f32c(rows)
+    assert rows.shape[-1] == 128
+    nt = n_tiles(rows.numel() // 128)
+    acc = g_tiles is not None
+    if g_tiles is None:
+        g_tiles = _bytes(nt * ACT_TILE_BYTES, rows.device)
+    call('cn_tile_add_rows', _ptr(g_tiles), _ptr(rows), nt, int(acc), _stream())
+    return g_tiles
+
+
 def mlp_readout_bwd(params, d_y, acts, act_stride: int, act_index: int, grad):
     nt = d_y.numel() // (4 * TILE_ROWS)
     g = _bytes(nt * ACT_TILE_BYTES, d_y.device)
@@ -243,13 +280,14 @@ def mlp_readout_bwd(params, d_y, acts, act_stride: int, act_index: int, grad):
 
 
 def mlp_block_bwd(packed, blk: int, acts, act_stride: int, act_index: int, gy_tiles, grad, gh_tiles=None,
-                  views: int = 1, scale: float = 1.0):
+                  views: int = 1, scale: float = 1.0, b: int = 1):
     """views > 1: ``gy_tiles`` is the fusion-stage gradient [b][tiles_per_view], shared by the ``views`` per-view
     tiles of every row tile (mean over views, layers.py:368-370); the result goes to a new per-view buffer."""
     nt = gy_tiles.numel() // ACT_TILE_BYTES
     tpv = 0
     if views > 1:
-        tpv = nt            # tiles per view summed over scenes: scenes are contiguous, so b folds into the index
+        assert nt % b == 0
+        tpv = nt // b       # gy_tiles is [b][tpv]; per-view tile (b, v, t) reads fusion tile (b, t)
         nt = nt * views
         assert gh_tiles is None
         gh_tiles = _bytes(nt * ACT_TILE_BYTES, gy_tiles.device)

@@ -1,0 +1,108 @@
+"""Differentiable pose-query call on the sm_100a kernels.
+
+``query_embeddings`` replaces everything of ``DeltaNGF._call`` / ``LanguageNeRF._call`` /
+``GraspMVNeRF._call`` between the pose matrices and the ``GraspReadout`` (reference
+``src/lib/delta_ngf/model.py:188-241``, ``lmvnerf/model_v4.py:208-261``,
+``grasp_mvnerf/model.py:113-155``): the 42 fixed query offsets of every pose are projected into the
+source views, the 259-channel map is gathered bilinearly, points and approach directions are
+position-encoded and the fine embedding runs with ``complete_output`` -- the same gather and
+tcgen05 MLP kernels as the render path, on rows with one sample per "ray" (S = 1, z = 0,
+origin = query point, direction = approach axis).  The backward returns the gradient with respect
+to the query points and directions (what ``DNGFOptimizer.optimize_pose`` and the gradient-matching
+loss of ``DeltaNGF.train_step`` differentiate), the embedding parameters and the feature maps."""
+from __future__ import annotations
+
+from typing import List
+
+import torch
+
+from . import ops
+from ._abi import NET_PARAMS, TILE_ROWS
+
+
+def _pad_rows(t: torch.Tensor, n_pad: int) -> torch.Tensor:
+    """[b, n, c] -> [b, n_pad, c]; the padding repeats row 0 (any valid point: its outputs are dropped)"""
+    b, n, c = t.shape
+    if n == n_pad:
+        return t.contiguous()
+    return torch.cat([t, t[:, :1].expand(b, n_pad - n, c)], dim=1).contiguous()
+
+
+class _QueryEmbedFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, params, features, images, intrinsics, extr_inv, points, dirs):
+        need_grad = any(ctx.needs_input_grad)
+        scene = ops.Scene(images, features, intrinsics, extr_inv)
+        b, n, _ = points.shape
+        n_pad = (n + TILE_ROWS - 1) // TILE_ROWS * TILE_ROWS
+        pts, drs = _pad_rows(ops._f32c(points), n_pad), _pad_rows(ops._f32c(dirs), n_pad)
+        z = torch.zeros(b, n_pad, 1, dtype=torch.float32, device=pts.device)
+        packed = ops.pack_weights(params)
+        x, ws = ops.project_gather_fwd(scene, pts, drs, z, return_ws=True)
+        h3, acts_f = ops.mlp_feature_fwd(packed, x, need_grad)
+        taps, _rgbs, acts_u = ops.mlp_fusion_fwd_taps(packed, h3, b, scene.nv, need_grad)
+        if need_grad:
+            ctx.scene, ctx.packed, ctx.n = scene, packed, n
+            ctx.saved = (pts, drs, z, x, ws, acts_f, acts_u)
+        return tuple(taps.view(4, b, n_pad, 128)[:, :, :n].unbind(0))
+
+    @staticmethod
+    def backward(ctx, *g_taps):
+        scene, packed, n = ctx.scene, ctx.packed, ctx.n
+        pts, drs, z, x, ws, acts_f, acts_u = ctx.saved
+        b, n_pad = z.shape[:2]
+        dev = z.device
+        grad = torch.zeros(NET_PARAMS, dtype=torch.float32, device=dev)
+
+        def rows(i):
+            g = g_taps[i]
+            g = torch.zeros(b, n, 128, dtype=torch.float32, device=dev) if g is None else g.to(torch.float32)
+            if n_pad != n:
+                g = torch.cat([g, torch.zeros(b, n_pad - n, 128, dtype=torch.float32, device=dev)], dim=1)
+            return g.reshape(b * n_pad, 128).contiguous()
+
+        # the gradient of every tapped stage output joins the bf16 gradient stream where the stage was produced
+        g = ops.tile_add_rows(None, rows(3))
+        for blk in (5, 4, 3):
+            ops.mlp_block_bwd(packed, blk, acts_u, ops.FUSION_ACTS, blk - 3, g, grad)
+            ops.tile_add_rows(g, rows(blk - 3))
+        s = 1.0 / scene.nv
+        gf = ops.mlp_block_bwd(packed, 2, acts_f, ops.FEATURE_ACTS, 2, g, grad, views=scene.nv, scale=s, b=scene.b) \
+            if scene.nv > 1 else ops.mlp_block_bwd(packed, 2, acts_f, ops.FEATURE_ACTS, 2, g, grad)
+        for blk in (1, 0):
+            ops.mlp_block_bwd(packed, blk, acts_f, ops.FEATURE_ACTS, blk, gf, grad, scale=s)
+        if ctx.needs_input_grad[0]:
+            ops.mlp_l0_wgrad(x, gf, grad, s)
+        d_features = d_pts = d_dirs = None
+        if ctx.needs_input_grad[1] or ctx.needs_input_grad[5] or ctx.needs_input_grad[6]:
+            dx = ops.mlp_l0_dgrad(packed, gf, s)
+            if ctx.needs_input_grad[5] or ctx.needs_input_grad[6]:
+                d_o, d_d, _ = ops.project_gather_bwd_rays(scene, pts, drs, z, dx, ws)
+                d_pts, d_dirs = d_o[:, :n], d_d[:, :n]
+            if ctx.needs_input_grad[1]:
+                d_features = torch.empty_like(scene.features)
+                ops.feature_grad(scene, [(ws, dx, n_pad, 1)], d_features, accumulate=False)
+        ctx.saved = ctx.scene = ctx.packed = None
+        return (grad if ctx.needs_input_grad[0] else None), d_features, None, None, None, d_pts, d_dirs
+
+
+def query_embeddings(params_fine: torch.Tensor, images, intrinsics, extr_inv, combined_features, points, dirs
+                     ) -> List[torch.Tensor]:
+    """``fine_embedding([camera_points, camera_directions, gathered])[4:]`` for world-frame query points.
+
+    params_fine: flat parameter vector of one net (``params.py``; the RenderReadout tail is unused);
+    images [b,nv,H,W,3] in [0,1], intrinsics / extr_inv [b,nv,4,4], combined_features [b,nv,H,W,256];
+    points, dirs [b, n, 3] (world frame).  Returns 4 tensors [b, n, 128] (mean over views and the outputs
+    of the three fusion blocks)."""
+    assert points.shape == dirs.shape and points.shape[-1] == 3
+    return list(_QueryEmbedFn.apply(params_fine, combined_features, images, intrinsics, extr_inv, points, dirs))
+
+
+def pose_query_points(transforms: torch.Tensor, transforms_to_check: torch.Tensor):
+    """poses = transforms . transforms_to_check (delta_ngf/model.py:199-200, 221): transforms [b, np, 4, 4],
+    transforms_to_check [n5, 4, 4] -> query points and approach directions [b, np * n5, 3] in the row order
+    '(np n5)' the embedding / GraspReadout use (model.py:228-238).  Tiny host-side torch algebra (np * n5 4x4
+    products); autograd carries the pose gradient through it."""
+    poses = transforms[:, :, None] @ transforms_to_check[None, None].to(transforms.dtype)
+    b, n_pts, n5 = poses.shape[:3]
+    return poses[..., :3, 3].reshape(b, n_pts * n5, 3), poses[..., :3, 2].reshape(b, n_pts * n5, 3)

@@ -45,7 +45,7 @@ def _pass_bwd(P: _Pass, params, grad, scene: ops.Scene, ray_o, ray_d, d_rgb, d_d
     # mean over views: every per-view tile reads the fusion-stage gradient tile itself; the factor 1/nv is
     # applied in fp32 wherever the per-view stage leaves the bf16 g stream (weight / bias gradients, dX)
     s = 1.0 / scene.nv
-    gf = ops.mlp_block_bwd(P.packed, 2, P.acts_f, ops.FEATURE_ACTS, 2, g, grad, views=scene.nv, scale=s) \
+    gf = ops.mlp_block_bwd(P.packed, 2, P.acts_f, ops.FEATURE_ACTS, 2, g, grad, views=scene.nv, scale=s, b=scene.b) \
         if scene.nv > 1 else ops.mlp_block_bwd(P.packed, 2, P.acts_f, ops.FEATURE_ACTS, 2, g, grad)
     for blk in (1, 0):
         ops.mlp_block_bwd(P.packed, blk, P.acts_f, ops.FEATURE_ACTS, blk, gf, grad, scale=s)

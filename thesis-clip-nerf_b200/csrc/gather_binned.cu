@@ -765,7 +765,8 @@ feature_grad_heavy_kernel(CnScene sc, GradArgs a, float *__restrict__ d_features
 __global__ void __launch_bounds__(128)
 project_dz_kernel(CnScene sc, const float *__restrict__ ray_o, const float *__restrict__ ray_d,
                   const float *__restrict__ z, int nr, int S, const uint8_t *__restrict__ dx_tiles,
-                  const float2 *__restrict__ gpix, float *__restrict__ dz) {
+                  const float2 *__restrict__ gpix, float *__restrict__ dz, float *__restrict__ d_ray_o,
+                  float *__restrict__ d_ray_d) {
   __shared__ __align__(1024) uint8_t sx[2 * CN_SLAB_BYTES];  // slabs 4 and 5 of this dX tile
   __shared__ __align__(8) uint64_t bar;
   const int tid = threadIdx.x;
@@ -829,12 +830,43 @@ project_dz_kernel(CnScene sc, const float *__restrict__ ray_o, const float *__re
   const float dq2 = (pr.q[2] >= 1e-8f) ? -(gpx * pr.rx + gpy * pr.ry) / pr.den : 0.f;
 #pragma unroll
   for (int j = 0; j < 3; ++j) dp[j] += K[0 + j] * dq0 + K[4 + j] * dq1 + K[8 + j] * dq2;
-  // p = E [o + z d; 1]  ->  dp_i/dz = sum_j E_ij d_j
-  float acc = 0.f;
+  // p = E [o + z d; 1]  ->  d/dx_j = sum_i dp_i E_ij,  d/dz = sum_j (d/dx_j) d_j
+  float gx[3];
 #pragma unroll
-  for (int ii = 0; ii < 3; ++ii)
-    acc += dp[ii] * (E[4 * ii + 0] * rc.d[0] + E[4 * ii + 1] * rc.d[1] + E[4 * ii + 2] * rc.d[2]);
-  atomicAdd(dz + id.n, acc);
+  for (int j = 0; j < 3; ++j) gx[j] = dp[0] * E[j] + dp[1] * E[4 + j] + dp[2] * E[8 + j];
+  if (dz) atomicAdd(dz + id.n, gx[0] * rc.d[0] + gx[1] * rc.d[1] + gx[2] * rc.d[2]);
+  if (d_ray_o) {
+    // pose-query models (delta_ngf/model.py:196-232): the query point is the ray origin and its approach
+    // direction the ray direction; d/d(origin) = d/dx, d/d(direction) = z d/dx + E3^T d/d(dcam), the latter
+    // from the posenc(direction) columns of dX (slab 4 words 30,31 and slab 5 words 0..27)
+    const float zz = z[id.n];
+    float dd[3] = {0.f, 0.f, 0.f};
+    float dcam[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) dcam[c] = dot4_rn(E + 4 * c, rc.d[0], rc.d[1], rc.d[2], 1.f);
+    const uint4 v7 = *reinterpret_cast<const uint4 *>(my4 + ((7u ^ sw) << 4));
+    uint32_t w[30];
+    w[0] = v7.z;
+    w[1] = v7.w;
+#pragma unroll
+    for (int q = 0; q < 7; ++q) {
+      const uint4 v = *reinterpret_cast<const uint4 *>(my5 + ((q ^ sw) << 4));
+      w[2 + 4 * q] = v.x; w[3 + 4 * q] = v.y; w[4 + 4 * q] = v.z; w[5 + 4 * q] = v.w;
+    }
+#pragma unroll
+    for (int l = 0; l < 30; ++l) {
+      const int c = l / 10, k = l % 10;
+      const float fk = pe_freq(k);
+      float s, co;
+      sincos_posenc(__fmul_rn(dcam[c], fk), s, co);
+      dd[c] += fk * (bf16_lo(w[l]) * co - bf16_hi(w[l]) * s);
+    }
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      atomicAdd(d_ray_o + id.ray * 3 + j, gx[j]);
+      atomicAdd(d_ray_d + id.ray * 3 + j, zz * gx[j] + dd[0] * E[j] + dd[1] * E[4 + j] + dd[2] * E[8 + j]);
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -971,7 +1003,7 @@ extern "C" int cn_project_gather_bwd(const CnScene *scene, const float *ray_o, c
   if (dz) {
     if (int e = run_tile_rows<true>(scene, g, kHdrCurZg, (uint8_t *)dx_tiles, st)) return e;
     project_dz_kernel<<<(unsigned)(g.rows / 128), 128, 0, st>>>(*scene, ray_o, ray_d, z, nr, S,
-                                                               (const uint8_t *)dx_tiles, g.gpix, dz);
+                                                               (const uint8_t *)dx_tiles, g.gpix, dz, nullptr, nullptr);
     if (int e = check_launch("cn_project_gather_bwd (dz)")) return e;
   }
   if (d_features) {
@@ -980,6 +1012,27 @@ extern "C" int cn_project_gather_bwd(const CnScene *scene, const float *ray_o, c
     if (int e = run_feature_grad(scene, 1, &gp, &dxp, d_features, 1, st)) return e;
   }
   return 0;
+}
+
+extern "C" int cn_project_gather_bwd_rays(const CnScene *scene, const float *ray_o, const float *ray_d, const float *z,
+                                          int32_t nr, int32_t S, const void *dx_tiles, void *ws, size_t ws_bytes,
+                                          float *dz, float *d_ray_o, float *d_ray_d, void *stream) {
+  using namespace cn;
+  if (int e = check_scene(scene, "cn_project_gather_bwd_rays")) return e;
+  CN_REQUIRE(ray_o && ray_d && z && dx_tiles && d_ray_o && d_ray_d, "cn_project_gather_bwd_rays: null pointer");
+  CN_REQUIRE(((uintptr_t)dx_tiles & 127) == 0, "cn_project_gather_bwd_rays: dx_tiles must be 128-byte aligned");
+  Ws g;
+  if (int e = get_ws(scene, nr, S, ws, ws_bytes, "cn_project_gather_bwd_rays", &g)) return e;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t ce = cudaMemsetAsync(g.hdr + kHdrCurZg, 0, sizeof(int), st);
+  if (ce != cudaSuccess) {
+    set_error("cn_project_gather_bwd_rays: cudaMemsetAsync: %s", cudaGetErrorString(ce));
+    return (int)ce;
+  }
+  if (int e = run_tile_rows<true>(scene, g, kHdrCurZg, (uint8_t *)dx_tiles, st)) return e;
+  project_dz_kernel<<<(unsigned)(g.rows / 128), 128, 0, st>>>(*scene, ray_o, ray_d, z, nr, S, (const uint8_t *)dx_tiles,
+                                                             g.gpix, dz, d_ray_o, d_ray_d);
+  return check_launch("cn_project_gather_bwd_rays");
 }
 
 extern "C" int cn_feature_grad(const CnScene *scene, int32_t n_sets, const int32_t *nr, const int32_t *S,

@@ -56,9 +56,11 @@ struct FwdBars {
 
 // TMEM accumulator (this thread's lane, 64 columns of half `half`) + bias -> (ReLU) -> bf16 half row
 // of the swizzled activation tile in shared memory.  Both 32-column loads are issued before the wait.
+// `tap` (optional): this row's 128 fp32 pre-activation values (h + bias) are also written there -- the stage
+// outputs MVResNetMLPNeRFEmbedding(complete_output=True) returns (layers.py:364-377).
 template <bool kRelu>
 __device__ __forceinline__ void epi_tmem_to_act(uint32_t taddr, const float *__restrict__ bias, uint8_t *act,
-                                                uint32_t row, uint32_t half) {
+                                                uint32_t row, uint32_t half, float *__restrict__ tap = nullptr) {
   uint32_t r[64];
   tmem_ld32(taddr + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
   tmem_ld32(taddr + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
@@ -72,6 +74,10 @@ __device__ __forceinline__ void epi_tmem_to_act(uint32_t taddr, const float *__r
     v[2] = __uint_as_float(r[q * 8 + 2]) + b0.z; v[3] = __uint_as_float(r[q * 8 + 3]) + b0.w;
     v[4] = __uint_as_float(r[q * 8 + 4]) + b1.x; v[5] = __uint_as_float(r[q * 8 + 5]) + b1.y;
     v[6] = __uint_as_float(r[q * 8 + 6]) + b1.z; v[7] = __uint_as_float(r[q * 8 + 7]) + b1.w;
+    if (tap) {
+      *reinterpret_cast<float4 *>(tap + half * 64 + q * 8) = make_float4(v[0], v[1], v[2], v[3]);
+      *reinterpret_cast<float4 *>(tap + half * 64 + q * 8 + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    }
     uint4 o;
     if (kRelu)  // relu folded into the conversion (F2FP.RELU): the epilogue is issue bound
       o = make_uint4(cvt_relu_bf16x2(v[0], v[1]), cvt_relu_bf16x2(v[2], v[3]), cvt_relu_bf16x2(v[4], v[5]),
@@ -86,7 +92,7 @@ template <bool kFusion>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ in_tiles, int64_t n_tiles,
                int nv, int64_t tiles_per_view, uint8_t *__restrict__ out_tiles, float *__restrict__ rgbs,
-               uint8_t *__restrict__ acts) {
+               uint8_t *__restrict__ acts, float *__restrict__ taps) {
   using L = FwdSmem<kFusion>;
   constexpr int kRingSlots = L::kRingSlots;
   extern __shared__ uint8_t smem_raw[];
@@ -346,6 +352,9 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
       const int64_t tile = 2 * p + t;
       if (tile >= n_tiles) break;
       uint8_t *my_acts = acts ? acts + tile * (int64_t)kActsPerTile * CN_ACT_TILE_BYTES : nullptr;
+      // fusion stage, pose-query models: taps[s][row][128] fp32, s = (mean, block 4, block 5, block 6 output)
+      const int64_t tap_stride = n_tiles * (int64_t)(128 * 128);
+      float *my_tap = (kFusion && taps) ? taps + (tile * 128 + row) * 128 : nullptr;
 
       if (kFusion) {
         // ---- mean over views -> fp32 residual stream in TMEM, relu(mean) -> first MMA operand
@@ -382,8 +391,13 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
             for (int i = 0; i < 8; ++i) {
               m[i] = acc[i] * inv_nv;
               r[q * 8 + i] = __float_as_uint(m[i]);
-              m[i] = fmaxf(m[i], 0.f);
             }
+            if (my_tap) {
+              *reinterpret_cast<float4 *>(my_tap + chunk * 8) = make_float4(m[0], m[1], m[2], m[3]);
+              *reinterpret_cast<float4 *>(my_tap + chunk * 8 + 4) = make_float4(m[4], m[5], m[6], m[7]);
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) m[i] = fmaxf(m[i], 0.f);
             *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, chunk)) =
                 make_uint4(pack_bf16x2(m[0], m[1]), pack_bf16x2(m[2], m[3]), pack_bf16x2(m[4], m[5]),
                            pack_bf16x2(m[6], m[7]));
@@ -409,7 +423,8 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         if (!(kFusion && blk == 0)) {
           // E_a: relu(h + cumulative bias) -> operand of the block's first Dense
           acquire();
-          epi_tmem_to_act<true>(t_h, tab + (2 * blk) * 128, act, row, half);
+          epi_tmem_to_act<true>(t_h, tab + (2 * blk) * 128, act, row, half,
+                                (kFusion && my_tap) ? my_tap + blk * tap_stride : nullptr);
           publish(my_acts ? my_acts + blk * CN_ACT_TILE_BYTES : nullptr, true);
           if (tr && blk == 0) CN_TRACE_AT(pi, 9);
         }
@@ -459,6 +474,15 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
               ya += v[i] * w.x;
               yb += v[i] * w.y;
             }
+            if (my_tap && mine) {
+              // e itself (pre-ReLU) is the tap; v[] holds relu(e), so re-add from the accumulator
+              float ev[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) ev[i] = __uint_as_float(r[q * 8 + i]) + tab[6 * 128 + c4 * 32 + q * 8 + i];
+              float *dst = my_tap + 3 * tap_stride + c4 * 32 + q * 8;
+              *reinterpret_cast<float4 *>(dst) = make_float4(ev[0], ev[1], ev[2], ev[3]);
+              *reinterpret_cast<float4 *>(dst + 4) = make_float4(ev[4], ev[5], ev[6], ev[7]);
+            }
             if (my_acts && mine)
               *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, c4 * 4 + q)) =
                   make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
@@ -486,7 +510,8 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
 CN_TRACE_READER(cn_debug_read_trace_fwd)
 
 static int launch_fwd(bool fusion, const void *packed, const void *in_tiles, int64_t n_tiles, int nv,
-                      int64_t tiles_per_view, void *out_tiles, float *rgbs, void *acts, cudaStream_t st) {
+                      int64_t tiles_per_view, void *out_tiles, float *rgbs, void *acts, float *taps,
+                      cudaStream_t st) {
   const int64_t n_pairs = (n_tiles + 1) / 2;
   const unsigned grid = (unsigned)(n_pairs < kNumSMs ? n_pairs : kNumSMs);
   cudaError_t e;
@@ -496,14 +521,14 @@ static int launch_fwd(bool fusion, const void *packed, const void *in_tiles, int
     if (e == cudaSuccess)
       mlp_fwd_kernel<true><<<grid, kFwdThreads, bytes, st>>>((const uint8_t *)packed, (const uint8_t *)in_tiles,
                                                              n_tiles, nv, tiles_per_view, (uint8_t *)out_tiles, rgbs,
-                                                             (uint8_t *)acts);
+                                                             (uint8_t *)acts, taps);
   } else {
     constexpr uint32_t bytes = FwdSmem<false>::kBytes;
     e = cudaFuncSetAttribute(mlp_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e == cudaSuccess)
       mlp_fwd_kernel<false><<<grid, kFwdThreads, bytes, st>>>((const uint8_t *)packed, (const uint8_t *)in_tiles,
                                                               n_tiles, nv, tiles_per_view, (uint8_t *)out_tiles, rgbs,
-                                                              (uint8_t *)acts);
+                                                              (uint8_t *)acts, nullptr);
   }
   if (e != cudaSuccess) {
     set_error("mlp_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
@@ -522,7 +547,8 @@ extern "C" int cn_mlp_feature_fwd(const void *packed, const void *x_tiles, int64
   CN_REQUIRE((((uintptr_t)packed | (uintptr_t)x_tiles | (uintptr_t)h3_tiles | (uintptr_t)acts) & 127) == 0,
              "cn_mlp_feature_fwd: buffers must be 128-byte aligned");
   if (n_tiles == 0) return 0;
-  return launch_fwd(false, packed, x_tiles, n_tiles, 1, n_tiles, h3_tiles, nullptr, acts, (cudaStream_t)stream);
+  return launch_fwd(false, packed, x_tiles, n_tiles, 1, n_tiles, h3_tiles, nullptr, acts, nullptr,
+                    (cudaStream_t)stream);
 }
 
 extern "C" int cn_mlp_fusion_fwd(const void *packed, const void *h3_tiles, int32_t b, int32_t nv,
@@ -535,5 +561,18 @@ extern "C" int cn_mlp_fusion_fwd(const void *packed, const void *h3_tiles, int32
              "cn_mlp_fusion_fwd: buffers must be 128-byte aligned");
   if (tiles_per_view == 0) return 0;
   return launch_fwd(true, packed, h3_tiles, (int64_t)b * tiles_per_view, nv, tiles_per_view, nullptr, rgbs, acts,
-                    (cudaStream_t)stream);
+                    nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int cn_mlp_fusion_fwd_taps(const void *packed, const void *h3_tiles, int32_t b, int32_t nv,
+                                      int64_t tiles_per_view, float *rgbs, void *acts, float *taps, void *stream) {
+  using namespace cn;
+  CN_REQUIRE(packed && h3_tiles && rgbs && taps, "cn_mlp_fusion_fwd_taps: null pointer");
+  CN_REQUIRE(b > 0 && nv > 0 && tiles_per_view >= 0, "cn_mlp_fusion_fwd_taps: b=%d nv=%d tiles_per_view=%lld", b, nv,
+             (long long)tiles_per_view);
+  CN_REQUIRE((((uintptr_t)packed | (uintptr_t)h3_tiles | (uintptr_t)rgbs | (uintptr_t)acts | (uintptr_t)taps) & 127) == 0,
+             "cn_mlp_fusion_fwd_taps: buffers must be 128-byte aligned");
+  if (tiles_per_view == 0) return 0;
+  return launch_fwd(true, packed, h3_tiles, (int64_t)b * tiles_per_view, nv, tiles_per_view, nullptr, rgbs, acts,
+                    taps, (cudaStream_t)stream);
 }

@@ -1,0 +1,81 @@
+"""Drop-in for the reference's ``src/lib/delta_ngf/layers.py`` (= ``lmvnerf/layers.py``) and, with
+``activation=``, ``grasp_mvnerf/layers.py``: the affordance head ``GraspReadout``.
+
+4 x [b, np, 42, 128] stage outputs -> Dense 128->64 (+act) each -> concat 256 -> Dense 64 (+act) ->
+flatten (42, 64) = 2688 -> ResNetMLPBlock(2688->128->64, linear shortcut) -> ResNetMLPBlock(64->64->64) ->
+relu -> Dense 64->1 (reference delta_ngf/layers.py:8-42).  582 337 parameters.
+
+The head is ~98 kFLOP per query point plus ~1 MFLOP per pose of plain dense layers on tensors the fused
+kernels hand over in fp32; it runs as torch (cuBLAS) modules so that torch autograd provides the double
+backward ``DeltaNGF.train_step`` takes through it (delta_ngf/model.py:264-296)."""
+import math
+
+import torch
+
+from ..mvnerf.layers import Readout, ResNetMLPBlock
+
+_ACT = {'elu': torch.nn.functional.elu, 'relu': torch.relu}
+
+
+def _he_normal_(linear):
+    with torch.no_grad():
+        linear.weight.normal_(0.0, math.sqrt(2.0 / linear.in_features))
+        if linear.bias is not None:
+            linear.bias.zero_()
+
+
+class GraspReadout(torch.nn.Module):
+    def __init__(self, use_bias=False, activation='elu', **kwargs):
+        super().__init__()
+        if activation not in _ACT:
+            raise ValueError(f'activation {activation} not supported')
+        self.act = _ACT[activation]
+        for i in range(1, 5):
+            setattr(self, f'activation_downscale_{i}', torch.nn.Linear(128, 64))
+        self.combined_activation_downscale = torch.nn.Linear(256, 64)
+        self.readout = torch.nn.Sequential(
+            ResNetMLPBlock(128, 64, transform_shortcut=True, activation=activation, input_size=42 * 64),
+            ResNetMLPBlock(64, 64, activation=activation),
+            Readout(1, use_bias=use_bias, input_size=64))
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        """he_normal kernels, zero biases (delta_ngf/layers.py:12-28); the combined downscale keeps the
+        Keras default (glorot_uniform)."""
+        for m in self.modules():
+            if isinstance(m, torch.nn.Linear) and m is not self.combined_activation_downscale:
+                _he_normal_(m)
+        torch.nn.init.xavier_uniform_(self.combined_activation_downscale.weight)
+        torch.nn.init.zeros_(self.combined_activation_downscale.bias)
+
+    def forward(self, inputs, *args, **kwargs):
+        ds = [self.act(getattr(self, f'activation_downscale_{i + 1}')(inputs[i])) for i in range(4)]
+        c = self.act(self.combined_activation_downscale(torch.cat(ds, dim=-1)))
+        c = c.reshape(*c.shape[:-2], -1)                      # 'b np n5 d -> b np (n5 d)'
+        return self.readout(c)[..., 0]
+
+    # ---- Keras-named view of the variables (kernel[in, out]), for parity tests and checkpoint interchange
+    def named_keras_variables(self, prefix='grasp_readout'):
+        out = {}
+        for i in range(1, 5):
+            l = getattr(self, f'activation_downscale_{i}')
+            out[f'{prefix}.activation_downscale_{i}.kernel'], out[f'{prefix}.activation_downscale_{i}.bias'] = l.weight.t(), l.bias
+        l = self.combined_activation_downscale
+        out[f'{prefix}.combined_activation_downscale.kernel'], out[f'{prefix}.combined_activation_downscale.bias'] = l.weight.t(), l.bias
+        for j in (0, 1):
+            blk = self.readout[j]
+            for ln in ('layer_0', 'layer_1'):
+                l = getattr(blk, ln)
+                out[f'{prefix}.readout.{j}.{ln}.kernel'], out[f'{prefix}.readout.{j}.{ln}.bias'] = l.weight.t(), l.bias
+            if blk.shortcut is not None:
+                out[f'{prefix}.readout.{j}.shortcut.kernel'] = blk.shortcut.weight.t()
+        l = self.readout[2].output_layer
+        out[f'{prefix}.readout.2.output_layer.kernel'] = l.weight.t()
+        if l.bias is not None:
+            out[f'{prefix}.readout.2.output_layer.bias'] = l.bias
+        return out
+
+    def load_keras_variables(self, named, prefix='grasp_readout'):
+        with torch.no_grad():
+            for name, v in self.named_keras_variables(prefix).items():
+                v.copy_(named[name].to(v.device))
