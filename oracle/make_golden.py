@@ -80,5 +80,45 @@ def generate():
         print(case, 'loss', float(loss), 'rgb[0]', out[0][0, 0].tolist())
 
 
+QUERY_CASES = {
+    'query_nv3_p6': dict(case='nv3_r8', seed=211, n_pts=6, rep='quaternion'),
+    'query_nv1_p6_6d': dict(case='nv1_r8', seed=213, n_pts=6, rep='6d'),
+}
+
+
+def make_query_inputs(qcase: str):
+    """(images, K, E^-1, features, translations, rotations, params incl. grasp_readout) of a pose-query case:
+    the scene of the render case plus poses and GraspReadout weights from numpy's legacy RandomState"""
+    c = QUERY_CASES[qcase]
+    inputs, feats, _, _, _, params = make_inputs(c['case'])
+    rs = np.random.RandomState(c['seed'])
+    t = lambda a: torch.tensor(np.asarray(a, dtype=np.float32))  # noqa: E731
+    tr = t(np.array([0.6, 0.0, 0.1]) + rs.uniform(-0.04, 0.04, (1, c['n_pts'], 3)))
+    if c['rep'] == 'quaternion':
+        q = rs.standard_normal((1, c['n_pts'], 4))
+        rot = t(q / np.linalg.norm(q, axis=-1, keepdims=True))
+    else:
+        rot = t(rs.standard_normal((1, c['n_pts'], 6)))
+    for name, shape in O.grasp_readout_param_shapes():
+        params[f'grasp_readout.{name}'] = t(rs.standard_normal(shape) * (math.sqrt(2.0 / shape[0]) if name.endswith('kernel') else 0.02))
+    return inputs[2], inputs[3], inputs[4], feats, tr, rot, params
+
+
+def generate_query():
+    """DeltaNGF._call from the reference's source (ref_runner.reference_query_call) + d(sum)/d(pose variables)"""
+    from .ref_runner import reference_compute_matrices, reference_query_call
+    for qcase, c in QUERY_CASES.items():
+        img, K, E, feats, tr, rot, params = make_query_inputs(qcase)
+        tr, rot = tr.clone().requires_grad_(True), rot.clone().requires_grad_(True)
+        M = reference_compute_matrices(tr, rot, c['rep'])
+        y = reference_query_call(img, K, E, M, feats, params)
+        y.sum().backward()
+        np.savez_compressed(os.path.join(GOLDEN_DIR, f'{qcase}.npz'), grasp_success=y.detach().numpy(),
+                            matrices=M.detach().numpy(), grad_translations=tr.grad.numpy(),
+                            grad_rotations=rot.grad.numpy())
+        print(qcase, 'grasp_success', y.detach()[0, :3].tolist())
+
+
 if __name__ == '__main__':
     generate()
+    generate_query()

@@ -118,3 +118,36 @@ def test_call_matches_reference_source_fp64(ref, nv):
     for k in g1:
         assert float((g1[k] - g2[k]).abs().max()) <= 1e-8 * max(1.0, float(g1[k].abs().max())), k
     assert float((f1 - f2).abs().max()) <= 1e-8 * max(1.0, float(f1.abs().max()))
+
+
+# ---------------------------------------------------------------- pose-query models (delta_ngf / grasp_mvnerf)
+def test_transforms_to_check_and_matrices_identical():
+    from oracle import ref_runner as R
+    p = {**O.init_params(0), **O.init_grasp_readout(1)}
+    model = R.build_reference_query_model(p, 1, 1, 4)
+    assert torch.equal(model.transforms_to_check[0, :, 0], O.transforms_to_check())
+    for rep in ('quaternion', '6d'):
+        t, r = O.synthetic_poses(0, 2, 5, rep)
+        assert torch.equal(R.reference_compute_matrices(t, r, rep), O.compute_matrices(t, r, rep))
+
+
+@pytest.mark.parametrize('which', ['delta_ngf', 'grasp_mvnerf'])
+@pytest.mark.parametrize('dtype,tol', [(torch.float64, 1e-10), (torch.float32, 5e-5)])
+def test_query_call_matches_reference_source(which, dtype, tol):
+    """DeltaNGF._call (delta_ngf/model.py:188-245) / GraspMVNeRF._call (grasp_mvnerf/model.py:113-158) and the
+    gradient of the summed grasp success w.r.t. the pose matrices, from the reference's own source"""
+    from oracle import ref_runner as R
+    sc = O.synthetic_scene(8, 2, 3, 6, 20, 28, dtype=dtype)
+    p = {**O.init_params(3, bias_std=0.02, dtype=dtype), **O.init_grasp_readout(4, bias_std=0.02, dtype=dtype)}
+    _, _, img, K, E = sc['inputs']
+    t, r = O.synthetic_poses(2, 2, 5, dtype=dtype)
+    Mo = O.compute_matrices(t, r).requires_grad_(True)
+    Mr = Mo.detach().clone().requires_grad_(True)
+    yo = O.query_call(img, K, E, Mo, sc['features'], p)
+    yr = R.reference_query_call(img, K, E, Mr, sc['features'], p, which)
+    assert yo.shape == yr.shape == (2, 5)
+    yo.sum().backward()
+    yr.sum().backward()
+    scale = float(yr.abs().max())
+    assert float((yo - yr).abs().max()) / scale < tol
+    assert float((Mo.grad - Mr.grad).abs().max() / Mr.grad.abs().max()) < (1e-8 if dtype == torch.float64 else 2e-2)

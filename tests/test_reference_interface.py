@@ -92,3 +92,48 @@ def test_layers_error_behaviour():
         ResNetMLPBlock(128, 128, activation='tanh')
     blk = ResNetMLPBlock(16, 8, transform_shortcut=True, activation='elu', input_size=32)
     assert tuple(blk(torch.randn(5, 32)).shape) == (5, 8)
+
+
+def test_pose_query_module_surface():
+    """what train_delta_ngf.py / train_language.py / train_goal.py consume"""
+    from src.lib.delta_ngf.grasp_optimizer import DNGFOptimizer
+    from src.lib.delta_ngf.layers import GraspReadout
+    from src.lib.delta_ngf.model import DeltaNGF
+    from src.lib.grasp_mvnerf.model import GraspMVNeRF
+    from src.lib.lmvnerf.model_v4 import LanguageNeRF
+    sig = inspect.signature(DeltaNGF.__init__).parameters
+    for k in ('n_features', 'original_image_size', 'n_points_train', 'n_views', 'n_5d_poses', 'pretrained',
+              'batch_size', 'rotation_representation', 'softmax_before_loss'):
+        assert k in sig
+    for cls in (DeltaNGF, LanguageNeRF, GraspMVNeRF):
+        for m in ('call', 'infer', '_call', 'train_step', 'compile', 'fit', 'store', 'load', 'load_backbone'):
+            assert hasattr(cls, m), (cls, m)
+    assert list(inspect.signature(DeltaNGF.infer).parameters)[1:] == ['inputs', 'transforms', 'n_points_infer',
+                                                                       'batched_features']
+    assert list(inspect.signature(GraspMVNeRF.infer).parameters)[1:] == ['inputs', 'n_points_infer', 'batched_features']
+    m = DeltaNGF(n_views=3, batch_size=2, n_points_train=5)
+    assert m.n_transforms_to_check == 42 and torch.equal(m.transforms_to_check, O.transforms_to_check())
+    assert sum(p.numel() for p in m.grasp_readout.parameters()) == 582337
+    assert hasattr(m.visual_features, 'vision_transformer') and m.n_views == 3
+    assert tuple(m.translations.shape) == (2, 5, 3) and tuple(m.quaternions.shape) == (2, 5, 4)
+    assert tuple(DeltaNGF(rotation_representation='6d').six_d_rotations.shape) == (1, 5, 6)
+    with pytest.raises(ValueError, match='Unknown rotation representation'):
+        DeltaNGF(rotation_representation='euler')
+    with pytest.raises(NotImplementedError):
+        DeltaNGF(pretrained=False)
+    # pose matrices and the affordance head agree with the oracle on CPU tensors
+    t, r = O.synthetic_poses(0, 2, 5)
+    m.set_pose(t, r)
+    assert torch.allclose(m.compute_matrices(), O.compute_matrices(t, r), atol=1e-7)
+    named = O.init_grasp_readout(2, bias_std=0.02)
+    m.grasp_readout.load_keras_variables(named)
+    emb = [torch.randn(2, 5, 42, 128) for _ in range(4)]
+    assert torch.allclose(m.grasp_readout(emb), O.grasp_readout(emb, named), atol=1e-4)
+    assert GraspReadout(use_bias=False).readout[2].output_layer.bias is None
+    opt = DNGFOptimizer(m, [[0, 1], [0, 1], [0, 1]], n_initial_guesses=8, n_images=3)
+    g = opt.generate_initial_guesses()
+    assert g[0].shape == (1, 8, 3) and g[1].shape == (1, 8, 4)
+    opt.set_initial_guesses(g)
+    assert len(opt.get_results()) == 8 and opt.get_results()[0].shape == (4, 4)
+    for a in ('compile', 'optimize_pose', 'compute_current_grasp_success', 'post_process'):
+        assert hasattr(opt, a)
