@@ -763,3 +763,28 @@ def synthetic_poses(seed: int, b: int, n_pts: int, representation: str = 'quater
     else:
         r = torch.randn((b, n_pts, 6), generator=g)
     return t.to(dtype), r.to(dtype)
+
+
+def delta_ngf_losses(images, K, Einv, features, p, landscape_pose, trajectory_pose, labels, *,
+                     rotation_representation: str = 'quaternion', quant: Optional[str] = None,
+                     loss_fn=None) -> Dict[str, Tensor]:
+    """the loss terms of ``DeltaNGF.train_step`` (``delta_ngf/model.py:258-291``): landscape loss at
+    ``landscape_pose = (T, R)`` (inputs[0:2]) + cosine similarity between d(sum prediction)/d(pose variables) at
+    ``trajectory_pose`` (inputs[2:4]) and ``labels[1]`` / ``labels[2]``.  Differentiable w.r.t. the
+    ``grasp_readout.*`` entries of ``p`` (the only variables the reference trains)."""
+    loss_fn = mse if loss_fn is None else loss_fn
+    y_pred = query_call(images, K, Einv, compute_matrices(*landscape_pose, rotation_representation), features, p,
+                        quant=quant)
+    landscape = loss_fn(labels[0], y_pred)
+    t = trajectory_pose[0].detach().clone().requires_grad_(True)
+    r = trajectory_pose[1].detach().clone().requires_grad_(True)
+    pred = query_call(images, K, Einv, compute_matrices(t, r, rotation_representation), features, p, quant=quant)
+    g_t, g_r = torch.autograd.grad(pred.sum(), (t, r), create_graph=True)
+    loss_t = cosine_similarity_loss(labels[1], g_t)
+    if rotation_representation == 'quaternion':
+        loss_r = cosine_similarity_loss(labels[2], g_r)
+    else:
+        loss_r = cosine_similarity_loss(labels[2][..., :3], g_r[..., :3]) + \
+            cosine_similarity_loss(labels[2][..., 3:], g_r[..., 3:])
+    return {'loss': loss_t + loss_r + landscape, 'landscape_loss': landscape, 'grad_loss_t': loss_t,
+            'grad_loss_r': loss_r, 'prediction': pred, 'output_gradients': (g_t, g_r)}

@@ -28,6 +28,11 @@ def _pad_rows(t: torch.Tensor, n_pad: int) -> torch.Tensor:
     return torch.cat([t, t[:, :1].expand(b, n_pad - n, c)], dim=1).contiguous()
 
 
+class _State:
+    """what the forward keeps for the backward and for the tangent pass of the double backward"""
+    __slots__ = ('scene', 'params', 'packed', 'n', 'pts', 'drs', 'z', 'x', 'ws', 'acts_f', 'acts_u', 'need')
+
+
 class _QueryEmbedFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, params, features, images, intrinsics, extr_inv, points, dirs):
@@ -42,21 +47,40 @@ class _QueryEmbedFn(torch.autograd.Function):
         h3, acts_f = ops.mlp_feature_fwd(packed, x, need_grad)
         taps, _rgbs, acts_u = ops.mlp_fusion_fwd_taps(packed, h3, b, scene.nv, need_grad)
         if need_grad:
-            ctx.scene, ctx.packed, ctx.n = scene, packed, n
-            ctx.saved = (pts, drs, z, x, ws, acts_f, acts_u)
+            st = _State()
+            st.scene, st.params, st.packed, st.n = scene, params.detach(), packed, n
+            st.pts, st.drs, st.z, st.x, st.ws, st.acts_f, st.acts_u = pts, drs, z, x, ws, acts_f, acts_u
+            st.need = tuple(ctx.needs_input_grad)
+            ctx.state = st
         return tuple(taps.view(4, b, n_pad, 128)[:, :, :n].unbind(0))
 
     @staticmethod
     def backward(ctx, *g_taps):
-        scene, packed, n = ctx.scene, ctx.packed, ctx.n
-        pts, drs, z, x, ws, acts_f, acts_u = ctx.saved
-        b, n_pad = z.shape[:2]
-        dev = z.device
+        st = ctx.state
+        b, n_pad = st.z.shape[:2]
+        g_taps = [torch.zeros(b, st.n, 128, dtype=torch.float32, device=st.z.device) if g is None else g for g in g_taps]
+        # a Function of its own, so that autograd can differentiate THIS backward w.r.t. the incoming tap
+        # gradients (create_graph=True in DeltaNGF.train_step)
+        d_pts, d_dirs, grad, d_features = _QueryBwdFn.apply(st, *g_taps)
+        need = st.need
+        return (grad if need[0] else None), (d_features if need[1] else None), None, None, None, \
+            (d_pts if need[5] else None), (d_dirs if need[6] else None)
+
+
+class _QueryBwdFn(torch.autograd.Function):
+    """(g_tap0..3) -> (d_points, d_dirs, d_params, d_features) on the CUDA kernels; its own backward is the
+    Jacobian-vector product of the forward (``query_tangent``)."""
+
+    @staticmethod
+    def forward(ctx, st, *g_taps):
+        scene, packed, n = st.scene, st.packed, st.n
+        b, n_pad = st.z.shape[:2]
+        dev = st.z.device
+        need = st.need
         grad = torch.zeros(NET_PARAMS, dtype=torch.float32, device=dev)
 
         def rows(i):
-            g = g_taps[i]
-            g = torch.zeros(b, n, 128, dtype=torch.float32, device=dev) if g is None else g.to(torch.float32)
+            g = g_taps[i].detach().to(torch.float32)
             if n_pad != n:
                 g = torch.cat([g, torch.zeros(b, n_pad - n, 128, dtype=torch.float32, device=dev)], dim=1)
             return g.reshape(b * n_pad, 128).contiguous()
@@ -64,26 +88,42 @@ class _QueryEmbedFn(torch.autograd.Function):
         # the gradient of every tapped stage output joins the bf16 gradient stream where the stage was produced
         g = ops.tile_add_rows(None, rows(3))
         for blk in (5, 4, 3):
-            ops.mlp_block_bwd(packed, blk, acts_u, ops.FUSION_ACTS, blk - 3, g, grad)
+            ops.mlp_block_bwd(packed, blk, st.acts_u, ops.FUSION_ACTS, blk - 3, g, grad)
             ops.tile_add_rows(g, rows(blk - 3))
         s = 1.0 / scene.nv
-        gf = ops.mlp_block_bwd(packed, 2, acts_f, ops.FEATURE_ACTS, 2, g, grad, views=scene.nv, scale=s, b=scene.b) \
-            if scene.nv > 1 else ops.mlp_block_bwd(packed, 2, acts_f, ops.FEATURE_ACTS, 2, g, grad)
+        gf = ops.mlp_block_bwd(packed, 2, st.acts_f, ops.FEATURE_ACTS, 2, g, grad, views=scene.nv, scale=s, b=scene.b) \
+            if scene.nv > 1 else ops.mlp_block_bwd(packed, 2, st.acts_f, ops.FEATURE_ACTS, 2, g, grad)
         for blk in (1, 0):
-            ops.mlp_block_bwd(packed, blk, acts_f, ops.FEATURE_ACTS, blk, gf, grad, scale=s)
-        if ctx.needs_input_grad[0]:
-            ops.mlp_l0_wgrad(x, gf, grad, s)
-        d_features = d_pts = d_dirs = None
-        if ctx.needs_input_grad[1] or ctx.needs_input_grad[5] or ctx.needs_input_grad[6]:
+            ops.mlp_block_bwd(packed, blk, st.acts_f, ops.FEATURE_ACTS, blk, gf, grad, scale=s)
+        if need[0]:
+            ops.mlp_l0_wgrad(st.x, gf, grad, s)
+        d_features = torch.empty(0, device=dev)
+        d_pts = torch.zeros(b, n, 3, dtype=torch.float32, device=dev)
+        d_dirs = torch.zeros(b, n, 3, dtype=torch.float32, device=dev)
+        if need[1] or need[5] or need[6]:
             dx = ops.mlp_l0_dgrad(packed, gf, s)
-            if ctx.needs_input_grad[5] or ctx.needs_input_grad[6]:
-                d_o, d_d, _ = ops.project_gather_bwd_rays(scene, pts, drs, z, dx, ws)
-                d_pts, d_dirs = d_o[:, :n], d_d[:, :n]
-            if ctx.needs_input_grad[1]:
+            if need[5] or need[6]:
+                d_o, d_d, _ = ops.project_gather_bwd_rays(scene, st.pts, st.drs, st.z, dx, st.ws)
+                d_pts, d_dirs = d_o[:, :n].contiguous(), d_d[:, :n].contiguous()
+            if need[1]:
                 d_features = torch.empty_like(scene.features)
-                ops.feature_grad(scene, [(ws, dx, n_pad, 1)], d_features, accumulate=False)
-        ctx.saved = ctx.scene = ctx.packed = None
-        return (grad if ctx.needs_input_grad[0] else None), d_features, None, None, None, d_pts, d_dirs
+                ops.feature_grad(scene, [(st.ws, dx, n_pad, 1)], d_features, accumulate=False)
+        ctx.state = st
+        ctx.mark_non_differentiable(grad, d_features)
+        return d_pts, d_dirs, grad, d_features
+
+    @staticmethod
+    def backward(ctx, u_pts, u_dirs, _ug, _uf):
+        from .query_tangent import query_tangent
+        st = ctx.state
+        b, n_pad = st.z.shape[:2]
+        n = st.n
+
+        def pad(u):
+            u = torch.zeros(b, n, 3, dtype=torch.float32, device=st.z.device) if u is None else u.to(torch.float32)
+            return torch.cat([u, u.new_zeros(b, n_pad - n, 3)], dim=1) if n_pad != n else u
+        taps = query_tangent(st.scene, st.params, st.pts, st.drs, st.z, st.acts_f, st.acts_u, pad(u_pts), pad(u_dirs))
+        return (None,) + tuple(t[:, :n] for t in taps)
 
 
 def query_embeddings(params_fine: torch.Tensor, images, intrinsics, extr_inv, combined_features, points, dirs

@@ -55,24 +55,30 @@ class GraspReadout(torch.nn.Module):
         return self.readout(c)[..., 0]
 
     # ---- Keras-named view of the variables (kernel[in, out]), for parity tests and checkpoint interchange
-    def named_keras_variables(self, prefix='grasp_readout'):
+    def named_keras_variables(self, prefix='grasp_readout', grad=False):
+        """{keras name: tensor}; ``grad=True`` returns the ``.grad`` of every variable in the same (kernel[in, out]) form"""
+        def kern(l):
+            return (l.weight.grad if grad else l.weight).t()
+
+        def bias(l):
+            return l.bias.grad if grad else l.bias
         out = {}
         for i in range(1, 5):
             l = getattr(self, f'activation_downscale_{i}')
-            out[f'{prefix}.activation_downscale_{i}.kernel'], out[f'{prefix}.activation_downscale_{i}.bias'] = l.weight.t(), l.bias
+            out[f'{prefix}.activation_downscale_{i}.kernel'], out[f'{prefix}.activation_downscale_{i}.bias'] = kern(l), bias(l)
         l = self.combined_activation_downscale
-        out[f'{prefix}.combined_activation_downscale.kernel'], out[f'{prefix}.combined_activation_downscale.bias'] = l.weight.t(), l.bias
+        out[f'{prefix}.combined_activation_downscale.kernel'], out[f'{prefix}.combined_activation_downscale.bias'] = kern(l), bias(l)
         for j in (0, 1):
             blk = self.readout[j]
             for ln in ('layer_0', 'layer_1'):
                 l = getattr(blk, ln)
-                out[f'{prefix}.readout.{j}.{ln}.kernel'], out[f'{prefix}.readout.{j}.{ln}.bias'] = l.weight.t(), l.bias
+                out[f'{prefix}.readout.{j}.{ln}.kernel'], out[f'{prefix}.readout.{j}.{ln}.bias'] = kern(l), bias(l)
             if blk.shortcut is not None:
-                out[f'{prefix}.readout.{j}.shortcut.kernel'] = blk.shortcut.weight.t()
+                out[f'{prefix}.readout.{j}.shortcut.kernel'] = kern(blk.shortcut)
         l = self.readout[2].output_layer
-        out[f'{prefix}.readout.2.output_layer.kernel'] = l.weight.t()
+        out[f'{prefix}.readout.2.output_layer.kernel'] = kern(l)
         if l.bias is not None:
-            out[f'{prefix}.readout.2.output_layer.bias'] = l.bias
+            out[f'{prefix}.readout.2.output_layer.bias'] = bias(l)
         return out
 
     def load_keras_variables(self, named, prefix='grasp_readout'):

@@ -241,24 +241,32 @@ class DeltaNGF(_PoseQueryModel):
         return self._query(inputs[4], inputs[5], inputs[6], transforms, n_points, batched_features)
 
     def train_step(self, data):
-        """reference :247-309.  landscape loss on the predicted grasp success at the landscape poses
-        (inputs[0:2]); the gradient-matching terms (cosine similarity between d prediction / d pose at the
-        trajectory poses inputs[2:4] and the labelled directions) need the derivative of the pose gradient
-        w.r.t. the head's weights, i.e. a forward-mode pass through gather + embedding; until that tangent
-        kernel exists they are REPORTED (loss_t / loss_r, from the CUDA pose gradient) but not trained on."""
+        """reference :247-309: landscape loss on the predicted grasp success at the landscape poses (inputs[0:2])
+        plus the gradient-matching terms -- cosine similarity between d prediction / d pose at the trajectory
+        poses (inputs[2:4]) and the labelled directions -- all differentiated w.r.t. the affordance head only.
+        The pose gradient comes from the CUDA backward; its derivative w.r.t. the head's weights goes through
+        the tangent pass of the query call (``clipnerf_b200.query_tangent``)."""
         inputs, labels = data
         readout_vars = list(self.grasp_readout.parameters())
         feats = self.encode(self._to_dev(inputs[4])).detach()
+        losses = self.compute_losses(inputs, labels, feats)
+        gradients = torch.autograd.grad(losses['loss'], readout_vars, allow_unused=True)
+        optimize(self.optimizer, readout_vars, gradients, 1.0)
+        out = {'landscape_loss': losses['landscape_loss'].detach(), 'grad_loss_t': losses['grad_loss_t'].detach(),
+               'grad_loss_r': losses['grad_loss_r'].detach(), 'pred': losses['prediction'].detach().mean()}
+        self.metrics_log.append({k: float(v) for k, v in out.items()})
+        return out
+
+    def compute_losses(self, inputs, labels, feats):
+        """the loss terms of ``train_step`` (reference :258-291) as differentiable tensors"""
         self.set_pose(inputs[0], inputs[1])
         y_pred = self._call(inputs, self.compute_matrices().detach(), self.n_points_train, feats)
         if self.softmax_before_loss:
             y_pred = torch.softmax(y_pred, dim=-1)
         landscape_loss = self.loss(self._to_dev(labels[0]), y_pred)
-        gradients = torch.autograd.grad(landscape_loss, readout_vars, allow_unused=True)
-
         self.set_pose(inputs[2], inputs[3])
         prediction = self._call(inputs, self.compute_matrices(), self.n_points_train, feats)
-        output_gradients = torch.autograd.grad(prediction.sum(), self.pose_variables)
+        output_gradients = torch.autograd.grad(prediction.sum(), self.pose_variables, create_graph=True)
         loss_t = self.cosine_similarity(self._to_dev(labels[1]), output_gradients[0])
         lab_r = self._to_dev(labels[2])
         if self.rotation_representation == 'quaternion':
@@ -266,8 +274,5 @@ class DeltaNGF(_PoseQueryModel):
         else:
             loss_r = self.cosine_similarity(lab_r[..., :3], output_gradients[1][..., :3]) + \
                 self.cosine_similarity(lab_r[..., 3:], output_gradients[1][..., 3:])
-        optimize(self.optimizer, readout_vars, gradients, 1.0)
-        out = {'landscape_loss': landscape_loss.detach(), 'grad_loss_t': loss_t.detach(),
-               'grad_loss_r': loss_r.detach(), 'pred': prediction.detach().mean()}
-        self.metrics_log.append({k: float(v) for k, v in out.items()})
-        return out
+        return {'loss': loss_t + loss_r + landscape_loss, 'landscape_loss': landscape_loss, 'grad_loss_t': loss_t,
+                'grad_loss_r': loss_r, 'prediction': prediction, 'output_gradients': output_gradients}
