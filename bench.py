@@ -163,7 +163,9 @@ def run_reference(args):
 
 
 def workload_config(args, nr):
-    return {'workload': f'cfg2: CLIP-feature-conditioned NeRF render fwd+bwd, {args.nv} views {H}x{W}x{C} fp32 maps, '
+    tag = 'cfg2' if (nr, args.nv) == (4096, 3) else 'cfg3(i)' if (nr, args.nv) == (8192, 1) else \
+        'cfg5 per-GPU shard' if nr >= 131072 else 'custom'
+    return {'workload': f'{tag}: CLIP-feature-conditioned NeRF render fwd+bwd, {args.nv} views {H}x{W}x{C} fp32 maps, '
                         f'{nr} rays x (64+128) samples per GPU, MSE(coarse)+MSE(fine), feature-map gradient, clip+Adam',
             'rays_per_gpu': nr, 'n_views': args.nv, 'samples': '64+128', 'image': [H, W], 'feature_channels': C,
             'parallelism': f'ray-sharded dp{args.gpus}', 'l2': 'inputs larger than L2 (943 MB of feature maps per scene)'}
@@ -198,7 +200,7 @@ def run_b200(args):
 
     def step_resident():
         feats.grad = None
-        return trainer.train_step(dev_inputs, feats, dev_u[2], dev_u[0], dev_u[1], NEAR, FAR)
+        return trainer.train_step(dev_inputs, feats, dev_u[2], dev_u[0], dev_u[1], NEAR, FAR, args.chunk_rays)
 
     h2d_bytes = sum(t.numel() * t.element_size() for t in sc['inputs']) + \
         sum(sc[k].numel() * sc[k].element_size() for k in ('u_strat', 'u_pdf', 'target'))
@@ -210,7 +212,7 @@ def run_b200(args):
         # the call a user makes: a training loop over host batches (the reference's 5-tuple + targets + random
         # draws, pinned memory).  Every step uploads its own batch (copy stream, one batch ahead of the kernels)
         # and returns its loss to the host.
-        losses = fit_host_batches(trainer, (host_batch for _ in range(steps)), feats, NEAR, FAR)
+        losses = fit_host_batches(trainer, (host_batch for _ in range(steps)), feats, NEAR, FAR, args.chunk_rays)
         assert len(losses) == steps and all(l == l for l in losses)
 
     def barrier():
@@ -345,6 +347,8 @@ def main():
     ap.add_argument('--rays', type=int, default=4096, help='rays per GPU per step')
     ap.add_argument('--nv', type=int, default=3, help='source views')
     ap.add_argument('--ref-rays', type=int, default=128, help='bounded CPU sample (rays) of the reference arm')
+    ap.add_argument('--chunk-rays', type=int, default=16384,
+                    help='batches with more rays per GPU are rendered in chunks of this many rays (gradients accumulate)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     args = ap.parse_args()
     if args.impl == 'reference':

@@ -143,6 +143,11 @@ def pose_query_points(transforms: torch.Tensor, transforms_to_check: torch.Tenso
     transforms_to_check [n5, 4, 4] -> query points and approach directions [b, np * n5, 3] in the row order
     '(np n5)' the embedding / GraspReadout use (model.py:228-238).  Tiny host-side torch algebra (np * n5 4x4
     products); autograd carries the pose gradient through it."""
-    poses = transforms[:, :, None] @ transforms_to_check[None, None].to(transforms.dtype)
-    b, n_pts, n5 = poses.shape[:3]
-    return poses[..., :3, 3].reshape(b, n_pts * n5, 3), poses[..., :3, 2].reshape(b, n_pts * n5, 3)
+    ttc = transforms_to_check.to(transforms.dtype)
+    R, t = transforms[:, :, :3, :3], transforms[:, :, :3, 3]
+    # rows of M . C_j written out (the bottom row of M is [0 0 0 1], C_j[3, 3] = 1): point = R c_j + t,
+    # direction = R (C_j[:3, :3] z); broadcast products instead of 4x4 batched GEMMs
+    pts = (R[:, :, None] * ttc[None, None, :, None, :3, 3]).sum(-1) + t[:, :, None]
+    dirs = (R[:, :, None] * ttc[None, None, :, None, :3, 2]).sum(-1)
+    b, n_pts, n5 = pts.shape[:3]
+    return pts.reshape(b, n_pts * n5, 3), dirs.reshape(b, n_pts * n5, 3)

@@ -47,13 +47,29 @@ class RenderTrainer:
     def fine(self):
         return self.params[1]
 
-    def loss_and_backward(self, inputs, features, target, u_strat, u_pdf, near, far):
-        """forward + backward of MSE(coarse) + MSE(fine) (model_v0.py:190-194); returns (loss, outputs)."""
+    def loss_and_backward(self, inputs, features, target, u_strat, u_pdf, near, far, max_rays: Optional[int] = None):
+        """forward + backward of MSE(coarse) + MSE(fine) (model_v0.py:190-194); returns (loss, outputs).
+        ``max_rays``: batches with more rays per scene are rendered in ray chunks of that size whose gradients
+        accumulate (rays are independent; the saved activations of one chunk are ~1.2 MB per ray at 3 views)."""
         self.params.grad = None
-        out = render_rays(self.params[0], self.params[1], inputs, features, u_strat, u_pdf, near, far)
-        loss = torch.mean((out[0] - target) ** 2) + torch.mean((out[2] - target) ** 2)
-        loss.backward()
-        return loss.detach(), out
+        nr = inputs[0].shape[1]
+        if max_rays is None or nr <= max_rays:
+            out = render_rays(self.params[0], self.params[1], inputs, features, u_strat, u_pdf, near, far)
+            loss = torch.mean((out[0] - target) ** 2) + torch.mean((out[2] - target) ** 2)
+            loss.backward()
+            return loss.detach(), out
+        ray_o, ray_d, images, K, Einv = inputs
+        total, outs = None, []
+        for s in range(0, nr, max_rays):
+            sl = slice(s, min(nr, s + max_rays))
+            out = render_rays(self.params[0], self.params[1], (ray_o[:, sl], ray_d[:, sl], images, K, Einv), features,
+                              u_strat[:, sl], u_pdf[:, sl], near, far)
+            tgt = target[:, sl]
+            loss = (((out[0] - tgt) ** 2).sum() + ((out[2] - tgt) ** 2).sum()) / target.numel()
+            loss.backward()
+            total = loss.detach() if total is None else total + loss.detach()
+            outs.append([o.detach() for o in out])
+        return total, tuple(torch.cat([o[i] for o in outs], dim=1) for i in range(4))
 
     def allreduce_gradients(self):
         """the one collective of the path: mean of the flat gradient buffer over ray shards."""
@@ -75,8 +91,8 @@ class RenderTrainer:
         self.v.mul_(self.beta2).addcmul_(g, g, value=1.0 - self.beta2)
         self.params.addcdiv_(self.m, self.v.sqrt().add_(self.eps), value=-lr_t)
 
-    def train_step(self, inputs, features, target, u_strat, u_pdf, near, far):
-        loss, _ = self.loss_and_backward(inputs, features, target, u_strat, u_pdf, near, far)
+    def train_step(self, inputs, features, target, u_strat, u_pdf, near, far, max_rays: Optional[int] = None):
+        loss, _ = self.loss_and_backward(inputs, features, target, u_strat, u_pdf, near, far, max_rays)
         self.allreduce_gradients()
         self.apply_gradients()
         return loss
@@ -136,7 +152,7 @@ class DevicePrefetcher:
         return batch, self.free[k]
 
 
-def fit_host_batches(trainer: RenderTrainer, batches, features, near, far):
+def fit_host_batches(trainer: RenderTrainer, batches, features, near, far, max_rays: Optional[int] = None):
     """Training loop over HOST batches ``(ray_o, ray_d, images, K, E^-1, target, u_strat, u_pdf)`` in pinned
     memory: prefetched uploads, one ``train_step`` per batch, the loss of every step copied back to the host
     asynchronously (read one step late, so the host never stalls the launch queue).  Returns the losses."""
@@ -145,7 +161,7 @@ def fit_host_batches(trainer: RenderTrainer, batches, features, near, far):
     losses, pending = [], []
     for batch, done in DevicePrefetcher(batches, dev):
         features.grad = None
-        loss = trainer.train_step(batch[:5], features, batch[5], batch[6], batch[7], near, far)
+        loss = trainer.train_step(batch[:5], features, batch[5], batch[6], batch[7], near, far, max_rays)
         done.record(cur)
         host_loss = torch.empty((), dtype=torch.float32, pin_memory=True)
         host_loss.copy_(loss, non_blocking=True)

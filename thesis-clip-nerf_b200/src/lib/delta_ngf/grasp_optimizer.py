@@ -32,6 +32,10 @@ class DNGFOptimizer(torch.nn.Module):
             raise ValueError('Unknown rotation representation: ' + rotation_representation)
         self.workspace_bounds = np.array(workspace_bounds)
         self.nerf_grasper = nerf_grasper
+        # test-time optimisation differentiates the pose variables only (reference :159-178: the tape's sources
+        # are self.pose_variables); the trained field is frozen so that no weight gradient is computed
+        for p in nerf_grasper.parameters():
+            p.requires_grad_(False)
         self.n_initial_guesses = n_initial_guesses
         self.n_images = n_images
         batch_size = self.n_images / self.nerf_grasper.n_views

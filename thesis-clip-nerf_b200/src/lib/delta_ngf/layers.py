@@ -17,6 +17,53 @@ from ..mvnerf.layers import Readout, ResNetMLPBlock
 _ACT = {'elu': torch.nn.functional.elu, 'relu': torch.relu}
 
 
+class _tf32_matmul:
+    """scoped TensorFloat-32 for torch's fp32 matmuls (the process-wide switch is restored on exit)"""
+
+    def __enter__(self):
+        self.old = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = True
+
+    def __exit__(self, *a):
+        torch.backends.cuda.matmul.allow_tf32 = self.old
+
+
+class _LinearTF32(torch.autograd.Function):
+    """y = x W^T + b with the three matmuls (forward, d/dx, d/dW) in TensorFloat-32.  TensorFlow, which the
+    reference runs on, executes fp32 matmuls in TF32 on Ampere-and-later GPUs by default
+    (tf.config.experimental.enable_tensor_float_32_execution), so this is the arithmetic of the reference's own
+    GraspReadout on such a GPU; it takes the head from 4 ms to well under 1 ms per optimize_pose step at the
+    validation size.  The backward is made of differentiable torch ops, so the double backward of
+    DeltaNGF.train_step goes through."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        ctx.save_for_backward(x, w)
+        ctx.has_bias = b is not None
+        with _tf32_matmul():
+            return torch.nn.functional.linear(x, w, b)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, w = ctx.saved_tensors
+        gx = gw = gb = None
+        g2 = gy.reshape(-1, gy.shape[-1])
+        with _tf32_matmul():
+            if ctx.needs_input_grad[0]:
+                gx = gy @ w
+            if ctx.needs_input_grad[1]:
+                gw = g2.t() @ x.reshape(-1, x.shape[-1])
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            gb = g2.sum(0)
+        return gx, gw, gb
+
+
+def _linear(layer, x, tf32):
+    if tf32 and x.is_cuda:
+        return _LinearTF32.apply(x, layer.weight, layer.bias)
+    return layer(x)
+
+
 def _he_normal_(linear):
     with torch.no_grad():
         linear.weight.normal_(0.0, math.sqrt(2.0 / linear.in_features))
@@ -30,6 +77,7 @@ class GraspReadout(torch.nn.Module):
         if activation not in _ACT:
             raise ValueError(f'activation {activation} not supported')
         self.act = _ACT[activation]
+        self.tf32 = False                 # set by the models (``tf32_head``); plain fp32 when used stand-alone
         for i in range(1, 5):
             setattr(self, f'activation_downscale_{i}', torch.nn.Linear(128, 64))
         self.combined_activation_downscale = torch.nn.Linear(256, 64)
@@ -49,10 +97,14 @@ class GraspReadout(torch.nn.Module):
         torch.nn.init.zeros_(self.combined_activation_downscale.bias)
 
     def forward(self, inputs, *args, **kwargs):
-        ds = [self.act(getattr(self, f'activation_downscale_{i + 1}')(inputs[i])) for i in range(4)]
-        c = self.act(self.combined_activation_downscale(torch.cat(ds, dim=-1)))
+        t = self.tf32
+        ds = [self.act(_linear(getattr(self, f'activation_downscale_{i + 1}'), inputs[i], t)) for i in range(4)]
+        c = self.act(_linear(self.combined_activation_downscale, torch.cat(ds, dim=-1), t))
         c = c.reshape(*c.shape[:-2], -1)                      # 'b np n5 d -> b np (n5 d)'
-        return self.readout(c)[..., 0]
+        for blk in (self.readout[0], self.readout[1]):        # ResNetMLPBlock (mvnerf/layers.py:262-298)
+            r = _linear(blk.layer_1, blk.act(_linear(blk.layer_0, blk.act(c), t)), t)
+            c = (c if blk.shortcut is None else _linear(blk.shortcut, c, t)) + r
+        return _linear(self.readout[2].output_layer, torch.relu(c), t)[..., 0]
 
     # ---- Keras-named view of the variables (kernel[in, out]), for parity tests and checkpoint interchange
     def named_keras_variables(self, prefix='grasp_readout', grad=False):

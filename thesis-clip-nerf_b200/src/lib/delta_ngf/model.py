@@ -89,7 +89,8 @@ class _PoseQueryModel(torch.nn.Module):
     _groups = ('fine_embedding', 'visual_features', 'grasp_readout')
     _backbone_groups = ('fine_embedding', 'visual_features')
 
-    def _init_common(self, n_views, n_5d_poses, readout):
+    def _init_common(self, n_views, n_5d_poses, readout, tf32_head=True):
+        readout.tf32 = bool(tf32_head)        # see GraspReadout: TensorFloat-32 matmuls, as TensorFlow runs them
         self.n_views = n_views
         self.fine_embedding = MVResNetMLPNeRFEmbedding(6, 128, n_views=n_views, embed_direction_vector=True,
                                                        complete_output=True)
@@ -185,7 +186,7 @@ class _PoseQueryModel(torch.nn.Module):
 class DeltaNGF(_PoseQueryModel):
     def __init__(self, n_features=256, original_image_size=(480, 640), n_points_train=5, n_views=1, n_5d_poses=7,
                  pretrained=True, batch_size=1, fixed_orientation=None, rotation_representation='quaternion',
-                 softmax_before_loss=False, device=None, **kwargs):
+                 softmax_before_loss=False, device=None, tf32_head=True, **kwargs):
         super().__init__()
         if not pretrained:
             raise NotImplementedError('GraspMVNeRF only supports pretrained models')
@@ -193,7 +194,7 @@ class DeltaNGF(_PoseQueryModel):
             raise ValueError('the sm_100a path is specialised for n_features=256')
         if rotation_representation not in ('quaternion', '6d'):
             raise ValueError('Unknown rotation representation: ' + rotation_representation)
-        self._init_common(n_views, n_5d_poses, GraspReadout(use_bias=True))
+        self._init_common(n_views, n_5d_poses, GraspReadout(use_bias=True), tf32_head)
         self.pretrained = pretrained
         self.n_points_train = n_points_train
         self.batch_size = batch_size

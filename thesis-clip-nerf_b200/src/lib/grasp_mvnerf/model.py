@@ -10,11 +10,11 @@ from .layers import GraspReadout
 
 class GraspMVNeRF(_PoseQueryModel):
     def __init__(self, n_features=256, original_image_size=(480, 640), n_points_train=2048, n_views=1, n_5d_poses=7,
-                 softmax_before_loss=False, device=None, **kwargs):
+                 softmax_before_loss=False, device=None, tf32_head=True, **kwargs):
         super().__init__()
         if n_features != 256:
             raise ValueError('the sm_100a path is specialised for n_features=256')
-        self._init_common(n_views, n_5d_poses, GraspReadout(activation='elu'))
+        self._init_common(n_views, n_5d_poses, GraspReadout(activation='elu'), tf32_head)
         self.n_points_train = n_points_train
         self.softmax_before_loss = softmax_before_loss
         self.original_image_size = tuple(original_image_size)
