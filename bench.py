@@ -298,12 +298,22 @@ def run_b200(args):
         stage_report[k] = ent
     dom = next(iter(stage_report))
     d = stage_report[dom]
+    # DRAM traffic per launch of the dominant kernel from the committed ncu --set full capture of this command
+    # (cfg2 only: the capture is of the default workload)
+    traffic = None
+    try:
+        if (nr, nv) == (4096, 3):
+            with open(os.path.join(ROOT, 'profiles', 'r01_v6_traffic.json')) as f:
+                traffic = json.load(f).get(dom, {}).get('dram_bytes_per_launch')
+    except Exception:
+        traffic = None
     if d.get('bound') == 'hbm':
         roofline = {'kernel': dom, 'bound': 'hbm', 'achieved': d['achieved_gbs'], 'peak': peaks['hbm_gbs'],
-                    'unit': 'GB/s', 'frac': d['frac'], 'traffic': None, 'peak_source': peaks['source']}
+                    'unit': 'GB/s', 'frac': d['frac'], 'traffic': traffic, 'peak_source': peaks['source']}
     elif d.get('bound') == 'tensor':
         roofline = {'kernel': dom, 'bound': 'tensor', 'achieved': d['achieved_tflops'], 'peak': peaks['tf_sustained'],
-                    'unit': 'TFLOP/s', 'frac': d['frac'], 'traffic': None, 'peak_source': peaks['source'] + ' (sustained)'}
+                    'unit': 'TFLOP/s', 'frac': d['frac'], 'traffic': traffic, 'traffic_unit': 'bytes per launch (ncu dram read+write, profiles/r01_v6_traffic.json)',
+                    'peak_source': peaks['source'] + ' (sustained)'}
     else:
         roofline = {'kernel': dom, 'bound': 'hbm', 'achieved': None, 'peak': peaks['hbm_gbs'], 'unit': 'GB/s',
                     'frac': None, 'traffic': None, 'peak_source': peaks['source']}

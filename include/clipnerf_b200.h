@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define CN_ABI_VERSION 4
+#define CN_ABI_VERSION 5
 #define CN_TILE_ROWS 128
 #define CN_HIDDEN 128
 #define CN_FEAT_C 256          /* combined_features channels (model_v0.py:60)            */
@@ -154,6 +154,19 @@ int cn_project_gather_bwd_rays(const CnScene *scene, const float *ray_o, const f
 int cn_feature_grad(const CnScene *scene, int32_t n_sets, const int32_t *nr_host, const int32_t *S_host,
                     void *const *ws_host, const size_t *ws_bytes_host, const void *const *dx_tiles_host,
                     float *d_features, int32_t accumulate, void *stream);
+
+/* ---- full-image bookkeeping of render_view (model_v0.py:243-281) ------------------------- */
+
+/* get_rays (nerf_utils.py:15-35) for pixels [first_pixel, first_pixel + n) of a W-wide image, row-major
+ * (u = column, v = row): ray_d [n,3] = normalise(rk_inv . [u, v, 1]), ray_o [n,3] = origin.
+ *   rk_inv_host [9]: pose[:3,:3] @ inv(K[:3,:3]) computed by the caller on the HOST (row-major, float64 storage);
+ *   single_precision: 1 = evaluate in float32 (numpy's arithmetic when pose and K are float32), 0 = float64. */
+int cn_generate_rays(const double *rk_inv_host, const float *origin_host, int32_t single_precision, int32_t W,
+                     int64_t first_pixel, int64_t n, float *ray_o, float *ray_d, void *stream);
+/* uint8 conversion of a rendered image (model_v0.py:272-280): rgb8 [n,3] = uint8(clip(rgb * 255, 0, 255)) by
+ * truncation, depth8 [n] = uint8((depth - min) / (max - min) * 255); minmax_ws: 8 bytes of device scratch. */
+int cn_quantize_render(const float *rgb, const float *depth, int64_t n, void *minmax_ws, uint8_t *rgb8,
+                       uint8_t *depth8, void *stream);
 
 /* ---- compositing --------------------------------------------------------------- */
 

@@ -141,3 +141,30 @@ def test_render_view_bookkeeping(cuda):
     diff = np.abs(rgb8.astype(int) - ref8.astype(int))
     assert diff.max() <= 4 and (diff <= 1).mean() > 0.9, (diff.max(), (diff <= 1).mean())
     assert np.abs(depth8.astype(int) - refd8.astype(int)).max() <= 6
+
+
+def test_device_rays_and_uint8_conversion(cuda):
+    """cn_generate_rays against the reference's numpy get_rays (pixel order exact, values to an fp32 ulp) and
+    cn_quantize_render against the reference's uint8 bookkeeping (bit-exact)."""
+    from clipnerf_b200 import ops
+    from oracle import nerf_oracle as O
+    H, W = 37, 53
+    pose = O.polar_pose(0.9, 0.6, 0.8)                                   # float64, like the dataset's camera configs
+    K = np.array([[55.4, 0, W / 2], [0, 55.4, H / 2], [0, 0, 1]], dtype=np.float32)
+    ro, rd = O.get_rays(W, H, pose, K)
+    for p in (pose, pose.astype(np.float32)):
+        ro_ref, rd_ref = O.get_rays(W, H, p, K)
+        o, d = ops.generate_rays(p, K, W, 0, H * W, cuda)
+        assert np.array_equal(o.cpu().numpy(), ro_ref.reshape(-1, 3).astype(np.float32))
+        err = np.abs(d.cpu().numpy() - rd_ref.reshape(-1, 3).astype(np.float32)).max()
+        assert err <= (1.2e-7 if p.dtype == np.float64 else 5e-7), err
+    # a pixel range in the middle of the image starts at the right pixel
+    o, d = ops.generate_rays(pose, K, W, 1000, 64, cuda)
+    assert np.abs(d.cpu().numpy() - rd.reshape(-1, 3)[1000:1064].astype(np.float32)).max() <= 1.2e-7
+    g = torch.Generator().manual_seed(1)
+    rgb = torch.rand(H * W, 3, generator=g) * 1.2 - 0.1                   # values below 0 and above 1
+    depth = torch.rand(H * W, generator=g) * 0.9 + 0.3
+    rgb8, depth8 = ops.quantize_render(rgb.to(cuda), depth.to(cuda))
+    ref8, refd8 = O.quantize_render(rgb.numpy(), depth.numpy(), (H, W))
+    assert np.array_equal(rgb8.cpu().numpy().reshape(H, W, 3), ref8)
+    assert np.array_equal(depth8.cpu().numpy().reshape(H, W, 1), refd8)

@@ -188,6 +188,33 @@ def feature_grad(scene: Scene, sets, d_features: torch.Tensor, accumulate: bool)
     call('cn_feature_grad', ctypes.byref(scene.c), n, nr, S, ws, wsb, dx, _ptr(d_features), int(accumulate), _stream())
 
 
+def generate_rays(pose, intrinsics, W: int, first_pixel: int, n: int, device):
+    """rays of pixels [first_pixel, first_pixel + n) of the target view (row-major), generated on the device"""
+    import numpy as np
+    pose, intrinsics = np.asarray(pose), np.asarray(intrinsics)
+    m = pose[:3, :3] @ np.linalg.inv(intrinsics[:3, :3])             # the reference's own host expression
+    single = int(m.dtype == np.float32)
+    m64 = np.ascontiguousarray(m, dtype=np.float64)
+    o32 = np.ascontiguousarray(pose[:3, 3], dtype=np.float32)
+    ray_o = torch.empty(n, 3, dtype=torch.float32, device=device)
+    ray_d = torch.empty(n, 3, dtype=torch.float32, device=device)
+    call('cn_generate_rays', m64.ctypes.data_as(ctypes.c_void_p), o32.ctypes.data_as(ctypes.c_void_p), single, int(W),
+         int(first_pixel), int(n), _ptr(ray_o), _ptr(ray_d), _stream())
+    return ray_o, ray_d
+
+
+def quantize_render(rgb, depth):
+    """(uint8 [n,3], uint8 [n]) of model_v0.py:272-280: x255 clip truncate; depth min-max normalised, x255, truncate"""
+    rgb, depth = _f32c(rgb), _f32c(depth)
+    n = depth.numel()
+    assert rgb.numel() == 3 * n
+    ws = torch.empty(2, dtype=torch.int32, device=rgb.device)
+    rgb8 = torch.empty(n, 3, dtype=torch.uint8, device=rgb.device)
+    depth8 = torch.empty(n, dtype=torch.uint8, device=rgb.device)
+    call('cn_quantize_render', _ptr(rgb), _ptr(depth), n, _ptr(ws), _ptr(rgb8), _ptr(depth8), _stream())
+    return rgb8, depth8
+
+
 def composite_fwd(z, rgbs):
     z, rgbs = _f32c(z), _f32c(rgbs)
     S = z.shape[-1]

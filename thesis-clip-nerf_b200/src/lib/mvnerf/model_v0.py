@@ -197,35 +197,30 @@ def render_view(model, src_colors, src_camera_configs, tgt_camera_config, chunk=
     """full-image render of the target view (reference :243-281) -> (uint8 HxWx3, uint8 HxWx1).
 
     Same bookkeeping: row-major rays over the source image size, fine rgb x255 clipped and
-    *truncated* to uint8, depth min-max normalised then truncated.  The reference walks the image
-    in 600 chunks of ``n_rays_infer`` = 512 rays with a device->host copy each; here the features
-    are encoded once and the image is rendered in a few large launches (``chunk`` rays each,
-    default 65536), results staying on the device until the end."""
+    *truncated* to uint8, depth min-max normalised then truncated.  The reference generates the rays with
+    numpy, walks the image in 600 chunks of ``n_rays_infer`` = 512 rays and copies every chunk's floats to
+    the host; here the rays are generated on the device (``cn_generate_rays``), the features are encoded
+    once, the image is rendered in a few large launches (``chunk`` rays each, default 65536), the uint8
+    conversion runs on the device (``cn_quantize_render``) and only the two uint8 images are copied back."""
     tgt_intrinsic = np.reshape(tgt_camera_config['intrinsics'], (3, 3)).astype(np.float32)
     image_shape = src_colors[0].shape[:2]
-    tgt_r_o, tgt_r_d = get_rays(image_shape[1], image_shape[0], tgt_camera_config['pose'], tgt_intrinsic)
-    all_o = np.reshape(tgt_r_o, (-1, 3))
-    all_d = np.reshape(tgt_r_d, (-1, 3))
+    H, W = image_shape
     src_images = np.array([[image[..., :3] / 255.0 for image in src_colors]])
     dev = model.device
     imgs = torch.as_tensor(src_images, dtype=torch.float32, device=dev)
     feats = model.encode(imgs.reshape(-1, *imgs.shape[2:])).reshape(1, imgs.shape[1], imgs.shape[2], imgs.shape[3], -1)
     e_invs, ks = zip(*[camera_parameters(c) for c in src_camera_configs])
     K, Einv = np.array([ks], dtype=np.float32), np.array([e_invs], dtype=np.float32)
-    n = len(all_o)
+    n = H * W
     chunk = chunk or 65536
     rgbs, depths = [], []
     for i in range(0, n, chunk):
-        o, d = all_o[i:i + chunk], all_d[i:i + chunk]
-        m = len(o)
-        if m % 2:                      # tiles hold two coarse rays: pad with a copy of the last ray
-            o, d = np.concatenate([o, o[-1:]]), np.concatenate([d, d[-1:]])
+        m = min(chunk, n - i)
+        m_pad = m + (m % 2)            # tiles hold two coarse rays: the padding ray is the next pixel, dropped below
+        o, d = ops.generate_rays(np.asarray(tgt_camera_config['pose']), tgt_intrinsic, W, i, m_pad, dev)
         with torch.no_grad():
-            _, _, fine_rgb, fine_depth = model._call((o[None], d[None], imgs, K, Einv), len(o), 1, feats)
+            _, _, fine_rgb, fine_depth = model._call((o[None], d[None], imgs, K, Einv), m_pad, 1, feats)
         rgbs.append(fine_rgb[0, :m])
         depths.append(fine_depth[0, :m])
-    all_rgbs = torch.cat(rgbs).cpu().numpy().reshape(*image_shape, 3) * 255
-    all_rgbs = np.clip(all_rgbs, 0, 255).astype(np.uint8)
-    all_depths = torch.cat(depths).cpu().numpy().reshape(*image_shape, 1)
-    norm = (all_depths - np.min(all_depths)) / (np.max(all_depths) - np.min(all_depths))
-    return all_rgbs, (norm * 255).astype(np.uint8)
+    rgb8, depth8 = ops.quantize_render(torch.cat(rgbs), torch.cat(depths))
+    return rgb8.cpu().numpy().reshape(H, W, 3), depth8.cpu().numpy().reshape(H, W, 1)
