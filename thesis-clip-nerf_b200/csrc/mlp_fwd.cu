@@ -363,10 +363,16 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         acquire();
         // ring position of this tile's view slabs: views(t0) | Wa0 (2 slots) | views(t1) | ...
         const uint32_t vbase = ring_base + (t ? view_slots + 2u : 0u);
+        if (tr) CN_TRACE_AT(pi, 15);
         if (staged) {
           mbar_wait(smem_u32(&bars.views_ready[t]), n_views & 1u);
           ++n_views;
         }
+        if (tr) CN_TRACE_AT(pi, 16);
+        const uint8_t *vslab[kMaxStageViews];
+#pragma unroll
+        for (int v = 0; v < kMaxStageViews; ++v)
+          vslab[v] = smem + kSmemRing + ((vbase + 2u * v + half) % kRingSlots) * CN_SLAB_BYTES;
 #pragma unroll 1
         for (int c2 = 0; c2 < 2; ++c2) {
           uint32_t r[32];
@@ -374,17 +380,27 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
           for (int q = 0; q < 4; ++q) {
             const uint32_t chunk = half * 8 + c2 * 4 + q;
             float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            for (int v = 0; v < nv; ++v) {
-              uint4 x;
-              if (staged)  // chunk's slab (= half) of view v sits in ring slot vbase + 2v + half
-                x = *reinterpret_cast<const uint4 *>(smem + kSmemRing +
-                                                     ((vbase + 2u * v + half) % kRingSlots) * CN_SLAB_BYTES +
-                                                     tile_chunk_off(row, chunk & 7u));
-              else
-                x = ldg_nc_u4(in_tiles + ((b * nv + v) * tiles_per_view + tt) * (int64_t)CN_ACT_TILE_BYTES +
-                              tile_chunk_off(row, chunk));
-              acc[0] += bf16_lo(x.x); acc[1] += bf16_hi(x.x); acc[2] += bf16_lo(x.y); acc[3] += bf16_hi(x.y);
-              acc[4] += bf16_lo(x.z); acc[5] += bf16_hi(x.z); acc[6] += bf16_lo(x.w); acc[7] += bf16_hi(x.w);
+            if (staged) {
+              // chunk's slab (= half) of view v sits in ring slot vbase + 2v + half.  All (<= 3) shared-memory
+              // loads are issued before the first use: a per-view loop with a dependent accumulate after every
+              // load made this prologue 4 900 cycles long (tools/trace_mlp_fusion.py).
+              const uint32_t off = tile_chunk_off(row, chunk & 7u);
+              uint4 x[kMaxStageViews];
+#pragma unroll
+              for (int v = 0; v < kMaxStageViews; ++v)
+                x[v] = v < nv ? *reinterpret_cast<const uint4 *>(vslab[v] + off) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+              for (int v = 0; v < kMaxStageViews; ++v) {
+                acc[0] += bf16_lo(x[v].x); acc[1] += bf16_hi(x[v].x); acc[2] += bf16_lo(x[v].y); acc[3] += bf16_hi(x[v].y);
+                acc[4] += bf16_lo(x[v].z); acc[5] += bf16_hi(x[v].z); acc[6] += bf16_lo(x[v].w); acc[7] += bf16_hi(x[v].w);
+              }
+            } else {
+              for (int v = 0; v < nv; ++v) {
+                const uint4 x = ldg_nc_u4(in_tiles + ((b * nv + v) * tiles_per_view + tt) * (int64_t)CN_ACT_TILE_BYTES +
+                                          tile_chunk_off(row, chunk));
+                acc[0] += bf16_lo(x.x); acc[1] += bf16_hi(x.x); acc[2] += bf16_lo(x.y); acc[3] += bf16_hi(x.y);
+                acc[4] += bf16_lo(x.z); acc[5] += bf16_hi(x.z); acc[6] += bf16_lo(x.w); acc[7] += bf16_hi(x.w);
+              }
             }
             float m[8];
 #pragma unroll
@@ -404,6 +420,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
           }
           tmem_st32(t_h + half * 64 + c2 * 32, r);
         }
+        if (tr) CN_TRACE_AT(pi, 19);
         if (staged) {
           // every thread has read its rows: hand the view slots back to the producer
           named_bar_sync(bar_id, kEpiThreads);
@@ -411,7 +428,9 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
             for (uint32_t i = 0; i < view_slots; ++i) mbar_arrive(smem_u32(&bars.empty[(vbase + i) % kRingSlots]));
         }
         tmem_wait_st();
+        if (tr) CN_TRACE_AT(pi, 20);
         publish(my_acts, true);
+        if (tr) CN_TRACE_AT(pi, 17);
       } else {
         mbar_wait(smem_u32(&bars.h_ready[t]), n_h & 1u);
         ++n_h;
@@ -456,7 +475,8 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         // warps of a row split the OUTPUTS (half 0: r,g; half 1: b,sigma), each over all 128 inputs; the
         // relu(e) tile saved for the backward is still written half by half.
         const float *wr = tab + 7 * 128;
-        float ya = wr[512 + 2 * half], yb = wr[512 + 2 * half + 1];
+        // two accumulator chains per output: one chain of 128 dependent FMAs per output made this epilogue latency bound
+        float ya = wr[512 + 2 * half], yb = wr[512 + 2 * half + 1], ya1 = 0.f, yb1 = 0.f;
 #pragma unroll 1
         for (int c4 = 0; c4 < 4; ++c4) {
           uint32_t r[32];
@@ -471,8 +491,13 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
               const int col = c4 * 32 + q * 8 + i;
               v[i] = fmaxf(__uint_as_float(r[q * 8 + i]) + tab[6 * 128 + col], 0.f);
               const float2 w = *reinterpret_cast<const float2 *>(wr + col * 4 + 2 * half);
-              ya += v[i] * w.x;
-              yb += v[i] * w.y;
+              if (i & 1) {
+                ya1 += v[i] * w.x;
+                yb1 += v[i] * w.y;
+              } else {
+                ya += v[i] * w.x;
+                yb += v[i] * w.y;
+              }
             }
             if (my_tap && mine) {
               // e itself (pre-ReLU) is the tap; v[] holds relu(e), so re-add from the accumulator
@@ -489,6 +514,8 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
                              pack_bf16x2(v[6], v[7]));
           }
         }
+        ya += ya1;
+        yb += yb1;
         float2 o;
         o.x = 1.f / (1.f + expf(-ya));
         o.y = half ? (yb > 20.f ? yb : log1pf(expf(yb))) : 1.f / (1.f + expf(-yb));
