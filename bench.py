@@ -242,7 +242,7 @@ def run_b200(args):
     with ClockSampler(local) as clocks:
         ms = timed(step_resident, args.steps)
     launches = _abi.LAUNCHES - launches0
-    run_e2e(2)
+    run_e2e(3)          # warm the loop's own allocations (device batch slots, pinned loss ring, copy stream)
     ms_e2e = timed(run_e2e, args.steps, loop=True)
 
     # ---- per-stage device times (CUDA events around every ABI call), separate instrumented pass
@@ -284,9 +284,25 @@ def run_b200(args):
         'cn_mlp_l0_dgrad': ('tensor', nr * 192 * nv * 2.0 * 384 * 128),
         'cn_mlp_l0_wgrad': ('tensor', nr * 192 * nv * 2.0 * 384 * 128),
     }
+    # measured DRAM traffic of every hot kernel (ncu capture of this command, cfg2 only): actual bytes moved through
+    # HBM per step / live stage time = the DRAM bandwidth the stage really draws (the `achieved_gbs` of the gather
+    # stages counts ALGORITHMIC bytes, most of which are served by L2 after the spatial binning -- hence > peak)
+    ncu_traffic = {}
+    try:
+        if (nr, nv) == (4096, 3):
+            with open(os.path.join(ROOT, 'profiles', 'r01_v6_traffic.json')) as f:
+                raw = json.load(f)
+            for k, v in raw.items():
+                if isinstance(v, dict):
+                    ncu_traffic[k.split(' ')[0]] = v['dram_bytes_per_launch'] * v['launches_per_step']
+    except Exception:
+        ncu_traffic = {}
     stage_report = {}
     for k, t in sorted(stage_ms.items(), key=lambda kv: -kv[1]):
         ent = {'ms_per_step': round(t, 4), 'calls_per_step': stage_calls[k]}
+        if k in ncu_traffic:
+            ent['dram_gbs_ncu_bytes'] = round(ncu_traffic[k] / (t * 1e-3) / 1e9, 1)
+            ent['dram_frac'] = round(ncu_traffic[k] / (t * 1e-3) / 1e9 / peaks['hbm_gbs'], 4)
         if k in alg:
             bound, work = alg[k]
             if bound == 'hbm':

@@ -275,3 +275,42 @@ def test_query_tangent_pass(cuda, nv, n):
     tang = torch.autograd.grad(S, cot)
     for i, name in enumerate(('mean', 'block4', 'block5', 'block6')):
         _check_rows(f'tangent nv={nv} n={n}', f'd tap {name}', tang[i], ref[i])
+
+
+def test_dngf_optimizer_graph_replay_matches_eager(cuda):
+    """DNGFOptimizer.capture(): the CUDA-graph replay of optimize_pose walks the same pose trajectory as eager steps"""
+    from clipnerf_b200 import params
+    from src.lib.delta_ngf.grasp_optimizer import DNGFOptimizer
+    from src.lib.delta_ngf.model import DeltaNGF
+    from oracle import nerf_oracle as O
+    nv, n_guess = 1, 64
+    sc = O.synthetic_scene(6, 3, nv, 8, 48, 64)
+    named = O.init_params(9, bias_std=0.02)
+    named.update(O.init_grasp_readout(2, bias_std=0.02))
+    _, _, img, K, E = sc['inputs']
+    model = DeltaNGF(n_views=nv, batch_size=1, n_points_train=n_guess, device=cuda)
+    with torch.no_grad():
+        model.fine_embedding.flat.copy_(params.from_named(named, 'fine')[:model.fine_embedding.flat.numel()].to(cuda))
+    model.grasp_readout.load_keras_variables(named)
+    inputs = [img.transpose(0, 1).to(cuda), K.transpose(0, 1).to(cuda), E.transpose(0, 1).to(cuda), None]
+    feats = sc['features'].transpose(0, 1).to(cuda)
+    bounds = [[0.55, 0.65], [-0.05, 0.05], [0.05, 0.15]]
+    runs = []
+    for graph in (False, True):
+        opt = DNGFOptimizer(model, bounds, n_initial_guesses=n_guess, n_images=3, clip_translation=True)
+        opt._rng = __import__('numpy').random.default_rng(5)
+        opt.compile()
+        opt.set_initial_guesses(opt.generate_initial_guesses())
+        if graph:
+            replay = opt.capture(inputs, feats, (True, True), warmup=3)
+            for _ in range(3):
+                out = replay()
+        else:
+            for _ in range(6):
+                out = opt.optimize_pose(inputs, feats, (True, True))
+        torch.cuda.synchronize()
+        runs.append((opt.translations.detach().clone(), opt.rotations.detach().clone(), out['loss'].clone()))
+    (t0, r0, l0), (t1, r1, l1) = runs
+    print('[dngf graph] max |dt|', float((t0 - t1).abs().max()), 'max |dr|', float((r0 - r1).abs().max()))
+    assert torch.allclose(t0, t1, atol=1e-5) and torch.allclose(r0, r1, atol=1e-5)
+    assert torch.allclose(l0, l1, rtol=1e-3, atol=1e-3)

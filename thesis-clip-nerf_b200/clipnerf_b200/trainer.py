@@ -159,11 +159,14 @@ def fit_host_batches(trainer: RenderTrainer, batches, features, near, far, max_r
     dev = trainer.params.device
     cur = torch.cuda.current_stream(dev)
     losses, pending = [], []
+    ring = torch.empty(4, dtype=torch.float32, pin_memory=True)     # pinned once: no host allocation inside the loop
+    k = 0
     for batch, done in DevicePrefetcher(batches, dev):
         features.grad = None
         loss = trainer.train_step(batch[:5], features, batch[5], batch[6], batch[7], near, far, max_rays)
         done.record(cur)
-        host_loss = torch.empty((), dtype=torch.float32, pin_memory=True)
+        host_loss = ring[k % 4]
+        k += 1
         host_loss.copy_(loss, non_blocking=True)
         ev = torch.cuda.Event()
         ev.record(cur)

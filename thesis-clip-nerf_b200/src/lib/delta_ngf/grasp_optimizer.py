@@ -51,6 +51,7 @@ class DNGFOptimizer(torch.nn.Module):
         self.optimizer = None
         self.loss_tracker = []
         self._rng = np.random.default_rng(0)
+        self._bounds = None
 
     @property
     def quaternions(self):
@@ -63,7 +64,9 @@ class DNGFOptimizer(torch.nn.Module):
     def compile(self, optimizer=None):
         """``optimizer``: [translation optimizer, rotation optimizer] over ``pose_variables[0 / 1]``"""
         if optimizer is None:
-            optimizer = [torch.optim.Adam(self.pose_variables[0], lr=1e-3), torch.optim.Adam(self.pose_variables[1], lr=1e-2)]
+            cap = self.translations.is_cuda          # capturable: the step can be recorded into a CUDA graph (capture())
+            optimizer = [torch.optim.Adam(self.pose_variables[0], lr=1e-3, capturable=cap),
+                         torch.optim.Adam(self.pose_variables[1], lr=1e-2, capturable=cap)]
         assert len(optimizer) == 2
         self.optimizer = optimizer
 
@@ -121,8 +124,11 @@ class DNGFOptimizer(torch.nn.Module):
     def post_process(self):
         with torch.no_grad():
             if self.clip_translation:
-                lo = torch.as_tensor(self.workspace_bounds[:, 0], dtype=torch.float32, device=self.translations.device)
-                hi = torch.as_tensor(self.workspace_bounds[:, 1], dtype=torch.float32, device=self.translations.device)
+                if self._bounds is None or self._bounds[0].device != self.translations.device:
+                    dev = self.translations.device
+                    self._bounds = (torch.as_tensor(self.workspace_bounds[:, 0], dtype=torch.float32, device=dev),
+                                    torch.as_tensor(self.workspace_bounds[:, 1], dtype=torch.float32, device=dev))
+                lo, hi = self._bounds
                 self.translations.copy_(torch.minimum(torch.maximum(self.translations, lo), hi))
             r = self.rotations
             if self.rotation_representation == 'quaternion':
@@ -130,6 +136,41 @@ class DNGFOptimizer(torch.nn.Module):
             else:
                 r.copy_(torch.cat([r[..., :3] / r[..., :3].norm(dim=-1, keepdim=True),
                                    r[..., 3:] / r[..., 3:].norm(dim=-1, keepdim=True)], dim=-1))
+
+    def _step(self, r_inputs, r_features, train_config):
+        grasp_success = self([r_inputs, r_features])
+        grasp_success = grasp_success.sum(dim=0, keepdim=True).transpose(0, 1)
+        loss = -grasp_success
+        grads = torch.autograd.grad(loss.sum(), [self.translations, self.rotations])
+        for i, t_c in enumerate(train_config):
+            if t_c:
+                optimize(self.optimizer[i], self.pose_variables[i], [grads[i]], 1.0)
+        self.post_process()
+        return grasp_success
+
+    def capture(self, inputs, features, train_config=(True, True), warmup=3):
+        """CUDA-graph form of ``optimize_pose`` for the test-time loop (32+ steps on fixed images, reference
+        src/utils/optimization.py:136-153): one step -- ~20 kernels of the query path, ~60 torch ops of the head,
+        the two optimizers and ``post_process`` -- is captured once and replayed; ``inputs`` / ``features`` must be
+        device tensors that stay alive, the optimizers must be capturable (``torch.optim.Adam(..., capturable=True)``).
+        Returns ``replay() -> {'loss': grasp_success [np, 1]}`` (the tensor is overwritten by the next replay).
+        The ``warmup`` eager steps that precede the capture DO update the poses."""
+        r_inputs, r_features = self._regroup(inputs, features)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self._step(r_inputs, r_features, train_config)
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            out = self._step(r_inputs, r_features, train_config).detach()
+
+        def replay():
+            graph.replay()
+            return {'loss': out}
+        replay.graph = graph
+        return replay
 
     def optimize_pose(self, inputs, features, train_config=(True, True)):
         r_inputs, r_features = self._regroup(inputs, features)

@@ -23,7 +23,8 @@ from .layers import GraspReadout
 def t_m_to_h_matrix(translations, rot_matrices):
     """[[R | t], [0 0 0 1]] (reference delta_ngf/model.py:16-25)"""
     top = torch.cat([rot_matrices, translations[..., None]], dim=-1)
-    last = torch.tensor([0., 0., 0., 1.], dtype=top.dtype, device=top.device).expand(*top.shape[:-2], 1, 4)
+    last = top.new_zeros(*top.shape[:-2], 1, 4)          # built on the device: no host copy (CUDA-graph capturable)
+    last[..., 0, 3] = 1.0
     return torch.cat([top, last], dim=-2)
 
 

@@ -54,7 +54,7 @@ def main():
     if args.case in ('all', 'optimize_pose'):
         n_img, n_guess = 3, args.guesses
         sc = synthetic.scene(0, 2, n_img, H, W, C, device=dev)           # [1, 3, ...]: 3 images, regrouped to b=3, nv=1
-        _, _, img, K, E = sc['inputs']
+        _, _, img, K, E = [t.to(dev) for t in sc['inputs']]
         model = DeltaNGF(n_views=1, batch_size=1, n_points_train=n_guess, device=dev)
         opt = DNGFOptimizer(model, bounds, n_initial_guesses=n_guess, n_images=n_img, clip_translation=True)
         opt.compile()
@@ -64,6 +64,11 @@ def main():
         ms = timed(lambda: opt.optimize_pose(inputs, feats, (True, True)), args.steps, args.warmup)
         launches = (_abi.LAUNCHES - l0) // (args.steps + args.warmup)
         rows = n_img * n_guess * 42
+        replay = opt.capture(inputs, feats, (True, True))
+        ms_g = timed(replay, args.steps, args.warmup)
+        print(json.dumps({'case': 'optimize_pose (CUDA graph replay)', 'metric': 'query_points_per_sec_fwd_bwd',
+                          'value': rows / (ms_g * 1e-3), 'unit': 'points/s', 'ms_per_step': ms_g, 'rows_per_step': rows,
+                          'graph': 'DNGFOptimizer.capture(): one step recorded with torch.cuda.graph, replayed'}))
         print(json.dumps({'case': 'optimize_pose', 'metric': 'query_points_per_sec_fwd_bwd', 'value': rows / (ms * 1e-3),
                           'unit': 'points/s', 'ms_per_step': ms, 'rows_per_step': rows, 'gpu_launches_per_step': launches,
                           'mlp_tflops': rows * 491264.0 * 3 / (ms * 1e-3) / 1e12,
@@ -73,7 +78,7 @@ def main():
     if args.case in ('all', 'train_step'):
         b, nv, n_pts = 1, 3, 192
         sc = synthetic.scene(1, 2, nv, H, W, C, device=dev)
-        _, _, img, K, E = sc['inputs']
+        _, _, img, K, E = [t.to(dev) for t in sc['inputs']]
         feats = sc['features']
         model = DeltaNGF(n_views=nv, batch_size=b, n_points_train=n_pts, device=dev)
         model.compile()
