@@ -156,7 +156,7 @@ def run_reference(args):
         'impl': 'reference', 'metric': 'rays_per_sec_fwd_bwd', 'value': value, 'unit': 'rays/s', 'n_gpus': args.gpus,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': workload_config(args, nr_sample),
+        'config': workload_config(args, args.rays),          # this repo's arm's config; each step = the bounded sample below
         'cpu_baseline': base,
         'e2e': {'value': value, 'unit': 'rays/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
     }))
@@ -372,7 +372,7 @@ def main():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--rays', type=int, default=4096, help='rays per GPU per step')
     ap.add_argument('--nv', type=int, default=3, help='source views')
-    ap.add_argument('--ref-rays', type=int, default=128, help='bounded CPU sample (rays) of the reference arm')
+    ap.add_argument('--ref-rays', type=int, default=512, help='bounded CPU sample (rays) of the reference arm')
     ap.add_argument('--chunk-rays', type=int, default=16384,
                     help='batches with more rays per GPU are rendered in chunks of this many rays (gradients accumulate)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
