@@ -251,3 +251,35 @@ def test_binned_scatter_many_rows(cuda, corner):
     # the workspace can be re-used: a second backward accumulates the same amounts again
     ops.project_gather_bwd(scene, ro, rd, z32.to(cuda), dx, d_feat, dz, ws)
     assert rel_err(d_feat, 2 * feats.grad) < 1e-4
+
+
+def test_project_gather_bwd_rays(cuda):
+    """cn_project_gather_bwd_rays with S > 1 and z != 0: d/d(ray origin), d/d(ray direction) (through x = o + z d AND
+    through posenc(E^-1 [d; 1])) and dz against the fp64 oracle for a given dX."""
+    from clipnerf_b200 import layout, ops
+    from oracle import nerf_oracle as O
+    sc = _scene(seed=5, b=2, nv=2, nr=4)
+    scene, ro, rd = _cuda_scene(sc, cuda)
+    i_ro, i_rd, img, K, E = [t.double() for t in sc['inputs']]
+    i_ro, i_rd = i_ro.requires_grad_(True), i_rd.requires_grad_(True)
+    _, z32 = O.sample_along_ray(sc['inputs'][0], sc['inputs'][1], NEAR, FAR, 64, sc['u_strat'])
+    z = z32.double().requires_grad_(True)
+    pts = i_ro[:, :, None, :] + z[..., None] * i_rd[:, :, None, :]
+    pix_r, cam_r = O.compute_pixel_in_image_mv(pts, K, E)
+    g_r = O.get_projection_features_mv(img * 2 - 1.0, sc['features'].double(), pix_r)
+    dirs = O.world_to_camera_direction_vector_mv(i_rd, E)[:, :, :, None, :].expand(-1, -1, -1, 64, -1)
+    x_ref = torch.cat([O.position_encoding(cam_r[..., :3]), O.position_encoding(dirs), g_r], -1).reshape(-1, 379)
+    gen = torch.Generator().manual_seed(11)
+    gx = torch.randn(x_ref.shape[0], 379, generator=gen)
+    gx[:, :120] *= 1e-3       # posenc gradients are amplified by f_k up to ~1.6e3
+    gx = gx.to(torch.bfloat16).to(torch.float32)
+    (x_ref * gx.double()).sum().backward()
+    cols = torch.tensor([layout.x_col_to_ref(j) for j in range(379)])
+    gint = torch.zeros(x_ref.shape[0], 384)
+    gint[:, :379] = gx[:, cols]
+    dx = layout.matrix_to_tiles(gint).to(cuda)
+    ws = ops.project_bin(scene, ro, rd, z32.to(cuda))
+    d_o, d_d, dz = ops.project_gather_bwd_rays(scene, ro, rd, z32.to(cuda), dx, ws, need_dz=True)
+    errs = dict(d_o=rel_err(d_o, i_ro.grad), d_d=rel_err(d_d, i_rd.grad), dz=rel_err(dz, z.grad))
+    print('[bwd_rays]', errs)
+    assert max(errs.values()) < 2e-3, errs

@@ -135,3 +135,23 @@ def test_render_inference_matches_training_forward(cuda):
     out_trn, *_ = _run(cuda, sc, named)
     for a, b_ in zip(out_inf, out_trn):
         assert torch.equal(a, b_.detach())
+
+
+def test_ray_chunked_training_step_matches_unchunked(cuda):
+    """RenderTrainer.loss_and_backward(max_rays=...): gradients accumulated over ray chunks equal the one-shot
+    gradients (rays are independent; the loss is normalised by the full batch)."""
+    from clipnerf_b200.trainer import RenderTrainer
+    from oracle import nerf_oracle as O
+    sc = O.synthetic_scene(21, 1, 2, 96, 48, 64)
+    inputs = [t.to(cuda) for t in sc['inputs']]
+    u_s, u_p, tgt = sc['u_strat'].to(cuda), sc['u_pdf'].to(cuda), sc['target'].to(cuda)
+    res = []
+    for max_rays in (None, 32):
+        tr = RenderTrainer(cuda, seed=3, bias_std=0.02)
+        feats = sc['features'].to(cuda).requires_grad_(True)
+        loss, out = tr.loss_and_backward(inputs, feats, tgt, u_s, u_p, NEAR, FAR, max_rays)
+        res.append((float(loss), tr.params.grad.clone(), feats.grad.clone(), out[2].clone()))
+    (l0, g0, f0, o0), (l1, g1, f1, o1) = res
+    assert abs(l0 - l1) < 1e-6 * max(1.0, abs(l0))
+    assert torch.equal(o0, o1)                                       # per-ray outputs do not depend on the chunking
+    assert rel_err(g1, g0) < 1e-3 and rel_err(f1, f0) < 1e-3, (rel_err(g1, g0), rel_err(f1, f0))
