@@ -45,10 +45,14 @@ def _peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    """nvidia-smi clocks / throttle reasons sampled while the GPU is under load.  The sampler is started BEFORE the
+    warm-up steps (nvidia-smi needs a few hundred ms to produce its first line) and polls every 20 ms; `mark()` brackets
+    the timed region, `summary()` uses the samples received inside it and -- when the region was shorter than a polling
+    period -- the samples of the last second of load before its end (warm-up steps run the same kernels)."""
 
     def __init__(self, gpu_index: int):
         self.rows, self.proc, self.gpu = [], None, gpu_index
+        self.t0 = self.t1 = None
 
     def __enter__(self):
         q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
@@ -56,7 +60,7 @@ class ClockSampler:
              'clocks_event_reasons.sw_power_cap')
         try:
             self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.gpu), f'--query-gpu={q}',
-                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                          '--format=csv,noheader,nounits', '-lms', '20'],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -66,11 +70,17 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(',')])
+            self.rows.append((time.time(), [x.strip() for x in line.split(',')]))
+
+    def mark(self, start: bool):
+        if start:
+            self.t0 = time.time()
+        else:
+            self.t1 = time.time()
 
     def __exit__(self, *a):
         if self.proc is not None:
-            time.sleep(0.15)
+            time.sleep(0.05)
             self.proc.terminate()
             try:
                 self.proc.wait(timeout=2)
@@ -78,9 +88,16 @@ class ClockSampler:
                 self.proc.kill()
 
     def summary(self):
+        t0 = self.t0 if self.t0 is not None else 0.0
+        t1 = self.t1 if self.t1 is not None else time.time()
+        inside = [r for ts, r in self.rows if t0 <= ts <= t1 + 0.03]
+        window = 'timed region'
+        if len(inside) < 2:
+            inside = [r for ts, r in self.rows if t1 - 1.0 <= ts <= t1 + 0.03]
+            window = 'last second of load up to the end of the timed region (warm-up + timed steps)'
         sm, mx, reasons = [], [], set()
         names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        for r in self.rows:
+        for r in inside:
             try:
                 sm.append(float(r[0])); mx.append(float(r[1]))
             except Exception:
@@ -91,7 +108,7 @@ class ClockSampler:
         if not sm:
             return dict(sm_mhz=None, sm_max_mhz=None, reasons=['unavailable'])
         sm.sort()
-        return dict(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return dict(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm), window=window)
 
 
 def make_scene(seed, nr, nv, device=None, pinned=False):
@@ -236,11 +253,14 @@ def run_b200(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms) / steps
 
-    for _ in range(max(args.warmup, 3)):
-        step_resident()
-    launches0 = _abi.LAUNCHES
     with ClockSampler(local) as clocks:
+        for _ in range(max(args.warmup, 3)):
+            step_resident()
+        launches0 = _abi.LAUNCHES
+        torch.cuda.synchronize()
+        clocks.mark(True)
         ms = timed(step_resident, args.steps)
+        clocks.mark(False)
     launches = _abi.LAUNCHES - launches0
     run_e2e(3)          # warm the loop's own allocations (device batch slots, pinned loss ring, copy stream)
     ms_e2e = timed(run_e2e, args.steps, loop=True)
