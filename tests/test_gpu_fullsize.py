@@ -1,0 +1,135 @@
+"""Parity at the size BASELINE.json's metric is quoted on (cfg2: b = 1, nv = 3, nr = 4096, 64 + 128 samples,
+480 x 640 x 256 fp32 maps), where the oracle cannot run the batch in seconds:
+
+  * a subset of the rays goes through the oracle ON THE FULL-SIZE MAPS and must agree with the rows of the
+    full CUDA batch (rays are independent units, model_v0.py:113-184);
+  * size-independent properties: ray permutation / chunk invariance (bit-exact), per-channel checksum of the
+    feature-map gradient (bilinear weights sum to one: the sum over texels equals the sum over rows of dX),
+    linearity of the whole backward in the loss scale."""
+import pytest
+import torch
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+NEAR, FAR = 0.3, 1.3
+NR, NV, H, W, C = 4096, 3, 480, 640, 256
+
+
+@pytest.fixture(scope='module')
+def cfg2(cuda):
+    from clipnerf_b200 import synthetic
+    from oracle import nerf_oracle as O
+    sc = synthetic.scene(0, NR, NV, H, W, C)
+    named = O.init_params(5, bias_std=0.02)
+    return sc, named
+
+
+def _rel(a, b):
+    """rel_err evaluated on the device (236 M-element maps)"""
+    return float((a.double() - b.double()).abs().max() / b.double().abs().max().clamp_min(1e-30))
+
+
+def _render(cuda, sc, named, sel=None, grad=False, loss_scale=1.0):
+    from clipnerf_b200 import params, render
+    pc = params.from_named(named, 'coarse').to(cuda).requires_grad_(grad)
+    pf = params.from_named(named, 'fine').to(cuda).requires_grad_(grad)
+    ro, rd, img, K, E = [t.to(cuda) for t in sc['inputs']]
+    u_s, u_p = sc['u_strat'].to(cuda), sc['u_pdf'].to(cuda)
+    if sel is not None:
+        ro, rd, u_s, u_p = ro[:, sel], rd[:, sel], u_s[:, sel], u_p[:, sel]
+    feats = sc['features'].to(cuda).requires_grad_(grad)
+    ctx = torch.enable_grad() if grad else torch.no_grad()
+    with ctx:
+        out = render.render_rays(pc, pf, [ro, rd, img, K, E], feats, u_s, u_p, NEAR, FAR)
+    if not grad:
+        return out
+    tgt = sc['target'].to(cuda)
+    loss = loss_scale * (torch.mean((out[0] - tgt) ** 2) + torch.mean((out[2] - tgt) ** 2))
+    loss.backward()
+    return out, pc.grad, pf.grad, feats.grad
+
+
+def test_cfg2_ray_subset_against_oracle(cuda, cfg2):
+    """16 of the 4096 rays through the oracle (bf16-operand form) on the full 3 x 480 x 640 x 259 maps"""
+    from oracle import nerf_oracle as O
+    sc, named = cfg2
+    out = _render(cuda, sc, named)
+    sel = torch.arange(0, NR, NR // 16)
+    ro, rd, img, K, E = sc['inputs']
+    with torch.no_grad():
+        ref = O.mvnerf_call((ro[:, sel], rd[:, sel], img, K, E), sc['features'], named, near=NEAR, far=FAR, n_samples=64,
+                            u_strat=sc['u_strat'][:, sel], u_pdf=sc['u_pdf'][:, sel], quant='bf16')
+    errs = {n: rel_err(a[:, sel.to(cuda)], r) for n, a, r in zip(('rgb', 'depth', 'fine_rgb', 'fine_depth'), out, ref)}
+    print(errs)
+    assert all(v < 1e-2 for v in errs.values()), errs            # tolerance of the bf16-operand path
+    for o in out:
+        assert bool(torch.isfinite(o).all())
+    assert float(out[0].min()) >= 0.0 and float(out[0].max()) <= 1.0 + 1e-5   # sum of w <= 1, sigmoid colours
+    assert float(out[3].max()) <= FAR + 1e-4
+
+
+def test_cfg2_permutation_and_chunk_invariance(cuda, cfg2):
+    """a ray's result does not depend on its position in the batch nor on the other rays (bit-exact): binning,
+    tile placement and the persistent-CTA schedule change, the arithmetic per row does not"""
+    sc, named = cfg2
+    out = _render(cuda, sc, named)
+    perm = torch.randperm(NR, generator=torch.Generator().manual_seed(1))
+    out_p = _render(cuda, sc, named, sel=perm)
+    for a, p_ in zip(out, out_p):
+        assert torch.equal(a[:, perm.to(cuda)], p_)
+    head = torch.arange(1000)                                   # ragged: 1000 rays = 7.8 tiles of coarse rows per view
+    out_h = _render(cuda, sc, named, sel=head)
+    for a, h_ in zip(out, out_h):
+        assert torch.equal(a[:, :1000], h_)
+
+
+def test_cfg2_feature_grad_channel_checksum(cuda, cfg2):
+    """sum over the texels of view v of d_features[..., c] == sum over the rows of view v of dX[:, c], for the coarse
+    (S = 64) and fine-sized (S = 128) row sets swept together, 2.36 M rows; and the sweep is linear in dX"""
+    from clipnerf_b200 import layout, ops
+    sc, _ = cfg2
+    ro, rd, img, K, E = [t.to(cuda) for t in sc['inputs']]
+    scene = ops.Scene(img, sc['features'].to(cuda), K, E)
+    g = torch.Generator(device=cuda).manual_seed(4)
+    sets, want = [], torch.zeros(NV, C, dtype=torch.float64, device=cuda)
+    for S in (64, 128):
+        u = torch.rand(1, NR, S, generator=g, device=cuda)
+        z = (NEAR + (FAR - NEAR) * (torch.arange(S, device=cuda) + u) / S).contiguous()
+        _x, ws = ops.project_gather_fwd(scene, ro, rd, z, return_ws=True)
+        rows = NV * NR * S
+        gx = torch.zeros(rows, 384, device=cuda)
+        gx[:, :C] = torch.randn(rows, C, generator=g, device=cuda)
+        gx = gx.to(torch.bfloat16).to(torch.float32)
+        want += gx[:, :C].view(NV, NR * S, C).double().sum(1)
+        sets.append((ws, layout.matrix_to_tiles(gx), NR, S))
+        del gx
+    d_feat = torch.full_like(scene.features, float('nan'))      # every texel is written
+    ops.feature_grad(scene, sets, d_feat, accumulate=False)
+    got = d_feat[0].double().sum(dim=(1, 2))
+    assert bool(torch.isfinite(d_feat).all())
+    assert rel_err(got, want) < 1e-5, rel_err(got, want)
+    # linearity: dX scaled by 2 (exact in bf16) doubles the map gradient up to the order of the few atomic partial sums
+    sets2 = []
+    for ws, dx, nr, S in sets:
+        m = layout.tiles_to_matrix(dx, 384) * 2.0
+        sets2.append((ws, layout.matrix_to_tiles(m), nr, S))
+        del m
+    d2 = torch.empty_like(d_feat)
+    ops.feature_grad(scene, sets2, d2, accumulate=False)
+    e = _rel(d2, 2.0 * d_feat)
+    assert e < 1e-6, e
+
+
+def test_cfg2_backward_is_linear_in_the_loss_scale(cuda, cfg2):
+    """the whole backward chain (composite, readout, 12 block backwards, l0 dgrad / wgrad, gather backward, sampler,
+    feature-map gradient) is linear in the cotangent and every bf16 rounding on it is invariant under a power-of-two
+    scale: gradients of 4 x loss == 4 x gradients, up to fp32 summation order of the atomics"""
+    sc, named = cfg2
+    _, gc1, gf1, gm1 = _render(cuda, sc, named, grad=True)
+    _, gc4, gf4, gm4 = _render(cuda, sc, named, grad=True, loss_scale=4.0)
+    for a, b_ in ((gc1, gc4), (gf1, gf4), (gm1, gm4)):
+        assert bool(torch.isfinite(a).all()) and float(a.abs().max()) > 0
+        e = _rel(b_, 4.0 * a)
+        assert e < 1e-4, e
