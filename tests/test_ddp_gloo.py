@@ -21,8 +21,15 @@ def _worker(rank, world, port, out):
     from clipnerf_b200.trainer import RenderTrainer
     t = RenderTrainer(torch.device('cpu'), seed=5, warmup_steps=1)
     assert t.world == world
-    for _ in range(3):
-        t.params.grad = _grad_for(rank, NET_PARAMS)
+    for i in range(3):
+        g = _grad_for(rank, NET_PARAMS)
+        t._synced = False                         # (loss_and_backward resets it)
+        if i == 1:
+            # the form used on the GPU: the sum is started inside the backward (render.GRAD_SYNC hook, asynchronous),
+            # allreduce_gradients then only takes the mean
+            work = t._sync_inside_backward(g)
+            work.wait()
+        t.params.grad = g
         t.allreduce_gradients()
         t.apply_gradients()
     out[rank] = t.params.detach().clone()

@@ -58,6 +58,11 @@ def _pass_bwd(P: _Pass, params, grad, scene: ops.Scene, ray_o, ray_d, d_rgb, d_d
     return dz, dx
 
 
+# Set by RenderTrainer for the duration of a backward on > 1 rank: callable([2, NET_PARAMS] gradient buffer) -> a
+# work handle with .wait() (torch.distributed all_reduce(async_op=True)); None = no collective inside the backward.
+GRAD_SYNC = None
+
+
 class _RenderFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, params_c, params_f, features, images, intrinsics, extr_inv, ray_o, ray_d, u_strat, u_pdf,
@@ -85,8 +90,8 @@ class _RenderFn(torch.autograd.Function):
         ray_o, ray_d = ctx.rays
         dev = params_c.device
         need_feat = ctx.needs_input_grad[2]
-        g_c = torch.zeros(NET_PARAMS, dtype=torch.float32, device=dev)
-        g_f = torch.zeros(NET_PARAMS, dtype=torch.float32, device=dev)
+        g_both = torch.zeros(2, NET_PARAMS, dtype=torch.float32, device=dev)   # one buffer: one collective (GRAD_SYNC)
+        g_c, g_f = g_both[0], g_both[1]
         # written exactly once per texel by ops.feature_grad: no zero fill
         d_features = torch.empty_like(scene.features) if need_feat else None
 
@@ -100,10 +105,15 @@ class _RenderFn(torch.autograd.Function):
                                True)
         dw_c = ops.sample_pdf_bwd(C.z, C.weights, ctx.u_pdf, ctx.perm, dz_f)
         _, dx_c = _pass_bwd(C, params_c, g_c, scene, ray_o, ray_d, d_rgb_c, z_or_none(d_depth_c), dw_c, need_feat, False)
+        # both nets' parameter gradients are complete here; the feature-map sweep below (the longest kernel of the
+        # step) does not touch them, so the data-parallel all-reduce is started now and runs under it
+        work = GRAD_SYNC(g_both) if GRAD_SYNC is not None else None
         if need_feat:
             nr = C.z.shape[1]
             ops.feature_grad(scene, [(Fp.ws, dx_f, nr, Fp.z.shape[2]), (C.ws, dx_c, nr, C.z.shape[2])], d_features,
                              accumulate=False)
+        if work is not None:
+            work.wait()                                   # the compute stream waits, the host does not
         ctx.C = ctx.F = ctx.scene = None
         return (g_c, g_f, d_features) + (None,) * 9
 

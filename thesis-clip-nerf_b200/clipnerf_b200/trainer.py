@@ -14,6 +14,7 @@ import torch.distributed as dist
 
 from . import params as P
 from ._abi import NET_PARAMS
+from . import render as _render
 from .render import render_rays
 
 
@@ -37,6 +38,11 @@ class RenderTrainer:
         self.target_lr, self.warmup_steps, self.clip = target_lr, warmup_steps, clip
         self.beta1, self.beta2, self.eps = 0.9, 0.999, 1e-7           # tf.keras.optimizers.Adam defaults
         self.group = process_group
+        # True: start the all-reduce inside the backward, under the feature-map sweep (render.GRAD_SYNC).  Measured on
+        # 8 B200s it is no faster than the plain all-reduce behind the backward (7.40 vs 7.32 ms / step; 7.31 vs 7.33 on 2):
+        # the 1.98 MB collective costs ~50 us over NVSwitch and its kernel competes with the sweep for SMs -- off by default
+        self.overlap_allreduce = False
+        self._synced = False
         self.world = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
 
     @property
@@ -52,11 +58,17 @@ class RenderTrainer:
         ``max_rays``: batches with more rays per scene are rendered in ray chunks of that size whose gradients
         accumulate (rays are independent; the saved activations of one chunk are ~1.2 MB per ray at 3 views)."""
         self.params.grad = None
+        self._synced = False
         nr = inputs[0].shape[1]
         if max_rays is None or nr <= max_rays:
             out = render_rays(self.params[0], self.params[1], inputs, features, u_strat, u_pdf, near, far)
             loss = torch.mean((out[0] - target) ** 2) + torch.mean((out[2] - target) ** 2)
-            loss.backward()
+            # one backward = the whole gradient: the all-reduce is issued inside it, under the feature-map sweep
+            _render.GRAD_SYNC = self._sync_inside_backward if (self.world > 1 and self.overlap_allreduce) else None
+            try:
+                loss.backward()
+            finally:
+                _render.GRAD_SYNC = None
             return loss.detach(), out
         ray_o, ray_d, images, K, Einv = inputs
         total, outs = None, []
@@ -71,10 +83,18 @@ class RenderTrainer:
             outs.append([o.detach() for o in out])
         return total, tuple(torch.cat([o[i] for o in outs], dim=1) for i in range(4))
 
+    def _sync_inside_backward(self, g_both):
+        """render.GRAD_SYNC hook: sum of the [2, NET_PARAMS] gradient buffer over ranks, asynchronous to the
+        compute stream (NCCL's own stream) so that it overlaps the kernels launched behind it"""
+        self._synced = True
+        return dist.all_reduce(g_both, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+
     def allreduce_gradients(self):
-        """the one collective of the path: mean of the flat gradient buffer over ray shards."""
+        """the one collective of the path: mean of the flat gradient buffer over ray shards (already summed inside
+        the backward when ``overlap_allreduce`` applied)."""
         if self.world > 1:
-            dist.all_reduce(self.params.grad, op=dist.ReduceOp.SUM, group=self.group)
+            if not self._synced:
+                dist.all_reduce(self.params.grad, op=dist.ReduceOp.SUM, group=self.group)
             self.params.grad.div_(self.world)
 
     @torch.no_grad()
