@@ -175,7 +175,8 @@ class DevicePrefetcher:
 def fit_host_batches(trainer: RenderTrainer, batches, features, near, far, max_rays: Optional[int] = None):
     """Training loop over HOST batches ``(ray_o, ray_d, images, K, E^-1, target, u_strat, u_pdf)`` in pinned
     memory: prefetched uploads, one ``train_step`` per batch, the loss of every step copied back to the host
-    asynchronously (read one step late, so the host never stalls the launch queue).  Returns the losses."""
+    asynchronously (read two steps late: the launch queue holds up to two steps, so host jitter of a whole step does
+    not idle the device).  Returns the losses."""
     dev = trainer.params.device
     cur = torch.cuda.current_stream(dev)
     losses, pending = [], []
@@ -191,7 +192,7 @@ def fit_host_batches(trainer: RenderTrainer, batches, features, near, far, max_r
         ev = torch.cuda.Event()
         ev.record(cur)
         pending.append((host_loss, ev))
-        if len(pending) > 1:
+        if len(pending) > 2:
             h, e = pending.pop(0)
             e.synchronize()
             losses.append(float(h))
