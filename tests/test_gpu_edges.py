@@ -1,0 +1,145 @@
+"""Edge cases of the render path against the oracle: the smallest batch (one 128-row tile), odd and empty ray
+batches (the reference accepts any n_rays, model_v0.py:113-184), rays whose samples lie behind / outside every source
+camera (pixel coordinates clamped at +-1e6 and the depth floor 1e-8, nerf_utils.py:64-81; the gather then reads the
+border texels, edge clamp of interpolate_bilinear), degenerate random draws (all 0, all just below 1)."""
+import pytest
+import torch
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+NEAR, FAR = 0.3, 1.3
+
+
+def _both(cuda, sc, named, grad=True):
+    """(CUDA outputs, oracle outputs, CUDA grads, oracle grads) of MSE(coarse) + MSE(fine)"""
+    from clipnerf_b200 import params, render
+    from oracle import nerf_oracle as O
+    p = {k: v.clone().requires_grad_(grad) for k, v in named.items()}
+    feats_r = sc['features'].clone().requires_grad_(grad)
+    ref = O.mvnerf_call(sc['inputs'], feats_r, p, near=NEAR, far=FAR, n_samples=64, u_strat=sc['u_strat'],
+                        u_pdf=sc['u_pdf'], quant='bf16')
+    pc = params.from_named(named, 'coarse').to(cuda).requires_grad_(grad)
+    pf = params.from_named(named, 'fine').to(cuda).requires_grad_(grad)
+    feats = sc['features'].to(cuda).requires_grad_(grad)
+    out = render.render_rays(pc, pf, [t.to(cuda) for t in sc['inputs']], feats, sc['u_strat'].to(cuda),
+                             sc['u_pdf'].to(cuda), NEAR, FAR)
+    if not grad:
+        return out, ref, None, None
+    O.train_loss(ref, sc['target']).backward()
+    tgt = sc['target'].to(cuda)
+    (torch.mean((out[0] - tgt) ** 2) + torch.mean((out[2] - tgt) ** 2)).backward()
+    g_cuda = {'fine': params.to_named(pf.grad.cpu(), 'fine'), 'coarse': params.to_named(pc.grad.cpu(), 'coarse'),
+              'features': feats.grad}
+    g_ref = {'named': {k: v.grad for k, v in p.items()}, 'features': feats_r.grad}
+    return out, ref, g_cuda, g_ref
+
+
+def _check_outputs(tag, out, ref, tol=1e-2):
+    errs = {n: rel_err(a, r) for n, a, r in zip(('rgb', 'depth', 'fine_rgb', 'fine_depth'), out, ref)}
+    print(tag, errs)
+    assert all(v < tol for v in errs.values()), errs
+
+
+@pytest.mark.parametrize('nr', [2, 1, 7])
+def test_smallest_and_odd_batches(cuda, nr):
+    """nr = 2 is one tile of coarse rows; odd nr runs with the last ray repeated and must not change any result or
+    gradient (fine-net gradients asserted; the coarse / map gradients carry the ill-conditioned sampler path and are
+    compared on the smallest case only through finiteness, see test_gpu_render.py)"""
+    from oracle import nerf_oracle as O
+    sc = O.synthetic_scene(31, 1, 2, nr, 24, 32)
+    named = O.init_params(3, bias_std=0.02)
+    out, ref, g, gr = _both(cuda, sc, named)
+    for o, r in zip(out, ref):
+        assert tuple(o.shape) == tuple(r.shape)
+    _check_outputs(f'nr={nr}', out, ref)
+    for name, gv in g['fine'].items():
+        r = gr['named'][name]
+        e = rel_err(gv, r)
+        l2 = float((gv.double() - r.double()).norm() / r.double().norm())
+        # a single ray sums only 128 x nv rows into every weight gradient: an element hit by one flipped ReLU mask of
+        # the bf16-operand path stands out in the max norm (measured 3.3e-2), not in L2
+        assert (e < 2e-2 if nr > 1 else (e < 5e-2 and l2 < 2e-2)), (name, e, l2)
+    assert bool(torch.isfinite(g['features']).all())
+    for gv in g['coarse'].values():
+        assert bool(torch.isfinite(gv).all())
+
+
+def test_odd_batch_equals_even_batch_rows(cuda):
+    """the padding ray of an odd batch leaves the real rays bit-identical and adds nothing to the gradients"""
+    from clipnerf_b200 import params, render
+    from oracle import nerf_oracle as O
+    sc = O.synthetic_scene(32, 1, 3, 8, 24, 32)
+    named = O.init_params(4, bias_std=0.02)
+    inputs = [t.to(cuda) for t in sc['inputs']]
+    u_s, u_p, tgt = sc['u_strat'].to(cuda), sc['u_pdf'].to(cuda), sc['target'].to(cuda)
+
+    def run(n):
+        pc = params.from_named(named, 'coarse').to(cuda).requires_grad_(True)
+        pf = params.from_named(named, 'fine').to(cuda).requires_grad_(True)
+        feats = sc['features'].to(cuda).requires_grad_(True)
+        out = render.render_rays(pc, pf, [inputs[0][:, :n], inputs[1][:, :n]] + inputs[2:], feats, u_s[:, :n], u_p[:, :n],
+                                 NEAR, FAR)
+        # loss over the first 7 rays only, normalised identically in both runs
+        (((out[0][:, :7] - tgt[:, :7]) ** 2).sum() + ((out[2][:, :7] - tgt[:, :7]) ** 2).sum()).backward()
+        return out, pc.grad, pf.grad, feats.grad
+    o7, c7, f7, m7 = run(7)
+    o8, c8, f8, m8 = run(8)
+    for a, b_ in zip(o7, o8):
+        assert torch.equal(a, b_[:, :7])
+    for a, b_ in ((c7, c8), (f7, f8), (m7, m8)):
+        assert rel_err(a, b_) < 1e-5, rel_err(a, b_)      # fp32 atomics order only
+
+
+def test_empty_batch(cuda):
+    from clipnerf_b200 import params, render
+    from oracle import nerf_oracle as O
+    sc = O.synthetic_scene(33, 2, 2, 2, 24, 32)
+    named = O.init_params(4)
+    pc = params.from_named(named, 'coarse').to(cuda)
+    pf = params.from_named(named, 'fine').to(cuda)
+    ro, rd, img, K, E = [t.to(cuda) for t in sc['inputs']]
+    out = render.render_rays(pc, pf, [ro[:, :0], rd[:, :0], img, K, E], sc['features'].to(cuda),
+                             sc['u_strat'][:, :0].to(cuda), sc['u_pdf'][:, :0].to(cuda), NEAR, FAR)
+    assert [tuple(o.shape) for o in out] == [(2, 0, 3), (2, 0), (2, 0, 3), (2, 0)]
+
+
+@pytest.mark.parametrize('mode', ['away', 'grazing'])
+def test_samples_outside_every_source_view(cuda, mode):
+    """'away': the rays point away from the scene, every sample projects behind or far outside the source cameras
+    (depth floor 1e-8, +-1e6 clamp, border texels); 'grazing': origins moved next to a source camera so that samples
+    cross its image plane (sign change of the camera depth along the ray)"""
+    from oracle import nerf_oracle as O
+    sc = O.synthetic_scene(34, 1, 3, 16, 24, 32)
+    ro, rd, img, K, E = sc['inputs']
+    if mode == 'away':
+        rd = -rd
+    else:
+        cam_centre = torch.linalg.inv(E[0, 0].double())[:3, 3].float()      # E is the inverse pose: centre of view 0
+        ro = (cam_centre + 0.05 * torch.randn(1, 16, 3, generator=torch.Generator().manual_seed(1))).contiguous()
+    sc = dict(sc, inputs=(ro, rd, img, K, E))
+    named = O.init_params(8, bias_std=0.02)
+    out, ref, g, gr = _both(cuda, sc, named)
+    _check_outputs(mode, out, ref)
+    for o in out:
+        assert bool(torch.isfinite(o).all())
+    assert bool(torch.isfinite(g['features']).all())
+    for name, gv in g['fine'].items():
+        assert bool(torch.isfinite(gv).all())
+        e = rel_err(gv, gr['named'][name])
+        print(f'[{mode}] grad {name:50s} {e:.3e}')
+        assert e < 3e-2, (name, e)
+
+
+@pytest.mark.parametrize('draw', ['zeros', 'ones'])
+def test_degenerate_random_draws(cuda, draw):
+    """u = 0 puts every stratified sample on its bin edge and every inverse-CDF draw on cdf = 0 (first bin, count-based
+    search); u = 1 - 2^-24 is the largest fp32 below one (last bin)"""
+    from oracle import nerf_oracle as O
+    sc = O.synthetic_scene(35, 1, 2, 8, 24, 32)
+    v = 0.0 if draw == 'zeros' else 1.0 - 2.0 ** -24
+    sc = dict(sc, u_strat=torch.full_like(sc['u_strat'], v), u_pdf=torch.full_like(sc['u_pdf'], v))
+    named = O.init_params(9, bias_std=0.02)
+    out, ref, _, _ = _both(cuda, sc, named, grad=False)
+    _check_outputs(draw, out, ref)

@@ -126,9 +126,16 @@ def render_rays(params_coarse: torch.Tensor, params_fine: torch.Tensor, inputs, 
     inputs: the 5-tuple of ``MVNeRFDataGenerator.get_input`` as CUDA tensors
     (ray_o [b,nr,3], ray_d [b,nr,3], images [b,nv,H,W,3] in [0,1], K [b,nv,4,4], E^-1 [b,nv,4,4]);
     ``params_*``: flat parameter vectors (``params.py``); n_samples is fixed at 64 coarse + 128 fine
-    (``u_strat`` / ``u_pdf`` are [b, nr, 64]); nr must be even (tiles of 128 rows)."""
+    (``u_strat`` / ``u_pdf`` are [b, nr, 64]).  Any nr: the kernels work on tiles of 128 rows = 2 rays of 64 coarse
+    samples, an odd batch is rendered with its last ray repeated (the copy's outputs are dropped and receive no
+    gradient); an empty batch returns empty outputs without a launch."""
     ray_o, ray_d, images, K, Einv = inputs
     assert u_strat.shape[-1] == 64 and u_pdf.shape[-1] == 64, 'n_samples is fixed at 64 (sample_pdf kernel)'
-    assert (ray_o.shape[1] * 64) % TILE_ROWS == 0, 'n_rays must be even'
-    return _RenderFn.apply(params_coarse, params_fine, combined_features, images, K, Einv, ray_o, ray_d, u_strat,
-                           u_pdf, float(near), float(far))
+    b, nr = ray_o.shape[:2]
+    if nr == 0:
+        return ray_o.new_zeros(b, 0, 3), ray_o.new_zeros(b, 0), ray_o.new_zeros(b, 0, 3), ray_o.new_zeros(b, 0)
+    if nr % 2:
+        ray_o, ray_d, u_strat, u_pdf = [torch.cat([t, t[:, -1:]], dim=1) for t in (ray_o, ray_d, u_strat, u_pdf)]
+    out = _RenderFn.apply(params_coarse, params_fine, combined_features, images, K, Einv, ray_o, ray_d, u_strat,
+                          u_pdf, float(near), float(far))
+    return tuple(o[:, :nr] for o in out) if nr % 2 else out
