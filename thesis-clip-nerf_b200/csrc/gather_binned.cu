@@ -423,14 +423,14 @@ tile_rows_kernel(CnScene sc, Ws g, int *__restrict__ cursor, uint8_t *__restrict
   } else {
     // =========================== consumers: one warp per row ===========================
     const uint32_t cw = warp - 1;
-    for (uint32_t k = 0;; ++k) {
-      const uint32_t slot = k & 1u;
-      mbar_wait(smem_u32(&bar_full[slot]), (k >> 1) & 1u);
-      const int count = sdesc[slot].count;
-      if (count == 0) break;
-      const float *tile = reinterpret_cast<const float *>(smem + slot * kRowsSlotBytes);
-      const int4 *recs = reinterpret_cast<const int4 *>(smem + slot * kRowsSlotBytes + kTileBytes);
-      if (!kBackward) {
+    if constexpr (!kBackward) {
+      for (uint32_t k = 0;; ++k) {
+        const uint32_t slot = k & 1u;
+        mbar_wait(smem_u32(&bar_full[slot]), (k >> 1) & 1u);
+        const int count = sdesc[slot].count;
+        if (count == 0) break;
+        const float *tile = reinterpret_cast<const float *>(smem + slot * kRowsSlotBytes);
+        const int4 *recs = reinterpret_cast<const int4 *>(smem + slot * kRowsSlotBytes + kTileBytes);
         for (int j = cw; j < count; j += kRowsConsumerWarps) {
           const int4 cur = recs[j];
           const float ax = __int_as_float(cur.z), ay = __int_as_float(cur.w);
@@ -445,46 +445,105 @@ tile_rows_kernel(CnScene sc, Ws g, int *__restrict__ cursor, uint8_t *__restrict
           *reinterpret_cast<uint2 *>(xt + tile_chunk_off(rr, 16 + (l >> 1)) + (l & 1) * 8) =
               make_uint2(pack_bf16x2(g1.x, g1.y), pack_bf16x2(g1.z, g1.w));
         }
-      } else {
-        // batches of 4 rows per warp: all dX loads of the batch are in flight before the first use
-        for (int j0 = cw; j0 < count; j0 += 4 * kRowsConsumerWarps) {
-          int4 rec[4];
-          uint2 ga[4], gb[4];
+        __syncwarp();
+        if (l == 0) mbar_arrive(smem_u32(&bar_empty[slot]));
+      }
+    } else {
+      // A warp works in batches of 4 rows (rows j0 + 16 u of the item): the 8 dX loads of a batch are issued one
+      // batch AHEAD of its math, across work items -- an item gives a warp only one or two batches, so a pipeline
+      // inside the item would expose the full load latency once per item.  The first batch of item k+1 goes out
+      // before the math of the warp's last batch of item k (its records are in the other slot, normally landed).
+      constexpr int kStride = 4 * kRowsConsumerWarps;
+      auto recs_of = [&](uint32_t kk) {
+        return reinterpret_cast<const int4 *>(smem + (kk & 1u) * kRowsSlotBytes + kTileBytes);
+      };
+      auto issue = [&](const int4 *recs, int count, int j0, uint2 (&ga)[4], uint2 (&gb)[4]) {
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const int j = j0 + u * kRowsConsumerWarps;
-            rec[u] = recs[min(j, count - 1)];
-            const uint8_t *t = x_tiles + (int64_t)(rec[u].x >> 7) * CN_X_TILE_BYTES;
-            const uint32_t rr = (uint32_t)rec[u].x & 127u;
-            ga[u] = __ldg(reinterpret_cast<const uint2 *>(t + tile_chunk_off(rr, l >> 1) + (l & 1) * 8));
-            gb[u] = __ldg(reinterpret_cast<const uint2 *>(t + tile_chunk_off(rr, 16 + (l >> 1)) + (l & 1) * 8));
+        for (int u = 0; u < 4; ++u) {
+          const int4 r = recs[min(j0 + u * kRowsConsumerWarps, count - 1)];
+          const uint8_t *t = x_tiles + (int64_t)(r.x >> 7) * CN_X_TILE_BYTES;
+          const uint32_t rr = (uint32_t)r.x & 127u;
+          ga[u] = __ldg(reinterpret_cast<const uint2 *>(t + tile_chunk_off(rr, l >> 1) + (l & 1) * 8));
+          gb[u] = __ldg(reinterpret_cast<const uint2 *>(t + tile_chunk_off(rr, 16 + (l >> 1)) + (l & 1) * 8));
+        }
+      };
+      uint32_t k = 0;
+      mbar_wait(smem_u32(&bar_full[0]), 0);
+      int count = sdesc[0].count;
+      uint2 ga[4], gb[4];
+      bool have = false;                 // ga / gb already hold the loads of the batch about to be computed
+      while (count != 0) {
+        const uint32_t slot = k & 1u;
+        const float *tile = reinterpret_cast<const float *>(smem + slot * kRowsSlotBytes);
+        const int4 *recs = recs_of(k);
+        int next_count = -1;             // rows of item k+1, once looked at
+        for (int j0 = cw; j0 < count; j0 += kStride) {
+          if (!have) issue(recs, count, j0, ga, gb);
+          uint2 na[4], nb[4];
+          bool have_next = false;
+          if (j0 + kStride < count) {
+            issue(recs, count, j0 + kStride, na, nb);
+            have_next = true;
+          } else {
+            const uint32_t nk = k + 1;
+            mbar_wait(smem_u32(&bar_full[nk & 1u]), (nk >> 1) & 1u);
+            next_count = sdesc[nk & 1u].count;
+            if ((int)cw < next_count) {
+              issue(recs_of(nk), next_count, (int)cw, na, nb);
+              have_next = true;
+            }
           }
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
-            if (j0 + u * kRowsConsumerWarps >= count) break;
-            const float ax = __int_as_float(rec[u].z), ay = __int_as_float(rec[u].w);
-            const Corners c = load_corners(tile, rec[u].y, l);
-            // d out / d ax = (1-ay)(TR-TL) + ay(BR-BL);  d out / d ay = (1-ax)(BL-TL) + ax(BR-TR)
+            const int j = j0 + u * kRowsConsumerWarps;
+            if (j >= count) break;
+            const int4 rec = recs[j];
+            const float ax = __int_as_float(rec.z), ay = __int_as_float(rec.w);
+            const Corners c = load_corners(tile, rec.y, l);
             const float gv[8] = {bf16_lo(ga[u].x), bf16_hi(ga[u].x), bf16_lo(ga[u].y), bf16_hi(ga[u].y),
                                  bf16_lo(gb[u].x), bf16_hi(gb[u].x), bf16_lo(gb[u].y), bf16_hi(gb[u].y)};
             const float tlv[8] = {c.tl0.x, c.tl0.y, c.tl0.z, c.tl0.w, c.tl1.x, c.tl1.y, c.tl1.z, c.tl1.w};
             const float trv[8] = {c.tr0.x, c.tr0.y, c.tr0.z, c.tr0.w, c.tr1.x, c.tr1.y, c.tr1.z, c.tr1.w};
             const float blv[8] = {c.bl0.x, c.bl0.y, c.bl0.z, c.bl0.w, c.bl1.x, c.bl1.y, c.bl1.z, c.bl1.w};
             const float brv[8] = {c.br0.x, c.br0.y, c.br0.z, c.br0.w, c.br1.x, c.br1.y, c.br1.z, c.br1.w};
-            float gax = 0.f, gay = 0.f;
+            // four dot products <g, corner> (32 FMAs), combined per lane:
+            //   d/d ax = (1-ay)(s_tr - s_tl) + ay (s_br - s_bl),  d/d ay = (1-ax)(s_bl - s_tl) + ax (s_br - s_tr)
+            float s_tl = 0.f, s_tr = 0.f, s_bl = 0.f, s_br = 0.f;
 #pragma unroll
             for (int ch = 0; ch < 8; ++ch) {
-              gax += gv[ch] * ((1.f - ay) * (trv[ch] - tlv[ch]) + ay * (brv[ch] - blv[ch]));
-              gay += gv[ch] * ((1.f - ax) * (blv[ch] - tlv[ch]) + ax * (brv[ch] - trv[ch]));
+              s_tl = fmaf(gv[ch], tlv[ch], s_tl);
+              s_tr = fmaf(gv[ch], trv[ch], s_tr);
+              s_bl = fmaf(gv[ch], blv[ch], s_bl);
+              s_br = fmaf(gv[ch], brv[ch], s_br);
             }
-            gax = warp_sum_f(gax);
-            gay = warp_sum_f(gay);
-            if (l == 0) g.gpix[rec[u].x] = make_float2(gax, gay);
+            const float gax = (1.f - ay) * (s_tr - s_tl) + ay * (s_br - s_bl);
+            const float gay = (1.f - ax) * (s_bl - s_tl) + ax * (s_br - s_tr);
+            // one butterfly for both sums: after the first exchange the lower half-warp carries d/d ax, the upper d/d ay
+            float v = (l < 16) ? gax : gay;
+            v += __shfl_xor_sync(0xffffffffu, (l < 16) ? gay : gax, 16);
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            const float v_hi = __shfl_sync(0xffffffffu, v, 16);
+            if (l == 0) g.gpix[rec.x] = make_float2(v, v_hi);
           }
+          if (have_next) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              ga[u] = na[u];
+              gb[u] = nb[u];
+            }
+          }
+          have = have_next;
         }
+        __syncwarp();
+        if (l == 0) mbar_arrive(smem_u32(&bar_empty[slot]));
+        ++k;
+        if (next_count < 0) {
+          mbar_wait(smem_u32(&bar_full[k & 1u]), (k >> 1) & 1u);
+          next_count = sdesc[k & 1u].count;
+        }
+        count = next_count;
       }
-      __syncwarp();
-      if (l == 0) mbar_arrive(smem_u32(&bar_empty[slot]));
     }
   }
 }
