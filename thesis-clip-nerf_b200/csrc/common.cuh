@@ -166,6 +166,10 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void *src, uin
                "l"(src), "r"(bytes), "r"(bar)
                : "memory");
 }
+// global -> L2 only: starts the DRAM fetch of a range whose shared-memory slot is not free yet (bytes % 16 == 0)
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void bulk_s2g(void *dst, uint32_t src_smem, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src_smem), "r"(bytes)
                : "memory");
