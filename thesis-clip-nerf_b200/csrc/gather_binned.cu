@@ -341,6 +341,9 @@ __global__ void __launch_bounds__(256) bin_fill_kernel(Ws g) {
 #endif
 // L2 prefetch of the next work item's tile while both slots are busy: measured -3 % on the backward sweep but +12 %
 // on the forward one (it competes with the X stores for L2); off
+#ifndef CN_DIAG
+#define CN_DIAG 0     // 1 / 2: timing diagnostics of the tile sweeps (wrong results): no tile loads / no row work
+#endif
 #ifndef CN_TILE_L2_PREFETCH
 #define CN_TILE_L2_PREFETCH 0
 #endif
@@ -434,12 +437,18 @@ tile_rows_kernel(CnScene sc, Ws g, int *__restrict__ cursor, uint8_t *__restrict
         sdesc[slot].count = item.z;
         const uint32_t row_bytes = (uint32_t)t.nx * kTexBytes;
         const uint32_t bar = smem_u32(&bar_full[slot]);
+#if CN_DIAG == 1   // timing diagnostic only (tools/diag_tile_rows.sh): no tile loads, the rows read stale shared memory
+        mbar_expect_tx(bar, (uint32_t)item.z * 16u);
+#else
         mbar_expect_tx(bar, row_bytes * (uint32_t)t.ny + (uint32_t)item.z * 16u);
+#endif
         const float *src = sc.features + (((int64_t)t.bv * sc.H + t.y0) * sc.W + t.x0) * CN_FEAT_C;
         const uint32_t dst = smem_u32(smem) + slot * kRowsSlotBytes;
         bulk_g2s(dst + kTileBytes, g.rec_s + item.y, (uint32_t)item.z * 16u, bar);
+#if CN_DIAG != 1
         for (int yy = 0; yy < t.ny; ++yy)
           bulk_g2s(dst + yy * (kTT * kTexBytes), src + (int64_t)yy * sc.W * CN_FEAT_C, row_bytes, bar);
+#endif
         it = atomicAdd(cursor, 1);
         item = it < n_items ? g.items[it] : make_int4(0, 0, 0, 0);
 #if CN_TILE_L2_PREFETCH
@@ -466,7 +475,7 @@ tile_rows_kernel(CnScene sc, Ws g, int *__restrict__ cursor, uint8_t *__restrict
         if (count == 0) break;
         const float *tile = reinterpret_cast<const float *>(smem + slot * kRowsSlotBytes);
         const int4 *recs = reinterpret_cast<const int4 *>(smem + slot * kRowsSlotBytes + kTileBytes);
-        for (int j = cw; j < count; j += kRowsConsumerWarps) {
+        for (int j = cw; j < (CN_DIAG == 2 ? 0 : count); j += kRowsConsumerWarps) {   // CN_DIAG 2: loads only
           const int4 cur = recs[j];
           const float ax = __int_as_float(cur.z), ay = __int_as_float(cur.w);
           const Corners c = load_corners(tile, cur.y, l);
@@ -512,7 +521,7 @@ tile_rows_kernel(CnScene sc, Ws g, int *__restrict__ cursor, uint8_t *__restrict
         const float *tile = reinterpret_cast<const float *>(smem + slot * kRowsSlotBytes);
         const int4 *recs = recs_of(k);
         int next_count = -1;             // rows of item k+1, once looked at
-        for (int j0 = cw; j0 < count; j0 += kStride) {
+        for (int j0 = cw; j0 < (CN_DIAG == 2 ? 0 : count); j0 += kStride) {
           if (!have) issue(recs, count, j0, ga, gb);
           uint2 na[4], nb[4];
           bool have_next = false;
