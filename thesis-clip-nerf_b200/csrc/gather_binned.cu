@@ -342,7 +342,7 @@ __global__ void __launch_bounds__(256) bin_fill_kernel(Ws g) {
 // L2 prefetch of the next work item's tile while both slots are busy: measured -3 % on the backward sweep but +12 %
 // on the forward one (it competes with the X stores for L2); off
 #ifndef CN_DIAG
-#define CN_DIAG 0     // 1 / 2: timing diagnostics of the tile sweeps (wrong results): no tile loads / no row work
+#define CN_DIAG 0     // 1 / 2 / 3: timing diagnostics of the tile sweeps (wrong results): no tile loads / no row work / no dX loads
 #endif
 #ifndef CN_TILE_L2_PREFETCH
 #define CN_TILE_L2_PREFETCH 0
@@ -507,8 +507,13 @@ tile_rows_kernel(CnScene sc, Ws g, int *__restrict__ cursor, uint8_t *__restrict
           const int4 r = recs[min(j0 + u * kRowsConsumerWarps, count - 1)];
           const uint8_t *t = x_tiles + (int64_t)(r.x >> 7) * CN_X_TILE_BYTES;
           const uint32_t rr = (uint32_t)r.x & 127u;
+#if CN_DIAG == 3   // timing diagnostic: no dX loads
+          ga[u] = make_uint2((uint32_t)(uintptr_t)t, rr);
+          gb[u] = make_uint2(rr, (uint32_t)(uintptr_t)t);
+#else
           ga[u] = __ldg(reinterpret_cast<const uint2 *>(t + tile_chunk_off(rr, l >> 1) + (l & 1) * 8));
           gb[u] = __ldg(reinterpret_cast<const uint2 *>(t + tile_chunk_off(rr, 16 + (l >> 1)) + (l & 1) * 8));
+#endif
         }
       };
       uint32_t k = 0;
