@@ -310,7 +310,7 @@ def run_b200(args):
     ncu_traffic = {}
     try:
         if (nr, nv) == (4096, 3):
-            with open(os.path.join(ROOT, 'profiles', 'r01_v6_traffic.json')) as f:
+            with open(os.path.join(ROOT, 'profiles', 'r01_v8_traffic.json')) as f:
                 raw = json.load(f)
             for k, v in raw.items():
                 if isinstance(v, dict):
@@ -339,7 +339,7 @@ def run_b200(args):
     traffic = None
     try:
         if (nr, nv) == (4096, 3):
-            with open(os.path.join(ROOT, 'profiles', 'r01_v6_traffic.json')) as f:
+            with open(os.path.join(ROOT, 'profiles', 'r01_v8_traffic.json')) as f:
                 traffic = json.load(f).get(dom, {}).get('dram_bytes_per_launch')
     except Exception:
         traffic = None
@@ -348,7 +348,7 @@ def run_b200(args):
                     'unit': 'GB/s', 'frac': d['frac'], 'traffic': traffic, 'peak_source': peaks['source']}
     elif d.get('bound') == 'tensor':
         roofline = {'kernel': dom, 'bound': 'tensor', 'achieved': d['achieved_tflops'], 'peak': peaks['tf_sustained'],
-                    'unit': 'TFLOP/s', 'frac': d['frac'], 'traffic': traffic, 'traffic_unit': 'bytes per launch (ncu dram read+write, profiles/r01_v6_traffic.json)',
+                    'unit': 'TFLOP/s', 'frac': d['frac'], 'traffic': traffic, 'traffic_unit': 'bytes per launch (ncu dram read+write, profiles/r01_v8_traffic.json)',
                     'peak_source': peaks['source'] + ' (sustained)'}
     else:
         roofline = {'kernel': dom, 'bound': 'hbm', 'achieved': None, 'peak': peaks['hbm_gbs'], 'unit': 'GB/s',
