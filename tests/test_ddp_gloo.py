@@ -33,6 +33,13 @@ def _worker(rank, world, port, out):
         t.allreduce_gradients()
         t.apply_gradients()
     out[rank] = t.params.detach().clone()
+    # the pose-query trainers' collective: mean of a list of gradients, None entries as zeros
+    from clipnerf_b200.trainer import allreduce_mean
+    like = [torch.zeros(3, 4), torch.zeros(5), torch.zeros(2, 2)]
+    grads = [torch.full((3, 4), float(rank + 1)), None if rank == 0 else torch.ones(5), torch.full((2, 2), 2.0 * rank)]
+    red = allreduce_mean(grads, like)
+    assert torch.equal(red[0], torch.full((3, 4), 1.5)) and torch.equal(red[1], torch.full((5,), 0.5))
+    assert torch.equal(red[2], torch.full((2, 2), 1.0))
     dist.destroy_process_group()
 
 

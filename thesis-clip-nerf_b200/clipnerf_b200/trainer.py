@@ -26,6 +26,22 @@ def warmup_lr(step: int, target_lr: float, warmup_steps: float = 10000.0, scale_
     return target_lr if step <= scale_down_after else 0.1 * target_lr
 
 
+def allreduce_mean(grads, like, group=None):
+    """mean over the ranks of a list of gradient tensors (``None`` entries count as zeros of the matching tensor in
+    ``like``) with ONE collective on a flat buffer -- the data-parallel step of the pose-query trainers
+    (``DeltaNGF.train_step``: the 582 337 GraspReadout parameters, 2.33 MB).  No-op on one rank."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return list(grads)
+    flat = torch.cat([(torch.zeros_like(p) if g is None else g).reshape(-1) for g, p in zip(grads, like)])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    flat /= dist.get_world_size(group)
+    out, o = [], 0
+    for p in like:
+        out.append(flat[o:o + p.numel()].view_as(p))
+        o += p.numel()
+    return out
+
+
 class RenderTrainer:
     def __init__(self, device, seed: int = 0, target_lr: float = 1e-4, warmup_steps: float = 10000.0,
                  clip: float = 1.0, bias_std: float = 0.0, process_group=None):

@@ -13,6 +13,7 @@ import numpy as np
 import torch
 
 from clipnerf_b200.query import pose_query_points, query_embeddings
+from clipnerf_b200.trainer import allreduce_mean
 
 from ..mvnerf.layers import MVResNetMLPNeRFEmbedding
 from ..mvnerf.model_v0 import _UpstreamStub
@@ -253,6 +254,8 @@ class DeltaNGF(_PoseQueryModel):
         feats = self.encode(self._to_dev(inputs[4])).detach()
         losses = self.compute_losses(inputs, labels, feats)
         gradients = torch.autograd.grad(losses['loss'], readout_vars, allow_unused=True)
+        # data parallel over scenes / poses: every rank steps on the mean gradient (one collective, no-op on one rank)
+        gradients = allreduce_mean(gradients, readout_vars, getattr(self, 'process_group', None))
         optimize(self.optimizer, readout_vars, gradients, 1.0)
         out = {'landscape_loss': losses['landscape_loss'].detach(), 'grad_loss_t': losses['grad_loss_t'].detach(),
                'grad_loss_r': losses['grad_loss_r'].detach(), 'pred': losses['prediction'].detach().mean()}

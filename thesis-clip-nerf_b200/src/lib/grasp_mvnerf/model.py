@@ -3,6 +3,8 @@ the pose matrices as an input (``inputs = (transforms, images, K, E^-1)``) and a
 (reference :160-171)."""
 import torch
 
+from clipnerf_b200.trainer import allreduce_mean
+
 from ..delta_ngf.model import _PoseQueryModel
 from ..mvnerf.nerf_utils import optimize
 from .layers import GraspReadout
@@ -44,6 +46,7 @@ class GraspMVNeRF(_PoseQueryModel):
             energies = torch.softmax(energies, dim=-1)
         loss = self.loss(self._to_dev(labels), energies)
         gradients = torch.autograd.grad(loss, readout_vars, allow_unused=True)
+        gradients = allreduce_mean(gradients, readout_vars, getattr(self, 'process_group', None))
         optimize(self.optimizer, readout_vars, gradients, 1.0)
         self.loss_tracker.append(float(loss.detach()))
         return {'loss': loss.detach()}

@@ -47,8 +47,19 @@ def main():
     from clipnerf_b200 import _abi, synthetic
     from src.lib.delta_ngf.grasp_optimizer import DNGFOptimizer
     from src.lib.delta_ngf.model import DeltaNGF
-    dev = torch.device('cuda:0')
+    import torch.distributed as dist
+    rank, world = int(os.environ.get('RANK', '0')), int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        # under torch.distributed.run: every rank trains on its own scene / poses, DeltaNGF.train_step averages the
+        # GraspReadout gradient over the ranks (one all-reduce of 2.33 MB); device time = max over ranks
+        os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
+        dist.init_process_group('nccl', device_id=dev)
+        args.case = 'train_step'
     _abi.load()
+    torch.manual_seed(0)          # identical initial weights on every rank (a DDP wrapper would broadcast them)
     bounds = [[0.55, 0.65], [-0.05, 0.05], [0.05, 0.15]]
 
     if args.case in ('all', 'optimize_pose'):
@@ -77,13 +88,13 @@ def main():
 
     if args.case in ('all', 'train_step'):
         b, nv, n_pts = 1, 3, 192
-        sc = synthetic.scene(1, 2, nv, H, W, C, device=dev)
+        sc = synthetic.scene(1 + rank, 2, nv, H, W, C, device=dev)
         _, _, img, K, E = [t.to(dev) for t in sc['inputs']]
         feats = sc['features']
         model = DeltaNGF(n_views=nv, batch_size=b, n_points_train=n_pts, device=dev)
         model.compile()
         model.feature_fn = lambda flat: feats.reshape(b * nv, H, W, C)
-        g = torch.Generator().manual_seed(0)
+        g = torch.Generator().manual_seed(rank)
         ctr = torch.tensor([0.6, 0.0, 0.1])
 
         def poses():
@@ -93,13 +104,29 @@ def main():
         data = ((lp[0], lp[1], tp[0], tp[1], img, K, E),
                 (torch.rand(b, n_pts, generator=g), torch.randn(b, n_pts, 3, generator=g), torch.randn(b, n_pts, 4, generator=g)))
         l0 = _abi.LAUNCHES
+        if world > 1:
+            dist.barrier()
         ms = timed(lambda: model.train_step(data), args.steps, args.warmup)
         launches = (_abi.LAUNCHES - l0) // (args.steps + args.warmup)
-        print(json.dumps({'case': 'train_step', 'metric': 'poses_per_sec_train_step', 'value': b * n_pts / (ms * 1e-3),
-                          'unit': 'poses/s', 'ms_per_step': ms, 'query_points_per_step': 2 * b * n_pts * 42,
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+            w0 = [p.detach().clone() for p in model.grasp_readout.parameters()]
+            for p in w0:                                  # every rank holds the same head after the averaged steps
+                ref = p.clone()
+                dist.broadcast(ref, 0)
+                assert torch.equal(ref, p), 'ranks diverged'
+        if rank == 0:
+            print(json.dumps({'case': 'train_step', 'metric': 'poses_per_sec_train_step',
+                          'value': world * b * n_pts / (ms * 1e-3), 'n_gpus': world,
+                          'unit': 'poses/s', 'ms_per_step': ms, 'query_points_per_step': 2 * world * b * n_pts * 42,
                           'gpu_launches_per_step': launches,
                           'config': {'workload': f'DeltaNGF.train_step: b={b}, nv={nv}, np={n_pts} (x42 offsets), landscape + '
                                                  f'gradient-matching losses, tangent pass in torch, Adam on GraspReadout'}}))
+
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == '__main__':
