@@ -89,7 +89,11 @@ def test_odd_batch_equals_even_batch_rows(cuda):
     for a, b_ in zip(o7, o8):
         assert torch.equal(a, b_[:, :7])
     for a, b_ in ((c7, c8), (f7, f8), (m7, m8)):
-        assert rel_err(a, b_) < 1e-4, rel_err(a, b_)      # fp32 summation order only (tiles land on other CTAs; measured 1e-5)
+        # not bit-equal: dz sums its per-view terms with fp32 atomics, and a last-bit change there can flip ONE bf16
+        # rounding of the coarse g stream (tools/diag_odd_batch.py bisects it: two identical runs differ the same way),
+        # i.e. 2^-8 of that element -- measured 1e-7 ... 1.7e-4 of the tensor maximum.  A gradient contribution of the
+        # padding ray would be O(1/8).
+        assert rel_err(a, b_) < 2e-3, rel_err(a, b_)
 
 
 def test_empty_batch(cuda):
