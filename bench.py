@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import argparse
 import contextlib
+import gc
 import json
 import os
 import subprocess
@@ -194,7 +195,7 @@ def workload_config(args, nr):
 def run_b200(args):
     import torch.distributed as dist
     from clipnerf_b200 import _abi
-    from clipnerf_b200.trainer import RenderTrainer, fit_host_batches
+    from clipnerf_b200.trainer import RenderTrainer, fit_host_batches, fit_host_batches_graph
 
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -222,6 +223,7 @@ def run_b200(args):
     h2d_bytes = sum(t.numel() * t.element_size() for t in sc['inputs']) + \
         sum(sc[k].numel() * sc[k].element_size() for k in ('u_strat', 'u_pdf', 'target'))
 
+    use_graph = world == 1 and nr <= args.chunk_rays and not args.no_graph
     host_batch = list(sc['inputs']) + [sc['target'], sc['u_strat'], sc['u_pdf']]
     assert all(t.is_pinned() for t in host_batch)
 
@@ -229,7 +231,12 @@ def run_b200(args):
         # the call a user makes: a training loop over host batches (the reference's 5-tuple + targets + random
         # draws, pinned memory).  Every step uploads its own batch (copy stream, one batch ahead of the kernels)
         # and returns its loss to the host.
-        losses = fit_host_batches(trainer, (host_batch for _ in range(steps)), feats, NEAR, FAR, args.chunk_rays)
+        if use_graph:
+            # the training step replayed from CUDA graphs (one rank, un-chunked batch): per step the host enqueues the
+            # uploads, one graph launch and the loss read-back, so a slow host no longer bounds the loop
+            losses = fit_host_batches_graph(trainer, (host_batch for _ in range(steps)), feats, NEAR, FAR)
+        else:
+            losses = fit_host_batches(trainer, (host_batch for _ in range(steps)), feats, NEAR, FAR, args.chunk_rays)
         assert len(losses) == steps and all(l == l for l in losses)
 
     def barrier():
@@ -238,14 +245,21 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     def timed(fn, steps, loop=False):
+        # the cyclic collector is run before and held during the timed region (as timeit does): a generation-2 pass
+        # over the autograd garbage of earlier steps can take longer than the two steps the launch queue runs ahead
+        gc.collect()
+        gc.disable()
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        if loop:
-            fn(steps)
-        else:
-            for _ in range(steps):
-                fn()
+        try:
+            if loop:
+                fn(steps)
+            else:
+                for _ in range(steps):
+                    fn()
+        finally:
+            gc.enable()
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -369,7 +383,8 @@ def run_b200(args):
             'data': 'synthetic', 'config': workload_config(args, nr),
             'e2e': {'value': world * nr / (ms_e2e * 1e-3), 'unit': 'rays/s', 'ms_per_step': ms_e2e,
                     'h2d_bytes_per_step': h2d_bytes, 'd2h_bytes_per_step': 4,
-                    'note': 'fit_host_batches(): host batch = the reference 5-tuple (rays, images, K, E^-1) + targets + '
+                    'loop': 'fit_host_batches_graph (train step replayed from a CUDA graph)' if use_graph else 'fit_host_batches (eager launches)',
+                    'note': 'host batch = the reference 5-tuple (rays, images, K, E^-1) + targets + '
                             'random draws in pinned memory, uploaded every step on a copy stream one batch ahead; loss '
                             'read back every step; combined_features stay on the device, where the upstream encoders '
                             'produce them'},
@@ -387,8 +402,9 @@ def run_b200(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=10)
+    ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--no-graph', action='store_true', help='e2e loop with eager launches instead of CUDA-graph replay')
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--rays', type=int, default=4096, help='rays per GPU per step')
     ap.add_argument('--nv', type=int, default=3, help='source views')

@@ -156,3 +156,40 @@ def test_ray_chunked_training_step_matches_unchunked(cuda):
     assert torch.equal(o0, o1)                                       # per-ray outputs do not depend on the chunking
     # (map gradient: single bf16 rounding flips of the g stream between two runs, see tests/test_gpu_edges.py)
     assert rel_err(g1, g0) < 1e-3 and rel_err(f1, f0) < 3e-3, (rel_err(g1, g0), rel_err(f1, f0))
+
+
+def test_graph_replayed_training_loop_matches_eager(cuda):
+    """fit_host_batches_graph (train step replayed from CUDA graphs, step counter / warm-up schedule / Adam bias
+    corrections on the device) walks the same parameters and losses as the eager loop"""
+    from clipnerf_b200.trainer import RenderTrainer, fit_host_batches, fit_host_batches_graph
+    from oracle import nerf_oracle as O
+    batches = []
+    for seed in (41, 42, 43):
+        sc = O.synthetic_scene(seed, 1, 2, 32, 48, 64)
+        batches.append([t.pin_memory() for t in list(sc['inputs']) + [sc['target'], sc['u_strat'], sc['u_pdf']]])
+    feats = O.synthetic_scene(41, 1, 2, 32, 48, 64)['features'].to(cuda)
+    seq = [batches[i % 3] for i in range(7)]
+
+    def both(lr):
+        res = []
+        for fit in (fit_host_batches, fit_host_batches_graph):
+            tr = RenderTrainer(cuda, seed=3, bias_std=0.02, warmup_steps=4, target_lr=lr)
+            f = feats.clone().requires_grad_(True)
+            losses = fit(tr, iter(seq), f, NEAR, FAR)
+            res.append((losses, tr.params.detach().clone(), tr.iterations, f.grad.clone()))
+        return res
+    # frozen parameters (lr = 0): every replay must return the losses and the map gradient of ITS batch
+    (l0, p0, n0, g0), (l1, p1, n1, g1) = both(0.0)
+    assert n0 == n1 == 7 and torch.equal(p0, p1)
+    print('lr=0: loss diff', max(abs(a - b_) for a, b_ in zip(l0, l1)), 'map grad diff', rel_err(g1, g0))
+    assert max(abs(a - b_) for a, b_ in zip(l0, l1)) < 1e-5 * max(l0)
+    assert rel_err(g1, g0) < 3e-3, rel_err(g1, g0)
+    # training: not bit-equal -- Adam's first updates are ~lr * sign(g), so the last-bit run-to-run noise of the
+    # gradients (fp32 atomics) moves parameters whose gradient is ~0 by up to lr per step; the optimizer arithmetic itself
+    # is compared exactly in tests/test_host.py::test_device_side_adam_matches_host_side
+    (l0, p0, n0, g0), (l1, p1, n1, g1) = both(1e-4)
+    dl = max(abs(a - b_) for a, b_ in zip(l0, l1))
+    print('lr=1e-4: loss diff', dl, 'param diff', rel_err(p1, p0))
+    assert n0 == n1 == 7
+    assert dl < 3e-3 * max(l0), dl
+    assert rel_err(p1, p0) < 5e-3, rel_err(p1, p0)

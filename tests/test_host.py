@@ -40,3 +40,21 @@ def test_x_column_order_is_a_permutation():
     cols = [layout.x_col_to_ref(j) for j in range(384)]
     assert sorted(cols[:379]) == list(range(379)) and cols[379:] == [-1] * 5
     assert cols[0] == 123 and cols[256] == 0 and cols[316] == 60 and cols[376] == 120
+
+
+def test_device_side_adam_matches_host_side():
+    """RenderTrainer.apply_gradients_on_device (step counter, warm-up schedule and bias corrections as device scalars:
+    the form a CUDA graph can replay) against apply_gradients, same gradients, across the warm-up boundary"""
+    import torch
+    from clipnerf_b200.trainer import RenderTrainer
+    dev = torch.device('cpu')
+    a, b = RenderTrainer(dev, seed=2, warmup_steps=3), RenderTrainer(dev, seed=2, warmup_steps=3)
+    g = torch.Generator().manual_seed(0)
+    for i in range(6):
+        grad = torch.randn(a.params.shape, generator=g) * (3.0 if i == 2 else 0.1)      # some entries beyond the clip
+        a.params.grad, b.params.grad = grad.clone(), grad.clone()
+        a.apply_gradients()
+        b.apply_gradients_on_device()
+        assert float(b._t_dev) == a.iterations == i + 1
+        err = float((a.params - b.params).abs().max() / a.params.abs().max())
+        assert err < 1e-6, (i, err)

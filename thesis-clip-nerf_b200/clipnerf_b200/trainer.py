@@ -58,6 +58,7 @@ class RenderTrainer:
         # 8 B200s it is no faster than the plain all-reduce behind the backward (7.40 vs 7.32 ms / step; 7.31 vs 7.33 on 2):
         # the 1.98 MB collective costs ~50 us over NVSwitch and its kernel competes with the sweep for SMs -- off by default
         self.overlap_allreduce = False
+        self._t_dev = None          # device-side step counter of apply_gradients_on_device
         self._synced = False
         self.world = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
 
@@ -127,6 +128,63 @@ class RenderTrainer:
         self.v.mul_(self.beta2).addcmul_(g, g, value=1.0 - self.beta2)
         self.params.addcdiv_(self.m, self.v.sqrt().add_(self.eps), value=-lr_t)
 
+    @torch.no_grad()
+    def apply_gradients_on_device(self):
+        """``apply_gradients`` with the step counter, the warm-up schedule and the bias corrections evaluated on the
+        device (float64 scalars), so that the update can be recorded into a CUDA graph and replayed."""
+        if self._t_dev is None:
+            self._t_dev = torch.zeros((), dtype=torch.float64, device=self.params.device)
+            self._t_dev.fill_(float(self.iterations))
+        g = self.params.grad
+        if self.clip > 0:
+            g.clamp_(-self.clip, self.clip)
+        self._t_dev += 1.0
+        t = self._t_dev
+        warm = max(1.0, float(self.warmup_steps))
+        lr = torch.where(t <= warm, t / warm * self.target_lr,
+                         torch.where(t <= 450000.0, torch.full_like(t, self.target_lr), torch.full_like(t, 0.1 * self.target_lr)))
+        lr_t = (lr * torch.sqrt(1.0 - self.beta2 ** t) / (1.0 - self.beta1 ** t)).to(torch.float32)
+        self.m.mul_(self.beta1).add_(g, alpha=1.0 - self.beta1)
+        self.v.mul_(self.beta2).addcmul_(g, g, value=1.0 - self.beta2)
+        self.params.sub_(lr_t * self.m / self.v.sqrt().add_(self.eps))
+
+    def capture(self, inputs, features, target, u_strat, u_pdf, near, far, pool=None, warmup: int = 0):
+        """One ``train_step`` on FIXED device buffers recorded into a CUDA graph: ~45 kernel launches of this library,
+        the loss, the all-reduce-free optimizer update (one rank) -- replayed with a single launch, so the host's
+        per-step work no longer bounds the loop.  Returns ``replay() -> loss`` (a device scalar overwritten by the next
+        replay).  ``features.grad`` is written by every replay (memory owned by the graph).  The ``warmup`` eager
+        steps DO update the parameters."""
+        assert self.world == 1, 'capture(): single-rank step (the all-reduce is not recorded)'
+        features.grad = None
+        if self._t_dev is None:
+            self._t_dev = torch.zeros((), dtype=torch.float64, device=self.params.device)
+        self._t_dev.fill_(float(self.iterations))      # (outside the graph) continue from the eager steps so far
+
+        def step():
+            features.grad = None
+            loss, _ = self.loss_and_backward(inputs, features, target, u_strat, u_pdf, near, far)
+            self.apply_gradients_on_device()
+            return loss
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                step()
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, pool=pool):
+            loss = step()
+        self.iterations += warmup              # the capture pass itself executes nothing
+        d_features = features.grad             # this graph's map gradient (graph-owned memory)
+
+        def replay():
+            graph.replay()
+            self.iterations += 1               # host mirror of the device-side counter
+            features.grad = d_features         # (another graph of the same pool may have been replayed in between)
+            return loss
+        replay.graph = graph
+        return replay
+
     def train_step(self, inputs, features, target, u_strat, u_pdf, near, far, max_rays: Optional[int] = None):
         loss, _ = self.loss_and_backward(inputs, features, target, u_strat, u_pdf, near, far, max_rays)
         self.allreduce_gradients()
@@ -143,11 +201,13 @@ class DevicePrefetcher:
     once; two device buffer sets are recycled, guarded by events (a set is overwritten only after the
     step that read it has finished)."""
 
-    def __init__(self, batches, device, depth: int = 2):
+    def __init__(self, batches, device, depth: int = 2, slots=None):
         self.it = iter(batches)
         self.device = device
         self.copy_stream = torch.cuda.Stream(device)
-        self.slots = [None] * depth            # device tensors of each buffer set
+        # device tensors of each buffer set; a caller that needs stable addresses (CUDA graphs) passes its own list
+        self.slots = slots if slots is not None else [None] * depth
+        depth = len(self.slots)
         self.free = [None] * depth             # event: the consumer is done with the set
         self.k = 0
         self.next = None
@@ -186,6 +246,46 @@ class DevicePrefetcher:
         batch = self.slots[k]
         self._upload()                          # next batch goes out while this one is consumed
         return batch, self.free[k]
+
+
+def fit_host_batches_graph(trainer: RenderTrainer, batches, features, near, far):
+    """``fit_host_batches`` with the training step replayed from CUDA graphs (one per device buffer set of the
+    prefetcher, sharing one memory pool): per step the host enqueues the uploads, one graph launch and the loss
+    read-back.  Single rank, fixed batch shapes."""
+    dev = trainer.params.device
+    cur = torch.cuda.current_stream(dev)
+    losses, pending = [], []
+    ring = torch.empty(4, dtype=torch.float32, pin_memory=True)
+    graphs = trainer.__dict__.setdefault('_graphs', {})
+    slots = trainer.__dict__.setdefault('_graph_slots', [None, None])
+    k = 0
+    for batch, done in DevicePrefetcher(batches, dev, slots=slots):
+        key = tuple(t.data_ptr() for t in batch) + (features.data_ptr(),)
+        if trainer.iterations == 0:
+            # the first step of a trainer's life runs eagerly (lazy initialisations must not happen under capture)
+            loss = trainer.train_step(batch[:5], features, batch[5], batch[6], batch[7], near, far)
+        else:
+            if key not in graphs:
+                pool = next(iter(graphs.values())).graph.pool() if graphs else None
+                torch.cuda.synchronize(dev)
+                graphs[key] = trainer.capture(batch[:5], features, batch[5], batch[6], batch[7], near, far, pool=pool)
+                torch.cuda.synchronize(dev)
+            loss = graphs[key]()
+        done.record(cur)
+        host_loss = ring[k % 4]
+        k += 1
+        host_loss.copy_(loss, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        pending.append((host_loss, ev))
+        if len(pending) > 2:
+            h, e = pending.pop(0)
+            e.synchronize()
+            losses.append(float(h))
+    for h, e in pending:
+        e.synchronize()
+        losses.append(float(h))
+    return losses
 
 
 def fit_host_batches(trainer: RenderTrainer, batches, features, near, far, max_rays: Optional[int] = None):
