@@ -223,7 +223,7 @@ def run_b200(args):
     h2d_bytes = sum(t.numel() * t.element_size() for t in sc['inputs']) + \
         sum(sc[k].numel() * sc[k].element_size() for k in ('u_strat', 'u_pdf', 'target'))
 
-    use_graph = world == 1 and nr <= args.chunk_rays and not args.no_graph
+    use_graph = nr <= args.chunk_rays and not args.no_graph      # (ray-chunked batches launch eagerly)
     host_batch = list(sc['inputs']) + [sc['target'], sc['u_strat'], sc['u_pdf']]
     assert all(t.is_pinned() for t in host_batch)
 
@@ -232,7 +232,7 @@ def run_b200(args):
         # draws, pinned memory).  Every step uploads its own batch (copy stream, one batch ahead of the kernels)
         # and returns its loss to the host.
         if use_graph:
-            # the training step replayed from CUDA graphs (one rank, un-chunked batch): per step the host enqueues the
+            # the training step replayed from CUDA graphs (un-chunked batch): per step the host enqueues the
             # uploads, one graph launch and the loss read-back, so a slow host no longer bounds the loop
             losses = fit_host_batches_graph(trainer, (host_batch for _ in range(steps)), feats, NEAR, FAR)
         else:
@@ -275,8 +275,8 @@ def run_b200(args):
         launches_per_step = (_abi.LAUNCHES - launches0) // n_warm
         step_timed = step_resident
         if use_graph:
-            # one rank, un-chunked batch: the step (this library's kernel launches, loss, optimizer) is recorded into a
-            # CUDA graph once and replayed -- the same launches without the host's per-launch cost between them
+            # un-chunked batch: the step (this library's kernel launches, loss, NCCL gradient all-reduce on > 1 rank,
+            # optimizer) is recorded into a CUDA graph once and replayed -- the same launches without the host's per-launch cost between them
             step_timed = trainer.capture(dev_inputs, feats, dev_u[2], dev_u[0], dev_u[1], NEAR, FAR)
             for _ in range(2):
                 step_timed()
@@ -405,6 +405,14 @@ def run_b200(args):
             out['cpu_baseline'] = base
         print(json.dumps(out))
     if world > 1:
+        sys.stdout.flush()
+        if use_graph:
+            # graphs that recorded NCCL work must be gone before the communicator is torn down
+            trainer.__dict__.pop('_graphs', None)
+            step_timed = None  # noqa: F841
+            gc.collect()
+            torch.cuda.synchronize()
+        dist.barrier()
         dist.destroy_process_group()
 
 
@@ -413,6 +421,7 @@ def main():
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--graph-multi', action='store_true', help='(default now) replay CUDA graphs, with the NCCL all-reduce recorded, on > 1 rank')
     ap.add_argument('--no-graph', action='store_true', help='e2e loop with eager launches instead of CUDA-graph replay')
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--rays', type=int, default=4096, help='rays per GPU per step')

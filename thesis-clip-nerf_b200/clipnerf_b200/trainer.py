@@ -150,11 +150,10 @@ class RenderTrainer:
 
     def capture(self, inputs, features, target, u_strat, u_pdf, near, far, pool=None, warmup: int = 0):
         """One ``train_step`` on FIXED device buffers recorded into a CUDA graph: ~45 kernel launches of this library,
-        the loss, the all-reduce-free optimizer update (one rank) -- replayed with a single launch, so the host's
+        the loss, the gradient all-reduce (more than one rank) and the optimizer update -- replayed with a single launch, so the host's
         per-step work no longer bounds the loop.  Returns ``replay() -> loss`` (a device scalar overwritten by the next
         replay).  ``features.grad`` is written by every replay (memory owned by the graph).  The ``warmup`` eager
         steps DO update the parameters."""
-        assert self.world == 1, 'capture(): single-rank step (the all-reduce is not recorded)'
         features.grad = None
         if self._t_dev is None:
             self._t_dev = torch.zeros((), dtype=torch.float64, device=self.params.device)
@@ -163,6 +162,7 @@ class RenderTrainer:
         def step():
             features.grad = None
             loss, _ = self.loss_and_backward(inputs, features, target, u_strat, u_pdf, near, far)
+            self.allreduce_gradients()         # > 1 rank: the NCCL all-reduce is recorded into the graph with the kernels
             self.apply_gradients_on_device()
             return loss
         side = torch.cuda.Stream()
@@ -251,7 +251,8 @@ class DevicePrefetcher:
 def fit_host_batches_graph(trainer: RenderTrainer, batches, features, near, far):
     """``fit_host_batches`` with the training step replayed from CUDA graphs (one per device buffer set of the
     prefetcher, sharing one memory pool): per step the host enqueues the uploads, one graph launch and the loss
-    read-back.  Single rank, fixed batch shapes."""
+    read-back.  Fixed batch shapes; on more than one rank the NCCL all-reduce is part of the graphs (drop
+    ``trainer._graphs`` before destroying the process group)."""
     dev = trainer.params.device
     cur = torch.cuda.current_stream(dev)
     losses, pending = [], []
