@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define CN_ABI_VERSION 5
+#define CN_ABI_VERSION 6
 #define CN_TILE_ROWS 128
 #define CN_HIDDEN 128
 #define CN_FEAT_C 256          /* combined_features channels (model_v0.py:60)            */
@@ -239,6 +239,23 @@ int cn_mlp_l0_dgrad(const void *packed, const void *g0_tiles, int64_t n_tiles, v
 /* ... and dW0 += scale * X^T . g0, db0 += scale * sum(g0), accumulated into grad.      */
 int cn_mlp_l0_wgrad(const void *x_tiles, const void *g0_tiles, int64_t n_tiles, float scale,
                     float *grad, void *stream);
+
+/* ---- parameter update ----------------------------------------------------------- */
+
+/* The update MVVNeRFRenderer.train_step applies (model_v0.py:186-197) as one launch over flat fp32 buffers:
+ * optimize() (nerf_utils.py:8-12: per-element clip_by_value(g, -clip, clip), clip <= 0 = off) followed by
+ * tf.keras.optimizers.Adam(learning_rate=WarmupScheduler(target_lr, warmup_steps, scale_down_after))
+ * (train_nerf.py:22-23, nerf_utils.py:288-300):
+ *   t = *step_counter + 1;  lr = t <= warmup ? t / warmup * target : (t <= scale_down_after ? target : 0.1 target)
+ *   g = clip(grad * grad_scale);  m = b1 m + (1-b1) g;  v = b2 v + (1-b2) g^2
+ *   p -= lr sqrt(1 - b2^t) / (1 - b1^t) * m / (sqrt(v) + eps);   *step_counter = t      (grad is left clipped)
+ * The buffers are [n_rows][row_stride]; the first n_update elements of every row are updated (the reference's
+ * optimizer groups hold the two embeddings only, train_nerf.py:27-32: n_update = CN_EMB_PARAMS leaves the readouts
+ * untouched).  step_counter is a DEVICE double, so a CUDA graph that recorded the launch replays the schedule.      */
+int cn_adam_step(float *params, float *grad, float *m, float *v, int64_t n_rows, int64_t row_stride,
+                 int64_t n_update, double *step_counter, double target_lr, double warmup_steps,
+                 double scale_down_after, float grad_scale, float clip, double beta1, double beta2, double eps,
+                 void *stream);
 
 /* ---- diagnostics ---------------------------------------------------------------- */
 

@@ -75,11 +75,15 @@ def test_model_call_infer_and_train_step(cuda, tmp_path):
         assert rel_err(a, b) < 1e-2
     # call() goes through the plug-in feature producer
     m.feature_fn = lambda images: feats.reshape(-1, *feats.shape[2:])
-    m.compile()
-    before = m.coarse_embedding.flat.detach().clone()
+    m.compile(warmup_steps=1)                                    # default optimizer: RenderTrainer on nerf_params
+    from clipnerf_b200.trainer import RenderTrainer
+    assert isinstance(m.optimizer, RenderTrainer) and m.optimizer.params is m.nerf_params
+    before, ro_before = m.coarse_embedding.flat.detach().clone(), m.fine_readout.flat.detach().clone()
     losses = [float(m.train_step((inputs_np, sc['target'].numpy()))['loss']) for _ in range(8)]
     assert np.isfinite(losses).all() and losses[-1] < losses[0]
     assert not torch.equal(before, m.coarse_embedding.flat.detach())
+    # the reference's optimizer groups hold the embeddings only (train_nerf.py:27-33): readouts keep their values
+    assert torch.equal(ro_before, m.fine_readout.flat.detach()) and m.optimizer.iterations == 8
     # store / load round trip, False when a group is missing
     path = str(tmp_path / 'model_final')
     assert m.load(path) is False
@@ -96,6 +100,43 @@ def test_model_call_infer_and_train_step(cuda, tmp_path):
     m.feature_fn = lambda images: torch.tanh(images.mean(-1, keepdim=True)).expand(-1, -1, -1, 256).contiguous()
     hist = m.fit(gen, epochs=2, initial_epoch=0)
     assert len(hist['loss']) == 2 and np.isfinite(hist['loss']).all()
+
+
+def test_fit_is_one_graph_launch_per_step(cuda, monkeypatch):
+    """MVVNeRFRenderer.fit with the default optimizer (what src/train_nerf.py:52 calls) drives RenderTrainer: after the
+    first (eager) step and one capture per device buffer set, every step is ONE CUDA-graph launch and no kernel of the
+    library is launched outside it; an explicit torch optimizer selects the plain eager step."""
+    from clipnerf_b200 import _abi
+    from clipnerf_b200.synthetic import SyntheticNerfDataset
+    from src.lib.data_generator.mvnerf import MVNeRFDataGenerator
+    ds = SyntheticNerfDataset(n_scenes=6, n_perspectives=4, H=24, W=32)
+    np.random.seed(3)
+    gen = MVNeRFDataGenerator(ds, n_rays_train=32, batch_size=1, n_views=2, shuffle=True)
+    m = _model(cuda, 2)
+    maps = torch.nn.Parameter(torch.randn(2, 24, 32, 256, device=cuda))          # "encoder output" that trains itself
+    m.feature_fn = lambda images: maps
+    m.compile(warmup_steps=2)
+    replays = []
+    real_replay = torch.cuda.CUDAGraph.replay
+    monkeypatch.setattr(torch.cuda.CUDAGraph, 'replay', lambda self: (replays.append(_abi.LAUNCHES), real_replay(self))[1])
+    p0 = m.nerf_params.detach().clone()
+    hist = m.fit(gen, epochs=1)                      # 6 steps: 1 eager, 2 captures (+ replay), 3 pure replays
+    assert len(replays) == 5 and m.optimizer.iterations == 6 and len(m.loss_tracker) == 6
+    launches_after_captures = replays[2]
+    assert _abi.LAUNCHES == launches_after_captures, 'a step launched library kernels outside the graph'
+    assert np.isfinite(hist['loss']).all() and not torch.equal(p0, m.nerf_params.detach())
+    assert maps.grad is not None and torch.isfinite(maps.grad).all() and float(maps.grad.abs().max()) > 0
+    assert float(m.optimizer._t_dev) == 6.0
+    hist = m.fit(gen, epochs=3, initial_epoch=1)     # graphs are reused across epochs
+    assert len(replays) == 5 + 12 and _abi.LAUNCHES == launches_after_captures and m.optimizer.iterations == 18
+    # explicit torch optimizer: eager autograd step over the same flat parameter
+    m2 = _model(cuda, 2)
+    m2.feature_fn = lambda images: maps.detach()
+    m2.compile(optimizer=torch.optim.Adam(m2.parameters(), lr=1e-3, eps=1e-7))
+    assert m2._trainer is None
+    q0 = m2.nerf_params.detach().clone()
+    m2.fit(gen, epochs=1)
+    assert not torch.equal(q0, m2.nerf_params.detach())
 
 
 def test_render_view_bookkeeping(cuda):

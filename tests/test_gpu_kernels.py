@@ -253,6 +253,30 @@ def test_binned_scatter_many_rows(cuda, corner):
     assert rel_err(d_feat, 2 * feats.grad) < 1e-4
 
 
+@pytest.mark.parametrize('cap', [0, 3, 17])
+def test_feature_grad_with_a_full_deferred_list(cuda, cap, monkeypatch):
+    """many texels with hundreds of rows (small map, many rays): the deferred-chunk list of the feature-gradient sweep
+    is sized from the row count and cannot fill up in production; CN_DEBUG_HEAVY_CAP forces the list-full path
+    (texels that do not fit are summed in place, the slots they had reserved are skip entries) -- the map must equal
+    the one of the default run, with and without accumulation, on a workspace that holds stale entries"""
+    from clipnerf_b200 import ops
+    sc = _scene(seed=8, b=1, nv=2, nr=512, H=6, W=8)
+    scene, ro, rd = _cuda_scene(sc, cuda)
+    z = ops.sample_coarse(sc['u_strat'].to(cuda), NEAR, FAR)
+    x, ws = ops.project_gather_fwd(scene, ro, rd, z, return_ws=True)
+    dx = (torch.randn(x.numel() // 2, generator=torch.Generator().manual_seed(1)) * 0.5).to(torch.bfloat16).view(
+        torch.uint8).to(cuda)
+    ref = torch.full_like(scene.features, float('nan'))
+    ops.feature_grad(scene, [(ws, dx, 512, 64)], ref, accumulate=False)          # also leaves entries in the list
+    assert torch.isfinite(ref).all()
+    monkeypatch.setenv('CN_DEBUG_HEAVY_CAP', str(cap))
+    got = torch.full_like(ref, float('nan'))
+    ops.feature_grad(scene, [(ws, dx, 512, 64)], got, accumulate=False)
+    assert rel_err(got, ref) < 1e-5, rel_err(got, ref)
+    ops.feature_grad(scene, [(ws, dx, 512, 64)], got, accumulate=True)
+    assert rel_err(got, 2 * ref) < 1e-5
+
+
 def test_project_gather_bwd_rays(cuda):
     """cn_project_gather_bwd_rays with S > 1 and z != 0: d/d(ray origin), d/d(ray direction) (through x = o + z d AND
     through posenc(E^-1 [d; 1])) and dz against the fp64 oracle for a given dX."""

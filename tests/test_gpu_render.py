@@ -158,38 +158,132 @@ def test_ray_chunked_training_step_matches_unchunked(cuda):
     assert rel_err(g1, g0) < 1e-3 and rel_err(f1, f0) < 3e-3, (rel_err(g1, g0), rel_err(f1, f0))
 
 
-def test_graph_replayed_training_loop_matches_eager(cuda):
-    """fit_host_batches_graph (train step replayed from CUDA graphs, step counter / warm-up schedule / Adam bias
-    corrections on the device) walks the same parameters and losses as the eager loop"""
-    from clipnerf_b200.trainer import RenderTrainer, fit_host_batches, fit_host_batches_graph
+def _loop_batches(cuda, nr=32):
     from oracle import nerf_oracle as O
     batches = []
     for seed in (41, 42, 43):
-        sc = O.synthetic_scene(seed, 1, 2, 32, 48, 64)
+        sc = O.synthetic_scene(seed, 1, 2, nr, 48, 64)
         batches.append([t.pin_memory() for t in list(sc['inputs']) + [sc['target'], sc['u_strat'], sc['u_pdf']]])
-    feats = O.synthetic_scene(41, 1, 2, 32, 48, 64)['features'].to(cuda)
+    feats = O.synthetic_scene(41, 1, 2, nr, 48, 64)['features'].to(cuda)
+    return batches, feats
+
+
+def test_update_kernel_matches_host_adam_on_the_gpu(cuda):
+    """cn_adam_step (clip + warm-up schedule + Keras Adam with the step counter on the device) against
+    RenderTrainer.apply_gradients (torch ops, host scalars): the SAME gradient tensor per step on both sides, across
+    the warm-up boundary, launched eagerly and replayed from a CUDA graph, with and without the readouts."""
+    from clipnerf_b200._abi import EMB_PARAMS
+    from clipnerf_b200.trainer import RenderTrainer
+    for train_readouts in (False, True):
+        kw = dict(seed=2, warmup_steps=3, target_lr=1e-3, train_readouts=train_readouts)
+        host, eager, graphed = RenderTrainer(cuda, **kw), RenderTrainer(cuda, **kw), RenderTrainer(cuda, **kw)
+        gbuf = torch.zeros_like(graphed.params)
+        graphed.params.grad = gbuf
+        graphed._counter()
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            graphed.apply_gradients_on_device()
+        g = torch.Generator(device='cuda').manual_seed(0)
+        for i in range(8):
+            grad = torch.randn(host.params.shape, generator=g, device=cuda) * (3.0 if i == 2 else 0.1)   # beyond the clip
+            host.params.grad, eager.params.grad = grad.clone(), grad.clone()
+            gbuf.copy_(grad)
+            host.apply_gradients()
+            eager._counter()
+            eager.apply_gradients_on_device()
+            eager.iterations += 1
+            graph.replay()
+            graphed.iterations += 1
+            assert float(eager._t_dev) == float(graphed._t_dev) == host.iterations == i + 1
+            for other in (eager, graphed):
+                assert rel_err(other.params, host.params) < 1e-6, (i, rel_err(other.params, host.params))
+                assert rel_err(other.m, host.m) < 1e-6 and rel_err(other.v, host.v) < 1e-6
+            assert torch.equal(eager.params.grad, grad.clamp(-1, 1))          # the gradient is left clipped
+        init = RenderTrainer(cuda, **kw).params.detach()
+        same_readouts = torch.equal(graphed.params.detach()[:, EMB_PARAMS:], init[:, EMB_PARAMS:])
+        assert same_readouts == (not train_readouts)
+
+
+def test_graph_replayed_step_walks_the_eager_step(cuda):
+    """Per-step lockstep of the CUDA-graph training loop against the eager step, ON THE GPU: before every step of a
+    graph-driven trainer its state (parameters, Adam moments, step count) is cloned into a second trainer that takes
+    the eager step on the same batch; the two updates must agree, at every step, across the warm-up boundary, with two
+    graphs (one per upload buffer set) alternating and an eager step interleaved between replays.  No chaos can build
+    up: every comparison starts from identical state."""
+    from clipnerf_b200.trainer import RenderTrainer
+    batches, feats0 = _loop_batches(cuda)
+    kw = dict(seed=3, bias_std=0.02, warmup_steps=4, target_lr=1e-4)
+    G = RenderTrainer(cuda, **kw)
+    slots = [[t.to(cuda) for t in batches[0]], [t.to(cuda) for t in batches[1]]]
+    fg = [feats0.clone().requires_grad_(True) for _ in range(2)]
+    graphs = {}
+    worst = 0.0
+    for i in range(9):
+        k = i % 2
+        for d, h in zip(slots[k], batches[i % 3]):
+            d.copy_(h)
+        bt = slots[k]
+        E = RenderTrainer(cuda, params=G.params.detach().clone().requires_grad_(True), **{kk: v for kk, v in kw.items()
+                                                                                          if kk not in ('seed', 'bias_std')})
+        E.m.copy_(G.m), E.v.copy_(G.v)
+        E.iterations = G.iterations
+        before = G.params.detach().clone()
+        if i == 0 or i == 5:                      # first step of a trainer's life, and an eager step between replays
+            lg = G.train_step(bt[:5], fg[k], bt[5], bt[6], bt[7], NEAR, FAR)
+        else:
+            if k not in graphs:
+                torch.cuda.synchronize()
+                graphs[k] = G.capture(bt[:5], fg[k], bt[5], bt[6], bt[7], NEAR, FAR,
+                                      pool=next(iter(graphs.values())).graph.pool() if graphs else None)
+            lg = graphs[k]()
+        fe = feats0.clone().requires_grad_(True)
+        le = E.train_step(bt[:5], fe, bt[5], bt[6], bt[7], NEAR, FAR)
+        assert float(G._t_dev) == G.iterations == E.iterations == i + 1          # ONE counter, never stale
+        assert abs(float(lg) - float(le)) < 1e-5 * abs(float(le)), (i, float(lg), float(le))
+        du_g, du_e = (G.params.detach() - before).double(), (E.params.detach() - before).double()
+        # Adam's update is ~lr * sign(g) for the first steps: parameters whose gradient is ~0 may flip on the last
+        # bits of the fp32 atomics, everything else must agree -> relative L2 of the whole update
+        err = float((du_g - du_e).norm() / du_e.norm())
+        worst = max(worst, err)
+        assert err < 5e-2, (i, err)
+        assert rel_err(fg[k].grad, fe.grad) < 3e-3
+    print('graph step vs eager step from identical state: worst relative L2 of the update', worst)
+
+
+def test_graph_replayed_training_loop_matches_eager(cuda):
+    """fit_host_batches_graph (train step replayed from CUDA graphs, step counter / warm-up schedule / Adam bias
+    corrections on the device) against the eager loop.  With frozen parameters every replay must return the loss and
+    the map gradient of ITS batch.  With training the two loops cannot be bit-equal: the backward's fp32 atomics make
+    gradients differ in the last bits from run to run, Adam's first updates are ~lr * sign(g), and the reference's
+    un-stopped sampler path (model_v0.py:153-158) amplifies parameter noise.  So the NOISE FLOOR is measured here --
+    the eager loop against itself, three runs with identical seeds -- and the graph loop must lie within 2x of it
+    (measured on a B200, tools/diag_graph_loop.py: eager/eager loss spread 2e-3 ... 8e-3 relative after 7 steps of 32
+    rays, graph/eager 6e-4 ... 9e-3).  The arithmetic of the step itself is pinned without noise by the two tests above."""
+    from clipnerf_b200.trainer import RenderTrainer, fit_host_batches, fit_host_batches_graph
+    batches, feats = _loop_batches(cuda)
     seq = [batches[i % 3] for i in range(7)]
 
-    def both(lr):
-        res = []
-        for fit in (fit_host_batches, fit_host_batches_graph):
-            tr = RenderTrainer(cuda, seed=3, bias_std=0.02, warmup_steps=4, target_lr=lr)
-            f = feats.clone().requires_grad_(True)
-            losses = fit(tr, iter(seq), f, NEAR, FAR)
-            res.append((losses, tr.params.detach().clone(), tr.iterations, f.grad.clone()))
-        return res
+    def run(fit, lr):
+        tr = RenderTrainer(cuda, seed=3, bias_std=0.02, warmup_steps=4, target_lr=lr)
+        f = feats.clone().requires_grad_(True)
+        losses = fit(tr, iter(seq), f, NEAR, FAR)
+        assert tr.iterations == 7 and float(tr._t_dev) == 7.0
+        return losses, tr.params.detach().clone(), f.grad.clone()
+
     # frozen parameters (lr = 0): every replay must return the losses and the map gradient of ITS batch
-    (l0, p0, n0, g0), (l1, p1, n1, g1) = both(0.0)
-    assert n0 == n1 == 7 and torch.equal(p0, p1)
+    (l0, p0, g0), (l1, p1, g1) = run(fit_host_batches, 0.0), run(fit_host_batches_graph, 0.0)
+    assert torch.equal(p0, p1)
     print('lr=0: loss diff', max(abs(a - b_) for a, b_ in zip(l0, l1)), 'map grad diff', rel_err(g1, g0))
     assert max(abs(a - b_) for a, b_ in zip(l0, l1)) < 1e-5 * max(l0)
     assert rel_err(g1, g0) < 3e-3, rel_err(g1, g0)
-    # training: not bit-equal -- Adam's first updates are ~lr * sign(g), so the last-bit run-to-run noise of the
-    # gradients (fp32 atomics) moves parameters whose gradient is ~0 by up to lr per step; the optimizer arithmetic itself
-    # is compared exactly in tests/test_host.py::test_device_side_adam_matches_host_side
-    (l0, p0, n0, g0), (l1, p1, n1, g1) = both(1e-4)
-    dl = max(abs(a - b_) for a, b_ in zip(l0, l1))
-    print('lr=1e-4: loss diff', dl, 'param diff', rel_err(p1, p0))
-    assert n0 == n1 == 7
-    assert dl < 3e-3 * max(l0), dl
-    assert rel_err(p1, p0) < 5e-3, rel_err(p1, p0)
+    # training: graph loop within the measured eager-vs-eager floor
+    dist = lambda a, b_: max(abs(x - y) for x, y in zip(a[0], b_[0]))  # noqa: E731
+    eager = [run(fit_host_batches, 1e-4) for _ in range(3)]
+    floor = max(dist(eager[i], eager[j]) for i in range(3) for j in range(i + 1, 3))
+    graph = run(fit_host_batches_graph, 1e-4)
+    d_graph = min(dist(graph, e) for e in eager)
+    print(f'lr=1e-4: eager-vs-eager loss floor {floor:.3e} (3 runs), graph loop to the nearest eager run {d_graph:.3e}, '
+          f'param diff eager/eager {rel_err(eager[1][1], eager[0][1]):.3e} graph/eager {rel_err(graph[1], eager[0][1]):.3e}')
+    assert d_graph <= 2.0 * floor + 1e-6 * max(eager[0][0]), (d_graph, floor)
+    assert abs(graph[0][0] - eager[0][0][0]) < 1e-5 * eager[0][0][0]          # the first step has no history: equal

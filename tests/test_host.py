@@ -42,19 +42,34 @@ def test_x_column_order_is_a_permutation():
     assert cols[0] == 123 and cols[256] == 0 and cols[316] == 60 and cols[376] == 120
 
 
-def test_device_side_adam_matches_host_side():
-    """RenderTrainer.apply_gradients_on_device (step counter, warm-up schedule and bias corrections as device scalars:
-    the form a CUDA graph can replay) against apply_gradients, same gradients, across the warm-up boundary"""
-    import torch
+def test_host_adam_follows_keras_and_the_reference_optimizer_groups():
+    """RenderTrainer.apply_gradients (torch ops, host scalars) against a literal restatement of optimize()
+    (nerf_utils.py:8-12) + tf.keras Adam + WarmupScheduler (nerf_utils.py:288-300) in float64; readouts are in no
+    optimizer group of the reference (train_nerf.py:27-33) and keep their values unless train_readouts=True"""
+    import numpy as np
+    from clipnerf_b200._abi import EMB_PARAMS
     from clipnerf_b200.trainer import RenderTrainer
     dev = torch.device('cpu')
-    a, b = RenderTrainer(dev, seed=2, warmup_steps=3), RenderTrainer(dev, seed=2, warmup_steps=3)
-    g = torch.Generator().manual_seed(0)
-    for i in range(6):
-        grad = torch.randn(a.params.shape, generator=g) * (3.0 if i == 2 else 0.1)      # some entries beyond the clip
-        a.params.grad, b.params.grad = grad.clone(), grad.clone()
-        a.apply_gradients()
-        b.apply_gradients_on_device()
-        assert float(b._t_dev) == a.iterations == i + 1
-        err = float((a.params - b.params).abs().max() / a.params.abs().max())
-        assert err < 1e-6, (i, err)
+    for train_readouts in (False, True):
+        tr = RenderTrainer(dev, seed=2, warmup_steps=3, target_lr=1e-3, train_readouts=train_readouts)
+        p = tr.params.detach().double().numpy().copy()
+        m, v = np.zeros_like(p), np.zeros_like(p)
+        g = torch.Generator().manual_seed(0)
+        for t in range(1, 7):
+            grad = torch.randn(tr.params.shape, generator=g) * (3.0 if t == 3 else 0.1)      # some entries beyond the clip
+            tr.params.grad = grad.clone()
+            tr.apply_gradients()
+            gc = np.clip(grad.double().numpy(), -1.0, 1.0)
+            lr = O.warmup_lr(t, 1e-3, 3, 450000)
+            m = 0.9 * m + 0.1 * gc
+            v = 0.999 * v + 0.001 * gc * gc
+            upd = lr * np.sqrt(1 - 0.999 ** t) / (1 - 0.9 ** t) * m / (np.sqrt(v) + 1e-7)
+            if not train_readouts:
+                upd[:, EMB_PARAMS:] = 0.0
+            p = p - upd
+            assert tr.iterations == t
+            err = np.abs(tr.params.detach().double().numpy() - p).max() / np.abs(p).max()
+            assert err < 1e-6, (t, err)
+        if not train_readouts:
+            init = RenderTrainer(dev, seed=2).params.detach()
+            assert torch.equal(tr.params.detach()[:, EMB_PARAMS:], init[:, EMB_PARAMS:])

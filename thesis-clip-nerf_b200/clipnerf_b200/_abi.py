@@ -11,7 +11,7 @@ from ctypes import c_char_p, c_double, c_float, c_int32, c_int64, c_size_t, c_vo
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), 'lib', 'libclipnerf_b200.so')
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 TILE_ROWS = 128
 SLAB_BYTES = 16384
 ACT_TILE_BYTES = 32768
@@ -59,6 +59,8 @@ PROTOTYPES = {
     'cn_mlp_mean_bwd': [_P, c_int32, c_int32, c_int64, _P, _P],
     'cn_mlp_l0_dgrad': [_P, _P, c_int64, _P, c_float, _P],
     'cn_mlp_l0_wgrad': [_P, _P, c_int64, c_float, _P, _P],
+    'cn_adam_step': [_P, _P, _P, _P, c_int64, c_int64, c_int64, _P, c_double, c_double, c_double, c_float, c_float,
+                     c_double, c_double, c_double, _P],
     'cn_probe_umma': [_P, c_int32, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,
                       c_int32, c_int32, _P, _P],
     'cn_probe_tile_reduce': [_P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P],
@@ -94,7 +96,7 @@ class CnError(RuntimeError):
 KERNELS_PER_CALL = {name: 1 for name in PROTOTYPES}
 KERNELS_PER_CALL.update({'cn_abi_version': 0, 'cn_last_error': 0, 'cn_gather_ws_bytes': 0,
                          'cn_project_bin': 4, 'cn_project_gather_fwd': 5, 'cn_feature_grad': 2,
-                         'cn_project_gather_bwd_rays': 2, 'cn_quantize_render': 2})
+                         'cn_project_gather_bwd_rays': 2, 'cn_quantize_render': 2, 'cn_adam_step': 2})
 
 LAUNCHES = 0          # running count of kernel launches issued through the ABI
 TIMER = None          # optional callable(name) -> context manager, set by bench.py to time stages

@@ -345,6 +345,20 @@ def mlp_l0_wgrad(x_tiles, g0_tiles, grad, scale: float = 1.0):
     call('cn_mlp_l0_wgrad', _ptr(x_tiles), _ptr(g0_tiles), nt, float(scale), _ptr(grad), _stream())
 
 
+def adam_step(params, grad, m, v, n_update: int, step_counter, target_lr: float, warmup_steps: float,
+              scale_down_after: float, grad_scale: float = 1.0, clip: float = 1.0, beta1: float = 0.9,
+              beta2: float = 0.999, eps: float = 1e-7) -> None:
+    """clip + warm-up schedule + Keras Adam on flat [n_rows, row_stride] fp32 buffers (first ``n_update`` of every row);
+    ``step_counter``: 0-dim float64 CUDA tensor, incremented on the device"""
+    for t in (params, grad, m, v):
+        assert t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.shape == params.shape
+    assert step_counter.is_cuda and step_counter.dtype == torch.float64 and step_counter.numel() == 1
+    n_rows, stride = (params.shape[0], params.shape[1]) if params.dim() == 2 else (1, params.numel())
+    call('cn_adam_step', _ptr(params), _ptr(grad), _ptr(m), _ptr(v), n_rows, stride, int(n_update), _ptr(step_counter),
+         float(target_lr), float(warmup_steps), float(scale_down_after), float(grad_scale), float(clip), float(beta1),
+         float(beta2), float(eps), _stream())
+
+
 def probe_tile_reduce(map_: torch.Tensor, iters: int, mode: int, ctas_per_sm: int = 1) -> None:
     n_img, H, W, C = map_.shape
     assert C == 256 and map_.dtype == torch.float32

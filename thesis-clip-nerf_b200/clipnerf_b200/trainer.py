@@ -7,13 +7,15 @@ One process per GPU.  All trainable NeRF variables of both nets live in ONE flat
 shards is exactly one NCCL all-reduce per step (no collective is needed for rendering)."""
 from __future__ import annotations
 
+import queue
+import threading
 from typing import Optional
 
 import torch
 import torch.distributed as dist
 
 from . import params as P
-from ._abi import NET_PARAMS
+from ._abi import EMB_PARAMS, NET_PARAMS
 from . import render as _render
 from .render import render_rays
 
@@ -43,22 +45,40 @@ def allreduce_mean(grads, like, group=None):
 
 
 class RenderTrainer:
+    """Flat-buffer trainer of the two NeRF nets.
+
+    Which variables are updated.  The reference's ``MultiOptimizer`` (``src/train_nerf.py:27-33``) holds
+    ``coarse_embedding`` and ``fine_embedding`` (plus the image encoders); ``coarse_readout`` / ``fine_readout`` are in
+    no optimizer group, so ``apply_gradients`` never touches them.  ``train_readouts=False`` (default) reproduces that:
+    Adam runs over the first ``EMB_PARAMS`` entries of every net, the 516 readout parameters keep their values (their
+    gradient is still computed, as in the reference).  ``train_readouts=True`` updates all ``NET_PARAMS``.
+
+    ``params``: an existing ``[2, NET_PARAMS]`` leaf tensor to train in place (``MVVNeRFRenderer`` passes its own
+    parameter buffer); default: a fresh glorot initialisation."""
+
     def __init__(self, device, seed: int = 0, target_lr: float = 1e-4, warmup_steps: float = 10000.0,
-                 clip: float = 1.0, bias_std: float = 0.0, process_group=None):
-        g = torch.Generator().manual_seed(seed)
-        flat = torch.stack([P.glorot_init(g, bias_std), P.glorot_init(g, bias_std)])
-        self.params = flat.to(device).requires_grad_(True)          # [2, NET_PARAMS]: coarse, fine
-        self.m = torch.zeros_like(self.params)
-        self.v = torch.zeros_like(self.params)
+                 clip: float = 1.0, bias_std: float = 0.0, process_group=None, params: Optional[torch.Tensor] = None,
+                 train_readouts: bool = False, scale_down_after: float = 450000.0):
+        if params is None:
+            g = torch.Generator().manual_seed(seed)
+            flat = torch.stack([P.glorot_init(g, bias_std), P.glorot_init(g, bias_std)])
+            self.params = flat.to(device).requires_grad_(True)          # [2, NET_PARAMS]: coarse, fine
+        else:
+            assert tuple(params.shape) == (2, NET_PARAMS) and params.is_contiguous() and params.dtype == torch.float32
+            self.params = params
+        self.m = torch.zeros_like(self.params, requires_grad=False)
+        self.v = torch.zeros_like(self.params, requires_grad=False)
         self.iterations = 0
-        self.target_lr, self.warmup_steps, self.clip = target_lr, warmup_steps, clip
+        self.target_lr, self.warmup_steps, self.clip = target_lr, max(1.0, float(warmup_steps)), clip
+        self.scale_down_after = float(scale_down_after)
         self.beta1, self.beta2, self.eps = 0.9, 0.999, 1e-7           # tf.keras.optimizers.Adam defaults
+        self.n_update = NET_PARAMS if train_readouts else EMB_PARAMS
         self.group = process_group
         # True: start the all-reduce inside the backward, under the feature-map sweep (render.GRAD_SYNC).  Measured on
         # 8 B200s it is no faster than the plain all-reduce behind the backward (7.40 vs 7.32 ms / step; 7.31 vs 7.33 on 2):
         # the 1.98 MB collective costs ~50 us over NVSwitch and its kernel competes with the sweep for SMs -- off by default
         self.overlap_allreduce = False
-        self._t_dev = None          # device-side step counter of apply_gradients_on_device
+        self._t_dev = None          # device-side step counter (float64) of apply_gradients_on_device
         self._synced = False
         self.world = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
 
@@ -116,37 +136,39 @@ class RenderTrainer:
 
     @torch.no_grad()
     def apply_gradients(self):
-        """per-element clip to [-clip, clip] (nerf_utils.py:9-11) then Keras-style Adam."""
+        """per-element clip to [-clip, clip] (nerf_utils.py:9-11) then Keras-style Adam, with torch ops and HOST
+        scalars: the device-independent statement of the update (CPU / gloo tests, and the reference the one-kernel
+        form ``apply_gradients_on_device`` is tested against).  Keeps the device-side counter in step."""
         g = self.params.grad
         if self.clip > 0:
             g.clamp_(-self.clip, self.clip)
         self.iterations += 1
         t = self.iterations
-        lr = warmup_lr(t, self.target_lr, self.warmup_steps)
+        lr = warmup_lr(t, self.target_lr, self.warmup_steps, self.scale_down_after)
         lr_t = lr * (1.0 - self.beta2 ** t) ** 0.5 / (1.0 - self.beta1 ** t)
-        self.m.mul_(self.beta1).add_(g, alpha=1.0 - self.beta1)
-        self.v.mul_(self.beta2).addcmul_(g, g, value=1.0 - self.beta2)
-        self.params.addcdiv_(self.m, self.v.sqrt().add_(self.eps), value=-lr_t)
+        n = self.n_update
+        p, m, v, g = self.params[:, :n], self.m[:, :n], self.v[:, :n], g[:, :n]
+        m.mul_(self.beta1).add_(g, alpha=1.0 - self.beta1)
+        v.mul_(self.beta2).addcmul_(g, g, value=1.0 - self.beta2)
+        p.sub_(float(torch.tensor(lr_t, dtype=torch.float32)) * m / v.sqrt().add_(self.eps))
+        if self._t_dev is not None:
+            self._t_dev.fill_(float(self.iterations))
 
-    @torch.no_grad()
-    def apply_gradients_on_device(self):
-        """``apply_gradients`` with the step counter, the warm-up schedule and the bias corrections evaluated on the
-        device (float64 scalars), so that the update can be recorded into a CUDA graph and replayed."""
+    def _counter(self):
         if self._t_dev is None:
             self._t_dev = torch.zeros((), dtype=torch.float64, device=self.params.device)
             self._t_dev.fill_(float(self.iterations))
-        g = self.params.grad
-        if self.clip > 0:
-            g.clamp_(-self.clip, self.clip)
-        self._t_dev += 1.0
-        t = self._t_dev
-        warm = max(1.0, float(self.warmup_steps))
-        lr = torch.where(t <= warm, t / warm * self.target_lr,
-                         torch.where(t <= 450000.0, torch.full_like(t, self.target_lr), torch.full_like(t, 0.1 * self.target_lr)))
-        lr_t = (lr * torch.sqrt(1.0 - self.beta2 ** t) / (1.0 - self.beta1 ** t)).to(torch.float32)
-        self.m.mul_(self.beta1).add_(g, alpha=1.0 - self.beta1)
-        self.v.mul_(self.beta2).addcmul_(g, g, value=1.0 - self.beta2)
-        self.params.sub_(lr_t * self.m / self.v.sqrt().add_(self.eps))
+        return self._t_dev
+
+    @torch.no_grad()
+    def apply_gradients_on_device(self):
+        """the same update as ONE kernel (``cn_adam_step``) with the step counter, the warm-up schedule and the bias
+        corrections evaluated on the device: what the training step launches, eagerly and recorded into a CUDA graph.
+        The caller keeps ``self.iterations`` (host mirror of the counter) in step."""
+        from . import ops
+        ops.adam_step(self.params.data, self.params.grad, self.m, self.v, self.n_update, self._counter(),
+                      self.target_lr, self.warmup_steps, self.scale_down_after, 1.0, self.clip, self.beta1, self.beta2,
+                      self.eps)
 
     def capture(self, inputs, features, target, u_strat, u_pdf, near, far, pool=None, warmup: int = 0):
         """One ``train_step`` on FIXED device buffers recorded into a CUDA graph: ~45 kernel launches of this library,
@@ -155,9 +177,7 @@ class RenderTrainer:
         replay).  ``features.grad`` is written by every replay (memory owned by the graph).  The ``warmup`` eager
         steps DO update the parameters."""
         features.grad = None
-        if self._t_dev is None:
-            self._t_dev = torch.zeros((), dtype=torch.float64, device=self.params.device)
-        self._t_dev.fill_(float(self.iterations))      # (outside the graph) continue from the eager steps so far
+        self._counter().fill_(float(self.iterations))  # (outside the graph) continue from the eager steps so far
 
         def step():
             features.grad = None
@@ -170,16 +190,20 @@ class RenderTrainer:
         with torch.cuda.stream(side):
             for _ in range(warmup):
                 step()
+                self.iterations += 1
         torch.cuda.current_stream().wait_stream(side)
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph, pool=pool):
             loss = step()
-        self.iterations += warmup              # the capture pass itself executes nothing
         d_features = features.grad             # this graph's map gradient (graph-owned memory)
+        t_dev = self._t_dev
 
         def replay():
+            # ONE counter: the device-side step count is refilled from the host's before every replay (a 5 us fill on
+            # the stream, no synchronisation), so eager steps taken between replays cannot leave it stale
+            t_dev.fill_(float(self.iterations))
             graph.replay()
-            self.iterations += 1               # host mirror of the device-side counter
+            self.iterations += 1
             features.grad = d_features         # (another graph of the same pool may have been replayed in between)
             return loss
         replay.graph = graph
@@ -188,8 +212,72 @@ class RenderTrainer:
     def train_step(self, inputs, features, target, u_strat, u_pdf, near, far, max_rays: Optional[int] = None):
         loss, _ = self.loss_and_backward(inputs, features, target, u_strat, u_pdf, near, far, max_rays)
         self.allreduce_gradients()
-        self.apply_gradients()
+        if self.params.is_cuda:
+            self._counter().fill_(float(self.iterations))
+            self.apply_gradients_on_device()       # the same kernel the graph replays: one update expression
+            self.iterations += 1
+        else:
+            self.apply_gradients()
         return loss
+
+
+class HostBatch(list):
+    """a host batch (list of pinned tensors) whose buffers are recycled by its producer: ``uploaded`` is set by the
+    ``DevicePrefetcher`` once the host->device copies are enqueued, ``copied`` is the CUDA event behind them"""
+
+    def __init__(self, tensors):
+        super().__init__(tensors)
+        self.uploaded = threading.Event()
+        self.copied = None
+
+
+class PinnedBatchQueue:
+    """``sequence[i]`` for ``i in indices`` -> pinned host batches, produced by ONE background thread a few batches
+    ahead of the consumer -- the role of Keras' ``OrderedEnqueuer`` (workers = 1) under ``fit``
+    (``src/train_nerf.py:52`` -> ``MVNeRFDataGenerator.__getitem__``).  One thread keeps the order of the numpy global
+    RNG draws of the generator (``bbox_biased_sample``, ``np.random.choice``) deterministic.  ``flatten(item)`` maps
+    the generator's item to a flat list of arrays; a ring of pinned buffer sets is recycled (a set is rewritten only
+    after its upload has completed)."""
+
+    def __init__(self, sequence, indices, flatten, depth: int = 3):
+        self.sequence, self.indices, self.flatten = sequence, list(indices), flatten
+        self.q = queue.Queue(maxsize=depth)
+        self.ring = [None] * (depth + 3)
+        self.error = None
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
+
+    def _run(self):
+        try:
+            for n, i in enumerate(self.indices):
+                arrays = [torch.as_tensor(a) for a in self.flatten(self.sequence[i])]
+                arrays = [a.to(torch.float32) if a.dtype == torch.float64 else a for a in arrays]
+                k = n % len(self.ring)
+                old = self.ring[k]
+                if old is not None:
+                    old.uploaded.wait()
+                    if old.copied is not None:
+                        old.copied.synchronize()
+                if old is None or any(o.shape != a.shape or o.dtype != a.dtype for o, a in zip(old, arrays)):
+                    bufs = [torch.empty(a.shape, dtype=a.dtype).pin_memory() for a in arrays]
+                else:
+                    bufs = list(old)
+                for b_, a in zip(bufs, arrays):
+                    b_.copy_(a)
+                self.ring[k] = HostBatch(bufs)
+                self.q.put(self.ring[k])
+        except BaseException as e:          # surfaced in the consumer
+            self.error = e
+        self.q.put(None)
+
+    def __iter__(self):
+        while True:
+            item = self.q.get()
+            if item is None:
+                if self.error is not None:
+                    raise self.error
+                return
+            yield item
 
 
 class DevicePrefetcher:
@@ -224,12 +312,15 @@ class DevicePrefetcher:
         with torch.cuda.stream(self.copy_stream):
             if self.free[k] is not None:
                 self.copy_stream.wait_event(self.free[k])
-            if self.slots[k] is None:
+            if self.slots[k] is None or any(d.shape != h.shape for d, h in zip(self.slots[k], host)):
                 self.slots[k] = [torch.empty_like(t, device=self.device) for t in host]
             for d, h in zip(self.slots[k], host):
                 d.copy_(h, non_blocking=True)
             ready = torch.cuda.Event()
             ready.record(self.copy_stream)
+        if isinstance(host, HostBatch):
+            host.copied = ready
+            host.uploaded.set()
         self.next = (k, ready)
 
     def __iter__(self):
@@ -245,75 +336,118 @@ class DevicePrefetcher:
             self.free[k] = torch.cuda.Event()
         batch = self.slots[k]
         self._upload()                          # next batch goes out while this one is consumed
-        return batch, self.free[k]
+        return k, batch, self.free[k]
 
 
-def fit_host_batches_graph(trainer: RenderTrainer, batches, features, near, far):
+class _LossReader:
+    """losses of the steps, copied to pinned host memory asynchronously and read two steps late (the launch queue
+    holds up to two steps, so host jitter of a whole step does not idle the device)"""
+
+    def __init__(self, device):
+        self.cur = torch.cuda.current_stream(device)
+        self.ring = torch.empty(4, dtype=torch.float32, pin_memory=True)     # pinned once: no host allocation in the loop
+        self.k, self.pending, self.losses = 0, [], []
+
+    def push(self, loss):
+        host_loss = self.ring[self.k % 4]
+        self.k += 1
+        host_loss.copy_(loss, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(self.cur)
+        self.pending.append((host_loss, ev))
+        if len(self.pending) > 2:
+            h, e = self.pending.pop(0)
+            e.synchronize()
+            self.losses.append(float(h))
+
+    def finish(self):
+        for h, e in self.pending:
+            e.synchronize()
+            self.losses.append(float(h))
+        self.pending = []
+        return self.losses
+
+
+def _step_operands(trainer, k, batch, features, draws, state):
+    """(inputs5, features tensor, target, u_strat, u_pdf) of device buffer set ``k``.  ``features``: a tensor, or a
+    callable ``images [b,nv,H,W,3] -> [b,nv,H,W,256]`` (the upstream encoders; its result is copied into a per-set
+    buffer when it does not keep its address, so that a recorded graph finds it).  ``draws``: None (the batch carries
+    u_strat / u_pdf) or a torch.Generator the stratified / inverse-CDF draws are taken from on the device."""
+    inputs, target = batch[:5], batch[5]
+    if draws is None:
+        u_s, u_p = batch[6], batch[7]
+    else:
+        us = state.setdefault(('u', k), None)
+        shape = tuple(inputs[0].shape[:2]) + (64,)
+        if us is None or tuple(us[0].shape) != shape:
+            us = state[('u', k)] = [torch.empty(shape, device=inputs[0].device) for _ in range(2)]
+        for u in us:
+            torch.rand(shape, generator=draws, out=u)
+        u_s, u_p = us
+    if callable(features):
+        f = features(inputs[2])
+        buf = state.get(('f', k))
+        if buf is None or buf.shape != f.shape:
+            buf = state[('f', k)] = f.detach()          # shares f's storage: an encoder that keeps its output buffer costs no copy
+            buf.requires_grad_(f.requires_grad)
+        elif f.data_ptr() != buf.data_ptr():
+            with torch.no_grad():
+                buf.copy_(f)
+        state[('f_out', k)] = f
+        feats = buf
+    else:
+        feats = features
+    return inputs, feats, target, u_s, u_p
+
+
+def fit_host_batches_graph(trainer: RenderTrainer, batches, features, near, far, draws=None, after_step=None):
     """``fit_host_batches`` with the training step replayed from CUDA graphs (one per device buffer set of the
     prefetcher, sharing one memory pool): per step the host enqueues the uploads, one graph launch and the loss
     read-back.  Fixed batch shapes; on more than one rank the NCCL all-reduce is part of the graphs (drop
-    ``trainer._graphs`` before destroying the process group)."""
+    ``trainer._graphs`` before destroying the process group).  ``features`` / ``draws``: see ``_step_operands``;
+    ``after_step(k, features_tensor, encoder_output)`` runs after every step (e.g. the encoders' own backward from
+    ``features_tensor.grad``)."""
     dev = trainer.params.device
     cur = torch.cuda.current_stream(dev)
-    losses, pending = [], []
-    ring = torch.empty(4, dtype=torch.float32, pin_memory=True)
+    reader = _LossReader(dev)
     graphs = trainer.__dict__.setdefault('_graphs', {})
     slots = trainer.__dict__.setdefault('_graph_slots', [None, None])
-    k = 0
-    for batch, done in DevicePrefetcher(batches, dev, slots=slots):
-        key = tuple(t.data_ptr() for t in batch) + (features.data_ptr(),)
+    state = trainer.__dict__.setdefault('_graph_state', {})
+    for k, batch, done in DevicePrefetcher(batches, dev, slots=slots):
+        inputs, feats, target, u_s, u_p = _step_operands(trainer, k, batch, features, draws, state)
+        key = tuple(t.data_ptr() for t in batch) + (feats.data_ptr(), u_s.data_ptr(), u_p.data_ptr())
         if trainer.iterations == 0:
             # the first step of a trainer's life runs eagerly (lazy initialisations must not happen under capture)
-            loss = trainer.train_step(batch[:5], features, batch[5], batch[6], batch[7], near, far)
+            loss = trainer.train_step(inputs, feats, target, u_s, u_p, near, far)
         else:
             if key not in graphs:
                 pool = next(iter(graphs.values())).graph.pool() if graphs else None
                 torch.cuda.synchronize(dev)
-                graphs[key] = trainer.capture(batch[:5], features, batch[5], batch[6], batch[7], near, far, pool=pool)
+                graphs[key] = trainer.capture(inputs, feats, target, u_s, u_p, near, far, pool=pool)
                 torch.cuda.synchronize(dev)
             loss = graphs[key]()
+        if after_step is not None:
+            after_step(k, feats, state.get(('f_out', k)))
         done.record(cur)
-        host_loss = ring[k % 4]
-        k += 1
-        host_loss.copy_(loss, non_blocking=True)
-        ev = torch.cuda.Event()
-        ev.record(cur)
-        pending.append((host_loss, ev))
-        if len(pending) > 2:
-            h, e = pending.pop(0)
-            e.synchronize()
-            losses.append(float(h))
-    for h, e in pending:
-        e.synchronize()
-        losses.append(float(h))
-    return losses
+        reader.push(loss)
+    return reader.finish()
 
 
-def fit_host_batches(trainer: RenderTrainer, batches, features, near, far, max_rays: Optional[int] = None):
-    """Training loop over HOST batches ``(ray_o, ray_d, images, K, E^-1, target, u_strat, u_pdf)`` in pinned
-    memory: prefetched uploads, one ``train_step`` per batch, the loss of every step copied back to the host
-    asynchronously (read two steps late: the launch queue holds up to two steps, so host jitter of a whole step does
-    not idle the device).  Returns the losses."""
+def fit_host_batches(trainer: RenderTrainer, batches, features, near, far, max_rays: Optional[int] = None, draws=None,
+                     after_step=None):
+    """Training loop over HOST batches ``(ray_o, ray_d, images, K, E^-1, target[, u_strat, u_pdf])`` in pinned
+    memory: prefetched uploads, one eager ``train_step`` per batch, the loss of every step copied back to the host
+    asynchronously.  Returns the losses."""
     dev = trainer.params.device
     cur = torch.cuda.current_stream(dev)
-    losses, pending = [], []
-    ring = torch.empty(4, dtype=torch.float32, pin_memory=True)     # pinned once: no host allocation inside the loop
-    k = 0
-    for batch, done in DevicePrefetcher(batches, dev):
-        features.grad = None
-        loss = trainer.train_step(batch[:5], features, batch[5], batch[6], batch[7], near, far, max_rays)
+    reader = _LossReader(dev)
+    state = {}
+    for k, batch, done in DevicePrefetcher(batches, dev):
+        inputs, feats, target, u_s, u_p = _step_operands(trainer, k, batch, features, draws, state)
+        feats.grad = None
+        loss = trainer.train_step(inputs, feats, target, u_s, u_p, near, far, max_rays)
+        if after_step is not None:
+            after_step(k, feats, state.get(('f_out', k)))
         done.record(cur)
-        host_loss = ring[k % 4]
-        k += 1
-        host_loss.copy_(loss, non_blocking=True)
-        ev = torch.cuda.Event()
-        ev.record(cur)
-        pending.append((host_loss, ev))
-        if len(pending) > 2:
-            h, e = pending.pop(0)
-            e.synchronize()
-            losses.append(float(h))
-    for h, e in pending:
-        e.synchronize()
-        losses.append(float(h))
-    return losses
+        reader.push(loss)
+    return reader.finish()

@@ -24,6 +24,18 @@ int check_launch(const char *what) {
   return 0;
 }
 
+int num_sms() {
+  static int cached[64];                 // benign race: every writer stores the same value
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
 }  // namespace cn
 
 extern "C" int cn_abi_version(void) { return CN_ABI_VERSION; }

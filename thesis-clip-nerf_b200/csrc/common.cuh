@@ -23,7 +23,9 @@ int check_scene(const CnScene *s, const char *who);
     }                                \
   } while (0)
 
-constexpr int kNumSMs = 148;
+// SM count of the current device (cudaDevAttrMultiProcessorCount, queried once per device): every persistent
+// grid is sized from it, so a MIG slice or another SKU gets its own grid instead of a silent 148
+int num_sms();
 
 // ---------------------------------------------------------------- tile addressing
 // byte offset of element (row, col) inside a bf16 tile image made of [128 x 64] slabs

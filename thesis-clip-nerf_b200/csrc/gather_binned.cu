@@ -24,6 +24,8 @@
 //                        tile is added to d_features with cp.reduce.async.bulk.add.f32
 //   project_dz_kernel    one CTA per dX tile: posenc'(p), image and pixel-coordinate gradients
 //                        chained through K and E^-1 to d/dz (quirk Q4: no stop_gradient)
+#include <cstdlib>
+
 #include "common.cuh"
 #include "project.cuh"
 
@@ -41,11 +43,16 @@ constexpr int kChunk = CN_CHUNK;                 // max rows per work item
 
 // header ints of the workspace
 enum { kHdrItems = 0, kHdrCurFwd = 1, kHdrCurZg = 2, kHdrCurSc = 3, kHdrHeavyN = 4 /* 2 ints */, kHdrTicket = 6, kHdrInts = 64 };
-constexpr int kHeavyCap = 65536;              // deferred (texel, chunk) entries of the feature-gradient sweep
+// Deferred (texel, chunk) entries of the feature-gradient sweep.  A deferred texel has n > kHeavyRows row visits and
+// ceil(n / kHeavyChunk) <= n (1/256 + 1/193) entries, and every row is visited by 4 texels, so all sets of one sweep
+// (<= 4, each at most as large as the largest) need at most 4 * 4 * rows_max * 0.0091 < rows_max / 4 entries: the list
+// is sized from the row count of its workspace and cn_feature_grad takes the list of the LARGEST set -- it cannot fill
+// up.  (The sweep still handles a full list -- see feature_grad_kernel -- which tests reach through CN_DEBUG_HEAVY_CAP.)
+static int heavy_cap_for(int64_t rows) { return (int)(rows / 4 + 1024); }
 
 struct Ws {
   int64_t rows;
-  int tiles_x, tiles_y, n_bins, n_keys, n_blk, max_items;
+  int tiles_x, tiles_y, n_bins, n_keys, n_blk, max_items, heavy_cap;
   int *hdr;        // [kHdrInts]
   int *count;      // [n_keys]   histogram, then (in place) start offset of every key
   int2 *blk_sum;   // [n_blk]    (rows, items) per scan block
@@ -55,7 +62,7 @@ struct Ws {
   int2 *keyrank;   // [rows]     (key, rank inside key)
   int4 *rec_s;     // [rows]     records sorted by key
   float2 *gpix;    // [rows]     feature part of d loss / d (alpha_x, alpha_y)
-  int2 *heavy;     // [kHeavyCap] (texel, first row) chunks deferred by feature_grad_kernel
+  int2 *heavy;     // [heavy_cap] (texel, first row) chunks deferred by feature_grad_kernel
   size_t total;
 };
 
@@ -70,6 +77,7 @@ static Ws ws_layout(int b, int nv, int H, int W, int64_t rows, void *base) {
   w.n_keys = w.n_bins * kCells;
   w.n_blk = (w.n_bins + 255) / 256;
   w.max_items = (int)(w.n_bins + rows / kChunk + 1);
+  w.heavy_cap = heavy_cap_for(rows);
   uint8_t *p = (uint8_t *)base;
   size_t o = 0;
   auto take = [&](size_t bytes) {
@@ -86,7 +94,7 @@ static Ws ws_layout(int b, int nv, int H, int W, int64_t rows, void *base) {
   w.keyrank = (int2 *)take((size_t)rows * 8);
   w.rec_s = (int4 *)take((size_t)rows * 16);
   w.gpix = (float2 *)take((size_t)rows * 8);
-  w.heavy = (int2 *)take((size_t)kHeavyCap * 8);
+  w.heavy = (int2 *)take((size_t)w.heavy_cap * 8);
   w.total = o;
   return w;
 }
@@ -812,7 +820,11 @@ feature_grad_kernel(CnScene sc, GradArgs a, float *__restrict__ d_features) {
               texel_store(d_features, texel, z8, 0);
             }
           } else {
-            rf0 = fetch_rows(a, st0, len0, off0, n0, 0);  // list full: do it here after all
+            // list full (unreachable with the list sized by heavy_cap_for; kept correct): the slots this texel
+            // reserved below the cap are published as skip entries -- heavy_n has already moved past them and the
+            // second kernel walks [0, min(heavy_n, cap)) -- and the texel is summed here after all
+            for (int c = slot + (int)l; c < min(slot + n_chunks, a.heavy_cap); c += 32) a.heavy_list[c] = make_int2(-1, 0);
+            rf0 = fetch_rows(a, st0, len0, off0, n0, 0);
           }
         }
         if (!deferred) {
@@ -843,6 +855,7 @@ feature_grad_heavy_kernel(CnScene sc, GradArgs a, float *__restrict__ d_features
     e = __shfl_sync(0xffffffffu, e, 0);
     if (e >= n_entries) break;
     const int2 ent = a.heavy_list[e];
+    if (ent.x < 0) continue;                       // skip entry of a texel that did not fit (summed by the main sweep)
     const int64_t texel = ent.x;
     const int X = (int)(texel % sc.W);
     const int Y = (int)((texel / sc.W) % sc.H);
@@ -1024,7 +1037,7 @@ static int run_tile_rows(const CnScene *scene, const Ws &g, int cursor_index, ui
     set_error("tile_rows: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     return (int)e;
   }
-  tile_rows_kernel<kBackward><<<kNumSMs, rows_threads<kBackward>(), kRowsSmem, st>>>(*scene, g, g.hdr + cursor_index, x_tiles);
+  tile_rows_kernel<kBackward><<<num_sms(), rows_threads<kBackward>(), kRowsSmem, st>>>(*scene, g, g.hdr + cursor_index, x_tiles);
   return check_launch("tile_rows");
 }
 
@@ -1049,16 +1062,24 @@ static int run_feature_grad(const CnScene *scene, int n_sets, const Ws *const *w
   a.n_units = scene->b * scene->nv * a.ttx * a.tty * (kT / kUnitRows);
   a.accumulate = accumulate;
   a.cursor = w0->hdr + kHdrCurSc;
+  // the deferred-chunk list of the largest set holds the chunks of every set (see heavy_cap_for)
+  const Ws *wl = w0;
+  for (int i = 1; i < n_sets; ++i)
+    if (ws[i]->rows > wl->rows) wl = ws[i];
   a.heavy_n = w0->hdr + kHdrHeavyN;
-  a.heavy_list = w0->heavy;
-  a.heavy_cap = kHeavyCap;
+  a.heavy_list = wl->heavy;
+  a.heavy_cap = wl->heavy_cap;
+  if (const char *dbg = getenv("CN_DEBUG_HEAVY_CAP")) {   // tests only: force the list-full path
+    const int cap = atoi(dbg);
+    if (cap >= 0 && cap < a.heavy_cap) a.heavy_cap = cap;
+  }
   cudaError_t ce = cudaMemsetAsync(w0->hdr + kHdrCurSc, 0, 3 * sizeof(int), st);  // cursor + deferred entries + their cursor
   if (ce != cudaSuccess) {
     set_error("cn_feature_grad: cudaMemsetAsync: %s", cudaGetErrorString(ce));
     return (int)ce;
   }
-  feature_grad_kernel<<<kFgCtasPerSm * kNumSMs, kFgThreads, 0, st>>>(*scene, a, d_features);
-  feature_grad_heavy_kernel<<<kFgCtasPerSm * kNumSMs, kFgThreads, 0, st>>>(*scene, a, d_features);
+  feature_grad_kernel<<<kFgCtasPerSm * num_sms(), kFgThreads, 0, st>>>(*scene, a, d_features);
+  feature_grad_heavy_kernel<<<kFgCtasPerSm * num_sms(), kFgThreads, 0, st>>>(*scene, a, d_features);
   return check_launch("cn_feature_grad");
 }
 

@@ -577,7 +577,7 @@ extern "C" int cn_mlp_block_bwd(const void *packed, int32_t blk, const void *act
     return (int)e;
   }
   const uint8_t *pk = (const uint8_t *)packed;
-  const unsigned grid = (unsigned)(n_tiles < kNumSMs ? n_tiles : kNumSMs);
+  const unsigned grid = (unsigned)(n_tiles < num_sms() ? n_tiles : num_sms());
   mlp_block_bwd_kernel<<<grid, kBwdThreads, kBwdSmemBytes, (cudaStream_t)stream>>>(
       pk + pack_bwd_block(blk, 0), pk + pack_bwd_block(blk, 1),
       reinterpret_cast<const float *>(pk + kPackTables) + (blk < 3 ? kTabFeature : kTabFusion) + (2 * (blk % 3) + 1) * 128,
@@ -602,7 +602,7 @@ extern "C" int cn_mlp_readout_bwd(const float *params, const float *d_y, const v
     set_error("cn_mlp_readout_bwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     return (int)e;
   }
-  const unsigned grid = (unsigned)(n_tiles < 2 * kNumSMs ? n_tiles : 2 * kNumSMs);
+  const unsigned grid = (unsigned)(n_tiles < 2 * num_sms() ? n_tiles : 2 * num_sms());
   readout_bwd_kernel<<<grid, kRoThreads, kRoSmemBytes, (cudaStream_t)stream>>>(
       params + kParamWr, d_y, (const uint8_t *)acts + (int64_t)act_index * CN_ACT_TILE_BYTES,
       (int64_t)act_stride_tiles * CN_ACT_TILE_BYTES, n_tiles, (uint8_t *)g_tiles, grad + kParamWr, grad + kParamBr);
@@ -616,7 +616,7 @@ extern "C" int cn_mlp_mean_bwd(const void *gm_tiles, int32_t b, int32_t nv, int6
   CN_REQUIRE(b > 0 && nv > 0 && tiles_per_view >= 0, "cn_mlp_mean_bwd: b=%d nv=%d tiles_per_view=%lld", b, nv,
              (long long)tiles_per_view);
   if (tiles_per_view == 0) return 0;
-  mean_bwd_kernel<<<kNumSMs * 8, 256, 0, (cudaStream_t)stream>>>((const uint4 *)gm_tiles, b, nv, tiles_per_view,
+  mean_bwd_kernel<<<num_sms() * 8, 256, 0, (cudaStream_t)stream>>>((const uint4 *)gm_tiles, b, nv, tiles_per_view,
                                                                  (uint4 *)gh3_tiles);
   return check_launch("cn_mlp_mean_bwd");
 }

@@ -540,7 +540,7 @@ static int launch_fwd(bool fusion, const void *packed, const void *in_tiles, int
                       int64_t tiles_per_view, void *out_tiles, float *rgbs, void *acts, float *taps,
                       cudaStream_t st) {
   const int64_t n_pairs = (n_tiles + 1) / 2;
-  const unsigned grid = (unsigned)(n_pairs < kNumSMs ? n_pairs : kNumSMs);
+  const unsigned grid = (unsigned)(n_pairs < num_sms() ? n_pairs : num_sms());
   cudaError_t e;
   if (fusion) {
     constexpr uint32_t bytes = FwdSmem<true>::kBytes;

@@ -305,7 +305,7 @@ extern "C" int cn_mlp_l0_dgrad(const void *packed, const void *g0_tiles, int64_t
     set_error("cn_mlp_l0_dgrad: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     return (int)e;
   }
-  const unsigned grid = (unsigned)(n_tiles < kNumSMs ? n_tiles : kNumSMs);
+  const unsigned grid = (unsigned)(n_tiles < num_sms() ? n_tiles : num_sms());
   mlp_l0_dgrad_kernel<<<grid, kDgThreads, kDgSmemBytes, (cudaStream_t)stream>>>(
       (const uint8_t *)packed + kPackBwdW0, (const uint8_t *)g0_tiles, n_tiles, (uint8_t *)dx_tiles, scale);
   return check_launch("cn_mlp_l0_dgrad");
@@ -325,7 +325,7 @@ extern "C" int cn_mlp_l0_wgrad(const void *x_tiles, const void *g0_tiles, int64_
     set_error("cn_mlp_l0_wgrad: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     return (int)e;
   }
-  const unsigned grid = (unsigned)(n_tiles < kNumSMs ? n_tiles : kNumSMs);
+  const unsigned grid = (unsigned)(n_tiles < num_sms() ? n_tiles : num_sms());
   mlp_l0_wgrad_kernel<<<grid, kWgThreads, kWgSmemBytes, (cudaStream_t)stream>>>(
       (const uint8_t *)x_tiles, (const uint8_t *)g0_tiles, n_tiles, grad + kParamW0, grad + kParamB0, scale);
   return check_launch("cn_mlp_l0_wgrad");

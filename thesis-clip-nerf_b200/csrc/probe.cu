@@ -122,7 +122,7 @@ extern "C" int cn_probe_tile_reduce(float *map, int32_t n_img, int32_t H, int32_
     set_error("cn_probe_tile_reduce: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     return (int)e;
   }
-  probe_tile_reduce_kernel<<<kNumSMs * ctas_per_sm, 256, smem, (cudaStream_t)stream>>>(map, n_img, H, W, iters, mode);
+  probe_tile_reduce_kernel<<<num_sms() * ctas_per_sm, 256, smem, (cudaStream_t)stream>>>(map, n_img, H, W, iters, mode);
   return check_launch("cn_probe_tile_reduce");
 }
 

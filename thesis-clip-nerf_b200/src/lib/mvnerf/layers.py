@@ -21,11 +21,28 @@ def _glorot_(t):
 
 
 class _FlatModule(torch.nn.Module):
+    """``flat``: the module's variables as ONE fp32 vector.  Stand-alone it is the module's own ``nn.Parameter``;
+    inside ``MVVNeRFRenderer`` it is a view into the model's ``[2, NET_PARAMS]`` parameter buffer (``share_storage``),
+    so that the whole model trains through one flat buffer / one all-reduce."""
     _table = ()
 
     def __init__(self, numel):
         super().__init__()
         self.flat = torch.nn.Parameter(torch.zeros(numel))
+
+    def share_storage(self, owner, attr, row, start):
+        """give up the own parameter: ``flat`` becomes ``getattr(owner, attr)[row, start:start + numel]`` (resolved at
+        every access, so ``owner.to(device)`` keeps working); the current values are NOT copied"""
+        import weakref
+        n = self._parameters['flat'].numel()
+        del self._parameters['flat']
+        self.__dict__['_view_of'] = (weakref.ref(owner), attr, row, start, n)
+
+    def __getattr__(self, name):
+        if name == 'flat' and '_view_of' in self.__dict__:
+            owner, attr, row, start, n = self.__dict__['_view_of']
+            return getattr(owner(), attr)[row, start:start + n]
+        return super().__getattr__(name)
 
     def variables(self):
         """{keras variable name: view}"""

@@ -14,6 +14,15 @@ What is and is not here
 * Keras plumbing (``compile`` / ``fit`` / ``summary`` / ``store`` / ``load``) is re-stated minimally
   on torch; checkpoints are one ``torch.save`` file per reference checkpoint group
   (``<path>_<group>.pt`` instead of the TF ``.index`` / ``.data`` pair).
+* Training.  All NeRF variables live in ONE ``[2, NET_PARAMS]`` parameter (``nerf_params``; the four layer modules
+  hold views), and ``compile()`` with the default optimizer drives ``clipnerf_b200.trainer.RenderTrainer`` on it:
+  ``train_step`` is the fused clip + warm-up + Adam kernel behind the render backward, ``fit`` uploads the generator's
+  batches from pinned memory one batch ahead and replays the step from a CUDA graph (one launch per step), with the
+  NCCL all-reduce of the flat gradient recorded in it when ``torch.distributed`` is initialised.  The optimizer
+  groups are the reference's (``src/train_nerf.py:27-33``): the two embeddings train (Adam 1e-4 with
+  ``WarmupScheduler(1e-4, 10000, 450000)``), the readouts are in no group and keep their values
+  (``train_readouts=True`` changes that), the encoders belong to the plug-in (``feature_optimizer``).
+  Passing a ``torch.optim.Optimizer`` or a custom loss selects a plain eager autograd step instead.
 """
 import os
 
@@ -21,6 +30,7 @@ import numpy as np
 import torch
 
 from clipnerf_b200 import ops
+from clipnerf_b200._abi import EMB_PARAMS, NET_PARAMS
 from clipnerf_b200.render import render_rays
 
 from ..data_generator.mvnerf import MVNeRFDataGenerator  # noqa: F401  (re-exported like the reference)
@@ -71,6 +81,15 @@ class MVVNeRFRenderer(torch.nn.Module):
         self.fine_embedding = MVResNetMLPNeRFEmbedding(6, 128, embed_direction_vector=embed_direction_vector,
                                                        n_views=n_views)
         self.fine_readout = RenderReadout(4)
+        # one flat buffer for every NeRF variable: row 0 = coarse net, row 1 = fine net, [embedding | readout]
+        with torch.no_grad():
+            init = torch.stack([torch.cat([self.coarse_embedding.flat, self.coarse_readout.flat]),
+                                torch.cat([self.fine_embedding.flat, self.fine_readout.flat])])
+        self.nerf_params = torch.nn.Parameter(init)
+        for row, (emb, ro) in enumerate(((self.coarse_embedding, self.coarse_readout),
+                                         (self.fine_embedding, self.fine_readout))):
+            emb.share_storage(self, 'nerf_params', row, 0)
+            ro.share_storage(self, 'nerf_params', row, EMB_PARAMS)
         self.visual_features = _UpstreamStub('VisualFeatures')
         self.clip_visual = _UpstreamStub('CLIPVisualEncoder')
         self.combine_clip_visual = _UpstreamStub('CombineCLIPVisualV0')
@@ -85,6 +104,8 @@ class MVVNeRFRenderer(torch.nn.Module):
         self.optimizer = None
         self.loss = None
         self.loss_tracker = []
+        self._trainer = None               # RenderTrainer on nerf_params (compile() with the default optimizer)
+        self._feature_optimizer = None
         self._generator = None
         if device is not None:
             self.to(device)
@@ -92,12 +113,198 @@ class MVVNeRFRenderer(torch.nn.Module):
     # ------------------------------------------------------------------ helpers
     @property
     def device(self):
-        return self.coarse_embedding.flat.device
+        return self.nerf_params.device
 
     def _flat(self, net):
-        emb = self.coarse_embedding if net == 'coarse' else self.fine_embedding
-        ro = self.coarse_readout if net == 'coarse' else self.fine_readout
-        return torch.cat([emb.flat, ro.flat])
+        return self.nerf_params[0 if net == 'coarse' else 1]
+
+    def _to_dev(self, x):
+        return torch.as_tensor(np.asarray(x) if not torch.is_tensor(x) else x, dtype=torch.float32).to(self.device)
+
+    def _rand(self, b, nr):
+        if self._generator is None:
+            self._generator = torch.Generator(device=self.device)
+            self._generator.manual_seed(torch.initial_seed() % (2 ** 31))
+        return torch.rand(b, nr, self.n_samples, device=self.device, generator=self._generator)
+
+    # ------------------------------------------------------------------ reference API
+    def encode(self, image):
+        if self.feature_fn is None:
+            return self.visual_features(image)
+        return self.feature_fn(self._to_dev(image))
+
+    def infer(self, inputs, batched_features, u_strat=None, u_pdf=None):
+        with torch.no_grad():
+            return self._call(inputs, self.n_rays_infer, self.infer_batch_size, batched_features, u_strat, u_pdf)
+
+    def call(self, inputs, training=False, mask=None):
+        src = self._to_dev(inputs[2])
+        b, n = src.shape[:2]
+        feats = self.encode(src.reshape(b * n, *src.shape[2:])).reshape(b, n, src.shape[2], src.shape[3], -1)
+        return self._call(inputs, self.n_rays_train, self.batch_size, feats)
+
+    def forward(self, inputs, training=False):
+        return self.call(inputs, training=training)
+
+    @staticmethod
+    def volumetric_render(zs, density, chromacity):
+        """(rgb, depth, weights) of reference :89-100 on the warp-scan compositing kernel."""
+        rgbs = torch.cat([chromacity, density[..., None]], dim=-1)
+        return ops.composite_fwd(zs, rgbs)
+
+    def _call(self, inputs, n_rays, batch_size, combined_features, u_strat=None, u_pdf=None):
+        """(rgb, depth, fine_rgb, fine_depth); reference :113-184.  ``n_rays`` is free (any even
+        number), not the 512 the reference's input_signature pins."""
+        ray_o, ray_d, images, K, Einv = [self._to_dev(t) for t in inputs]
+        feats = combined_features if torch.is_tensor(combined_features) else self._to_dev(combined_features)
+        b, nr = ray_o.shape[:2]
+        u_strat = self._rand(b, nr) if u_strat is None else self._to_dev(u_strat)
+        u_pdf = self._rand(b, nr) if u_pdf is None else self._to_dev(u_pdf)
+        return render_rays(self._flat('coarse'), self._flat('fine'), (ray_o, ray_d, images, K, Einv),
+                           feats.to(self.device), u_strat, u_pdf, self.near, self.far)
+
+    # ------------------------------------------------------------------ training plumbing (Keras-like)
+    def compile(self, optimizer=None, loss=None, feature_optimizer=None, train_readouts=False, target_lr=1e-4,
+                warmup_steps=10000, scale_down_after=450000):
+        """``optimizer`` None (default): the reference's NeRF optimizer group -- Adam on the two embeddings with
+        ``WarmupScheduler(target_lr, warmup_steps, scale_down_after)`` (``train_nerf.py:22-33``), per-element gradient
+        clip 1.0 (``model_v0.py:195``) -- as ``RenderTrainer`` on ``nerf_params``: fused update kernel, CUDA-graph
+        ``fit``, one NCCL all-reduce per step when ``torch.distributed`` is initialised.  ``feature_optimizer``: a torch
+        optimizer over the plug-in encoders' parameters (the reference's second group), stepped with the feature-map
+        gradient of every step.  ``optimizer`` = a ``torch.optim.Optimizer`` or a custom ``loss``
+        (``(labels, prediction) -> scalar``): plain eager autograd step on ``self.parameters()``."""
+        self.loss = loss if loss is not None else (lambda y, p: torch.mean((p - y) ** 2))
+        self._feature_optimizer = feature_optimizer
+        if optimizer is None and loss is None:
+            from clipnerf_b200.trainer import RenderTrainer
+            self._trainer = RenderTrainer(self.device, params=self.nerf_params, target_lr=target_lr,
+                                          warmup_steps=warmup_steps, scale_down_after=scale_down_after, clip=1.0,
+                                          train_readouts=train_readouts)
+            self.optimizer = self._trainer
+        else:
+            self._trainer = None
+            self.optimizer = optimizer if optimizer is not None else torch.optim.Adam(self.parameters(), lr=target_lr,
+                                                                                     eps=1e-7)
+
+    def _features_for(self, images):
+        """combined_features of a device image batch [b,nv,H,W,3] through the plug-in encoder"""
+        b, n = images.shape[:2]
+        return self.encode(images.reshape(b * n, *images.shape[2:])).reshape(b, n, images.shape[2], images.shape[3], -1)
+
+    def _encoder_backward(self, k, feats, f_out):
+        """hand the feature-map gradient of a step to the plug-in encoders (their own backward + optimizer step)"""
+        if f_out is None or not f_out.requires_grad or feats.grad is None:
+            return
+        base = f_out._base if f_out._base is not None else f_out
+        if base.grad_fn is None and base.numel() == feats.grad.numel() and base.is_contiguous():
+            base.grad = feats.grad.view_as(base)     # the maps are themselves the trainable leaf: no accumulation pass
+        else:
+            f_out.backward(feats.grad)
+        if self._feature_optimizer is not None:
+            self._feature_optimizer.step()
+            self._feature_optimizer.zero_grad(set_to_none=True)
+
+    def train_step(self, data):
+        """reference :186-197: loss = L(labels, rgb) + L(labels, fine_rgb); per-element clip 1.0; optimizer."""
+        inputs, labels = data
+        labels = self._to_dev(labels)
+        if self._trainer is not None:
+            dev_in = [self._to_dev(t) for t in inputs]
+            f_out = self._features_for(dev_in[2])
+            feats = f_out.detach().requires_grad_(f_out.requires_grad)
+            b, nr = dev_in[0].shape[:2]
+            loss = self._trainer.train_step(dev_in, feats, labels, self._rand(b, nr), self._rand(b, nr), self.near,
+                                            self.far)
+            self._encoder_backward(0, feats, f_out)
+            self.loss_tracker.append(loss)
+            return {'loss': loss}
+        rgb, depth, fine_rgb, fine_depth = self.call(inputs, training=True)
+        loss = self.loss(labels, rgb) + self.loss(labels, fine_rgb)
+        variables = [p for p in self.parameters() if p.requires_grad]
+        gradients = torch.autograd.grad(loss, variables, allow_unused=True)
+        optimize(self.optimizer, variables, gradients, 1.0)
+        self.loss_tracker.append(loss.detach())
+        return {'loss': loss.detach()}
+
+    def fit(self, generator, epochs=1, initial_epoch=0, verbose=0, graph=True):
+        """Keras ``fit`` over a ``Sequence`` (``train_nerf.py:52``).  With the default optimizer every epoch runs
+        ``clipnerf_b200.trainer.fit_host_batches_graph``: a background thread pulls ``generator[i]`` into pinned
+        memory (Keras' enqueuer), uploads run one batch ahead on a copy stream, the step is ONE CUDA-graph launch
+        (``graph=False``: eager launches), the losses come back asynchronously."""
+        history = []
+        for epoch in range(initial_epoch, epochs):
+            if self._trainer is not None:
+                from clipnerf_b200 import trainer as T
+                if self._generator is None:
+                    self._rand(1, 2)
+                batches = T.PinnedBatchQueue(generator, range(len(generator)), lambda item: list(item[0]) + [item[1]])
+                loop = T.fit_host_batches_graph if graph else T.fit_host_batches
+                losses = loop(self._trainer, batches, self._features_for, self.near, self.far, draws=self._generator,
+                              after_step=self._encoder_backward)
+            else:
+                losses = [float(self.train_step(generator[i])['loss']) for i in range(len(generator))]
+            self.loss_tracker.extend(losses)
+            generator.on_epoch_end()
+            history.append(float(np.mean(losses)) if len(losses) else float('nan'))
+            if verbose:
+                print(f'Epoch {epoch + 1}/{epochs} - loss: {history[-1]:.6f}')
+        return {'loss': history}
+
+    def summary(self):
+        print(f'{self.what}: out of scope (plug-in)')
+
+
+class MVVNeRFRenderer(torch.nn.Module):
+    def __init__(self, n_rays_train, n_rays_infer, n_views=2, n_samples=64, n_features=256,
+                 embed_direction_vector=True, batch_size=1, near=0.7, far=1.5, original_image_size=(480, 640),
+                 feature_fn=None, device=None, **kwargs):
+        super().__init__()
+        if n_samples != 64 or n_features != 256:
+            raise ValueError('the sm_100a path is specialised for n_samples=64 and n_features=256 '
+                             '(src/configs/nerf_model/default.yaml)')
+        self.n_views = n_views
+        self.coarse_embedding = MVResNetMLPNeRFEmbedding(6, 128, embed_direction_vector=embed_direction_vector,
+                                                         n_views=n_views)
+        self.coarse_readout = RenderReadout(4)
+        self.fine_embedding = MVResNetMLPNeRFEmbedding(6, 128, embed_direction_vector=embed_direction_vector,
+                                                       n_views=n_views)
+        self.fine_readout = RenderReadout(4)
+        # one flat buffer for every NeRF variable: row 0 = coarse net, row 1 = fine net, [embedding | readout]
+        with torch.no_grad():
+            init = torch.stack([torch.cat([self.coarse_embedding.flat, self.coarse_readout.flat]),
+                                torch.cat([self.fine_embedding.flat, self.fine_readout.flat])])
+        self.nerf_params = torch.nn.Parameter(init)
+        for row, (emb, ro) in enumerate(((self.coarse_embedding, self.coarse_readout),
+                                         (self.fine_embedding, self.fine_readout))):
+            emb.share_storage(self, 'nerf_params', row, 0)
+            ro.share_storage(self, 'nerf_params', row, EMB_PARAMS)
+        self.visual_features = _UpstreamStub('VisualFeatures')
+        self.clip_visual = _UpstreamStub('CLIPVisualEncoder')
+        self.combine_clip_visual = _UpstreamStub('CombineCLIPVisualV0')
+        self.feature_fn = feature_fn
+        self.n_samples = n_samples
+        self.n_rays_train = n_rays_train
+        self.n_rays_infer = n_rays_infer
+        self.batch_size = batch_size
+        self.infer_batch_size = 1
+        self.near, self.far = near, far
+        self.original_image_size = tuple(original_image_size)
+        self.optimizer = None
+        self.loss = None
+        self.loss_tracker = []
+        self._trainer = None               # RenderTrainer on nerf_params (compile() with the default optimizer)
+        self._feature_optimizer = None
+        self._generator = None
+        if device is not None:
+            self.to(device)
+
+    # ------------------------------------------------------------------ helpers
+    @property
+    def device(self):
+        return self.nerf_params.device
+
+    def _flat(self, net):
+        return self.nerf_params[0 if net == 'coarse' else 1]
 
     def _to_dev(self, x):
         return torch.as_tensor(np.asarray(x) if not torch.is_tensor(x) else x, dtype=torch.float32).to(self.device)
@@ -179,9 +386,13 @@ class MVVNeRFRenderer(torch.nn.Module):
         print(f'MVVNeRFRenderer (clipnerf_b200): {n} trainable NeRF parameters '
               f'(coarse/fine embedding 246784 each, readouts 516 each); encoders are plug-ins')
 
+    def _group_state(self, g):
+        mod = getattr(self, g)
+        return {'flat': mod.flat.detach().cpu().clone()} if hasattr(mod, 'share_storage') else mod.state_dict()
+
     def store(self, path):
         for g in _GROUPS:
-            torch.save(getattr(self, g).state_dict(), f'{path}_{g}.pt')
+            torch.save(self._group_state(g), f'{path}_{g}.pt')
 
     def load(self, path, old=False):
         """returns False unless every checkpoint group exists (reference :213-240)."""
@@ -189,7 +400,12 @@ class MVVNeRFRenderer(torch.nn.Module):
         if not all(os.path.exists(f) for f in files):
             return False
         for g, f in zip(_GROUPS, files):
-            getattr(self, g).load_state_dict(torch.load(f, map_location=self.device))
+            mod, state = getattr(self, g), torch.load(f, map_location=self.device)
+            if hasattr(mod, 'share_storage'):
+                with torch.no_grad():
+                    mod.flat.copy_(state['flat'])
+            else:
+                mod.load_state_dict(state)
         return True
 
 

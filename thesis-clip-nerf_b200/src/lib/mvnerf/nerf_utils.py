@@ -21,9 +21,8 @@ def optimize(optimizer, variables, gradients, gradients_clip=0.0):
     """per-element ``clip_by_value`` then ``apply_gradients`` (reference :8-12).  ``optimizer`` is a
     ``torch.optim.Optimizer`` over ``variables``."""
     for v, g in zip(variables, gradients):
-        if g is None:
-            continue
-        v.grad = g.clamp(-gradients_clip, gradients_clip) if gradients_clip > 0 else g
+        # a variable without a gradient this step must not see the previous step's (optimizer.step() skips None)
+        v.grad = None if g is None else (g.clamp(-gradients_clip, gradients_clip) if gradients_clip > 0 else g)
     optimizer.step()
 
 
