@@ -119,6 +119,27 @@ def make_scene(seed, nr, nv, device=None, pinned=False):
 
 
 # ----------------------------------------------------------------------------------------------
+# workloads (BASELINE.json configs)
+# ----------------------------------------------------------------------------------------------
+WORKLOADS = {
+    # name: (rays per GPU, source views, what BASELINE.json calls it)
+    'cfg2': (4096, 3, 'cfg2: CLIP-feature-conditioned NeRF render fwd+bwd, 3 views, 4096 rays x (64+128) samples'),
+    'cfg1': (1024, 1, 'cfg1: train_nerf.py default config (nerf_1_view), 1024 rays'),
+    'cfg3i': (8192, 1, 'cfg3(i): NeRF training step, 8192 rays/GPU, 1 view, ray-sharded DDP'),
+    'cfg5shard': (131072, 3, 'cfg5 per-GPU shard: 1M rays x 192 samples over 8 GPUs = 131072 rays/GPU, ray-chunked'),
+}
+
+
+def workload_config(args, nr):
+    tag = WORKLOADS[args.workload][2] if args.workload in WORKLOADS and WORKLOADS[args.workload][:2] == (nr, args.nv) \
+        else f'custom: {nr} rays, {args.nv} views'
+    return {'workload': f'{tag}; {args.nv} views {H}x{W}x{C} fp32 maps, {nr} rays x (64+128) samples per GPU, '
+                        f'MSE(coarse)+MSE(fine), feature-map gradient, clip+Adam',
+            'rays_per_gpu': nr, 'n_views': args.nv, 'samples': '64+128', 'image': [H, W], 'feature_channels': C,
+            'parallelism': f'ray-sharded dp{args.gpus}', 'l2': 'inputs larger than L2 (943 MB of feature maps per scene)'}
+
+
+# ----------------------------------------------------------------------------------------------
 # reference arm: the reference's algorithm on the host cores (oracle port; TensorFlow is absent)
 # ----------------------------------------------------------------------------------------------
 def oracle_step(sc, params, nr_sample):
@@ -156,7 +177,7 @@ def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
-    nr_sample = args.ref_rays
+    nr_sample = min(args.ref_rays, args.rays)
     base, _ = cpu_baseline(args.nv, nr_sample)
     times = []
     from oracle import nerf_oracle as O
@@ -170,32 +191,39 @@ def run_reference(args):
     ms = 1e3 * sum(times) / len(times)
     value = nr_sample / (ms / 1e3)
     base['value'] = value
+    cfg = workload_config(args, args.rays)       # this repo's arm's workload ...
+    # ... of which every CPU pass renders a BOUNDED SAMPLE: rays_per_pass rays (not rays_per_gpu), same maps / views
+    cfg['rays_per_pass'] = nr_sample
+    cfg['reference_arm'] = (f'one host process on {base["cores"]} cores, whatever --gpus says; each pass = {nr_sample} of the '
+                            f'{args.rays} rays of the workload on the full-size maps (the fixed per-pass cost of the 0.94 GB '
+                            f'map -- zero fill + gradient -- is spread over {nr_sample} rays)')
     print(json.dumps({
         'impl': 'reference', 'metric': 'rays_per_sec_fwd_bwd', 'value': value, 'unit': 'rays/s', 'n_gpus': args.gpus,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak',
-        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': workload_config(args, args.rays),          # this repo's arm's config; each step = the bounded sample below
-        'cpu_baseline': base,
+        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': cfg, 'cpu_baseline': base,
+        'host_processes': 1,
         'e2e': {'value': value, 'unit': 'rays/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
     }))
-
-
-def workload_config(args, nr):
-    tag = 'cfg2' if (nr, args.nv) == (4096, 3) else 'cfg3(i)' if (nr, args.nv) == (8192, 1) else \
-        'cfg5 per-GPU shard' if nr >= 131072 else 'custom'
-    return {'workload': f'{tag}: CLIP-feature-conditioned NeRF render fwd+bwd, {args.nv} views {H}x{W}x{C} fp32 maps, '
-                        f'{nr} rays x (64+128) samples per GPU, MSE(coarse)+MSE(fine), feature-map gradient, clip+Adam',
-            'rays_per_gpu': nr, 'n_views': args.nv, 'samples': '64+128', 'image': [H, W], 'feature_channels': C,
-            'parallelism': f'ray-sharded dp{args.gpus}', 'l2': 'inputs larger than L2 (943 MB of feature maps per scene)'}
 
 
 # ----------------------------------------------------------------------------------------------
 # this repo's arm
 # ----------------------------------------------------------------------------------------------
+def _traffic_file():
+    for name in ('r02_traffic.json', 'r01_v8_traffic.json'):
+        path = os.path.join(ROOT, 'profiles', name)
+        if os.path.exists(path):
+            return path
+    return None
+
+
 def run_b200(args):
+    import numpy as np
     import torch.distributed as dist
     from clipnerf_b200 import _abi
-    from clipnerf_b200.trainer import RenderTrainer, fit_host_batches, fit_host_batches_graph
+    from clipnerf_b200.synthetic import SyntheticNerfDataset
+    from src.lib.data_generator.mvnerf import MVNeRFDataGenerator
+    from src.lib.mvnerf.model_v0 import MVVNeRFRenderer
 
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -211,8 +239,16 @@ def run_b200(args):
 
     nr, nv = args.rays, args.nv
     sc = make_scene(100 + rank, nr, nv, device=dev, pinned=True)
-    feats = sc['features'].requires_grad_(True)
-    trainer = RenderTrainer(dev, seed=0)
+    # combined_features: produced upstream by the image encoders (out of scope), resident on the device; the plug-in
+    # below hands them to the model and receives their gradient every step (model.feature_fn)
+    maps = torch.nn.Parameter(sc['features'].reshape(nv, H, W, C))
+    model = MVVNeRFRenderer(n_rays_train=nr, n_rays_infer=nr, n_views=nv, near=NEAR, far=FAR,
+                            original_image_size=(H, W), feature_fn=lambda images: maps, device=dev)
+    torch.manual_seed(0)
+    model.compile()                      # default optimizer: RenderTrainer on the model's flat parameter buffer
+    model.max_rays_per_step = args.chunk_rays
+    trainer = model.optimizer
+    feats = maps.detach().reshape(1, nv, H, W, C).requires_grad_(True)       # same storage, the trainer's leaf
     dev_inputs = [t.to(dev, non_blocking=True) for t in sc['inputs']]
     dev_u = [sc[k].to(dev, non_blocking=True) for k in ('u_strat', 'u_pdf', 'target')]
 
@@ -220,24 +256,24 @@ def run_b200(args):
         feats.grad = None
         return trainer.train_step(dev_inputs, feats, dev_u[2], dev_u[0], dev_u[1], NEAR, FAR, args.chunk_rays)
 
-    h2d_bytes = sum(t.numel() * t.element_size() for t in sc['inputs']) + \
-        sum(sc[k].numel() * sc[k].element_size() for k in ('u_strat', 'u_pdf', 'target'))
-
     use_graph = nr <= args.chunk_rays and not args.no_graph      # (ray-chunked batches launch eagerly)
-    host_batch = list(sc['inputs']) + [sc['target'], sc['u_strat'], sc['u_pdf']]
-    assert all(t.is_pinned() for t in host_batch)
+
+    # ---- end to end: MVVNeRFRenderer.fit over a MVNeRFDataGenerator (what src/train_nerf.py:52 calls)
+    def make_generator(n_scenes, seed):
+        ds = SyntheticNerfDataset(n_scenes=n_scenes, n_perspectives=nv + 1, H=H, W=W, seed=seed)
+        return MVNeRFDataGenerator(ds, n_rays_train=nr, batch_size=1, n_views=nv, shuffle=True)
+    np.random.seed(1000 + rank)
+    gen_warm, gen_timed = make_generator(4, 7 + rank), make_generator(args.steps, 11 + rank)
+    item = gen_warm.compact_item(0)
+    h2d_bytes = sum(int(np.asarray(a).nbytes) for a in item[0]) + int(np.asarray(item[1]).size) * 4   # targets go up as fp32
+    n_tracked = [0]
 
     def run_e2e(steps):
-        # the call a user makes: a training loop over host batches (the reference's 5-tuple + targets + random
-        # draws, pinned memory).  Every step uploads its own batch (copy stream, one batch ahead of the kernels)
-        # and returns its loss to the host.
-        if use_graph:
-            # the training step replayed from CUDA graphs (un-chunked batch): per step the host enqueues the
-            # uploads, one graph launch and the loss read-back, so a slow host no longer bounds the loop
-            losses = fit_host_batches_graph(trainer, (host_batch for _ in range(steps)), feats, NEAR, FAR)
-        else:
-            losses = fit_host_batches(trainer, (host_batch for _ in range(steps)), feats, NEAR, FAR, args.chunk_rays)
-        assert len(losses) == steps and all(l == l for l in losses)
+        gen = gen_timed if steps == args.steps else gen_warm
+        n0 = len(model.loss_tracker)
+        hist = model.fit(gen, epochs=1, graph=use_graph)
+        n_tracked[0] = len(model.loss_tracker) - n0
+        assert n_tracked[0] == len(gen) and all(l == l for l in hist['loss'])
 
     def barrier():
         if world > 1:
@@ -262,10 +298,15 @@ def run_b200(args):
             gc.enable()
         e1.record()
         barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        mine = e0.elapsed_time(e1) / steps
+        ms = torch.tensor([mine], device=dev)
+        per_rank = [mine]
         if world > 1:
+            allr = [torch.zeros_like(ms) for _ in range(world)]
+            dist.all_gather(allr, ms)
+            per_rank = [float(t) for t in allr]
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms) / steps
+        return float(ms), per_rank
 
     with ClockSampler(local) as clocks:
         n_warm = max(args.warmup, 3)
@@ -282,11 +323,11 @@ def run_b200(args):
                 step_timed()
         torch.cuda.synchronize()
         clocks.mark(True)
-        ms = timed(step_timed, args.steps)
+        ms, ms_per_rank = timed(step_timed, args.steps)
         clocks.mark(False)
     launches = launches_per_step * args.steps      # kernels of this library inside the timed region (replayed or eager)
-    run_e2e(3)          # warm the loop's own allocations (device batch slots, pinned loss ring, copy stream)
-    ms_e2e = timed(run_e2e, args.steps, loop=True)
+    run_e2e(4)          # warm the loop: device batch slots, pinned rings, copy stream, one graph per buffer set
+    ms_e2e, ms_e2e_per_rank = timed(run_e2e, args.steps, loop=True)
 
     # ---- per-stage device times (CUDA events around every ABI call), separate instrumented pass
     stages = {}
@@ -302,10 +343,18 @@ def run_b200(args):
 
     _abi.TIMER = timer
     n_prof = min(args.steps, 3)
+    real_allreduce = trainer.allreduce_gradients
+
+    def timed_allreduce():
+        with timer('nccl_allreduce_gradients'):
+            real_allreduce()
+    if world > 1:
+        trainer.allreduce_gradients = timed_allreduce
     for _ in range(n_prof):
         step_resident()
     torch.cuda.synchronize()
     _abi.TIMER = None
+    trainer.allreduce_gradients = real_allreduce
     for name, a, b in records:
         st = stages.setdefault(name, [0.0, 0])
         st[0] += a.elapsed_time(b)
@@ -315,73 +364,96 @@ def run_b200(args):
 
     peaks = _peaks()
     rows_per_step = nr * 192 * nv
-    # algorithmic work per step of each stage: gather reads 4144 B per sample-view row in the
-    # forward; the backward re-reads them for the fine pass (coordinate gradient) and scatter-adds
-    # (read+write) for both passes
+    # algorithmic work per step of each stage.  Tensor stages: credited FLOPs (recompute not
+    # counted).  Gather stages: SURVEY 8(d)'s 4 144 B per sample-view row -- after the spatial binning most of these
+    # bytes are served from shared memory, so they are reported as `algorithmic_gbs` only; the roofline fraction of a
+    # gather stage is the DRAM traffic ncu measured for it (profiles/*_traffic.json) over its live time.
     alg = {
         'cn_project_gather_fwd': ('hbm', rows_per_step * GATHER_BYTES_PER_ROW),
-        'cn_project_gather_bwd': ('hbm', rows_per_step * GATHER_BYTES_PER_ROW * 2 + nr * 128 * nv * GATHER_BYTES_PER_ROW),
+        'cn_project_gather_bwd': ('hbm', nr * 128 * nv * GATHER_BYTES_PER_ROW),
+        'cn_feature_grad': ('hbm', rows_per_step * GATHER_BYTES_PER_ROW * 2),
         'cn_mlp_feature_fwd': ('tensor', nr * 192 * nv * 293632.0),
         'cn_mlp_fusion_fwd': ('tensor', nr * 192 * 197632.0),
         'cn_mlp_block_bwd': ('tensor', 2.0 * (nr * 192 * nv * 3 + nr * 192 * 3) * 4 * 128 * 128),
         'cn_mlp_l0_dgrad': ('tensor', nr * 192 * nv * 2.0 * 384 * 128),
         'cn_mlp_l0_wgrad': ('tensor', nr * 192 * nv * 2.0 * 384 * 128),
     }
-    # measured DRAM traffic of every hot kernel (ncu capture of this command, cfg2 only): actual bytes moved through
-    # HBM per step / live stage time = the DRAM bandwidth the stage really draws (the `achieved_gbs` of the gather
-    # stages counts ALGORITHMIC bytes, most of which are served by L2 after the spatial binning -- hence > peak)
-    ncu_traffic = {}
+    ncu_traffic, ncu_per_launch, traffic_src = {}, {}, None
     try:
-        if (nr, nv) == (4096, 3):
-            with open(os.path.join(ROOT, 'profiles', 'r01_v8_traffic.json')) as f:
+        if (nr, nv) == (4096, 3) and _traffic_file():
+            traffic_src = os.path.relpath(_traffic_file(), ROOT)
+            with open(_traffic_file()) as f:
                 raw = json.load(f)
             for k, v in raw.items():
                 if isinstance(v, dict):
-                    ncu_traffic[k.split(' ')[0]] = v['dram_bytes_per_launch'] * v['launches_per_step']
+                    name = k.split(' ')[0]
+                    ncu_traffic[name] = ncu_traffic.get(name, 0) + v['dram_bytes_per_launch'] * v['launches_per_step']
+                    ncu_per_launch.setdefault(name, v['dram_bytes_per_launch'])
     except Exception:
         ncu_traffic = {}
     stage_report = {}
     for k, t in sorted(stage_ms.items(), key=lambda kv: -kv[1]):
         ent = {'ms_per_step': round(t, 4), 'calls_per_step': stage_calls[k]}
         if k in ncu_traffic:
-            ent['dram_gbs_ncu_bytes'] = round(ncu_traffic[k] / (t * 1e-3) / 1e9, 1)
+            ent['dram_gbs'] = round(ncu_traffic[k] / (t * 1e-3) / 1e9, 1)
             ent['dram_frac'] = round(ncu_traffic[k] / (t * 1e-3) / 1e9 / peaks['hbm_gbs'], 4)
         if k in alg:
             bound, work = alg[k]
             if bound == 'hbm':
-                ent.update(bound='hbm', achieved_gbs=round(work / (t * 1e-3) / 1e9, 1),
-                           frac=round(work / (t * 1e-3) / 1e9 / peaks['hbm_gbs'], 4))
+                ent.update(bound='hbm', algorithmic_gbs=round(work / (t * 1e-3) / 1e9, 1))
+                if 'dram_frac' in ent:
+                    ent['frac'] = ent['dram_frac']            # roofline fraction = measured DRAM bytes / live time / peak
             else:
-                ent.update(bound='tensor', achieved_tflops=round(work / (t * 1e-3) / 1e12, 1),
-                           frac=round(work / (t * 1e-3) / 1e12 / peaks['tf_sustained'], 4))
+                tf = work / (t * 1e-3) / 1e12
+                ent.update(bound='tensor', achieved_tflops=round(tf, 1), frac_burst=round(tf / peaks['tf_burst'], 4),
+                           frac_sustained=round(tf / peaks['tf_sustained'], 4), frac=round(tf / peaks['tf_burst'], 4))
         stage_report[k] = ent
-    dom = next(iter(stage_report))
+    dom = next(k for k in stage_report if k in alg)
     d = stage_report[dom]
-    # DRAM traffic per launch of the dominant kernel from the committed ncu --set full capture of this command
-    # (cfg2 only: the capture is of the default workload)
-    traffic = None
-    try:
-        if (nr, nv) == (4096, 3):
-            with open(os.path.join(ROOT, 'profiles', 'r01_v8_traffic.json')) as f:
-                traffic = json.load(f).get(dom, {}).get('dram_bytes_per_launch')
-    except Exception:
-        traffic = None
+    traffic = ncu_per_launch.get(dom)
     if d.get('bound') == 'hbm':
-        roofline = {'kernel': dom, 'bound': 'hbm', 'achieved': d['achieved_gbs'], 'peak': peaks['hbm_gbs'],
-                    'unit': 'GB/s', 'frac': d['frac'], 'traffic': traffic, 'peak_source': peaks['source']}
-    elif d.get('bound') == 'tensor':
-        roofline = {'kernel': dom, 'bound': 'tensor', 'achieved': d['achieved_tflops'], 'peak': peaks['tf_sustained'],
-                    'unit': 'TFLOP/s', 'frac': d['frac'], 'traffic': traffic, 'traffic_unit': 'bytes per launch (ncu dram read+write, profiles/r01_v8_traffic.json)',
-                    'peak_source': peaks['source'] + ' (sustained)'}
+        roofline = {'kernel': dom, 'bound': 'hbm', 'achieved': d.get('dram_gbs'), 'peak': peaks['hbm_gbs'],
+                    'unit': 'GB/s', 'frac': d.get('frac'), 'traffic': traffic, 'algorithmic_gbs': d['algorithmic_gbs'],
+                    'peak_source': peaks['source'], 'traffic_source': traffic_src}
     else:
-        roofline = {'kernel': dom, 'bound': 'hbm', 'achieved': None, 'peak': peaks['hbm_gbs'], 'unit': 'GB/s',
-                    'frac': None, 'traffic': None, 'peak_source': peaks['source']}
+        # the timed region is a burst (tens of ms at full clocks, no power cap): burst peak is the honest denominator
+        roofline = {'kernel': dom, 'bound': 'tensor', 'achieved': d['achieved_tflops'], 'peak': peaks['tf_burst'],
+                    'unit': 'TFLOP/s', 'frac': d['frac_burst'], 'frac_burst': d['frac_burst'],
+                    'frac_sustained': d['frac_sustained'], 'peak_sustained': peaks['tf_sustained'], 'traffic': traffic,
+                    'traffic_unit': f'bytes per launch (ncu dram read+write, {traffic_src})',
+                    'peak_source': peaks['source'] + ' (burst)'}
     mlp_ms = sum(t for k, t in stage_ms.items() if k.startswith('cn_mlp'))
-    whole = {
-        'mlp_tensor_frac_of_sustained': round(nr * FLOP_PER_RAY.get(nv, 0) / (mlp_ms * 1e-3) / 1e12 / peaks['tf_sustained'], 4)
-        if mlp_ms > 0 and nv in FLOP_PER_RAY else None,
-        'mlp_ms_per_step': round(mlp_ms, 4),
-    }
+    whole = {}
+    if nv in FLOP_PER_RAY:
+        step_tf = nr * FLOP_PER_RAY[nv] / (ms * 1e-3) / 1e12
+        whole = {'step_mlp_tflops': round(step_tf, 1), 'step_frac_of_burst': round(step_tf / peaks['tf_burst'], 4),
+                 'step_frac_of_sustained': round(step_tf / peaks['tf_sustained'], 4),
+                 'mlp_kernels_ms_per_step': round(mlp_ms, 4),
+                 'mlp_kernels_frac_of_burst': round(nr * FLOP_PER_RAY[nv] / (mlp_ms * 1e-3) / 1e12 / peaks['tf_burst'], 4)
+                 if mlp_ms > 0 else None}
+
+    # ---- cfg5 strong-scaling shard under the 8-GPU run: ONE scene, its maps broadcast once, 2^20 rays / world per rank
+    extra = {}
+    if world == 8 and not args.no_cfg5 and (nr, nv) == (4096, 3):
+        shard = (1 << 20) // world
+        with torch.no_grad():
+            dist.broadcast(maps, src=0)                          # features of the one scene, NCCL over NVSwitch
+            for t in dev_inputs[2:]:
+                dist.broadcast(t, src=0)
+        sc5 = make_scene(500 + rank, shard, nv)                  # this rank's ray range of the target view
+        in5 = [t.to(dev) for t in sc5['inputs'][:2]] + dev_inputs[2:]
+        u5 = [sc5[k].to(dev) for k in ('u_strat', 'u_pdf', 'target')]
+        del sc5
+
+        def step5():
+            feats.grad = None
+            return trainer.train_step(in5, feats, u5[2], u5[0], u5[1], NEAR, FAR, args.chunk_rays)
+        step5()
+        ms5, ms5_ranks = timed(step5, 3)
+        extra['cfg5_strong'] = {'workload': 'cfg5: 2^20 rays x 192 samples of ONE scene (maps broadcast once), sharded '
+                                            f'{shard} rays per GPU over {world} GPUs, fwd+bwd, ray-chunked ({args.chunk_rays})',
+                                'value': (1 << 20) / (ms5 * 1e-3), 'unit': 'rays/s', 'ms_per_step': ms5,
+                                'ms_per_step_per_rank': [round(x, 3) for x in ms5_ranks], 'steps': 3, 'scaling': 'strong'}
 
     if rank == 0:
         value = world * nr / (ms * 1e-3)
@@ -392,26 +464,33 @@ def run_b200(args):
             'data': 'synthetic', 'config': workload_config(args, nr),
             'e2e': {'value': world * nr / (ms_e2e * 1e-3), 'unit': 'rays/s', 'ms_per_step': ms_e2e,
                     'h2d_bytes_per_step': h2d_bytes, 'd2h_bytes_per_step': 4,
-                    'loop': 'fit_host_batches_graph (train step replayed from a CUDA graph)' if use_graph else 'fit_host_batches (eager launches)',
-                    'note': 'host batch = the reference 5-tuple (rays, images, K, E^-1) + targets + '
-                            'random draws in pinned memory, uploaded every step on a copy stream one batch ahead; loss '
-                            'read back every step; combined_features stay on the device, where the upstream encoders '
-                            'produce them'},
-            'gpu_launches': launches, 'launch_mode': 'cuda graph replay' if use_graph else 'eager', 'clocks': clocks.summary(), 'roofline': roofline, 'stages': stage_report,
-            'mlp': whole,
+                    'loop': 'MVVNeRFRenderer.fit(MVNeRFDataGenerator) -> ' +
+                            ('fit_host_batches_graph (one CUDA-graph launch per step)' if use_graph else 'fit_host_batches (eager, ray-chunked)'),
+                    'note': 'the call src/train_nerf.py:52 makes: model.fit over a MVNeRFDataGenerator on a synthetic '
+                            'in-memory dataset (its batches assembled by a background thread: random source / target '
+                            'views, bbox_biased_sample, get_specific_rays, targets), every step uploads its batch from '
+                            'pinned memory (rays, uint8 source images converted on the device, K, E^-1, targets) one batch '
+                            'ahead on a copy stream and its loss is read back; the stratified / inverse-CDF draws are made '
+                            'on the device as the reference does; combined_features stay on the device, where the upstream '
+                            'encoders produce them (model.feature_fn plug-in returns the resident maps and receives their gradient)'},
+            'gpu_launches': launches, 'launch_mode': 'cuda graph replay' if use_graph else 'eager',
+            'clocks': clocks.summary(), 'roofline': roofline, 'stages': stage_report, 'mlp': whole,
         }
+        if world > 1:
+            out['ms_per_step_per_rank'] = [round(x, 4) for x in ms_per_rank]
+            out['e2e']['ms_per_step_per_rank'] = [round(x, 4) for x in ms_e2e_per_rank]
+        out.update(extra)
         if world == 1 and not args.no_cpu_baseline:
-            base, _ = cpu_baseline(nv, args.ref_rays)
+            base, _ = cpu_baseline(nv, min(args.ref_rays, nr))
             out['cpu_baseline'] = base
         print(json.dumps(out))
     if world > 1:
         sys.stdout.flush()
-        if use_graph:
-            # graphs that recorded NCCL work must be gone before the communicator is torn down
-            trainer.__dict__.pop('_graphs', None)
-            step_timed = None  # noqa: F841
-            gc.collect()
-            torch.cuda.synchronize()
+        # graphs that recorded NCCL work must be gone before the communicator is torn down
+        trainer.__dict__.pop('_graphs', None)
+        step_timed = None  # noqa: F841
+        gc.collect()
+        torch.cuda.synchronize()
         dist.barrier()
         dist.destroy_process_group()
 
@@ -421,16 +500,21 @@ def main():
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=3)
-    ap.add_argument('--graph-multi', action='store_true', help='(default now) replay CUDA graphs, with the NCCL all-reduce recorded, on > 1 rank')
-    ap.add_argument('--no-graph', action='store_true', help='e2e loop with eager launches instead of CUDA-graph replay')
+    ap.add_argument('--no-graph', action='store_true', help='eager launches instead of CUDA-graph replay')
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--rays', type=int, default=4096, help='rays per GPU per step')
-    ap.add_argument('--nv', type=int, default=3, help='source views')
-    ap.add_argument('--ref-rays', type=int, default=512, help='bounded CPU sample (rays) of the reference arm')
+    ap.add_argument('--workload', default='cfg2', choices=sorted(WORKLOADS),
+                    help='BASELINE.json config (rays per GPU, views); --rays / --nv override')
+    ap.add_argument('--rays', type=int, default=None, help='rays per GPU per step')
+    ap.add_argument('--nv', type=int, default=None, help='source views')
+    ap.add_argument('--ref-rays', type=int, default=1024, help='bounded CPU sample (rays per pass) of the reference arm')
     ap.add_argument('--chunk-rays', type=int, default=16384,
                     help='batches with more rays per GPU are rendered in chunks of this many rays (gradients accumulate)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-cfg5', action='store_true', help='skip the cfg5 strong-scaling shard of the 8-GPU run')
     args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    args.rays = wl[0] if args.rays is None else args.rays
+    args.nv = wl[1] if args.nv is None else args.nv
     if args.impl == 'reference':
         run_reference(args)
     else:

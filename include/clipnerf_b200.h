@@ -168,6 +168,12 @@ int cn_generate_rays(const double *rk_inv_host, const float *origin_host, int32_
 int cn_quantize_render(const float *rgb, const float *depth, int64_t n, void *minmax_ws, uint8_t *rgb8,
                        uint8_t *depth8, void *stream);
 
+/* source images of MVNeRFDataGenerator.get_input (data_generator/mvnerf.py:37-38: `np.array(colors) / 255.0` cast to
+ * float32) from the dataset's uint8 pixels: dst [n_pixels,3] = float32(double(src[p, c]) / 255.0), c < 3 of
+ * src_channels (3 = RGB, 4 = RGBA as stored).  Lets the training loop upload uint8 images and keeps the host out
+ * of the per-step float conversion; bit-identical to the numpy expression.                                        */
+int cn_images_u8_to_f32(const uint8_t *src, int64_t n_pixels, int32_t src_channels, float *dst, void *stream);
+
 /* ---- compositing --------------------------------------------------------------- */
 
 /* volumetric_render (model_v0.py:89-100): z [n,S], rgbs [n,S,4] = (r,g,b,sigma)

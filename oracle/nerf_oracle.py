@@ -381,6 +381,24 @@ class _RoundBF16(torch.autograd.Function):
         return g
 
 
+class _RoundTF32(torch.autograd.Function):
+    """round to TensorFloat-32 (10 explicit mantissa bits, round-to-nearest-even), straight-through gradient: the
+    operand rounding of TensorFlow's default matmul path on Ampere-and-later GPUs (``tf.config.experimental.
+    enable_tensor_float_32_execution`` defaults to True), i.e. the arithmetic class the reference itself trains in"""
+
+    @staticmethod
+    def forward(ctx, x):
+        if x.dtype != torch.float32:
+            return x
+        i = x.contiguous().view(torch.int32)
+        r = (i + 0x0FFF + ((i >> 13) & 1)) & ~0x1FFF
+        return r.view(torch.float32)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g
+
+
 def _ident(x):
     return x
 
@@ -395,6 +413,9 @@ def _quantizer(quant: Optional[str]):
         return _ident
     if quant == 'bf16':
         return _RoundBF16.apply
+    if quant == 'tf32':
+        # matmul operands only, as TF32 execution does (the per-view stage output is not a stored bf16 tile there)
+        return _RoundTF32.apply
     raise ValueError(f'unknown quant {quant!r}')
 
 
@@ -425,7 +446,8 @@ def mv_embedding_from_x(x: Tensor, p: Dict[str, Tensor], prefix: str, n_views: i
     outputs = [x]
     for i in range(3):
         outputs.append(resnet_mlp_block(outputs[-1], p, f'{prefix}.feature_blocks.{i}', quant=quant))
-    pre = q(outputs[-1]).reshape(-1, n_views, *outputs[-1].shape[1:])
+    q_store = q if quant == 'bf16' else _ident          # the CUDA path stores the per-view stage output as bf16 tiles
+    pre = q_store(outputs[-1]).reshape(-1, n_views, *outputs[-1].shape[1:])
     outputs.append(pre.mean(dim=1))
     for i in range(3):
         outputs.append(resnet_mlp_block(outputs[-1], p, f'{prefix}.fusion_blocks.{i}', quant=quant))

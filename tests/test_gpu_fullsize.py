@@ -136,3 +136,39 @@ def test_cfg2_backward_is_linear_in_the_loss_scale(cuda, cfg2):
         e = _rel(b_, 4.0 * a)
         print('linearity', e)
         assert e < tol, e
+
+
+def test_cfg2_bias_gradient_column_sums(cuda):
+    """The block backward takes its bias gradients from the registers of the epilogue with a butterfly whose first two
+    levels add in packed bf16x2 (mlp_bwd.cu: colsum_bf16x2).  Here at the row count of the cfg2 fine pass -- 12 288
+    tiles = 1.57 M rows per column sum, 83 tiles per CTA -- against fp64 column sums of the same bf16 streams, for
+    zero-mean and for biased gradient streams (2e-2 bar of BASELINE.json; measured ~1e-3)."""
+    from clipnerf_b200 import layout, ops, params
+    from oracle import nerf_oracle as O
+    nt = 12288
+    rows = nt * 128
+    named = O.init_params(3, bias_std=0.02)
+    flat = params.from_named(named, 'fine').to(cuda)
+    packed = ops.pack_weights(flat)
+    g = torch.Generator(device=cuda).manual_seed(5)
+    bf = lambda t: t.to(torch.bfloat16).to(torch.float32)  # noqa: E731
+    a1 = bf(torch.relu(torch.randn(rows, 128, generator=g, device=cuda)))
+    blk = 1
+    wa = bf(named[f'fine_embedding.feature_blocks.{blk}.layer_0.kernel'].to(cuda))
+    wb = bf(named[f'fine_embedding.feature_blocks.{blk}.layer_1.kernel'].to(cuda))
+    ba = named[f'fine_embedding.feature_blocks.{blk}.layer_0.bias'].to(cuda)
+    a1_t = layout.matrix_to_tiles(a1)
+    for mean in (0.0, 0.05):
+        gy = bf(torch.randn(rows, 128, generator=g, device=cuda) * 0.1 + mean)
+        gy_t = layout.matrix_to_tiles(gy)
+        grad = torch.zeros_like(flat)
+        ops.mlp_block_bwd(packed, blk, a1_t, 1, 0, gy_t.clone(), grad)
+        gv = params.views(grad)
+        t = a1 @ wa + ba
+        g_t = bf(gy @ wb.t()) * (bf(torch.relu(t)) > 0)
+        want_bb, want_ba = gy.double().sum(0), g_t.double().sum(0)
+        e_bb = rel_err(gv[f'embedding.feature_blocks.{blk}.layer_1.bias'], want_bb)
+        e_ba = rel_err(gv[f'embedding.feature_blocks.{blk}.layer_0.bias'], want_ba)
+        print(f'bias gradients over {rows} rows, stream mean {mean}: d layer_1.bias {e_bb:.2e}  d layer_0.bias {e_ba:.2e}')
+        assert e_bb < 2e-2 and e_ba < 2e-2, (mean, e_bb, e_ba)
+        del gy, gy_t, g_t, t

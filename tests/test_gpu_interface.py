@@ -104,8 +104,9 @@ def test_model_call_infer_and_train_step(cuda, tmp_path):
 
 def test_fit_is_one_graph_launch_per_step(cuda, monkeypatch):
     """MVVNeRFRenderer.fit with the default optimizer (what src/train_nerf.py:52 calls) drives RenderTrainer: after the
-    first (eager) step and one capture per device buffer set, every step is ONE CUDA-graph launch and no kernel of the
-    library is launched outside it; an explicit torch optimizer selects the plain eager step."""
+    first (eager) step and one capture per device buffer set, every step is ONE CUDA-graph launch behind the single
+    uint8 -> float conversion launch of the uploaded source images (the generator's compact batches); an explicit
+    torch optimizer selects the plain eager step."""
     from clipnerf_b200 import _abi
     from clipnerf_b200.synthetic import SyntheticNerfDataset
     from src.lib.data_generator.mvnerf import MVNeRFDataGenerator
@@ -122,13 +123,14 @@ def test_fit_is_one_graph_launch_per_step(cuda, monkeypatch):
     p0 = m.nerf_params.detach().clone()
     hist = m.fit(gen, epochs=1)                      # 6 steps: 1 eager, 2 captures (+ replay), 3 pure replays
     assert len(replays) == 5 and m.optimizer.iterations == 6 and len(m.loss_tracker) == 6
-    launches_after_captures = replays[2]
-    assert _abi.LAUNCHES == launches_after_captures, 'a step launched library kernels outside the graph'
+    # between two replays the library launches exactly one kernel outside the graph: cn_images_u8_to_f32
+    assert replays[3] - replays[2] == 1 and replays[4] - replays[3] == 1, replays
+    launches_end = _abi.LAUNCHES
     assert np.isfinite(hist['loss']).all() and not torch.equal(p0, m.nerf_params.detach())
     assert maps.grad is not None and torch.isfinite(maps.grad).all() and float(maps.grad.abs().max()) > 0
     assert float(m.optimizer._t_dev) == 6.0
     hist = m.fit(gen, epochs=3, initial_epoch=1)     # graphs are reused across epochs
-    assert len(replays) == 5 + 12 and _abi.LAUNCHES == launches_after_captures and m.optimizer.iterations == 18
+    assert len(replays) == 5 + 12 and _abi.LAUNCHES == launches_end + 12 and m.optimizer.iterations == 18
     # explicit torch optimizer: eager autograd step over the same flat parameter
     m2 = _model(cuda, 2)
     m2.feature_fn = lambda images: maps.detach()
@@ -209,3 +211,24 @@ def test_device_rays_and_uint8_conversion(cuda):
     ref8, refd8 = O.quantize_render(rgb.numpy(), depth.numpy(), (H, W))
     assert np.array_equal(rgb8.cpu().numpy().reshape(H, W, 3), ref8)
     assert np.array_equal(depth8.cpu().numpy().reshape(H, W, 1), refd8)
+
+
+def test_compact_batches_equal_the_reference_batches(cuda):
+    """MVNeRFDataGenerator.compact_item (uint8 source images, converted by cn_images_u8_to_f32 on the device) against
+    __getitem__ (the reference's host expression np.array(colors) / 255.0 -> float32): same numpy RNG draws, every
+    array bit-identical"""
+    from clipnerf_b200 import ops
+    from clipnerf_b200.synthetic import SyntheticNerfDataset
+    from src.lib.data_generator.mvnerf import MVNeRFDataGenerator
+    ds = SyntheticNerfDataset(n_scenes=3, n_perspectives=4, H=30, W=41)
+    gen = MVNeRFDataGenerator(ds, n_rays_train=64, batch_size=2, n_views=3, shuffle=False)
+    np.random.seed(5)
+    ref_in, ref_t = gen[0]
+    np.random.seed(5)
+    cmp_in, cmp_t = gen.compact_item(0)
+    assert cmp_in[2].dtype == np.uint8 and cmp_in[2].shape == (2, 3, 30, 41, 4)
+    for k in (0, 1, 3, 4):
+        assert np.array_equal(ref_in[k], cmp_in[k])
+    assert np.array_equal(ref_t, cmp_t)
+    img = ops.images_u8_to_f32(torch.as_tensor(cmp_in[2]).to(cuda))
+    assert img.shape == (2, 3, 30, 41, 3) and np.array_equal(img.cpu().numpy(), ref_in[2])

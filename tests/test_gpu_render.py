@@ -102,10 +102,19 @@ def test_fine_pass_and_sampler_gradients(cuda, nv):
 
 
 def test_render_end_to_end(cuda):
-    """Whole _call, both losses.  Outputs and fine-net gradients are asserted; the coarse-net and
-    feature-map gradients contain the ill-conditioned sampler path (see above) and are reported."""
+    """Whole _call, both losses, against the bf16-operand oracle and the PLAIN-fp32 oracle.
+
+    Outputs (1e-2) and fine-net gradients (2e-2, max-norm) are asserted against both.  The coarse-net and feature-map
+    gradients contain the path through the un-stopped sampler, which is ill-conditioned in the reference itself: its
+    own TF32 arithmetic moves them by 2 ... 15 % (tests/test_oracle.py::test_reference_gradient_spread_fp32_vs_tf32).
+    They are asserted per tensor, statistically, against the fp32 oracle: relative L2 <= 6 x the oracle's own
+    fp32-vs-TF32 spread of that tensor (bf16 operands round 2^3 coarser than TF32; measured 3.5 ... 4 x) and
+    cosine >= 0.8; and in max-norm (6e-2; the map 0.2: single texels do not average over rays) against the oracle
+    that rounds operands where the kernels do."""
     from clipnerf_b200 import params
     from oracle import nerf_oracle as O
+    from test_oracle import _e2e_gradients, spread
+    floor = spread(_e2e_gradients('tf32')[0], _e2e_gradients(None)[0])
     for quant in ('bf16', None):
         sc = O.synthetic_scene(13, 1, 3, 64, 48, 64)
         named = O.init_params(7, bias_std=0.02)
@@ -118,12 +127,27 @@ def test_render_end_to_end(cuda):
         tgt = sc['target'].to(cuda)
         (torch.mean((out[0] - tgt) ** 2) + torch.mean((out[2] - tgt) ** 2)).backward()
         errs = {n_: rel_err(a, b_) for n_, a, b_ in zip(('rgb', 'depth', 'fine_rgb', 'fine_depth'), out, ref)}
+        got, want = {}, {}
         for net, flat in (('coarse', pc), ('fine', pf)):
             for name, gv in params.to_named(flat.grad.cpu(), net).items():
                 errs[f'grad {name}'] = rel_err(gv, p[name].grad)
+                got[name], want[name] = gv, p[name].grad
         errs['grad features'] = rel_err(fd.grad, feats.grad)
-        skip = [k for k in errs if 'coarse' in k or 'features' in k]
-        _report(f'e2e quant={quant}', errs, skip=skip)
+        got['features'], want['features'] = fd.grad.cpu(), feats.grad
+        ill = [k for k in errs if 'coarse' in k or 'features' in k]
+        _report(f'e2e quant={quant}', errs, skip=ill)
+        if quant == 'bf16':
+            bad = {k: errs[k] for k in ill if not errs[k] < (0.2 if 'features' in k else 6e-2)}
+            assert not bad, bad
+        else:
+            sp = spread(got, want)
+            for k in sorted(sp):
+                if k.startswith('coarse') or k == 'features':
+                    l2, cos = sp[k]
+                    print(f'[e2e vs fp32] {k:58s} rel L2 {l2:.4f} (fp32-vs-TF32 floor {floor[k][0]:.4f}, x{l2 / floor[k][0]:.1f})  '
+                          f'cos {cos:.4f} (floor {floor[k][1]:.4f})')
+                    assert l2 <= 6.0 * floor[k][0], (k, l2, floor[k][0])
+                    assert cos >= 0.8, (k, cos)
 
 
 def test_render_inference_matches_training_forward(cuda):
@@ -199,7 +223,8 @@ def test_update_kernel_matches_host_adam_on_the_gpu(cuda):
             for other in (eager, graphed):
                 assert rel_err(other.params, host.params) < 1e-6, (i, rel_err(other.params, host.params))
                 assert rel_err(other.m, host.m) < 1e-6 and rel_err(other.v, host.v) < 1e-6
-            assert torch.equal(eager.params.grad, grad.clamp(-1, 1))          # the gradient is left clipped
+            n = eager.n_update                                                 # the updated gradient entries are left clipped
+            assert torch.equal(eager.params.grad[:, :n], grad.clamp(-1, 1)[:, :n])
         init = RenderTrainer(cuda, **kw).params.detach()
         same_readouts = torch.equal(graphed.params.detach()[:, EMB_PARAMS:], init[:, EMB_PARAMS:])
         assert same_readouts == (not train_readouts)
@@ -230,6 +255,7 @@ def test_graph_replayed_step_walks_the_eager_step(cuda):
         E.iterations = G.iterations
         before = G.params.detach().clone()
         if i == 0 or i == 5:                      # first step of a trainer's life, and an eager step between replays
+            fg[k].grad = None                     # (autograd accumulates into an existing .grad)
             lg = G.train_step(bt[:5], fg[k], bt[5], bt[6], bt[7], NEAR, FAR)
         else:
             if k not in graphs:
@@ -257,7 +283,7 @@ def test_graph_replayed_training_loop_matches_eager(cuda):
     the map gradient of ITS batch.  With training the two loops cannot be bit-equal: the backward's fp32 atomics make
     gradients differ in the last bits from run to run, Adam's first updates are ~lr * sign(g), and the reference's
     un-stopped sampler path (model_v0.py:153-158) amplifies parameter noise.  So the NOISE FLOOR is measured here --
-    the eager loop against itself, three runs with identical seeds -- and the graph loop must lie within 2x of it
+    the eager loop against itself, five runs with identical seeds -- and the graph loop must lie within 2x of it
     (measured on a B200, tools/diag_graph_loop.py: eager/eager loss spread 2e-3 ... 8e-3 relative after 7 steps of 32
     rays, graph/eager 6e-4 ... 9e-3).  The arithmetic of the step itself is pinned without noise by the two tests above."""
     from clipnerf_b200.trainer import RenderTrainer, fit_host_batches, fit_host_batches_graph
@@ -279,11 +305,11 @@ def test_graph_replayed_training_loop_matches_eager(cuda):
     assert rel_err(g1, g0) < 3e-3, rel_err(g1, g0)
     # training: graph loop within the measured eager-vs-eager floor
     dist = lambda a, b_: max(abs(x - y) for x, y in zip(a[0], b_[0]))  # noqa: E731
-    eager = [run(fit_host_batches, 1e-4) for _ in range(3)]
-    floor = max(dist(eager[i], eager[j]) for i in range(3) for j in range(i + 1, 3))
+    eager = [run(fit_host_batches, 1e-4) for _ in range(5)]
+    floor = max(dist(eager[i], eager[j]) for i in range(5) for j in range(i + 1, 5))
     graph = run(fit_host_batches_graph, 1e-4)
     d_graph = min(dist(graph, e) for e in eager)
-    print(f'lr=1e-4: eager-vs-eager loss floor {floor:.3e} (3 runs), graph loop to the nearest eager run {d_graph:.3e}, '
+    print(f'lr=1e-4: eager-vs-eager loss floor {floor:.3e} (5 runs, 10 pairs), graph loop to the nearest eager run {d_graph:.3e}, '
           f'param diff eager/eager {rel_err(eager[1][1], eager[0][1]):.3e} graph/eager {rel_err(graph[1], eager[0][1]):.3e}')
     assert d_graph <= 2.0 * floor + 1e-6 * max(eager[0][0]), (d_graph, floor)
     assert abs(graph[0][0] - eager[0][0][0]) < 1e-5 * eager[0][0][0]          # the first step has no history: equal

@@ -47,6 +47,7 @@ PROTOTYPES = {
     'cn_feature_grad': [ctypes.POINTER(CnScene), c_int32, _P, _P, _P, _P, _P, _P, c_int32, _P],
     'cn_generate_rays': [_P, _P, c_int32, c_int32, c_int64, c_int64, _P, _P, _P],
     'cn_quantize_render': [_P, _P, c_int64, _P, _P, _P, _P],
+    'cn_images_u8_to_f32': [_P, c_int64, c_int32, _P, _P],
     'cn_composite_fwd': [_P, _P, c_int64, c_int32, _P, _P, _P, _P],
     'cn_composite_bwd': [_P, _P, c_int64, c_int32, _P, _P, _P, _P, _P, _P],
     'cn_pack_weights': [_P, _P, _P],

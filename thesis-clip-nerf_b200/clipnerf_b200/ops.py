@@ -215,6 +215,16 @@ def quantize_render(rgb, depth):
     return rgb8, depth8
 
 
+def images_u8_to_f32(src: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """uint8 [..., H, W, C>=3] -> float32 [..., H, W, 3] = float32(double(u8) / 255.0), the reference's host expression"""
+    assert src.is_cuda and src.dtype == torch.uint8 and src.is_contiguous() and src.shape[-1] >= 3
+    if out is None:
+        out = torch.empty(*src.shape[:-1], 3, dtype=torch.float32, device=src.device)
+    assert out.is_contiguous() and out.dtype == torch.float32 and out.numel() == src.numel() // src.shape[-1] * 3
+    call('cn_images_u8_to_f32', _ptr(src), src.numel() // src.shape[-1], src.shape[-1], _ptr(out), _stream())
+    return out
+
+
 def composite_fwd(z, rgbs):
     z, rgbs = _f32c(z), _f32c(rgbs)
     S = z.shape[-1]

@@ -239,10 +239,15 @@ class PinnedBatchQueue:
     the generator's item to a flat list of arrays; a ring of pinned buffer sets is recycled (a set is rewritten only
     after its upload has completed)."""
 
-    def __init__(self, sequence, indices, flatten, depth: int = 3):
+    def __init__(self, sequence, indices, flatten, depth: int = 3, getter=None, ring=None):
         self.sequence, self.indices, self.flatten = sequence, list(indices), flatten
+        self.getter = getter if getter is not None else sequence.__getitem__
         self.q = queue.Queue(maxsize=depth)
-        self.ring = [None] * (depth + 3)
+        # pinned buffer sets; a caller that runs many epochs passes its own list so that they are allocated once
+        self.ring = ring if ring is not None and len(ring) == depth + 3 else [None] * (depth + 3)
+        if ring is not None and ring is not self.ring:
+            ring[:] = self.ring
+            self.ring = ring
         self.error = None
         self.thread = threading.Thread(target=self._run, daemon=True)
         self.thread.start()
@@ -250,7 +255,7 @@ class PinnedBatchQueue:
     def _run(self):
         try:
             for n, i in enumerate(self.indices):
-                arrays = [torch.as_tensor(a) for a in self.flatten(self.sequence[i])]
+                arrays = [torch.as_tensor(a) for a in self.flatten(self.getter(i))]
                 arrays = [a.to(torch.float32) if a.dtype == torch.float64 else a for a in arrays]
                 k = n % len(self.ring)
                 old = self.ring[k]
@@ -373,7 +378,16 @@ def _step_operands(trainer, k, batch, features, draws, state):
     callable ``images [b,nv,H,W,3] -> [b,nv,H,W,256]`` (the upstream encoders; its result is copied into a per-set
     buffer when it does not keep its address, so that a recorded graph finds it).  ``draws``: None (the batch carries
     u_strat / u_pdf) or a torch.Generator the stratified / inverse-CDF draws are taken from on the device."""
-    inputs, target = batch[:5], batch[5]
+    inputs, target = list(batch[:5]), batch[5]
+    if inputs[2].dtype == torch.uint8:
+        # source images uploaded as the dataset's uint8 pixels (MVNeRFDataGenerator.get_data_compact): the reference's
+        # `colors / 255.0` runs on the device, into a float buffer of this set (stable address for a recorded graph)
+        from . import ops
+        img = state.get(('img', k))
+        shape = tuple(inputs[2].shape[:-1]) + (3,)
+        if img is None or tuple(img.shape) != shape:
+            img = state[('img', k)] = torch.empty(shape, dtype=torch.float32, device=inputs[2].device)
+        inputs[2] = ops.images_u8_to_f32(inputs[2], out=img)
     if draws is None:
         u_s, u_p = batch[6], batch[7]
     else:

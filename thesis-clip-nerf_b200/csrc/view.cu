@@ -78,7 +78,31 @@ __global__ void __launch_bounds__(256) quantize_kernel(const float *__restrict__
   depth8[i] = (uint8_t)(int)__fmul_rn(nd, 255.f);
 }
 
+// images of MVNeRFDataGenerator.get_input (mvnerf.py:37-38): np.array(colors) / 255.0 (float64) cast to float32 --
+// evaluated on the device from the dataset's uint8 pixels (first 3 of src_channels channels), bit-identical to numpy
+__global__ void __launch_bounds__(256) images_u8_kernel(const uint8_t *__restrict__ src, int64_t n_pixels,
+                                                        int src_channels, float *__restrict__ dst) {
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n_pixels * 3; i += (int64_t)gridDim.x * 256) {
+    const int64_t p = i / 3;
+    const int c = (int)(i - p * 3);
+    dst[i] = (float)((double)src[p * src_channels + c] / 255.0);
+  }
+}
+
 }  // namespace cn
+
+extern "C" int cn_images_u8_to_f32(const uint8_t *src, int64_t n_pixels, int32_t src_channels, float *dst,
+                                   void *stream) {
+  using namespace cn;
+  CN_REQUIRE(src && dst, "cn_images_u8_to_f32: null pointer");
+  CN_REQUIRE(n_pixels >= 0 && src_channels >= 3, "cn_images_u8_to_f32: n_pixels=%lld src_channels=%d",
+             (long long)n_pixels, src_channels);
+  if (n_pixels == 0) return 0;
+  const int64_t want = (n_pixels * 3 + 255) / 256;
+  const unsigned blocks = (unsigned)(want < 16 * num_sms() ? want : 16 * num_sms());
+  images_u8_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(src, n_pixels, src_channels, dst);
+  return check_launch("cn_images_u8_to_f32");
+}
 
 extern "C" int cn_generate_rays(const double *rk_inv_host, const float *origin_host, int32_t single_precision, int32_t W,
                                 int64_t first_pixel, int64_t n, float *ray_o, float *ray_d, void *stream) {

@@ -38,6 +38,19 @@ class MVNeRFDataGenerator(DataGenerator):
         return np.array(color[rays[:, 0], rays[:, 1], :3]) / 255.0
 
     def get_data(self, batch):
+        return self._assemble(batch, compact=False)
+
+    def get_data_compact(self, batch):
+        """``get_data`` with the source images left as the dataset's uint8 pixels ``[b, nv, H, W, C]`` (all stored
+        channels): ``MVVNeRFRenderer.fit`` uploads those and evaluates the reference's ``colors / 255.0`` on the device
+        (``cn_images_u8_to_f32``, bit-identical), which takes ~20 ms of numpy float conversion per 3 x 480 x 640 batch
+        off the host.  Same numpy RNG draw sequence as ``get_data``."""
+        return self._assemble(batch, compact=True)
+
+    def compact_item(self, index):
+        return self.get_data_compact(self.indices[index * self.batch_size:(index + 1) * self.batch_size])
+
+    def _assemble(self, batch, compact):
         cols = [[] for _ in range(5)]
         targets = []
         color_ds, cam_ds = self.dataset.datasets['color'], self.dataset.datasets['camera_config']
@@ -47,8 +60,14 @@ class MVNeRFDataGenerator(DataGenerator):
             tgt_color = color_ds.read_sample_at_idx(i, tgt_index)[..., :3]
             r_d, r_o, rays = self.generate_rays(tgt_color, cam_ds.read_sample_at_idx(i, tgt_index))
             targets.append(MVNeRFDataGenerator.get_target(tgt_color, rays))
-            src_colors = [color_ds.read_sample_at_idx(i, s)[..., :3] for s in src_indices]
             src_cfgs = [cam_ds.read_sample_at_idx(i, s) for s in src_indices]
-            for col, part in zip(cols, MVNeRFDataGenerator.get_input(src_colors, src_cfgs, r_d, r_o)):
+            if compact:
+                e_invs, ks = zip(*[camera_parameters(c) for c in src_cfgs])
+                parts = ([r_o], [r_d], [np.stack([color_ds.read_sample_at_idx(i, s) for s in src_indices])], [ks], [e_invs])
+            else:
+                src_colors = [color_ds.read_sample_at_idx(i, s)[..., :3] for s in src_indices]
+                parts = MVNeRFDataGenerator.get_input(src_colors, src_cfgs, r_d, r_o)
+            for col, part in zip(cols, parts):
                 col.extend(part)
-        return tuple(np.array(c, dtype=np.float32) for c in cols), np.array(targets)
+        out = tuple(np.array(c, dtype=np.uint8 if (compact and k == 2) else np.float32) for k, c in enumerate(cols))
+        return out, np.array(targets)

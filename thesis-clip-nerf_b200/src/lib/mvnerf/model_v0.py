@@ -105,6 +105,8 @@ class MVVNeRFRenderer(torch.nn.Module):
         self.loss = None
         self.loss_tracker = []
         self._trainer = None               # RenderTrainer on nerf_params (compile() with the default optimizer)
+        self._pinned_ring = []             # pinned host batch buffers of fit(), allocated once
+        self.max_rays_per_step = None      # larger batches are rendered in ray chunks whose gradients accumulate (eager)
         self._feature_optimizer = None
         self._generator = None
         if device is not None:
@@ -230,153 +232,30 @@ class MVVNeRFRenderer(torch.nn.Module):
         """Keras ``fit`` over a ``Sequence`` (``train_nerf.py:52``).  With the default optimizer every epoch runs
         ``clipnerf_b200.trainer.fit_host_batches_graph``: a background thread pulls ``generator[i]`` into pinned
         memory (Keras' enqueuer), uploads run one batch ahead on a copy stream, the step is ONE CUDA-graph launch
-        (``graph=False``: eager launches), the losses come back asynchronously."""
+        (``graph=False``: eager launches) behind the uint8 -> float conversion of the uploaded source images, the
+        losses come back asynchronously."""
         history = []
         for epoch in range(initial_epoch, epochs):
             if self._trainer is not None:
                 from clipnerf_b200 import trainer as T
                 if self._generator is None:
                     self._rand(1, 2)
-                batches = T.PinnedBatchQueue(generator, range(len(generator)), lambda item: list(item[0]) + [item[1]])
-                loop = T.fit_host_batches_graph if graph else T.fit_host_batches
-                losses = loop(self._trainer, batches, self._features_for, self.near, self.far, draws=self._generator,
-                              after_step=self._encoder_backward)
+                # (a generator with `compact_item` hands the source images as uint8: converted on the device)
+                batches = T.PinnedBatchQueue(generator, range(len(generator)), lambda item: list(item[0]) + [item[1]],
+                                             getter=getattr(generator, 'compact_item', None), ring=self._pinned_ring)
+                chunked = self.max_rays_per_step is not None and self.n_rays_train > self.max_rays_per_step
+                if graph and not chunked:
+                    losses = T.fit_host_batches_graph(self._trainer, batches, self._features_for, self.near, self.far,
+                                                      draws=self._generator, after_step=self._encoder_backward)
+                else:
+                    losses = T.fit_host_batches(self._trainer, batches, self._features_for, self.near, self.far,
+                                                self.max_rays_per_step, draws=self._generator,
+                                                after_step=self._encoder_backward)
+                self.loss_tracker.extend(losses)
             else:
                 losses = [float(self.train_step(generator[i])['loss']) for i in range(len(generator))]
-            self.loss_tracker.extend(losses)
             generator.on_epoch_end()
             history.append(float(np.mean(losses)) if len(losses) else float('nan'))
-            if verbose:
-                print(f'Epoch {epoch + 1}/{epochs} - loss: {history[-1]:.6f}')
-        return {'loss': history}
-
-    def summary(self):
-        print(f'{self.what}: out of scope (plug-in)')
-
-
-class MVVNeRFRenderer(torch.nn.Module):
-    def __init__(self, n_rays_train, n_rays_infer, n_views=2, n_samples=64, n_features=256,
-                 embed_direction_vector=True, batch_size=1, near=0.7, far=1.5, original_image_size=(480, 640),
-                 feature_fn=None, device=None, **kwargs):
-        super().__init__()
-        if n_samples != 64 or n_features != 256:
-            raise ValueError('the sm_100a path is specialised for n_samples=64 and n_features=256 '
-                             '(src/configs/nerf_model/default.yaml)')
-        self.n_views = n_views
-        self.coarse_embedding = MVResNetMLPNeRFEmbedding(6, 128, embed_direction_vector=embed_direction_vector,
-                                                         n_views=n_views)
-        self.coarse_readout = RenderReadout(4)
-        self.fine_embedding = MVResNetMLPNeRFEmbedding(6, 128, embed_direction_vector=embed_direction_vector,
-                                                       n_views=n_views)
-        self.fine_readout = RenderReadout(4)
-        # one flat buffer for every NeRF variable: row 0 = coarse net, row 1 = fine net, [embedding | readout]
-        with torch.no_grad():
-            init = torch.stack([torch.cat([self.coarse_embedding.flat, self.coarse_readout.flat]),
-                                torch.cat([self.fine_embedding.flat, self.fine_readout.flat])])
-        self.nerf_params = torch.nn.Parameter(init)
-        for row, (emb, ro) in enumerate(((self.coarse_embedding, self.coarse_readout),
-                                         (self.fine_embedding, self.fine_readout))):
-            emb.share_storage(self, 'nerf_params', row, 0)
-            ro.share_storage(self, 'nerf_params', row, EMB_PARAMS)
-        self.visual_features = _UpstreamStub('VisualFeatures')
-        self.clip_visual = _UpstreamStub('CLIPVisualEncoder')
-        self.combine_clip_visual = _UpstreamStub('CombineCLIPVisualV0')
-        self.feature_fn = feature_fn
-        self.n_samples = n_samples
-        self.n_rays_train = n_rays_train
-        self.n_rays_infer = n_rays_infer
-        self.batch_size = batch_size
-        self.infer_batch_size = 1
-        self.near, self.far = near, far
-        self.original_image_size = tuple(original_image_size)
-        self.optimizer = None
-        self.loss = None
-        self.loss_tracker = []
-        self._trainer = None               # RenderTrainer on nerf_params (compile() with the default optimizer)
-        self._feature_optimizer = None
-        self._generator = None
-        if device is not None:
-            self.to(device)
-
-    # ------------------------------------------------------------------ helpers
-    @property
-    def device(self):
-        return self.nerf_params.device
-
-    def _flat(self, net):
-        return self.nerf_params[0 if net == 'coarse' else 1]
-
-    def _to_dev(self, x):
-        return torch.as_tensor(np.asarray(x) if not torch.is_tensor(x) else x, dtype=torch.float32).to(self.device)
-
-    def _rand(self, b, nr):
-        if self._generator is None:
-            self._generator = torch.Generator(device=self.device)
-            self._generator.manual_seed(torch.initial_seed() % (2 ** 31))
-        return torch.rand(b, nr, self.n_samples, device=self.device, generator=self._generator)
-
-    # ------------------------------------------------------------------ reference API
-    def encode(self, image):
-        if self.feature_fn is None:
-            return self.visual_features(image)
-        return self.feature_fn(self._to_dev(image))
-
-    def infer(self, inputs, batched_features, u_strat=None, u_pdf=None):
-        with torch.no_grad():
-            return self._call(inputs, self.n_rays_infer, self.infer_batch_size, batched_features, u_strat, u_pdf)
-
-    def call(self, inputs, training=False, mask=None):
-        src = self._to_dev(inputs[2])
-        b, n = src.shape[:2]
-        feats = self.encode(src.reshape(b * n, *src.shape[2:])).reshape(b, n, src.shape[2], src.shape[3], -1)
-        return self._call(inputs, self.n_rays_train, self.batch_size, feats)
-
-    def forward(self, inputs, training=False):
-        return self.call(inputs, training=training)
-
-    @staticmethod
-    def volumetric_render(zs, density, chromacity):
-        """(rgb, depth, weights) of reference :89-100 on the warp-scan compositing kernel."""
-        rgbs = torch.cat([chromacity, density[..., None]], dim=-1)
-        return ops.composite_fwd(zs, rgbs)
-
-    def _call(self, inputs, n_rays, batch_size, combined_features, u_strat=None, u_pdf=None):
-        """(rgb, depth, fine_rgb, fine_depth); reference :113-184.  ``n_rays`` is free (any even
-        number), not the 512 the reference's input_signature pins."""
-        ray_o, ray_d, images, K, Einv = [self._to_dev(t) for t in inputs]
-        feats = combined_features if torch.is_tensor(combined_features) else self._to_dev(combined_features)
-        b, nr = ray_o.shape[:2]
-        u_strat = self._rand(b, nr) if u_strat is None else self._to_dev(u_strat)
-        u_pdf = self._rand(b, nr) if u_pdf is None else self._to_dev(u_pdf)
-        return render_rays(self._flat('coarse'), self._flat('fine'), (ray_o, ray_d, images, K, Einv),
-                           feats.to(self.device), u_strat, u_pdf, self.near, self.far)
-
-    # ------------------------------------------------------------------ training plumbing (Keras-like)
-    def compile(self, optimizer=None, loss=None):
-        """``optimizer``: a torch optimizer (or None -> Adam 1e-4 on the NeRF MLPs); ``loss``: callable
-        ``(labels, prediction) -> scalar`` (default mean squared error)."""
-        self.optimizer = optimizer if optimizer is not None else torch.optim.Adam(self.parameters(), lr=1e-4,
-                                                                                 eps=1e-7)
-        self.loss = loss if loss is not None else (lambda y, p: torch.mean((p - y) ** 2))
-
-    def train_step(self, data):
-        """reference :186-197: loss = L(labels, rgb) + L(labels, fine_rgb); per-element clip 1.0."""
-        inputs, labels = data
-        labels = self._to_dev(labels)
-        rgb, depth, fine_rgb, fine_depth = self.call(inputs, training=True)
-        loss = self.loss(labels, rgb) + self.loss(labels, fine_rgb)
-        variables = [p for p in self.parameters() if p.requires_grad]
-        gradients = torch.autograd.grad(loss, variables, allow_unused=True)
-        optimize(self.optimizer, variables, gradients, 1.0)
-        self.loss_tracker.append(float(loss.detach()))
-        return {'loss': loss.detach()}
-
-    def fit(self, generator, epochs=1, initial_epoch=0, verbose=0):
-        history = []
-        for epoch in range(initial_epoch, epochs):
-            losses = [float(self.train_step(generator[i])['loss']) for i in range(len(generator))]
-            generator.on_epoch_end()
-            history.append(float(np.mean(losses)) if losses else float('nan'))
             if verbose:
                 print(f'Epoch {epoch + 1}/{epochs} - loss: {history[-1]:.6f}')
         return {'loss': history}
