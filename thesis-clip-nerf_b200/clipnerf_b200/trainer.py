@@ -193,7 +193,9 @@ class RenderTrainer:
                 self.iterations += 1
         torch.cuda.current_stream().wait_stream(side)
         graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph, pool=pool):
+        # thread-local capture mode: the batch-producer thread of fit() pins host memory and waits for copy events
+        # while this thread records (under the default global mode any such call invalidates the capture)
+        with torch.cuda.graph(graph, pool=pool, capture_error_mode='thread_local'):
             loss = step()
         d_features = features.grad             # this graph's map gradient (graph-owned memory)
         t_dev = self._t_dev
