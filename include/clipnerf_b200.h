@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define CN_ABI_VERSION 6
+#define CN_ABI_VERSION 7
 #define CN_TILE_ROWS 128
 #define CN_HIDDEN 128
 #define CN_FEAT_C 256          /* combined_features channels (model_v0.py:60)            */
@@ -236,6 +236,23 @@ int cn_mlp_readout_bwd(const float *params, const float *d_y, const void *acts, 
 int cn_mlp_block_bwd(const void *packed, int32_t blk, const void *acts, int32_t act_stride_tiles,
                      int32_t act_index, int64_t n_tiles, const void *gy_tiles, int32_t gy_views,
                      int64_t gy_tiles_per_view, void *gh_tiles, float scale, float *grad, void *stream);
+/* Backward of a whole MLP stage in ONE launch (layers.py:363-375 in reverse): stage 1 = fusion blocks 5, 4, 3,
+ * stage 0 = per-view blocks 2, 1, 0 and -- when x_tiles / dx_tiles are given -- the first Dense's weight gradient
+ * (cn_mlp_l0_wgrad) and input gradient (cn_mlp_l0_dgrad).  Role-specialised persistent CTAs (one role per block, one
+ * each for the first Dense's dgrad / wgrad) pass the gradient stream from role to role through small tile rings in
+ * `ws` that stay in L2, so g never makes the HBM round trips it makes between the per-block launches; results equal
+ * the chain of the per-block calls (the bf16 g stream bit for bit, the fp32 sums up to summation order).
+ *   acts             [n_tiles][act_stride_tiles] saved relu(h) tiles, tile index 0..2 = the stage's blocks in order
+ *   gy_tiles         gradient w.r.t. the stage output; gy_views / gy_tiles_per_view as in cn_mlp_block_bwd
+ *   gh_tiles         gradient w.r.t. the stage input (may alias gy_tiles when gy_views == 1), or NULL when the
+ *                    first Dense roles consume it (stage 0 with x_tiles and / or dx_tiles; it is then not stored)
+ *   x_tiles, dx_tiles  nullable: MLP-input tiles (-> dW0, db0 accumulated into grad) / their gradient (written)
+ *   ws               cn_mlp_stage_bwd_ws_bytes() bytes of device scratch, 256-byte aligned (rings + counters)     */
+size_t cn_mlp_stage_bwd_ws_bytes(void);
+int cn_mlp_stage_bwd(const void *packed, int32_t stage, const void *acts, int32_t act_stride_tiles, int64_t n_tiles,
+                     const void *gy_tiles, int32_t gy_views, int64_t gy_tiles_per_view, void *gh_tiles,
+                     const void *x_tiles, void *dx_tiles, float scale, float *grad, void *ws, size_t ws_bytes,
+                     void *stream);
 /* mean-over-views backward: g_m [b][tiles_per_view] -> g_h3 [b][nv][tiles_per_view] = g_m / nv */
 int cn_mlp_mean_bwd(const void *gm_tiles, int32_t b, int32_t nv, int64_t tiles_per_view,
                     void *gh3_tiles, void *stream);

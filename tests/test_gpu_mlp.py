@@ -183,3 +183,56 @@ def test_mlp_many_tiles_per_cta(cuda):
     g0 = layout.tiles_to_matrix(gf, 128).cpu()
     dx_ref = s * (g0 @ named['fine_embedding.layer_0.kernel'].to(torch.bfloat16).to(torch.float32).t())
     assert rel_err(dxm, dx_ref) < 1e-2
+
+
+@pytest.mark.parametrize('nv,rows', [(3, 128 * 310), (2, 128 * 5), (1, 128 * 40)])
+def test_stage_backward_matches_the_block_by_block_chain(cuda, nv, rows):
+    """cn_mlp_stage_bwd (one launch per stage: role-specialised CTAs chained through L2 tile rings) against the chain
+    of per-block launches it replaces: the bf16 gradient stream and dX must be BIT-identical (same kernels' role
+    bodies, same per-tile arithmetic), the fp32 parameter gradients equal up to the order of the per-CTA partial sums.
+    Sizes: many tiles per CTA (ring wrap-around, counter phases), fewer tiles than CTAs of a role, one view."""
+    from clipnerf_b200 import layout, ops
+    b = 1
+    named, flat, x_ref, x_tiles = _setup(cuda, b, nv, rows, seed=3)
+    dev_flat = flat.to(cuda)
+    packed = ops.pack_weights(dev_flat)
+    h3, acts_f = ops.mlp_feature_fwd(packed, x_tiles, True)
+    rgbs, acts_u = ops.mlp_fusion_fwd(packed, h3, b, nv, True)
+    d_y = torch.randn(b * rows, 4, generator=torch.Generator().manual_seed(9)).to(cuda)
+    s = 1.0 / nv
+    # ---- block by block
+    grad_a = torch.zeros_like(dev_flat)
+    g_a = ops.mlp_readout_bwd(dev_flat, d_y, acts_u, 4, 3, grad_a)
+    g_start = g_a.clone()
+    grad_ro = grad_a.clone()
+    for blk in (5, 4, 3):
+        ops.mlp_block_bwd(packed, blk, acts_u, 4, blk - 3, g_a, grad_a)
+    gf_a = ops.mlp_block_bwd(packed, 2, acts_f, 3, 2, g_a, grad_a, views=nv, scale=s, b=b) if nv > 1 else \
+        ops.mlp_block_bwd(packed, 2, acts_f, 3, 2, g_a.clone(), grad_a)
+    for blk in (1, 0):
+        ops.mlp_block_bwd(packed, blk, acts_f, 3, blk, gf_a, grad_a, scale=s)
+    ops.mlp_l0_wgrad(x_tiles, gf_a, grad_a, s)
+    dx_a = ops.mlp_l0_dgrad(packed, gf_a, s)
+    # ---- chained
+    ws = ops.stage_bwd_workspace(cuda)
+    ws.fill_(0xA5)                                  # the rings and counters start from garbage: the call resets what it needs
+    grad_b = grad_ro.clone()
+    g_b = g_start.clone()
+    out = ops.mlp_stage_bwd(packed, 1, acts_u, 4, g_b, grad_b, ws)
+    assert out.data_ptr() == g_b.data_ptr() and torch.equal(g_b, g_a)
+    dx_b = ops.mlp_stage_bwd(packed, 0, acts_f, 3, g_b, grad_b, ws, views=nv, b=b, scale=s, x_tiles=x_tiles,
+                             want_dx=True, first_dense=True)
+    assert torch.equal(dx_b, dx_a)
+    assert rel_err(grad_b, grad_a) < 2e-5, rel_err(grad_b, grad_a)
+    # ---- per-view stage without the first Dense (gradient w.r.t. the stage input is stored), and wgrad only
+    grad_c = grad_ro.clone()
+    g_c = g_start.clone()
+    ops.mlp_stage_bwd(packed, 1, acts_u, 4, g_c, grad_c, ws)
+    gf_c = ops.mlp_stage_bwd(packed, 0, acts_f, 3, g_c, grad_c, ws, views=nv, b=b, scale=s)
+    assert torch.equal(gf_c, gf_a)
+    grad_d = grad_ro.clone()
+    g_d = g_start.clone()
+    ops.mlp_stage_bwd(packed, 1, acts_u, 4, g_d, grad_d, ws)
+    none = ops.mlp_stage_bwd(packed, 0, acts_f, 3, g_d, grad_d, ws, views=nv, b=b, scale=s, x_tiles=x_tiles,
+                             want_dx=False, first_dense=True)
+    assert none is None and rel_err(grad_d, grad_a) < 2e-5

@@ -11,7 +11,7 @@ from ctypes import c_char_p, c_double, c_float, c_int32, c_int64, c_size_t, c_vo
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), 'lib', 'libclipnerf_b200.so')
 
-ABI_VERSION = 6
+ABI_VERSION = 7
 TILE_ROWS = 128
 SLAB_BYTES = 16384
 ACT_TILE_BYTES = 32768
@@ -57,6 +57,8 @@ PROTOTYPES = {
     'cn_tile_add_rows': [_P, _P, c_int64, c_int32, _P],
     'cn_mlp_readout_bwd': [_P, _P, _P, c_int32, c_int32, c_int64, _P, _P, _P],
     'cn_mlp_block_bwd': [_P, c_int32, _P, c_int32, c_int32, c_int64, _P, c_int32, c_int64, _P, c_float, _P, _P],
+    'cn_mlp_stage_bwd_ws_bytes': [],
+    'cn_mlp_stage_bwd': [_P, c_int32, _P, c_int32, c_int64, _P, c_int32, c_int64, _P, _P, _P, c_float, _P, _P, c_size_t, _P],
     'cn_mlp_mean_bwd': [_P, c_int32, c_int32, c_int64, _P, _P],
     'cn_mlp_l0_dgrad': [_P, _P, c_int64, _P, c_float, _P],
     'cn_mlp_l0_wgrad': [_P, _P, c_int64, c_float, _P, _P],
@@ -66,7 +68,7 @@ PROTOTYPES = {
                       c_int32, c_int32, _P, _P],
     'cn_probe_tile_reduce': [_P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P],
 }
-_RESTYPES = {'cn_last_error': c_char_p, 'cn_gather_ws_bytes': c_size_t}
+_RESTYPES = {'cn_last_error': c_char_p, 'cn_gather_ws_bytes': c_size_t, 'cn_mlp_stage_bwd_ws_bytes': c_size_t}
 
 _lib = None
 
@@ -95,7 +97,7 @@ class CnError(RuntimeError):
 
 # kernels launched by each entry point (for launch accounting in bench.py)
 KERNELS_PER_CALL = {name: 1 for name in PROTOTYPES}
-KERNELS_PER_CALL.update({'cn_abi_version': 0, 'cn_last_error': 0, 'cn_gather_ws_bytes': 0,
+KERNELS_PER_CALL.update({'cn_abi_version': 0, 'cn_last_error': 0, 'cn_gather_ws_bytes': 0, 'cn_mlp_stage_bwd_ws_bytes': 0,
                          'cn_project_bin': 4, 'cn_project_gather_fwd': 5, 'cn_feature_grad': 2,
                          'cn_project_gather_bwd_rays': 2, 'cn_quantize_render': 2, 'cn_adam_step': 2})
 

@@ -335,6 +335,36 @@ def mlp_block_bwd(packed, blk: int, acts, act_stride: int, act_index: int, gy_ti
     return gh_tiles
 
 
+def stage_bwd_workspace(device) -> torch.Tensor:
+    """scratch of cn_mlp_stage_bwd (tile rings + counters, ~19 MiB: L2-resident)"""
+    return _bytes(int(_abi.load().cn_mlp_stage_bwd_ws_bytes()), device)
+
+
+def mlp_stage_bwd(packed, stage: int, acts, act_stride: int, gy_tiles, grad, ws=None, views: int = 1, b: int = 1,
+                  scale: float = 1.0, x_tiles=None, want_dx: bool = False, first_dense: bool = False):
+    """backward of a whole MLP stage in one launch (stage 1: fusion blocks; stage 0: per-view blocks and, with
+    ``first_dense``, the first Dense's wgrad (+ dgrad when ``want_dx``)).  Returns the gradient w.r.t. the stage
+    input (tile images; in place over ``gy_tiles`` when ``views == 1``) or, with ``first_dense``, dX (or None)."""
+    nt = gy_tiles.numel() // ACT_TILE_BYTES
+    tpv = 0
+    if views > 1:
+        assert nt % b == 0
+        tpv = nt // b
+        nt = nt * views
+    if ws is None:
+        ws = stage_bwd_workspace(gy_tiles.device)
+    gh = dx = None
+    if first_dense:
+        assert stage == 0 and x_tiles is not None
+        if want_dx:
+            dx = _bytes(nt * X_TILE_BYTES, gy_tiles.device)
+    else:
+        gh = gy_tiles if views == 1 else _bytes(nt * ACT_TILE_BYTES, gy_tiles.device)
+    call('cn_mlp_stage_bwd', _ptr(packed), stage, _ptr(acts), act_stride, nt, _ptr(gy_tiles), views, tpv, _ptr(gh),
+         _ptr(x_tiles) if first_dense else None, _ptr(dx), float(scale), _ptr(grad), _ptr(ws), ws.numel(), _stream())
+    return dx if first_dense else gh
+
+
 def mlp_mean_bwd(gm_tiles, b: int, nv: int):
     nt = gm_tiles.numel() // ACT_TILE_BYTES
     tpv = nt // b

@@ -40,6 +40,15 @@ def _pass_bwd(P: _Pass, params, grad, scene: ops.Scene, ray_o, ray_d, d_rgb, d_d
     passes is taken from the two dX images in one sweep afterwards (ops.feature_grad)."""
     d_y, dz = ops.composite_bwd(P.z, P.rgbs.view(*P.z.shape, 4), d_rgb, d_depth, d_weights, need_dz)
     g = ops.mlp_readout_bwd(params, d_y, P.acts_u, ops.FUSION_ACTS, 3, grad)
+    if CHAINED_STAGES:
+        # one launch per stage: role-specialised CTAs pass the gradient stream through L2-resident tile rings
+        ws = ops.stage_bwd_workspace(g.device)
+        ops.mlp_stage_bwd(P.packed, 1, P.acts_u, ops.FUSION_ACTS, g, grad, ws)
+        dx = ops.mlp_stage_bwd(P.packed, 0, P.acts_f, ops.FEATURE_ACTS, g, grad, ws, views=scene.nv, b=scene.b,
+                               scale=1.0 / scene.nv, x_tiles=P.x, want_dx=want_dx or need_dz, first_dense=True)
+        if need_dz:
+            ops.project_gather_bwd(scene, ray_o, ray_d, P.z, dx, None, dz, P.ws)
+        return dz, dx
     for blk in (5, 4, 3):
         ops.mlp_block_bwd(P.packed, blk, P.acts_u, ops.FUSION_ACTS, blk - 3, g, grad)
     # mean over views: every per-view tile reads the fusion-stage gradient tile itself; the factor 1/nv is
@@ -57,6 +66,9 @@ def _pass_bwd(P: _Pass, params, grad, scene: ops.Scene, ray_o, ray_d, d_rgb, d_d
             ops.project_gather_bwd(scene, ray_o, ray_d, P.z, dx, None, dz, P.ws)
     return dz, dx
 
+
+# True: the MLP backward of a pass is two launches (cn_mlp_stage_bwd per stage); False: one launch per block / Dense
+CHAINED_STAGES = True
 
 # Set by RenderTrainer for the duration of a backward on > 1 rank: callable([2, NET_PARAMS] gradient buffer) -> a
 # work handle with .wait() (torch.distributed all_reduce(async_op=True)); None = no collective inside the backward.
