@@ -162,6 +162,28 @@ def test_render_inference_matches_training_forward(cuda):
         assert torch.equal(a, b_.detach())
 
 
+def test_chained_stage_backward_gives_the_per_block_gradients(cuda, monkeypatch):
+    """render.CHAINED_STAGES: the two-launch backward of a pass (cn_mlp_stage_bwd) and the launch-per-block one walk
+    the same bf16 g stream; the outputs are bit-identical and the gradients differ by the fp32 atomic order only"""
+    from clipnerf_b200 import render
+    from oracle import nerf_oracle as O
+    sc = O.synthetic_scene(13, 1, 3, 160, 48, 64)
+    named = O.init_params(7, bias_std=0.02)
+    tgt = sc['target'].to(cuda)
+    res = []
+    for chained in (False, True):
+        monkeypatch.setattr(render, 'CHAINED_STAGES', chained)
+        out, pc, pf, fd = _run(cuda, sc, named)
+        (torch.mean((out[0] - tgt) ** 2) + torch.mean((out[2] - tgt) ** 2)).backward()
+        res.append((out, pc.grad.clone(), pf.grad.clone(), fd.grad.clone()))
+    (o0, c0, f0, m0), (o1, c1, f1, m1) = res
+    for a, b_ in zip(o0, o1):
+        assert torch.equal(a, b_)
+    errs = (rel_err(c1, c0), rel_err(f1, f0), rel_err(m1, m0))
+    print('chained vs per-block gradients', errs)
+    assert errs[0] < 1e-3 and errs[1] < 1e-3 and errs[2] < 3e-3, errs
+
+
 def test_ray_chunked_training_step_matches_unchunked(cuda):
     """RenderTrainer.loss_and_backward(max_rays=...): gradients accumulated over ray chunks equal the one-shot
     gradients (rays are independent; the loss is normalised by the full batch)."""

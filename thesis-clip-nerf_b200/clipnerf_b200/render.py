@@ -9,6 +9,7 @@ fine samples through the inverse-CDF sampler into the coarse net (no stop_gradie
 Random draws are explicit inputs (``u_strat``, ``u_pdf``)."""
 from __future__ import annotations
 
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -67,8 +68,11 @@ def _pass_bwd(P: _Pass, params, grad, scene: ops.Scene, ray_o, ray_d, d_rgb, d_d
     return dz, dx
 
 
-# True: the MLP backward of a pass is two launches (cn_mlp_stage_bwd per stage); False: one launch per block / Dense
-CHAINED_STAGES = True
+# True: the MLP backward of a pass is two launches (cn_mlp_stage_bwd per stage, role-specialised CTAs chained through
+# L2 tile rings: 45 % less DRAM traffic); False: one launch per block / Dense, every SM on every tile.  Measured on the
+# cfg2 step the two are within 2 % (profiles/README.md, round 2), the per-block launches ahead: the block backward is
+# bound by shared-memory bandwidth inside the SM, not by HBM, so the default stays False.
+CHAINED_STAGES = os.environ.get('CN_CHAINED_STAGES', '0') == '1'
 
 # Set by RenderTrainer for the duration of a backward on > 1 rank: callable([2, NET_PARAMS] gradient buffer) -> a
 # work handle with .wait() (torch.distributed all_reduce(async_op=True)); None = no collective inside the backward.

@@ -38,7 +38,7 @@
 namespace cn {
 
 // ---------------------------------------------------------------- tile links between roles of one launch
-constexpr int kRingSlots = 4;
+constexpr int kRingSlots = 6;
 struct TileLink {
   uint8_t *ring;       // [n_prod][kRingSlots][CN_ACT_TILE_BYTES]; nullptr = no link (plain global buffer)
   uint32_t *filled;    // [n_prod][kRingSlots] times the slot has been filled (release store by the producer)
@@ -54,9 +54,17 @@ __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t *p) {
 __device__ __forceinline__ void red_release_gpu_add(uint32_t *p, uint32_t v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void red_relaxed_gpu_add(uint32_t *p, uint32_t v) {
+  asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// optional per-CTA accounting of the time one thread spends waiting on tile links (tools/trace_stage_bwd.py)
+struct LinkStats {
+  long long wait_filled = 0, wait_released = 0;
+};
 // bounded spin (a protocol bug becomes a trap, not a hung GPU)
-__device__ __forceinline__ void spin_until_ge(const uint32_t *p, uint32_t want) {
+__device__ __forceinline__ void spin_until_ge(const uint32_t *p, uint32_t want, long long *acc = nullptr) {
   if (ld_acquire_gpu(p) >= want) return;
+  const long long c0 = acc ? clock64() : 0;
   const uint64_t t0 = globaltimer_ns();
   while (ld_acquire_gpu(p) < want) {
     __nanosleep(64);
@@ -66,6 +74,7 @@ __device__ __forceinline__ void spin_until_ge(const uint32_t *p, uint32_t want) 
       __trap();
     }
   }
+  if (acc) *acc += clock64() - c0;
 }
 // generic-proxy <-> async-proxy ordering for global memory touched by both bulk copies and flags
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
@@ -81,20 +90,21 @@ __device__ __forceinline__ LinkSlot link_slot(const TileLink &l, int64_t tile) {
   return s;
 }
 // consumer side, before the bulk load of `tile`: wait until its producer has filled the slot
-__device__ __forceinline__ const uint8_t *link_wait_filled(const TileLink &l, int64_t tile) {
+__device__ __forceinline__ const uint8_t *link_wait_filled(const TileLink &l, int64_t tile, LinkStats *st = nullptr) {
   const LinkSlot s = link_slot(l, tile);
-  spin_until_ge(l.filled + s.idx, s.use + 1);
+  spin_until_ge(l.filled + s.idx, s.use + 1, st ? &st->wait_filled : nullptr);
   fence_proxy_async_all();
   return l.ring + s.idx * (int64_t)CN_ACT_TILE_BYTES;
 }
-// consumer side, once the bulk load of `tile` has landed in shared memory
+// consumer side, once the bulk load of `tile` has landed in shared memory (observed through its mbarrier: the read
+// of the slot is complete, nothing this thread wrote has to become visible -> a relaxed reduction, no fence)
 __device__ __forceinline__ void link_release(const TileLink &l, int64_t tile) {
-  red_release_gpu_add(l.released + link_slot(l, tile).idx, 1u);
+  red_relaxed_gpu_add(l.released + link_slot(l, tile).idx, 1u);
 }
 // producer side, before the bulk store of `tile`: wait until every consumer of the slot's previous tile has read it
-__device__ __forceinline__ uint8_t *link_wait_released(const TileLink &l, int64_t tile) {
+__device__ __forceinline__ uint8_t *link_wait_released(const TileLink &l, int64_t tile, LinkStats *st = nullptr) {
   const LinkSlot s = link_slot(l, tile);
-  spin_until_ge(l.released + s.idx, s.use * (uint32_t)l.n_cons);
+  spin_until_ge(l.released + s.idx, s.use * (uint32_t)l.n_cons, st ? &st->wait_released : nullptr);
   return l.ring + s.idx * (int64_t)CN_ACT_TILE_BYTES;
 }
 // producer side, after the bulk store of `tile` has COMPLETED (cp.async.bulk.wait_group 0)
@@ -178,6 +188,7 @@ struct BlockBwdArgs {
   float scale;
   float *g_wa, *g_ba, *g_wb, *g_bb;
   TileLink in, out;                   // g_y from / g_h to another role of the launch
+  long long *stats;                   // nullable: [3] cycles in the role, waiting for the upstream / downstream role
 };
 
 // role arguments of block `blk` (0..5) of a packed net; g_y source / g_h destination are left to the caller
@@ -245,12 +256,14 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
         bulk_g2s(s_base + kBwSmemA1 + b * CN_ACT_TILE_BYTES, acts + tile * act_stride_bytes, CN_ACT_TILE_BYTES,
                  smem_u32(&bars.full_a1[b]));
       };
+      LinkStats lst;
+      const long long c_start = clock64();
       auto load_gy = [&](int64_t it) {
         const int64_t tile = cta + it * n_cta;
         const uint32_t b = (uint32_t)it & 1u;
         const uint8_t *src;
         if (A.in.ring) {
-          src = link_wait_filled(A.in, tile);        // the upstream role has produced this tile (it stays in L2)
+          src = link_wait_filled(A.in, tile, &lst);  // the upstream role has produced this tile (it stays in L2)
         } else {
           // mean over views folded in: every view tile of a (scene, row tile) reads the same fusion-stage g tile
           const int64_t st = gy_views > 1 ? (tile / (gy_views * gy_tpv)) * gy_tpv + tile % gy_tpv : tile;
@@ -269,22 +282,28 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
         // E2 of this tile has replaced g_y by g_h in place: stream it out, then refill the buffer
         mbar_wait(smem_u32(&bars.gy_staged[b]), ph2);
         CN_TRACE_AT(it, 24);
-        uint8_t *dst = A.out.ring ? link_wait_released(A.out, tile) : A.gh_tiles + tile * (int64_t)CN_ACT_TILE_BYTES;
+        if (A.out.ring && it > 0) {
+          bulk_wait0();                               // the previous tile's store has completed (a tile time ago):
+          link_publish(A.out, tile - n_cta);          // hand it to the next role
+        }
+        uint8_t *dst = A.out.ring ? link_wait_released(A.out, tile, &lst) : A.gh_tiles + tile * (int64_t)CN_ACT_TILE_BYTES;
         bulk_s2g(dst, s_base + kBwSmemGy + b * CN_ACT_TILE_BYTES, CN_ACT_TILE_BYTES);
         bulk_commit();
-        if (A.out.ring) {
-          bulk_wait0();                               // the tile is in global memory (L2): hand it to the next role
-          link_publish(A.out, tile);
-        }
         if (it + 2 < n_mine) {
-          if (!A.out.ring) bulk_wait_read0();
           mbar_wait(smem_u32(&bars.free_a1[b]), ph2);
           CN_TRACE_AT(it, 26);
           load_a1(it + 2);
+          bulk_wait_read0();                          // the store has read the buffer: refill it
           load_gy(it + 2);                            // (may wait for the upstream role: last)
         }
       }
       bulk_wait0();
+      if (A.out.ring && n_mine > 0) link_publish(A.out, cta + (n_mine - 1) * (int64_t)n_cta);
+      if (A.stats) {
+        A.stats[0] = clock64() - c_start;
+        A.stats[1] = lst.wait_filled;
+        A.stats[2] = lst.wait_released;
+      }
     }
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
@@ -328,7 +347,6 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
         const bool has_next = it + 1 < n_mine;
         const uint32_t nb = b ^ 1u, nph2 = ((uint32_t)(it + 1) >> 1) & 1u;
         mbar_wait(smem_u32(&bars.full_gy[b]), ph2);
-        if (A.in.ring) link_release(A.in, cta + it * n_cta);      // g_y is in shared memory: its ring slot is free
         mbar_wait(smem_u32(&bars.acc1_free), par ^ 1u);          // E2 of the previous tile has drained acc1
         tc_fence_after();
         CN_TRACE_AT(it, 0);
@@ -385,6 +403,12 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
       const uint8_t *const a1buf = smem + kBwSmemA1 + b * CN_ACT_TILE_BYTES;
       uint8_t *const gybuf = smem + kBwSmemGy + b * CN_ACT_TILE_BYTES;
       uint32_t a2w[16];                               // A2 of this thread: ReLU mask source of E1
+      if (A.in.ring && threadIdx.x == 64) {
+        // g_y of this tile is in shared memory (it landed long before t_ready): its ring slot is free.  Done by an
+        // epilogue thread: the MMA-issuing thread is the critical one
+        mbar_wait(smem_u32(&bars.full_gy[b]), ((uint32_t)it >> 1) & 1u);
+        link_release(A.in, cta + it * (int64_t)n_cta);
+      }
       // ---- E0: A2 = relu(t + ba) -> bf16 operand tile
       mbar_wait(smem_u32(&bars.t_ready), par);
       mbar_wait(smem_u32(&bars.a2buf_free), par ^ 1u);  // WA of the previous tile is done with g_t

@@ -16,11 +16,11 @@ namespace cn {
 // ============================================================================================
 // dgrad
 // ============================================================================================
-constexpr int kDgThreads = 64 + 256;  // producer, MMA, 8 epilogue warps (4 lane quadrants x 2 column halves)
+constexpr int kDgThreads = 64 + 512;  // producer, MMA, 2 epilogue groups of 8 warps (4 lane quadrants x 2 column halves)
 constexpr uint32_t kDgSmemW = 0;                          // 3 x 32 KiB, resident
 constexpr uint32_t kDgSmemG = 3 * CN_ACT_TILE_BYTES;      // 2 x 32 KiB (double buffer)
-constexpr uint32_t kDgSmemOut = 5 * CN_ACT_TILE_BYTES;    // 32 KiB staging for the bulk store
-constexpr uint32_t kDgSmemBytes = 6 * CN_ACT_TILE_BYTES + 1024;
+constexpr uint32_t kDgSmemOut = 5 * CN_ACT_TILE_BYTES;    // 2 x 32 KiB staging for the bulk stores
+constexpr uint32_t kDgSmemBytes = 7 * CN_ACT_TILE_BYTES + 1024;
 
 struct DgBars {
   uint64_t w_full;
@@ -105,27 +105,29 @@ __device__ __forceinline__ void l0_dgrad_role(const L0DgradArgs &A, DgBars &bars
       }
     }
   } else {
+    // Two epilogue groups of 8 warps take the accumulators alternately (unit u -> group u % 2, staging buffer u % 2):
+    // a single epilogue is a latency chain (tcgen05.ld -> convert -> st.shared -> barrier -> bulk store, ~1400 cycles
+    // with 8 warps) three times longer than the 8 MMAs that feed it, two of them in flight hide half of it
     const uint32_t quad = warp & 3u;
-    const uint32_t half = (warp - 2) >> 2;
+    const uint32_t grp = (warp - 2) >> 3;                     // epilogue group 0 / 1
+    const uint32_t half = ((warp - 2) >> 2) & 1u;
     const uint32_t row = quad * 32u + lane;
     const uint32_t lane_off = (quad * 32u) << 16;
-    const bool leader = (warp == 2 && lane == 0);
-    uint8_t *out = smem + kDgSmemOut;
+    const bool leader = (((warp - 2) & 7u) == 0 && lane == 0);
+    uint8_t *out = smem + kDgSmemOut + grp * CN_ACT_TILE_BYTES;
     uint32_t unit = 0;
-    bool pending = false;
     for (int64_t tile = cta; tile < n_tiles; tile += n_cta) {
       for (int c = 0; c < 3; ++c, ++unit) {
+        if ((unit & 1u) != grp) continue;
         const uint32_t slot = unit & 3u;
         mbar_wait(smem_u32(&bars.acc_ready[slot]), (unit >> 2) & 1u);
         tc_fence_after();
         uint32_t r[64];
         tmem_ld32(tmem + lane_off + slot * 128 + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
         tmem_ld32(tmem + lane_off + slot * 128 + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
-        if (pending) {
-          if (leader) bulk_wait_read0();
-          named_bar_sync(1, 256);
-          pending = false;
-        }
+        // this group's previous store (two units ago) has been read out of the staging buffer
+        if (leader) bulk_wait_read0();
+        named_bar_sync(1 + grp, 256);
         tmem_wait_ld();
         tc_fence_before();
         __syncwarp();
@@ -138,13 +140,12 @@ __device__ __forceinline__ void l0_dgrad_role(const L0DgradArgs &A, DgBars &bars
               cvt_bf16x2(__uint_as_float(r[q * 8 + 4]) * scale, __uint_as_float(r[q * 8 + 5]) * scale),
               cvt_bf16x2(__uint_as_float(r[q * 8 + 6]) * scale, __uint_as_float(r[q * 8 + 7]) * scale));
         fence_proxy_async_smem();
-        named_bar_sync(1, 256);
+        named_bar_sync(1 + grp, 256);
         if (leader) {
-          bulk_s2g(dx_tiles + tile * (int64_t)CN_X_TILE_BYTES + c * CN_ACT_TILE_BYTES, s_base + kDgSmemOut,
-                   CN_ACT_TILE_BYTES);
+          bulk_s2g(dx_tiles + tile * (int64_t)CN_X_TILE_BYTES + c * CN_ACT_TILE_BYTES,
+                   s_base + kDgSmemOut + grp * CN_ACT_TILE_BYTES, CN_ACT_TILE_BYTES);
           bulk_commit();
         }
-        pending = true;
       }
     }
     if (leader) bulk_wait0();
@@ -155,7 +156,7 @@ __device__ __forceinline__ void l0_dgrad_role(const L0DgradArgs &A, DgBars &bars
 // wgrad
 // ============================================================================================
 constexpr int kWgThreads = 192;
-constexpr int kWgSlots = 12;  // 16 KiB slabs; a tile = 2 (g0) + 6 (X) slabs, pairs never wrap
+constexpr int kWgSlots = 14;  // 16 KiB slabs in pairs; a tile = 1 (g0) + 3 (X) pairs: 1.75 tiles in flight
 constexpr uint32_t kWgSmemBytes = kWgSlots * CN_SLAB_BYTES + 1024;
 
 struct WgBars {
@@ -204,9 +205,8 @@ __device__ __forceinline__ void l0_wgrad_role(const L0WgradArgs &A, WgBars &bars
         ++pc;
       };
       for (int64_t tile = cta; tile < n_tiles; tile += n_cta) {
-        // X first: its copies do not depend on the upstream role
-        for (int c = 0; c < 3; ++c) load_pair(x_tiles + tile * (int64_t)CN_X_TILE_BYTES + c * CN_ACT_TILE_BYTES);
         load_pair(A.in.ring ? link_wait_filled(A.in, tile) : A.g0_tiles + tile * (int64_t)CN_ACT_TILE_BYTES);
+        for (int c = 0; c < 3; ++c) load_pair(x_tiles + tile * (int64_t)CN_X_TILE_BYTES + c * CN_ACT_TILE_BYTES);
       }
     }
   } else if (warp == 1) {
@@ -221,12 +221,10 @@ __device__ __forceinline__ void l0_wgrad_role(const L0WgradArgs &A, WgBars &bars
         return ps;
       };
       for (int64_t tile = cta; tile < n_tiles; tile += n_cta) {
-        uint32_t pxs[3];
-        for (int c = 0; c < 3; ++c) pxs[c] = next_pair();
         const uint32_t pg = next_pair();
         if (A.in.ring) link_release(A.in, tile);              // g0 is in shared memory: its ring slot is free
         for (int c = 0; c < 3; ++c) {
-          const uint32_t px = pxs[c];
+          const uint32_t px = next_pair();                    // the chunk's MMAs start as soon as ITS X pair has landed
           tc_fence_after();
 #pragma unroll
           for (int j = 0; j < 8; ++j)
@@ -254,7 +252,7 @@ __device__ __forceinline__ void l0_wgrad_role(const L0WgradArgs &A, WgBars &bars
         for (int p = 0; p < 4; ++p, ++cc) {
           const uint32_t ps = cc % kPairs;
           mbar_wait(smem_u32(&bars.full[ps]), (cc / kPairs) & 1u);
-          if (p == 3) {                                  // the g0 pair comes last in a tile's four pairs
+          if (p == 0) {                                  // the g0 pair comes first in a tile's four pairs
             const uint8_t *g = smem + ps * CN_ACT_TILE_BYTES + within;
 #pragma unroll 8
             for (uint32_t r = quad * 32u; r < quad * 32u + 32u; ++r) {

@@ -39,6 +39,7 @@ struct StageArgs {
   L0WgradArgs wg;
   int n_blk_cta;            // CTAs per block role
   int n_dg_cta, n_wg_cta;   // 0 = role absent
+  long long *stats;         // nullable: [grid][4] (role, cycles, cycles waiting upstream, cycles waiting downstream)
 };
 
 union StageBars {
@@ -83,9 +84,20 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_stage_bwd_kernel(const __g
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = tmem_slot;
-  if (role < 3) block_bwd_role(S.blk[role], bars.blk, s_ba, smem, tmem, cta, S.n_blk_cta);
-  else if (role == 3) l0_dgrad_role(S.dg, bars.dg, smem, tmem, cta, S.n_dg_cta);
-  else l0_wgrad_role(S.wg, bars.wg, smem, tmem, cta, S.n_wg_cta);
+  const long long c0 = clock64();
+  if (role < 3) {
+    BlockBwdArgs A = S.blk[role];
+    A.stats = S.stats ? S.stats + (size_t)bid * 4 + 1 : nullptr;
+    block_bwd_role(A, bars.blk, s_ba, smem, tmem, cta, S.n_blk_cta);
+  } else if (role == 3) {
+    l0_dgrad_role(S.dg, bars.dg, smem, tmem, cta, S.n_dg_cta);
+  } else {
+    l0_wgrad_role(S.wg, bars.wg, smem, tmem, cta, S.n_wg_cta);
+  }
+  if (S.stats && threadIdx.x == 0) {
+    S.stats[(size_t)bid * 4] = role;
+    if (role >= 3) S.stats[(size_t)bid * 4 + 1] = clock64() - c0;
+  }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem, 512);
@@ -139,7 +151,15 @@ static StagePlan stage_plan(int64_t n_tiles, bool with_dgrad, bool with_wgrad) {
   return p;
 }
 
+// diagnostics (tools/trace_stage_bwd.py): device buffer [<= 160 CTAs][4] long long that the next launches fill
+static long long *g_stage_stats = nullptr;
+
 }  // namespace cn
+
+extern "C" int cn_debug_stage_stats(long long *device_buffer) {
+  cn::g_stage_stats = device_buffer;
+  return 0;
+}
 
 extern "C" size_t cn_mlp_stage_bwd_ws_bytes(void) {
   // an upper bound independent of the tile count and of which roles run (the split only shrinks n_blk)
@@ -224,6 +244,7 @@ extern "C" int cn_mlp_stage_bwd(const void *packed, int32_t stage, const void *a
     S.wg.scale = scale;
     S.wg.in = link[2];
   }
+  S.stats = g_stage_stats;
   const unsigned grid = (unsigned)(3 * S.n_blk_cta + S.n_dg_cta + S.n_wg_cta);
   mlp_stage_bwd_kernel<<<grid, kBwdThreads, kBwdSmemBytes, st>>>(S);
   return check_launch("cn_mlp_stage_bwd");
