@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define CN_ABI_VERSION 7
+#define CN_ABI_VERSION 8
 #define CN_TILE_ROWS 128
 #define CN_HIDDEN 128
 #define CN_FEAT_C 256          /* combined_features channels (model_v0.py:60)            */
@@ -64,10 +64,17 @@ const char *cn_last_error(void);
  * (src/lib/data_generator/mvnerf.py:28-43) plus combined_features (model_v0.py:60). */
 typedef struct CnScene {
   const float *images;     /* [b, nv, H, W, 3]  in [0,1]                  */
-  const float *features;   /* [b, nv, H, W, 256]                          */
+  const float *features;   /* [b, nv, H / feat_up, W / feat_up, 256]      */
   const float *intrinsics; /* [b, nv, 4, 4]                               */
   const float *extr_inv;   /* [b, nv, 4, 4]  world -> camera              */
   int32_t b, nv, H, W;
+  /* 1: `features` is combined_features itself (model_v0.py:60).
+   * 2: `features` is the INPUT of the encoder's final UpSampling2D(2, 'bilinear') (layers.py:589,659;
+   *    legacy_layers.py:190; model_without.py:76): every gather evaluates
+   *    interpolate_bilinear(UpSampling2D(x)) as the composed <= 3x3 stencil on the [H/2, W/2] map (fixed
+   *    0.25 / 0.75 weights, half-pixel centres, edge clamp) and every d_features is the gradient w.r.t. that
+   *    low-resolution map; H and W must be even.  Pixel coordinates, images and dz are unchanged.          */
+  int32_t feat_up;
 } CnScene;
 
 /* ---- sampling ------------------------------------------------------------------ */
@@ -150,7 +157,9 @@ int cn_project_gather_bwd_rays(const CnScene *scene, const float *ray_o, const f
  * d_features [b,nv,H,W,256] sums the rows of its four neighbouring cells of every set and is
  * written exactly once (accumulate = 0: the map needs no zero fill; accumulate = 1: +=).
  * Host arrays of length n_sets (<= 4): nr, S, ws, ws_bytes, dx_tiles; every workspace must have
- * been filled by cn_project_gather_fwd / cn_project_bin for this scene.                       */
+ * been filled by cn_project_gather_fwd / cn_project_bin for this scene.
+ * feat_up == 2 (n_sets <= 3): the rows of one low-resolution cell row are summed once into a sliding 3x3
+ * register window and added to d_features [b,nv,H/2,W/2,256] with red.global (accumulate = 0 zero-fills first). */
 int cn_feature_grad(const CnScene *scene, int32_t n_sets, const int32_t *nr_host, const int32_t *S_host,
                     void *const *ws_host, const size_t *ws_bytes_host, const void *const *dx_tiles_host,
                     float *d_features, int32_t accumulate, void *stream);

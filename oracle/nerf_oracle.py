@@ -228,6 +228,103 @@ def interpolate_bilinear(grid: Tensor, query_points: Tensor, indexing: str = 'xy
     return ay * (bottom - top) + top
 
 
+def upsample2x_bilinear(x: Tensor) -> Tensor:
+    """``tf.keras.layers.UpSampling2D(size=(2, 2), interpolation='bilinear')`` -- the last layer of every
+    CombineCLIPVisual variant (``layers.py:547,589``, ``617,659``; ``legacy_layers.py:190``; ``model_without.py:28,76``).
+
+    Keras forwards to ``tf.image.resize(..., method='bilinear')``; TensorFlow (third-party, absent here; the
+    reference pins tensorflow 2.x in its environment) computes it with half-pixel centres and no antialiasing
+    (``ResizeBilinear`` kernel, ``half_pixel_centers=True``).  Per axis, for output index o of an input of
+    ``size`` elements:
+
+        in    = (o + 0.5) * 0.5 - 0.5
+        lower = max(floor(in), 0),  upper = min(ceil(in), size - 1),  lerp = in - floor(in)
+
+    and per pixel ``top = TL + (TR - TL) * x_lerp``, ``bottom = BL + (BR - BL) * x_lerp``,
+    ``out = top + (bottom - top) * y_lerp``.  x [..., H, W, C] -> [..., 2H, 2W, C].
+    ``tests/test_oracle.py`` pins this against ``torch.nn.functional.interpolate(scale_factor=2, mode='bilinear',
+    align_corners=False)``, an independent implementation of the same convention.
+    """
+    H, W = x.shape[-3], x.shape[-2]
+
+    def axis(size):
+        o = torch.arange(2 * size, dtype=torch.float64)
+        src = (o + 0.5) * 0.5 - 0.5
+        fl = torch.floor(src)
+        lower = torch.clamp(fl, min=0).to(torch.int64)
+        upper = torch.clamp(torch.ceil(src), max=size - 1).to(torch.int64)
+        return lower, upper, (src - fl).to(x.dtype)                 # lerp is 0.25 or 0.75, exact in any float type
+
+    ly, uy, wy = axis(H)
+    lx, ux, wx = axis(W)
+    wx = wx[:, None]
+    wy = wy[:, None, None]
+    rows_l, rows_u = x.index_select(-3, ly), x.index_select(-3, uy)
+
+    def x_pass(r):
+        left, right = r.index_select(-2, lx), r.index_select(-2, ux)
+        return left + (right - left) * wx
+
+    top, bottom = x_pass(rows_l), x_pass(rows_u)
+    return top + (bottom - top) * wy
+
+
+def lowres_stencil(f0: Tensor, alpha: Tensor, size_lr: int):
+    """One axis of ``interpolate_bilinear(upsample2x_bilinear(x))`` written as taps on the LOW-resolution axis.
+
+    ``f0`` (int64) / ``alpha`` are the clamped floor and weight of ``interpolate_bilinear`` on the 2 * size_lr axis
+    (f0 in [0, 2 size_lr - 2]).  With k = f0 >> 1 the two upsampled texels U[f0], U[f0+1] are
+
+        f0 even:  U[2k]   = 0.25 x[k-1] + 0.75 x[k],   U[2k+1] = 0.75 x[k] + 0.25 x[k+1]
+        f0 odd :  U[2k+1] = 0.75 x[k] + 0.25 x[k+1],   U[2k+2] = 0.25 x[k] + 0.75 x[k+1]
+
+    (indices clamped to [0, size_lr - 1]: the resize clamps ``lower`` / ``upper`` the same way), so
+    (1 - a) U[f0] + a U[f0+1] = sum_j w_j x[clamp(k + j - 1)] with
+
+        even: w = (0.25 (1 - a), 0.75, 0.25 a)        odd: w = (0, 0.75 - 0.5 a, 0.25 + 0.5 a)
+
+    Returns (idx [..., 3] int64, w [..., 3], dw/da [..., 3]).
+    """
+    k = f0 >> 1
+    odd = (f0 & 1).to(alpha.dtype)
+    even = 1.0 - odd
+    w = torch.stack([even * 0.25 * (1.0 - alpha), even * 0.75 + odd * (0.75 - 0.5 * alpha),
+                     even * 0.25 * alpha + odd * (0.25 + 0.5 * alpha)], dim=-1)
+    dw = torch.stack([even * -0.25, odd * -0.5, even * 0.25 + odd * 0.5], dim=-1).expand_as(w)
+    idx = torch.stack([k - 1, k, k + 1], dim=-1).clamp(0, size_lr - 1)
+    return idx, w, dw
+
+
+def interpolate_bilinear_lowres(grid_lr: Tensor, query_points: Tensor, indexing: str = 'xy') -> Tensor:
+    """``interpolate_bilinear(upsample2x_bilinear(grid_lr), query_points)`` without the upsampled map: the 2x2
+    footprint on the [2H, 2W] map is the 3x3 (at most) stencil of ``lowres_stencil`` on grid_lr [B, H, W, C].
+    This is the form the CUDA path evaluates when ``CnScene.feat_up == 2``; ``tests/test_oracle.py`` proves it equal
+    to the two-stage form (fp64: 1e-13, fp32: 1e-6 of the map's range)."""
+    B, H, W, C = grid_lr.shape
+    if indexing == 'xy':
+        qx, qy = query_points[..., 0], query_points[..., 1]
+    else:
+        qy, qx = query_points[..., 0], query_points[..., 1]
+
+    def axis(q, size_hr):
+        fl = torch.clamp(torch.floor(q), min=0.0, max=float(size_hr - 2))
+        return fl.detach().to(torch.int64), torch.clamp(q - fl.detach(), min=0.0, max=1.0)
+
+    fy, ay = axis(qy, 2 * H)
+    fx, ax = axis(qx, 2 * W)
+    iy, wy, _ = lowres_stencil(fy, ay, H)
+    ix, wx, _ = lowres_stencil(fx, ax, W)
+    flat = grid_lr.reshape(B, H * W, C)
+    out = 0
+    for i in range(3):
+        row = 0
+        for j in range(3):
+            lin = (iy[..., i] * W + ix[..., j])[..., None].expand(-1, -1, C)
+            row = row + wx[..., j, None] * torch.gather(flat, 1, lin)
+        out = out + wy[..., i, None] * row
+    return out
+
+
 def get_projection_features_mv(inputs: Tensor, features: Tensor, pixel_locations: Tensor) -> Tensor:
     """``nerf_utils.py:277-285``: concat(image*2-1, features) (259 ch) and bilinear gather.
 
@@ -494,8 +591,12 @@ def _render_pass(ray_o, ray_d, zs, norm_images, feats, K, Einv, p, net, n_views,
 
 def mvnerf_call(inputs: Sequence[Tensor], combined_features: Tensor, p: Dict[str, Tensor], *,
                 near: float, far: float, n_samples: int, u_strat: Tensor, u_pdf: Tensor,
-                return_aux: bool = False, quant: Optional[str] = None):
+                return_aux: bool = False, quant: Optional[str] = None, feat_up: int = 1):
     """``MVVNeRFRenderer._call`` (``model_v0.py:113-184``).
+
+    ``feat_up == 2``: ``combined_features`` is the [b,nv,H/2,W/2,256] input of the encoder's final
+    ``UpSampling2D`` (``layers.py:589``; ``model_without.py:76-79``) and is upsampled here first, the way
+    the reference does it -- the two-stage form the CUDA low-resolution gather is tested against.
 
     inputs = (ray_o [b,nr,3], ray_d [b,nr,3], images [b,nv,H,W,3] in [0,1],
     K [b,nv,4,4], E^-1 [b,nv,4,4]); combined_features [b,nv,H,W,256].
@@ -505,6 +606,10 @@ def mvnerf_call(inputs: Sequence[Tensor], combined_features: Tensor, p: Dict[str
     ray_o, ray_d, images, K, Einv = inputs
     n_views = images.shape[1]
     norm_images = images * 2 - 1.0
+    if feat_up == 2:
+        combined_features = upsample2x_bilinear(combined_features)
+    else:
+        assert feat_up == 1
     _, z = sample_along_ray(ray_o, ray_d, near, far, n_samples, u_strat)
     rgb, depth, weights, _, _ = _render_pass(ray_o, ray_d, z, norm_images, combined_features,
                                              K, Einv, p, 'coarse', n_views, quant)

@@ -249,3 +249,81 @@ def test_reference_gradient_spread_fp32_vs_tf32():
     assert min(coarse) > 1.5e-2 and max(coarse) > 5e-2      # ill-conditioned in the reference's own arithmetic ...
     assert max(coarse) < 0.3 and sp['features'][0] < 0.3    # ... but still the same direction
     assert min(v[1] for v in sp.values()) > 0.97
+
+
+# --------------------------------------------------------------------------
+# N2: the encoder's final 2x bilinear UpSampling2D folded into the gather
+# --------------------------------------------------------------------------
+def _lowres_queries(g, B, N, H2, W2, dtype):
+    """queries on the [H2, W2] (upsampled) map: interior, exactly on texels / half texels, on and beyond every border"""
+    q = torch.rand(B, N, 2, generator=g, dtype=torch.float64) * torch.tensor([W2 + 3.0, H2 + 3.0]) - 1.5
+    special = torch.tensor([[0.0, 0.0], [W2 - 1.0, H2 - 1.0], [W2 - 2.0, H2 - 2.0], [1.0, 1.0], [2.0, 3.0], [0.5, 1.5],
+                            [W2 - 1.5, 0.25], [-7.0, 2.2], [3.3, H2 + 9.0], [1e6, -1e6], [W2 - 2.0 + 1e-9, 1.0 - 1e-9]],
+                           dtype=torch.float64)
+    q[:, :special.shape[0]] = special
+    return q.to(dtype)
+
+
+def test_upsample2x_is_the_half_pixel_bilinear_resize():
+    """pin of the TensorFlow resize restatement: torch's bilinear interpolate with align_corners=False is an
+    independent implementation of the same half-pixel-centre convention; also the closed form of rows 0, 1, 2"""
+    g = torch.Generator().manual_seed(3)
+    for shape in ((2, 5, 7, 3), (1, 2, 2, 4), (1, 1, 3, 1), (2, 3, 6, 8, 2)):
+        x = torch.randn(*shape, generator=g, dtype=torch.float64)
+        up = O.upsample2x_bilinear(x)
+        assert tuple(up.shape) == (*shape[:-3], 2 * shape[-3], 2 * shape[-2], shape[-1])
+        x4 = x.reshape(-1, *shape[-3:]).permute(0, 3, 1, 2)
+        ref = torch.nn.functional.interpolate(x4, scale_factor=2, mode='bilinear', align_corners=False)
+        assert torch.allclose(up.reshape(-1, *up.shape[-3:]), ref.permute(0, 2, 3, 1), atol=1e-14, rtol=0)
+    x = torch.randn(1, 4, 1, 1, generator=g, dtype=torch.float64)
+    up = O.upsample2x_bilinear(x)[0, :, 0, 0]
+    v = x[0, :, 0, 0]
+    want = torch.stack([v[0], 0.75 * v[0] + 0.25 * v[1], 0.25 * v[0] + 0.75 * v[1], 0.75 * v[1] + 0.25 * v[2]])
+    assert torch.allclose(up[:4], want, atol=1e-15) and float(up[-1]) == float(v[-1])
+    # a constant map stays constant, a linear ramp stays linear away from the clamped border
+    ramp = torch.arange(6, dtype=torch.float64).view(1, 1, 6, 1).expand(1, 3, 6, 1)
+    up = O.upsample2x_bilinear(ramp)[0, 0, :, 0]
+    assert torch.allclose(up[1:-1], torch.arange(1, 11, dtype=torch.float64) * 0.5 - 0.25, atol=1e-15)
+
+
+@pytest.mark.parametrize('dtype,tol', [(torch.float64, 1e-13), (torch.float32, 1e-6)])
+def test_lowres_stencil_equals_upsample_then_gather(dtype, tol):
+    """the composed (at most 3x3, fixed 0.25 / 0.75) stencil on the low-resolution map == the reference's two-stage
+    interpolate_bilinear(UpSampling2D(bilinear)(x)) -- values, d/d map and d/d query"""
+    g = torch.Generator().manual_seed(4)
+    for (H, W) in ((6, 9), (2, 2), (1, 5), (8, 8)):   # (1, 5): the [2, 10] upsampled map clamps every row floor to 0
+        grid = torch.randn(2, H, W, 5, generator=g, dtype=torch.float64).to(dtype)
+        q = _lowres_queries(g, 2, 64, 2 * H, 2 * W, dtype)
+        ga, qa = grid.clone().requires_grad_(True), q.clone().requires_grad_(True)
+        gb, qb = grid.clone().requires_grad_(True), q.clone().requires_grad_(True)
+        two_stage = O.interpolate_bilinear(O.upsample2x_bilinear(ga), qa)
+        folded = O.interpolate_bilinear_lowres(gb, qb)
+        scale = float(grid.abs().max())
+        assert float((two_stage - folded).detach().abs().max()) <= tol * scale, (H, W)
+        cot = torch.randn(two_stage.shape, generator=g, dtype=torch.float64).to(dtype)
+        (two_stage * cot).sum().backward()
+        (folded * cot).sum().backward()
+        assert float((ga.grad - gb.grad).abs().max()) <= 10 * tol * float(ga.grad.abs().max())
+        assert float((qa.grad - qb.grad).abs().max()) <= 10 * tol * max(1.0, float(qa.grad.abs().max()))
+
+
+def test_lowres_stencil_weights_and_taps():
+    f0 = torch.tensor([0, 1, 2, 3, 8, 9, 10])
+    a = torch.tensor([0.25, 0.5, 0.0, 1.0, 0.75, 0.3, 1.0], dtype=torch.float64)
+    idx, w, dw = O.lowres_stencil(f0, a, 6)                  # 12 upsampled texels: f0 <= 10
+    assert torch.allclose(w.sum(-1), torch.ones(7, dtype=torch.float64)) and float(dw.sum(-1).abs().max()) == 0.0
+    assert idx.tolist() == [[0, 0, 1], [0, 0, 1], [0, 1, 2], [0, 1, 2], [3, 4, 5], [3, 4, 5], [4, 5, 5]]
+    assert torch.allclose(w[0], torch.tensor([0.1875, 0.75, 0.0625], dtype=torch.float64))      # even: .25(1-a), .75, .25a
+    assert torch.allclose(w[1], torch.tensor([0.0, 0.5, 0.5], dtype=torch.float64))             # odd: 0, .75-.5a, .25+.5a
+    assert torch.allclose(w[6], torch.tensor([0.0, 0.75, 0.25], dtype=torch.float64))           # f0 = 10, a = 1: U[11] = x[5]
+
+
+def test_call_with_lowres_features_is_the_call_on_the_upsampled_map():
+    sc = O.synthetic_scene(2, 1, 2, 4, 16, 20)
+    p = O.init_params(0, bias_std=0.02)
+    lr = torch.randn(1, 2, 8, 10, 256, generator=torch.Generator().manual_seed(1)) * 0.5
+    kw = dict(near=NEAR, far=FAR, n_samples=64, u_strat=sc['u_strat'], u_pdf=sc['u_pdf'])
+    a = O.mvnerf_call(sc['inputs'], lr, p, feat_up=2, **kw)
+    b_ = O.mvnerf_call(sc['inputs'], O.upsample2x_bilinear(lr), p, **kw)
+    for x, y in zip(a, b_):
+        assert torch.equal(x, y)

@@ -11,7 +11,7 @@ from ctypes import c_char_p, c_double, c_float, c_int32, c_int64, c_size_t, c_vo
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), 'lib', 'libclipnerf_b200.so')
 
-ABI_VERSION = 7
+ABI_VERSION = 8
 TILE_ROWS = 128
 SLAB_BYTES = 16384
 ACT_TILE_BYTES = 32768
@@ -23,7 +23,7 @@ PACKED_BYTES = 2 * 491520 + 16384
 
 class CnScene(ctypes.Structure):
     _fields_ = [('images', c_void_p), ('features', c_void_p), ('intrinsics', c_void_p), ('extr_inv', c_void_p),
-                ('b', c_int32), ('nv', c_int32), ('H', c_int32), ('W', c_int32)]
+                ('b', c_int32), ('nv', c_int32), ('H', c_int32), ('W', c_int32), ('feat_up', c_int32)]
 
 
 _P = c_void_p

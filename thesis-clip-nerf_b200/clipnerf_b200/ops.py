@@ -33,17 +33,27 @@ def _bytes(n: int, device) -> torch.Tensor:
 
 
 class Scene:
-    """Source views: images [b,nv,H,W,3], features [b,nv,H,W,256], K [b,nv,4,4], E^-1 [b,nv,4,4]."""
+    """Source views: images [b,nv,H,W,3], features [b,nv,H,W,256], K [b,nv,4,4], E^-1 [b,nv,4,4].
+
+    features [b,nv,H/2,W/2,256] = the input of the encoder's final 2x bilinear UpSampling2D (layers.py:589):
+    the upsample is folded into the gather (CnScene.feat_up = 2) and every feature gradient is low-resolution."""
 
     def __init__(self, images, features, intrinsics, extr_inv):
         self.images, self.features = _f32c(images), _f32c(features)
         self.intrinsics, self.extr_inv = _f32c(intrinsics), _f32c(extr_inv)
         b, nv, H, W, c3 = self.images.shape
-        assert c3 == 3 and tuple(self.features.shape) == (b, nv, H, W, 256), 'features must be [b,nv,H,W,256]'
+        shape = tuple(self.features.shape)
+        if shape == (b, nv, H, W, 256):
+            self.feat_up = 1
+        else:
+            assert c3 == 3 and H % 2 == 0 and W % 2 == 0 and shape == (b, nv, H // 2, W // 2, 256), \
+                'features must be [b,nv,H,W,256] or the pre-upsample [b,nv,H/2,W/2,256]'
+            self.feat_up = 2
+        assert c3 == 3
         assert tuple(self.intrinsics.shape) == (b, nv, 4, 4) and tuple(self.extr_inv.shape) == (b, nv, 4, 4)
         self.b, self.nv, self.H, self.W = b, nv, H, W
         self.c = CnScene(self.images.data_ptr(), self.features.data_ptr(), self.intrinsics.data_ptr(),
-                         self.extr_inv.data_ptr(), b, nv, H, W)
+                         self.extr_inv.data_ptr(), b, nv, H, W, self.feat_up)
 
     @property
     def device(self):

@@ -10,6 +10,22 @@ namespace cn {
 // ------------------------------------------------------------------------------------------
 // fp32 debug view (parity tests): reference tensor layouts
 // ------------------------------------------------------------------------------------------
+// one texel of tf.image.resize(x, 2x, 'bilinear', half_pixel_centers) (Keras UpSampling2D(2, 'bilinear')):
+//   in = (o + 0.5) / 2 - 0.5, lower = max(floor(in), 0), upper = min(ceil(in), size - 1), lerp = in - floor(in)
+//   top = TL + (TR - TL) * x_lerp, bottom = BL + (BR - BL) * x_lerp, out = top + (bottom - top) * y_lerp
+__device__ __forceinline__ float upsampled_texel(const float *__restrict__ x, int Hl, int Wl, int oy, int ox, int c) {
+  const float iy = (oy + 0.5f) * 0.5f - 0.5f, ix = (ox + 0.5f) * 0.5f - 0.5f;   // exact in fp32
+  const float fy = floorf(iy), fx = floorf(ix);
+  const int y0 = max((int)fy, 0), y1 = min((int)ceilf(iy), Hl - 1);
+  const int x0 = max((int)fx, 0), x1 = min((int)ceilf(ix), Wl - 1);
+  const float wy = iy - fy, wx = ix - fx;
+  const float tl = x[((int64_t)y0 * Wl + x0) * CN_FEAT_C + c], tr = x[((int64_t)y0 * Wl + x1) * CN_FEAT_C + c];
+  const float bl = x[((int64_t)y1 * Wl + x0) * CN_FEAT_C + c], br = x[((int64_t)y1 * Wl + x1) * CN_FEAT_C + c];
+  const float top = __fadd_rn(tl, __fmul_rn(__fsub_rn(tr, tl), wx));
+  const float bot = __fadd_rn(bl, __fmul_rn(__fsub_rn(br, bl), wx));
+  return __fadd_rn(top, __fmul_rn(__fsub_rn(bot, top), wy));
+}
+
 __global__ void __launch_bounds__(256)
 project_gather_debug_kernel(CnScene sc, const float *__restrict__ ray_o, const float *__restrict__ ray_d,
                             const float *__restrict__ z, int nr, int S, float *__restrict__ pix,
@@ -40,10 +56,22 @@ project_gather_debug_kernel(CnScene sc, const float *__restrict__ ray_o, const f
     }
     if (!gathered) continue;
     const int64_t pix00 = ((int64_t)bv * H + pr.y0) * W + pr.x0;
-    const float *f00 = sc.features + pix00 * CN_FEAT_C;
-    const float *f10 = f00 + (int64_t)W * CN_FEAT_C;
-    for (int c = l; c < CN_FEAT_C; c += 32)
-      gathered[o * 259 + 3 + c] = lerp2_rn(f00[c], f00[CN_FEAT_C + c], f10[c], f10[CN_FEAT_C + c], pr.ax, pr.ay);
+    if (sc.feat_up == 2) {
+      // the reference's own two-stage form, texel by texel: UpSampling2D(2, 'bilinear') of the low-resolution map at
+      // the four corners, then interpolate_bilinear -- the fp32 statement the folded stencil of gather_binned.cu
+      // is compared with
+      const float *fl = sc.features + (int64_t)bv * (H / 2) * (W / 2) * CN_FEAT_C;
+      for (int c = l; c < CN_FEAT_C; c += 32) {
+        const float tl = upsampled_texel(fl, H / 2, W / 2, pr.y0, pr.x0, c), tr = upsampled_texel(fl, H / 2, W / 2, pr.y0, pr.x0 + 1, c);
+        const float bl = upsampled_texel(fl, H / 2, W / 2, pr.y0 + 1, pr.x0, c), br = upsampled_texel(fl, H / 2, W / 2, pr.y0 + 1, pr.x0 + 1, c);
+        gathered[o * 259 + 3 + c] = lerp2_rn(tl, tr, bl, br, pr.ax, pr.ay);
+      }
+    } else {
+      const float *f00 = sc.features + pix00 * CN_FEAT_C;
+      const float *f10 = f00 + (int64_t)W * CN_FEAT_C;
+      for (int c = l; c < CN_FEAT_C; c += 32)
+        gathered[o * 259 + 3 + c] = lerp2_rn(f00[c], f00[CN_FEAT_C + c], f10[c], f10[CN_FEAT_C + c], pr.ax, pr.ay);
+    }
     if (l < 3) {
       const float *i00 = sc.images + pix00 * 3;
       const float *i10 = i00 + (int64_t)W * 3;
@@ -93,6 +121,8 @@ int check_scene(const CnScene *s, const char *who) {
   CN_REQUIRE(s->b > 0 && s->nv > 0 && s->H >= 2 && s->W >= 2, "%s: bad scene dims b=%d nv=%d H=%d W=%d", who, s->b,
              s->nv, s->H, s->W);
   CN_REQUIRE(((uintptr_t)s->features & 15) == 0, "%s: features must be 16-byte aligned", who);
+  CN_REQUIRE(s->feat_up == 1 || (s->feat_up == 2 && s->H % 2 == 0 && s->W % 2 == 0),
+             "%s: feat_up must be 1, or 2 with even H and W (feat_up=%d H=%d W=%d)", who, s->feat_up, s->H, s->W);
   return 0;
 }
 

@@ -50,9 +50,12 @@ enum { kHdrItems = 0, kHdrCurFwd = 1, kHdrCurZg = 2, kHdrCurSc = 3, kHdrHeavyN =
 // up.  (The sweep still handles a full list -- see feature_grad_kernel -- which tests reach through CN_DEBUG_HEAVY_CAP.)
 static int heavy_cap_for(int64_t rows) { return (int)(rows / 4 + 1024); }
 
+constexpr int kChunkLr = 256;                    // feat_up == 2: rows per work item (its tile is 100 KiB, see gather_lowres.cuh)
+
 struct Ws {
   int64_t rows;
   int tiles_x, tiles_y, n_bins, n_keys, n_blk, max_items, heavy_cap;
+  int chunk;       // max rows per work item
   int *hdr;        // [kHdrInts]
   int *count;      // [n_keys]   histogram, then (in place) start offset of every key
   int2 *blk_sum;   // [n_blk]    (rows, items) per scan block
@@ -68,15 +71,20 @@ struct Ws {
 
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
-static Ws ws_layout(int b, int nv, int H, int W, int64_t rows, void *base) {
+// Cells of the key grid: feat_up == 1, the (W-1) x (H-1) clamped 2x2 footprints of the map itself; feat_up == 2, the
+// (W/2) x (H/2) base texels k = f0 >> 1 of the composed stencil on the low-resolution map (f0 <= W - 2, so k <= W/2 - 1).
+// The feat_up == 2 layout is never larger than the feat_up == 1 one: cn_gather_ws_bytes bounds both.
+static Ws ws_layout(int b, int nv, int H, int W, int up, int64_t rows, void *base) {
   Ws w;
   w.rows = rows;
-  w.tiles_x = (W - 1 + kT - 1) / kT;
-  w.tiles_y = (H - 1 + kT - 1) / kT;
+  const int cells_x = up == 2 ? W / 2 : W - 1, cells_y = up == 2 ? H / 2 : H - 1;
+  w.chunk = up == 2 ? kChunkLr : kChunk;
+  w.tiles_x = (cells_x + kT - 1) / kT;
+  w.tiles_y = (cells_y + kT - 1) / kT;
   w.n_bins = b * nv * w.tiles_x * w.tiles_y;
   w.n_keys = w.n_bins * kCells;
   w.n_blk = (w.n_bins + 255) / 256;
-  w.max_items = (int)(w.n_bins + rows / kChunk + 1);
+  w.max_items = (int)(w.n_bins + rows / w.chunk + 1);
   w.heavy_cap = heavy_cap_for(rows);
   uint8_t *p = (uint8_t *)base;
   size_t o = 0;
@@ -136,8 +144,13 @@ project_bin_kernel(CnScene sc, const float *__restrict__ ray_o, const float *__r
   const Proj pr = project(E, K, rc.x[0], rc.x[1], rc.x[2], sc.H, sc.W);
 
   // ---- key, rank inside the key (one atomic per distinct key of the warp), record
-  const int lx = pr.x0 & (kT - 1), ly = pr.y0 & (kT - 1);
-  const int bin = (id.bv * g.tiles_y + (pr.y0 / kT)) * g.tiles_x + (pr.x0 / kT);
+  // feat_up == 2: the cell is the base texel (x0 >> 1, y0 >> 1) of the low-resolution stencil; the parities of x0, y0
+  // select its weights and ride in bits 16, 17 of the record's cell word
+  const int up_shift = sc.feat_up == 2 ? 1 : 0;
+  const int cx = pr.x0 >> up_shift, cy = pr.y0 >> up_shift;
+  const int par = up_shift ? ((pr.x0 & 1) | ((pr.y0 & 1) << 1)) : 0;
+  const int lx = cx & (kT - 1), ly = cy & (kT - 1);
+  const int bin = (id.bv * g.tiles_y + (cy / kT)) * g.tiles_x + (cx / kT);
   const int key = bin * kCells + ly * kT + lx;
   {
     const unsigned peers = __match_any_sync(0xffffffffu, key);
@@ -146,7 +159,7 @@ project_bin_kernel(CnScene sc, const float *__restrict__ ray_o, const float *__r
     if (lane == leader) base = atomicAdd(g.count + key, __popc(peers));
     base = __shfl_sync(0xffffffffu, base, leader);
     const int rank = base + __popc(peers & ((1u << lane) - 1u));
-    g.rec_u[row] = make_int4((int)row, lx | (ly << 8), __float_as_int(pr.ax), __float_as_int(pr.ay));
+    g.rec_u[row] = make_int4((int)row, lx | (ly << 8) | (par << 16), __float_as_int(pr.ax), __float_as_int(pr.ay));
     g.keyrank[row] = make_int2(key, rank);
   }
   if (!x_tiles) return;
@@ -274,7 +287,7 @@ __global__ void __launch_bounds__(256) bin_scan1_kernel(Ws g) {
   const int bin = blockIdx.x * 256 + threadIdx.x;
   const int tot = bin < g.n_bins ? bin_total(g.count, bin) : 0;
   int2 total;
-  (void)block_excl_scan2(make_int2(tot, (tot + kChunk - 1) / kChunk), s_warp, total);
+  (void)block_excl_scan2(make_int2(tot, (tot + g.chunk - 1) / g.chunk), s_warp, total);
   if (threadIdx.x == 0) {
     g.blk_sum[blockIdx.x] = total;
     __threadfence();
@@ -307,7 +320,7 @@ __global__ void __launch_bounds__(256) bin_scan2_kernel(Ws g) {
   __shared__ int2 s_warp[8];
   const int bin = blockIdx.x * 256 + threadIdx.x;
   const int tot = bin < g.n_bins ? bin_total(g.count, bin) : 0;
-  const int nit = (tot + kChunk - 1) / kChunk;
+  const int nit = (tot + g.chunk - 1) / g.chunk;
   int2 total;
   const int2 ex = block_excl_scan2(make_int2(tot, nit), s_warp, total);
   if (bin >= g.n_bins) return;
@@ -325,7 +338,7 @@ __global__ void __launch_bounds__(256) bin_scan2_kernel(Ws g) {
     o.w = run; run += v.w;
     c4[q] = o;
   }
-  for (int q = 0; q < nit; ++q) g.items[item0 + q] = make_int4(bin, row0 + q * kChunk, min(kChunk, tot - q * kChunk), 0);
+  for (int q = 0; q < nit; ++q) g.items[item0 + q] = make_int4(bin, row0 + q * g.chunk, min(g.chunk, tot - q * g.chunk), 0);
 }
 
 __global__ void __launch_bounds__(256) bin_fill_kernel(Ws g) {
@@ -990,6 +1003,12 @@ project_dz_kernel(CnScene sc, const float *__restrict__ ray_o, const float *__re
   }
 }
 
+}  // namespace cn
+
+#include "gather_lowres.cuh"
+
+namespace cn {
+
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
@@ -1008,7 +1027,7 @@ static int get_ws(const CnScene *scene, int nr, int S, void *ws, size_t ws_bytes
   int64_t rows;
   if (int e = check_rows(scene, nr, S, who, &rows)) return e;
   CN_REQUIRE(ws && ((uintptr_t)ws & 255) == 0, "%s: workspace must be a 256-byte aligned device pointer", who);
-  *out = ws_layout(scene->b, scene->nv, scene->H, scene->W, rows, ws);
+  *out = ws_layout(scene->b, scene->nv, scene->H, scene->W, scene->feat_up, rows, ws);
   CN_REQUIRE(ws_bytes >= out->total, "%s: workspace too small (%zu < %zu bytes)", who, ws_bytes, out->total);
   return 0;
 }
@@ -1031,6 +1050,17 @@ static int run_bin(const CnScene *scene, const float *ray_o, const float *ray_d,
 
 template <bool kBackward>
 static int run_tile_rows(const CnScene *scene, const Ws &g, int cursor_index, uint8_t *x_tiles, cudaStream_t st) {
+  if (scene->feat_up == 2) {
+    cudaError_t e = cudaFuncSetAttribute(tile_rows_lr_kernel<kBackward>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)kRowsSmemLr);
+    if (e != cudaSuccess) {
+      set_error("tile_rows_lr: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      return (int)e;
+    }
+    tile_rows_lr_kernel<kBackward><<<num_sms(), lr_threads<kBackward>(), kRowsSmemLr, st>>>(*scene, g, g.hdr + cursor_index,
+                                                                                            x_tiles);
+    return check_launch("tile_rows_lr");
+  }
   cudaError_t e = cudaFuncSetAttribute(tile_rows_kernel<kBackward>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)kRowsSmem);
   if (e != cudaSuccess) {
@@ -1042,8 +1072,50 @@ static int run_tile_rows(const CnScene *scene, const Ws &g, int cursor_index, ui
 }
 
 
+static int run_feature_grad_lr(const CnScene *scene, int n_sets, const Ws *const *ws, const void *const *dx,
+                               float *d_features, int accumulate, cudaStream_t st) {
+  CN_REQUIRE(n_sets <= kLrMaxSets, "cn_feature_grad: feat_up == 2 takes at most %d row sets (got %d)", kLrMaxSets, n_sets);
+  LrGradArgs a;
+  a.n_sets = n_sets;
+  for (int i = 0; i < kLrMaxSets; ++i) {
+    const Ws *w = ws[i < n_sets ? i : 0];
+    a.set[i].key_off = w->count;
+    a.set[i].rec_s = w->rec_s;
+    a.set[i].dx = (const uint8_t *)dx[i < n_sets ? i : 0];
+    a.set[i].rows = (int)w->rows;
+  }
+  const Ws *w0 = ws[0];
+  a.n_keys = w0->n_keys;
+  a.tiles_x = w0->tiles_x;
+  a.tiles_y = w0->tiles_y;
+  CN_REQUIRE((int64_t)w0->n_bins * kT * 4 < ((int64_t)1 << 31), "cn_feature_grad: too many cell rows");
+  a.n_units = w0->n_bins * kT;
+  a.cursor = w0->hdr + kHdrCurSc;
+  const Ws *wl = w0;
+  for (int i = 1; i < n_sets; ++i)
+    if (ws[i]->rows > wl->rows) wl = ws[i];
+  a.heavy_n = w0->hdr + kHdrHeavyN;
+  a.heavy_list = wl->heavy;
+  a.heavy_cap = wl->heavy_cap;
+  if (const char *dbg = getenv("CN_DEBUG_HEAVY_CAP")) {   // tests only: force the list-full path
+    const int cap = atoi(dbg);
+    if (cap >= 0 && cap < a.heavy_cap) a.heavy_cap = cap;
+  }
+  cudaError_t ce = cudaMemsetAsync(w0->hdr + kHdrCurSc, 0, 3 * sizeof(int), st);
+  if (ce == cudaSuccess && !accumulate)   // every contribution arrives as a reduction
+    ce = cudaMemsetAsync(d_features, 0, (size_t)scene->b * scene->nv * (scene->H / 2) * (scene->W / 2) * CN_FEAT_C * 4, st);
+  if (ce != cudaSuccess) {
+    set_error("cn_feature_grad: cudaMemsetAsync: %s", cudaGetErrorString(ce));
+    return (int)ce;
+  }
+  feature_grad_lr_kernel<<<kLrCtasPerSm * num_sms(), kLrThreads, 0, st>>>(*scene, a, d_features);
+  feature_grad_lr_heavy_kernel<<<kLrCtasPerSm * num_sms(), kLrThreads, 0, st>>>(*scene, a, d_features);
+  return check_launch("cn_feature_grad (feat_up 2)");
+}
+
 static int run_feature_grad(const CnScene *scene, int n_sets, const Ws *const *ws, const void *const *dx,
                             float *d_features, int accumulate, cudaStream_t st) {
+  if (scene->feat_up == 2) return run_feature_grad_lr(scene, n_sets, ws, dx, d_features, accumulate, st);
   GradArgs a;
   a.n_sets = n_sets;
   for (int i = 0; i < kMaxSets; ++i) {
@@ -1087,7 +1159,7 @@ static int run_feature_grad(const CnScene *scene, int n_sets, const Ws *const *w
 
 extern "C" size_t cn_gather_ws_bytes(int32_t b, int32_t nv, int32_t H, int32_t W, int32_t nr, int32_t S) {
   if (b <= 0 || nv <= 0 || H < 2 || W < 2 || nr <= 0 || S <= 0) return 0;
-  return cn::ws_layout(b, nv, H, W, (int64_t)b * nv * nr * S, nullptr).total;
+  return cn::ws_layout(b, nv, H, W, 1, (int64_t)b * nv * nr * S, nullptr).total;
 }
 
 extern "C" int cn_project_bin(const CnScene *scene, const float *ray_o, const float *ray_d, const float *z,
