@@ -133,10 +133,19 @@ WORKLOADS = {
 def workload_config(args, nr):
     tag = WORKLOADS[args.workload][2] if args.workload in WORKLOADS and WORKLOADS[args.workload][:2] == (nr, args.nv) \
         else f'custom: {nr} rays, {args.nv} views'
-    return {'workload': f'{tag}; {args.nv} views {H}x{W}x{C} fp32 maps, {nr} rays x (64+128) samples per GPU, '
-                        f'MSE(coarse)+MSE(fine), feature-map gradient, clip+Adam',
-            'rays_per_gpu': nr, 'n_views': args.nv, 'samples': '64+128', 'image': [H, W], 'feature_channels': C,
-            'parallelism': f'ray-sharded dp{args.gpus}', 'l2': 'inputs larger than L2 (943 MB of feature maps per scene)'}
+    low = getattr(args, 'lowres_features', False)
+    maps = (f'{H // 2}x{W // 2}x{C} fp32 maps = the input of the final 2x bilinear UpSampling2D, upsample folded into the '
+            f'gather (same function of the same data as the {H}x{W} maps)') if low else f'{H}x{W}x{C} fp32 maps'
+    cfg = {'workload': f'{tag}; {args.nv} views {maps}, {nr} rays x (64+128) samples per GPU, '
+                       f'MSE(coarse)+MSE(fine), feature-map gradient, clip+Adam',
+           'rays_per_gpu': nr, 'n_views': args.nv, 'samples': '64+128', 'image': [H, W], 'feature_channels': C,
+           'parallelism': f'ray-sharded dp{args.gpus}',
+           'l2': ('L2 flushed by the step itself (every step streams > 10 GB of activations through HBM; the 236 MB of '
+                  'low-resolution maps exceed the 126 MB L2 as well)') if low
+           else 'inputs larger than L2 (943 MB of feature maps per scene)'}
+    if low:
+        cfg['lowres_features'] = True
+    return cfg
 
 
 # ----------------------------------------------------------------------------------------------
@@ -209,8 +218,8 @@ def run_reference(args):
 # ----------------------------------------------------------------------------------------------
 # this repo's arm
 # ----------------------------------------------------------------------------------------------
-def _traffic_file():
-    for name in ('r02_traffic.json', 'r01_v8_traffic.json'):
+def _traffic_file(lowres=False):
+    for name in (('r02_lowres_traffic.json',) if lowres else ('r02_traffic.json', 'r01_v8_traffic.json')):
         path = os.path.join(ROOT, 'profiles', name)
         if os.path.exists(path):
             return path
@@ -241,14 +250,19 @@ def run_b200(args):
     sc = make_scene(100 + rank, nr, nv, device=dev, pinned=True)
     # combined_features: produced upstream by the image encoders (out of scope), resident on the device; the plug-in
     # below hands them to the model and receives their gradient every step (model.feature_fn)
-    maps = torch.nn.Parameter(sc['features'].reshape(nv, H, W, C))
+    Hf, Wf = (H // 2, W // 2) if args.lowres_features else (H, W)
+    if args.lowres_features:
+        # the input of the encoder's final 2x bilinear UpSampling2D (layers.py:589,659): the upsample is folded into the
+        # gather (CnScene.feat_up = 2), the map and its gradient stay 240 x 320
+        sc['features'] = sc['features'][:, :, ::2, ::2].contiguous()
+    maps = torch.nn.Parameter(sc['features'].reshape(nv, Hf, Wf, C))
     model = MVVNeRFRenderer(n_rays_train=nr, n_rays_infer=nr, n_views=nv, near=NEAR, far=FAR,
                             original_image_size=(H, W), feature_fn=lambda images: maps, device=dev)
     torch.manual_seed(0)
     model.compile()                      # default optimizer: RenderTrainer on the model's flat parameter buffer
     model.max_rays_per_step = args.chunk_rays
     trainer = model.optimizer
-    feats = maps.detach().reshape(1, nv, H, W, C).requires_grad_(True)       # same storage, the trainer's leaf
+    feats = maps.detach().reshape(1, nv, Hf, Wf, C).requires_grad_(True)       # same storage, the trainer's leaf
     dev_inputs = [t.to(dev, non_blocking=True) for t in sc['inputs']]
     dev_u = [sc[k].to(dev, non_blocking=True) for k in ('u_strat', 'u_pdf', 'target')]
 
@@ -380,12 +394,12 @@ def run_b200(args):
     }
     ncu_traffic, ncu_per_launch, traffic_src = {}, {}, None
     try:
-        if (nr, nv) == (4096, 3) and _traffic_file():
-            traffic_src = os.path.relpath(_traffic_file(), ROOT)
-            with open(_traffic_file()) as f:
+        if (nr, nv) == (4096, 3) and _traffic_file(args.lowres_features):
+            traffic_src = os.path.relpath(_traffic_file(args.lowres_features), ROOT)
+            with open(_traffic_file(args.lowres_features)) as f:
                 raw = json.load(f)
             for k, v in raw.items():
-                if isinstance(v, dict):
+                if isinstance(v, dict) and 'dram_bytes_per_launch' in v:
                     name = k.split(' ')[0]
                     ncu_traffic[name] = ncu_traffic.get(name, 0) + v['dram_bytes_per_launch'] * v['launches_per_step']
                     ncu_per_launch.setdefault(name, v['dram_bytes_per_launch'])
@@ -510,6 +524,8 @@ def main():
     ap.add_argument('--chunk-rays', type=int, default=16384,
                     help='batches with more rays per GPU are rendered in chunks of this many rays (gradients accumulate)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--lowres-features', action='store_true',
+                    help='feed the 240x320 input of the final 2x bilinear UpSampling2D; the upsample is folded into the gather')
     ap.add_argument('--no-cfg5', action='store_true', help='skip the cfg5 strong-scaling shard of the 8-GPU run')
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]

@@ -142,7 +142,7 @@ class MVVNeRFRenderer(torch.nn.Module):
     def call(self, inputs, training=False, mask=None):
         src = self._to_dev(inputs[2])
         b, n = src.shape[:2]
-        feats = self.encode(src.reshape(b * n, *src.shape[2:])).reshape(b, n, src.shape[2], src.shape[3], -1)
+        feats = self._features_for(src)
         return self._call(inputs, self.n_rays_train, self.batch_size, feats)
 
     def forward(self, inputs, training=False):
@@ -189,9 +189,12 @@ class MVVNeRFRenderer(torch.nn.Module):
                                                                                      eps=1e-7)
 
     def _features_for(self, images):
-        """combined_features of a device image batch [b,nv,H,W,3] through the plug-in encoder"""
+        """combined_features of a device image batch [b,nv,H,W,3] through the plug-in encoder: [b,nv,H,W,C], or
+        [b,nv,H/2,W/2,C] when the plug-in stops before the final 2x bilinear UpSampling2D (layers.py:589,659) -- the
+        gather then composes the upsample (CnScene.feat_up = 2)"""
         b, n = images.shape[:2]
-        return self.encode(images.reshape(b * n, *images.shape[2:])).reshape(b, n, images.shape[2], images.shape[3], -1)
+        f = self.encode(images.reshape(b * n, *images.shape[2:]))
+        return f.reshape(b, n, *f.shape[-3:])
 
     def _encoder_backward(self, k, feats, f_out):
         """hand the feature-map gradient of a step to the plug-in encoders (their own backward + optimizer step)"""
