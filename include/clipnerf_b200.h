@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define CN_ABI_VERSION 8
+#define CN_ABI_VERSION 9
 #define CN_TILE_ROWS 128
 #define CN_HIDDEN 128
 #define CN_FEAT_C 256          /* combined_features channels (model_v0.py:60)            */
@@ -56,6 +56,15 @@ extern "C" {
 
 /* bytes of the packed (bf16 operand images + fp32 bias tables) form of one net */
 #define CN_PACKED_BYTES (2 * 491520 + 16384)
+
+/* GraspReadout (delta_ngf/layers.py:8-28): fp32 parameters in Keras variable order, kernel[in][out] --
+ * activation_downscale_{1..4} (kernel [128][64], bias [64]), combined_activation_downscale ([256][64], [64]),
+ * readout.0 layer_0 ([2688][128], [128]), layer_1 ([128][64], [64]), shortcut ([2688][64]), readout.1 layer_0 / layer_1
+ * ([64][64], [64] each), readout.2 output_layer ([64][1], [1]; zero when use_bias is False) -- and the size of their
+ * packed form (bf16 operand images in both orientations + fp32 bias table, cn_grasp_head_pack). */
+#define CN_HEAD_PARAMS 582337
+#define CN_HEAD_PACK_BYTES 2329600
+#define CN_HEAD_OFFSETS 42     /* query offsets per pose: 6 gripper bases x n_5d_poses = 7 (delta_ngf/model.py:63-97) */
 
 int cn_abi_version(void);
 const char *cn_last_error(void);
@@ -228,6 +237,29 @@ int cn_mlp_fusion_fwd_taps(const void *packed, const void *h3_tiles, int32_t b, 
 /* g_tiles [n_tiles] (bf16 activation-tile images) = (accumulate ? g_tiles : 0) + rows [n_tiles*128][128] fp32:
  * the gradient of a tapped stage output joins the gradient stream of cn_mlp_block_bwd.        */
 int cn_tile_add_rows(void *g_tiles, const float *rows, int64_t n_tiles, int32_t accumulate, void *stream);
+/* g_tiles [n_tiles] += src_tiles [n_tiles] (both bf16 activation-tile images): the tap gradients cn_grasp_head_bwd
+ * returns as tiles join the gradient stream without an fp32 round trip.                        */
+int cn_tile_add_tiles(void *g_tiles, const void *src_tiles, int64_t n_tiles, void *stream);
+
+/* ---- GraspReadout.call (delta_ngf/layers.py:30-42; relu variant grasp_mvnerf/layers.py:22-31) on tcgen05, and its
+ * backward to the four stage outputs -- the gradient DNGFOptimizer.optimize_pose takes (grasp_optimizer.py:158-184).
+ * Rows are the fusion-stage rows of the pose-query call, '(b (np n5))' padded per scene: row R belongs to scene
+ * R / n_pad, i = R % n_pad, pose i / 42 and offset i % 42 of that scene for i < np * 42 (padding rows are computed and
+ * dropped).  n_tiles = b * n_pad / 128.  activation: 1 = elu, 0 = relu.
+ *   cn_grasp_head_pack: params [CN_HEAD_PARAMS] fp32 -> pack [CN_HEAD_PACK_BYTES] (once per weight version).
+ *   cn_grasp_head_fwd : taps [4][n_tiles*128][128] fp32 (cn_mlp_fusion_fwd_taps) -> y [b*np] fp32.  Kept for the
+ *     backward (caller-allocated, P = ceil(b*np / 128) pose tiles): vslabs [P][42][2][16 KiB] (the flattened
+ *     'b np (n5 d)' activations and their second activation as bf16 K-chunks), acat (nullable) [n_tiles][64 KiB],
+ *     saved [P][80 KiB] (activation outputs of the per-pose tail).
+ *   cn_grasp_head_bwd : gy [b*np] fp32 -> dtap_tiles [4][n_tiles] bf16 activation-tile images (d y / d tap_s);
+ *     dpc_ws [P][42][16 KiB] is scratch.  No parameter gradients: training the head goes through the differentiable
+ *     torch form (src/lib/delta_ngf/layers.py), which the double backward of DeltaNGF.train_step needs anyway.   */
+int cn_grasp_head_pack(const float *params, void *pack, void *stream);
+int cn_grasp_head_fwd(const float *taps, int64_t n_tiles, int32_t b, int32_t n_pad, int32_t np, const void *pack,
+                      int32_t activation, void *vslabs, void *acat, void *saved, float *y, void *stream);
+int cn_grasp_head_bwd(const float *gy, int64_t n_tiles, int32_t b, int32_t n_pad, int32_t np, const void *pack,
+                      int32_t activation, const void *vslabs, const void *acat, const void *saved, void *dpc_ws,
+                      void *dtap_tiles, void *stream);
 
 /* readout backward: d_y [rows,4] + relu(e) tiles -> g tiles (bf16), d(output_layer)
  * accumulated into grad (flat layout above).                                           */

@@ -815,22 +815,24 @@ def init_grasp_readout(seed: int, bias_std: float = 0.0, use_bias: bool = True, 
 
 
 def grasp_readout(embeddings: Sequence[Tensor], p: Dict[str, Tensor], prefix: str = 'grasp_readout',
-                  activation: str = 'elu') -> Tensor:
+                  activation: str = 'elu', quant: Optional[str] = None, return_pre_relu: bool = False):
     """``GraspReadout.call`` (``delta_ngf/layers.py:30-42``; relu variant ``grasp_mvnerf/layers.py:22-31``):
-    4 x [b, np, n5, 128] -> [b, np]."""
+    4 x [b, np, n5, 128] -> [b, np] (``return_pre_relu``: also the input of the final Readout's ReLU, [b, np, 64]).  ``quant='bf16'`` rounds every matmul operand (inputs, kernels, activation
+    outputs) where the tcgen05 head (``cn_grasp_head_fwd``) stores bf16 operand tiles."""
+    q = _quantizer(quant)
     act = F.elu if activation == 'elu' else F.relu
-    ds = [act(embeddings[i] @ p[f'{prefix}.activation_downscale_{i + 1}.kernel']
-              + p[f'{prefix}.activation_downscale_{i + 1}.bias']) for i in range(4)]
+    ds = [q(act(q(embeddings[i]) @ q(p[f'{prefix}.activation_downscale_{i + 1}.kernel'])
+                + p[f'{prefix}.activation_downscale_{i + 1}.bias'])) for i in range(4)]
     c = torch.cat(ds, dim=-1)
-    c = act(c @ p[f'{prefix}.combined_activation_downscale.kernel'] + p[f'{prefix}.combined_activation_downscale.bias'])
+    c = q(act(c @ q(p[f'{prefix}.combined_activation_downscale.kernel']) + p[f'{prefix}.combined_activation_downscale.bias']))
     c = c.reshape(*c.shape[:-2], -1)                                   # 'b np n5 d -> b np (n5 d)'
     y = resnet_mlp_block(c, p, f'{prefix}.readout.0', activation=activation,
-                         shortcut_kernel=p[f'{prefix}.readout.0.shortcut.kernel'])
-    y = resnet_mlp_block(y, p, f'{prefix}.readout.1', activation=activation)
-    y = F.relu(y) @ p[f'{prefix}.readout.2.output_layer.kernel']
+                         shortcut_kernel=q(p[f'{prefix}.readout.0.shortcut.kernel']), quant=quant)
+    o2 = resnet_mlp_block(y, p, f'{prefix}.readout.1', activation=activation, quant=quant)
+    y = F.relu(o2) @ p[f'{prefix}.readout.2.output_layer.kernel']
     if f'{prefix}.readout.2.output_layer.bias' in p:
         y = y + p[f'{prefix}.readout.2.output_layer.bias']
-    return y[..., 0]
+    return (y[..., 0], o2) if return_pre_relu else y[..., 0]
 
 
 def query_embeddings_from_points(images: Tensor, K: Tensor, Einv: Tensor, pts: Tensor, dirs: Tensor, features: Tensor,
@@ -867,10 +869,12 @@ def query_embeddings(images: Tensor, K: Tensor, Einv: Tensor, transforms: Tensor
 
 
 def query_call(images: Tensor, K: Tensor, Einv: Tensor, transforms: Tensor, features: Tensor,
-               p: Dict[str, Tensor], net: str = 'fine', quant: Optional[str] = None, activation: str = 'elu') -> Tensor:
-    """``DeltaNGF._call`` (``delta_ngf/model.py:188-245``) -> grasp_success [b, np]."""
+               p: Dict[str, Tensor], net: str = 'fine', quant: Optional[str] = None, activation: str = 'elu',
+               head_quant: Optional[str] = None, return_pre_relu: bool = False):
+    """``DeltaNGF._call`` (``delta_ngf/model.py:188-245``) -> grasp_success [b, np].  ``quant`` rounds the
+    embedding's operands, ``head_quant`` the ``GraspReadout``'s (the tcgen05 head; the torch head runs TF32)."""
     return grasp_readout(query_embeddings(images, K, Einv, transforms, features, p, net, quant), p,
-                         activation=activation)
+                         activation=activation, quant=head_quant, return_pre_relu=return_pre_relu)
 
 
 def cosine_similarity_loss(y_true: Tensor, y_pred: Tensor) -> Tensor:

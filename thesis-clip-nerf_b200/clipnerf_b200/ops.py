@@ -10,7 +10,7 @@ from typing import Optional, Tuple
 import torch
 
 from . import _abi
-from ._abi import ACT_TILE_BYTES, PACKED_BYTES, TILE_ROWS, X_TILE_BYTES, CnScene, call
+from ._abi import ACT_TILE_BYTES, PACKED_BYTES, SLAB_BYTES, TILE_ROWS, X_TILE_BYTES, CnScene, call
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -316,6 +316,57 @@ def tile_add_rows(g_tiles: Optional[torch.Tensor], rows: torch.Tensor) -> torch.
         g_tiles = _bytes(nt * ACT_TILE_BYTES, rows.device)
     call('cn_tile_add_rows', _ptr(g_tiles), _ptr(rows), nt, int(acc), _stream())
     return g_tiles
+
+
+def tile_add_tiles(g_tiles: torch.Tensor, src_tiles: torch.Tensor) -> torch.Tensor:
+    """g_tiles += src_tiles (both bf16 activation-tile images)"""
+    assert g_tiles.numel() == src_tiles.numel() and g_tiles.numel() % ACT_TILE_BYTES == 0
+    call('cn_tile_add_tiles', _ptr(g_tiles), _ptr(src_tiles), g_tiles.numel() // ACT_TILE_BYTES, _stream())
+    return g_tiles
+
+
+# ---- GraspReadout on tcgen05 (delta_ngf/layers.py:8-42): forward + backward to the four stage outputs
+def grasp_head_pack(params_flat: torch.Tensor) -> torch.Tensor:
+    """Keras-order flat fp32 variables [HEAD_PARAMS] -> packed bf16 operand images + bias table"""
+    params_flat = _f32c(params_flat)
+    assert params_flat.numel() == _abi.HEAD_PARAMS
+    pack = _bytes(_abi.HEAD_PACK_BYTES, params_flat.device)
+    call('cn_grasp_head_pack', _ptr(params_flat), _ptr(pack), _stream())
+    return pack
+
+
+class HeadState:
+    """what cn_grasp_head_fwd keeps for cn_grasp_head_bwd"""
+    __slots__ = ('n_tiles', 'b', 'n_pad', 'np', 'pack', 'elu', 'vslabs', 'acat', 'saved')
+
+
+def grasp_head_fwd(taps: torch.Tensor, b: int, n_pad: int, n_poses_per_scene: int, pack: torch.Tensor, elu: bool,
+                   save: bool):
+    """taps [4, b * n_pad, 128] fp32 (rows '(b (np n5))' padded per scene to n_pad) -> y [b, np], HeadState"""
+    assert taps.dtype == torch.float32 and taps.is_contiguous() and tuple(taps.shape) == (4, b * n_pad, 128)
+    st = HeadState()
+    st.n_tiles, st.b, st.n_pad, st.np, st.pack, st.elu = n_tiles(b * n_pad), b, n_pad, n_poses_per_scene, pack, int(elu)
+    p_tiles = (b * n_poses_per_scene + 127) // 128
+    dev = taps.device
+    st.vslabs = _bytes(p_tiles * _abi.HEAD_OFFSETS * 2 * SLAB_BYTES, dev)
+    st.acat = _bytes(st.n_tiles * 4 * SLAB_BYTES, dev) if save else None
+    st.saved = _bytes(p_tiles * 5 * SLAB_BYTES, dev)
+    y = torch.empty(b, n_poses_per_scene, dtype=torch.float32, device=dev)
+    call('cn_grasp_head_fwd', _ptr(taps), st.n_tiles, b, n_pad, n_poses_per_scene, _ptr(pack), st.elu, _ptr(st.vslabs),
+         _ptr(st.acat), _ptr(st.saved), _ptr(y), _stream())
+    return y, st
+
+
+def grasp_head_bwd(gy: torch.Tensor, st: HeadState) -> torch.Tensor:
+    """gy [b, np] -> d y / d tap_s as bf16 activation-tile images, uint8 [4, n_tiles * ACT_TILE_BYTES]"""
+    gy = _f32c(gy)
+    assert gy.numel() == st.b * st.np and st.acat is not None
+    p_tiles = (st.b * st.np + 127) // 128
+    dpc = _bytes(p_tiles * _abi.HEAD_OFFSETS * SLAB_BYTES, gy.device)
+    dtap = torch.empty(4, st.n_tiles * ACT_TILE_BYTES, dtype=torch.uint8, device=gy.device)
+    call('cn_grasp_head_bwd', _ptr(gy), st.n_tiles, st.b, st.n_pad, st.np, _ptr(st.pack), st.elu, _ptr(st.vslabs),
+         _ptr(st.acat), _ptr(st.saved), _ptr(dpc), _ptr(dtap), _stream())
+    return dtap
 
 
 def mlp_readout_bwd(params, d_y, acts, act_stride: int, act_index: int, grad):

@@ -17,7 +17,7 @@ from typing import List
 import torch
 
 from . import ops
-from ._abi import NET_PARAMS, TILE_ROWS
+from ._abi import HEAD_OFFSETS as _HEAD_OFFSETS, NET_PARAMS, TILE_ROWS
 
 
 def _pad_rows(t: torch.Tensor, n_pad: int) -> torch.Tensor:
@@ -124,6 +124,67 @@ class _QueryBwdFn(torch.autograd.Function):
             return torch.cat([u, u.new_zeros(b, n_pad - n, 3)], dim=1) if n_pad != n else u
         taps = query_tangent(st.scene, st.params, st.pts, st.drs, st.z, st.acts_f, st.acts_u, pad(u_pts), pad(u_dirs))
         return (None,) + tuple(t[:, :n] for t in taps)
+
+
+class _QueryGraspFn(torch.autograd.Function):
+    """query points -> grasp success with the affordance head on the CUDA kernels too (``cn_grasp_head_fwd`` /
+    ``_bwd``): the path of ``infer`` and of ``DNGFOptimizer.optimize_pose`` (grasp_optimizer.py:158-184), where the
+    field and the head are frozen and only d success / d (points, directions) is wanted.  The head's tap gradients
+    come back as bf16 tiles and join the gradient stream of the block backward directly.  Once differentiable;
+    training the head (``DeltaNGF.train_step``, double backward) uses ``query_embeddings`` + the torch head."""
+
+    @staticmethod
+    def forward(ctx, params, head_pack, features, images, intrinsics, extr_inv, points, dirs, n_poses, elu):
+        need_grad = ctx.needs_input_grad[6] or ctx.needs_input_grad[7]
+        scene = ops.Scene(images, features, intrinsics, extr_inv)
+        b, n, _ = points.shape
+        n_pad = (n + TILE_ROWS - 1) // TILE_ROWS * TILE_ROWS
+        pts, drs = _pad_rows(ops._f32c(points), n_pad), _pad_rows(ops._f32c(dirs), n_pad)
+        z = torch.zeros(b, n_pad, 1, dtype=torch.float32, device=pts.device)
+        packed = ops.pack_weights(params)
+        x, ws = ops.project_gather_fwd(scene, pts, drs, z, return_ws=True)
+        h3, acts_f = ops.mlp_feature_fwd(packed, x, need_grad)
+        taps, _rgbs, acts_u = ops.mlp_fusion_fwd_taps(packed, h3, b, scene.nv, need_grad)
+        y, head = ops.grasp_head_fwd(taps, b, n_pad, n_poses, head_pack, elu, need_grad)
+        if need_grad:
+            st = _State()
+            st.scene, st.params, st.packed, st.n = scene, None, packed, n
+            st.pts, st.drs, st.z, st.x, st.ws, st.acts_f, st.acts_u = pts, drs, z, None, ws, acts_f, acts_u
+            st.need = tuple(ctx.needs_input_grad)
+            ctx.state, ctx.head = st, head
+        return y
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, gy):
+        st, head = ctx.state, ctx.head
+        scene, packed, n = st.scene, st.packed, st.n
+        dev = st.z.device
+        dtap = ops.grasp_head_bwd(gy.contiguous(), head)
+        grad = torch.zeros(NET_PARAMS, dtype=torch.float32, device=dev)     # the frozen field's gradient: not returned
+        g = dtap[3]
+        for blk in (5, 4, 3):
+            ops.mlp_block_bwd(packed, blk, st.acts_u, ops.FUSION_ACTS, blk - 3, g, grad)
+            ops.tile_add_tiles(g, dtap[blk - 3])
+        s = 1.0 / scene.nv
+        gf = ops.mlp_block_bwd(packed, 2, st.acts_f, ops.FEATURE_ACTS, 2, g, grad, views=scene.nv, scale=s, b=scene.b) \
+            if scene.nv > 1 else ops.mlp_block_bwd(packed, 2, st.acts_f, ops.FEATURE_ACTS, 2, g, grad)
+        for blk in (1, 0):
+            ops.mlp_block_bwd(packed, blk, st.acts_f, ops.FEATURE_ACTS, blk, gf, grad, scale=s)
+        dx = ops.mlp_l0_dgrad(packed, gf, s)
+        d_o, d_d, _ = ops.project_gather_bwd_rays(scene, st.pts, st.drs, st.z, dx, st.ws)
+        need = st.need
+        return (None,) * 6 + ((d_o[:, :n].contiguous() if need[6] else None),
+                              (d_d[:, :n].contiguous() if need[7] else None), None, None)
+
+
+def query_grasp_success(params_fine: torch.Tensor, head_pack: torch.Tensor, images, intrinsics, extr_inv,
+                        combined_features, points, dirs, n_poses: int, elu: bool = True) -> torch.Tensor:
+    """grasp success [b, n_poses] of the poses whose 42 query points / directions are ``points`` / ``dirs``
+    [b, n_poses * 42, 3]: embedding + ``GraspReadout`` on the CUDA kernels, differentiable w.r.t. points and dirs."""
+    assert points.shape == dirs.shape and points.shape[1] == n_poses * _HEAD_OFFSETS
+    return _QueryGraspFn.apply(params_fine, head_pack, combined_features, images, intrinsics, extr_inv, points, dirs,
+                               int(n_poses), bool(elu))
 
 
 def query_embeddings(params_fine: torch.Tensor, images, intrinsics, extr_inv, combined_features, points, dirs

@@ -77,6 +77,8 @@ class GraspReadout(torch.nn.Module):
         if activation not in _ACT:
             raise ValueError(f'activation {activation} not supported')
         self.act = _ACT[activation]
+        self.activation = activation
+        self._pack_cache = None           # (versions, packed operand images) of the fused inference kernels
         self.tf32 = False                 # set by the models (``tf32_head``); plain fp32 when used stand-alone
         for i in range(1, 5):
             setattr(self, f'activation_downscale_{i}', torch.nn.Linear(128, 64))
@@ -105,6 +107,29 @@ class GraspReadout(torch.nn.Module):
             r = _linear(blk.layer_1, blk.act(_linear(blk.layer_0, blk.act(c), t)), t)
             c = (c if blk.shortcut is None else _linear(blk.shortcut, c, t)) + r
         return _linear(self.readout[2].output_layer, torch.relu(c), t)[..., 0]
+
+    # ---- fused inference path (cn_grasp_head_fwd / _bwd): frozen weights, gradient to the inputs only
+    def flat_keras(self):
+        """the variables as ONE fp32 vector in Keras order, kernel[in][out] (include/clipnerf_b200.h CN_HEAD_PARAMS)"""
+        named = self.named_keras_variables()
+        parts = [v.detach().reshape(-1) for v in named.values()]
+        if 'grasp_readout.readout.2.output_layer.bias' not in named:
+            parts.append(parts[0].new_zeros(1))
+        return torch.cat(parts).to(torch.float32)
+
+    def packed(self):
+        """bf16 operand images of the head's matrices, rebuilt only when a variable changed (tensor version counters)"""
+        from clipnerf_b200 import ops
+        params = list(self.parameters())
+        key = tuple((p.data_ptr(), p._version) for p in params)
+        if self._pack_cache is None or self._pack_cache[0] != key:
+            self._pack_cache = (key, ops.grasp_head_pack(self.flat_keras()))
+        return self._pack_cache[1]
+
+    def fused_available(self, n_offsets, grad_to_weights):
+        """the tcgen05 head covers 42 query offsets per pose and returns no parameter gradients"""
+        w0 = self.readout[0].layer_0.weight
+        return w0.is_cuda and n_offsets == 42 and w0.shape[1] == 42 * 64 and not grad_to_weights
 
     # ---- Keras-named view of the variables (kernel[in, out]), for parity tests and checkpoint interchange
     def named_keras_variables(self, prefix='grasp_readout', grad=False):

@@ -12,7 +12,7 @@ import os
 import numpy as np
 import torch
 
-from clipnerf_b200.query import pose_query_points, query_embeddings
+from clipnerf_b200.query import pose_query_points, query_embeddings, query_grasp_success
 from clipnerf_b200.trainer import allreduce_mean
 
 from ..mvnerf.layers import MVResNetMLPNeRFEmbedding
@@ -104,6 +104,7 @@ class _PoseQueryModel(torch.nn.Module):
         self.feature_fn = None
         self.optimizer = None
         self.loss = None
+        self.fused_head = True                # cn_grasp_head_* whenever no parameter / feature-map gradient is asked for
 
     @property
     def device(self):
@@ -132,6 +133,13 @@ class _PoseQueryModel(torch.nn.Module):
         if transforms.shape[0] != b or transforms.shape[1] != n_points:
             raise ValueError(f'transforms must be [{b}, {n_points}, 4, 4], got {tuple(transforms.shape)}')
         pts, dirs = pose_query_points(transforms.to(self.device), self.transforms_to_check)
+        head = self.grasp_readout
+        trains = torch.is_grad_enabled() and (any(p.requires_grad for p in head.parameters())
+                                              or self.fine_embedding.flat.requires_grad or feats.requires_grad)
+        if self.fused_head and head.fused_available(self.n_transforms_to_check, trains):
+            # inference / pose optimisation (frozen field): embedding AND head on the CUDA kernels, gradient to the poses
+            return query_grasp_success(self._net_params(), head.packed(), images, K, Einv, feats.to(self.device), pts, dirs,
+                                       n_points, elu=head.activation == 'elu')
         emb = query_embeddings(self._net_params(), images, K, Einv, feats.to(self.device), pts, dirs)
         emb = [e.reshape(b, n_points, self.n_transforms_to_check, 128) for e in emb]
         return self.grasp_readout(emb)
