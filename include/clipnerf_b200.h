@@ -237,6 +237,11 @@ int cn_mlp_fusion_fwd_taps(const void *packed, const void *h3_tiles, int32_t b, 
 /* g_tiles [n_tiles] (bf16 activation-tile images) = (accumulate ? g_tiles : 0) + rows [n_tiles*128][128] fp32:
  * the gradient of a tapped stage output joins the gradient stream of cn_mlp_block_bwd.        */
 int cn_tile_add_rows(void *g_tiles, const float *rows, int64_t n_tiles, int32_t accumulate, void *stream);
+/* cn_mlp_fusion_fwd_taps with the four stage outputs written as bf16 activation-tile images
+ * tap_tiles [4][b*tiles_per_view][32 KiB] -- the operand tiles cn_grasp_head_fwd consumes (half the bytes of the
+ * fp32 rows, no conversion pass).                                                               */
+int cn_mlp_fusion_fwd_tap_tiles(const void *packed, const void *h3_tiles, int32_t b, int32_t nv,
+                                int64_t tiles_per_view, float *rgbs, void *acts, void *tap_tiles, void *stream);
 /* g_tiles [n_tiles] += src_tiles [n_tiles] (both bf16 activation-tile images): the tap gradients cn_grasp_head_bwd
  * returns as tiles join the gradient stream without an fp32 round trip.                        */
 int cn_tile_add_tiles(void *g_tiles, const void *src_tiles, int64_t n_tiles, void *stream);
@@ -247,7 +252,8 @@ int cn_tile_add_tiles(void *g_tiles, const void *src_tiles, int64_t n_tiles, voi
  * R / n_pad, i = R % n_pad, pose i / 42 and offset i % 42 of that scene for i < np * 42 (padding rows are computed and
  * dropped).  n_tiles = b * n_pad / 128.  activation: 1 = elu, 0 = relu.
  *   cn_grasp_head_pack: params [CN_HEAD_PARAMS] fp32 -> pack [CN_HEAD_PACK_BYTES] (once per weight version).
- *   cn_grasp_head_fwd : taps [4][n_tiles*128][128] fp32 (cn_mlp_fusion_fwd_taps) -> y [b*np] fp32.  Kept for the
+ *   cn_grasp_head_fwd : tap_tiles [4][n_tiles][32 KiB] bf16 tile images (cn_mlp_fusion_fwd_tap_tiles, or fp32 rows
+ *     through cn_tile_add_rows) -> y [b*np] fp32.  Kept for the
  *     backward (caller-allocated, P = ceil(b*np / 128) pose tiles): vslabs [P][42][2][16 KiB] (the flattened
  *     'b np (n5 d)' activations and their second activation as bf16 K-chunks), acat (nullable) [n_tiles][64 KiB],
  *     saved [P][80 KiB] (activation outputs of the per-pose tail).
@@ -255,7 +261,7 @@ int cn_tile_add_tiles(void *g_tiles, const void *src_tiles, int64_t n_tiles, voi
  *     dpc_ws [P][42][16 KiB] is scratch.  No parameter gradients: training the head goes through the differentiable
  *     torch form (src/lib/delta_ngf/layers.py), which the double backward of DeltaNGF.train_step needs anyway.   */
 int cn_grasp_head_pack(const float *params, void *pack, void *stream);
-int cn_grasp_head_fwd(const float *taps, int64_t n_tiles, int32_t b, int32_t n_pad, int32_t np, const void *pack,
+int cn_grasp_head_fwd(const void *tap_tiles, int64_t n_tiles, int32_t b, int32_t n_pad, int32_t np, const void *pack,
                       int32_t activation, void *vslabs, void *acat, void *saved, float *y, void *stream);
 int cn_grasp_head_bwd(const float *gy, int64_t n_tiles, int32_t b, int32_t n_pad, int32_t np, const void *pack,
                       int32_t activation, const void *vslabs, const void *acat, const void *saved, void *dpc_ws,

@@ -306,6 +306,21 @@ def mlp_fusion_fwd_taps(packed, h3_tiles, b: int, nv: int, save_acts: bool):
     return taps, rgbs, acts
 
 
+def mlp_fusion_fwd_tap_tiles(packed, h3_tiles, b: int, nv: int, save_acts: bool):
+    """fusion stage returning the four `complete_output` stage outputs as bf16 activation-tile images
+    [4, n_tiles * ACT_TILE_BYTES] uint8 (the operand tiles of ``grasp_head_fwd``)."""
+    nt = h3_tiles.numel() // ACT_TILE_BYTES
+    assert nt % (b * nv) == 0
+    tpv = nt // (b * nv)
+    rows = b * tpv * TILE_ROWS
+    rgbs = torch.empty(rows, 4, dtype=torch.float32, device=h3_tiles.device)
+    taps = torch.empty(4, b * tpv * ACT_TILE_BYTES, dtype=torch.uint8, device=h3_tiles.device)
+    acts = _bytes(b * tpv * FUSION_ACTS * ACT_TILE_BYTES, h3_tiles.device) if save_acts else None
+    call('cn_mlp_fusion_fwd_tap_tiles', _ptr(packed), _ptr(h3_tiles), b, nv, tpv, _ptr(rgbs), _ptr(acts), _ptr(taps),
+         _stream())
+    return taps, rgbs, acts
+
+
 def tile_add_rows(g_tiles: Optional[torch.Tensor], rows: torch.Tensor) -> torch.Tensor:
     """g_tiles (bf16 tile images; created when None) (+)= rows [n_tiles*128, 128] fp32"""
     rows = _f32c(rows)
@@ -342,8 +357,13 @@ class HeadState:
 
 def grasp_head_fwd(taps: torch.Tensor, b: int, n_pad: int, n_poses_per_scene: int, pack: torch.Tensor, elu: bool,
                    save: bool):
-    """taps [4, b * n_pad, 128] fp32 (rows '(b (np n5))' padded per scene to n_pad) -> y [b, np], HeadState"""
-    assert taps.dtype == torch.float32 and taps.is_contiguous() and tuple(taps.shape) == (4, b * n_pad, 128)
+    """taps: bf16 activation-tile images uint8 [4, b * n_pad / 128 * ACT_TILE_BYTES] (``mlp_fusion_fwd_tap_tiles``),
+    or fp32 rows [4, b * n_pad, 128] (converted with ``tile_add_rows``); rows '(b (np n5))' padded per scene to
+    n_pad -> y [b, np], HeadState"""
+    if taps.dtype == torch.float32:
+        assert tuple(taps.shape) == (4, b * n_pad, 128)
+        taps = torch.stack([tile_add_rows(None, taps[s]) for s in range(4)])
+    assert taps.dtype == torch.uint8 and taps.is_contiguous() and tuple(taps.shape) == (4, b * n_pad // TILE_ROWS * ACT_TILE_BYTES)
     st = HeadState()
     st.n_tiles, st.b, st.n_pad, st.np, st.pack, st.elu = n_tiles(b * n_pad), b, n_pad, n_poses_per_scene, pack, int(elu)
     p_tiles = (b * n_poses_per_scene + 127) // 128

@@ -144,7 +144,7 @@ class _QueryGraspFn(torch.autograd.Function):
         packed = ops.pack_weights(params)
         x, ws = ops.project_gather_fwd(scene, pts, drs, z, return_ws=True)
         h3, acts_f = ops.mlp_feature_fwd(packed, x, need_grad)
-        taps, _rgbs, acts_u = ops.mlp_fusion_fwd_taps(packed, h3, b, scene.nv, need_grad)
+        taps, _rgbs, acts_u = ops.mlp_fusion_fwd_tap_tiles(packed, h3, b, scene.nv, need_grad)
         y, head = ops.grasp_head_fwd(taps, b, n_pad, n_poses, head_pack, elu, need_grad)
         if need_grad:
             st = _State()

@@ -8,7 +8,7 @@
 //
 // Four kernels.  "point" kernels work on the 128-row tiles of the fusion stage (rows = (scene, pose, offset)); "pose"
 // kernels on tiles of 128 poses whose 2688-wide input is streamed as 42 K-chunks of 64:
-//   grasp_point_fwd_kernel  taps (fp32 rows) -> bf16 operand tiles -> 4 + 1 GEMMs -> V slabs: per (pose tile, offset j) a
+//   grasp_point_fwd_kernel  taps (bf16 tiles written by the fusion stage's epilogues = the A operands) -> 4 + 1 GEMMs -> V slabs: per (pose tile, offset j) a
 //                           [128 poses x 64] bf16 slab of v and one of act(v), i.e. the K-chunks of the pose kernel's A operand,
 //                           written straight from the epilogue registers (the 'b np n5 d -> b np (n5 d)' rearrange is the store address)
 //   grasp_pose_fwd_kernel   TMA ring over the 42 chunks (V pair + W_0 chunk + W_sc chunk), two accumulators, then the
@@ -63,7 +63,9 @@ constexpr uint32_t kVPair = 2 * CN_SLAB_BYTES;                   // v slab | act
 constexpr uint32_t kSavedTile = 5 * CN_SLAB_BYTES;               // act(r0) (2 slabs) | act(o1) | act(r2) | relu(o2)
 constexpr uint32_t kAcatTile = 4 * CN_SLAB_BYTES;                // a_1 .. a_4
 
-__device__ __forceinline__ float act_fwd(float x, int elu) { return x > 0.f ? x : (elu ? expm1f(x) : 0.f); }
+// elu's negative branch as ex2.approx(x log2 e) - 1: absolute error ~1e-7 (the cancellation near 0 costs relative, not
+// absolute, accuracy), far inside the bf16 rounding of the stored output; expm1f made the forward epilogues 2x longer
+__device__ __forceinline__ float act_fwd(float x, int elu) { return x > 0.f ? x : (elu ? __expf(x) - 1.f : 0.f); }
 // derivative of the activation from its OUTPUT y
 __device__ __forceinline__ float act_der(float y, int elu) { return y > 0.f ? 1.f : (elu ? y + 1.f : 0.f); }
 
@@ -126,28 +128,45 @@ __device__ __forceinline__ bool row_pose(const HeadGeom &g, int64_t R, int &pose
 // ------------------------------------------------------------------------------------------------ point forward
 constexpr int kPtThreads = 256;
 constexpr uint32_t kPfSmemW = 0;                       // pack [0, 98304): W_1..4 (4 x 16 KiB), W_c (32 KiB)
-constexpr uint32_t kPfSmemA = 98304;                   // 2 x 32 KiB tap operand tiles = the 4 slabs of [a_1 .. a_4]
-constexpr uint32_t kPfSmemBytes = kPfSmemA + 2 * CN_ACT_TILE_BYTES + 1024;
+constexpr uint32_t kPfSmemA = 98304;                   // 2 x 32 KiB tap operand tiles (TMA ring)
+constexpr uint32_t kPfSmemCat = kPfSmemA + 2 * CN_ACT_TILE_BYTES;   // [a_1 .. a_4]: 4 slabs
+constexpr uint32_t kPfSmemBytes = kPfSmemCat + kAcatTile + 1024;
 
+// taps: bf16 activation-tile images [4][n_tiles][32 KiB] (cn_mlp_fusion_fwd_tap_tiles): a tap tile IS the A operand
+// of its GEMM, one bulk copy each through a two-slot ring.  Thread 0 feeds the ring and issues the GEMMs; the loads
+// of the next tile's first two taps fly under this tile's epilogues.
 __global__ void __launch_bounds__(kPtThreads, 1)
-grasp_point_fwd_kernel(const float *__restrict__ taps, int64_t tap_stride, const uint8_t *__restrict__ pack, HeadGeom g,
+grasp_point_fwd_kernel(const uint8_t *__restrict__ taps, int64_t tap_stride, const uint8_t *__restrict__ pack, HeadGeom g,
                        uint8_t *__restrict__ vslabs, uint8_t *__restrict__ acat) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bar_w, bar_mma[2], bar_c;
+  __shared__ __align__(8) uint64_t bar_w, bar_full[2], bar_mma[2], bar_taps, bar_c;
   __shared__ uint32_t tmem_slot;
   __shared__ float s_bias[320];
   uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const uint32_t s_base = smem_u32(smem);
   const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
   for (int i = tid; i < 320; i += kPtThreads) s_bias[i] = reinterpret_cast<const float *>(pack + kHeadTab)[i];
+  auto load_tap = [&](int64_t tile, int s) {           // thread 0 only
+    const uint32_t buf = (uint32_t)s & 1u;
+    mbar_expect_tx(smem_u32(&bar_full[buf]), CN_ACT_TILE_BYTES);
+    bulk_g2s(s_base + kPfSmemA + buf * CN_ACT_TILE_BYTES, taps + s * tap_stride + tile * (int64_t)CN_ACT_TILE_BYTES,
+             CN_ACT_TILE_BYTES, smem_u32(&bar_full[buf]));
+  };
   if (tid == 0) {
     mbar_init(smem_u32(&bar_w), 1);
-    mbar_init(smem_u32(&bar_mma[0]), 1);
-    mbar_init(smem_u32(&bar_mma[1]), 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&bar_full[i]), 1);
+      mbar_init(smem_u32(&bar_mma[i]), 1);
+    }
+    mbar_init(smem_u32(&bar_taps), 1);
     mbar_init(smem_u32(&bar_c), 1);
     fence_barrier_init();
     mbar_expect_tx(smem_u32(&bar_w), 98304);
     bulk_g2s(s_base + kPfSmemW, pack, 98304, smem_u32(&bar_w));
+    if ((int64_t)blockIdx.x < g.n_tiles) {
+      load_tap(blockIdx.x, 0);
+      load_tap(blockIdx.x, 1);
+    }
   }
   if (warp == 0) {
     tmem_alloc(smem_u32(&tmem_slot), 512);
@@ -161,42 +180,14 @@ grasp_point_fwd_kernel(const float *__restrict__ taps, int64_t tap_stride, const
   const uint32_t lane_off = (quad * 32u) << 16;
   constexpr uint32_t idesc64 = umma_idesc(128, 64, 0, 0);
 
-  float4 r[16];
-  auto load_tap = [&](int64_t tile, int s) {
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const uint32_t q = tid + 256u * i;
-      const float *src = taps + s * tap_stride + (tile * 128 + (q >> 4)) * 128 + (q & 15u) * 8;
-      r[2 * i] = ldg_nc_f4(src);
-      r[2 * i + 1] = ldg_nc_f4(src + 4);
-    }
-  };
-  uint32_t ph[2] = {0, 0}, phc = 0;
-  int64_t tile = blockIdx.x;
-  if (tile < g.n_tiles) load_tap(tile, 0);
-  bool first = true;
-  for (; tile < g.n_tiles; tile += gridDim.x) {
-    for (int s = 0; s < 4; ++s) {
-      const uint32_t buf = (uint32_t)s & 1u;
-      if (s >= 2) {                                   // the GEMM that read this buffer two taps ago is done
-        mbar_wait(smem_u32(&bar_mma[buf]), ph[buf] & 1u);
-        ++ph[buf];
-      }
-      uint8_t *A = smem + kPfSmemA + buf * CN_ACT_TILE_BYTES;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const uint32_t q = tid + 256u * i;
-        *reinterpret_cast<uint4 *>(A + tile_chunk_off(q >> 4, q & 15u)) =
-            make_uint4(pack_bf16x2(r[2 * i].x, r[2 * i].y), pack_bf16x2(r[2 * i].z, r[2 * i].w),
-                       pack_bf16x2(r[2 * i + 1].x, r[2 * i + 1].y), pack_bf16x2(r[2 * i + 1].z, r[2 * i + 1].w));
-      }
-      // the next tap's rows are requested before this one's GEMM is issued: they fly under the GEMMs and epilogues
-      if (s < 3) load_tap(tile, s + 1);
-      else if (tile + gridDim.x < g.n_tiles) load_tap(tile + gridDim.x, 0);
-      fence_proxy_async_smem();
-      __syncthreads();
-      if (tid == 0) {
-        if (first) mbar_wait(smem_u32(&bar_w), 0);
+  uint32_t it = 0;
+  for (int64_t tile = blockIdx.x; tile < g.n_tiles; tile += gridDim.x, ++it) {
+    if (tid == 0) {
+      if (it == 0) mbar_wait(smem_u32(&bar_w), 0);
+      const int64_t next = tile + gridDim.x;
+      for (int s = 0; s < 4; ++s) {
+        const uint32_t buf = (uint32_t)s & 1u, ph = (2u * it + ((uint32_t)s >> 1)) & 1u;   // 2 fills per slot and tile
+        mbar_wait(smem_u32(&bar_full[buf]), ph);
         tc_fence_after();
         const uint32_t a = s_base + kPfSmemA + buf * CN_ACT_TILE_BYTES, w = s_base + kPfSmemW + s * img(64, 128);
 #pragma unroll
@@ -206,22 +197,25 @@ grasp_point_fwd_kernel(const float *__restrict__ taps, int64_t tap_stride, const
             umma_f16(tmem + s * 64, umma_desc(a + sl * CN_SLAB_BYTES + k * kKmajKstep, kKmajLbo, kSboBytes),
                      umma_desc(w + sl * 8192 + k * kKmajKstep, kKmajLbo, kSboBytes), idesc64, (sl | k) ? 1u : 0u);
         umma_commit(smem_u32(&bar_mma[buf]));
+        if (s == 3) umma_commit(smem_u32(&bar_taps));
+        // refill the slot with the tap two ahead once this GEMM has read it
+        if (s < 2 || next < g.n_tiles) {
+          mbar_wait(smem_u32(&bar_mma[buf]), ph);
+          if (s < 2) load_tap(tile, s + 2);
+          else load_tap(next, s - 2);
+        }
       }
-      first = false;
     }
-    for (int buf = 0; buf < 2; ++buf) {
-      mbar_wait(smem_u32(&bar_mma[buf]), ph[buf] & 1u);
-      ++ph[buf];
-    }
+    mbar_wait(smem_u32(&bar_taps), it & 1u);
     tc_fence_after();
-    // ---- a_s = act(tap_s W_s + b_s) -> slab s of the [128 x 256] operand (over the tap tiles: their GEMMs are done)
+    // ---- a_s = act(tap_s W_s + b_s) -> slab s of the [128 x 256] operand of the combined downscale
     for (int ss = 0; ss < 2; ++ss) {
       const int s = 2 * (int)half + ss;
       uint32_t v[64];
       tmem_ld32(tmem + lane_off + s * 64, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
       tmem_ld32(tmem + lane_off + s * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
       tmem_wait_ld();
-      uint8_t *dst = smem + kPfSmemA + s * CN_SLAB_BYTES + row * 128u;
+      uint8_t *dst = smem + kPfSmemCat + s * CN_SLAB_BYTES + row * 128u;
 #pragma unroll
       for (int c8 = 0; c8 < 8; ++c8) {
         float a[8];
@@ -236,7 +230,7 @@ grasp_point_fwd_kernel(const float *__restrict__ taps, int64_t tap_stride, const
     __syncthreads();
     if (tid == 0) {
       tc_fence_after();
-      const uint32_t a = s_base + kPfSmemA, w = s_base + kPfSmemW + kHfComb;
+      const uint32_t a = s_base + kPfSmemCat, w = s_base + kPfSmemW + kHfComb;
 #pragma unroll
       for (int sl = 0; sl < 4; ++sl)
 #pragma unroll
@@ -249,8 +243,7 @@ grasp_point_fwd_kernel(const float *__restrict__ taps, int64_t tap_stride, const
         bulk_commit();
       }
     }
-    mbar_wait(smem_u32(&bar_c), phc & 1u);
-    ++phc;
+    mbar_wait(smem_u32(&bar_c), it & 1u);
     tc_fence_after();
     // ---- c = act(. + b_c): this thread's 32 columns go to row (pose % 128) of the V slabs of (pose tile, offset j)
     {
@@ -873,11 +866,11 @@ extern "C" int cn_grasp_head_pack(const float *params, void *pack, void *stream)
   return check_launch("cn_grasp_head_pack");
 }
 
-extern "C" int cn_grasp_head_fwd(const float *taps, int64_t n_tiles, int32_t b, int32_t n_pad, int32_t np, const void *pack,
+extern "C" int cn_grasp_head_fwd(const void *tap_tiles, int64_t n_tiles, int32_t b, int32_t n_pad, int32_t np, const void *pack,
                                  int32_t activation, void *vslabs, void *acat, void *saved, float *y, void *stream) {
   using namespace cn;
-  CN_REQUIRE(taps && pack && vslabs && saved && y, "cn_grasp_head_fwd: null pointer");
-  CN_REQUIRE((((uintptr_t)taps | (uintptr_t)pack | (uintptr_t)vslabs | (uintptr_t)acat | (uintptr_t)saved) & 127) == 0,
+  CN_REQUIRE(tap_tiles && pack && vslabs && saved && y, "cn_grasp_head_fwd: null pointer");
+  CN_REQUIRE((((uintptr_t)tap_tiles | (uintptr_t)pack | (uintptr_t)vslabs | (uintptr_t)acat | (uintptr_t)saved) & 127) == 0,
              "cn_grasp_head_fwd: buffers must be 128-byte aligned");
   HeadGeom g;
   if (int rc = head_geom(g, n_tiles, b, n_pad, np, activation, "cn_grasp_head_fwd")) return rc;
@@ -885,7 +878,8 @@ extern "C" int cn_grasp_head_fwd(const float *taps, int64_t n_tiles, int32_t b, 
   if (int rc = set_smem(grasp_pose_fwd_kernel, kPsSmemBytes, "cn_grasp_head_fwd")) return rc;
   const unsigned grid = (unsigned)(n_tiles < num_sms() ? n_tiles : num_sms());
   grasp_point_fwd_kernel<<<grid, kPtThreads, kPfSmemBytes, (cudaStream_t)stream>>>(
-      taps, n_tiles * (int64_t)(128 * 128), (const uint8_t *)pack, g, (uint8_t *)vslabs, (uint8_t *)acat);
+      (const uint8_t *)tap_tiles, n_tiles * (int64_t)CN_ACT_TILE_BYTES, (const uint8_t *)pack, g, (uint8_t *)vslabs,
+      (uint8_t *)acat);
   if (int rc = check_launch("cn_grasp_head_fwd (points)")) return rc;
   const unsigned p_tiles = (unsigned)((g.n_poses + 127) / 128);
   grasp_pose_fwd_kernel<<<p_tiles, kPoseThreads, kPsSmemBytes, (cudaStream_t)stream>>>(

@@ -58,9 +58,11 @@ struct FwdBars {
 // of the swizzled activation tile in shared memory.  Both 32-column loads are issued before the wait.
 // `tap` (optional): this row's 128 fp32 pre-activation values (h + bias) are also written there -- the stage
 // outputs MVResNetMLPNeRFEmbedding(complete_output=True) returns (layers.py:364-377).
+// `tap16` (optional): the same values as a bf16 activation-tile image (this thread writes its row's 128-byte line).
 template <bool kRelu>
 __device__ __forceinline__ void epi_tmem_to_act(uint32_t taddr, const float *__restrict__ bias, uint8_t *act,
-                                                uint32_t row, uint32_t half, float *__restrict__ tap = nullptr) {
+                                                uint32_t row, uint32_t half, float *__restrict__ tap = nullptr,
+                                                uint8_t *__restrict__ tap16 = nullptr) {
   uint32_t r[64];
   tmem_ld32(taddr + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
   tmem_ld32(taddr + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
@@ -78,6 +80,9 @@ __device__ __forceinline__ void epi_tmem_to_act(uint32_t taddr, const float *__r
       *reinterpret_cast<float4 *>(tap + half * 64 + q * 8) = make_float4(v[0], v[1], v[2], v[3]);
       *reinterpret_cast<float4 *>(tap + half * 64 + q * 8 + 4) = make_float4(v[4], v[5], v[6], v[7]);
     }
+    if (tap16)
+      *reinterpret_cast<uint4 *>(tap16 + tile_chunk_off(row, half * 8 + q)) =
+          make_uint4(cvt_bf16x2(v[0], v[1]), cvt_bf16x2(v[2], v[3]), cvt_bf16x2(v[4], v[5]), cvt_bf16x2(v[6], v[7]));
     uint4 o;
     if (kRelu)  // relu folded into the conversion (F2FP.RELU): the epilogue is issue bound
       o = make_uint4(cvt_relu_bf16x2(v[0], v[1]), cvt_relu_bf16x2(v[2], v[3]), cvt_relu_bf16x2(v[4], v[5]),
@@ -92,7 +97,7 @@ template <bool kFusion>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ in_tiles, int64_t n_tiles,
                int nv, int64_t tiles_per_view, uint8_t *__restrict__ out_tiles, float *__restrict__ rgbs,
-               uint8_t *__restrict__ acts, float *__restrict__ taps) {
+               uint8_t *__restrict__ acts, float *__restrict__ taps, int tap_bf16) {
   using L = FwdSmem<kFusion>;
   constexpr int kRingSlots = L::kRingSlots;
   extern __shared__ uint8_t smem_raw[];
@@ -354,7 +359,11 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
       uint8_t *my_acts = acts ? acts + tile * (int64_t)kActsPerTile * CN_ACT_TILE_BYTES : nullptr;
       // fusion stage, pose-query models: taps[s][row][128] fp32, s = (mean, block 4, block 5, block 6 output)
       const int64_t tap_stride = n_tiles * (int64_t)(128 * 128);
-      float *my_tap = (kFusion && taps) ? taps + (tile * 128 + row) * 128 : nullptr;
+      float *my_tap = (kFusion && taps && !tap_bf16) ? taps + (tile * 128 + row) * 128 : nullptr;
+      // ... or as bf16 activation-tile images [4][n_tiles][32 KiB] (the operand tiles of cn_grasp_head_fwd)
+      const int64_t tap16_stride = n_tiles * (int64_t)CN_ACT_TILE_BYTES;
+      uint8_t *my_tap16 = (kFusion && taps && tap_bf16)
+                              ? reinterpret_cast<uint8_t *>(taps) + tile * (int64_t)CN_ACT_TILE_BYTES : nullptr;
 
       if (kFusion) {
         // ---- mean over views -> fp32 residual stream in TMEM, relu(mean) -> first MMA operand
@@ -412,6 +421,10 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
               *reinterpret_cast<float4 *>(my_tap + chunk * 8) = make_float4(m[0], m[1], m[2], m[3]);
               *reinterpret_cast<float4 *>(my_tap + chunk * 8 + 4) = make_float4(m[4], m[5], m[6], m[7]);
             }
+            if (my_tap16)
+              *reinterpret_cast<uint4 *>(my_tap16 + tile_chunk_off(row, chunk)) =
+                  make_uint4(pack_bf16x2(m[0], m[1]), pack_bf16x2(m[2], m[3]), pack_bf16x2(m[4], m[5]),
+                             pack_bf16x2(m[6], m[7]));
 #pragma unroll
             for (int i = 0; i < 8; ++i) m[i] = fmaxf(m[i], 0.f);
             *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, chunk)) =
@@ -443,7 +456,8 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
           // E_a: relu(h + cumulative bias) -> operand of the block's first Dense
           acquire();
           epi_tmem_to_act<true>(t_h, tab + (2 * blk) * 128, act, row, half,
-                                (kFusion && my_tap) ? my_tap + blk * tap_stride : nullptr);
+                                (kFusion && my_tap) ? my_tap + blk * tap_stride : nullptr,
+                                (kFusion && my_tap16) ? my_tap16 + blk * tap16_stride : nullptr);
           publish(my_acts ? my_acts + blk * CN_ACT_TILE_BYTES : nullptr, true);
           if (tr && blk == 0) CN_TRACE_AT(pi, 9);
         }
@@ -499,14 +513,20 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
                 yb += v[i] * w.y;
               }
             }
-            if (my_tap && mine) {
+            if ((my_tap || my_tap16) && mine) {
               // e itself (pre-ReLU) is the tap; v[] holds relu(e), so re-add from the accumulator
               float ev[8];
 #pragma unroll
               for (int i = 0; i < 8; ++i) ev[i] = __uint_as_float(r[q * 8 + i]) + tab[6 * 128 + c4 * 32 + q * 8 + i];
-              float *dst = my_tap + 3 * tap_stride + c4 * 32 + q * 8;
-              *reinterpret_cast<float4 *>(dst) = make_float4(ev[0], ev[1], ev[2], ev[3]);
-              *reinterpret_cast<float4 *>(dst + 4) = make_float4(ev[4], ev[5], ev[6], ev[7]);
+              if (my_tap) {
+                float *dst = my_tap + 3 * tap_stride + c4 * 32 + q * 8;
+                *reinterpret_cast<float4 *>(dst) = make_float4(ev[0], ev[1], ev[2], ev[3]);
+                *reinterpret_cast<float4 *>(dst + 4) = make_float4(ev[4], ev[5], ev[6], ev[7]);
+              } else {
+                *reinterpret_cast<uint4 *>(my_tap16 + 3 * tap16_stride + tile_chunk_off(row, c4 * 4 + q)) =
+                    make_uint4(pack_bf16x2(ev[0], ev[1]), pack_bf16x2(ev[2], ev[3]), pack_bf16x2(ev[4], ev[5]),
+                               pack_bf16x2(ev[6], ev[7]));
+              }
             }
             if (my_acts && mine)
               *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, c4 * 4 + q)) =
@@ -538,7 +558,7 @@ CN_TRACE_READER(cn_debug_read_trace_fwd)
 
 static int launch_fwd(bool fusion, const void *packed, const void *in_tiles, int64_t n_tiles, int nv,
                       int64_t tiles_per_view, void *out_tiles, float *rgbs, void *acts, float *taps,
-                      cudaStream_t st) {
+                      cudaStream_t st, int tap_bf16 = 0) {
   const int64_t n_pairs = (n_tiles + 1) / 2;
   const unsigned grid = (unsigned)(n_pairs < num_sms() ? n_pairs : num_sms());
   cudaError_t e;
@@ -548,14 +568,14 @@ static int launch_fwd(bool fusion, const void *packed, const void *in_tiles, int
     if (e == cudaSuccess)
       mlp_fwd_kernel<true><<<grid, kFwdThreads, bytes, st>>>((const uint8_t *)packed, (const uint8_t *)in_tiles,
                                                              n_tiles, nv, tiles_per_view, (uint8_t *)out_tiles, rgbs,
-                                                             (uint8_t *)acts, taps);
+                                                             (uint8_t *)acts, taps, tap_bf16);
   } else {
     constexpr uint32_t bytes = FwdSmem<false>::kBytes;
     e = cudaFuncSetAttribute(mlp_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e == cudaSuccess)
       mlp_fwd_kernel<false><<<grid, kFwdThreads, bytes, st>>>((const uint8_t *)packed, (const uint8_t *)in_tiles,
                                                               n_tiles, nv, tiles_per_view, (uint8_t *)out_tiles, rgbs,
-                                                              (uint8_t *)acts, nullptr);
+                                                              (uint8_t *)acts, nullptr, 0);
   }
   if (e != cudaSuccess) {
     set_error("mlp_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
@@ -602,4 +622,17 @@ extern "C" int cn_mlp_fusion_fwd_taps(const void *packed, const void *h3_tiles, 
   if (tiles_per_view == 0) return 0;
   return launch_fwd(true, packed, h3_tiles, (int64_t)b * tiles_per_view, nv, tiles_per_view, nullptr, rgbs, acts,
                     taps, (cudaStream_t)stream);
+}
+
+extern "C" int cn_mlp_fusion_fwd_tap_tiles(const void *packed, const void *h3_tiles, int32_t b, int32_t nv,
+                                           int64_t tiles_per_view, float *rgbs, void *acts, void *tap_tiles, void *stream) {
+  using namespace cn;
+  CN_REQUIRE(packed && h3_tiles && rgbs && tap_tiles, "cn_mlp_fusion_fwd_tap_tiles: null pointer");
+  CN_REQUIRE(b > 0 && nv > 0 && tiles_per_view >= 0, "cn_mlp_fusion_fwd_tap_tiles: b=%d nv=%d tiles_per_view=%lld", b, nv,
+             (long long)tiles_per_view);
+  CN_REQUIRE((((uintptr_t)packed | (uintptr_t)h3_tiles | (uintptr_t)rgbs | (uintptr_t)acts | (uintptr_t)tap_tiles) & 127) == 0,
+             "cn_mlp_fusion_fwd_tap_tiles: buffers must be 128-byte aligned");
+  if (tiles_per_view == 0) return 0;
+  return launch_fwd(true, packed, h3_tiles, (int64_t)b * tiles_per_view, nv, tiles_per_view, nullptr, rgbs, acts,
+                    (float *)tap_tiles, (cudaStream_t)stream, 1);
 }
