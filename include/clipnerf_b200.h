@@ -246,6 +246,15 @@ int cn_mlp_fusion_fwd_tap_tiles(const void *packed, const void *h3_tiles, int32_
  * returns as tiles join the gradient stream without an fp32 round trip.                        */
 int cn_tile_add_tiles(void *g_tiles, const void *src_tiles, int64_t n_tiles, void *stream);
 
+/* poses = transforms @ transforms_to_check (delta_ngf/model.py:199-200, 221-223; same lines in lmvnerf/model_v4.py,
+ * grasp_mvnerf/model.py): transforms [n_poses][4][4] (bottom row [0 0 0 1]), transforms_to_check [n5][4][4] ->
+ * query points and approach directions [n_poses * n5][3] in '(np n5)' row order, and the backward to the pose
+ * matrices (d_transforms [n_poses][4][4], bottom row zero).                                      */
+int cn_pose_points_fwd(const float *transforms, const float *transforms_to_check, int64_t n_poses, int32_t n5,
+                       float *points, float *dirs, void *stream);
+int cn_pose_points_bwd(const float *d_points, const float *d_dirs, const float *transforms_to_check, int64_t n_poses,
+                       int32_t n5, float *d_transforms, void *stream);
+
 /* ---- GraspReadout.call (delta_ngf/layers.py:30-42; relu variant grasp_mvnerf/layers.py:22-31) on tcgen05, and its
  * backward to the four stage outputs -- the gradient DNGFOptimizer.optimize_pose takes (grasp_optimizer.py:158-184).
  * Rows are the fusion-stage rows of the pose-query call, '(b (np n5))' padded per scene: row R belongs to scene
@@ -279,7 +288,9 @@ int cn_mlp_readout_bwd(const float *params, const float *d_y, const void *acts, 
  * (b, v, t) reads the fusion-stage gradient tile (b, t) of gy_tiles [b][gy_tiles_per_view]
  * (gh_tiles must then be a separate [n_tiles] buffer) and `scale` = 1/nv multiplies what is
  * accumulated into grad, in fp32 (the bf16 g stream itself stays unscaled; every later
- * per-view stage kernel takes the same scale).  gy_views = 1, scale = 1: plain block.   */
+ * per-view stage kernel takes the same scale).  gy_views = 1, scale = 1: plain block.
+ * grad == NULL: only g_h is formed (no weight-gradient GEMMs) -- the backward of a frozen
+ * field to the query poses (grasp_optimizer.py:158-184).                                 */
 int cn_mlp_block_bwd(const void *packed, int32_t blk, const void *acts, int32_t act_stride_tiles,
                      int32_t act_index, int64_t n_tiles, const void *gy_tiles, int32_t gy_views,
                      int64_t gy_tiles_per_view, void *gh_tiles, float scale, float *grad, void *stream);

@@ -150,3 +150,30 @@ def test_frozen_field_call_uses_the_fused_head(cuda, rep):
         print(f'[fused {rep}] grad {name}: median {med:.2e} p90 {p90:.2e} max {mx:.2e} L2 {l2:.2e}; '
               f'vs torch head L2 {_row_stats(got, gt_t if name == "translations" else gr_t)[3]:.2e}')
         assert p90 < 2e-2 and l2 < 5e-2, (name, med, p90, mx, l2)
+
+
+def test_pose_points_kernels_match_the_broadcast_form(cuda):
+    """cn_pose_points_fwd / _bwd against the torch broadcast algebra (the CPU branch of pose_query_points):
+    forward, backward and the backward's own backward (the double backward of DeltaNGF.train_step)."""
+    from clipnerf_b200.query import pose_query_points
+    from src.lib.delta_ngf.model import build_transforms_to_check
+    g = torch.Generator().manual_seed(3)
+    ttc = build_transforms_to_check(7)
+    M = torch.randn(2, 37, 4, 4, generator=g)
+    M[..., 3, :] = torch.tensor([0.0, 0.0, 0.0, 1.0])
+    wp, wd = torch.randn(2, 37 * 42, 3, generator=g), torch.randn(2, 37 * 42, 3, generator=g)
+    v = torch.randn(2, 37, 4, 4, generator=g)
+
+    def run(dev):
+        m = M.to(dev).requires_grad_(True)
+        a, c = wp.to(dev).requires_grad_(True), wd.to(dev).requires_grad_(True)
+        pts, dirs = pose_query_points(m, ttc.to(dev))
+        gm, = torch.autograd.grad((pts * a).sum() + (dirs * c).sum(), m, create_graph=True)
+        ga, gc = torch.autograd.grad((gm * v.to(dev)).sum(), [a, c])          # d/d(weights) of <dM, v>
+        return [t.detach().cpu() for t in (pts, dirs, gm, ga, gc)]
+    ref, got = run(torch.device('cpu')), run(cuda)
+    assert rel_err(got[0], ref[0]) < 1e-6 and rel_err(got[1], ref[1]) < 1e-6      # (the kernel contracts to FMAs)
+    for name, a, c in zip(('dM', 'second-order d_pts', 'second-order d_dirs'), got[2:], ref[2:]):
+        if name == 'dM':
+            a, c = a[..., :3, :], c[..., :3, :]
+        assert rel_err(a, c) < 1e-5, (name, rel_err(a, c))

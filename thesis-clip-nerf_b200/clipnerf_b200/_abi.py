@@ -60,6 +60,8 @@ PROTOTYPES = {
     'cn_tile_add_rows': [_P, _P, c_int64, c_int32, _P],
     'cn_mlp_fusion_fwd_tap_tiles': [_P, _P, c_int32, c_int32, c_int64, _P, _P, _P, _P],
     'cn_tile_add_tiles': [_P, _P, c_int64, _P],
+    'cn_pose_points_fwd': [_P, _P, c_int64, c_int32, _P, _P, _P],
+    'cn_pose_points_bwd': [_P, _P, _P, c_int64, c_int32, _P, _P],
     'cn_grasp_head_pack': [_P, _P, _P],
     'cn_grasp_head_fwd': [_P, c_int64, c_int32, c_int32, c_int32, _P, c_int32, _P, _P, _P, _P, _P],
     'cn_grasp_head_bwd': [_P, c_int64, c_int32, c_int32, c_int32, _P, c_int32, _P, _P, _P, _P, _P, _P],

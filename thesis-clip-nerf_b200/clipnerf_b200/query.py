@@ -161,7 +161,7 @@ class _QueryGraspFn(torch.autograd.Function):
         scene, packed, n = st.scene, st.packed, st.n
         dev = st.z.device
         dtap = ops.grasp_head_bwd(gy.contiguous(), head)
-        grad = torch.zeros(NET_PARAMS, dtype=torch.float32, device=dev)     # the frozen field's gradient: not returned
+        grad = None                                   # frozen field: the block backwards form no weight gradients
         g = dtap[3]
         for blk in (5, 4, 3):
             ops.mlp_block_bwd(packed, blk, st.acts_u, ops.FUSION_ACTS, blk - 3, g, grad)
@@ -199,15 +199,67 @@ def query_embeddings(params_fine: torch.Tensor, images, intrinsics, extr_inv, co
     return list(_QueryEmbedFn.apply(params_fine, combined_features, images, intrinsics, extr_inv, points, dirs))
 
 
+class _PosePointsFn(torch.autograd.Function):
+    """transforms [b, np, 4, 4] -> (points, dirs) [b, np * n5, 3] on the device kernels (cn_pose_points_fwd / _bwd);
+    its backward is linear in the incoming gradients and written with the same kernel, so the double backward of
+    DeltaNGF.train_step passes through it."""
+
+    @staticmethod
+    def forward(ctx, transforms, ttc):
+        b, n_poses = transforms.shape[:2]
+        n5 = ttc.shape[0]
+        M, ttc = ops._f32c(transforms), ops._f32c(ttc)
+        pts = torch.empty(b, n_poses * n5, 3, dtype=torch.float32, device=M.device)
+        dirs = torch.empty_like(pts)
+        ops.call('cn_pose_points_fwd', ops._ptr(M), ops._ptr(ttc), b * n_poses, n5, ops._ptr(pts), ops._ptr(dirs), ops._stream())
+        ctx.save_for_backward(ttc)
+        ctx.shape = (b, n_poses, n5)
+        return pts, dirs
+
+    @staticmethod
+    def backward(ctx, d_pts, d_dirs):
+        ttc, = ctx.saved_tensors
+        return _PosePointsBwdFn.apply(d_pts, d_dirs, ttc, ctx.shape), None
+
+
+class _PosePointsBwdFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, d_pts, d_dirs, ttc, shape):
+        b, n_poses, n5 = shape
+        z = None
+        if d_pts is None or d_dirs is None:
+            z = torch.zeros(b, n_poses * n5, 3, dtype=torch.float32, device=ttc.device)
+        d_pts = ops._f32c(d_pts) if d_pts is not None else z
+        d_dirs = ops._f32c(d_dirs) if d_dirs is not None else z
+        dM = torch.empty(b, n_poses, 4, 4, dtype=torch.float32, device=ttc.device)
+        ops.call('cn_pose_points_bwd', ops._ptr(d_pts), ops._ptr(d_dirs), ops._ptr(ttc), b * n_poses, n5, ops._ptr(dM),
+                 ops._stream())
+        ctx.save_for_backward(ttc)
+        return dM
+
+    @staticmethod
+    def backward(ctx, u):
+        # dM = sum_j d_pt c_j^T + d_dir z_j^T is linear in (d_pts, d_dirs): its adjoint is the forward map applied to u
+        ttc, = ctx.saved_tensors
+        u = ops._f32c(u)                                  # (the kernel reads rows 0..2 of every matrix only)
+        b, n_poses = u.shape[:2]
+        n5 = ttc.shape[0]
+        g_pts = torch.empty(b, n_poses * n5, 3, dtype=torch.float32, device=u.device)
+        g_dirs = torch.empty_like(g_pts)
+        ops.call('cn_pose_points_fwd', ops._ptr(u), ops._ptr(ttc), b * n_poses, n5, ops._ptr(g_pts), ops._ptr(g_dirs),
+                 ops._stream())
+        return g_pts, g_dirs, None, None
+
+
 def pose_query_points(transforms: torch.Tensor, transforms_to_check: torch.Tensor):
     """poses = transforms . transforms_to_check (delta_ngf/model.py:199-200, 221): transforms [b, np, 4, 4],
     transforms_to_check [n5, 4, 4] -> query points and approach directions [b, np * n5, 3] in the row order
-    '(np n5)' the embedding / GraspReadout use (model.py:228-238).  Tiny host-side torch algebra (np * n5 4x4
-    products); autograd carries the pose gradient through it."""
+    '(np n5)' the embedding / GraspReadout use (model.py:228-238): point = R c_j + t, direction = R (C_j[:3, :3] z)
+    (the bottom row of M is [0 0 0 1], C_j[3, 3] = 1).  CUDA tensors go through cn_pose_points_fwd / _bwd."""
+    if transforms.is_cuda:
+        return _PosePointsFn.apply(transforms, transforms_to_check.to(transforms.device))
     ttc = transforms_to_check.to(transforms.dtype)
     R, t = transforms[:, :, :3, :3], transforms[:, :, :3, 3]
-    # rows of M . C_j written out (the bottom row of M is [0 0 0 1], C_j[3, 3] = 1): point = R c_j + t,
-    # direction = R (C_j[:3, :3] z); broadcast products instead of 4x4 batched GEMMs
     pts = (R[:, :, None] * ttc[None, None, :, None, :3, 3]).sum(-1) + t[:, :, None]
     dirs = (R[:, :, None] * ttc[None, None, :, None, :3, 2]).sum(-1)
     b, n_pts, n5 = pts.shape[:3]

@@ -4,6 +4,7 @@
 
 namespace cn {
 
+template <bool kWgrad>
 __global__ void __launch_bounds__(kBwdThreads, 1) mlp_block_bwd_kernel(BlockBwdArgs A) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) BwdBars bars;
@@ -24,7 +25,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_block_bwd_kernel(BlockBwdA
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = tmem_slot;
-  block_bwd_role(A, bars, s_ba, smem, tmem, (int)blockIdx.x, (int)gridDim.x);
+  block_bwd_role<kWgrad>(A, bars, s_ba, smem, tmem, (int)blockIdx.x, (int)gridDim.x);
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem, 512);
@@ -172,7 +173,7 @@ extern "C" int cn_mlp_block_bwd(const void *packed, int32_t blk, const void *act
                                 int32_t act_index, int64_t n_tiles, const void *gy_tiles, int32_t gy_views,
                                 int64_t gy_tiles_per_view, void *gh_tiles, float scale, float *grad, void *stream) {
   using namespace cn;
-  CN_REQUIRE(packed && acts && gy_tiles && gh_tiles && grad, "cn_mlp_block_bwd: null pointer");
+  CN_REQUIRE(packed && acts && gy_tiles && gh_tiles, "cn_mlp_block_bwd: null pointer");
   CN_REQUIRE(blk >= 0 && blk < 6, "cn_mlp_block_bwd: blk %d", blk);
   CN_REQUIRE(act_stride_tiles >= 1 && act_index >= 0 && act_index < act_stride_tiles,
              "cn_mlp_block_bwd: act_stride_tiles=%d act_index=%d", act_stride_tiles, act_index);
@@ -185,20 +186,26 @@ extern "C" int cn_mlp_block_bwd(const void *packed, int32_t blk, const void *act
                  ((uintptr_t)grad & 15) == 0,
              "cn_mlp_block_bwd: alignment");
   if (n_tiles == 0) return 0;
-  cudaError_t e =
-      cudaFuncSetAttribute(mlp_block_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBwdSmemBytes);
+  cudaError_t e = grad ? cudaFuncSetAttribute(mlp_block_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)kBwdSmemBytes)
+                       : cudaFuncSetAttribute(mlp_block_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)kBwdSmemBytes);
   if (e != cudaSuccess) {
     set_error("cn_mlp_block_bwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     return (int)e;
   }
   const uint8_t *pk = (const uint8_t *)packed;
   const unsigned grid = (unsigned)(n_tiles < num_sms() ? n_tiles : num_sms());
-  BlockBwdArgs A = block_bwd_args(pk, blk, (const uint8_t *)acts, act_stride_tiles, act_index, n_tiles, scale, grad);
+  // grad == NULL: gradient to the block input only (no weight / bias gradients are formed)
+  static float dummy_grad;   // block_bwd_args only forms addresses from it
+  BlockBwdArgs A = block_bwd_args(pk, blk, (const uint8_t *)acts, act_stride_tiles, act_index, n_tiles, scale,
+                                  grad ? grad : &dummy_grad);
   A.gy_tiles = (const uint8_t *)gy_tiles;
   A.gy_views = gy_views;
   A.gy_tpv = gy_tiles_per_view;
   A.gh_tiles = (uint8_t *)gh_tiles;
-  mlp_block_bwd_kernel<<<grid, kBwdThreads, kBwdSmemBytes, (cudaStream_t)stream>>>(A);
+  if (grad) mlp_block_bwd_kernel<true><<<grid, kBwdThreads, kBwdSmemBytes, (cudaStream_t)stream>>>(A);
+  else mlp_block_bwd_kernel<false><<<grid, kBwdThreads, kBwdSmemBytes, (cudaStream_t)stream>>>(A);
   return check_launch("cn_mlp_block_bwd");
 }
 

@@ -232,6 +232,9 @@ __device__ __forceinline__ void block_bwd_init_barriers(BwdBars &bars) {
 // The role body: CTA `cta` of `n_cta` CTAs of this role works on tiles cta, cta + n_cta, ...  Called by all
 // kBwdThreads threads after the barriers are initialised, s_ba holds the 128 floats of bias_a, 512 TMEM columns are
 // allocated at `tmem` and the CTA has synchronised.
+// kWgrad = false: gradient w.r.t. the block input only (the pose-query backward of a frozen field,
+// grasp_optimizer.py:158-184): no weight-gradient GEMMs, no bias column sums, no flush.
+template <bool kWgrad = true>
 __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &bars, const float *s_ba, uint8_t *smem,
                                                uint32_t tmem, int cta, int n_cta) {
   const uint32_t s_base = smem_u32(smem);
@@ -355,7 +358,7 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
         mbar_wait(smem_u32(&bars.a2_ready), par);                 // (also: E0 has drained acc0)
         tc_fence_after();
         CN_TRACE_AT(it, 2);
-        wgrad(t_dwb, kBwSmemA2, gy, it == 0);                     // WB: dWb += A2^T g_y
+        if (kWgrad) wgrad(t_dwb, kBwSmemA2, gy, it == 0);         // WB: dWb += A2^T g_y
         umma_commit(smem_u32(&bars.g2wb_done));
         CN_TRACE_AT(it, 3);
         bool next_issued = false;
@@ -372,7 +375,7 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
         gemm_kk(t_acc1, kBwSmemA2, kBwSmemWa);                    // G1: g_a1 = g_t Wa^T
         umma_commit(smem_u32(&bars.g1_ready));
         CN_TRACE_AT(it, 6);
-        wgrad(t_dwa, a1, kBwSmemA2, it == 0);                     // WA: dWa += A1^T g_t
+        if (kWgrad) wgrad(t_dwa, a1, kBwSmemA2, it == 0);         // WA: dWa += A1^T g_t
         umma_commit(smem_u32(&bars.free_a1[b]));
         umma_commit(smem_u32(&bars.a2buf_free));
         CN_TRACE_AT(it, 7);
@@ -456,7 +459,7 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&bars.gt_ready));
       if (threadIdx.x == 64) CN_TRACE_AT(it, 14);
-      {
+      if (kWgrad) {
         dba += colsum_bf16x2(a2w, lane);               // off the critical path: G1 is running
       }
       // ---- E2: g_h = g_y + g_a1 * [A1 > 0], in place over g_y (TMA store by the producer warp); dbb += colsum(g_y)
@@ -470,7 +473,7 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
           gw[q * 4 + 0] = g[q].x; gw[q * 4 + 1] = g[q].y; gw[q * 4 + 2] = g[q].z; gw[q * 4 + 3] = g[q].w;
         }
       }
-      {
+      if (kWgrad) {
         uint32_t t16[16];                              // the butterfly consumes its input: work on a copy, while G1 runs
 #pragma unroll
         for (int j = 0; j < 16; ++j) t16[j] = gw[j];
@@ -510,7 +513,7 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
     // ---- flush the weight gradients held in TMEM (each thread: its input unit, 32 output units)
     mbar_wait(smem_u32(&bars.all_done), 0);
     tc_fence_after();
-    if (n_mine > 0) {
+    if (kWgrad && n_mine > 0) {
 #pragma unroll 1
       for (int mtx = 0; mtx < 2; ++mtx) {
         float *gdst = (mtx == 0 ? A.g_wa : A.g_wb) + row * 128 + cq * 32;  // accumulator row = input unit
