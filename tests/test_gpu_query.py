@@ -314,3 +314,46 @@ def test_dngf_optimizer_graph_replay_matches_eager(cuda):
     print('[dngf graph] max |dt|', float((t0 - t1).abs().max()), 'max |dr|', float((r0 - r1).abs().max()))
     assert torch.allclose(t0, t1, atol=1e-5) and torch.allclose(r0, r1, atol=1e-5)
     assert torch.allclose(l0, l1, rtol=1e-3, atol=1e-3)
+
+
+def test_delta_ngf_graph_replayed_train_step_walks_the_eager_one(cuda):
+    """DeltaNGF.capture_train_step: three replayed steps on changing batches leave the same GraspReadout as three
+    eager train_steps (same kernels in the same order; atomics only inside the frozen field's unused gradient)."""
+    import copy
+    from clipnerf_b200 import params
+    from src.lib.delta_ngf.model import DeltaNGF
+    from oracle import nerf_oracle as O
+    b, nv, n_pts = 1, 2, 24
+    sc = O.synthetic_scene(12, b, nv, 8, 48, 64)
+    named = O.init_params(9, bias_std=0.02)
+    named.update(O.init_grasp_readout(2, bias_std=0.02))
+    _, _, img, K, E = sc['inputs']
+    feats = sc['features'].to(cuda)
+
+    def batch(seed):
+        lp, tp = O.synthetic_poses(seed, b, n_pts), O.synthetic_poses(seed + 50, b, n_pts)
+        g = torch.Generator().manual_seed(seed)
+        labels = (torch.rand(b, n_pts, generator=g), torch.randn(b, n_pts, 3, generator=g), torch.randn(b, n_pts, 4, generator=g))
+        return (lp[0], lp[1], tp[0], tp[1], img, K, E), labels
+    batches = [batch(s) for s in (1, 2, 3, 4)]
+
+    def make():
+        m = DeltaNGF(n_views=nv, batch_size=b, n_points_train=n_pts, device=cuda)
+        with torch.no_grad():
+            m.fine_embedding.flat.copy_(params.from_named(named, 'fine')[:m.fine_embedding.flat.numel()].to(cuda))
+        m.grasp_readout.load_keras_variables(named)
+        m.feature_fn = lambda flat: feats.reshape(b * nv, *feats.shape[2:])
+        m.compile()
+        return m
+    eager, graphed = make(), make()
+    logs_e = [eager.train_step(d) for d in batches][1:]
+    replay = graphed.capture_train_step(batches[0], warmup=1)          # one eager step on batch 0 (creates the Adam state)
+    logs_g = [{k: v.clone() for k, v in replay(d).items()} for d in batches[1:]]
+    for i, (le, lg) in enumerate(zip(logs_e, logs_g)):
+        print(f'[graph train_step] step {i}: eager', {k: round(float(v), 5) for k, v in le.items()},
+              'replayed', {k: round(float(v), 5) for k, v in lg.items()})
+    for le, lg in zip(logs_e, logs_g):
+        for k in le:
+            assert abs(float(le[k]) - float(lg[k])) < 1e-4 * max(1.0, abs(float(le[k]))), (k, float(le[k]), float(lg[k]))
+    for (n, pe), pg in zip(eager.grasp_readout.named_parameters(), graphed.grasp_readout.parameters()):
+        assert rel_err(pg, pe) < 1e-4, (n, rel_err(pg, pe))

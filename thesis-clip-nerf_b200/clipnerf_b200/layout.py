@@ -19,6 +19,12 @@ def _elem_index(ncols: int) -> torch.Tensor:
     return (byte // 2).to(torch.int64)
 
 
+@functools.lru_cache(maxsize=None)
+def _elem_index_on(ncols: int, device: str) -> torch.Tensor:
+    """the index table on a device, copied once (a host -> device copy cannot be recorded into a CUDA graph)"""
+    return _elem_index(ncols).to(torch.device(device)).view(-1)
+
+
 def x_col_to_ref(j: int) -> int:
     """internal column of the MLP input X -> reference column (layers.py:362), -1 = zero pad."""
     if j < 256:
@@ -36,7 +42,7 @@ def tiles_to_matrix(buf: torch.Tensor, ncols: int) -> torch.Tensor:
     """uint8 tile images -> [n_tiles*128, ncols] float32."""
     elems = ncols * TILE_ROWS
     t = buf.view(torch.bfloat16).view(-1, elems)
-    idx = _elem_index(ncols).to(buf.device).view(-1)
+    idx = _elem_index_on(ncols, str(buf.device))
     return t[:, idx].view(-1, ncols).to(torch.float32)
 
 
@@ -46,7 +52,7 @@ def matrix_to_tiles(mat: torch.Tensor) -> torch.Tensor:
     assert rows % TILE_ROWS == 0 and ncols % 64 == 0
     nt = rows // TILE_ROWS
     out = torch.zeros(nt, ncols * TILE_ROWS, dtype=torch.bfloat16, device=mat.device)
-    idx = _elem_index(ncols).to(mat.device).view(-1)
+    idx = _elem_index_on(ncols, str(mat.device))
     out[:, idx] = mat.to(torch.bfloat16).view(nt, -1)
     return out.view(torch.uint8).view(-1)
 

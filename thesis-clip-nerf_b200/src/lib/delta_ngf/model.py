@@ -172,14 +172,24 @@ class _PoseQueryModel(torch.nn.Module):
 
     def compile(self, optimizer=None, loss=None):
         """only the affordance head trains (reference train_step: ``tape.watch(grasp_readout.trainable_variables)``)"""
-        self.optimizer = optimizer if optimizer is not None else torch.optim.Adam(self.grasp_readout.parameters(),
-                                                                                 lr=1e-4, eps=1e-7)
+        # capturable on a CUDA device: the step can be recorded into a CUDA graph (capture_train_step)
+        self.optimizer = optimizer if optimizer is not None else torch.optim.Adam(
+            self.grasp_readout.parameters(), lr=1e-4, eps=1e-7, capturable=self.device.type == 'cuda')
         self.loss = loss if loss is not None else (lambda y, p: torch.mean((p - y) ** 2))
 
-    def fit(self, generator, epochs=1, initial_epoch=0, verbose=0):
+    def fit(self, generator, epochs=1, initial_epoch=0, verbose=0, graph=False):
+        """Keras ``fit`` over a ``Sequence``.  ``graph=True`` (models with ``capture_train_step``): the first batch's
+        step is recorded into a CUDA graph, every batch is copied into its static buffers and replayed -- the ~700 small
+        launches of a step (double backward of the head, tangent pass) then cost the host one launch."""
         history = []
+        replay = None
         for epoch in range(initial_epoch, epochs):
-            logs = [self.train_step(generator[i]) for i in range(len(generator))]
+            if graph and hasattr(self, 'capture_train_step') and len(generator):
+                if replay is None:
+                    replay = self.capture_train_step(generator[0])
+                logs = [dict(replay(generator[i])) for i in range(len(generator))]
+            else:
+                logs = [self.train_step(generator[i]) for i in range(len(generator))]
             if hasattr(generator, 'on_epoch_end'):
                 generator.on_epoch_end()
             history.append({k: float(np.mean([float(l[k]) for l in logs])) for k in (logs[0] if logs else {})})
@@ -269,6 +279,49 @@ class DeltaNGF(_PoseQueryModel):
                'grad_loss_r': losses['grad_loss_r'].detach(), 'pred': losses['prediction'].detach().mean()}
         self.metrics_log.append({k: float(v) for k, v in out.items()})
         return out
+
+    def capture_train_step(self, data, warmup=2):
+        """CUDA-graph form of ``train_step``: both ``_call``s, the pose gradient with its double backward through the
+        head and the tangent pass, the (data-parallel) gradient mean, clip and the optimizer step are recorded once and
+        replayed.  ``data`` fixes the shapes; the optimizer must be capturable (``compile()``'s default on CUDA) and the
+        feature plug-in must not synchronise with the host.  Returns ``replay(data=None) -> metrics`` (device tensors,
+        overwritten by the next replay); ``warmup`` >= 1 eager steps on ``data`` precede the capture and DO train (the
+        optimizer state has to exist before the capture: a state tensor created while recording would be re-initialised
+        by every replay)."""
+        assert warmup >= 1, 'the optimizer state must be created by an eager step before the capture'
+        inputs, labels = data
+        s_in = [self._to_dev(x).clone() for x in inputs[:7]]
+        s_lab = [self._to_dev(x).clone() for x in labels]
+        readout_vars = list(self.grasp_readout.parameters())
+
+        def step():
+            feats = self.encode(s_in[4]).detach()
+            losses = self.compute_losses(s_in, s_lab, feats)
+            gradients = torch.autograd.grad(losses['loss'], readout_vars, allow_unused=True)
+            gradients = allreduce_mean(gradients, readout_vars, getattr(self, 'process_group', None))
+            optimize(self.optimizer, readout_vars, gradients, 1.0)
+            return {'landscape_loss': losses['landscape_loss'].detach(), 'grad_loss_t': losses['grad_loss_t'].detach(),
+                    'grad_loss_r': losses['grad_loss_r'].detach(), 'pred': losses['prediction'].detach().mean()}
+        from clipnerf_b200 import layout
+        layout._elem_index_on(128, str(self.device))       # index table of the tangent pass: on the device before capture
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                step()
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            out = step()
+
+        def replay(data=None):
+            if data is not None:
+                for dst, src in zip(s_in + s_lab, list(data[0][:7]) + list(data[1])):
+                    dst.copy_(self._to_dev(src), non_blocking=True)
+            graph.replay()
+            return out
+        replay.graph = graph
+        return replay
 
     def compute_losses(self, inputs, labels, feats):
         """the loss terms of ``train_step`` (reference :258-291) as differentiable tensors"""

@@ -117,6 +117,12 @@ def main():
                 ref = p.clone()
                 dist.broadcast(ref, 0)
                 assert torch.equal(ref, p), 'ranks diverged'
+        if world == 1:
+            replay = model.capture_train_step(data)
+            ms_g = timed(lambda: replay(data), args.steps, args.warmup)
+            print(json.dumps({'case': 'train_step (CUDA graph replay)', 'metric': 'poses_per_sec_train_step',
+                              'value': b * n_pts / (ms_g * 1e-3), 'unit': 'poses/s', 'ms_per_step': ms_g,
+                              'graph': 'DeltaNGF.capture_train_step(): the batch is copied into static buffers, one graph launch per step'}))
         if rank == 0:
             print(json.dumps({'case': 'train_step', 'metric': 'poses_per_sec_train_step',
                           'value': world * b * n_pts / (ms * 1e-3), 'n_gpus': world,
