@@ -246,6 +246,27 @@ int cn_mlp_fusion_fwd_tap_tiles(const void *packed, const void *h3_tiles, int32_
  * returns as tiles join the gradient stream without an fp32 round trip.                        */
 int cn_tile_add_tiles(void *g_tiles, const void *src_tiles, int64_t n_tiles, void *stream);
 
+/* ---- tangent (forward-mode) pass of the pose-query embedding: the double backward of DeltaNGF.train_step /
+ * LanguageNeRF.train_step (delta_ngf/model.py:264-296, lmvnerf/model_v4.py:284-322: tape_1.gradient(prediction,
+ * pose_variables) inside the outer tape) differentiates d prediction / d pose w.r.t. the head's weights, which needs
+ * J . u of the embedding for a pose-space direction u -- the forward kernels on tangent inputs, with the ReLU patterns
+ * of the primal pass (its saved activation tiles) and without biases.
+ *   cn_query_tangent_x: points, dirs, u_points, u_dirs [b][n][3] (n a multiple of 128; one sample per "ray") ->
+ *     x_tiles [b*nv*n/128][96 KiB], the tangent of the MLP-input rows in the layout of cn_project_gather_fwd.
+ *   cn_mlp_feature_fwd_ex / cn_mlp_fusion_fwd_taps_ex: cn_mlp_feature_fwd / cn_mlp_fusion_fwd_taps(_tap_tiles) with
+ *     save_hidden = 1: acts holds 3 more tiles per tile, the hidden activations relu(t + ba) of the blocks behind the
+ *       usual ones (per-view stage 6 tiles per tile, fusion stage 7: act_stride_tiles of the backward kernels);
+ *     mask_acts != NULL (acts must be NULL): the tangent pass -- mask_acts is the acts buffer a save_hidden forward
+ *       of the same rows wrote; every ReLU becomes a multiplication by the sign pattern of the saved tile, every
+ *       bias is dropped; taps then are the tangents of the four stage outputs (rgbs is scratch).               */
+int cn_query_tangent_x(const CnScene *scene, const float *points, const float *dirs, const float *u_points,
+                       const float *u_dirs, int32_t n, void *x_tiles, void *stream);
+int cn_mlp_feature_fwd_ex(const void *packed, const void *x_tiles, int64_t n_tiles, void *h3_tiles, void *acts,
+                          int32_t save_hidden, const void *mask_acts, void *stream);
+int cn_mlp_fusion_fwd_taps_ex(const void *packed, const void *h3_tiles, int32_t b, int32_t nv, int64_t tiles_per_view,
+                              float *rgbs, void *acts, void *taps, int32_t tap_bf16, int32_t save_hidden,
+                              const void *mask_acts, void *stream);
+
 /* poses = transforms @ transforms_to_check (delta_ngf/model.py:199-200, 221-223; same lines in lmvnerf/model_v4.py,
  * grasp_mvnerf/model.py): transforms [n_poses][4][4] (bottom row [0 0 0 1]), transforms_to_check [n5][4][4] ->
  * query points and approach directions [n_poses * n5][3] in '(np n5)' row order, and the backward to the pose

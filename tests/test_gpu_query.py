@@ -357,3 +357,34 @@ def test_delta_ngf_graph_replayed_train_step_walks_the_eager_one(cuda):
             assert abs(float(le[k]) - float(lg[k])) < 1e-4 * max(1.0, abs(float(le[k]))), (k, float(le[k]), float(lg[k]))
     for (n, pe), pg in zip(eager.grasp_readout.named_parameters(), graphed.grasp_readout.parameters()):
         assert rel_err(pg, pe) < 1e-4, (n, rel_err(pg, pe))
+
+
+@pytest.mark.parametrize('nv,n', [(1, 128), (3, 384)])
+def test_tangent_kernels_match_the_torch_form(cuda, nv, n):
+    """cn_query_tangent_x + the forward kernels with external masks against the same Jacobian-vector product written
+    with torch ops on the saved tiles (query_tangent_reference): tangent MLP-input rows and the four tangent taps."""
+    from clipnerf_b200 import layout, ops, params, query_tangent as QT
+    from oracle import nerf_oracle as O
+    b = 2
+    sc = O.synthetic_scene(3, b, nv, 8, 48, 64)
+    named = O.init_params(7, bias_std=0.02)
+    _, _, img, K, E = [t.to(cuda) for t in sc['inputs']]
+    pts, dirs = [t.to(cuda) for t in _points(O, sc, n, 5)]
+    g = torch.Generator().manual_seed(9)
+    u_p, u_d = torch.randn(b, n, 3, generator=g).to(cuda), torch.randn(b, n, 3, generator=g).to(cuda)
+    pf = params.from_named(named, 'fine').to(cuda)
+    scene = ops.Scene(img, sc['features'].to(cuda), K, E)
+    z = torch.zeros(b, n, 1, device=cuda)
+    packed = ops.pack_weights(pf)
+    x, _ws = ops.project_gather_fwd(scene, pts, dirs, z, return_ws=True)
+    h3, acts_f = ops.mlp_feature_fwd(packed, x, True, save_hidden=True)
+    taps, _, acts_u = ops.mlp_fusion_fwd_taps(packed, h3, b, nv, True, save_hidden=True)
+    # the saved hidden tiles do not disturb the primal outputs
+    taps0, _, _ = ops.mlp_fusion_fwd_taps(packed, ops.mlp_feature_fwd(packed, x, False)[0], b, nv, False)
+    assert torch.equal(taps, taps0)
+    got = QT.query_tangent(scene, packed, pts, dirs, acts_f, acts_u, u_p, u_d)
+    ref = QT.query_tangent_reference(scene, pf, pts, dirs, z, acts_f, acts_u, u_p, u_d)
+    for i, name in enumerate(('mean', 'block4', 'block5', 'block6')):
+        med, p90, mx, l2 = _row_stats(got[i], ref[i])
+        print(f'[tangent kernels nv={nv} n={n}] d tap {name}: median {med:.2e} p90 {p90:.2e} max {mx:.2e} L2 {l2:.2e}')
+        assert p90 < 1e-2 and l2 < 1e-2 and mx < 3e-2, (name, med, p90, mx, l2)

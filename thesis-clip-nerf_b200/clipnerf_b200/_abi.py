@@ -60,6 +60,9 @@ PROTOTYPES = {
     'cn_tile_add_rows': [_P, _P, c_int64, c_int32, _P],
     'cn_mlp_fusion_fwd_tap_tiles': [_P, _P, c_int32, c_int32, c_int64, _P, _P, _P, _P],
     'cn_tile_add_tiles': [_P, _P, c_int64, _P],
+    'cn_query_tangent_x': [ctypes.POINTER(CnScene), _P, _P, _P, _P, c_int32, _P, _P],
+    'cn_mlp_feature_fwd_ex': [_P, _P, c_int64, _P, _P, c_int32, _P, _P],
+    'cn_mlp_fusion_fwd_taps_ex': [_P, _P, c_int32, c_int32, c_int64, _P, _P, _P, c_int32, c_int32, _P, _P],
     'cn_pose_points_fwd': [_P, _P, c_int64, c_int32, _P, _P, _P],
     'cn_pose_points_bwd': [_P, _P, _P, c_int64, c_int32, _P, _P],
     'cn_grasp_head_pack': [_P, _P, _P],

@@ -274,12 +274,28 @@ def pack_weights(params: torch.Tensor) -> torch.Tensor:
     return packed
 
 
-def mlp_feature_fwd(packed, x_tiles, save_acts: bool):
+def mlp_feature_fwd(packed, x_tiles, save_acts: bool, save_hidden: bool = False, mask_acts=None):
+    """per-view stage.  ``save_hidden``: acts holds FEATURE_ACTS + 3 tiles per tile (the hidden activations behind the
+    usual ones); ``mask_acts``: the tangent pass with the ReLU patterns of that buffer (nothing is saved)."""
     nt = x_tiles.numel() // X_TILE_BYTES
     h3 = _bytes(nt * ACT_TILE_BYTES, x_tiles.device)
-    acts = _bytes(nt * FEATURE_ACTS * ACT_TILE_BYTES, x_tiles.device) if save_acts else None
-    call('cn_mlp_feature_fwd', _ptr(packed), _ptr(x_tiles), nt, _ptr(h3), _ptr(acts), _stream())
+    if not save_hidden and mask_acts is None:
+        acts = _bytes(nt * FEATURE_ACTS * ACT_TILE_BYTES, x_tiles.device) if save_acts else None
+        call('cn_mlp_feature_fwd', _ptr(packed), _ptr(x_tiles), nt, _ptr(h3), _ptr(acts), _stream())
+        return h3, acts
+    acts = _bytes(nt * (FEATURE_ACTS + 3) * ACT_TILE_BYTES, x_tiles.device) if (save_acts and mask_acts is None) else None
+    call('cn_mlp_feature_fwd_ex', _ptr(packed), _ptr(x_tiles), nt, _ptr(h3), _ptr(acts), int(save_hidden), _ptr(mask_acts),
+         _stream())
     return h3, acts
+
+
+def query_tangent_x(scene: Scene, pts, drs, u_pts, u_dirs) -> torch.Tensor:
+    """tangent of the MLP-input rows of the pose-query call: pts, drs, u_* [b, n, 3] (n % 128 == 0) -> X tiles"""
+    pts, drs, u_pts, u_dirs = _f32c(pts), _f32c(drs), _f32c(u_pts), _f32c(u_dirs)
+    b, n, _ = pts.shape
+    x = _bytes(n_tiles(b * scene.nv * n) * X_TILE_BYTES, pts.device)
+    call('cn_query_tangent_x', ctypes.byref(scene.c), _ptr(pts), _ptr(drs), _ptr(u_pts), _ptr(u_dirs), n, _ptr(x), _stream())
+    return x
 
 
 def mlp_fusion_fwd(packed, h3_tiles, b: int, nv: int, save_acts: bool):
@@ -292,17 +308,23 @@ def mlp_fusion_fwd(packed, h3_tiles, b: int, nv: int, save_acts: bool):
     return rgbs, acts
 
 
-def mlp_fusion_fwd_taps(packed, h3_tiles, b: int, nv: int, save_acts: bool):
-    """fusion stage returning the four `complete_output` stage outputs: taps [4, b*tpv*128, 128] fp32."""
+def mlp_fusion_fwd_taps(packed, h3_tiles, b: int, nv: int, save_acts: bool, save_hidden: bool = False, mask_acts=None):
+    """fusion stage returning the four `complete_output` stage outputs: taps [4, b*tpv*128, 128] fp32.
+    ``save_hidden`` / ``mask_acts`` as for ``mlp_feature_fwd`` (FUSION_ACTS + 3 tiles per tile)."""
     nt = h3_tiles.numel() // ACT_TILE_BYTES
     assert nt % (b * nv) == 0
     tpv = nt // (b * nv)
     rows = b * tpv * TILE_ROWS
     rgbs = torch.empty(rows, 4, dtype=torch.float32, device=h3_tiles.device)
     taps = torch.empty(4, rows, 128, dtype=torch.float32, device=h3_tiles.device)
-    acts = _bytes(b * tpv * FUSION_ACTS * ACT_TILE_BYTES, h3_tiles.device) if save_acts else None
-    call('cn_mlp_fusion_fwd_taps', _ptr(packed), _ptr(h3_tiles), b, nv, tpv, _ptr(rgbs), _ptr(acts), _ptr(taps),
-         _stream())
+    if not save_hidden and mask_acts is None:
+        acts = _bytes(b * tpv * FUSION_ACTS * ACT_TILE_BYTES, h3_tiles.device) if save_acts else None
+        call('cn_mlp_fusion_fwd_taps', _ptr(packed), _ptr(h3_tiles), b, nv, tpv, _ptr(rgbs), _ptr(acts), _ptr(taps),
+             _stream())
+        return taps, rgbs, acts
+    acts = _bytes(b * tpv * (FUSION_ACTS + 3) * ACT_TILE_BYTES, h3_tiles.device) if (save_acts and mask_acts is None) else None
+    call('cn_mlp_fusion_fwd_taps_ex', _ptr(packed), _ptr(h3_tiles), b, nv, tpv, _ptr(rgbs), _ptr(acts), _ptr(taps), 0,
+         int(save_hidden), _ptr(mask_acts), _stream())
     return taps, rgbs, acts
 
 

@@ -30,7 +30,7 @@ def _pad_rows(t: torch.Tensor, n_pad: int) -> torch.Tensor:
 
 class _State:
     """what the forward keeps for the backward and for the tangent pass of the double backward"""
-    __slots__ = ('scene', 'params', 'packed', 'n', 'pts', 'drs', 'z', 'x', 'ws', 'acts_f', 'acts_u', 'need')
+    __slots__ = ('scene', 'params', 'packed', 'n', 'pts', 'drs', 'z', 'x', 'ws', 'acts_f', 'acts_u', 'need', 'fa', 'ua')
 
 
 class _QueryEmbedFn(torch.autograd.Function):
@@ -44,10 +44,13 @@ class _QueryEmbedFn(torch.autograd.Function):
         z = torch.zeros(b, n_pad, 1, dtype=torch.float32, device=pts.device)
         packed = ops.pack_weights(params)
         x, ws = ops.project_gather_fwd(scene, pts, drs, z, return_ws=True)
-        h3, acts_f = ops.mlp_feature_fwd(packed, x, need_grad)
-        taps, _rgbs, acts_u = ops.mlp_fusion_fwd_taps(packed, h3, b, scene.nv, need_grad)
+        # the hidden activations are kept as well (3 more tiles per tile): the tangent pass of a double backward
+        # (DeltaNGF.train_step) takes its ReLU patterns from them
+        h3, acts_f = ops.mlp_feature_fwd(packed, x, need_grad, save_hidden=need_grad)
+        taps, _rgbs, acts_u = ops.mlp_fusion_fwd_taps(packed, h3, b, scene.nv, need_grad, save_hidden=need_grad)
         if need_grad:
             st = _State()
+            st.fa, st.ua = ops.FEATURE_ACTS + 3, ops.FUSION_ACTS + 3      # act_stride_tiles of the backward kernels
             st.scene, st.params, st.packed, st.n = scene, params.detach(), packed, n
             st.pts, st.drs, st.z, st.x, st.ws, st.acts_f, st.acts_u = pts, drs, z, x, ws, acts_f, acts_u
             st.need = tuple(ctx.needs_input_grad)
@@ -88,13 +91,13 @@ class _QueryBwdFn(torch.autograd.Function):
         # the gradient of every tapped stage output joins the bf16 gradient stream where the stage was produced
         g = ops.tile_add_rows(None, rows(3))
         for blk in (5, 4, 3):
-            ops.mlp_block_bwd(packed, blk, st.acts_u, ops.FUSION_ACTS, blk - 3, g, grad)
+            ops.mlp_block_bwd(packed, blk, st.acts_u, st.ua, blk - 3, g, grad)
             ops.tile_add_rows(g, rows(blk - 3))
         s = 1.0 / scene.nv
-        gf = ops.mlp_block_bwd(packed, 2, st.acts_f, ops.FEATURE_ACTS, 2, g, grad, views=scene.nv, scale=s, b=scene.b) \
-            if scene.nv > 1 else ops.mlp_block_bwd(packed, 2, st.acts_f, ops.FEATURE_ACTS, 2, g, grad)
+        gf = ops.mlp_block_bwd(packed, 2, st.acts_f, st.fa, 2, g, grad, views=scene.nv, scale=s, b=scene.b) \
+            if scene.nv > 1 else ops.mlp_block_bwd(packed, 2, st.acts_f, st.fa, 2, g, grad)
         for blk in (1, 0):
-            ops.mlp_block_bwd(packed, blk, st.acts_f, ops.FEATURE_ACTS, blk, gf, grad, scale=s)
+            ops.mlp_block_bwd(packed, blk, st.acts_f, st.fa, blk, gf, grad, scale=s)
         if need[0]:
             ops.mlp_l0_wgrad(st.x, gf, grad, s)
         d_features = torch.empty(0, device=dev)
@@ -122,7 +125,7 @@ class _QueryBwdFn(torch.autograd.Function):
         def pad(u):
             u = torch.zeros(b, n, 3, dtype=torch.float32, device=st.z.device) if u is None else u.to(torch.float32)
             return torch.cat([u, u.new_zeros(b, n_pad - n, 3)], dim=1) if n_pad != n else u
-        taps = query_tangent(st.scene, st.params, st.pts, st.drs, st.z, st.acts_f, st.acts_u, pad(u_pts), pad(u_dirs))
+        taps = query_tangent(st.scene, st.packed, st.pts, st.drs, st.acts_f, st.acts_u, pad(u_pts), pad(u_dirs))
         return (None,) + tuple(t[:, :n] for t in taps)
 
 
@@ -148,6 +151,7 @@ class _QueryGraspFn(torch.autograd.Function):
         y, head = ops.grasp_head_fwd(taps, b, n_pad, n_poses, head_pack, elu, need_grad)
         if need_grad:
             st = _State()
+            st.fa, st.ua = ops.FEATURE_ACTS, ops.FUSION_ACTS
             st.scene, st.params, st.packed, st.n = scene, None, packed, n
             st.pts, st.drs, st.z, st.x, st.ws, st.acts_f, st.acts_u = pts, drs, z, None, ws, acts_f, acts_u
             st.need = tuple(ctx.needs_input_grad)

@@ -4,10 +4,14 @@ points / directions, with the ReLU masks of the primal pass held fixed.
 Only ``DeltaNGF.train_step`` needs it (reference ``src/lib/delta_ngf/model.py:264-296``): the loss compares
 d prediction / d pose with labelled directions and is differentiated w.r.t. the ``GraspReadout`` weights, so
 autograd asks the backward of the query call for its own derivative w.r.t. the incoming tap gradients --
-which is this Jacobian-vector product.  It runs once per training step on b * np * 42 * nv rows (24 192 at the
-reference's training size), outside the inference loop; ROUND-1 STATUS: it is written with torch ops on the
-device (library GEMMs + index gathers) on top of the CUDA kernels' own saved tiles, projection records
-(``cn_project_gather_debug``) and bf16-rounded weights; a fused tcgen05 tangent kernel is the next step."""
+which is this Jacobian-vector product.  It runs on the same tcgen05 kernels as the forward:
+
+  ``cn_query_tangent_x``        tangent of the MLP-input rows (projection, bilinear coordinates, posenc) as X tiles
+  ``cn_mlp_feature_fwd_ex``     per-view stage on the tangent rows: every ReLU multiplies by the sign pattern of the
+  ``cn_mlp_fusion_fwd_taps_ex`` activation tile the primal forward saved (``save_hidden``), biases dropped
+
+``query_tangent_reference`` keeps the same computation written with torch ops on the kernels' saved tiles (library
+GEMMs, index gathers): the GPU tests compare the two."""
 from __future__ import annotations
 
 from typing import List
@@ -19,6 +23,18 @@ from . import params as P
 from ._abi import TILE_ROWS
 
 _PI32 = 3.14159274101257324
+
+
+def query_tangent(scene: ops.Scene, packed: torch.Tensor, pts, drs, acts_f, acts_u, u_pts, u_dirs) -> List[torch.Tensor]:
+    """J . (u_pts, u_dirs): pts, drs, u_* [b, n_pad, 3]; acts_f / acts_u: the activation tiles of a ``save_hidden``
+    forward of the same rows -> 4 tangent taps [b, n_pad, 128]."""
+    with torch.no_grad():
+        b, n = pts.shape[:2]
+        assert n % TILE_ROWS == 0
+        x_dot = ops.query_tangent_x(scene, pts, drs, u_pts, u_dirs)
+        h3_dot, _ = ops.mlp_feature_fwd(packed, x_dot, False, mask_acts=acts_f)
+        taps, _, _ = ops.mlp_fusion_fwd_taps(packed, h3_dot, b, scene.nv, False, mask_acts=acts_u)
+        return list(taps.view(4, b, n, 128).unbind(0))
 
 
 def _posenc_tangent(v: torch.Tensor, v_dot: torch.Tensor) -> torch.Tensor:
@@ -34,20 +50,17 @@ def _q(w: torch.Tensor) -> torch.Tensor:
     return w.to(torch.bfloat16).to(torch.float32)
 
 
-def _block_tangent(h_dot, relu_h, wa, ba, wb):
+def _block_tangent(h_dot, relu_h, relu_t, wa, wb):
     """tangent of y = h + relu(relu(h) Wa + ba) Wb + bb with the primal masks (layers.py:262-298)"""
-    m_h = (relu_h > 0).to(h_dot.dtype)
-    m_t = ((relu_h @ wa + ba) > 0).to(h_dot.dtype)
-    return h_dot + (((h_dot * m_h) @ wa) * m_t) @ wb
+    return h_dot + (((h_dot * (relu_h > 0).to(h_dot.dtype)) @ wa) * (relu_t > 0).to(h_dot.dtype)) @ wb
 
 
-def query_tangent(scene: ops.Scene, params: torch.Tensor, pts, drs, z, acts_f, acts_u, u_pts, u_dirs
-                  ) -> List[torch.Tensor]:
-    """J . (u_pts, u_dirs): pts, drs, u_* [b, n_pad, 3] -> 4 tangent taps [b, n_pad, 128]."""
+def query_tangent_reference(scene: ops.Scene, params: torch.Tensor, pts, drs, z, acts_f, acts_u, u_pts, u_dirs
+                            ) -> List[torch.Tensor]:
+    """the same Jacobian-vector product with torch ops (fp32 GEMMs on bf16-rounded weights) -- test reference"""
     with torch.no_grad():
         b, nv, H, W = scene.b, scene.nv, scene.H, scene.W
         n = pts.shape[1]
-        assert n % TILE_ROWS == 0
         E, K = scene.extr_inv, scene.intrinsics
         pix, corner, _, cam = ops.project_gather_debug(scene, pts, drs, z, gather=False, cam=True)
         pix, corner, cam = pix[:, :, :, 0], corner[:, :, :, 0].long(), cam[:, :, :, 0]        # [b, nv, n, .]
@@ -55,7 +68,6 @@ def query_tangent(scene: ops.Scene, params: torch.Tensor, pts, drs, z, acts_f, a
         p_dot = torch.einsum('bvij,bnj->bvni', E3, u_pts)
         d_dot = torch.einsum('bvij,bnj->bvni', E3, u_dirs)
         dcam = torch.einsum('bvij,bnj->bvni', E3, drs) + E[:, :, None, :3, 3]                # E [d; 1] (quirk Q1)
-        # pixel tangent through q = K p, pix = q.xy / max(q.z, 1e-8), clip +-1e6, alpha clamp
         q = torch.einsum('bvij,bvnj->bvni', K[:, :, :3, :], cam)
         q_dot = torch.einsum('bvij,bvnj->bvni', K[:, :, :3, :3], p_dot)
         den = torch.clamp(q[..., 2], min=1e-8)
@@ -67,38 +79,32 @@ def query_tangent(scene: ops.Scene, params: torch.Tensor, pts, drs, z, acts_f, a
         px_dot = torch.where(ok_x, (q_dot[..., 0] - rx * qz_dot) / den, torch.zeros_like(den))
         py_dot = torch.where(ok_y, (q_dot[..., 1] - ry * qz_dot) / den, torch.zeros_like(den))
         ax, ay = tx.clamp(0, 1)[..., None], ty.clamp(0, 1)[..., None]
-        # bilinear tangent: the four corners of the 256-channel map and of 2 * image - 1
         bv = torch.arange(b * nv, device=pts.device).view(b, nv, 1)
         i00 = ((bv * H + corner[..., 1]) * W + corner[..., 0]).reshape(-1)
 
-        def corners(grid, c):
-            g = grid.reshape(-1, c)
-            return g[i00], g[i00 + 1], g[i00 + W], g[i00 + W + 1]
-
         def lerp_tangent(grid, c, scale):
-            tl, tr, bl, br = corners(grid, c)
+            g = grid.reshape(-1, c)
+            tl, tr, bl, br = g[i00], g[i00 + 1], g[i00 + W], g[i00 + W + 1]
             axf, ayf = ax.reshape(-1, 1), ay.reshape(-1, 1)
             gx = (1 - ayf) * (tr - tl) + ayf * (br - bl)
             gy = (1 - axf) * (bl - tl) + axf * (br - tr)
             return scale * (px_dot.reshape(-1, 1) * gx + py_dot.reshape(-1, 1) * gy)
 
-        f_dot = lerp_tangent(scene.features, 256, 1.0)
-        i_dot = lerp_tangent(scene.images, 3, 2.0)
         x_dot = torch.cat([_posenc_tangent(cam[..., :3], p_dot).reshape(-1, 60),
-                           _posenc_tangent(dcam, d_dot).reshape(-1, 60), i_dot, f_dot], dim=-1)   # layers.py:362 order
+                           _posenc_tangent(dcam, d_dot).reshape(-1, 60), lerp_tangent(scene.images, 3, 2.0),
+                           lerp_tangent(scene.features, 256, 1.0)], dim=-1)                       # layers.py:362 order
         w = P.views(params)
         h_dot = x_dot @ _q(w['embedding.layer_0.kernel'])
         rows_v = b * nv * n
-        a_f = layout.tiles_to_matrix(acts_f, 128).view(rows_v // TILE_ROWS, ops.FEATURE_ACTS, TILE_ROWS, 128)
+        a_f = layout.tiles_to_matrix(acts_f, 128).view(rows_v // TILE_ROWS, ops.FEATURE_ACTS + 3, TILE_ROWS, 128)
         for i in range(3):
             pre = f'embedding.feature_blocks.{i}'
-            h_dot = _block_tangent(h_dot, a_f[:, i].reshape(rows_v, 128), _q(w[f'{pre}.layer_0.kernel']),
-                                   w[f'{pre}.layer_0.bias'], _q(w[f'{pre}.layer_1.kernel']))
-        m_dot = h_dot.view(b, nv, n, 128).mean(dim=1).reshape(b * n, 128)
-        taps = [m_dot]
-        a_u = layout.tiles_to_matrix(acts_u, 128).view(b * n // TILE_ROWS, ops.FUSION_ACTS, TILE_ROWS, 128)
+            h_dot = _block_tangent(h_dot, a_f[:, i].reshape(rows_v, 128), a_f[:, 3 + i].reshape(rows_v, 128),
+                                   _q(w[f'{pre}.layer_0.kernel']), _q(w[f'{pre}.layer_1.kernel']))
+        taps = [h_dot.view(b, nv, n, 128).mean(dim=1).reshape(b * n, 128)]
+        a_u = layout.tiles_to_matrix(acts_u, 128).view(b * n // TILE_ROWS, ops.FUSION_ACTS + 3, TILE_ROWS, 128)
         for i in range(3):
             pre = f'embedding.fusion_blocks.{i}'
-            taps.append(_block_tangent(taps[-1], a_u[:, i].reshape(b * n, 128), _q(w[f'{pre}.layer_0.kernel']),
-                                       w[f'{pre}.layer_0.bias'], _q(w[f'{pre}.layer_1.kernel'])))
+            taps.append(_block_tangent(taps[-1], a_u[:, i].reshape(b * n, 128), a_u[:, 4 + i].reshape(b * n, 128),
+                                       _q(w[f'{pre}.layer_0.kernel']), _q(w[f'{pre}.layer_1.kernel'])))
         return [t.view(b, n, 128) for t in taps]

@@ -59,10 +59,12 @@ struct FwdBars {
 // `tap` (optional): this row's 128 fp32 pre-activation values (h + bias) are also written there -- the stage
 // outputs MVResNetMLPNeRFEmbedding(complete_output=True) returns (layers.py:364-377).
 // `tap16` (optional): the same values as a bf16 activation-tile image (this thread writes its row's 128-byte line).
+// `mask` (optional, kRelu): tile whose sign pattern replaces the ReLU (Jacobian-vector product with the primal masks).
 template <bool kRelu>
 __device__ __forceinline__ void epi_tmem_to_act(uint32_t taddr, const float *__restrict__ bias, uint8_t *act,
                                                 uint32_t row, uint32_t half, float *__restrict__ tap = nullptr,
-                                                uint8_t *__restrict__ tap16 = nullptr) {
+                                                uint8_t *__restrict__ tap16 = nullptr,
+                                                const uint8_t *__restrict__ mask = nullptr) {
   uint32_t r[64];
   tmem_ld32(taddr + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
   tmem_ld32(taddr + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
@@ -84,7 +86,12 @@ __device__ __forceinline__ void epi_tmem_to_act(uint32_t taddr, const float *__r
       *reinterpret_cast<uint4 *>(tap16 + tile_chunk_off(row, half * 8 + q)) =
           make_uint4(cvt_bf16x2(v[0], v[1]), cvt_bf16x2(v[2], v[3]), cvt_bf16x2(v[4], v[5]), cvt_bf16x2(v[6], v[7]));
     uint4 o;
-    if (kRelu)  // relu folded into the conversion (F2FP.RELU): the epilogue is issue bound
+    if (kRelu && mask) {
+      // tangent pass: the activation's derivative is the PRIMAL mask, read from the tile the forward saved
+      const uint4 m = ldg_nc_u4(mask + tile_chunk_off(row, half * 8 + q));
+      o = make_uint4(mul_bf16x2(cvt_bf16x2(v[0], v[1]), gt0_bf16x2(m.x)), mul_bf16x2(cvt_bf16x2(v[2], v[3]), gt0_bf16x2(m.y)),
+                     mul_bf16x2(cvt_bf16x2(v[4], v[5]), gt0_bf16x2(m.z)), mul_bf16x2(cvt_bf16x2(v[6], v[7]), gt0_bf16x2(m.w)));
+    } else if (kRelu)  // relu folded into the conversion (F2FP.RELU): the epilogue is issue bound
       o = make_uint4(cvt_relu_bf16x2(v[0], v[1]), cvt_relu_bf16x2(v[2], v[3]), cvt_relu_bf16x2(v[4], v[5]),
                      cvt_relu_bf16x2(v[6], v[7]));
     else
@@ -97,7 +104,8 @@ template <bool kFusion>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ in_tiles, int64_t n_tiles,
                int nv, int64_t tiles_per_view, uint8_t *__restrict__ out_tiles, float *__restrict__ rgbs,
-               uint8_t *__restrict__ acts, float *__restrict__ taps, int tap_bf16) {
+               uint8_t *__restrict__ acts, float *__restrict__ taps, int tap_bf16, int save_hidden,
+               const uint8_t *__restrict__ mask_acts) {
   using L = FwdSmem<kFusion>;
   constexpr int kRingSlots = L::kRingSlots;
   extern __shared__ uint8_t smem_raw[];
@@ -110,6 +118,10 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
   const uint32_t lane = lane_id();
   float *tab = reinterpret_cast<float *>(smem + L::kTab);
   constexpr int kActsPerTile = kFusion ? 4 : 3;  // relu(h) of every block (+ relu(e)); relu(t) is recomputed by the backward
+  // pose-query training (double backward): the hidden activations relu(t + ba) are saved too (3 more tiles per tile),
+  // and the TANGENT pass (mask_acts != nullptr) re-runs this kernel on tangent inputs with the saved tiles as masks
+  // and without biases -- the Jacobian-vector product of the embedding with the primal ReLU pattern
+  const int acts_stride = kActsPerTile + ((save_hidden || mask_acts) ? 3 : 0);
   constexpr int kBlk0 = kFusion ? 3 : 0;
   const bool staged = kFusion && nv <= kMaxStageViews;  // view tiles go through the ring (else: global loads)
   const uint32_t view_slots = staged ? 2u * (uint32_t)nv : 0u;
@@ -117,7 +129,8 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
   // ---- one-time setup
   {
     const float *gt = reinterpret_cast<const float *>(packed + kPackTables);
-    for (int i = threadIdx.x; i < 7 * 128; i += kFwdThreads) tab[i] = gt[(kFusion ? kTabFusion : kTabFeature) + i];
+    for (int i = threadIdx.x; i < 7 * 128; i += kFwdThreads)
+      tab[i] = mask_acts ? 0.f : gt[(kFusion ? kTabFusion : kTabFeature) + i];
     if (kFusion)
       for (int i = threadIdx.x; i < 516; i += kFwdThreads) tab[7 * 128 + i] = gt[kTabReadoutW + i];
   }
@@ -356,7 +369,8 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
     for (int64_t p = blockIdx.x; p < n_pairs; p += gridDim.x, ++pi) {
       const int64_t tile = 2 * p + t;
       if (tile >= n_tiles) break;
-      uint8_t *my_acts = acts ? acts + tile * (int64_t)kActsPerTile * CN_ACT_TILE_BYTES : nullptr;
+      uint8_t *my_acts = acts ? acts + tile * (int64_t)acts_stride * CN_ACT_TILE_BYTES : nullptr;
+      const uint8_t *my_mask = mask_acts ? mask_acts + tile * (int64_t)acts_stride * CN_ACT_TILE_BYTES : nullptr;
       // fusion stage, pose-query models: taps[s][row][128] fp32, s = (mean, block 4, block 5, block 6 output)
       const int64_t tap_stride = n_tiles * (int64_t)(128 * 128);
       float *my_tap = (kFusion && taps && !tap_bf16) ? taps + (tile * 128 + row) * 128 : nullptr;
@@ -425,11 +439,18 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
               *reinterpret_cast<uint4 *>(my_tap16 + tile_chunk_off(row, chunk)) =
                   make_uint4(pack_bf16x2(m[0], m[1]), pack_bf16x2(m[2], m[3]), pack_bf16x2(m[4], m[5]),
                              pack_bf16x2(m[6], m[7]));
+            if (my_mask) {
+              const uint4 mk = ldg_nc_u4(my_mask + tile_chunk_off(row, chunk));
+              *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, chunk)) =
+                  make_uint4(mul_bf16x2(pack_bf16x2(m[0], m[1]), gt0_bf16x2(mk.x)), mul_bf16x2(pack_bf16x2(m[2], m[3]), gt0_bf16x2(mk.y)),
+                             mul_bf16x2(pack_bf16x2(m[4], m[5]), gt0_bf16x2(mk.z)), mul_bf16x2(pack_bf16x2(m[6], m[7]), gt0_bf16x2(mk.w)));
+            } else {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) m[i] = fmaxf(m[i], 0.f);
-            *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, chunk)) =
-                make_uint4(pack_bf16x2(m[0], m[1]), pack_bf16x2(m[2], m[3]), pack_bf16x2(m[4], m[5]),
-                           pack_bf16x2(m[6], m[7]));
+              for (int i = 0; i < 8; ++i) m[i] = fmaxf(m[i], 0.f);
+              *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, chunk)) =
+                  make_uint4(pack_bf16x2(m[0], m[1]), pack_bf16x2(m[2], m[3]), pack_bf16x2(m[4], m[5]),
+                             pack_bf16x2(m[6], m[7]));
+            }
           }
           tmem_st32(t_h + half * 64 + c2 * 32, r);
         }
@@ -457,7 +478,8 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
           acquire();
           epi_tmem_to_act<true>(t_h, tab + (2 * blk) * 128, act, row, half,
                                 (kFusion && my_tap) ? my_tap + blk * tap_stride : nullptr,
-                                (kFusion && my_tap16) ? my_tap16 + blk * tap16_stride : nullptr);
+                                (kFusion && my_tap16) ? my_tap16 + blk * tap16_stride : nullptr,
+                                my_mask ? my_mask + blk * CN_ACT_TILE_BYTES : nullptr);
           publish(my_acts ? my_acts + blk * CN_ACT_TILE_BYTES : nullptr, true);
           if (tr && blk == 0) CN_TRACE_AT(pi, 9);
         }
@@ -467,8 +489,9 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         tc_fence_after();
         if (tr && blk == 0) CN_TRACE_AT(pi, 10);
         acquire();
-        epi_tmem_to_act<true>(t_tmp, tab + (2 * blk + 1) * 128, act, row, half);
-        publish(nullptr, true);
+        epi_tmem_to_act<true>(t_tmp, tab + (2 * blk + 1) * 128, act, row, half, nullptr, nullptr,
+                              my_mask ? my_mask + (kActsPerTile + blk) * CN_ACT_TILE_BYTES : nullptr);
+        publish((save_hidden && my_acts) ? my_acts + (kActsPerTile + blk) * CN_ACT_TILE_BYTES : nullptr, true);
         if (tr && blk == 0) CN_TRACE_AT(pi, 11);
         mbar_wait(smem_u32(&bars.h_ready[t]), n_h & 1u);
         ++n_h;
@@ -558,7 +581,7 @@ CN_TRACE_READER(cn_debug_read_trace_fwd)
 
 static int launch_fwd(bool fusion, const void *packed, const void *in_tiles, int64_t n_tiles, int nv,
                       int64_t tiles_per_view, void *out_tiles, float *rgbs, void *acts, float *taps,
-                      cudaStream_t st, int tap_bf16 = 0) {
+                      cudaStream_t st, int tap_bf16 = 0, int save_hidden = 0, const void *mask_acts = nullptr) {
   const int64_t n_pairs = (n_tiles + 1) / 2;
   const unsigned grid = (unsigned)(n_pairs < num_sms() ? n_pairs : num_sms());
   cudaError_t e;
@@ -568,14 +591,16 @@ static int launch_fwd(bool fusion, const void *packed, const void *in_tiles, int
     if (e == cudaSuccess)
       mlp_fwd_kernel<true><<<grid, kFwdThreads, bytes, st>>>((const uint8_t *)packed, (const uint8_t *)in_tiles,
                                                              n_tiles, nv, tiles_per_view, (uint8_t *)out_tiles, rgbs,
-                                                             (uint8_t *)acts, taps, tap_bf16);
+                                                             (uint8_t *)acts, taps, tap_bf16, save_hidden,
+                                                             (const uint8_t *)mask_acts);
   } else {
     constexpr uint32_t bytes = FwdSmem<false>::kBytes;
     e = cudaFuncSetAttribute(mlp_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e == cudaSuccess)
       mlp_fwd_kernel<false><<<grid, kFwdThreads, bytes, st>>>((const uint8_t *)packed, (const uint8_t *)in_tiles,
                                                               n_tiles, nv, tiles_per_view, (uint8_t *)out_tiles, rgbs,
-                                                              (uint8_t *)acts, nullptr, 0);
+                                                              (uint8_t *)acts, nullptr, 0, save_hidden,
+                                                              (const uint8_t *)mask_acts);
   }
   if (e != cudaSuccess) {
     set_error("mlp_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
@@ -635,4 +660,33 @@ extern "C" int cn_mlp_fusion_fwd_tap_tiles(const void *packed, const void *h3_ti
   if (tiles_per_view == 0) return 0;
   return launch_fwd(true, packed, h3_tiles, (int64_t)b * tiles_per_view, nv, tiles_per_view, nullptr, rgbs, acts,
                     (float *)tap_tiles, (cudaStream_t)stream, 1);
+}
+
+// ---- pose-query training (delta_ngf/model.py:264-296: d/dW of a function of d prediction / d pose)
+extern "C" int cn_mlp_feature_fwd_ex(const void *packed, const void *x_tiles, int64_t n_tiles, void *h3_tiles, void *acts,
+                                     int32_t save_hidden, const void *mask_acts, void *stream) {
+  using namespace cn;
+  CN_REQUIRE(packed && x_tiles && h3_tiles, "cn_mlp_feature_fwd_ex: null pointer");
+  CN_REQUIRE(n_tiles >= 0, "cn_mlp_feature_fwd_ex: n_tiles %lld", (long long)n_tiles);
+  CN_REQUIRE(!(mask_acts && acts), "cn_mlp_feature_fwd_ex: the tangent pass (mask_acts) saves nothing");
+  CN_REQUIRE((((uintptr_t)packed | (uintptr_t)x_tiles | (uintptr_t)h3_tiles | (uintptr_t)acts | (uintptr_t)mask_acts) & 127) == 0,
+             "cn_mlp_feature_fwd_ex: buffers must be 128-byte aligned");
+  if (n_tiles == 0) return 0;
+  return launch_fwd(false, packed, x_tiles, n_tiles, 1, n_tiles, h3_tiles, nullptr, acts, nullptr, (cudaStream_t)stream, 0,
+                    save_hidden, mask_acts);
+}
+
+extern "C" int cn_mlp_fusion_fwd_taps_ex(const void *packed, const void *h3_tiles, int32_t b, int32_t nv,
+                                         int64_t tiles_per_view, float *rgbs, void *acts, void *taps, int32_t tap_bf16,
+                                         int32_t save_hidden, const void *mask_acts, void *stream) {
+  using namespace cn;
+  CN_REQUIRE(packed && h3_tiles && rgbs && taps, "cn_mlp_fusion_fwd_taps_ex: null pointer");
+  CN_REQUIRE(b > 0 && nv > 0 && tiles_per_view >= 0, "cn_mlp_fusion_fwd_taps_ex: b=%d nv=%d tiles_per_view=%lld", b, nv,
+             (long long)tiles_per_view);
+  CN_REQUIRE(!(mask_acts && acts), "cn_mlp_fusion_fwd_taps_ex: the tangent pass (mask_acts) saves nothing");
+  CN_REQUIRE((((uintptr_t)packed | (uintptr_t)h3_tiles | (uintptr_t)rgbs | (uintptr_t)acts | (uintptr_t)taps |
+               (uintptr_t)mask_acts) & 127) == 0, "cn_mlp_fusion_fwd_taps_ex: buffers must be 128-byte aligned");
+  if (tiles_per_view == 0) return 0;
+  return launch_fwd(true, packed, h3_tiles, (int64_t)b * tiles_per_view, nv, tiles_per_view, nullptr, rgbs, acts,
+                    (float *)taps, (cudaStream_t)stream, tap_bf16, save_hidden, mask_acts);
 }

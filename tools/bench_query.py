@@ -7,7 +7,7 @@
                     480x640x256 fp32 maps), 4096 pose guesses x 42 query offsets = 516 096 query rows per step,
                     forward + pose-gradient backward + optimizer step (grasp_optimizer.py:158-184)
   * train_step    : DeltaNGF.train_step at the reference's training size -- b = 1, nv = 3, np = 192 poses
-                    (8 064 query points, 24 192 per-view rows), two forwards, pose gradient, tangent pass, head update
+                    (8 064 query points, 24 192 per-view rows), two forwards, pose gradient, tangent pass (forward kernels with the primal masks), head update
 Device-timed with CUDA events; synthetic scene, random-init weights."""
 from __future__ import annotations
 
