@@ -497,6 +497,12 @@ def run_b200(args):
         if world == 1 and not args.no_cpu_baseline:
             base, _ = cpu_baseline(nv, min(args.ref_rays, nr))
             out['cpu_baseline'] = base
+        if world == 1 and args.other_configs and args.workload == 'cfg2' and not args.lowres_features:
+            # this process keeps its buffers; drop what the timed loops held so that the children have the device
+            del step_timed, trainer, model, feats, maps
+            gc.collect()
+            torch.cuda.empty_cache()
+            out['other_configs'] = other_configs()
         print(json.dumps(out))
     if world > 1:
         sys.stdout.flush()
@@ -507,6 +513,44 @@ def run_b200(args):
         torch.cuda.synchronize()
         dist.barrier()
         dist.destroy_process_group()
+
+
+def other_configs():
+    """The other BASELINE.json configs, each measured by its own short child process on the same GPU after the main
+    measurement (device-timed inside the child; see the tools' docstrings): cfg1 / cfg3(i) / the cfg5 per-GPU shard
+    through this file, cfg4 through tools/bench_render_view.py, cfg3(ii) through tools/bench_query.py."""
+    py = sys.executable
+    runs = {
+        'cfg1': [py, os.path.join(ROOT, 'bench.py'), '--workload', 'cfg1', '--steps', '10', '--no-cpu-baseline', '--no-other-configs'],
+        'cfg3i': [py, os.path.join(ROOT, 'bench.py'), '--workload', 'cfg3i', '--steps', '10', '--no-cpu-baseline', '--no-other-configs'],
+        'cfg2_lowres_features': [py, os.path.join(ROOT, 'bench.py'), '--lowres-features', '--steps', '10', '--no-cpu-baseline'],
+        'cfg5_shard_1gpu': [py, os.path.join(ROOT, 'bench.py'), '--workload', 'cfg5shard', '--steps', '2', '--warmup', '3',
+                            '--no-cpu-baseline', '--no-other-configs'],
+        'cfg4_render_view_224': [py, os.path.join(ROOT, 'tools', 'bench_render_view.py'), '--size', '224x224'],
+        'cfg4_render_view_480x640': [py, os.path.join(ROOT, 'tools', 'bench_render_view.py'), '--size', '480x640', '--steps', '3'],
+        'cfg3ii_pose_query': [py, os.path.join(ROOT, 'tools', 'bench_query.py'), '--steps', '10'],
+    }
+    keep = ('case', 'metric', 'value', 'unit', 'ms_per_step', 'ms_per_image', 'rows_per_step', 'gpu_launches', 'launch_mode')
+    res = {}
+    for name, cmd in runs.items():
+        try:
+            r = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
+            lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith('{')]
+            if r.returncode != 0 or not lines:
+                res[name] = {'error': (r.stderr or 'no output').strip().splitlines()[-1][:200]}
+                continue
+            ents = []
+            for d in lines:
+                e = {k: d[k] for k in keep if k in d}
+                if isinstance(d.get('config'), dict):
+                    e['workload'] = d['config'].get('workload')
+                if isinstance(d.get('e2e'), dict):
+                    e['e2e'] = {k: d['e2e'][k] for k in ('value', 'unit', 'ms_per_step') if k in d['e2e']}
+                ents.append(e)
+            res[name] = ents[0] if len(ents) == 1 else ents
+        except Exception as ex:          # a child that fails or hangs must not take the headline line with it
+            res[name] = {'error': f'{type(ex).__name__}: {ex}'[:200]}
+    return res
 
 
 def main():
@@ -526,6 +570,8 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--lowres-features', action='store_true',
                     help='feed the 240x320 input of the final 2x bilinear UpSampling2D; the upsample is folded into the gather')
+    ap.add_argument('--no-other-configs', dest='other_configs', action='store_false',
+                    help='skip the short child runs of the other BASELINE.json configs (cfg1, cfg3, cfg4, cfg5 shard) behind the default line')
     ap.add_argument('--no-cfg5', action='store_true', help='skip the cfg5 strong-scaling shard of the 8-GPU run')
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
