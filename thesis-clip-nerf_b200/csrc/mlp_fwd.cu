@@ -100,13 +100,17 @@ __device__ __forceinline__ void epi_tmem_to_act(uint32_t taddr, const float *__r
   }
 }
 
-template <bool kFusion>
+// kExt: the pose-query extensions (bf16 tap tiles, saved hidden activations, tangent pass with external masks) are
+// compiled into their own instantiations -- the render path's kernels carry none of their predicates or registers.
+template <bool kFusion, bool kExt>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ in_tiles, int64_t n_tiles,
                int nv, int64_t tiles_per_view, uint8_t *__restrict__ out_tiles, float *__restrict__ rgbs,
-               uint8_t *__restrict__ acts, float *__restrict__ taps, int tap_bf16, int save_hidden,
-               const uint8_t *__restrict__ mask_acts) {
+               uint8_t *__restrict__ acts, float *__restrict__ taps, int tap_bf16_arg, int save_hidden_arg,
+               const uint8_t *__restrict__ mask_acts_arg) {
   using L = FwdSmem<kFusion>;
+  const int tap_bf16 = kExt ? tap_bf16_arg : 0, save_hidden = kExt ? save_hidden_arg : 0;
+  const uint8_t *const mask_acts = kExt ? mask_acts_arg : nullptr;
   constexpr int kRingSlots = L::kRingSlots;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) FwdBars bars;
@@ -579,29 +583,36 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
 
 CN_TRACE_READER(cn_debug_read_trace_fwd)
 
+template <bool kFusion, bool kExt>
+static cudaError_t launch_fwd_t(unsigned grid, const void *packed, const void *in_tiles, int64_t n_tiles, int nv,
+                                int64_t tiles_per_view, void *out_tiles, float *rgbs, void *acts, float *taps,
+                                cudaStream_t st, int tap_bf16, int save_hidden, const void *mask_acts) {
+  constexpr uint32_t bytes = FwdSmem<kFusion>::kBytes;
+  cudaError_t e = cudaFuncSetAttribute(mlp_fwd_kernel<kFusion, kExt>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (e == cudaSuccess)
+    mlp_fwd_kernel<kFusion, kExt><<<grid, kFwdThreads, bytes, st>>>(
+        (const uint8_t *)packed, (const uint8_t *)in_tiles, n_tiles, nv, tiles_per_view, (uint8_t *)out_tiles, rgbs,
+        (uint8_t *)acts, taps, tap_bf16, save_hidden, (const uint8_t *)mask_acts);
+  return e;
+}
+
 static int launch_fwd(bool fusion, const void *packed, const void *in_tiles, int64_t n_tiles, int nv,
                       int64_t tiles_per_view, void *out_tiles, float *rgbs, void *acts, float *taps,
                       cudaStream_t st, int tap_bf16 = 0, int save_hidden = 0, const void *mask_acts = nullptr) {
   const int64_t n_pairs = (n_tiles + 1) / 2;
   const unsigned grid = (unsigned)(n_pairs < num_sms() ? n_pairs : num_sms());
+  const bool ext = tap_bf16 || save_hidden || mask_acts;
   cudaError_t e;
-  if (fusion) {
-    constexpr uint32_t bytes = FwdSmem<true>::kBytes;
-    e = cudaFuncSetAttribute(mlp_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-    if (e == cudaSuccess)
-      mlp_fwd_kernel<true><<<grid, kFwdThreads, bytes, st>>>((const uint8_t *)packed, (const uint8_t *)in_tiles,
-                                                             n_tiles, nv, tiles_per_view, (uint8_t *)out_tiles, rgbs,
-                                                             (uint8_t *)acts, taps, tap_bf16, save_hidden,
-                                                             (const uint8_t *)mask_acts);
-  } else {
-    constexpr uint32_t bytes = FwdSmem<false>::kBytes;
-    e = cudaFuncSetAttribute(mlp_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-    if (e == cudaSuccess)
-      mlp_fwd_kernel<false><<<grid, kFwdThreads, bytes, st>>>((const uint8_t *)packed, (const uint8_t *)in_tiles,
-                                                              n_tiles, nv, tiles_per_view, (uint8_t *)out_tiles, rgbs,
-                                                              (uint8_t *)acts, nullptr, 0, save_hidden,
-                                                              (const uint8_t *)mask_acts);
-  }
+  if (fusion)
+    e = ext ? launch_fwd_t<true, true>(grid, packed, in_tiles, n_tiles, nv, tiles_per_view, out_tiles, rgbs, acts, taps, st,
+                                       tap_bf16, save_hidden, mask_acts)
+            : launch_fwd_t<true, false>(grid, packed, in_tiles, n_tiles, nv, tiles_per_view, out_tiles, rgbs, acts, taps, st,
+                                        0, 0, nullptr);
+  else
+    e = ext ? launch_fwd_t<false, true>(grid, packed, in_tiles, n_tiles, nv, tiles_per_view, out_tiles, rgbs, acts, nullptr,
+                                        st, 0, save_hidden, mask_acts)
+            : launch_fwd_t<false, false>(grid, packed, in_tiles, n_tiles, nv, tiles_per_view, out_tiles, rgbs, acts, nullptr,
+                                         st, 0, 0, nullptr);
   if (e != cudaSuccess) {
     set_error("mlp_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     return (int)e;
