@@ -262,6 +262,7 @@ def run_b200(args):
     model.compile()                      # default optimizer: RenderTrainer on the model's flat parameter buffer
     model.max_rays_per_step = args.chunk_rays
     trainer = model.optimizer
+    trainer.overlap_allreduce = not args.no_overlap_allreduce   # all-reduce started inside the backward, under the map sweep
     feats = maps.detach().reshape(1, nv, Hf, Wf, C).requires_grad_(True)       # same storage, the trainer's leaf
     dev_inputs = [t.to(dev, non_blocking=True) for t in sc['inputs']]
     dev_u = [sc[k].to(dev, non_blocking=True) for k in ('u_strat', 'u_pdf', 'target')]
@@ -340,6 +341,17 @@ def run_b200(args):
         ms, ms_per_rank = timed(step_timed, args.steps)
         clocks.mark(False)
     launches = launches_per_step * args.steps      # kernels of this library inside the timed region (replayed or eager)
+    # > 1 rank: the same step WITHOUT the gradient all-reduce (every rank on its own), to attribute the growth of the
+    # step from 1 to N ranks: collective (+ the rank skew it absorbs) vs per-GPU slow-down on a fully loaded node
+    ms_solo_per_rank = None
+    if world > 1 and use_graph:
+        trainer.world = 1
+        solo = trainer.capture(dev_inputs, feats, dev_u[2], dev_u[0], dev_u[1], NEAR, FAR)
+        trainer.world = world
+        for _ in range(2):
+            solo()
+        _, ms_solo_per_rank = timed(solo, args.steps)
+        del solo
     run_e2e(4)          # warm the loop: device batch slots, pinned rings, copy stream, one graph per buffer set
     ms_e2e, ms_e2e_per_rank = timed(run_e2e, args.steps, loop=True)
 
@@ -488,11 +500,19 @@ def run_b200(args):
                             'on the device as the reference does; combined_features stay on the device, where the upstream '
                             'encoders produce them (model.feature_fn plug-in returns the resident maps and receives their gradient)'},
             'gpu_launches': launches, 'launch_mode': 'cuda graph replay' if use_graph else 'eager',
+            'overlap_allreduce': world > 1 and not args.no_overlap_allreduce,
             'clocks': clocks.summary(), 'roofline': roofline, 'stages': stage_report, 'mlp': whole,
         }
         if world > 1:
             out['ms_per_step_per_rank'] = [round(x, 4) for x in ms_per_rank]
             out['e2e']['ms_per_step_per_rank'] = [round(x, 4) for x in ms_e2e_per_rank]
+            if ms_solo_per_rank is not None:
+                out['ms_per_step_without_allreduce_per_rank'] = [round(x, 4) for x in ms_solo_per_rank]
+                out['scaling_note'] = ('with the all-reduce recorded in the graph every rank reports the same step (the '
+                                       'collective absorbs the skew); ms_per_step_without_allreduce_per_rank is the same '
+                                       'graph without it, all ranks running at once: step minus its max = the cost of the '
+                                       'collective, its spread = rank skew, its level vs the 1-GPU run = what a fully '
+                                       'loaded node (power cap, shared host) costs every GPU')
         out.update(extra)
         if world == 1 and not args.no_cpu_baseline:
             base, _ = cpu_baseline(nv, min(args.ref_rays, nr))
@@ -572,6 +592,8 @@ def main():
                     help='feed the 240x320 input of the final 2x bilinear UpSampling2D; the upsample is folded into the gather')
     ap.add_argument('--no-other-configs', dest='other_configs', action='store_false',
                     help='skip the short child runs of the other BASELINE.json configs (cfg1, cfg3, cfg4, cfg5 shard) behind the default line')
+    ap.add_argument('--no-overlap-allreduce', action='store_true',
+                    help='> 1 rank: all-reduce behind the backward instead of inside it (NCCL stream, under the feature-map sweep)')
     ap.add_argument('--no-cfg5', action='store_true', help='skip the cfg5 strong-scaling shard of the 8-GPU run')
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]

@@ -77,7 +77,9 @@ class RenderTrainer:
         # True: start the all-reduce inside the backward, under the feature-map sweep (render.GRAD_SYNC).  Measured on
         # 8 B200s it is no faster than the plain all-reduce behind the backward (7.40 vs 7.32 ms / step; 7.31 vs 7.33 on 2):
         # the 1.98 MB collective costs ~50 us over NVSwitch and its kernel competes with the sweep for SMs -- off by default
-        self.overlap_allreduce = False
+        # > 1 rank: the all-reduce starts inside the backward, right after the last weight-gradient kernel, and runs on
+        # NCCL's stream under the feature-map sweep (8 GPUs, graph replay: 7.08 -> 7.04 ms per step, the whole cost of the collective)
+        self.overlap_allreduce = True
         self._t_dev = None          # device-side step counter (float64) of apply_gradients_on_device
         self._synced = False
         self.world = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1

@@ -2,9 +2,9 @@
 # ncu --set full over the launches of ONE DNGFOptimizer.optimize_pose step (our kernels only) of tools/bench_query.py;
 # raw page exported on the box and summarised.   usage: tools/gpu_profile_query.sh <out name> [launches per step]
 mkdir -p gpurun_out
-N=${2:-21}
+N=${2:-26}
 CMD="python tools/bench_query.py --case optimize_pose --steps 1 --warmup 3"
-RE='^(bin_|composite_|feature_grad|mlp_|pack_weights|project_|readout_|sample_|tile_rows|tile_add_rows|generate_rays|quantize|depth_minmax)'
+RE='^(bin_|composite_|feature_grad|mlp_|pack_weights|project_|readout_|sample_|tile_rows|tile_add_rows|tile_add_tiles|grasp_|pose_points|query_tangent|generate_rays|quantize|depth_minmax)'
 $CMD > gpurun_out/plain_$1.json 2> gpurun_out/plain_$1.err || { echo "plain run failed"; exit 1; }
 ncu --set full --clock-control none -k "regex:$RE" -s $((3 * N)) -c $N -o /tmp/$1 -f $CMD > gpurun_out/ncu_$1.log 2>&1
 echo "capture rc=$?"
