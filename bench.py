@@ -278,7 +278,7 @@ def run_b200(args):
         ds = SyntheticNerfDataset(n_scenes=n_scenes, n_perspectives=nv + 1, H=H, W=W, seed=seed)
         return MVNeRFDataGenerator(ds, n_rays_train=nr, batch_size=1, n_views=nv, shuffle=True)
     np.random.seed(1000 + rank)
-    gen_warm, gen_timed = make_generator(4, 7 + rank), make_generator(args.steps, 11 + rank)
+    gen_warm, gen_timed = make_generator(8, 7 + rank), make_generator(args.steps, 11 + rank)   # 8 warm batches: every slot of the pinned ring (6) exists
     item = gen_warm.compact_item(0)
     h2d_bytes = sum(int(np.asarray(a).nbytes) for a in item[0]) + int(np.asarray(item[1]).size) * 4   # targets go up as fp32
     n_tracked = [0]
@@ -352,7 +352,7 @@ def run_b200(args):
             solo()
         _, ms_solo_per_rank = timed(solo, args.steps)
         del solo
-    run_e2e(4)          # warm the loop: device batch slots, pinned rings, copy stream, one graph per buffer set
+    run_e2e(8)          # warm the loop: device batch slots, all 6 pinned ring slots, copy stream, one graph per buffer set
     ms_e2e, ms_e2e_per_rank = timed(run_e2e, args.steps, loop=True)
 
     # ---- per-stage device times (CUDA events around every ABI call), separate instrumented pass

@@ -308,13 +308,14 @@ class DevicePrefetcher:
         self.free = [None] * depth             # event: the consumer is done with the set
         self.k = 0
         self.next = None
-        self._upload()
+        self.exhausted = False
 
     def _upload(self):
         try:
             host = next(self.it)
         except StopIteration:
             self.next = None
+            self.exhausted = True
             return
         k = self.k % len(self.slots)
         self.k += 1
@@ -336,16 +337,21 @@ class DevicePrefetcher:
         return self
 
     def __next__(self):
+        # The upload of batch i is enqueued here, i.e. right after the host has enqueued step i-1: it runs on the copy
+        # stream while step i-1 runs on the device (the host is ahead of the device in steady state), and the FIRST
+        # step of a loop is enqueued as soon as its own batch exists -- not after the producer has made a second one
+        # (that cost every fit() call ~2 ms of an idle device per 1.2 ms batch the producer needs)
+        if self.next is None and not self.exhausted:
+            self._upload()
         if self.next is None:
             raise StopIteration
         k, ready = self.next
+        self.next = None
         cur = torch.cuda.current_stream(self.device)
         cur.wait_event(ready)
         if self.free[k] is None:
             self.free[k] = torch.cuda.Event()
-        batch = self.slots[k]
-        self._upload()                          # next batch goes out while this one is consumed
-        return k, batch, self.free[k]
+        return k, self.slots[k], self.free[k]
 
 
 class _LossReader:
