@@ -11,8 +11,8 @@ import json
 import sys
 
 # kernel name prefix -> ABI stage it belongs to (the stage's other kernels are small)
-STAGE = [('void tile_rows_kernel<0>', 'cn_project_gather_fwd (tile_rows)'), ('void mlp_fwd_kernel<0>', 'cn_mlp_feature_fwd'),
-         ('void mlp_fwd_kernel<1>', 'cn_mlp_fusion_fwd'), ('mlp_block_bwd_kernel', 'cn_mlp_block_bwd'),
+STAGE = [('void tile_rows_kernel<0>', 'cn_project_gather_fwd (tile_rows)'), ('mlp_fwd_kernel<0', 'cn_mlp_feature_fwd'),
+         ('mlp_fwd_kernel<1', 'cn_mlp_fusion_fwd'), ('mlp_block_bwd_kernel', 'cn_mlp_block_bwd'),
          ('mlp_l0_wgrad_kernel', 'cn_mlp_l0_wgrad'), ('mlp_l0_dgrad_kernel', 'cn_mlp_l0_dgrad'),
          ('void tile_rows_kernel<1>', 'cn_project_gather_bwd (tile_rows)'), ('feature_grad_kernel', 'cn_feature_grad'),
          ('void tile_rows_lr_kernel<0>', 'cn_project_gather_fwd (tile_rows)'),
@@ -37,7 +37,7 @@ def main(src, dst):
         total_us += float(r[col['gpu__time_duration.sum']]) * {'us': 1.0, 'ms': 1e3, 'ns': 1e-3}[units[col['gpu__time_duration.sum']]]
         n_all += 1
         for prefix, stage in STAGE:
-            if name.startswith(prefix):
+            if prefix.replace('void ', '') in name:
                 a = acc.setdefault(stage, [0, 0.0, 0.0])
                 a[0] += 1
                 a[1] += gb(r, 'dram__bytes_read.sum') + gb(r, 'dram__bytes_write.sum')
