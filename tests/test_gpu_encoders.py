@@ -33,3 +33,32 @@ def test_model_v4_call_with_and_without_the_final_upsample(cuda):
         assert x.shape == y.shape and torch.isfinite(x).all()
         print(f'[model_v4] {name}: folded vs full-resolution {rel_err(y, x):.2e}')
         assert rel_err(y, x) < 1e-2
+
+
+def test_language_nerf_call_runs_the_reference_chain(cuda):
+    """LanguageNeRF(encoders=True): CLIP plug-ins -> VisualFeatures -> CombineCLIPVisualV4(use_dense, elu) -> the sm_100a
+    pose-query path (lmvnerf/model_v4.py:178-187), full-resolution maps against the pre-upsample maps."""
+    from oracle import nerf_oracle as O
+    from src.lib.lmvnerf.model_v4 import LanguageNeRF
+    b, nv, n_pts = 1, 2, 6
+    sc = O.synthetic_scene(3, b, nv, 8, 480, 640, C=8)
+    g = torch.Generator().manual_seed(5)
+    pyramid = [torch.randn(nv, 1024, generator=g), torch.randn(nv, 56, 56, 256, generator=g), torch.randn(nv, 28, 28, 512, generator=g),
+               torch.randn(nv, 14, 14, 1024, generator=g), torch.randn(nv, 7, 7, 2048, generator=g)]
+    text = torch.randn(nv, 1024, generator=g)
+    clip_v = lambda images: tuple(t.to(images.device) for t in pyramid)   # noqa: E731
+    clip_t = lambda tokens: text.to(cuda)                                 # noqa: E731
+    torch.manual_seed(0)
+    models = [LanguageNeRF(n_views=nv, batch_size=b, n_points_train=n_pts, encoders=True, clip_visual=clip_v, clip_textual=clip_t,
+                           lowres_features=low, device=cuda).eval() for low in (False, True)]
+    models[1].load_state_dict(models[0].state_dict())
+    t, r = O.synthetic_poses(0, b, n_pts)
+    _, _, img, K, E = sc['inputs']
+    outs = []
+    for m in models:
+        m.set_pose(t, r)
+        with torch.no_grad():
+            outs.append(m.call((None, None, None, None, img, K, E, torch.zeros(nv, 77, dtype=torch.long))))
+    assert outs[0].shape == (b, n_pts) and torch.isfinite(outs[0]).all()
+    print('[LanguageNeRF] folded vs full-resolution maps', rel_err(outs[1], outs[0]))
+    assert rel_err(outs[1], outs[0]) < 1e-2
