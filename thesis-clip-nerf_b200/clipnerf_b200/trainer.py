@@ -235,6 +235,36 @@ class HostBatch(list):
         self.copied = None
 
 
+# One long-lived producer thread per process: starting a thread cost every fit() call ~3 ms before its second batch
+# could begin (tools/diag_fit.py); jobs that arrive while it is busy get a thread of their own.
+_producer_jobs = queue.Queue()
+_producer_state = {'thread': None, 'busy': False}
+_producer_lock = threading.Lock()
+
+
+def _producer_loop():
+    while True:
+        job = _producer_jobs.get()
+        try:
+            job()
+        finally:
+            with _producer_lock:
+                _producer_state['busy'] = False
+
+
+def _producer_submit(job):
+    with _producer_lock:
+        if _producer_state['thread'] is None or not _producer_state['thread'].is_alive():
+            _producer_state['thread'] = threading.Thread(target=_producer_loop, daemon=True)
+            _producer_state['thread'].start()
+            _producer_state['busy'] = False
+        if _producer_state['busy']:
+            threading.Thread(target=job, daemon=True).start()
+            return
+        _producer_state['busy'] = True
+    _producer_jobs.put(job)
+
+
 class PinnedBatchQueue:
     """``sequence[i]`` for ``i in indices`` -> pinned host batches, produced by ONE background thread a few batches
     ahead of the consumer -- the role of Keras' ``OrderedEnqueuer`` (workers = 1) under ``fit``
@@ -253,28 +283,42 @@ class PinnedBatchQueue:
             ring[:] = self.ring
             self.ring = ring
         self.error = None
-        self.thread = threading.Thread(target=self._run, daemon=True)
-        self.thread.start()
+        # The FIRST batch is assembled by the calling thread, the rest by the background thread (same order of the
+        # numpy RNG draws): the caller's core is awake, a freshly started thread on an idle core needed 4 ms instead
+        # of 1.1 ms for it (tools/diag_fit.py) -- and the device sits idle until the first batch exists
+        self.first = 0
+        if self.indices:
+            try:
+                self._produce(0, self.indices[0])
+                self.first = 1
+            except BaseException as e:
+                self.error = e
+                self.first = len(self.indices)
+        _producer_submit(self._run)
+
+    def _produce(self, n, i):
+        arrays = [torch.as_tensor(a) for a in self.flatten(self.getter(i))]
+        arrays = [a.to(torch.float32) if a.dtype == torch.float64 else a for a in arrays]
+        k = n % len(self.ring)
+        old = self.ring[k]
+        if old is not None:
+            old.uploaded.wait()
+            if old.copied is not None:
+                old.copied.synchronize()
+        if old is None or any(o.shape != a.shape or o.dtype != a.dtype for o, a in zip(old, arrays)):
+            bufs = [torch.empty(a.shape, dtype=a.dtype).pin_memory() for a in arrays]
+        else:
+            bufs = list(old)
+        for b_, a in zip(bufs, arrays):
+            b_.copy_(a)
+        self.ring[k] = HostBatch(bufs)
+        self.q.put(self.ring[k])
 
     def _run(self):
         try:
             for n, i in enumerate(self.indices):
-                arrays = [torch.as_tensor(a) for a in self.flatten(self.getter(i))]
-                arrays = [a.to(torch.float32) if a.dtype == torch.float64 else a for a in arrays]
-                k = n % len(self.ring)
-                old = self.ring[k]
-                if old is not None:
-                    old.uploaded.wait()
-                    if old.copied is not None:
-                        old.copied.synchronize()
-                if old is None or any(o.shape != a.shape or o.dtype != a.dtype for o, a in zip(old, arrays)):
-                    bufs = [torch.empty(a.shape, dtype=a.dtype).pin_memory() for a in arrays]
-                else:
-                    bufs = list(old)
-                for b_, a in zip(bufs, arrays):
-                    b_.copy_(a)
-                self.ring[k] = HostBatch(bufs)
-                self.q.put(self.ring[k])
+                if n >= self.first:
+                    self._produce(n, i)
         except BaseException as e:          # surfaced in the consumer
             self.error = e
         self.q.put(None)
@@ -298,10 +342,10 @@ class DevicePrefetcher:
     once; two device buffer sets are recycled, guarded by events (a set is overwritten only after the
     step that read it has finished)."""
 
-    def __init__(self, batches, device, depth: int = 2, slots=None):
+    def __init__(self, batches, device, depth: int = 2, slots=None, copy_stream=None):
         self.it = iter(batches)
         self.device = device
-        self.copy_stream = torch.cuda.Stream(device)
+        self.copy_stream = copy_stream if copy_stream is not None else torch.cuda.Stream(device)
         # device tensors of each buffer set; a caller that needs stable addresses (CUDA graphs) passes its own list
         self.slots = slots if slots is not None else [None] * depth
         depth = len(self.slots)
@@ -358,9 +402,11 @@ class _LossReader:
     """losses of the steps, copied to pinned host memory asynchronously and read two steps late (the launch queue
     holds up to two steps, so host jitter of a whole step does not idle the device)"""
 
-    def __init__(self, device):
+    def __init__(self, device, ring=None):
         self.cur = torch.cuda.current_stream(device)
-        self.ring = torch.empty(4, dtype=torch.float32, pin_memory=True)     # pinned once: no host allocation in the loop
+        # pinned once: no host allocation in the loop -- and, handed in by a caller that loops over many fit() calls,
+        # none per call either (cudaHostAlloc + stream creation cost the first launch of every call ~3 ms)
+        self.ring = ring if ring is not None else torch.empty(4, dtype=torch.float32, pin_memory=True)
         self.k, self.pending, self.losses = 0, [], []
 
     def push(self, loss):
@@ -433,11 +479,14 @@ def fit_host_batches_graph(trainer: RenderTrainer, batches, features, near, far,
     ``features_tensor.grad``)."""
     dev = trainer.params.device
     cur = torch.cuda.current_stream(dev)
-    reader = _LossReader(dev)
     graphs = trainer.__dict__.setdefault('_graphs', {})
     slots = trainer.__dict__.setdefault('_graph_slots', [None, None])
     state = trainer.__dict__.setdefault('_graph_state', {})
-    for k, batch, done in DevicePrefetcher(batches, dev, slots=slots):
+    if 'loss_ring' not in state:           # per-trainer, not per call: pinned loss ring and the copy stream
+        state['loss_ring'] = torch.empty(4, dtype=torch.float32, pin_memory=True)
+        state['copy_stream'] = torch.cuda.Stream(dev)
+    reader = _LossReader(dev, state['loss_ring'])
+    for k, batch, done in DevicePrefetcher(batches, dev, slots=slots, copy_stream=state['copy_stream']):
         inputs, feats, target, u_s, u_p = _step_operands(trainer, k, batch, features, draws, state)
         key = tuple(t.data_ptr() for t in batch) + (feats.data_ptr(), u_s.data_ptr(), u_p.data_ptr())
         if trainer.iterations == 0:

@@ -31,6 +31,17 @@ _ci = g.compact_item
 def ci(i):
     a = time.perf_counter(); r = _ci(i); prod.append((a, time.perf_counter())); return r
 g.compact_item = ci
+from clipnerf_b200 import trainer as T
+marks = []
+def wrap(obj, name, tag):
+    f = getattr(obj, name)
+    def g_(*a, **k):
+        a0 = time.perf_counter(); r = f(*a, **k); marks.append((tag, a0, time.perf_counter())); return r
+    setattr(obj, name, g_)
+wrap(T.DevicePrefetcher, '_upload', 'upload')
+wrap(T, '_step_operands', 'operands')
+wrap(T.PinnedBatchQueue, '_produce', 'produce')
+wrap(T._LossReader, 'push', 'push')
 e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
 t0 = time.perf_counter(); e0.record()
 model.fit(g, epochs=1)
@@ -39,6 +50,7 @@ e1.record(); torch.cuda.synchronize()
 print('fit: host', round(1e3 * t_fit, 2), 'ms, device', round(e0.elapsed_time(e1), 2), 'ms for 20 steps')
 print('device: start -> end of step 0:', round(e0.elapsed_time(events[0]), 2), 'ms; step intervals:',
       [round(events[i].elapsed_time(events[i + 1]), 2) for i in range(len(events) - 1)], '; last step -> end', round(events[-1].elapsed_time(e1), 2))
+print('main/producer marks (ms after start):', [(t, round(1e3 * (a - t0), 2), round(1e3 * (b - t0), 2)) for t, a, b in marks[:14]])
 print('producer: compact_item (start, end) ms after start:', [(round(1e3 * (a - t0), 1), round(1e3 * (b - t0), 1)) for a, b in prod[:6]])
 print('host: enqueue times of the steps (ms after start):', [round(1e3 * (h - t0), 1) for h in hosts])
 import cProfile, pstats
