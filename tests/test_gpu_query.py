@@ -388,3 +388,37 @@ def test_tangent_kernels_match_the_torch_form(cuda, nv, n):
         med, p90, mx, l2 = _row_stats(got[i], ref[i])
         print(f'[tangent kernels nv={nv} n={n}] d tap {name}: median {med:.2e} p90 {p90:.2e} max {mx:.2e} L2 {l2:.2e}')
         assert p90 < 1e-2 and l2 < 1e-2 and mx < 3e-2, (name, med, p90, mx, l2)
+
+
+def test_delta_ngf_fit_with_graph_trains_every_batch_once(cuda):
+    """DeltaNGF.fit(graph=True) == the eager fit: first step eager (creates the Adam state), the rest replayed"""
+    from clipnerf_b200 import params
+    from src.lib.delta_ngf.model import DeltaNGF
+    from oracle import nerf_oracle as O
+    b, nv, n_pts = 1, 2, 24
+    sc = O.synthetic_scene(12, b, nv, 8, 48, 64)
+    named = O.init_params(9, bias_std=0.02)
+    named.update(O.init_grasp_readout(2, bias_std=0.02))
+    _, _, img, K, E = sc['inputs']
+    feats = sc['features'].to(cuda)
+
+    def batch(seed):
+        lp, tp = O.synthetic_poses(seed, b, n_pts), O.synthetic_poses(seed + 50, b, n_pts)
+        g = torch.Generator().manual_seed(seed)
+        return (lp[0], lp[1], tp[0], tp[1], img, K, E), (torch.rand(b, n_pts, generator=g), torch.randn(b, n_pts, 3, generator=g),
+                                                           torch.randn(b, n_pts, 4, generator=g))
+    batches = [batch(s) for s in (1, 2, 3)]
+    hist = []
+    for graph in (False, True):
+        m = DeltaNGF(n_views=nv, batch_size=b, n_points_train=n_pts, device=cuda)
+        with torch.no_grad():
+            m.fine_embedding.flat.copy_(params.from_named(named, 'fine')[:m.fine_embedding.flat.numel()].to(cuda))
+        m.grasp_readout.load_keras_variables(named)
+        m.feature_fn = lambda flat: feats.reshape(b * nv, *feats.shape[2:])
+        m.compile()
+        hist.append((m.fit(batches, epochs=2, graph=graph), [p.detach().clone() for p in m.grasp_readout.parameters()]))
+    for he, hg in zip(hist[0][0], hist[1][0]):
+        for k in he:
+            assert abs(he[k] - hg[k]) < 1e-4 * max(1.0, abs(he[k])), (k, he[k], hg[k])
+    for pe, pg in zip(hist[0][1], hist[1][1]):
+        assert rel_err(pg, pe) < 1e-4

@@ -185,9 +185,14 @@ class _PoseQueryModel(torch.nn.Module):
         replay = None
         for epoch in range(initial_epoch, epochs):
             if graph and hasattr(self, 'capture_train_step') and len(generator):
+                logs, first = [], 0
                 if replay is None:
-                    replay = self.capture_train_step(generator[0])
-                logs = [dict(replay(generator[i])) for i in range(len(generator))]
+                    # the very first step runs eagerly (it creates the optimizer state), the recording follows it
+                    # without training: every batch is trained on exactly once
+                    logs.append(self.train_step(generator[0]))
+                    replay = self.capture_train_step(generator[0], warmup=0)
+                    first = 1
+                logs += [{k: v.clone() for k, v in replay(generator[i]).items()} for i in range(first, len(generator))]
             else:
                 logs = [self.train_step(generator[i]) for i in range(len(generator))]
             if hasattr(generator, 'on_epoch_end'):
@@ -288,7 +293,8 @@ class DeltaNGF(_PoseQueryModel):
         overwritten by the next replay); ``warmup`` >= 1 eager steps on ``data`` precede the capture and DO train (the
         optimizer state has to exist before the capture: a state tensor created while recording would be re-initialised
         by every replay)."""
-        assert warmup >= 1, 'the optimizer state must be created by an eager step before the capture'
+        has_state = len(getattr(self.optimizer, 'state', {})) > 0
+        assert warmup >= 1 or has_state, 'the optimizer state must be created by an eager step before the capture'
         inputs, labels = data
         s_in = [self._to_dev(x).clone() for x in inputs[:7]]
         s_lab = [self._to_dev(x).clone() for x in labels]
