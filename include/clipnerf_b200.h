@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define CN_ABI_VERSION 9
+#define CN_ABI_VERSION 10
 #define CN_TILE_ROWS 128
 #define CN_HIDDEN 128
 #define CN_FEAT_C 256          /* combined_features channels (model_v0.py:60)            */
@@ -227,6 +227,17 @@ int cn_mlp_feature_fwd(const void *packed, const void *x_tiles, int64_t n_tiles,
  *   acts (nullable): [n_out_tiles][4] activation tiles (3 x relu(h), relu(e)).           */
 int cn_mlp_fusion_fwd(const void *packed, const void *h3_tiles, int32_t b, int32_t nv,
                       int64_t tiles_per_view, float *rgbs, void *acts, void *stream);
+
+/* ONE source view (nv = 1: nerf_1_view, the reference's default config; the pose-query validation loop): the mean
+ * over views (layers.py:368-370) is the identity, so both stages and the readout run in one launch --
+ * cn_mlp_feature_fwd + cn_mlp_fusion_fwd[_taps / _tap_tiles] (+ the _ex options) with bit-identical results; the bf16
+ * per-view output never reaches memory.  n_tiles = b * nr * S / 128.  acts_f / acts_u (both or neither): the saved
+ * activation tiles of the two stages in the layouts above (3 and 4 tiles per tile; 6 and 7 with save_hidden).
+ * taps / tap_mode: 0 none, 1 fp32 rows [4][n_tiles*128][128], 2 bf16 tile images [4][n_tiles][32 KiB].
+ * mask_acts_f / mask_acts_u (both or neither, acts must be NULL): the tangent pass.               */
+int cn_mlp_chain_fwd(const void *packed, const void *x_tiles, int64_t n_tiles, float *rgbs, void *acts_f, void *acts_u,
+                     void *taps, int32_t tap_mode, int32_t save_hidden, const void *mask_acts_f, const void *mask_acts_u,
+                     void *stream);
 
 /* fusion stage with `complete_output` taps (layers.py:352,376-377; consumed as
  * `fine_embedding(...)[4:]` by delta_ngf/model.py:240-241, lmvnerf/model_v4.py, grasp_mvnerf/model.py):

@@ -236,3 +236,32 @@ def test_stage_backward_matches_the_block_by_block_chain(cuda, nv, rows):
     none = ops.mlp_stage_bwd(packed, 0, acts_f, 3, g_d, grad_d, ws, views=nv, b=b, scale=s, x_tiles=x_tiles,
                              want_dx=False, first_dense=True)
     assert none is None and rel_err(grad_d, grad_a) < 2e-5
+
+
+@pytest.mark.parametrize('n_tiles', [2, 5, 301])
+def test_chained_single_view_forward_is_the_two_kernel_path_bit_for_bit(cuda, n_tiles):
+    """cn_mlp_chain_fwd (nv = 1: per-view stage + fusion stage + readout in one launch) against cn_mlp_feature_fwd +
+    cn_mlp_fusion_fwd_taps: rgb / sigma, all seven saved activation tiles (ten with the hidden ones), the four taps as
+    fp32 rows and as bf16 tiles, and the tangent pass -- identical bits."""
+    from clipnerf_b200 import _abi, ops
+    g = torch.Generator().manual_seed(n_tiles)
+    params = (torch.randn(_abi.NET_PARAMS, generator=g) * 0.08).to(cuda)
+    packed = ops.pack_weights(params)
+    x = (torch.randn(n_tiles * 128 * 384, generator=g) * 0.5).to(torch.bfloat16).to(cuda).view(torch.uint8)
+    for hidden in (False, True):
+        h3, acts_f = ops.mlp_feature_fwd(packed, x, True, save_hidden=hidden)
+        taps, rgbs, acts_u = ops.mlp_fusion_fwd_taps(packed, h3, 1, 1, True, save_hidden=hidden)
+        c_rgbs, c_af, c_au, c_taps = ops.mlp_chain_fwd(packed, x, True, taps='f32', save_hidden=hidden)
+        assert torch.equal(c_rgbs, rgbs) and torch.equal(c_taps, taps)
+        assert torch.equal(c_af, acts_f) and torch.equal(c_au, acts_u)
+    # plain render-path form (no taps) and the bf16 tap tiles
+    rgbs0, acts_u0 = ops.mlp_fusion_fwd(packed, ops.mlp_feature_fwd(packed, x, True)[0], 1, 1, True)
+    c_rgbs, _, c_au, none = ops.mlp_chain_fwd(packed, x, True)
+    assert none is None and torch.equal(c_rgbs, rgbs0) and torch.equal(c_au, acts_u0)
+    tiles, _, _ = ops.mlp_fusion_fwd_tap_tiles(packed, ops.mlp_feature_fwd(packed, x, False)[0], 1, 1, False)
+    assert torch.equal(ops.mlp_chain_fwd(packed, x, False, taps='bf16')[3], tiles)
+    # tangent pass: masks of a save_hidden forward, tangent rows in
+    xd = (torch.randn(n_tiles * 128 * 384, generator=g) * 0.5).to(torch.bfloat16).to(cuda).view(torch.uint8)
+    h3d, _ = ops.mlp_feature_fwd(packed, xd, False, mask_acts=acts_f)
+    td, _, _ = ops.mlp_fusion_fwd_taps(packed, h3d, 1, 1, False, mask_acts=acts_u)
+    assert torch.equal(ops.mlp_chain_fwd(packed, xd, False, taps='f32', mask_acts_f=acts_f, mask_acts_u=acts_u)[3], td)

@@ -11,7 +11,7 @@ from ctypes import c_char_p, c_double, c_float, c_int32, c_int64, c_size_t, c_vo
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), 'lib', 'libclipnerf_b200.so')
 
-ABI_VERSION = 9
+ABI_VERSION = 10
 TILE_ROWS = 128
 SLAB_BYTES = 16384
 ACT_TILE_BYTES = 32768
@@ -56,6 +56,7 @@ PROTOTYPES = {
     'cn_pack_weights': [_P, _P, _P],
     'cn_mlp_feature_fwd': [_P, _P, c_int64, _P, _P, _P],
     'cn_mlp_fusion_fwd': [_P, _P, c_int32, c_int32, c_int64, _P, _P, _P],
+    'cn_mlp_chain_fwd': [_P, _P, c_int64, _P, _P, _P, _P, c_int32, c_int32, _P, _P, _P],
     'cn_mlp_fusion_fwd_taps': [_P, _P, c_int32, c_int32, c_int64, _P, _P, _P, _P],
     'cn_tile_add_rows': [_P, _P, c_int64, c_int32, _P],
     'cn_mlp_fusion_fwd_tap_tiles': [_P, _P, c_int32, c_int32, c_int64, _P, _P, _P, _P],

@@ -298,6 +298,29 @@ def query_tangent_x(scene: Scene, pts, drs, u_pts, u_dirs) -> torch.Tensor:
     return x
 
 
+def mlp_chain_fwd(packed, x_tiles, save_acts: bool, taps: Optional[str] = None, save_hidden: bool = False,
+                  mask_acts_f=None, mask_acts_u=None):
+    """ONE source view: per-view stage, fusion stage and readout in one launch (bit-identical to the two-kernel path).
+    ``taps``: None, 'f32' (rows [4, rows, 128]) or 'bf16' (tile images [4, n_tiles * ACT_TILE_BYTES]).
+    Returns (rgbs [rows, 4], acts_f, acts_u, taps)."""
+    nt = x_tiles.numel() // X_TILE_BYTES
+    dev = x_tiles.device
+    rows = nt * TILE_ROWS
+    rgbs = torch.empty(rows, 4, dtype=torch.float32, device=dev)
+    tangent = mask_acts_f is not None
+    extra = 3 if (save_hidden or tangent) else 0
+    acts_f = _bytes(nt * (FEATURE_ACTS + extra) * ACT_TILE_BYTES, dev) if (save_acts and not tangent) else None
+    acts_u = _bytes(nt * (FUSION_ACTS + extra) * ACT_TILE_BYTES, dev) if (save_acts and not tangent) else None
+    t, mode = None, 0
+    if taps == 'f32':
+        t, mode = torch.empty(4, rows, 128, dtype=torch.float32, device=dev), 1
+    elif taps == 'bf16':
+        t, mode = torch.empty(4, nt * ACT_TILE_BYTES, dtype=torch.uint8, device=dev), 2
+    call('cn_mlp_chain_fwd', _ptr(packed), _ptr(x_tiles), nt, _ptr(rgbs), _ptr(acts_f), _ptr(acts_u), _ptr(t), mode,
+         int(save_hidden), _ptr(mask_acts_f), _ptr(mask_acts_u), _stream())
+    return rgbs, acts_f, acts_u, t
+
+
 def mlp_fusion_fwd(packed, h3_tiles, b: int, nv: int, save_acts: bool):
     nt = h3_tiles.numel() // ACT_TILE_BYTES
     assert nt % (b * nv) == 0

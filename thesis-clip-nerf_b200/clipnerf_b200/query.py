@@ -17,6 +17,7 @@ from typing import List
 import torch
 
 from . import ops
+from . import render as _render
 from ._abi import HEAD_OFFSETS as _HEAD_OFFSETS, NET_PARAMS, TILE_ROWS
 
 
@@ -46,8 +47,11 @@ class _QueryEmbedFn(torch.autograd.Function):
         x, ws = ops.project_gather_fwd(scene, pts, drs, z, return_ws=True)
         # the hidden activations are kept as well (3 more tiles per tile): the tangent pass of a double backward
         # (DeltaNGF.train_step) takes its ReLU patterns from them
-        h3, acts_f = ops.mlp_feature_fwd(packed, x, need_grad, save_hidden=need_grad)
-        taps, _rgbs, acts_u = ops.mlp_fusion_fwd_taps(packed, h3, b, scene.nv, need_grad, save_hidden=need_grad)
+        if scene.nv == 1 and _render.CHAIN_SINGLE_VIEW:
+            _rgbs, acts_f, acts_u, taps = ops.mlp_chain_fwd(packed, x, need_grad, taps='f32', save_hidden=need_grad)
+        else:
+            h3, acts_f = ops.mlp_feature_fwd(packed, x, need_grad, save_hidden=need_grad)
+            taps, _rgbs, acts_u = ops.mlp_fusion_fwd_taps(packed, h3, b, scene.nv, need_grad, save_hidden=need_grad)
         if need_grad:
             st = _State()
             st.fa, st.ua = ops.FEATURE_ACTS + 3, ops.FUSION_ACTS + 3      # act_stride_tiles of the backward kernels
@@ -146,8 +150,11 @@ class _QueryGraspFn(torch.autograd.Function):
         z = torch.zeros(b, n_pad, 1, dtype=torch.float32, device=pts.device)
         packed = ops.pack_weights(params)
         x, ws = ops.project_gather_fwd(scene, pts, drs, z, return_ws=True)
-        h3, acts_f = ops.mlp_feature_fwd(packed, x, need_grad)
-        taps, _rgbs, acts_u = ops.mlp_fusion_fwd_tap_tiles(packed, h3, b, scene.nv, need_grad)
+        if scene.nv == 1 and _render.CHAIN_SINGLE_VIEW:
+            _rgbs, acts_f, acts_u, taps = ops.mlp_chain_fwd(packed, x, need_grad, taps='bf16')
+        else:
+            h3, acts_f = ops.mlp_feature_fwd(packed, x, need_grad)
+            taps, _rgbs, acts_u = ops.mlp_fusion_fwd_tap_tiles(packed, h3, b, scene.nv, need_grad)
         y, head = ops.grasp_head_fwd(taps, b, n_pad, n_poses, head_pack, elu, need_grad)
         if need_grad:
             st = _State()

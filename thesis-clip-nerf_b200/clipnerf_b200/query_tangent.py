@@ -32,8 +32,12 @@ def query_tangent(scene: ops.Scene, packed: torch.Tensor, pts, drs, acts_f, acts
         b, n = pts.shape[:2]
         assert n % TILE_ROWS == 0
         x_dot = ops.query_tangent_x(scene, pts, drs, u_pts, u_dirs)
-        h3_dot, _ = ops.mlp_feature_fwd(packed, x_dot, False, mask_acts=acts_f)
-        taps, _, _ = ops.mlp_fusion_fwd_taps(packed, h3_dot, b, scene.nv, False, mask_acts=acts_u)
+        from . import render as _render
+        if scene.nv == 1 and _render.CHAIN_SINGLE_VIEW:
+            _, _, _, taps = ops.mlp_chain_fwd(packed, x_dot, False, taps='f32', mask_acts_f=acts_f, mask_acts_u=acts_u)
+        else:
+            h3_dot, _ = ops.mlp_feature_fwd(packed, x_dot, False, mask_acts=acts_f)
+            taps, _, _ = ops.mlp_fusion_fwd_taps(packed, h3_dot, b, scene.nv, False, mask_acts=acts_u)
         return list(taps.view(4, b, n, 128).unbind(0))
 
 

@@ -27,8 +27,12 @@ def _pass_fwd(packed, scene: ops.Scene, ray_o, ray_d, z, save: bool) -> _Pass:
     P = _Pass()
     P.z, P.packed = z, packed
     P.x, P.ws = ops.project_gather_fwd(scene, ray_o, ray_d, z, return_ws=True)
-    h3, P.acts_f = ops.mlp_feature_fwd(packed, P.x, save)
-    P.rgbs, P.acts_u = ops.mlp_fusion_fwd(packed, h3, scene.b, scene.nv, save)
+    if scene.nv == 1 and CHAIN_SINGLE_VIEW:
+        # one source view: both MLP stages + readout in one launch (cn_mlp_chain_fwd), same bits
+        P.rgbs, P.acts_f, P.acts_u, _ = ops.mlp_chain_fwd(packed, P.x, save)
+    else:
+        h3, P.acts_f = ops.mlp_feature_fwd(packed, P.x, save)
+        P.rgbs, P.acts_u = ops.mlp_fusion_fwd(packed, h3, scene.b, scene.nv, save)
     P.rgb, P.depth, P.weights = ops.composite_fwd(z, P.rgbs.view(*z.shape, 4))
     if not save:
         P.x = P.ws = None
@@ -73,6 +77,9 @@ def _pass_bwd(P: _Pass, params, grad, scene: ops.Scene, ray_o, ray_d, d_rgb, d_d
 # cfg2 step the two are within 2 % (profiles/README.md, round 2), the per-block launches ahead: the block backward is
 # bound by shared-memory bandwidth inside the SM, not by HBM, so the default stays False.
 CHAINED_STAGES = os.environ.get('CN_CHAINED_STAGES', '0') == '1'
+
+# nv = 1: chain the fusion stage onto the per-view stage in one kernel (False: the two-kernel path, for comparison)
+CHAIN_SINGLE_VIEW = os.environ.get('CN_CHAIN_SINGLE_VIEW', '1') == '1'
 
 # Set by RenderTrainer for the duration of a backward on > 1 rank: callable([2, NET_PARAMS] gradient buffer) -> a
 # work handle with .wait() (torch.distributed all_reduce(async_op=True)); None = no collective inside the backward.

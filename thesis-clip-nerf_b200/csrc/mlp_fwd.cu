@@ -29,17 +29,18 @@ constexpr int kMaxStageViews = 3;                                  // views stag
 constexpr uint32_t kSmemAct = 0;                                   // 2 x 32 KiB
 constexpr uint32_t kSmemRing = 2 * CN_ACT_TILE_BYTES;
 constexpr uint32_t kSmemTabBytes = 7 * 128 * 4 + 512 * 4 + 16;
+constexpr uint32_t kSmemTabBytesChain = 14 * 128 * 4 + 512 * 4 + 16;   // both stages' tables (chained kernel)
 // Rings of 16 KiB slabs.  Fusion stage: ONE 8-slot ring (per-view tiles + weights).  Per-view stage: a 4-slot weight
 // ring and a 5-slot ring of X slabs with its own producer warp, so that the first X slabs of the NEXT pair stream in
 // from HBM while the blocks of this pair run.  tools/trace_mlp_fwd.py: the first Dense of a pair still takes ~9000 of
 // the pair's ~28000 cycles -- 80 KiB in flight against ~3500 cycles of loaded HBM latency is 23 B/clk, the SM's fair
 // share of HBM; the stage moves 224 KiB per tile through HBM (X in, 3 activation tiles + h3 out) and is bound by that.
-template <bool kFusion> struct FwdSmem {
+template <bool kFusion, bool kChain = false> struct FwdSmem {
   static constexpr int kRingSlots = kFusion ? 8 : 4;
   static constexpr int kXSlots = kFusion ? 0 : 5;
   static constexpr uint32_t kXRing = kSmemRing + kRingSlots * CN_SLAB_BYTES;
   static constexpr uint32_t kTab = kXRing + kXSlots * CN_SLAB_BYTES;
-  static constexpr uint32_t kBytes = kTab + kSmemTabBytes + 1024;  // + alignment slack
+  static constexpr uint32_t kBytes = kTab + (kChain ? kSmemTabBytesChain : kSmemTabBytes) + 1024;  // + alignment slack
 };
 
 struct FwdBars {
@@ -102,15 +103,25 @@ __device__ __forceinline__ void epi_tmem_to_act(uint32_t taddr, const float *__r
 
 // kExt: the pose-query extensions (bf16 tap tiles, saved hidden activations, tangent pass with external masks) are
 // compiled into their own instantiations -- the render path's kernels carry none of their predicates or registers.
-template <bool kFusion, bool kExt>
+// kChain (per-view stage only, nv = 1): with ONE source view the mean over views is the identity, so the fusion stage
+// is chained onto the per-view stage inside the same kernel -- six blocks and the readout per tile; the bf16 per-view
+// output never leaves the SM (it is rounded to bf16 in registers exactly as the two-kernel path stores it, so the
+// results are bit-identical), the fusion stage's lock-step prologue disappears, and both stages' saved activation
+// tiles are written in the layouts the backward kernels already read.
+template <bool kFusion, bool kExt, bool kChain = false>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ in_tiles, int64_t n_tiles,
                int nv, int64_t tiles_per_view, uint8_t *__restrict__ out_tiles, float *__restrict__ rgbs,
                uint8_t *__restrict__ acts, float *__restrict__ taps, int tap_bf16_arg, int save_hidden_arg,
-               const uint8_t *__restrict__ mask_acts_arg) {
-  using L = FwdSmem<kFusion>;
+               const uint8_t *__restrict__ mask_acts_arg, uint8_t *__restrict__ acts_u = nullptr,
+               const uint8_t *__restrict__ mask_acts_u_arg = nullptr) {
+  static_assert(!(kFusion && kChain), "the chained kernel is the per-view kernel continued");
+  using L = FwdSmem<kFusion, kChain>;
   const int tap_bf16 = kExt ? tap_bf16_arg : 0, save_hidden = kExt ? save_hidden_arg : 0;
   const uint8_t *const mask_acts = kExt ? mask_acts_arg : nullptr;
+  const uint8_t *const mask_acts_u = kExt ? mask_acts_u_arg : nullptr;
+  constexpr int kNumBlk = kChain ? 6 : 3;                 // blocks per tile
+  constexpr int kRoOff = (kChain ? 14 : 7) * 128;         // readout weights behind the bias tables
   constexpr int kRingSlots = L::kRingSlots;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) FwdBars bars;
@@ -135,8 +146,10 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
     const float *gt = reinterpret_cast<const float *>(packed + kPackTables);
     for (int i = threadIdx.x; i < 7 * 128; i += kFwdThreads)
       tab[i] = mask_acts ? 0.f : gt[(kFusion ? kTabFusion : kTabFeature) + i];
-    if (kFusion)
-      for (int i = threadIdx.x; i < 516; i += kFwdThreads) tab[7 * 128 + i] = gt[kTabReadoutW + i];
+    if (kChain)
+      for (int i = threadIdx.x; i < 7 * 128; i += kFwdThreads) tab[7 * 128 + i] = mask_acts ? 0.f : gt[kTabFusion + i];
+    if (kFusion || kChain)
+      for (int i = threadIdx.x; i < 516; i += kFwdThreads) tab[kRoOff + i] = gt[kTabReadoutW + i];
   }
   if (threadIdx.x == 0) {
     for (int i = 0; i < kRingSlots; ++i) {
@@ -194,7 +207,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         if (!kFusion) {
           for (int kb = 0; kb < 6; ++kb) load(packed + kPackFwdW0 + kb * CN_SLAB_BYTES);
           CN_TRACE_AT(pi, 21);
-          for (int blk = 0; blk < 3; ++blk)
+          for (int blk = 0; blk < kNumBlk; ++blk)
             for (int j = 0; j < 2; ++j) load_weights(blk, j);
           CN_TRACE_AT(pi, 22);
         } else {
@@ -290,7 +303,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
           }
           CN_TRACE_AT(pi, 1);
         }
-        for (int blk = 0; blk < 3; ++blk) {
+        for (int blk = 0; blk < kNumBlk; ++blk) {
           for (int j = 0; j < 2; ++j) {
             // ring order of the fusion stage: views(t0), Wa0, views(t1), Wb0, ...  The view slabs are read by
             // the epilogue warps, but this thread stays the ONLY in-order waiter on the ring's full barriers
@@ -310,7 +323,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
               ++n_act[t];
               tc_fence_after();
               if (blk == 0 && j == 0 && t == 0) CN_TRACE_AT(pi, 2);
-              if (blk == 2 && j == 1 && t == 1) CN_TRACE_AT(pi, 3);
+              if (blk == kNumBlk - 1 && j == 1 && t == 1) CN_TRACE_AT(pi, 3);
               if (j == 0) {
                 gemm_act(t, tmem + t * 256 + 128, s0, s1, false);
                 umma_commit(smem_u32(&bars.tmp_ready[t]));
@@ -377,10 +390,10 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
       const uint8_t *my_mask = mask_acts ? mask_acts + tile * (int64_t)acts_stride * CN_ACT_TILE_BYTES : nullptr;
       // fusion stage, pose-query models: taps[s][row][128] fp32, s = (mean, block 4, block 5, block 6 output)
       const int64_t tap_stride = n_tiles * (int64_t)(128 * 128);
-      float *my_tap = (kFusion && taps && !tap_bf16) ? taps + (tile * 128 + row) * 128 : nullptr;
+      float *my_tap = ((kFusion || kChain) && taps && !tap_bf16) ? taps + (tile * 128 + row) * 128 : nullptr;
       // ... or as bf16 activation-tile images [4][n_tiles][32 KiB] (the operand tiles of cn_grasp_head_fwd)
       const int64_t tap16_stride = n_tiles * (int64_t)CN_ACT_TILE_BYTES;
-      uint8_t *my_tap16 = (kFusion && taps && tap_bf16)
+      uint8_t *my_tap16 = ((kFusion || kChain) && taps && tap_bf16)
                               ? reinterpret_cast<uint8_t *>(taps) + tile * (int64_t)CN_ACT_TILE_BYTES : nullptr;
 
       if (kFusion) {
@@ -476,15 +489,18 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         if (tr) CN_TRACE_AT(pi, 8);
       }
 
-      for (int blk = 0; blk < 3; ++blk) {
-        if (!(kFusion && blk == 0)) {
+      // one ResNet block of a stage: tb = the stage's cumulative-bias tables, sacts = its saved-activation tiles of this
+      // tile (n_acts regular ones, the hidden activations behind them), smask = the tangent pass's mask tiles
+      auto run_block = [&](int blk, bool skip_ea, const float *tb, uint8_t *sacts, int n_acts, const uint8_t *smask,
+                           bool with_taps) {
+        if (!skip_ea) {
           // E_a: relu(h + cumulative bias) -> operand of the block's first Dense
           acquire();
-          epi_tmem_to_act<true>(t_h, tab + (2 * blk) * 128, act, row, half,
-                                (kFusion && my_tap) ? my_tap + blk * tap_stride : nullptr,
-                                (kFusion && my_tap16) ? my_tap16 + blk * tap16_stride : nullptr,
-                                my_mask ? my_mask + blk * CN_ACT_TILE_BYTES : nullptr);
-          publish(my_acts ? my_acts + blk * CN_ACT_TILE_BYTES : nullptr, true);
+          epi_tmem_to_act<true>(t_h, tb + (2 * blk) * 128, act, row, half,
+                                (with_taps && my_tap) ? my_tap + blk * tap_stride : nullptr,
+                                (with_taps && my_tap16) ? my_tap16 + blk * tap16_stride : nullptr,
+                                smask ? smask + blk * CN_ACT_TILE_BYTES : nullptr);
+          publish(sacts ? sacts + blk * CN_ACT_TILE_BYTES : nullptr, true);
           if (tr && blk == 0) CN_TRACE_AT(pi, 9);
         }
         // E_b: relu(t + ba) -> operand of the block's second Dense
@@ -493,29 +509,20 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         tc_fence_after();
         if (tr && blk == 0) CN_TRACE_AT(pi, 10);
         acquire();
-        epi_tmem_to_act<true>(t_tmp, tab + (2 * blk + 1) * 128, act, row, half, nullptr, nullptr,
-                              my_mask ? my_mask + (kActsPerTile + blk) * CN_ACT_TILE_BYTES : nullptr);
-        publish((save_hidden && my_acts) ? my_acts + (kActsPerTile + blk) * CN_ACT_TILE_BYTES : nullptr, true);
+        epi_tmem_to_act<true>(t_tmp, tb + (2 * blk + 1) * 128, act, row, half, nullptr, nullptr,
+                              smask ? smask + (n_acts + blk) * CN_ACT_TILE_BYTES : nullptr);
+        publish((save_hidden && sacts) ? sacts + (n_acts + blk) * CN_ACT_TILE_BYTES : nullptr, true);
         if (tr && blk == 0) CN_TRACE_AT(pi, 11);
         mbar_wait(smem_u32(&bars.h_ready[t]), n_h & 1u);
         ++n_h;
         tc_fence_after();
         if (tr && blk == 0) CN_TRACE_AT(pi, 12);
-      }
-      if (tr) CN_TRACE_AT(pi, 13);
-
-      acquire();
-      if (!kFusion) {
-        // ---- h3 = h + cumulative bias -> bf16 tile for the fusion stage
-        epi_tmem_to_act<false>(t_h, tab + 6 * 128, act, row, half);
-        tc_fence_before();
-        mbar_arrive(smem_u32(&bars.h_free[t]));
-        publish(out_tiles + tile * (int64_t)CN_ACT_TILE_BYTES, false);
-      } else {
+      };
+      auto readout = [&](const float *tb, uint8_t *sacts, bool release_h) {
         // ---- readout: relu(e) . Wr + br, sigmoid / softplus (layers.py:392-397).  The two column-half
         // warps of a row split the OUTPUTS (half 0: r,g; half 1: b,sigma), each over all 128 inputs; the
         // relu(e) tile saved for the backward is still written half by half.
-        const float *wr = tab + 7 * 128;
+        const float *wr = tab + kRoOff;
         // two accumulator chains per output: one chain of 128 dependent FMAs per output made this epilogue latency bound
         float ya = wr[512 + 2 * half], yb = wr[512 + 2 * half + 1], ya1 = 0.f, yb1 = 0.f;
 #pragma unroll 1
@@ -530,7 +537,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
               const int col = c4 * 32 + q * 8 + i;
-              v[i] = fmaxf(__uint_as_float(r[q * 8 + i]) + tab[6 * 128 + col], 0.f);
+              v[i] = fmaxf(__uint_as_float(r[q * 8 + i]) + tb[6 * 128 + col], 0.f);
               const float2 w = *reinterpret_cast<const float2 *>(wr + col * 4 + 2 * half);
               if (i & 1) {
                 ya1 += v[i] * w.x;
@@ -544,7 +551,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
               // e itself (pre-ReLU) is the tap; v[] holds relu(e), so re-add from the accumulator
               float ev[8];
 #pragma unroll
-              for (int i = 0; i < 8; ++i) ev[i] = __uint_as_float(r[q * 8 + i]) + tab[6 * 128 + c4 * 32 + q * 8 + i];
+              for (int i = 0; i < 8; ++i) ev[i] = __uint_as_float(r[q * 8 + i]) + tb[6 * 128 + c4 * 32 + q * 8 + i];
               if (my_tap) {
                 float *dst = my_tap + 3 * tap_stride + c4 * 32 + q * 8;
                 *reinterpret_cast<float4 *>(dst) = make_float4(ev[0], ev[1], ev[2], ev[3]);
@@ -555,7 +562,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
                                pack_bf16x2(ev[6], ev[7]));
               }
             }
-            if (my_acts && mine)
+            if (sacts && mine)
               *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, c4 * 4 + q)) =
                   make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
                              pack_bf16x2(v[6], v[7]));
@@ -567,7 +574,75 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         o.x = 1.f / (1.f + expf(-ya));
         o.y = half ? (yb > 20.f ? yb : log1pf(expf(yb))) : 1.f / (1.f + expf(-yb));
         reinterpret_cast<float2 *>(rgbs)[(tile * 128 + row) * 2 + half] = o;
-        publish(my_acts ? my_acts + 3 * CN_ACT_TILE_BYTES : nullptr, false);
+        if (release_h) {                                   // chained kernel: the next pair's first Dense overwrites h
+          tc_fence_before();
+          mbar_arrive(smem_u32(&bars.h_free[t]));
+        }
+        publish(sacts ? sacts + 3 * CN_ACT_TILE_BYTES : nullptr, false);
+      };
+
+      for (int blk = 0; blk < 3; ++blk) run_block(blk, kFusion && blk == 0, tab, my_acts, kActsPerTile, my_mask, kFusion);
+      if (tr) CN_TRACE_AT(pi, 13);
+
+      acquire();
+      if (kFusion) {
+        readout(tab, my_acts, false);
+      } else if (!kChain) {
+        // ---- h3 = h + cumulative bias -> bf16 tile for the fusion stage
+        epi_tmem_to_act<false>(t_h, tab + 6 * 128, act, row, half);
+        tc_fence_before();
+        mbar_arrive(smem_u32(&bars.h_free[t]));
+        publish(out_tiles + tile * (int64_t)CN_ACT_TILE_BYTES, false);
+      } else {
+        // ---- chained fusion stage (nv = 1).  m = bf16(h + cumulative bias) is what the two-kernel path stores as the
+        // per-view output and reads back as the mean over its one view: the fp32 stream restarts from it.
+        const float *tabu = tab + 7 * 128;
+        const int acts_stride_u = 4 + ((save_hidden || mask_acts_u) ? 3 : 0);
+        uint8_t *my_acts_u = acts_u ? acts_u + tile * (int64_t)acts_stride_u * CN_ACT_TILE_BYTES : nullptr;
+        const uint8_t *my_mask_u = mask_acts_u ? mask_acts_u + tile * (int64_t)acts_stride_u * CN_ACT_TILE_BYTES : nullptr;
+#pragma unroll 1
+        for (int c2 = 0; c2 < 2; ++c2) {
+          uint32_t r[32];
+          tmem_ld32(t_h + half * 64 + c2 * 32, r);
+          tmem_wait_ld();
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t chunk = half * 8 + c2 * 4 + q;
+            const float *bq = tab + 6 * 128 + chunk * 8;
+            uint32_t w[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              w[i] = cvt_bf16x2(__uint_as_float(r[q * 8 + 2 * i]) + bq[2 * i], __uint_as_float(r[q * 8 + 2 * i + 1]) + bq[2 * i + 1]);
+              r[q * 8 + 2 * i] = __float_as_uint(bf16_lo(w[i]));
+              r[q * 8 + 2 * i + 1] = __float_as_uint(bf16_hi(w[i]));
+            }
+            if (my_tap) {
+              *reinterpret_cast<float4 *>(my_tap + chunk * 8) = make_float4(__uint_as_float(r[q * 8]), __uint_as_float(r[q * 8 + 1]),
+                                                                            __uint_as_float(r[q * 8 + 2]), __uint_as_float(r[q * 8 + 3]));
+              *reinterpret_cast<float4 *>(my_tap + chunk * 8 + 4) = make_float4(__uint_as_float(r[q * 8 + 4]), __uint_as_float(r[q * 8 + 5]),
+                                                                                __uint_as_float(r[q * 8 + 6]), __uint_as_float(r[q * 8 + 7]));
+            }
+            if (my_tap16) *reinterpret_cast<uint4 *>(my_tap16 + tile_chunk_off(row, chunk)) = make_uint4(w[0], w[1], w[2], w[3]);
+            uint4 o;
+            if (my_mask_u) {
+              const uint4 mk = ldg_nc_u4(my_mask_u + tile_chunk_off(row, chunk));
+              o = make_uint4(mul_bf16x2(w[0], gt0_bf16x2(mk.x)), mul_bf16x2(w[1], gt0_bf16x2(mk.y)),
+                             mul_bf16x2(w[2], gt0_bf16x2(mk.z)), mul_bf16x2(w[3], gt0_bf16x2(mk.w)));
+            } else {
+              float m[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) m[i] = fmaxf(__uint_as_float(r[q * 8 + i]), 0.f);
+              o = make_uint4(pack_bf16x2(m[0], m[1]), pack_bf16x2(m[2], m[3]), pack_bf16x2(m[4], m[5]), pack_bf16x2(m[6], m[7]));
+            }
+            *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, chunk)) = o;
+          }
+          tmem_st32(t_h + half * 64 + c2 * 32, r);
+        }
+        tmem_wait_st();
+        publish(my_acts_u, true);
+        for (int blk = 0; blk < 3; ++blk) run_block(blk, blk == 0, tabu, my_acts_u, 4, my_mask_u, true);
+        acquire();
+        readout(tabu, my_acts_u, true);
       }
       if (tr) CN_TRACE_AT(pi, 14);
       ring_base += 12u + view_slots * ((2 * p + 1 < n_tiles) ? 2u : 1u);
@@ -583,16 +658,19 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
 
 CN_TRACE_READER(cn_debug_read_trace_fwd)
 
-template <bool kFusion, bool kExt>
+template <bool kFusion, bool kExt, bool kChain = false>
 static cudaError_t launch_fwd_t(unsigned grid, const void *packed, const void *in_tiles, int64_t n_tiles, int nv,
                                 int64_t tiles_per_view, void *out_tiles, float *rgbs, void *acts, float *taps,
-                                cudaStream_t st, int tap_bf16, int save_hidden, const void *mask_acts) {
-  constexpr uint32_t bytes = FwdSmem<kFusion>::kBytes;
-  cudaError_t e = cudaFuncSetAttribute(mlp_fwd_kernel<kFusion, kExt>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+                                cudaStream_t st, int tap_bf16, int save_hidden, const void *mask_acts,
+                                void *acts_u = nullptr, const void *mask_acts_u = nullptr) {
+  constexpr uint32_t bytes = FwdSmem<kFusion, kChain>::kBytes;
+  cudaError_t e = cudaFuncSetAttribute(mlp_fwd_kernel<kFusion, kExt, kChain>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)bytes);
   if (e == cudaSuccess)
-    mlp_fwd_kernel<kFusion, kExt><<<grid, kFwdThreads, bytes, st>>>(
+    mlp_fwd_kernel<kFusion, kExt, kChain><<<grid, kFwdThreads, bytes, st>>>(
         (const uint8_t *)packed, (const uint8_t *)in_tiles, n_tiles, nv, tiles_per_view, (uint8_t *)out_tiles, rgbs,
-        (uint8_t *)acts, taps, tap_bf16, save_hidden, (const uint8_t *)mask_acts);
+        (uint8_t *)acts, taps, tap_bf16, save_hidden, (const uint8_t *)mask_acts, (uint8_t *)acts_u,
+        (const uint8_t *)mask_acts_u);
   return e;
 }
 
@@ -700,4 +778,34 @@ extern "C" int cn_mlp_fusion_fwd_taps_ex(const void *packed, const void *h3_tile
   if (tiles_per_view == 0) return 0;
   return launch_fwd(true, packed, h3_tiles, (int64_t)b * tiles_per_view, nv, tiles_per_view, nullptr, rgbs, acts,
                     (float *)taps, (cudaStream_t)stream, tap_bf16, save_hidden, mask_acts);
+}
+
+// ---- nv = 1: per-view stage + fusion stage + readout in one launch (the mean over one view is the identity)
+extern "C" int cn_mlp_chain_fwd(const void *packed, const void *x_tiles, int64_t n_tiles, float *rgbs, void *acts_f,
+                                void *acts_u, void *taps, int32_t tap_mode, int32_t save_hidden, const void *mask_acts_f,
+                                const void *mask_acts_u, void *stream) {
+  using namespace cn;
+  CN_REQUIRE(packed && x_tiles && rgbs, "cn_mlp_chain_fwd: null pointer");
+  CN_REQUIRE(n_tiles >= 0, "cn_mlp_chain_fwd: n_tiles %lld", (long long)n_tiles);
+  CN_REQUIRE(tap_mode >= 0 && tap_mode <= 2 && (tap_mode == 0) == (taps == nullptr), "cn_mlp_chain_fwd: tap_mode %d (0 none, "
+             "1 fp32 rows, 2 bf16 tiles) does not match taps", tap_mode);
+  CN_REQUIRE((acts_f == nullptr) == (acts_u == nullptr), "cn_mlp_chain_fwd: acts_f and acts_u go together");
+  CN_REQUIRE((mask_acts_f == nullptr) == (mask_acts_u == nullptr) && !(mask_acts_f && acts_f),
+             "cn_mlp_chain_fwd: the tangent pass takes both mask buffers and saves nothing");
+  CN_REQUIRE((((uintptr_t)packed | (uintptr_t)x_tiles | (uintptr_t)rgbs | (uintptr_t)acts_f | (uintptr_t)acts_u | (uintptr_t)taps |
+               (uintptr_t)mask_acts_f | (uintptr_t)mask_acts_u) & 127) == 0, "cn_mlp_chain_fwd: buffers must be 128-byte aligned");
+  if (n_tiles == 0) return 0;
+  const int64_t n_pairs = (n_tiles + 1) / 2;
+  const unsigned grid = (unsigned)(n_pairs < num_sms() ? n_pairs : num_sms());
+  const bool ext = tap_mode || save_hidden || mask_acts_f;
+  cudaError_t e = ext ? launch_fwd_t<false, true, true>(grid, packed, x_tiles, n_tiles, 1, n_tiles, nullptr, rgbs, acts_f,
+                                                        (float *)taps, (cudaStream_t)stream, tap_mode == 2, save_hidden,
+                                                        mask_acts_f, acts_u, mask_acts_u)
+                      : launch_fwd_t<false, false, true>(grid, packed, x_tiles, n_tiles, 1, n_tiles, nullptr, rgbs, acts_f,
+                                                         nullptr, (cudaStream_t)stream, 0, 0, nullptr, acts_u, nullptr);
+  if (e != cudaSuccess) {
+    set_error("cn_mlp_chain_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
+  return check_launch("cn_mlp_chain_fwd");
 }
