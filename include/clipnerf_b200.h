@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define CN_ABI_VERSION 10
+#define CN_ABI_VERSION 11
 #define CN_TILE_ROWS 128
 #define CN_HIDDEN 128
 #define CN_FEAT_C 256          /* combined_features channels (model_v0.py:60)            */
@@ -307,6 +307,22 @@ int cn_grasp_head_fwd(const void *tap_tiles, int64_t n_tiles, int32_t b, int32_t
 int cn_grasp_head_bwd(const float *gy, int64_t n_tiles, int32_t b, int32_t n_pad, int32_t np, const void *pack,
                       int32_t activation, const void *vslabs, const void *acat, const void *saved, void *dpc_ws,
                       void *dtap_tiles, void *stream);
+
+/* cn_grasp_head_bwd without the dpc_ws argument.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  The scratch is a file-scope `static __device__` array inside the library, sized
+ * for at most CN_HEAD_BWD_STATIC_MAX_POSES poses (b * np; 8 pose tiles x 42 x 16 KiB = 5.25 MiB, held by every GPU that
+ * loads the library until the process exits); more poses are rejected with an error (cn_last_error) and nothing is
+ * launched.  The call allocates nothing (no cudaMalloc / cudaFree); inputs and outputs are the caller's, as above, and
+ * the results are those of cn_grasp_head_bwd bit for bit (same kernels).  ALL calls on a device share the one array:
+ * calls that may overlap on the GPU (different streams without an ordering between them) race on it -- order them,
+ * or use cn_grasp_head_bwd with one dpc_ws per stream.  The array keeps the previous call's contents; nothing in it
+ * needs clearing (every row that is read is written first by the same call).  The first call on each device resolves
+ * the array's device address (cudaGetSymbolAddress, with that device current): make it at set-up, outside capture. */
+#define CN_HEAD_BWD_STATIC_MAX_POSES 1024
+int cn_grasp_head_bwd_static(const float *gy, int64_t n_tiles, int32_t b, int32_t n_pad, int32_t np, const void *pack,
+                             int32_t activation, const void *vslabs, const void *acat, const void *saved,
+                             void *dtap_tiles, void *stream);
 
 /* readout backward: d_y [rows,4] + relu(e) tiles -> g tiles (bf16), d(output_layer)
  * accumulated into grad (flat layout above).                                           */

@@ -11,7 +11,7 @@ from ctypes import c_char_p, c_double, c_float, c_int32, c_int64, c_size_t, c_vo
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), 'lib', 'libclipnerf_b200.so')
 
-ABI_VERSION = 10
+ABI_VERSION = 11
 TILE_ROWS = 128
 SLAB_BYTES = 16384
 ACT_TILE_BYTES = 32768
@@ -22,6 +22,7 @@ PACKED_BYTES = 2 * 491520 + 16384
 HEAD_PARAMS = 582337
 HEAD_PACK_BYTES = 2329600
 HEAD_OFFSETS = 42
+HEAD_BWD_STATIC_MAX_POSES = 1024   # CN_HEAD_BWD_STATIC_MAX_POSES: poses cn_grasp_head_bwd_static's built-in scratch holds
 
 
 class CnScene(ctypes.Structure):
@@ -69,6 +70,7 @@ PROTOTYPES = {
     'cn_grasp_head_pack': [_P, _P, _P],
     'cn_grasp_head_fwd': [_P, c_int64, c_int32, c_int32, c_int32, _P, c_int32, _P, _P, _P, _P, _P],
     'cn_grasp_head_bwd': [_P, c_int64, c_int32, c_int32, c_int32, _P, c_int32, _P, _P, _P, _P, _P, _P],
+    'cn_grasp_head_bwd_static': [_P, c_int64, c_int32, c_int32, c_int32, _P, c_int32, _P, _P, _P, _P, _P],
     'cn_mlp_readout_bwd': [_P, _P, _P, c_int32, c_int32, c_int64, _P, _P, _P],
     'cn_mlp_block_bwd': [_P, c_int32, _P, c_int32, c_int32, c_int64, _P, c_int32, c_int64, _P, c_float, _P, _P],
     'cn_mlp_stage_bwd_ws_bytes': [],
@@ -114,7 +116,7 @@ KERNELS_PER_CALL = {name: 1 for name in PROTOTYPES}
 KERNELS_PER_CALL.update({'cn_abi_version': 0, 'cn_last_error': 0, 'cn_gather_ws_bytes': 0, 'cn_mlp_stage_bwd_ws_bytes': 0,
                          'cn_project_bin': 4, 'cn_project_gather_fwd': 5, 'cn_feature_grad': 2,
                          'cn_project_gather_bwd_rays': 2, 'cn_quantize_render': 2, 'cn_adam_step': 2,
-                         'cn_grasp_head_fwd': 2, 'cn_grasp_head_bwd': 2})
+                         'cn_grasp_head_fwd': 2, 'cn_grasp_head_bwd': 2, 'cn_grasp_head_bwd_static': 2})
 
 LAUNCHES = 0          # running count of kernel launches issued through the ABI
 TIMER = None          # optional callable(name) -> context manager, set by bench.py to time stages

@@ -21,6 +21,7 @@
 // operand tiles.  Weights: bf16 K-major images of every matrix in both orientations + one fp32 bias table, built once
 // per weight version by cn_grasp_head_pack from the Keras-order flat parameter vector.
 #include "common.cuh"
+#include <mutex>
 
 namespace cn {
 
@@ -907,6 +908,57 @@ extern "C" int cn_grasp_head_bwd(const float *gy, int64_t n_tiles, int32_t b, in
       (const uint8_t *)dpc_ws, (const uint8_t *)acat, (const uint8_t *)pack, g, (uint8_t *)dtap_tiles,
       n_tiles * (int64_t)CN_ACT_TILE_BYTES);
   return check_launch("cn_grasp_head_bwd (points)");
+}
+
+// ---- cn_grasp_head_bwd without a caller-provided scratch buffer (no counterpart in the reference; added
+// for callers that cannot allocate: code under CUDA-graph capture, serving loops).
+// The d(pre-activation of c) slabs live in a file-scope device array instead: CN_HEAD_BWD_STATIC_MAX_POSES poses =
+// 8 pose tiles x 42 x 16 KiB = 5.25 MiB, held by every GPU that loads the library until the process exits.
+namespace cn {
+constexpr int64_t kStaticDpcBytes = (int64_t)(CN_HEAD_BWD_STATIC_MAX_POSES / 128) * kN5 * CN_SLAB_BYTES;
+static __device__ __align__(256) uint8_t g_head_bwd_dpc[kStaticDpcBytes];
+
+// In host code `g_head_bwd_dpc` is only a stand-in for the symbol, NOT a device address: the address is asked for
+// once per device, with that device current, and cached.
+constexpr int kMaxDevices = 64;
+static std::mutex g_dpc_mutex;
+static void *g_dpc_ptr[kMaxDevices] = {};
+
+static int static_dpc_address(void **out, const char *who) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    set_error("%s: cudaGetDevice: %s (device %d)", who, cudaGetErrorString(e), dev);
+    return e != cudaSuccess ? (int)e : -1;
+  }
+  std::lock_guard<std::mutex> lock(g_dpc_mutex);
+  if (!g_dpc_ptr[dev]) {
+    void *ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_head_bwd_dpc);
+    if (e != cudaSuccess || !ptr) {
+      set_error("%s: cudaGetSymbolAddress(g_head_bwd_dpc) on device %d: %s", who, dev, cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : -1;
+    }
+    g_dpc_ptr[dev] = ptr;
+  }
+  *out = g_dpc_ptr[dev];
+  return 0;
+}
+}  // namespace cn
+
+extern "C" int cn_grasp_head_bwd_static(const float *gy, int64_t n_tiles, int32_t b, int32_t n_pad, int32_t np,
+                                        const void *pack, int32_t activation, const void *vslabs, const void *acat,
+                                        const void *saved, void *dtap_tiles, void *stream) {
+  using namespace cn;
+  CN_REQUIRE(b > 0 && np > 0, "cn_grasp_head_bwd_static: b=%d np=%d", b, np);
+  CN_REQUIRE((int64_t)b * np <= CN_HEAD_BWD_STATIC_MAX_POSES,
+             "cn_grasp_head_bwd_static: %lld poses exceed the static scratch (CN_HEAD_BWD_STATIC_MAX_POSES = %d); "
+             "use cn_grasp_head_bwd with a caller-provided dpc_ws", (long long)b * np, CN_HEAD_BWD_STATIC_MAX_POSES);
+  void *dpc = nullptr;
+  if (int rc = static_dpc_address(&dpc, "cn_grasp_head_bwd_static")) return rc;
+  // every slab row the point kernel reads is written by the pose kernel of the SAME call (rows of valid poses only):
+  // nothing in the array has to start at zero, the previous call's contents are simply overwritten
+  return cn_grasp_head_bwd(gy, n_tiles, b, n_pad, np, pack, activation, vslabs, acat, saved, dpc, dtap_tiles, stream);
 }
 
 extern "C" int cn_tile_add_tiles(void *g_tiles, const void *src_tiles, int64_t n_tiles, void *stream) {
