@@ -56,12 +56,19 @@ static __device__ long long cn_trace_buf[32 * 32];
   do {                                                                                  \
     if (blockIdx.x == 0 && (it) < 32) cn_trace_buf[(it) * 32 + (k)] = clock64();        \
   } while (0)
+#define CN_TRACE_VAL(it, k, v)                                                          \
+  do {                                                                                  \
+    if (blockIdx.x == 0 && (it) < 32) cn_trace_buf[(it) * 32 + (k)] = (long long)(v);   \
+  } while (0)
+#define CN_TRACE_CLOCK() clock64()
 #define CN_TRACE_READER(name)                                                           \
   extern "C" int name(long long *dst, int n) {                                          \
     return (int)cudaMemcpyFromSymbol(dst, cn_trace_buf, sizeof(long long) * n);         \
   }
 #else
 #define CN_TRACE_AT(it, k) do { } while (0)
+#define CN_TRACE_VAL(it, k, v) do { } while (0)
+#define CN_TRACE_CLOCK() 0ll
 #define CN_TRACE_READER(name)
 #endif
 

@@ -491,8 +491,10 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
 
       // one ResNet block of a stage: tb = the stage's cumulative-bias tables, sacts = its saved-activation tiles of this
       // tile (n_acts regular ones, the hidden activations behind them), smask = the tangent pass's mask tiles
+      long long tr_epi = 0, tr_wait_tmp = 0, tr_wait_h = 0;   // CN_TRACE: cycles of thread `tr` in epilogues / waiting for the MMAs
       auto run_block = [&](int blk, bool skip_ea, const float *tb, uint8_t *sacts, int n_acts, const uint8_t *smask,
                            bool with_taps) {
+        long long c0 = CN_TRACE_CLOCK();
         if (!skip_ea) {
           // E_a: relu(h + cumulative bias) -> operand of the block's first Dense
           acquire();
@@ -504,19 +506,26 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
           if (tr && blk == 0) CN_TRACE_AT(pi, 9);
         }
         // E_b: relu(t + ba) -> operand of the block's second Dense
+        long long c1 = CN_TRACE_CLOCK();
         mbar_wait(smem_u32(&bars.tmp_ready[t]), n_tmp & 1u);
         ++n_tmp;
         tc_fence_after();
+        long long c2 = CN_TRACE_CLOCK();
         if (tr && blk == 0) CN_TRACE_AT(pi, 10);
         acquire();
         epi_tmem_to_act<true>(t_tmp, tb + (2 * blk + 1) * 128, act, row, half, nullptr, nullptr,
                               smask ? smask + (n_acts + blk) * CN_ACT_TILE_BYTES : nullptr);
         publish((save_hidden && sacts) ? sacts + (n_acts + blk) * CN_ACT_TILE_BYTES : nullptr, true);
         if (tr && blk == 0) CN_TRACE_AT(pi, 11);
+        long long c3 = CN_TRACE_CLOCK();
         mbar_wait(smem_u32(&bars.h_ready[t]), n_h & 1u);
         ++n_h;
         tc_fence_after();
         if (tr && blk == 0) CN_TRACE_AT(pi, 12);
+        long long c4 = CN_TRACE_CLOCK();
+        tr_epi += (c1 - c0) + (c3 - c2);
+        tr_wait_tmp += c2 - c1;
+        tr_wait_h += c4 - c3;
       };
       auto readout = [&](const float *tb, uint8_t *sacts, bool release_h) {
         // ---- readout: relu(e) . Wr + br, sigmoid / softplus (layers.py:392-397).  The two column-half
@@ -645,6 +654,11 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         readout(tabu, my_acts_u, true);
       }
       if (tr) CN_TRACE_AT(pi, 14);
+      if (tr) {
+        CN_TRACE_VAL(pi, 24, tr_epi);
+        CN_TRACE_VAL(pi, 25, tr_wait_tmp);
+        CN_TRACE_VAL(pi, 26, tr_wait_h);
+      }
       ring_base += 12u + view_slots * ((2 * p + 1 < n_tiles) ? 2u : 1u);
     }
     if (wg_leader) bulk_wait0();
