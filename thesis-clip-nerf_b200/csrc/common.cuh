@@ -60,7 +60,11 @@ static __device__ long long cn_trace_buf[32 * 32];
   do {                                                                                  \
     if (blockIdx.x == 0 && (it) < 32) cn_trace_buf[(it) * 32 + (k)] = (long long)(v);   \
   } while (0)
-#define CN_TRACE_CLOCK() clock64()
+#ifdef CN_TRACE_FINE   // per-epilogue accumulators: many clock reads in one warp, the traced tile runs ~30 % slower
+#define CN_TRACE_CLOCK_IF(cond) ((cond) ? clock64() : 0ll)
+#else
+#define CN_TRACE_CLOCK_IF(cond) 0ll
+#endif
 #define CN_TRACE_READER(name)                                                           \
   extern "C" int name(long long *dst, int n) {                                          \
     return (int)cudaMemcpyFromSymbol(dst, cn_trace_buf, sizeof(long long) * n);         \
@@ -68,7 +72,7 @@ static __device__ long long cn_trace_buf[32 * 32];
 #else
 #define CN_TRACE_AT(it, k) do { } while (0)
 #define CN_TRACE_VAL(it, k, v) do { } while (0)
-#define CN_TRACE_CLOCK() 0ll
+#define CN_TRACE_CLOCK_IF(cond) 0ll
 #define CN_TRACE_READER(name)
 #endif
 
@@ -239,6 +243,7 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
 constexpr uint32_t kSboBytes = 1024;
 constexpr uint32_t kKmajLbo = 16;
 constexpr uint32_t kKmajKstep = 32;
+constexpr uint64_t kKmajKstepEnc = kKmajKstep >> 4;   // the same step on an encoded descriptor (start address field, no carry: smem < 256 KiB)
 constexpr uint32_t kMNmajLbo = CN_SLAB_BYTES;
 constexpr uint32_t kMNmajKstep = 2048;
 

@@ -314,28 +314,33 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
       constexpr uint32_t idesc_kk = umma_idesc(128, 128, 0, 0);  // dgrad: both operands K-major
       constexpr uint32_t idesc_kn = umma_idesc(128, 128, 0, 1);  // recompute: A K-major, B MN-major
       constexpr uint32_t idesc_mn = umma_idesc(128, 128, 1, 1);  // wgrad: both operands MN-major
+      // descriptors: one base per operand layout, built once; an operand at byte offset `off` of the CTA's shared memory
+      // is base + (off >> 4) on the encoded start address (no carry: shared memory < 256 KiB).  Rebuilding the
+      // descriptor from the address for every MMA costs the issuing thread ~20 % of the tensor rate when the
+      // epilogue warps share its scheduler (tools/ubench_mma_issue.cu).
+      const uint64_t d_k = umma_desc(s_base, kKmajLbo, kSboBytes), d_mn = umma_desc(s_base, kMNmajLbo, kSboBytes);
       auto gemm_kk = [&](uint32_t d_tmem, uint32_t a_off, uint32_t b_off) {
+        const uint64_t da = d_k + (a_off >> 4), db = d_k + (b_off >> 4);
 #pragma unroll
         for (int s = 0; s < 2; ++s)
 #pragma unroll
           for (int j = 0; j < 4; ++j)
-            umma_f16(d_tmem, umma_desc(s_base + a_off + s * CN_SLAB_BYTES + j * kKmajKstep, kKmajLbo, kSboBytes),
-                     umma_desc(s_base + b_off + s * CN_SLAB_BYTES + j * kKmajKstep, kKmajLbo, kSboBytes), idesc_kk,
-                     (s | j) ? 1u : 0u);
+            umma_f16(d_tmem, da + ((s * CN_SLAB_BYTES + j * kKmajKstep) >> 4), db + ((s * CN_SLAB_BYTES + j * kKmajKstep) >> 4),
+                     idesc_kk, (s | j) ? 1u : 0u);
       };
       // t = A1 Wa with Wa stored [in][out] (K rows, N contiguous): K step 16 = 16 rows of the weight image
       auto gemm_t = [&](uint32_t a_off) {
+        const uint64_t da = d_k + (a_off >> 4), db = d_mn + (kBwSmemWa >> 4);
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-          umma_f16(t_acc0, umma_desc(s_base + a_off + (j >> 2) * CN_SLAB_BYTES + (j & 3) * kKmajKstep, kKmajLbo, kSboBytes),
-                   umma_desc(s_base + kBwSmemWa + j * kMNmajKstep, kMNmajLbo, kSboBytes), idesc_kn, j ? 1u : 0u);
+          umma_f16(t_acc0, da + (((j >> 2) * CN_SLAB_BYTES + (j & 3) * kKmajKstep) >> 4), db + ((j * kMNmajKstep) >> 4), idesc_kn,
+                   j ? 1u : 0u);
       };
       auto wgrad = [&](uint32_t d_tmem, uint32_t a_off, uint32_t b_off, bool first) {
+        const uint64_t da = d_mn + (a_off >> 4), db = d_mn + (b_off >> 4);
 #pragma unroll
         for (int j = 0; j < 8; ++j)  // 8 steps of 16 rows
-          umma_f16(d_tmem, umma_desc(s_base + a_off + j * kMNmajKstep, kMNmajLbo, kSboBytes),
-                   umma_desc(s_base + b_off + j * kMNmajKstep, kMNmajLbo, kSboBytes), idesc_mn,
-                   (!first || j) ? 1u : 0u);
+          umma_f16(d_tmem, da + ((j * kMNmajKstep) >> 4), db + ((j * kMNmajKstep) >> 4), idesc_mn, (!first || j) ? 1u : 0u);
       };
       mbar_wait(smem_u32(&bars.w_full), 0);
       if (n_mine > 0) {

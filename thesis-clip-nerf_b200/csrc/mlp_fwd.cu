@@ -25,6 +25,7 @@ namespace cn {
 
 constexpr int kFwdThreads = 608;                                   // 2 + 16 warps + the X producer warp
 constexpr int kEpiThreads = 256;                                   // epilogue threads per tile
+constexpr int kEpiWarps = kEpiThreads / 32;
 constexpr int kMaxStageViews = 3;                                  // views staged in smem by the fusion prologue
 constexpr uint32_t kSmemAct = 0;                                   // 2 x 32 KiB
 constexpr uint32_t kSmemRing = 2 * CN_ACT_TILE_BYTES;
@@ -51,7 +52,6 @@ struct FwdBars {
   uint64_t h_ready[2];
   uint64_t tmp_ready[2];
   uint64_t act_ready[2];
-  uint64_t h_free[2];
   uint64_t views_ready[2];  // fusion stage: the ring slots holding tile t's per-view slabs have landed
 };
 
@@ -66,14 +66,29 @@ __device__ __forceinline__ void epi_tmem_to_act(uint32_t taddr, const float *__r
                                                 uint32_t row, uint32_t half, float *__restrict__ tap = nullptr,
                                                 uint8_t *__restrict__ tap16 = nullptr,
                                                 const uint8_t *__restrict__ mask = nullptr) {
+#ifndef CN_EXP
+#define CN_EXP 0
+#endif
   uint32_t r[64];
   tmem_ld32(taddr + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
-  tmem_ld32(taddr + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+#if CN_EXP & 2
   tmem_wait_ld();
+#endif
+  tmem_ld32(taddr + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+#if !(CN_EXP & 2)
+  tmem_wait_ld();
+#endif
 #pragma unroll
   for (int q = 0; q < 8; ++q) {
+#if CN_EXP & 2
+    if (q == 4) tmem_wait_ld();
+#endif
+#if CN_EXP & 1
+    const float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
+#else
     const float4 b0 = *reinterpret_cast<const float4 *>(bias + half * 64 + q * 8);
     const float4 b1 = *reinterpret_cast<const float4 *>(bias + half * 64 + q * 8 + 4);
+#endif
     float v[8];
     v[0] = __uint_as_float(r[q * 8 + 0]) + b0.x; v[1] = __uint_as_float(r[q * 8 + 1]) + b0.y;
     v[2] = __uint_as_float(r[q * 8 + 2]) + b0.z; v[3] = __uint_as_float(r[q * 8 + 3]) + b0.w;
@@ -163,8 +178,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
     for (int t = 0; t < 2; ++t) {
       mbar_init(smem_u32(&bars.h_ready[t]), 1);
       mbar_init(smem_u32(&bars.tmp_ready[t]), 1);
-      mbar_init(smem_u32(&bars.act_ready[t]), kEpiThreads);
-      mbar_init(smem_u32(&bars.h_free[t]), kEpiThreads);
+      mbar_init(smem_u32(&bars.act_ready[t]), kEpiWarps);   // one arrival per epilogue warp (behind a __syncwarp)
       mbar_init(smem_u32(&bars.views_ready[t]), 1);
     }
     fence_barrier_init();
@@ -246,7 +260,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc(128, 128, 0, 0);
       uint32_t cc = 0;
-      uint32_t n_act[2] = {0, 0}, n_free[2] = {0, 0};
+      uint32_t n_act[2] = {0, 0};
       auto next_slot = [&]() -> uint32_t {
         const uint32_t slot = cc % kRingSlots;
         mbar_wait(smem_u32(&bars.full[slot]), (cc / kRingSlots) & 1u);
@@ -267,41 +281,51 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         const uint32_t a_base = s_base + kSmemAct + t * CN_ACT_TILE_BYTES;
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
-          const uint32_t b_base = slot_addr(s ? s1 : s0);
+          const uint64_t da = umma_desc(a_base + s * CN_SLAB_BYTES, kKmajLbo, kSboBytes);
+          const uint64_t db = umma_desc(slot_addr(s ? s1 : s0), kKmajLbo, kSboBytes);
 #pragma unroll
           for (int j = 0; j < 4; ++j)
-            umma_f16(d_tmem, umma_desc(a_base + s * CN_SLAB_BYTES + j * kKmajKstep, kKmajLbo, kSboBytes),
-                     umma_desc(b_base + j * kKmajKstep, kKmajLbo, kSboBytes), idesc,
-                     (accumulate || s || j) ? 1u : 0u);
+            umma_f16(d_tmem, da + j * kKmajKstepEnc, db + j * kKmajKstepEnc, idesc, (accumulate || s || j) ? 1u : 0u);
         }
       };
       int64_t pi = 0;
       for (int64_t p = blockIdx.x; p < n_pairs; p += gridDim.x, ++pi) {
         const int nt = (2 * p + 1 < n_tiles) ? 2 : 1;
         CN_TRACE_AT(pi, 0);
+        // per-view / chained kernel: the two 128-column accumulators of a tile SWAP roles every pair.  The first Dense
+        // of pair p+1 accumulates into the columns pair p used as `tmp` (idle since the last E_b, which the act_ready
+        // wait of the last GEMM already covers) while the final epilogue of pair p is still reading the old `h`: the
+        // X-bound first Dense overlaps the readout instead of waiting for it.  The old `h` columns become `tmp`, first
+        // written by the block GEMM behind act_ready of E_a -- which the same epilogue warps signal after their readout.
+        const uint32_t col_h = (!kFusion && (pi & 1)) ? 128u : 0u, col_tmp = 128u - col_h;
         if (!kFusion) {
-          // the previous pair's final epilogue must have drained h before it is overwritten
-          for (int t = 0; t < nt; ++t) {
-            mbar_wait(smem_u32(&bars.h_free[t]), (n_free[t] & 1u) ^ 1u);
-            ++n_free[t];
-          }
-          tc_fence_after();
+          long long tw_w = 0, tw_x = 0;   // CN_TRACE_FINE: cycles this thread waits for weight slabs / X slabs in the first Dense
           for (int kb = 0; kb < 6; ++kb) {
+            const long long w0 = CN_TRACE_CLOCK_IF(true);
             const uint32_t sw = next_slot();
+            tw_w += CN_TRACE_CLOCK_IF(true) - w0;
+            // descriptors are built once per slab; a K step of 16 (32 bytes) is +2 on the encoded start address --
+            // rebuilding them per MMA costs the issuing thread ~20 % of the tensor rate (tools/ubench_mma_issue.cu)
+            const uint64_t dw = umma_desc(slot_addr(sw), kKmajLbo, kSboBytes);
             for (int t = 0; t < nt; ++t) {
+              const long long x0 = CN_TRACE_CLOCK_IF(true);
               const uint32_t sx = next_x_slot();
-              const uint32_t x_addr = s_base + L::kXRing + sx * CN_SLAB_BYTES;
+              const uint64_t dx = umma_desc(s_base + L::kXRing + sx * CN_SLAB_BYTES, kKmajLbo, kSboBytes);
+              tw_x += CN_TRACE_CLOCK_IF(true) - x0;
+              if (t == 0 && kb < 4) CN_TRACE_AT(pi, 4 + kb);
+              if (t == 0 && kb >= 4) CN_TRACE_AT(pi, 24 + kb);
               tc_fence_after();
 #pragma unroll
               for (int j = 0; j < 4; ++j)
-                umma_f16(tmem + t * 256, umma_desc(x_addr + j * kKmajKstep, kKmajLbo, kSboBytes),
-                         umma_desc(slot_addr(sw) + j * kKmajKstep, kKmajLbo, kSboBytes), idesc, (kb | j) ? 1u : 0u);
+                umma_f16(tmem + t * 256 + col_h, dx + j * kKmajKstepEnc, dw + j * kKmajKstepEnc, idesc, (kb | j) ? 1u : 0u);
               umma_commit(smem_u32(&bars.xempty[sx]));
               if (kb == 5) umma_commit(smem_u32(&bars.h_ready[t]));
             }
             umma_commit(smem_u32(&bars.empty[sw]));
           }
           CN_TRACE_AT(pi, 1);
+          CN_TRACE_VAL(pi, 30, tw_w);
+          CN_TRACE_VAL(pi, 31, tw_x);
         }
         for (int blk = 0; blk < kNumBlk; ++blk) {
           for (int j = 0; j < 2; ++j) {
@@ -325,10 +349,10 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
               if (blk == 0 && j == 0 && t == 0) CN_TRACE_AT(pi, 2);
               if (blk == kNumBlk - 1 && j == 1 && t == 1) CN_TRACE_AT(pi, 3);
               if (j == 0) {
-                gemm_act(t, tmem + t * 256 + 128, s0, s1, false);
+                gemm_act(t, tmem + t * 256 + col_tmp, s0, s1, false);
                 umma_commit(smem_u32(&bars.tmp_ready[t]));
               } else {
-                gemm_act(t, tmem + t * 256, s0, s1, true);
+                gemm_act(t, tmem + t * 256 + col_h, s0, s1, true);
                 umma_commit(smem_u32(&bars.h_ready[t]));
               }
             }
@@ -349,8 +373,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
     const uint32_t bar_id = 1 + t;
     uint8_t *act = smem + kSmemAct + t * CN_ACT_TILE_BYTES;
     const uint32_t act_u32 = s_base + kSmemAct + t * CN_ACT_TILE_BYTES;
-    const uint32_t t_h = tmem + ((quad * 32u) << 16) + t * 256;
-    const uint32_t t_tmp = t_h + 128;
+    const uint32_t t_base = tmem + ((quad * 32u) << 16) + t * 256;
     uint32_t n_h = 0, n_tmp = 0, n_views = 0;
     uint32_t ring_base = 0;                         // ring position at the start of the current pair
     bool store_pending = false;
@@ -368,8 +391,10 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         store_pending = true;
       }
       if (signal_mma) {
+        // 256 arrivals on one mbarrier serialise in shared memory: every lane fences, lane 0 arrives for the warp
         tc_fence_before();
-        mbar_arrive(smem_u32(&bars.act_ready[t]));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bars.act_ready[t]));
       }
     };
     // ACT may only be overwritten once a pending bulk store has finished reading it
@@ -386,6 +411,8 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
     for (int64_t p = blockIdx.x; p < n_pairs; p += gridDim.x, ++pi) {
       const int64_t tile = 2 * p + t;
       if (tile >= n_tiles) break;
+      const uint32_t t_h = t_base + ((!kFusion && (pi & 1)) ? 128u : 0u);   // column roles alternate per pair (MMA issuer)
+      const uint32_t t_tmp = t_base + ((!kFusion && (pi & 1)) ? 0u : 128u);
       uint8_t *my_acts = acts ? acts + tile * (int64_t)acts_stride * CN_ACT_TILE_BYTES : nullptr;
       const uint8_t *my_mask = mask_acts ? mask_acts + tile * (int64_t)acts_stride * CN_ACT_TILE_BYTES : nullptr;
       // fusion stage, pose-query models: taps[s][row][128] fp32, s = (mean, block 4, block 5, block 6 output)
@@ -491,10 +518,10 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
 
       // one ResNet block of a stage: tb = the stage's cumulative-bias tables, sacts = its saved-activation tiles of this
       // tile (n_acts regular ones, the hidden activations behind them), smask = the tangent pass's mask tiles
-      long long tr_epi = 0, tr_wait_tmp = 0, tr_wait_h = 0;   // CN_TRACE: cycles of thread `tr` in epilogues / waiting for the MMAs
+      long long tr_epi = 0, tr_wait_tmp = 0, tr_wait_h = 0, tr_pub = 0;   // CN_TRACE: cycles of thread `tr` in epilogues / waiting for the MMAs
       auto run_block = [&](int blk, bool skip_ea, const float *tb, uint8_t *sacts, int n_acts, const uint8_t *smask,
                            bool with_taps) {
-        long long c0 = CN_TRACE_CLOCK();
+        long long c0 = CN_TRACE_CLOCK_IF(tr);
         if (!skip_ea) {
           // E_a: relu(h + cumulative bias) -> operand of the block's first Dense
           acquire();
@@ -502,32 +529,36 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
                                 (with_taps && my_tap) ? my_tap + blk * tap_stride : nullptr,
                                 (with_taps && my_tap16) ? my_tap16 + blk * tap16_stride : nullptr,
                                 smask ? smask + blk * CN_ACT_TILE_BYTES : nullptr);
+          const long long p0 = CN_TRACE_CLOCK_IF(tr);
           publish(sacts ? sacts + blk * CN_ACT_TILE_BYTES : nullptr, true);
+          tr_pub += CN_TRACE_CLOCK_IF(tr) - p0;
           if (tr && blk == 0) CN_TRACE_AT(pi, 9);
         }
         // E_b: relu(t + ba) -> operand of the block's second Dense
-        long long c1 = CN_TRACE_CLOCK();
+        long long c1 = CN_TRACE_CLOCK_IF(tr);
         mbar_wait(smem_u32(&bars.tmp_ready[t]), n_tmp & 1u);
         ++n_tmp;
         tc_fence_after();
-        long long c2 = CN_TRACE_CLOCK();
+        long long c2 = CN_TRACE_CLOCK_IF(tr);
         if (tr && blk == 0) CN_TRACE_AT(pi, 10);
         acquire();
         epi_tmem_to_act<true>(t_tmp, tb + (2 * blk + 1) * 128, act, row, half, nullptr, nullptr,
                               smask ? smask + (n_acts + blk) * CN_ACT_TILE_BYTES : nullptr);
+        const long long p1 = CN_TRACE_CLOCK_IF(tr);
         publish((save_hidden && sacts) ? sacts + (n_acts + blk) * CN_ACT_TILE_BYTES : nullptr, true);
+        tr_pub += CN_TRACE_CLOCK_IF(tr) - p1;
         if (tr && blk == 0) CN_TRACE_AT(pi, 11);
-        long long c3 = CN_TRACE_CLOCK();
+        long long c3 = CN_TRACE_CLOCK_IF(tr);
         mbar_wait(smem_u32(&bars.h_ready[t]), n_h & 1u);
         ++n_h;
         tc_fence_after();
         if (tr && blk == 0) CN_TRACE_AT(pi, 12);
-        long long c4 = CN_TRACE_CLOCK();
+        long long c4 = CN_TRACE_CLOCK_IF(tr);
         tr_epi += (c1 - c0) + (c3 - c2);
         tr_wait_tmp += c2 - c1;
         tr_wait_h += c4 - c3;
       };
-      auto readout = [&](const float *tb, uint8_t *sacts, bool release_h) {
+      auto readout = [&](const float *tb, uint8_t *sacts) {
         // ---- readout: relu(e) . Wr + br, sigmoid / softplus (layers.py:392-397).  The two column-half
         // warps of a row split the OUTPUTS (half 0: r,g; half 1: b,sigma), each over all 128 inputs; the
         // relu(e) tile saved for the backward is still written half by half.
@@ -583,10 +614,6 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         o.x = 1.f / (1.f + expf(-ya));
         o.y = half ? (yb > 20.f ? yb : log1pf(expf(yb))) : 1.f / (1.f + expf(-yb));
         reinterpret_cast<float2 *>(rgbs)[(tile * 128 + row) * 2 + half] = o;
-        if (release_h) {                                   // chained kernel: the next pair's first Dense overwrites h
-          tc_fence_before();
-          mbar_arrive(smem_u32(&bars.h_free[t]));
-        }
         publish(sacts ? sacts + 3 * CN_ACT_TILE_BYTES : nullptr, false);
       };
 
@@ -595,12 +622,10 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
 
       acquire();
       if (kFusion) {
-        readout(tab, my_acts, false);
+        readout(tab, my_acts);
       } else if (!kChain) {
         // ---- h3 = h + cumulative bias -> bf16 tile for the fusion stage
         epi_tmem_to_act<false>(t_h, tab + 6 * 128, act, row, half);
-        tc_fence_before();
-        mbar_arrive(smem_u32(&bars.h_free[t]));
         publish(out_tiles + tile * (int64_t)CN_ACT_TILE_BYTES, false);
       } else {
         // ---- chained fusion stage (nv = 1).  m = bf16(h + cumulative bias) is what the two-kernel path stores as the
@@ -651,13 +676,14 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         publish(my_acts_u, true);
         for (int blk = 0; blk < 3; ++blk) run_block(blk, blk == 0, tabu, my_acts_u, 4, my_mask_u, true);
         acquire();
-        readout(tabu, my_acts_u, true);
+        readout(tabu, my_acts_u);
       }
       if (tr) CN_TRACE_AT(pi, 14);
       if (tr) {
         CN_TRACE_VAL(pi, 24, tr_epi);
         CN_TRACE_VAL(pi, 25, tr_wait_tmp);
         CN_TRACE_VAL(pi, 26, tr_wait_h);
+        CN_TRACE_VAL(pi, 27, tr_pub);
       }
       ring_base += 12u + view_slots * ((2 * p + 1 < n_tiles) ? 2u : 1u);
     }

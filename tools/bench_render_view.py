@@ -12,6 +12,8 @@ import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
 from clipnerf_b200 import _abi, synthetic  # noqa: E402
+if os.environ.get('CN_LIB'):            # another build of the library (before / after comparisons)
+    _abi.LIB_PATH = os.path.abspath(os.environ['CN_LIB'])
 from src.lib.mvnerf.model_v0 import MVVNeRFRenderer, render_view  # noqa: E402
 
 ap = argparse.ArgumentParser()

@@ -4,6 +4,8 @@ import ctypes, sys, os
 import numpy as np, torch
 sys.path.insert(0, os.path.join(os.path.dirname(__file__), '..', 'thesis-clip-nerf_b200'))
 from clipnerf_b200 import _abi, ops
+if os.environ.get('CN_LIB'):
+    _abi.LIB_PATH = os.path.abspath(os.environ['CN_LIB'])
 lib = _abi.load()
 dev = torch.device('cuda:0')
 nt = 148 * 48
@@ -13,7 +15,8 @@ packed = ops.pack_weights(params)
 x = (torch.randn(nt * 128 * 384, generator=g)).to(torch.bfloat16).to(dev).view(torch.uint8)
 names = {0: 'MMA pair start', 1: 'MMA L0 issued', 2: 'MMA blk0 Wa t0 issue', 3: 'MMA last blk Wb t1 issue', 8: 'EPI h0 ready',
          9: 'EPI Ea(blk0) published', 10: 'EPI tmp ready (blk0)', 11: 'EPI Eb(blk0) published', 12: 'EPI h ready (blk0)',
-         13: 'EPI per-view blocks done', 14: 'EPI readout done', 20: 'XPROD first X load', 21: 'PROD last L0 weight load',
+         4: 'MMA L0 kb0 t0 issue', 5: 'MMA L0 kb1 t0 issue', 6: 'MMA L0 kb2 t0 issue', 7: 'MMA L0 kb3 t0 issue',
+         28: 'MMA L0 kb4 t0 issue', 29: 'MMA L0 kb5 t0 issue', 13: 'EPI per-view blocks done', 14: 'EPI readout done', 20: 'XPROD first X load', 21: 'PROD last L0 weight load',
          22: 'PROD last weight load'}
 for save in (False, True):
     for _ in range(3):
@@ -34,5 +37,6 @@ for save in (False, True):
         print(f'--- pair {it} (cycles relative to MMA pair start; pair period {int(t[it + 1, 0] - t[it, 0])})')
         for c, n in ev:
             print(f'{c:8d}  {n}')
-        print(f'          traced epilogue thread (tile 0): {int(t[it, 24])} cycles in 12 block epilogues, '
+        print(f'          MMA thread in the first Dense (CN_TRACE_FINE): {int(t[it, 30])} cycles waiting for weight slabs, {int(t[it, 31])} for X slabs')
+        print(f'          traced epilogue thread (tile 0): {int(t[it, 24])} cycles in the block epilogues (of which {int(t[it, 27])} in publish = fence + arrive), '
               f'{int(t[it, 25])} waiting for tmp (6 first Denses), {int(t[it, 26])} waiting for h (6 second Denses)')
