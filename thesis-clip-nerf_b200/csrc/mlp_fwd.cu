@@ -26,7 +26,14 @@ namespace cn {
 constexpr int kFwdThreads = 608;                                   // 2 + 16 warps + the X producer warp
 constexpr int kEpiThreads = 256;                                   // epilogue threads per tile
 constexpr int kEpiWarps = kEpiThreads / 32;
-constexpr int kMaxStageViews = 3;                                  // views staged in smem by the fusion prologue
+constexpr int kMaxStageViews = 3;
+// First Dense of a pair: order of its 12 (K block, tile) steps.  Tile 0 runs two K blocks ahead of tile 1, so tile 1
+// enters the blocks ~half a layer period after tile 0: the two tiles' epilogues then ALTERNATE (each overlaps the other
+// tile's GEMM) instead of running at the same time on the same schedulers.  An offset between the tiles of more than one
+// GEMM is self-sustaining under in-order issue (the issuer waits for the later tile), so it only has to be created here.
+// The X producer loads in the same order; a weight slab is released after tile 1 has used it (3 of 4 ring slots live).
+__device__ constexpr int8_t kL0StepKb[12] = {0, 1, 2, 0, 3, 1, 4, 2, 5, 3, 4, 5};
+__device__ constexpr int8_t kL0StepT[12] = {0, 0, 0, 1, 0, 1, 0, 1, 0, 1, 1, 1};                                  // views staged in smem by the fusion prologue
 constexpr uint32_t kSmemAct = 0;                                   // 2 x 32 KiB
 constexpr uint32_t kSmemRing = 2 * CN_ACT_TILE_BYTES;
 constexpr uint32_t kSmemTabBytes = 7 * 128 * 4 + 512 * 4 + 16;
@@ -242,8 +249,10 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
       int64_t pi = 0;
       for (int64_t p = blockIdx.x; p < n_pairs; p += gridDim.x, ++pi) {
         const int nt = (2 * p + 1 < n_tiles) ? 2 : 1;
-        for (int kb = 0; kb < 6; ++kb)
-          for (int t = 0; t < nt; ++t) {
+#pragma unroll
+        for (int st = 0; st < 12; ++st) {
+            const int kb = kL0StepKb[st], t = kL0StepT[st];
+            if (t >= nt) continue;
             const uint32_t slot = xc % kXS;
             mbar_wait(smem_u32(&bars.xempty[slot]), ((xc / kXS) & 1u) ^ 1u);
             mbar_expect_tx(smem_u32(&bars.xfull[slot]), CN_SLAB_BYTES);
@@ -300,32 +309,36 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         const uint32_t col_h = (!kFusion && (pi & 1)) ? 128u : 0u, col_tmp = 128u - col_h;
         if (!kFusion) {
           long long tw_w = 0, tw_x = 0;   // CN_TRACE_FINE: cycles this thread waits for weight slabs / X slabs in the first Dense
-          for (int kb = 0; kb < 6; ++kb) {
-            const long long w0 = CN_TRACE_CLOCK_IF(true);
-            const uint32_t sw = next_slot();
-            tw_w += CN_TRACE_CLOCK_IF(true) - w0;
-            // descriptors are built once per slab; a K step of 16 (32 bytes) is +2 on the encoded start address --
-            // rebuilding them per MMA costs the issuing thread ~20 % of the tensor rate (tools/ubench_mma_issue.cu)
-            const uint64_t dw = umma_desc(slot_addr(sw), kKmajLbo, kSboBytes);
-            for (int t = 0; t < nt; ++t) {
-              const long long x0 = CN_TRACE_CLOCK_IF(true);
-              const uint32_t sx = next_x_slot();
-              const uint64_t dx = umma_desc(s_base + L::kXRing + sx * CN_SLAB_BYTES, kKmajLbo, kSboBytes);
-              tw_x += CN_TRACE_CLOCK_IF(true) - x0;
-              if (t == 0 && kb < 4) CN_TRACE_AT(pi, 4 + kb);
-              if (t == 0 && kb >= 4) CN_TRACE_AT(pi, 24 + kb);
-              tc_fence_after();
+          // descriptors are built once per slab; a K step of 16 (32 bytes) is +2 on the encoded start address --
+          // rebuilding them per MMA costs the issuing thread ~20 % of the tensor rate (tools/ubench_mma_issue.cu)
+          uint32_t sw[6];
 #pragma unroll
-              for (int j = 0; j < 4; ++j)
-                umma_f16(tmem + t * 256 + col_h, dx + j * kKmajKstepEnc, dw + j * kKmajKstepEnc, idesc, (kb | j) ? 1u : 0u);
-              umma_commit(smem_u32(&bars.xempty[sx]));
-              if (kb == 5) umma_commit(smem_u32(&bars.h_ready[t]));
+          for (int st = 0; st < 12; ++st) {
+            const int kb = kL0StepKb[st], t = kL0StepT[st];
+            if (t >= nt) continue;
+            if (t == 0) {                                  // tile 0 is the first user of every weight slab
+              const long long w0 = CN_TRACE_CLOCK_IF(true);
+              sw[kb] = next_slot();
+              tw_w += CN_TRACE_CLOCK_IF(true) - w0;
             }
-            umma_commit(smem_u32(&bars.empty[sw]));
+            const uint64_t dw = umma_desc(slot_addr(sw[kb]), kKmajLbo, kSboBytes);
+            const long long x0 = CN_TRACE_CLOCK_IF(true);
+            const uint32_t sx = next_x_slot();
+            const uint64_t dx = umma_desc(s_base + L::kXRing + sx * CN_SLAB_BYTES, kKmajLbo, kSboBytes);
+            tw_x += CN_TRACE_CLOCK_IF(true) - x0;
+            tc_fence_after();
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              umma_f16(tmem + t * 256 + col_h, dx + j * kKmajKstepEnc, dw + j * kKmajKstepEnc, idesc, (kb | j) ? 1u : 0u);
+            umma_commit(smem_u32(&bars.xempty[sx]));
+            if (kb == 5) umma_commit(smem_u32(&bars.h_ready[t]));
+            if (t == nt - 1) umma_commit(smem_u32(&bars.empty[sw[kb]]));   // last user of this weight slab
           }
           CN_TRACE_AT(pi, 1);
+#ifdef CN_TRACE_FINE
           CN_TRACE_VAL(pi, 30, tw_w);
           CN_TRACE_VAL(pi, 31, tw_x);
+#endif
         }
         for (int blk = 0; blk < kNumBlk; ++blk) {
           for (int j = 0; j < 2; ++j) {
@@ -348,6 +361,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
               tc_fence_after();
               if (blk == 0 && j == 0 && t == 0) CN_TRACE_AT(pi, 2);
               if (blk == kNumBlk - 1 && j == 1 && t == 1) CN_TRACE_AT(pi, 3);
+              if (blk == 1 && t == 0) CN_TRACE_AT(pi, j ? 30 : 4);      // one steady-state layer of tile 0, end to end
               if (j == 0) {
                 gemm_act(t, tmem + t * 256 + col_tmp, s0, s1, false);
                 umma_commit(smem_u32(&bars.tmp_ready[t]));
@@ -355,6 +369,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
                 gemm_act(t, tmem + t * 256 + col_h, s0, s1, true);
                 umma_commit(smem_u32(&bars.h_ready[t]));
               }
+              if (blk == 1 && t == 0) CN_TRACE_AT(pi, j ? 31 : 5);
             }
             umma_commit(smem_u32(&bars.empty[s0]));
             umma_commit(smem_u32(&bars.empty[s1]));
@@ -408,6 +423,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
 
     int64_t pi = 0;
     const bool tr = threadIdx.x == 64;
+    const bool tr1 = threadIdx.x == 64 + kEpiThreads;   // the same lane of tile slot 1 (coarse milestones only)
     for (int64_t p = blockIdx.x; p < n_pairs; p += gridDim.x, ++pi) {
       const int64_t tile = 2 * p + t;
       if (tile >= n_tiles) break;
@@ -541,18 +557,22 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         tc_fence_after();
         long long c2 = CN_TRACE_CLOCK_IF(tr);
         if (tr && blk == 0) CN_TRACE_AT(pi, 10);
+        if (tr && blk == 1 && tb == tab) CN_TRACE_AT(pi, 6);
         acquire();
         epi_tmem_to_act<true>(t_tmp, tb + (2 * blk + 1) * 128, act, row, half, nullptr, nullptr,
                               smask ? smask + (n_acts + blk) * CN_ACT_TILE_BYTES : nullptr);
+        if (tr && blk == 1 && tb == tab) CN_TRACE_AT(pi, 28);
         const long long p1 = CN_TRACE_CLOCK_IF(tr);
         publish((save_hidden && sacts) ? sacts + (n_acts + blk) * CN_ACT_TILE_BYTES : nullptr, true);
         tr_pub += CN_TRACE_CLOCK_IF(tr) - p1;
+        if (tr && blk == 1 && tb == tab) CN_TRACE_AT(pi, 29);
         if (tr && blk == 0) CN_TRACE_AT(pi, 11);
         long long c3 = CN_TRACE_CLOCK_IF(tr);
         mbar_wait(smem_u32(&bars.h_ready[t]), n_h & 1u);
         ++n_h;
         tc_fence_after();
         if (tr && blk == 0) CN_TRACE_AT(pi, 12);
+        if (tr && blk == 1 && tb == tab) CN_TRACE_AT(pi, 7);
         long long c4 = CN_TRACE_CLOCK_IF(tr);
         tr_epi += (c1 - c0) + (c3 - c2);
         tr_wait_tmp += c2 - c1;
@@ -619,6 +639,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
 
       for (int blk = 0; blk < 3; ++blk) run_block(blk, kFusion && blk == 0, tab, my_acts, kActsPerTile, my_mask, kFusion);
       if (tr) CN_TRACE_AT(pi, 13);
+      if (tr1) CN_TRACE_AT(pi, 18);
 
       acquire();
       if (kFusion) {
@@ -679,6 +700,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         readout(tabu, my_acts_u);
       }
       if (tr) CN_TRACE_AT(pi, 14);
+      if (tr1) CN_TRACE_AT(pi, 23);
       if (tr) {
         CN_TRACE_VAL(pi, 24, tr_epi);
         CN_TRACE_VAL(pi, 25, tr_wait_tmp);

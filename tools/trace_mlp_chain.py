@@ -15,8 +15,9 @@ packed = ops.pack_weights(params)
 x = (torch.randn(nt * 128 * 384, generator=g)).to(torch.bfloat16).to(dev).view(torch.uint8)
 names = {0: 'MMA pair start', 1: 'MMA L0 issued', 2: 'MMA blk0 Wa t0 issue', 3: 'MMA last blk Wb t1 issue', 8: 'EPI h0 ready',
          9: 'EPI Ea(blk0) published', 10: 'EPI tmp ready (blk0)', 11: 'EPI Eb(blk0) published', 12: 'EPI h ready (blk0)',
-         4: 'MMA L0 kb0 t0 issue', 5: 'MMA L0 kb1 t0 issue', 6: 'MMA L0 kb2 t0 issue', 7: 'MMA L0 kb3 t0 issue',
-         28: 'MMA L0 kb4 t0 issue', 29: 'MMA L0 kb5 t0 issue', 13: 'EPI per-view blocks done', 14: 'EPI readout done', 20: 'XPROD first X load', 21: 'PROD last L0 weight load',
+         4: '  blk1 t0: MMA woke on act_ready (Wa)', 5: '  blk1 t0: MMA Wa issued + committed', 6: '  blk1 t0: EPI woke on tmp_ready',
+         28: '  blk1 t0: EPI E_b stores done', 29: '  blk1 t0: EPI E_b published', 30: '  blk1 t0: MMA woke on act_ready (Wb)',
+         31: '  blk1 t0: MMA Wb issued + committed', 7: '  blk1 t0: EPI woke on h_ready', 13: 'EPI per-view blocks done', 18: 'EPI (tile 1) per-view blocks done', 23: 'EPI (tile 1) readout done', 14: 'EPI readout done', 20: 'XPROD first X load', 21: 'PROD last L0 weight load',
          22: 'PROD last weight load'}
 for save in (False, True):
     for _ in range(3):
@@ -37,6 +38,7 @@ for save in (False, True):
         print(f'--- pair {it} (cycles relative to MMA pair start; pair period {int(t[it + 1, 0] - t[it, 0])})')
         for c, n in ev:
             print(f'{c:8d}  {n}')
+        if t[it, 31] != 0 and False: pass
         print(f'          MMA thread in the first Dense (CN_TRACE_FINE): {int(t[it, 30])} cycles waiting for weight slabs, {int(t[it, 31])} for X slabs')
         print(f'          traced epilogue thread (tile 0): {int(t[it, 24])} cycles in the block epilogues (of which {int(t[it, 27])} in publish = fence + arrive), '
               f'{int(t[it, 25])} waiting for tmp (6 first Denses), {int(t[it, 26])} waiting for h (6 second Denses)')
