@@ -334,5 +334,9 @@ def test_graph_replayed_training_loop_matches_eager(cuda):
     d_graph = min(dist(graph, e) for e in eager)
     print(f'lr=1e-4: eager-vs-eager loss floor {floor:.3e} (5 runs, 10 pairs), graph loop to the nearest eager run {d_graph:.3e}, '
           f'param diff eager/eager {rel_err(eager[1][1], eager[0][1]):.3e} graph/eager {rel_err(graph[1], eager[0][1]):.3e}')
-    assert d_graph <= 2.0 * floor + 1e-6 * max(eager[0][0]), (d_graph, floor)
+    # The floor of ONE run is itself a sample of ten pairs: on a B200 it came out between 4.9e-4 and 1.7e-3 (absolute, loss
+    # ~0.45) over nine runs of this test, the graph loop's distance between 6e-5 and 1.5e-3 -- once 3x a floor that
+    # happened to be small.  So the bound is the larger of 2x the measured floor and the largest eager-vs-eager spread
+    # seen on this hardware (4e-3 relative); a wrong step counter, bias correction or stale batch is 1e-1 and up.
+    assert d_graph <= max(2.0 * floor, 4e-3 * max(eager[0][0])) + 1e-6 * max(eager[0][0]), (d_graph, floor)
     assert abs(graph[0][0] - eager[0][0][0]) < 1e-5 * eager[0][0][0]          # the first step has no history: equal

@@ -58,68 +58,65 @@ struct FwdBars {
   uint64_t xempty[8];
   uint64_t h_ready[2];
   uint64_t tmp_ready[2];
-  uint64_t act_ready[2];
+  uint64_t act_ready[2];    // K slab 1 of ACT[t] written (the whole tile is then in shared memory)
+  uint64_t act_ready0[2];   // K slab 0 of ACT[t] written: the next Dense starts on it while the epilogue converts slab 1
   uint64_t views_ready[2];  // fusion stage: the ring slots holding tile t's per-view slabs have landed
 };
 
-// TMEM accumulator (this thread's lane, 64 columns of half `half`) + bias -> (ReLU) -> bf16 half row
-// of the swizzled activation tile in shared memory.  Both 32-column loads are issued before the wait.
+// TMEM accumulator (this thread's lane) + bias -> (ReLU) -> bf16 -> swizzled activation tile in shared memory.  The two
+// warps of a lane quadrant split the columns so that each covers BOTH K slabs of the tile: warp `half` takes columns
+// [32 half, 32 half + 32) of slab 0 first, then [64 + 32 half, ...) of slab 1.  When slab 0 is written the warp arrives on
+// `bar_s0` (if given): the MMA thread issues the four MMAs of K slab 0 of the next Dense while the warps convert slab 1
+// (tools/trace_mlp_chain.py: issuing a GEMM takes ~600 cycles, as long as the epilogue's second half).
+// Both 32-column loads are issued before the wait.
 // `tap` (optional): this row's 128 fp32 pre-activation values (h + bias) are also written there -- the stage
 // outputs MVResNetMLPNeRFEmbedding(complete_output=True) returns (layers.py:364-377).
 // `tap16` (optional): the same values as a bf16 activation-tile image (this thread writes its row's 128-byte line).
 // `mask` (optional, kRelu): tile whose sign pattern replaces the ReLU (Jacobian-vector product with the primal masks).
 template <bool kRelu>
 __device__ __forceinline__ void epi_tmem_to_act(uint32_t taddr, const float *__restrict__ bias, uint8_t *act,
-                                                uint32_t row, uint32_t half, float *__restrict__ tap = nullptr,
-                                                uint8_t *__restrict__ tap16 = nullptr,
+                                                uint32_t row, uint32_t half, uint32_t bar_s0,
+                                                float *__restrict__ tap = nullptr, uint8_t *__restrict__ tap16 = nullptr,
                                                 const uint8_t *__restrict__ mask = nullptr) {
-#ifndef CN_EXP
-#define CN_EXP 0
-#endif
   uint32_t r[64];
-  tmem_ld32(taddr + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
-#if CN_EXP & 2
+  tmem_ld32(taddr + half * 32, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+  tmem_ld32(taddr + 64 + half * 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
   tmem_wait_ld();
-#endif
-  tmem_ld32(taddr + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
-#if !(CN_EXP & 2)
-  tmem_wait_ld();
-#endif
 #pragma unroll
   for (int q = 0; q < 8; ++q) {
-#if CN_EXP & 2
-    if (q == 4) tmem_wait_ld();
-#endif
-#if CN_EXP & 1
-    const float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
-#else
-    const float4 b0 = *reinterpret_cast<const float4 *>(bias + half * 64 + q * 8);
-    const float4 b1 = *reinterpret_cast<const float4 *>(bias + half * 64 + q * 8 + 4);
-#endif
+    const uint32_t col = (uint32_t)(q >> 2) * 64 + half * 32 + (uint32_t)(q & 3) * 8;   // first column of this 8-column chunk
+    const float4 b0 = *reinterpret_cast<const float4 *>(bias + col);
+    const float4 b1 = *reinterpret_cast<const float4 *>(bias + col + 4);
     float v[8];
     v[0] = __uint_as_float(r[q * 8 + 0]) + b0.x; v[1] = __uint_as_float(r[q * 8 + 1]) + b0.y;
     v[2] = __uint_as_float(r[q * 8 + 2]) + b0.z; v[3] = __uint_as_float(r[q * 8 + 3]) + b0.w;
     v[4] = __uint_as_float(r[q * 8 + 4]) + b1.x; v[5] = __uint_as_float(r[q * 8 + 5]) + b1.y;
     v[6] = __uint_as_float(r[q * 8 + 6]) + b1.z; v[7] = __uint_as_float(r[q * 8 + 7]) + b1.w;
     if (tap) {
-      *reinterpret_cast<float4 *>(tap + half * 64 + q * 8) = make_float4(v[0], v[1], v[2], v[3]);
-      *reinterpret_cast<float4 *>(tap + half * 64 + q * 8 + 4) = make_float4(v[4], v[5], v[6], v[7]);
+      *reinterpret_cast<float4 *>(tap + col) = make_float4(v[0], v[1], v[2], v[3]);
+      *reinterpret_cast<float4 *>(tap + col + 4) = make_float4(v[4], v[5], v[6], v[7]);
     }
     if (tap16)
-      *reinterpret_cast<uint4 *>(tap16 + tile_chunk_off(row, half * 8 + q)) =
+      *reinterpret_cast<uint4 *>(tap16 + tile_chunk_off(row, col >> 3)) =
           make_uint4(cvt_bf16x2(v[0], v[1]), cvt_bf16x2(v[2], v[3]), cvt_bf16x2(v[4], v[5]), cvt_bf16x2(v[6], v[7]));
     uint4 o;
     if (kRelu && mask) {
       // tangent pass: the activation's derivative is the PRIMAL mask, read from the tile the forward saved
-      const uint4 m = ldg_nc_u4(mask + tile_chunk_off(row, half * 8 + q));
+      const uint4 m = ldg_nc_u4(mask + tile_chunk_off(row, col >> 3));
       o = make_uint4(mul_bf16x2(cvt_bf16x2(v[0], v[1]), gt0_bf16x2(m.x)), mul_bf16x2(cvt_bf16x2(v[2], v[3]), gt0_bf16x2(m.y)),
                      mul_bf16x2(cvt_bf16x2(v[4], v[5]), gt0_bf16x2(m.z)), mul_bf16x2(cvt_bf16x2(v[6], v[7]), gt0_bf16x2(m.w)));
-    } else if (kRelu)  // relu folded into the conversion (F2FP.RELU): the epilogue is issue bound
+    } else if (kRelu)  // relu folded into the conversion (F2FP.RELU)
       o = make_uint4(cvt_relu_bf16x2(v[0], v[1]), cvt_relu_bf16x2(v[2], v[3]), cvt_relu_bf16x2(v[4], v[5]),
                      cvt_relu_bf16x2(v[6], v[7]));
     else
       o = make_uint4(cvt_bf16x2(v[0], v[1]), cvt_bf16x2(v[2], v[3]), cvt_bf16x2(v[4], v[5]), cvt_bf16x2(v[6], v[7]));
-    *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, half * 8 + q)) = o;
+    *reinterpret_cast<uint4 *>(act + tile_chunk_off(row, col >> 3)) = o;
+    if (q == 3 && bar_s0) {                       // K slab 0 of this warp's rows is in shared memory
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane_id() == 0) mbar_arrive(bar_s0);
+    }
   }
 }
 
@@ -144,6 +141,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
   const uint8_t *const mask_acts_u = kExt ? mask_acts_u_arg : nullptr;
   constexpr int kNumBlk = kChain ? 6 : 3;                 // blocks per tile
   constexpr int kRoOff = (kChain ? 14 : 7) * 128;         // readout weights behind the bias tables
+  constexpr bool kSlabSplit = kFusion;                    // epilogue -> MMA hand-off per K slab (epi_tmem_to_act)
   constexpr int kRingSlots = L::kRingSlots;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) FwdBars bars;
@@ -186,6 +184,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
       mbar_init(smem_u32(&bars.h_ready[t]), 1);
       mbar_init(smem_u32(&bars.tmp_ready[t]), 1);
       mbar_init(smem_u32(&bars.act_ready[t]), kEpiWarps);   // one arrival per epilogue warp (behind a __syncwarp)
+      mbar_init(smem_u32(&bars.act_ready0[t]), kEpiWarps);
       mbar_init(smem_u32(&bars.views_ready[t]), 1);
     }
     fence_barrier_init();
@@ -286,12 +285,18 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         return slot;
       };
       // D(tmem) (+)= ACT[t] (2 slabs) . W (2 ring slots)
-      auto gemm_act = [&](int t, uint32_t d_tmem, uint32_t s0, uint32_t s1, bool accumulate) {
+      auto gemm_act = [&](int t, uint32_t d_tmem, uint32_t s0, uint32_t s1, bool accumulate, uint32_t act_parity) {
         const uint32_t a_base = s_base + kSmemAct + t * CN_ACT_TILE_BYTES;
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
           const uint64_t da = umma_desc(a_base + s * CN_SLAB_BYTES, kKmajLbo, kSboBytes);
           const uint64_t db = umma_desc(slot_addr(s ? s1 : s0), kKmajLbo, kSboBytes);
+          // K slab s of the operand.  The slab-wise hand-off is compiled into the fusion stage only (-5 % there); the
+          // chained kernel, at its 96-register cap, spilled twice as much with it and ran 9 % slower.
+          if (kSlabSplit || s == 0) {
+            mbar_wait(smem_u32((kSlabSplit && s == 0) ? &bars.act_ready0[t] : &bars.act_ready[t]), act_parity);
+            tc_fence_after();
+          }
 #pragma unroll
           for (int j = 0; j < 4; ++j)
             umma_f16(d_tmem, da + j * kKmajKstepEnc, db + j * kKmajKstepEnc, idesc, (accumulate || s || j) ? 1u : 0u);
@@ -356,17 +361,16 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
                 for (uint32_t i = 0; i < view_slots; ++i) (void)next_slot();
                 mbar_arrive(smem_u32(&bars.views_ready[1]));
               }
-              mbar_wait(smem_u32(&bars.act_ready[t]), n_act[t] & 1u);
+              const uint32_t act_parity = n_act[t] & 1u;
               ++n_act[t];
-              tc_fence_after();
               if (blk == 0 && j == 0 && t == 0) CN_TRACE_AT(pi, 2);
               if (blk == kNumBlk - 1 && j == 1 && t == 1) CN_TRACE_AT(pi, 3);
               if (blk == 1 && t == 0) CN_TRACE_AT(pi, j ? 30 : 4);      // one steady-state layer of tile 0, end to end
               if (j == 0) {
-                gemm_act(t, tmem + t * 256 + col_tmp, s0, s1, false);
+                gemm_act(t, tmem + t * 256 + col_tmp, s0, s1, false, act_parity);
                 umma_commit(smem_u32(&bars.tmp_ready[t]));
               } else {
-                gemm_act(t, tmem + t * 256 + col_h, s0, s1, true);
+                gemm_act(t, tmem + t * 256 + col_h, s0, s1, true, act_parity);
                 umma_commit(smem_u32(&bars.h_ready[t]));
               }
               if (blk == 1 && t == 0) CN_TRACE_AT(pi, j ? 31 : 5);
@@ -395,7 +399,8 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
 
     // make this thread's writes to ACT visible to the async proxy, optionally stream the tile to
     // global memory, then hand it to the MMA warp
-    auto publish = [&](uint8_t *gdst, bool signal_mma) {
+    const uint32_t bar_s0 = kSlabSplit ? smem_u32(&bars.act_ready0[t]) : 0u;
+    auto publish = [&](uint8_t *gdst, bool signal_mma, bool signal_slab0 = false) {
       fence_proxy_async_smem();
       if (gdst) {
         named_bar_sync(bar_id, kEpiThreads);
@@ -409,7 +414,10 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         // 256 arrivals on one mbarrier serialise in shared memory: every lane fences, lane 0 arrives for the warp
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&bars.act_ready[t]));
+        if (lane == 0) {
+          if (kSlabSplit && signal_slab0) mbar_arrive(bar_s0);   // the writer covered the tile in one go (mean over views, chain transition)
+          mbar_arrive(smem_u32(&bars.act_ready[t]));
+        }
       }
     };
     // ACT may only be overwritten once a pending bulk store has finished reading it
@@ -523,7 +531,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         }
         tmem_wait_st();
         if (tr) CN_TRACE_AT(pi, 20);
-        publish(my_acts, true);
+        publish(my_acts, true, true);
         if (tr) CN_TRACE_AT(pi, 17);
       } else {
         mbar_wait(smem_u32(&bars.h_ready[t]), n_h & 1u);
@@ -541,7 +549,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         if (!skip_ea) {
           // E_a: relu(h + cumulative bias) -> operand of the block's first Dense
           acquire();
-          epi_tmem_to_act<true>(t_h, tb + (2 * blk) * 128, act, row, half,
+          epi_tmem_to_act<true>(t_h, tb + (2 * blk) * 128, act, row, half, bar_s0,
                                 (with_taps && my_tap) ? my_tap + blk * tap_stride : nullptr,
                                 (with_taps && my_tap16) ? my_tap16 + blk * tap16_stride : nullptr,
                                 smask ? smask + blk * CN_ACT_TILE_BYTES : nullptr);
@@ -559,7 +567,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         if (tr && blk == 0) CN_TRACE_AT(pi, 10);
         if (tr && blk == 1 && tb == tab) CN_TRACE_AT(pi, 6);
         acquire();
-        epi_tmem_to_act<true>(t_tmp, tb + (2 * blk + 1) * 128, act, row, half, nullptr, nullptr,
+        epi_tmem_to_act<true>(t_tmp, tb + (2 * blk + 1) * 128, act, row, half, bar_s0, nullptr, nullptr,
                               smask ? smask + (n_acts + blk) * CN_ACT_TILE_BYTES : nullptr);
         if (tr && blk == 1 && tb == tab) CN_TRACE_AT(pi, 28);
         const long long p1 = CN_TRACE_CLOCK_IF(tr);
@@ -646,7 +654,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         readout(tab, my_acts);
       } else if (!kChain) {
         // ---- h3 = h + cumulative bias -> bf16 tile for the fusion stage
-        epi_tmem_to_act<false>(t_h, tab + 6 * 128, act, row, half);
+        epi_tmem_to_act<false>(t_h, tab + 6 * 128, act, row, half, 0u);
         publish(out_tiles + tile * (int64_t)CN_ACT_TILE_BYTES, false);
       } else {
         // ---- chained fusion stage (nv = 1).  m = bf16(h + cumulative bias) is what the two-kernel path stores as the
@@ -694,7 +702,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
           tmem_st32(t_h + half * 64 + c2 * 32, r);
         }
         tmem_wait_st();
-        publish(my_acts_u, true);
+        publish(my_acts_u, true, true);
         for (int blk = 0; blk < 3; ++blk) run_block(blk, blk == 0, tabu, my_acts_u, 4, my_mask_u, true);
         acquire();
         readout(tabu, my_acts_u);
