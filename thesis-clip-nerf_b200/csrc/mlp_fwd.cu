@@ -18,6 +18,11 @@
 // The second GEMM of every block accumulates straight into `h`, so the residual add is free and
 // the stream stays fp32; Dense biases of the residual branch are applied as cumulative bias
 // vectors when `h` is read (tables built by cn_pack_weights).
+// Scheduling (tools/trace_mlp_chain.py): a layer of one tile is a serial chain -- 8 MMAs issued
+// (~600 cycles), epilogue wake-up (~250), conversion (~750), publish + MMA wake-up (~350) -- so the pair advances one layer
+// per ~2 000 cycles.  Three things shorten or hide parts of it: the two accumulators of a tile swap roles every pair
+// (the first Dense of the next pair runs under this pair's readout), the first Dense staggers the two tiles by two K
+// blocks (their epilogues alternate), and in the fusion stage the operand tile is handed over per K slab.
 #include "common.cuh"
 #include "mlp_layout.cuh"
 
