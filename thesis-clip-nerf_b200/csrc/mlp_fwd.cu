@@ -61,7 +61,10 @@ struct FwdBars {
   uint64_t empty[8];
   uint64_t xfull[8];
   uint64_t xempty[8];
-  uint64_t h_ready[2];
+  uint64_t h_ready[2];      // second Dense of a block committed (residual stream updated)
+  uint64_t h0_ready[2];     // first Dense of the pair committed.  Its own barrier: it is issued right behind the last block GEMM
+                            // of the previous pair (no epilogue step in between), and two completions of ONE barrier that
+                            // the waiter has not observed in between would alias its phase parity
   uint64_t tmp_ready[2];
   uint64_t act_ready[2];    // K slab 1 of ACT[t] written (the whole tile is then in shared memory)
   uint64_t act_ready0[2];   // K slab 0 of ACT[t] written: the next Dense starts on it while the epilogue converts slab 1
@@ -187,6 +190,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
     }
     for (int t = 0; t < 2; ++t) {
       mbar_init(smem_u32(&bars.h_ready[t]), 1);
+      mbar_init(smem_u32(&bars.h0_ready[t]), 1);
       mbar_init(smem_u32(&bars.tmp_ready[t]), 1);
       mbar_init(smem_u32(&bars.act_ready[t]), kEpiWarps);   // one arrival per epilogue warp (behind a __syncwarp)
       mbar_init(smem_u32(&bars.act_ready0[t]), kEpiWarps);
@@ -341,7 +345,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
             for (int j = 0; j < 4; ++j)
               umma_f16(tmem + t * 256 + col_h, dx + j * kKmajKstepEnc, dw + j * kKmajKstepEnc, idesc, (kb | j) ? 1u : 0u);
             umma_commit(smem_u32(&bars.xempty[sx]));
-            if (kb == 5) umma_commit(smem_u32(&bars.h_ready[t]));
+            if (kb == 5) umma_commit(smem_u32(&bars.h0_ready[t]));
             if (t == nt - 1) umma_commit(smem_u32(&bars.empty[sw[kb]]));   // last user of this weight slab
           }
           CN_TRACE_AT(pi, 1);
@@ -539,8 +543,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         publish(my_acts, true, true);
         if (tr) CN_TRACE_AT(pi, 17);
       } else {
-        mbar_wait(smem_u32(&bars.h_ready[t]), n_h & 1u);
-        ++n_h;
+        mbar_wait(smem_u32(&bars.h0_ready[t]), (uint32_t)pi & 1u);     // one completion per pair
         tc_fence_after();
         if (tr) CN_TRACE_AT(pi, 8);
       }
