@@ -238,7 +238,7 @@ def test_stage_backward_matches_the_block_by_block_chain(cuda, nv, rows):
     assert none is None and rel_err(grad_d, grad_a) < 2e-5
 
 
-@pytest.mark.parametrize('n_tiles', [2, 5, 301])
+@pytest.mark.parametrize('n_tiles', [1, 2, 5, 301, 889])   # one tile; odd tails; 3 pairs per CTA + a half pair (accumulator roles alternate per pair)
 def test_chained_single_view_forward_is_the_two_kernel_path_bit_for_bit(cuda, n_tiles):
     """cn_mlp_chain_fwd (nv = 1: per-view stage + fusion stage + readout in one launch) against cn_mlp_feature_fwd +
     cn_mlp_fusion_fwd_taps: rgb / sigma, all seven saved activation tiles (ten with the hidden ones), the four taps as
