@@ -81,17 +81,23 @@ struct FwdBars {
 // outputs MVResNetMLPNeRFEmbedding(complete_output=True) returns (layers.py:364-377).
 // `tap16` (optional): the same values as a bf16 activation-tile image (this thread writes its row's 128-byte line).
 // `mask` (optional, kRelu): tile whose sign pattern replaces the ReLU (Jacobian-vector product with the primal masks).
-template <bool kRelu>
+// kPhased: the 32 columns of slab 1 are loaded from TMEM only after slab 0 has been converted and signalled -- half the
+// live registers (the kernels sit at their 96-register cap), the second load's latency hides under the MMAs just released.
+template <bool kRelu, bool kPhased = false>
 __device__ __forceinline__ void epi_tmem_to_act(uint32_t taddr, const float *__restrict__ bias, uint8_t *act,
                                                 uint32_t row, uint32_t half, uint32_t bar_s0,
                                                 float *__restrict__ tap = nullptr, uint8_t *__restrict__ tap16 = nullptr,
                                                 const uint8_t *__restrict__ mask = nullptr) {
   uint32_t r[64];
   tmem_ld32(taddr + half * 32, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
-  tmem_ld32(taddr + 64 + half * 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+  if (!kPhased) tmem_ld32(taddr + 64 + half * 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
   tmem_wait_ld();
 #pragma unroll
   for (int q = 0; q < 8; ++q) {
+    if (kPhased && q == 4) {
+      tmem_ld32(taddr + 64 + half * 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+      tmem_wait_ld();
+    }
     const uint32_t col = (uint32_t)(q >> 2) * 64 + half * 32 + (uint32_t)(q & 3) * 8;   // first column of this 8-column chunk
     const float4 b0 = *reinterpret_cast<const float4 *>(bias + col);
     const float4 b1 = *reinterpret_cast<const float4 *>(bias + col + 4);
@@ -149,7 +155,12 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
   const uint8_t *const mask_acts_u = kExt ? mask_acts_u_arg : nullptr;
   constexpr int kNumBlk = kChain ? 6 : 3;                 // blocks per tile
   constexpr int kRoOff = (kChain ? 14 : 7) * 128;         // readout weights behind the bias tables
-  constexpr bool kSlabSplit = kFusion;                    // epilogue -> MMA hand-off per K slab (epi_tmem_to_act)
+  // Epilogue -> MMA hand-off per K slab (epi_tmem_to_act), with the TMEM loads phased: fusion stage only.  Measured on the
+  // per-view and chained kernels too (tools/bench_mlp_fwd.py): with phased loads they no longer spill more, but the
+  // chained kernel without saves still ran 2.5 % slower and the per-view stage 4 % slower (their tiles are already
+  // staggered by the first Dense), the fusion stage 5 ... 9 % faster.
+  constexpr bool kSlabSplit = kFusion;
+  constexpr bool kPhased = kFusion;
   constexpr int kRingSlots = L::kRingSlots;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) FwdBars bars;
@@ -557,7 +568,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         if (!skip_ea) {
           // E_a: relu(h + cumulative bias) -> operand of the block's first Dense
           acquire();
-          epi_tmem_to_act<true>(t_h, tb + (2 * blk) * 128, act, row, half, bar_s0,
+          epi_tmem_to_act<true, kPhased>(t_h, tb + (2 * blk) * 128, act, row, half, bar_s0,
                                 (with_taps && my_tap) ? my_tap + blk * tap_stride : nullptr,
                                 (with_taps && my_tap16) ? my_tap16 + blk * tap16_stride : nullptr,
                                 smask ? smask + blk * CN_ACT_TILE_BYTES : nullptr);
@@ -575,7 +586,7 @@ mlp_fwd_kernel(const uint8_t *__restrict__ packed, const uint8_t *__restrict__ i
         if (tr && blk == 0) CN_TRACE_AT(pi, 10);
         if (tr && blk == 1 && tb == tab) CN_TRACE_AT(pi, 6);
         acquire();
-        epi_tmem_to_act<true>(t_tmp, tb + (2 * blk + 1) * 128, act, row, half, bar_s0, nullptr, nullptr,
+        epi_tmem_to_act<true, kPhased>(t_tmp, tb + (2 * blk + 1) * 128, act, row, half, bar_s0, nullptr, nullptr,
                               smask ? smask + (n_acts + blk) * CN_ACT_TILE_BYTES : nullptr);
         if (tr && blk == 1 && tb == tab) CN_TRACE_AT(pi, 28);
         const long long p1 = CN_TRACE_CLOCK_IF(tr);
