@@ -366,12 +366,30 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
         if (kWgrad) wgrad(t_dwb, kBwSmemA2, gy, it == 0);         // WB: dWb += A2^T g_y
         umma_commit(smem_u32(&bars.g2wb_done));
         CN_TRACE_AT(it, 3);
+        // T of the next tile goes out behind WB, into the ~1 000 cycles the tensor pipe idles while E1 runs -- if its
+        // A1 has landed by then.  E2 releases the A1 buffer before it waits for G1 (below), so the buffer is free as soon
+        // as WA has read it and the load of tile it+2 lands ~1 000 ... 1 500 cycles into tile it+1: in time.  A T that
+        // misses the window is issued after WA (not before it: a late WA releases A1 late, and the next load is late
+        // again -- tools/trace_block_bwd.py showed that state sustaining itself).  The test is repeated for a bounded
+        // time only: a T that starts late in E1 would hold up G1, which the epilogue is waiting for.  Measured
+        // (tools/bench_block_bwd.py, one box, per-view / fusion blocks of cfg2): no polling 292.9 / 114.7 us, 300 cycles
+        // 289.8 / 112.7, 600 -2.9 / -3.7 %, 900 -3.6 / -3.7 %, 1 200 and "until gt_ready" slower than 900 again.
+#ifndef CN_BWD_POLL_CYCLES
+#define CN_BWD_POLL_CYCLES 900
+#endif
         bool next_issued = false;
-        if (has_next && mbar_try_wait(smem_u32(&bars.full_a1[nb]), nph2)) {
-          tc_fence_after();
-          gemm_t(kBwSmemA1 + nb * CN_ACT_TILE_BYTES);             // T of the next tile, behind WB
-          umma_commit(smem_u32(&bars.t_ready));
-          next_issued = true;
+        auto try_next_t = [&]() {
+          if (has_next && !next_issued && mbar_try_wait(smem_u32(&bars.full_a1[nb]), nph2)) {
+            tc_fence_after();
+            gemm_t(kBwSmemA1 + nb * CN_ACT_TILE_BYTES);
+            umma_commit(smem_u32(&bars.t_ready));
+            next_issued = true;
+          }
+        };
+        try_next_t();
+        if (CN_BWD_POLL_CYCLES > 0 && has_next && !next_issued) {
+          const long long c0 = clock64();
+          while (!next_issued && clock64() - c0 < CN_BWD_POLL_CYCLES) try_next_t();
         }
         CN_TRACE_AT(it, 4);
         mbar_wait(smem_u32(&bars.gt_ready), par);
@@ -418,7 +436,9 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
         link_release(A.in, cta + it * (int64_t)n_cta);
       }
       // ---- E0: A2 = relu(t + ba) -> bf16 operand tile
+      if (threadIdx.x == 64) CN_TRACE_AT(it, 18);
       mbar_wait(smem_u32(&bars.t_ready), par);
+      if (threadIdx.x == 64) CN_TRACE_AT(it, 19);
       mbar_wait(smem_u32(&bars.a2buf_free), par ^ 1u);  // WA of the previous tile is done with g_t
       tc_fence_after();
       if (threadIdx.x == 64) CN_TRACE_AT(it, 8);
@@ -484,15 +504,20 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
         for (int j = 0; j < 16; ++j) t16[j] = gw[j];
         dbb += colsum_bf16x2(t16, lane);
       }
+      // the ReLU mask of E2 comes from A1: its chunks are taken into registers NOW, and the buffer is released as far as
+      // the epilogue is concerned -- it is then free as soon as WA has read it, ~1 300 cycles before the end of E2, and the
+      // A1 of tile it+2 lands in time for T to be issued while E1 of tile it+1 runs (tools/trace_block_bwd.py)
+      uint4 a[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) a[q] = *reinterpret_cast<const uint4 *>(a1buf + choff[q]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&bars.free_a1[b]));
       mbar_wait(smem_u32(&bars.g1_ready), par);
       tc_fence_after();
       if (threadIdx.x == 64) CN_TRACE_AT(it, 15);
       {
         uint32_t r[32];
         tmem_ld32(t_acc1 + lane_off + cq * 32, r);
-        uint4 a[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) a[q] = *reinterpret_cast<const uint4 *>(a1buf + choff[q]);
         tmem_wait_ld();
         tc_fence_before();
         __syncwarp();
@@ -508,11 +533,8 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
         }
       }
       fence_proxy_async_smem();
-      __syncwarp();                                  // every lane has consumed its A1 chunks and written g_h
-      if (lane == 0) {
-        mbar_arrive(smem_u32(&bars.free_a1[b]));
-        mbar_arrive(smem_u32(&bars.gy_staged[b]));
-      }
+      __syncwarp();                                  // every lane has written g_h
+      if (lane == 0) mbar_arrive(smem_u32(&bars.gy_staged[b]));
       if (threadIdx.x == 64) CN_TRACE_AT(it, 17);
     }
     // ---- flush the weight gradients held in TMEM (each thread: its input unit, 32 output units)
