@@ -131,6 +131,7 @@ struct BwdBars {
   uint64_t free_a1[2];                 // E2 warps + commit behind WA
   uint64_t gy_staged[2];               // E2 warps: g_h has replaced g_y in its buffer (G2 / WB are behind G1: done)
   uint64_t t_ready, g2wb_done, g1_ready;  // commits
+  uint64_t g2_ready;                   // commit behind G2 alone: E1 loads and masks g_a2 while WB is still reading A2
   uint64_t a2_ready, gt_ready;         // epilogue warps
   uint64_t a2buf_free;                 // commit behind WA
   uint64_t acc1_free;                  // E2 warps
@@ -221,6 +222,7 @@ __device__ __forceinline__ void block_bwd_init_barriers(BwdBars &bars) {
   }
   mbar_init(smem_u32(&bars.t_ready), 1);
   mbar_init(smem_u32(&bars.g2wb_done), 1);
+  mbar_init(smem_u32(&bars.g2_ready), 1);
   mbar_init(smem_u32(&bars.g1_ready), 1);
   mbar_init(smem_u32(&bars.a2_ready), kBwdEpiWarps);
   mbar_init(smem_u32(&bars.gt_ready), kBwdEpiWarps);
@@ -359,6 +361,7 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
         tc_fence_after();
         CN_TRACE_AT(it, 0);
         gemm_kk(t_acc1, gy, kBwSmemWb);                           // G2: g_a2 = g_y Wb^T
+        umma_commit(smem_u32(&bars.g2_ready));
         CN_TRACE_AT(it, 1);
         mbar_wait(smem_u32(&bars.a2_ready), par);                 // (also: E0 has drained acc0)
         tc_fence_after();
@@ -373,7 +376,9 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
         // again -- tools/trace_block_bwd.py showed that state sustaining itself).  The test is repeated for a bounded
         // time only: a T that starts late in E1 would hold up G1, which the epilogue is waiting for.  Measured
         // (tools/bench_block_bwd.py, one box, per-view / fusion blocks of cfg2): no polling 292.9 / 114.7 us, 300 cycles
-        // 289.8 / 112.7, 600 -2.9 / -3.7 %, 900 -3.6 / -3.7 %, 1 200 and "until gt_ready" slower than 900 again.
+        // 289.8 / 112.7, 600 -2.9 / -3.7 %, 900 -3.6 / -3.7 %, 1 200 and "until gt_ready" slower than 900 again.  With E1
+        // loading g_a2 before WB is done (below) the order is the same: 0 / 300 / 600 / 900 cycles = 297.0 / 283.5 /
+        // 282.7 / 280.6 us (per-view blocks; until gt_ready = 280.6).
 #ifndef CN_BWD_POLL_CYCLES
 #define CN_BWD_POLL_CYCLES 900
 #endif
@@ -463,8 +468,9 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&bars.a2_ready));
       if (threadIdx.x == 64) CN_TRACE_AT(it, 11);
-      // ---- E1: g_t = g_a2 * [A2 > 0], over A2 (WB has finished reading it); dba += colsum(g_t)
-      mbar_wait(smem_u32(&bars.g2wb_done), par);
+      // ---- E1: g_t = g_a2 * [A2 > 0], over A2; dba += colsum(g_t).  Only the STORES wait for WB (it reads A2): g_a2 is
+      // loaded and masked as soon as G2 alone has completed, while the MMA thread is still issuing WB
+      mbar_wait(smem_u32(&bars.g2_ready), par);
       tc_fence_after();
       if (threadIdx.x == 64) CN_TRACE_AT(it, 12);
       {
@@ -474,11 +480,13 @@ __device__ __forceinline__ void block_bwd_role(const BlockBwdArgs &A, BwdBars &b
 #pragma unroll
         for (int j = 0; j < 16; ++j)
           a2w[j] = mul_bf16x2(cvt_bf16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1])), gt0_bf16x2(a2w[j]));
-#pragma unroll
-        for (int q = 0; q < 4; ++q)
-          *reinterpret_cast<uint4 *>(a2buf + choff[q]) =
-              make_uint4(a2w[q * 4 + 0], a2w[q * 4 + 1], a2w[q * 4 + 2], a2w[q * 4 + 3]);
       }
+      mbar_wait(smem_u32(&bars.g2wb_done), par);      // WB has finished reading A2
+      if (threadIdx.x == 64) CN_TRACE_AT(it, 13);
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        *reinterpret_cast<uint4 *>(a2buf + choff[q]) =
+            make_uint4(a2w[q * 4 + 0], a2w[q * 4 + 1], a2w[q * 4 + 2], a2w[q * 4 + 3]);
       fence_proxy_async_smem();
       tc_fence_before();
       __syncwarp();

@@ -22,7 +22,7 @@ rc = lib.cn_debug_read_trace(buf, 1024)
 t = np.array(buf[:], dtype=np.int64).reshape(32, 32)
 names = {0: 'MMA G2 issue', 1: 'MMA G2 issued', 2: 'MMA WB issue (a2_ready seen)', 3: 'MMA WB issued+commit', 4: 'MMA T(next) done/skip',
          5: 'MMA gt_ready seen', 6: 'MMA G1 issued+commit', 7: 'MMA WA issued', 8: 'E0 start', 9: 'E0 tmem loaded', 10: 'E0 stored',
-         11: 'E0 arrived', 12: 'E1 start', 14: 'E1 arrived', 15: 'E2 start', 17: 'E2 arrived', 18: 'EPI loop top (before the t_ready wait)', 19: 'EPI t_ready seen (before the a2buf_free wait)', 20: 'biasGy start', 21: 'biasGy end',
+         11: 'E0 arrived', 12: 'E1 start (G2 done)', 13: 'E1 WB done seen (stores may start)', 14: 'E1 arrived', 15: 'E2 start', 17: 'E2 arrived', 18: 'EPI loop top (before the t_ready wait)', 19: 'EPI t_ready seen (before the a2buf_free wait)', 20: 'biasGy start', 21: 'biasGy end',
          22: 'biasGt start', 23: 'biasGt end', 24: 'PROD gy_staged seen', 25: 'PROD gy reload issued', 26: 'PROD free_a1 seen'}
 for it in (10, 11):
     base = t[it, 8]
