@@ -153,7 +153,8 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 // The %globaltimer read in every failed poll doubles as the back-off of the wait.  Measured alternatives (round 2): reading
 // the clock only every 4096th poll (tight polling) made the MLP kernels 5 ... 13 % SLOWER -- sixteen polling warps take
 // issue slots and shared-memory bandwidth from the MMA thread and the working epilogue warps; try_wait with a 2 us
-// suspend-time hint was no faster than this loop either.
+// suspend-time hint was no faster than this loop either; and 48 quick polls before this loop for the ONE MMA-issuing
+// thread alone (its first poll often fails by a few cycles) made cn_mlp_block_bwd 2 % slower.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const uint64_t t0 = globaltimer_ns();
